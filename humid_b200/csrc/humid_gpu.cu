@@ -1,0 +1,361 @@
+// C ABI of libhumid_gpu (include/humid_gpu.h): handle management, argument checks, stage
+// sequencing and timing.  All compute lives in the stage_* launchers (CUDA kernels); there is
+// deliberately no host implementation of any stage — without a CUDA device every call fails.
+#include <cstring>
+#include <functional>
+
+#include "state.cuh"
+
+using namespace humid;
+
+struct humid_gpu {
+  State s;
+};
+
+static thread_local std::string g_create_error;
+
+static int fail(humid_gpu *h, int code, const std::string &msg) {
+  if (h) h->s.last_error = msg; else g_create_error = msg;
+  return code;
+}
+
+// Runs `body`, mapping C++ failures onto the C error codes.
+static int guarded(humid_gpu *h, const std::function<void()> &body) {
+  try {
+    body();
+    return HUMID_GPU_OK;
+  } catch (const CudaError &e) {
+    bool oom = e.msg.find("out of memory") != std::string::npos;
+    return fail(h, oom ? HUMID_GPU_ERR_MEMORY : HUMID_GPU_ERR_CUDA, e.msg);
+  } catch (const std::bad_alloc &) {
+    return fail(h, HUMID_GPU_ERR_MEMORY, "host allocation failed");
+  } catch (const std::exception &e) {
+    return fail(h, HUMID_GPU_ERR_CUDA, e.what());
+  }
+}
+
+static void timed_stage(State &s, const char *name, uint64_t units, uint64_t bytes_per_unit,
+                        const std::function<int()> &run) {
+  StageStat st;
+  st.name = name;
+  HUMID_CUDA(cudaEventCreate(&st.e0));
+  HUMID_CUDA(cudaEventCreate(&st.e1));
+  HUMID_CUDA(cudaEventRecord(st.e0, s.stream));
+  st.launches = (uint32_t)run();
+  HUMID_CUDA(cudaEventRecord(st.e1, s.stream));
+  st.units = units;
+  st.algo_bytes = units * bytes_per_unit;
+  s.stats.push_back(st);
+}
+
+static void resolve_stats(State &s) {
+  for (auto &st : s.stats) {
+    if (!st.e0) continue;
+    HUMID_CUDA(cudaEventSynchronize(st.e1));
+    HUMID_CUDA(cudaEventElapsedTime(&st.ms, st.e0, st.e1));
+    cudaEventDestroy(st.e0);
+    cudaEventDestroy(st.e1);
+    st.e0 = st.e1 = nullptr;
+  }
+}
+
+static void clear_stats(State &s) {
+  for (auto &st : s.stats) {
+    if (st.e0) cudaEventDestroy(st.e0);
+    if (st.e1) cudaEventDestroy(st.e1);
+  }
+  s.stats.clear();
+}
+
+extern "C" {
+
+int humid_gpu_abi_version(void) { return HUMID_GPU_ABI_VERSION; }
+
+const char *humid_gpu_last_error(const humid_gpu *h) { return h ? h->s.last_error.c_str() : g_create_error.c_str(); }
+
+int humid_gpu_create(const humid_gpu_config *cfg, humid_gpu **out) {
+  if (!cfg || !out) return fail(nullptr, HUMID_GPU_ERR_ARG, "humid_gpu_create: null argument");
+  *out = nullptr;
+  if (cfg->word_length == 0 || cfg->word_length > HUMID_MAX_WORD_LENGTH)
+    return fail(nullptr, HUMID_GPU_ERR_UNSUPPORTED,
+                "word length must be 1.." + std::to_string(HUMID_MAX_WORD_LENGTH) + " (one 64-bit key per word)");
+  if (cfg->n_segments == 0 || cfg->n_segments > HUMID_MAX_SEGMENTS)
+    return fail(nullptr, HUMID_GPU_ERR_ARG, "n_segments out of range");
+  uint64_t sum = 0;
+  for (uint32_t i = 0; i < cfg->n_segments; i++) sum += cfg->seg_take[i];
+  if (sum != cfg->word_length) return fail(nullptr, HUMID_GPU_ERR_ARG, "seg_take must sum to word_length");
+  humid_gpu *h = new (std::nothrow) humid_gpu();
+  if (!h) return fail(nullptr, HUMID_GPU_ERR_MEMORY, "host allocation failed");
+  h->s.cfg = *cfg;
+  int rc = guarded(h, [&] {
+    State &s = h->s;
+    int count = 0;
+    HUMID_CUDA(cudaGetDeviceCount(&count));
+    if (count == 0) throw CudaError{"no CUDA device (there is no CPU fallback)"};
+    if (cfg->device >= 0) HUMID_CUDA(cudaSetDevice(cfg->device));
+    HUMID_CUDA(cudaGetDevice(&s.device));
+    HUMID_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    s.counters.ensure(16);
+    HUMID_CUDA(cudaMemsetAsync(s.counters.p, 0, 16 * sizeof(unsigned long long), s.stream));
+    if (cfg->expected_tuples) s.tuple_key.ensure(cfg->expected_tuples);
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+  });
+  if (rc != HUMID_GPU_OK) {
+    g_create_error = h->s.last_error;
+    delete h;
+    return rc;
+  }
+  *out = h;
+  return HUMID_GPU_OK;
+}
+
+void humid_gpu_destroy(humid_gpu *h) {
+  if (!h) return;
+  State &s = h->s;
+  cudaSetDevice(s.device);
+  if (s.stream) cudaStreamSynchronize(s.stream);
+  clear_stats(s);
+  s.tuple_key.release(); s.stage_chars.release(); s.stage_seg_len.release(); s.counters.release();
+  s.slots.release(); s.word_key.release(); s.key_alt.release(); s.word_slot.release(); s.slot_alt.release();
+  s.word_count.release(); s.word_first.release(); s.entries.release(); s.entries_alt.release();
+  s.entry_val.release(); s.entry_val_alt.release(); s.row_ptr.release(); s.col.release();
+  s.comp.release(); s.label.release(); s.members.release(); s.seg_start.release(); s.seg_end.release();
+  s.work_a.release(); s.work_b.release(); s.work_c.release(); s.seed_flag.release(); s.seed_index.release();
+  s.seed_size.release(); s.seed_max.release(); s.cluster_size.release(); s.cluster_max.release();
+  s.keep_bits.release(); s.out_ids.release(); s.scratch.release(); s.scan_scratch.release();
+  if (s.stream) cudaStreamDestroy(s.stream);
+  delete h;
+}
+
+int humid_gpu_reset(humid_gpu *h) {
+  if (!h) return HUMID_GPU_ERR_ARG;
+  return guarded(h, [&] {
+    State &s = h->s;
+    HUMID_CUDA(cudaSetDevice(s.device));
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    clear_stats(s);
+    s.n_tuples = s.usable = s.unique = s.n_entries = s.n_clusters = 0;
+    s.finalized = false;
+    for (int i = 0; i < 3; i++) s.hist_done[i] = false;
+    HUMID_CUDA(cudaMemsetAsync(s.counters.p, 0, 16 * sizeof(unsigned long long), s.stream));
+  });
+}
+
+static int add_batch_impl(humid_gpu *h, const uint8_t *chars, const uint16_t *seg_len, uint64_t first, uint64_t n,
+                          bool on_device) {
+  if (!h) return HUMID_GPU_ERR_ARG;
+  State &s = h->s;
+  if (s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "add_batch after finalize (call humid_gpu_reset first)");
+  if (first != s.n_tuples) return fail(h, HUMID_GPU_ERR_ARG, "batches must be added in input order, without gaps");
+  if (n && !chars) return fail(h, HUMID_GPU_ERR_ARG, "chars is null");
+  if (s.n_tuples + n >= 0xFFFFFFFFull) return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "more than 2^32-2 tuples");
+  if (n == 0) return HUMID_GPU_OK;
+  return guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(s.device));
+    const uint32_t wl = s.cfg.word_length, ns = s.cfg.n_segments;
+    s.tuple_key.grow(s.n_tuples + n, s.n_tuples, s.stream);
+    const uint8_t *d_chars = chars;
+    const uint16_t *d_len = seg_len;
+    if (!on_device) {
+      s.stage_chars.ensure(n * wl);
+      HUMID_CUDA(cudaMemcpyAsync(s.stage_chars.p, chars, n * wl, cudaMemcpyHostToDevice, s.stream));
+      d_chars = s.stage_chars.p;
+      if (seg_len) {
+        s.stage_seg_len.ensure(n * ns);
+        HUMID_CUDA(cudaMemcpyAsync(s.stage_seg_len.p, seg_len, n * ns * sizeof(uint16_t), cudaMemcpyHostToDevice,
+                                   s.stream));
+        d_len = s.stage_seg_len.p;
+      }
+    }
+    // makeWord: n ASCII bytes in, one 8-byte key out
+    timed_stage(s, "pack", n, wl + 8, [&] { return stage_pack(s, d_chars, d_len, first, n); });
+    s.n_tuples += n;
+    if (!on_device) HUMID_CUDA(cudaStreamSynchronize(s.stream));  // the caller may reuse its buffers
+  });
+}
+
+int humid_gpu_add_batch(humid_gpu *h, const uint8_t *chars, const uint16_t *seg_len, uint64_t first_tuple_index,
+                        uint64_t n_tuples) {
+  return add_batch_impl(h, chars, seg_len, first_tuple_index, n_tuples, false);
+}
+
+int humid_gpu_add_batch_device(humid_gpu *h, const uint8_t *d_chars, const uint16_t *d_seg_len,
+                               uint64_t first_tuple_index, uint64_t n_tuples) {
+  return add_batch_impl(h, d_chars, d_seg_len, first_tuple_index, n_tuples, true);
+}
+
+int humid_gpu_finalize(humid_gpu *h) {
+  if (!h) return HUMID_GPU_ERR_ARG;
+  State &s = h->s;
+  if (s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "finalize called twice");
+  return guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(s.device));
+    const uint32_t n = s.cfg.word_length;
+    // K1 insert: key in (8) + slot key (8) + count RMW (8) + first RMW (8); K2: keys+slot ids
+    // read and written once (2*(8+4)) + rank columns (4+4+4)
+    timed_stage(s, "table", s.n_tuples, 32, [&] { return stage_build_table(s); });
+    const bool edit2 = s.cfg.edit && s.cfg.distance >= 2;
+    uint64_t probes = 0;  // expected number of probed variants per word (uniform letters)
+    if (!edit2) {
+      double p1 = 1.5 * n, p2 = p1 + 2.25 * n * (n - 1) / 2.0;
+      probes = s.cfg.distance == 0 ? 0 : s.cfg.distance == 1 ? (uint64_t)p1 : (uint64_t)p2;
+    }
+    timed_stage(s, edit2 ? "neigh_edit" : "neigh_hamming", s.unique, 8 * (1 + probes), [&] {
+      return edit2 ? stage_neighbours_edit(s) : stage_neighbours_hamming(s);
+    });
+    timed_stage(s, "csr", s.n_entries, 16, [&] { return stage_csr(s); });
+    timed_stage(s, "cluster", s.n_entries + s.unique, 16, [&] { return stage_cluster(s); });
+    timed_stage(s, "keep", s.n_clusters, 12, [&] { return stage_keep(s); });
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    resolve_stats(s);
+    s.finalized = true;
+  });
+}
+
+int humid_gpu_counts(humid_gpu *h, uint64_t *total, uint64_t *usable, uint64_t *unique, uint64_t *clusters) {
+  if (!h) return HUMID_GPU_ERR_ARG;
+  if (!h->s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "not finalized");
+  if (total) *total = h->s.n_tuples;
+  if (usable) *usable = h->s.usable;
+  if (unique) *unique = h->s.unique;
+  if (clusters) *clusters = h->s.n_clusters;
+  return HUMID_GPU_OK;
+}
+
+int humid_gpu_histogram(humid_gpu *h, int which, uint64_t *keys, uint64_t *vals, uint64_t *n) {
+  if (!h || !n) return HUMID_GPU_ERR_ARG;
+  State &s = h->s;
+  if (!s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "not finalized");
+  if (which < 0 || which > 2) return fail(h, HUMID_GPU_ERR_ARG, "unknown histogram");
+  int rc = HUMID_GPU_OK;
+  if (!s.hist_done[which]) rc = guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(s.device));
+    static const char *names[3] = {"hist_counts", "hist_neigh", "hist_clusters"};
+    uint64_t m = which == HUMID_HIST_CLUSTERS ? s.n_clusters : s.unique;
+    timed_stage(s, names[which], m, 8, [&] { return stage_histogram(s, which); });
+    resolve_stats(s);
+  });
+  if (rc != HUMID_GPU_OK) return rc;
+  uint64_t m = s.hist_k[which].size();
+  if (keys && vals) {
+    if (*n < m) { *n = m; return fail(h, HUMID_GPU_ERR_ARG, "histogram buffer too small"); }
+    std::memcpy(keys, s.hist_k[which].data(), m * sizeof(uint64_t));
+    std::memcpy(vals, s.hist_v[which].data(), m * sizeof(uint64_t));
+  }
+  *n = m;
+  return HUMID_GPU_OK;
+}
+
+int humid_gpu_keep_mask(humid_gpu *h, uint64_t first_tuple, uint64_t n, uint64_t *bits) {
+  if (!h || (n && !bits)) return HUMID_GPU_ERR_ARG;
+  State &s = h->s;
+  if (!s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "not finalized");
+  if (first_tuple + n > s.n_tuples) return fail(h, HUMID_GPU_ERR_ARG, "tuple range out of bounds");
+  if (first_tuple % 64) return fail(h, HUMID_GPU_ERR_ARG, "first_tuple must be a multiple of 64");
+  if (n == 0) return HUMID_GPU_OK;
+  return guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(s.device));
+    uint64_t words = (n + 63) / 64;
+    HUMID_CUDA(cudaMemcpyAsync(bits, s.keep_bits.p + first_tuple / 32, words * 8, cudaMemcpyDeviceToHost, s.stream));
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    if (n % 64) bits[words - 1] &= (~0ull) >> (64 - n % 64);
+  });
+}
+
+int humid_gpu_cluster_ids(humid_gpu *h, uint64_t first_tuple, uint64_t n, uint32_t *ids) {
+  if (!h || (n && !ids)) return HUMID_GPU_ERR_ARG;
+  State &s = h->s;
+  if (!s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "not finalized");
+  if (first_tuple + n > s.n_tuples) return fail(h, HUMID_GPU_ERR_ARG, "tuple range out of bounds");
+  if (n == 0) return HUMID_GPU_OK;
+  return guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(s.device));
+    s.out_ids.ensure(n);
+    // K5: key (8) + slot (16) + label (4) + seed index (4) + id out (4)
+    timed_stage(s, "cluster_ids", n, 36, [&] { return stage_cluster_ids(s, first_tuple, n, s.out_ids.p); });
+    HUMID_CUDA(cudaMemcpyAsync(ids, s.out_ids.p, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    resolve_stats(s);
+  });
+}
+
+// ---- introspection for the parity tests ---------------------------------------------------
+__global__ void word_cluster_ids_kernel(const uint32_t *label, const uint32_t *seed_index, uint64_t U, uint32_t *out) {
+  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < U) out[r] = seed_index[label[r]] + 1u;
+}
+
+int humid_gpu_debug_words(humid_gpu *h, uint64_t cap, uint64_t *keys, uint32_t *counts, uint32_t *first_tuple,
+                          uint32_t *cluster_ids) {
+  if (!h) return HUMID_GPU_ERR_ARG;
+  State &s = h->s;
+  if (!s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "not finalized");
+  if (cap < s.unique) return fail(h, HUMID_GPU_ERR_ARG, "buffers too small");
+  const uint64_t U = s.unique;
+  if (U == 0) return HUMID_GPU_OK;
+  return guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(s.device));
+    if (keys) HUMID_CUDA(cudaMemcpyAsync(keys, s.word_key.p, U * 8, cudaMemcpyDeviceToHost, s.stream));
+    if (counts) HUMID_CUDA(cudaMemcpyAsync(counts, s.word_count.p, U * 4, cudaMemcpyDeviceToHost, s.stream));
+    if (first_tuple) HUMID_CUDA(cudaMemcpyAsync(first_tuple, s.word_first.p, U * 4, cudaMemcpyDeviceToHost, s.stream));
+    if (cluster_ids) {
+      s.out_ids.ensure(U);
+      word_cluster_ids_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.label.p, s.seed_index.p, U, s.out_ids.p);
+      HUMID_CUDA(cudaMemcpyAsync(cluster_ids, s.out_ids.p, U * 4, cudaMemcpyDeviceToHost, s.stream));
+    }
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+  });
+}
+
+int humid_gpu_debug_neighbours(humid_gpu *h, uint64_t *row_ptr, uint32_t *col, uint64_t *n_entries) {
+  if (!h || !n_entries) return HUMID_GPU_ERR_ARG;
+  State &s = h->s;
+  if (!s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "not finalized");
+  if (col && *n_entries < s.n_entries) return fail(h, HUMID_GPU_ERR_ARG, "col buffer too small");
+  *n_entries = s.n_entries;
+  return guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(s.device));
+    if (row_ptr) HUMID_CUDA(cudaMemcpyAsync(row_ptr, s.row_ptr.p, (s.unique + 1) * 8, cudaMemcpyDeviceToHost, s.stream));
+    if (col && s.n_entries)
+      HUMID_CUDA(cudaMemcpyAsync(col, s.col.p, s.n_entries * 4, cudaMemcpyDeviceToHost, s.stream));
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+  });
+}
+
+int humid_gpu_debug_clusters(humid_gpu *h, uint64_t cap, uint64_t *sizes, uint32_t *max_leaf_rank) {
+  if (!h) return HUMID_GPU_ERR_ARG;
+  State &s = h->s;
+  if (!s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "not finalized");
+  if (cap < s.n_clusters) return fail(h, HUMID_GPU_ERR_ARG, "buffers too small");
+  if (s.n_clusters == 0) return HUMID_GPU_OK;
+  return guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(s.device));
+    if (sizes) HUMID_CUDA(cudaMemcpyAsync(sizes, s.cluster_size.p, s.n_clusters * 8, cudaMemcpyDeviceToHost, s.stream));
+    if (max_leaf_rank)
+      HUMID_CUDA(cudaMemcpyAsync(max_leaf_rank, s.cluster_max.p, s.n_clusters * 4, cudaMemcpyDeviceToHost, s.stream));
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+  });
+}
+
+int humid_gpu_stage_stats(humid_gpu *h, humid_gpu_stage_stat *out, uint32_t *n) {
+  if (!h || !n) return HUMID_GPU_ERR_ARG;
+  State &s = h->s;
+  int rc = guarded(h, [&] { resolve_stats(s); });
+  if (rc != HUMID_GPU_OK) return rc;
+  uint32_t m = (uint32_t)s.stats.size();
+  if (out) {
+    if (*n < m) { *n = m; return fail(h, HUMID_GPU_ERR_ARG, "stats buffer too small"); }
+    for (uint32_t i = 0; i < m; i++) {
+      std::memset(&out[i], 0, sizeof(out[i]));
+      std::strncpy(out[i].name, s.stats[i].name, sizeof(out[i].name) - 1);
+      out[i].ms = s.stats[i].ms;
+      out[i].launches = s.stats[i].launches;
+      out[i].units = s.stats[i].units;
+      out[i].algo_bytes = s.stats[i].algo_bytes;
+    }
+  }
+  *n = m;
+  return HUMID_GPU_OK;
+}
+
+}  // extern "C"

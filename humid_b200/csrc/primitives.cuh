@@ -1,0 +1,45 @@
+// Device-wide primitives written for this library (no CUB/Thrust): exclusive scan and a
+// stable LSD radix sort.  Both are plain HBM-streaming kernels: coalesced loads, shared
+// memory staging, warp match/ballot/shuffle for the in-tile ranking.
+#pragma once
+#include "common.cuh"
+
+namespace humid {
+
+// Scratch arena owned by the handle; grows on demand, never shrinks.
+struct Scratch {
+  void *ptr = nullptr;
+  size_t bytes = 0;
+  void *get(size_t need) {
+    if (need > bytes) {
+      if (ptr) cudaFree(ptr);
+      ptr = nullptr;
+      bytes = 0;
+      size_t want = need + need / 4 + 4096;
+      HUMID_CUDA(cudaMalloc(&ptr, want));
+      bytes = want;
+    }
+    return ptr;
+  }
+  void release() {
+    if (ptr) cudaFree(ptr);
+    ptr = nullptr;
+    bytes = 0;
+  }
+};
+
+// out[i] = sum(in[0..i)), n up to 2^32-1 elements, sums must fit uint32_t.
+// If total_dev != nullptr the grand total is written there.  in may alias out.
+// Returns the number of kernels launched.
+int exclusive_scan_u32(const uint32_t *in, uint32_t *out, uint64_t n, uint32_t *total_dev,
+                       Scratch &scratch, cudaStream_t stream);
+
+// Stable LSD radix sort on bits [0, end_bit) of 64-bit keys, 8 bits per pass.
+// keys/vals are double buffers: input in index 0; the function returns the index (0 or 1)
+// of the buffer pair holding the sorted result.  vals may be {nullptr,nullptr} (keys only).
+// *launches is incremented by the number of kernels launched.
+// `scratch` holds the per-tile digit histograms, `scan_scratch` is handed to the scan.
+int radix_sort_u64(uint64_t *keys[2], uint32_t *vals[2], uint64_t n, int end_bit, Scratch &scratch,
+                   Scratch &scan_scratch, cudaStream_t stream, int *launches);
+
+}  // namespace humid

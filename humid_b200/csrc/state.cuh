@@ -1,0 +1,119 @@
+// Device-resident state of one humid_gpu handle and the stage launchers that operate on it.
+// Data layout in HBM (all structure-of-arrays, indices are 32-bit):
+//   per tuple t:    tuple_key[t]                     packed word or KEY_INVALID        8 B
+//   table:          slots[cap]                       {key, count|rank, first}         16 B
+//   per rank r:     word_key[r], word_count[r], word_first[r]                        8+4+4 B
+//                   row_ptr[r] (u64), label[r] (cluster seed rank), comp[r]
+//   per entry:      col[e]                           neighbour rank                    4 B
+//   per cluster:    indexed by seed rank (sparse) then compacted by id
+#pragma once
+#include <vector>
+
+#include "../../include/humid_gpu.h"
+#include "primitives.cuh"
+
+namespace humid {
+
+template <typename T>
+struct DevBuf {
+  T *p = nullptr;
+  size_t cap = 0;  // elements
+  // Make room for n elements; contents are NOT preserved when reallocating.
+  T *ensure(size_t n) {
+    if (n > cap) {
+      release();
+      size_t want = n + n / 8 + 64;
+      HUMID_CUDA(cudaMalloc((void **)&p, want * sizeof(T)));
+      cap = want;
+    }
+    return p;
+  }
+  // Make room for n elements, preserving the first `keep` ones.
+  T *grow(size_t n, size_t keep, cudaStream_t stream) {
+    if (n > cap) {
+      size_t want = n + n / 2 + 64;
+      T *q = nullptr;
+      HUMID_CUDA(cudaMalloc((void **)&q, want * sizeof(T)));
+      if (keep) HUMID_CUDA(cudaMemcpyAsync(q, p, keep * sizeof(T), cudaMemcpyDeviceToDevice, stream));
+      HUMID_CUDA(cudaStreamSynchronize(stream));
+      if (p) cudaFree(p);
+      p = q;
+      cap = want;
+    }
+    return p;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+
+struct StageStat {
+  const char *name;
+  float ms = 0.f;
+  uint32_t launches = 0;
+  uint64_t units = 0, algo_bytes = 0;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+};
+
+struct State {
+  humid_gpu_config cfg{};
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool finalized = false;
+
+  // pass 1
+  uint64_t n_tuples = 0;
+  DevBuf<uint64_t> tuple_key;
+  DevBuf<uint8_t> stage_chars;     // H2D staging for add_batch
+  DevBuf<uint16_t> stage_seg_len;
+  DevBuf<unsigned long long> counters;  // [0] usable, [1] unique, [2] entries, [3..] misc
+  uint64_t usable = 0, unique = 0, n_entries = 0, n_clusters = 0;
+
+  // word table
+  DevBuf<Slot> slots;
+  uint64_t table_cap = 0;  // power of two
+
+  // rank-ordered columns
+  DevBuf<uint64_t> word_key, key_alt;
+  DevBuf<uint32_t> word_slot, slot_alt;
+  DevBuf<uint32_t> word_count, word_first;
+
+  // neighbour lists
+  DevBuf<uint64_t> entries, entries_alt;  // (src rank << 32 | payload), see neighbours.cu
+  DevBuf<uint32_t> entry_val, entry_val_alt;
+  DevBuf<uint64_t> row_ptr;               // [U+1]
+  DevBuf<uint32_t> col;                   // [n_entries]
+
+  // clustering
+  DevBuf<uint32_t> comp, label, members, seg_start, seg_end, work_a, work_b, work_c;
+  DevBuf<uint32_t> seed_flag, seed_index;     // seed_index = exclusive scan of seed_flag
+  DevBuf<uint64_t> seed_size;                 // Cluster::size, indexed by seed rank
+  DevBuf<uint32_t> seed_max;                  // rank of Cluster::maxLeaf, indexed by seed rank
+  DevBuf<uint64_t> cluster_size;              // compacted by id-1
+  DevBuf<uint32_t> cluster_max;
+
+  // outputs
+  DevBuf<uint32_t> keep_bits;  // ceil(R/32) words
+  DevBuf<uint32_t> out_ids;
+  std::vector<uint64_t> hist_k[3], hist_v[3];
+  bool hist_done[3] = {false, false, false};
+
+  Scratch scratch, scan_scratch;
+  std::vector<StageStat> stats;
+  std::string last_error;
+};
+
+// ---- stage launchers (each returns the number of kernels it launched) --------------------
+int stage_pack(State &s, const uint8_t *d_chars, const uint16_t *d_seg_len, uint64_t first, uint64_t n);
+int stage_build_table(State &s);       // insert + compact + sort + rank columns
+int stage_neighbours_hamming(State &s);
+int stage_neighbours_edit(State &s);
+int stage_csr(State &s);               // sort entries, row_ptr / col
+int stage_cluster(State &s);           // components, replay, ids, sizes, maxLeaf
+int stage_keep(State &s);              // keep bitmap
+int stage_cluster_ids(State &s, uint64_t first, uint64_t n, uint32_t *d_out);
+int stage_histogram(State &s, int which);
+
+}  // namespace humid

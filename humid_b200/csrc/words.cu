@@ -1,0 +1,194 @@
+// K1/K2 — word construction, distinct-word table with counts, rank order.
+//
+// Replaces makeWord/getNucleotides/makeStringSize_ (reference src/fastq.cc:57-66, :116-161),
+// Trie::add (lib/trie/src/trieFunctions.tcc:45-59) and Trie::walk order (:129-143).
+#include "state.cuh"
+
+namespace humid {
+
+struct PackParams {
+  uint32_t n, n_segs;
+  uint32_t take[HUMID_MAX_SEGMENTS];
+};
+
+constexpr int PACK_THREADS = 256;
+
+// A=0 C=1 G=2 T=3 (src/fastq.cc:12); anything else filters the word (:151-158).
+__device__ __forceinline__ uint32_t nt_code(uint32_t ch, bool &bad) {
+  bad |= !(ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T');
+  uint32_t x = (ch >> 1) & 3u;  // A:0 C:1 G:3 T:2
+  return x ^ (x >> 1);          // A:0 C:1 G:2 T:3
+}
+
+// One CTA packs PACK_THREADS consecutive tuples: the CTA's n*256 characters are staged into
+// shared memory with coalesced 16-byte loads, then thread t encodes tuple t from its row.
+__global__ void __launch_bounds__(PACK_THREADS)
+    pack_words_kernel(const uint8_t *__restrict__ chars, const uint16_t *__restrict__ seg_len, uint64_t n_tuples,
+                      PackParams pp, uint64_t *__restrict__ keys_out, unsigned long long *__restrict__ usable) {
+  extern __shared__ __align__(16) uint8_t tile[];
+  const uint64_t t0 = (uint64_t)blockIdx.x * PACK_THREADS;
+  const uint32_t rows = (uint32_t)min((uint64_t)PACK_THREADS, n_tuples - t0);
+  const uint32_t bytes = rows * pp.n;
+  const uint8_t *src = chars + t0 * pp.n;
+  if ((((uintptr_t)src) & 15u) == 0) {
+    const uint32_t vecs = bytes >> 4;
+    for (uint32_t i = threadIdx.x; i < vecs; i += PACK_THREADS)
+      reinterpret_cast<uint4 *>(tile)[i] = ld_stream_u128(src + 16ull * i);
+    for (uint32_t i = (vecs << 4) + threadIdx.x; i < bytes; i += PACK_THREADS) tile[i] = src[i];
+  } else {
+    for (uint32_t i = threadIdx.x; i < bytes; i += PACK_THREADS) tile[i] = src[i];
+  }
+  __syncthreads();
+
+  bool ok = threadIdx.x < rows;
+  uint64_t key = 0;
+  bool bad = false;
+  if (ok) {
+    const uint8_t *row = tile + threadIdx.x * pp.n;
+    const uint16_t *sl = seg_len ? seg_len + (t0 + threadIdx.x) * pp.n_segs : nullptr;
+    uint32_t p = 0;
+    for (uint32_t s = 0; s < pp.n_segs; s++) {
+      // makeStringSize_: a segment shorter than its share is padded with 'N' => filtered
+      uint32_t have = sl ? sl[s] : pp.take[s];
+      bad |= have < pp.take[s];
+      for (uint32_t q = 0; q < pp.take[s]; q++, p++) key = (key << 2) | nt_code(row[p], bad);
+    }
+    keys_out[t0 + threadIdx.x] = bad ? KEY_INVALID : key;
+  }
+  unsigned good = __ballot_sync(0xffffffffu, ok && !bad);
+  if (lane_id() == 0 && good) atomicAdd(usable, (unsigned long long)__popc(good));
+}
+
+int stage_pack(State &s, const uint8_t *d_chars, const uint16_t *d_seg_len, uint64_t first, uint64_t n) {
+  if (n == 0) return 0;
+  PackParams pp{};
+  pp.n = s.cfg.word_length;
+  pp.n_segs = s.cfg.n_segments;
+  for (uint32_t i = 0; i < pp.n_segs; i++) pp.take[i] = s.cfg.seg_take[i];
+  unsigned grid = grid_for(n, PACK_THREADS);
+  size_t smem = (size_t)PACK_THREADS * pp.n;
+  pack_words_kernel<<<grid, PACK_THREADS, smem, s.stream>>>(d_chars, d_seg_len, n, pp, s.tuple_key.p + first,
+                                                            s.counters.p + 0);
+  HUMID_CUDA(cudaGetLastError());
+  return 1;
+}
+
+// ------------------------------------------------------------------------------------
+// Distinct-word table: open addressing, linear probing, 16-B slots (two per 32-B sector).
+// ------------------------------------------------------------------------------------
+__global__ void table_clear_kernel(Slot *slots, uint64_t cap) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < cap) {
+    uint4 v;
+    v.x = v.y = 0xFFFFFFFFu;  // key = KEY_INVALID
+    v.z = 0u;                 // count
+    v.w = 0xFFFFFFFFu;        // first
+    reinterpret_cast<uint4 *>(slots)[i] = v;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+    table_insert_kernel(const uint64_t *__restrict__ keys, uint64_t n_tuples, Slot *slots, uint64_t mask) {
+  uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_tuples) return;
+  uint64_t key = ld_stream_u64(keys + t);
+  if (key == KEY_INVALID) return;
+  uint64_t idx = mix64(key) & mask;
+  while (true) {
+    uint64_t cur = *reinterpret_cast<volatile uint64_t *>(&slots[idx].key);
+    if (cur == key) break;
+    if (cur == KEY_INVALID) {
+      unsigned long long prev = atomicCAS(reinterpret_cast<unsigned long long *>(&slots[idx].key),
+                                          (unsigned long long)KEY_INVALID, (unsigned long long)key);
+      if (prev == KEY_INVALID || prev == key) break;
+    }
+    idx = (idx + 1) & mask;
+  }
+  atomicAdd(&slots[idx].count, 1u);            // Leaf::count++
+  atomicMin(&slots[idx].first, (uint32_t)t);   // first tuple in input order
+}
+
+// Occupied slots -> (key, slot) pairs, any order (they are sorted next).
+__global__ void __launch_bounds__(256)
+    table_compact_kernel(const Slot *__restrict__ slots, uint64_t cap, uint64_t *__restrict__ keys_out,
+                         uint32_t *__restrict__ slot_out, unsigned long long *__restrict__ counter) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  uint64_t key = KEY_INVALID;
+  if (i < cap) key = slots[i].key;
+  bool occ = key != KEY_INVALID;
+  unsigned m = __ballot_sync(0xffffffffu, occ);
+  if (m == 0) return;
+  unsigned long long base = 0;
+  int leader = __ffs(m) - 1;
+  if ((int)lane_id() == leader) base = atomicAdd(counter, (unsigned long long)__popc(m));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (occ) {
+    uint64_t pos = base + __popc(m & ((1u << lane_id()) - 1u));
+    keys_out[pos] = key;
+    slot_out[pos] = (uint32_t)i;
+  }
+}
+
+// Rank-ordered columns; the slot's count field is overwritten with the rank so that one
+// probe of the table answers "which rank is this key".
+__global__ void __launch_bounds__(256)
+    rank_columns_kernel(Slot *slots, const uint32_t *__restrict__ word_slot, uint64_t U,
+                        uint32_t *__restrict__ word_count, uint32_t *__restrict__ word_first) {
+  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= U) return;
+  Slot *sl = slots + word_slot[r];
+  uint4 v = *reinterpret_cast<const uint4 *>(sl);
+  word_count[r] = v.z;
+  word_first[r] = v.w;
+  sl->count = (uint32_t)r;
+}
+
+int stage_build_table(State &s) {
+  int k = 0;
+  HUMID_CUDA(cudaMemcpyAsync(&s.usable, s.counters.p + 0, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+  HUMID_CUDA(cudaStreamSynchronize(s.stream));
+  uint64_t cap = 1024;
+  while (cap < 2 * s.usable) cap <<= 1;
+  if (cap > (1ull << 32)) throw CudaError{"word table would exceed 2^32 slots"};
+  s.table_cap = cap;
+  s.slots.ensure(cap);
+  table_clear_kernel<<<grid_for(cap, 256), 256, 0, s.stream>>>(s.slots.p, cap);
+  k++;
+  if (s.n_tuples) {
+    table_insert_kernel<<<grid_for(s.n_tuples, 256), 256, 0, s.stream>>>(s.tuple_key.p, s.n_tuples, s.slots.p,
+                                                                        cap - 1);
+    k++;
+  }
+  // distinct words cannot outnumber usable tuples
+  s.word_key.ensure(s.usable + 1);
+  s.key_alt.ensure(s.usable + 1);
+  s.word_slot.ensure(s.usable + 1);
+  s.slot_alt.ensure(s.usable + 1);
+  HUMID_CUDA(cudaMemsetAsync(s.counters.p + 1, 0, sizeof(unsigned long long), s.stream));
+  table_compact_kernel<<<grid_for(cap, 256), 256, 0, s.stream>>>(s.slots.p, cap, s.word_key.p, s.word_slot.p,
+                                                                 s.counters.p + 1);
+  k++;
+  HUMID_CUDA(cudaMemcpyAsync(&s.unique, s.counters.p + 1, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+  HUMID_CUDA(cudaStreamSynchronize(s.stream));
+  const uint64_t U = s.unique;
+  uint64_t *kb[2] = {s.word_key.p, s.key_alt.p};
+  uint32_t *vb[2] = {s.word_slot.p, s.slot_alt.p};
+  int launches = 0;
+  int cur = radix_sort_u64(kb, vb, U, 2 * (int)s.cfg.word_length, s.scratch, s.scan_scratch, s.stream, &launches);
+  k += launches;
+  if (cur == 1) {
+    std::swap(s.word_key, s.key_alt);
+    std::swap(s.word_slot, s.slot_alt);
+  }
+  s.word_count.ensure(U + 1);
+  s.word_first.ensure(U + 1);
+  if (U) {
+    rank_columns_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.slots.p, s.word_slot.p, U, s.word_count.p,
+                                                                s.word_first.p);
+    k++;
+  }
+  HUMID_CUDA(cudaGetLastError());
+  return k;
+}
+
+}  // namespace humid

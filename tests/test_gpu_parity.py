@@ -1,0 +1,183 @@
+"""Parity of the CUDA path (through the C ABI) with the reference.
+
+  * golden fixtures = outputs of the unmodified reference binary (tests/golden/*.npz);
+  * the CPU oracle on seeded synthetic inputs, including what the binary never prints
+    (rank-ordered words, neighbour lists with order and multiplicity, cluster sizes and
+    maxLeaf);
+  * the reference's own edge cases: empty input, all tuples filtered, short segments,
+    count ties in maximum mode, the dominance rule at distance 2.
+Everything here is integer work: the bar is bit-exact.
+"""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from humid_b200 import api
+from humid_b200.synth import Synth, baseline_config
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+
+
+def load_golden(path):
+    z = np.load(path)
+    g = {k: z[k] for k in z.files}
+    for k in ("n", "d", "edit", "maximum"):
+        g[k] = int(g[k])
+    for k in ("counts", "neigh", "clusters", "stats"):
+        g[k] = bytes(g[k]).decode()
+    return g
+
+
+def run_gpu(chars, seg_take, n, d, edit, maximum, seg_len=None, batches=1):
+    dd = api.Dedup(word_length=n, distance=d, seg_take=seg_take, edit=edit, maximum=maximum)
+    R = chars.shape[0]
+    step = max(1, (R + batches - 1) // batches)
+    for lo in range(0, R, step):
+        dd.add_batch(chars[lo:lo + step], None if seg_len is None else seg_len[lo:lo + step])
+    dd.finalize()
+    return dd
+
+
+def assert_same_as_oracle(dd, r, R):
+    c = dd.counts()
+    assert (c["total"], c["usable"], c["unique"], c["clusters"]) == (r.total, r.usable, r.unique, r.clusters)
+    keys, cnt, first, cid = dd.words()
+    assert np.array_equal(keys, r.keys)
+    assert np.array_equal(cnt.astype(np.uint64), r.count)
+    assert np.array_equal(first.astype(np.uint64), r.first)
+    row_ptr, col = dd.neighbours()
+    assert np.array_equal(row_ptr, r.row_ptr)
+    assert np.array_equal(col, r.col)
+    assert np.array_equal(cid, r.cluster_of)
+    size, mx = dd.clusters()
+    assert np.array_equal(size, r.cluster_size)
+    assert np.array_equal(mx, r.cluster_max)
+    assert np.array_equal(dd.keep_mask(), r.keep.astype(bool))
+    assert np.array_equal(dd.cluster_ids(), r.cid)
+    assert dd.stats_text() == r.stats_text()
+    assert int(dd.keep_mask().sum()) == r.clusters
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[:-4] for p in GOLDEN])
+def test_golden_reference_outputs(path):
+    g = load_golden(path)
+    dd = run_gpu(g["chars"], g["seg_take"], g["n"], g["d"], bool(g["edit"]), bool(g["maximum"]), batches=3)
+    txt = dd.stats_text()
+    assert txt["stats.dat"] == g["stats"]
+    assert txt["counts.dat"] == g["counts"]
+    assert txt["neigh.dat"] == g["neigh"]
+    assert txt["clusters.dat"] == g["clusters"]
+    assert np.array_equal(dd.keep_mask(), g["keep"].astype(bool))
+    assert np.array_equal(dd.cluster_ids(), g["cid"])
+
+
+CASES = [  # (config index, tuples, overrides)
+    (0, 40000, {}),
+    (0, 40000, dict(maximum=False)),
+    (1, 30000, {}),
+    (2, 30000, {}),
+    (2, 30000, dict(maximum=True)),
+    (2, 4000, dict(distance=3)),
+    (4, 50000, {}),
+    (0, 20000, dict(word_length=8, genome_len=2000)),
+    (0, 20000, dict(word_length=8, genome_len=2000, maximum=False)),
+    (2, 20000, dict(word_length=10, genome_len=3000, maximum=True)),
+    (2, 20000, dict(word_length=10, genome_len=3000)),
+    (3, 8000, dict(distance=1)),
+    (3, 8000, {}),
+    (3, 8000, dict(maximum=True)),
+    (3, 4000, dict(word_length=10, genome_len=3000)),
+    (3, 1500, dict(distance=3, word_length=12, genome_len=3000)),
+]
+
+
+@pytest.mark.parametrize("ci,R,kw", CASES, ids=[f"c{c + 1}_{R}_{'_'.join(f'{k}{v}' for k, v in kw.items())}" for c, R, kw in CASES])
+def test_against_oracle(ci, R, kw):
+    cfg = baseline_config(ci, R, **kw)
+    s = Synth(cfg)
+    chars = s.word_chars()
+    hdr, take = s.layout()
+    seg_take = ([hdr] if hdr else []) + take
+    keys = oracle.pack_words(chars, seg_take)
+    r = oracle.Result(keys, cfg.word_length, cfg.distance, cfg.edit, cfg.maximum)
+    dd = run_gpu(chars, seg_take, cfg.word_length, cfg.distance, cfg.edit, cfg.maximum, batches=2)
+    assert_same_as_oracle(dd, r, R)
+
+
+def _chars(words):
+    return np.frombuffer("".join(words).encode(), dtype=np.uint8).reshape(len(words), -1).copy()
+
+
+def test_empty_input():
+    dd = api.Dedup(word_length=8, distance=1, seg_take=[4, 4])
+    dd.finalize()
+    assert dd.counts() == dict(total=0, usable=0, unique=0, clusters=0)
+    assert dd.stats_text() == {"counts.dat": "", "neigh.dat": "", "clusters.dat": "",
+                               "stats.dat": "total: 0\nusable: 0\nunique: 0\nclusters: 0\n"}
+
+
+def test_all_filtered():
+    dd = run_gpu(_chars(["ACGN", "NNNN", "acgt"]), [2, 2], 4, 1, False, True)
+    assert dd.counts() == dict(total=3, usable=0, unique=0, clusters=0)
+    assert not dd.keep_mask().any()
+    assert list(dd.cluster_ids()) == [0, 0, 0]
+
+
+def test_short_segments_filter():  # makeStringSize_ pads with 'N' (src/fastq.cc:57-66)
+    chars = _chars(["ACGTACGT", "ACGTACGT", "ACGTACGT"])
+    seg_len = np.array([[4, 4], [4, 3], [2, 4]], dtype=np.uint16)
+    keys = oracle.pack_words(chars, [4, 4], seg_len)
+    r = oracle.Result(keys, 8, 1, False, False)
+    dd = run_gpu(chars, [4, 4], 8, 1, False, False, seg_len=seg_len)
+    assert_same_as_oracle(dd, r, 3)
+    assert dd.counts()["usable"] == 1
+
+
+def test_dominance_rule_distance2():  # AC / CA are never linked
+    chars = _chars(["AA", "AC", "CA", "CC"])
+    dd = run_gpu(chars, [2], 2, 2, False, True)
+    row_ptr, col = dd.neighbours()
+    nb = [list(col[int(row_ptr[i]):int(row_ptr[i + 1])]) for i in range(4)]
+    assert nb == [[1, 2, 3], [0, 3], [0, 3], [0, 1, 2]]
+
+
+def test_maxleaf_dfs_tiebreak():  # AA(1) AC(1) CA(5) CC(5) keeps the first CC read
+    words = ["AA", "AC"] + ["CA"] * 5 + ["CC"] * 5
+    dd = run_gpu(_chars(words), [2], 2, 1, False, True)
+    assert dd.counts()["clusters"] == 1
+    assert list(np.nonzero(dd.keep_mask())[0]) == [7]
+    dd = run_gpu(_chars(words), [2], 2, 1, False, False)
+    assert dd.counts()["clusters"] == 2
+    assert list(np.nonzero(dd.keep_mask())[0]) == [2, 7]
+    assert dd.stats_text()["clusters.dat"] == "6 2\n"
+
+
+def test_reset_reuses_handle():
+    s = Synth(baseline_config(0, 5000))
+    chars = s.word_chars()
+    dd = api.Dedup(word_length=24, distance=1, seg_take=[8, 8, 8], maximum=True)
+    dd.add_batch(chars)
+    dd.finalize()
+    a = (dd.counts(), dd.keep_mask().copy(), dd.stats_text())
+    dd.reset()
+    dd.add_batch(chars[:2500])
+    dd.add_batch(chars[2500:])
+    dd.finalize()
+    assert a[0] == dd.counts() and np.array_equal(a[1], dd.keep_mask()) and a[2] == dd.stats_text()
+
+
+def test_call_order_errors():
+    dd = api.Dedup(word_length=4, distance=1, seg_take=[4])
+    with pytest.raises(api.HumidGpuError):
+        dd.counts()
+    dd.add_batch(_chars(["ACGT"]))
+    dd.finalize()
+    with pytest.raises(api.HumidGpuError):
+        dd.add_batch(_chars(["ACGT"]))
+    with pytest.raises(api.HumidGpuError):
+        api.Dedup(word_length=40, distance=1, seg_take=[40])
