@@ -24,7 +24,7 @@ EXPORTS = [
     "humid_gpu_abi_version", "humid_gpu_create", "humid_gpu_destroy", "humid_gpu_reset", "humid_gpu_last_error",
     "humid_gpu_add_batch", "humid_gpu_add_batch_device", "humid_gpu_finalize", "humid_gpu_counts",
     "humid_gpu_histogram", "humid_gpu_keep_mask", "humid_gpu_cluster_ids", "humid_gpu_debug_words",
-    "humid_gpu_debug_neighbours", "humid_gpu_debug_clusters", "humid_gpu_stage_stats",
+    "humid_gpu_debug_neighbours", "humid_gpu_debug_clusters", "humid_gpu_stage_stats", "humid_gpu_stream",
 ]
 
 
@@ -77,6 +77,8 @@ def load_library() -> C.CDLL:
     L.humid_gpu_debug_neighbours.argtypes = [vp, vp, vp, P(u64)]
     L.humid_gpu_debug_clusters.argtypes = [vp, u64, vp, vp]
     L.humid_gpu_stage_stats.argtypes = [vp, P(StageStat), P(u32)]
+    L.humid_gpu_stream.argtypes = [vp]
+    L.humid_gpu_stream.restype = vp
     _lib = L
     return L
 
@@ -135,6 +137,11 @@ class Dedup:
 
     def __exit__(self, *exc):
         self.close()
+
+    @property
+    def stream(self) -> int:
+        """Raw cudaStream_t of the handle (e.g. for torch.cuda.ExternalStream)."""
+        return int(self._L.humid_gpu_stream(self._h) or 0)
 
     def reset(self):
         self._check(self._L.humid_gpu_reset(self._h), "reset")

@@ -215,9 +215,14 @@ int stage_cluster(State &s) {
   s.comp.ensure(U);
   s.label.ensure(U);
   s.work_a.ensure(U);
-  iota_kernel<<<g256, 256, 0, s.stream>>>(s.work_a.p, U);  // parent
-  uf_union_kernel<<<g256, 256, 0, s.stream>>>(s.row_ptr.p, s.col.p, s.n_entries, U, s.work_a.p);
-  uf_flatten_kernel<<<g256, 256, 0, s.stream>>>(s.work_a.p, s.comp.p, U);
+  {
+    // 8 (entry) + 8 (two parent reads) per entry; 12 per word
+    Timed t(s, "union_find", s.n_entries, s.n_entries * 16 + U * 12);
+    iota_kernel<<<g256, 256, 0, s.stream>>>(s.work_a.p, U);  // parent
+    uf_union_kernel<<<g256, 256, 0, s.stream>>>(s.row_ptr.p, s.col.p, s.n_entries, U, s.work_a.p);
+    uf_flatten_kernel<<<g256, 256, 0, s.stream>>>(s.work_a.p, s.comp.p, U);
+    t.launches = 3;
+  }
   k += 3;
 
   // members grouped by component (stable sort keeps rank order inside a component)
@@ -227,18 +232,21 @@ int stage_cluster(State &s) {
   s.slot_alt.ensure(U + 1);
   uint64_t *kb[2] = {s.key_alt.p, s.entries_alt.p};
   uint32_t *vb[2] = {s.members.p, s.slot_alt.p};
-  member_keys_kernel<<<g256, 256, 0, s.stream>>>(s.comp.p, U, kb[0], vb[0]);
-  k++;
   int ubits = 1;
   while ((1ull << ubits) < U) ubits++;
   int launches = 0;
-  int cur = radix_sort_u64(kb, vb, U, ubits, s.scratch, s.scan_scratch, s.stream, &launches);
-  k += launches;
-  if (cur == 1) std::swap(s.members, s.slot_alt);
+  int cur;
   s.seg_start.ensure(U);
   s.seg_end.ensure(U);
-  segment_bounds_kernel<<<g256, 256, 0, s.stream>>>(kb[cur], U, s.seg_start.p, s.seg_end.p);
-  k++;
+  {
+    Timed t(s, "group_members", U, U * (4 + 2 * 12 + 8));
+    member_keys_kernel<<<g256, 256, 0, s.stream>>>(s.comp.p, U, kb[0], vb[0]);
+    cur = radix_sort_u64(kb, vb, U, ubits, s.scratch, s.scan_scratch, s.stream, &launches);
+    if (cur == 1) std::swap(s.members, s.slot_alt);
+    segment_bounds_kernel<<<g256, 256, 0, s.stream>>>(kb[cur], U, s.seg_start.p, s.seg_end.p);
+    t.launches = launches + 2;
+  }
+  k += launches + 2;
 
   s.seed_flag.ensure(U);
   s.seed_index.ensure(U);
@@ -247,6 +255,8 @@ int stage_cluster(State &s) {
   s.work_b.ensure(U);
   s.work_c.ensure(U);
   Graph g{s.row_ptr.p, s.col.p, s.word_count.p};
+  size_t t_replay = s.timer_begin(s.cfg.maximum ? "replay_maximum" : "replay_directional", U,
+                                  s.n_entries * 8 + U * 24);
   if (s.cfg.maximum) {
     HUMID_CUDA(cudaMemsetAsync(s.work_c.p, 0, U * sizeof(uint32_t), s.stream));  // visited
     replay_maximum_kernel<<<g128, 128, 0, s.stream>>>(g, U, s.comp.p, s.members.p, s.seg_start.p, s.seg_end.p,
@@ -259,17 +269,24 @@ int stage_cluster(State &s) {
                                                           s.work_a.p, s.label.p, s.seed_flag.p, s.seed_size.p,
                                                           s.seed_max.p);
   }
+  s.timer_end(t_replay, 1);
   k++;
   uint32_t *total = reinterpret_cast<uint32_t *>(s.counters.p + 3);
-  k += exclusive_scan_u32(s.seed_flag.p, s.seed_index.p, U, total, s.scan_scratch, s.stream);
+  size_t t_ids = s.timer_begin("cluster_ids_scan", U, U * 8);
+  int scan_launches = exclusive_scan_u32(s.seed_flag.p, s.seed_index.p, U, total, s.scan_scratch, s.stream);
+  s.timer_end(t_ids, scan_launches);
+  k += scan_launches;
   uint32_t C = 0;
   HUMID_CUDA(cudaMemcpyAsync(&C, total, sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
   HUMID_CUDA(cudaStreamSynchronize(s.stream));
   s.n_clusters = C;
   s.cluster_size.ensure(C + 1);
   s.cluster_max.ensure(C + 1);
-  compact_clusters_kernel<<<g256, 256, 0, s.stream>>>(s.seed_flag.p, s.seed_index.p, s.seed_size.p, s.seed_max.p, U,
-                                                      s.cluster_size.p, s.cluster_max.p);
+  {
+    Timed t(s, "compact_clusters", U, U * 8 + (uint64_t)C * 24);
+    compact_clusters_kernel<<<g256, 256, 0, s.stream>>>(s.seed_flag.p, s.seed_index.p, s.seed_size.p, s.seed_max.p,
+                                                        U, s.cluster_size.p, s.cluster_max.p);
+  }
   k++;
   HUMID_CUDA(cudaGetLastError());
   return k;

@@ -34,20 +34,6 @@ static int guarded(humid_gpu *h, const std::function<void()> &body) {
   }
 }
 
-static void timed_stage(State &s, const char *name, uint64_t units, uint64_t bytes_per_unit,
-                        const std::function<int()> &run) {
-  StageStat st;
-  st.name = name;
-  HUMID_CUDA(cudaEventCreate(&st.e0));
-  HUMID_CUDA(cudaEventCreate(&st.e1));
-  HUMID_CUDA(cudaEventRecord(st.e0, s.stream));
-  st.launches = (uint32_t)run();
-  HUMID_CUDA(cudaEventRecord(st.e1, s.stream));
-  st.units = units;
-  st.algo_bytes = units * bytes_per_unit;
-  s.stats.push_back(st);
-}
-
 static void resolve_stats(State &s) {
   for (auto &st : s.stats) {
     if (!st.e0) continue;
@@ -70,6 +56,8 @@ static void clear_stats(State &s) {
 extern "C" {
 
 int humid_gpu_abi_version(void) { return HUMID_GPU_ABI_VERSION; }
+
+void *humid_gpu_stream(humid_gpu *h) { return h ? (void *)h->s.stream : nullptr; }
 
 const char *humid_gpu_last_error(const humid_gpu *h) { return h ? h->s.last_error.c_str() : g_create_error.c_str(); }
 
@@ -168,7 +156,7 @@ static int add_batch_impl(humid_gpu *h, const uint8_t *chars, const uint16_t *se
       }
     }
     // makeWord: n ASCII bytes in, one 8-byte key out
-    timed_stage(s, "pack", n, wl + 8, [&] { return stage_pack(s, d_chars, d_len, first, n); });
+    stage_pack(s, d_chars, d_len, first, n);
     s.n_tuples += n;
     if (!on_device) HUMID_CUDA(cudaStreamSynchronize(s.stream));  // the caller may reuse its buffers
   });
@@ -190,22 +178,12 @@ int humid_gpu_finalize(humid_gpu *h) {
   if (s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "finalize called twice");
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
-    const uint32_t n = s.cfg.word_length;
-    // K1 insert: key in (8) + slot key (8) + count RMW (8) + first RMW (8); K2: keys+slot ids
-    // read and written once (2*(8+4)) + rank columns (4+4+4)
-    timed_stage(s, "table", s.n_tuples, 32, [&] { return stage_build_table(s); });
     const bool edit2 = s.cfg.edit && s.cfg.distance >= 2;
-    uint64_t probes = 0;  // expected number of probed variants per word (uniform letters)
-    if (!edit2) {
-      double p1 = 1.5 * n, p2 = p1 + 2.25 * n * (n - 1) / 2.0;
-      probes = s.cfg.distance == 0 ? 0 : s.cfg.distance == 1 ? (uint64_t)p1 : (uint64_t)p2;
-    }
-    timed_stage(s, edit2 ? "neigh_edit" : "neigh_hamming", s.unique, 8 * (1 + probes), [&] {
-      return edit2 ? stage_neighbours_edit(s) : stage_neighbours_hamming(s);
-    });
-    timed_stage(s, "csr", s.n_entries, 16, [&] { return stage_csr(s); });
-    timed_stage(s, "cluster", s.n_entries + s.unique, 16, [&] { return stage_cluster(s); });
-    timed_stage(s, "keep", s.n_clusters, 12, [&] { return stage_keep(s); });
+    stage_build_table(s);
+    if (edit2) stage_neighbours_edit(s); else stage_neighbours_hamming(s);
+    stage_csr(s);
+    stage_cluster(s);
+    stage_keep(s);
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     resolve_stats(s);
     s.finalized = true;
@@ -230,9 +208,7 @@ int humid_gpu_histogram(humid_gpu *h, int which, uint64_t *keys, uint64_t *vals,
   int rc = HUMID_GPU_OK;
   if (!s.hist_done[which]) rc = guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
-    static const char *names[3] = {"hist_counts", "hist_neigh", "hist_clusters"};
-    uint64_t m = which == HUMID_HIST_CLUSTERS ? s.n_clusters : s.unique;
-    timed_stage(s, names[which], m, 8, [&] { return stage_histogram(s, which); });
+    stage_histogram(s, which);
     resolve_stats(s);
   });
   if (rc != HUMID_GPU_OK) return rc;
@@ -272,7 +248,7 @@ int humid_gpu_cluster_ids(humid_gpu *h, uint64_t first_tuple, uint64_t n, uint32
     HUMID_CUDA(cudaSetDevice(s.device));
     s.out_ids.ensure(n);
     // K5: key (8) + slot (16) + label (4) + seed index (4) + id out (4)
-    timed_stage(s, "cluster_ids", n, 36, [&] { return stage_cluster_ids(s, first_tuple, n, s.out_ids.p); });
+    stage_cluster_ids(s, first_tuple, n, s.out_ids.p);
     HUMID_CUDA(cudaMemcpyAsync(ids, s.out_ids.p, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     resolve_stats(s);

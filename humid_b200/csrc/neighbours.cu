@@ -146,6 +146,10 @@ int stage_neighbours_hamming(State &s) {
     cap = s.entries.cap;
     HUMID_CUDA(cudaMemsetAsync(s.counters.p + 2, 0, sizeof(unsigned long long), s.stream));
     uint64_t threads = U * n;
+    // 8 B per probed upward variant (expected 1.5 n at d=1, + 2.25 C(n,2) at d=2) + the word
+    double probes = d == 1 ? 1.5 * n : d == 2 ? 1.5 * n + 2.25 * n * (n - 1) / 2.0 : 0.0;
+    Timed t(s, d == 1 ? "probe_hamming1" : d == 2 ? "probe_hamming2" : "probe_hammingd", U,
+            (uint64_t)(U * 8.0 * (1.0 + probes)));
     if (d == 1)
       hamming1_probe_kernel<<<grid_for(threads, 256), 256, 0, s.stream>>>(
           s.word_key.p, U, n, s.slots.p, s.table_cap - 1, s.entries.p, cap, s.counters.p + 2);
@@ -199,7 +203,12 @@ int stage_csr(State &s) {
       vb[1] = s.entry_val_alt.p;
     }
     int launches = 0;
-    int cur = radix_sort_u64(kb, vb, E, 32 + ubits, s.scratch, s.scan_scratch, s.stream, &launches);
+    int cur;
+    {
+      Timed t(s, "sort_entries", E, E * 16);
+      cur = radix_sort_u64(kb, vb, E, 32 + ubits, s.scratch, s.scan_scratch, s.stream, &launches);
+      t.launches = launches;
+    }
     k += launches;
     if (cur == 1) {
       std::swap(s.entries, s.entries_alt);
@@ -207,7 +216,10 @@ int stage_csr(State &s) {
     }
     if (pairs) vals = s.entry_val.p;
   }
-  csr_split_kernel<<<grid_for(E + 1, 256), 256, 0, s.stream>>>(s.entries.p, vals, E, U, s.row_ptr.p, s.col.p);
+  {
+    Timed t(s, "csr_split", E, E * 12 + U * 8);
+    csr_split_kernel<<<grid_for(E + 1, 256), 256, 0, s.stream>>>(s.entries.p, vals, E, U, s.row_ptr.p, s.col.p);
+  }
   k++;
   HUMID_CUDA(cudaGetLastError());
   return k;

@@ -26,6 +26,7 @@ int stage_keep(State &s) {
   s.keep_bits.ensure(words);
   HUMID_CUDA(cudaMemsetAsync(s.keep_bits.p, 0, words * sizeof(uint32_t), s.stream));
   if (s.n_clusters == 0) return 0;
+  Timed t(s, "keep", s.n_clusters, s.n_clusters * 12);
   keep_scatter_kernel<<<grid_for(s.n_clusters, 256), 256, 0, s.stream>>>(s.cluster_max.p, s.word_first.p,
                                                                          s.n_clusters, s.keep_bits.p);
   HUMID_CUDA(cudaGetLastError());
@@ -55,6 +56,8 @@ __global__ void __launch_bounds__(256)
 
 int stage_cluster_ids(State &s, uint64_t first, uint64_t n, uint32_t *d_out) {
   if (n == 0) return 0;
+  // K5: key (8) + slot (16) + label (4) + seed index (4) + id out (4)
+  Timed t(s, "cluster_ids", n, n * 36);
   cluster_ids_kernel<<<grid_for(n, 256), 256, 0, s.stream>>>(s.tuple_key.p, first, n, s.slots.p, s.table_cap - 1,
                                                              s.label.p, s.seed_index.p, d_out);
   HUMID_CUDA(cudaGetLastError());
@@ -94,6 +97,8 @@ int stage_histogram(State &s, int which) {
   s.hist_done[which] = true;
   if (m == 0) return 0;
   int k = 0;
+  static const char *names[3] = {"hist_counts", "hist_neigh", "hist_clusters"};
+  Timed t(s, names[which], m, m * 8);
   s.key_alt.ensure(m + 1);
   s.entries_alt.ensure(m + 1);
   uint64_t *kb[2] = {s.key_alt.p, s.entries_alt.p};
@@ -135,6 +140,7 @@ int stage_histogram(State &s, int which) {
     s.hist_k[which].push_back(hv[order[j]]);
     s.hist_v[which].push_back(end - hs[order[j]]);
   }
+  t.launches = k;
   return k;
 }
 

@@ -103,6 +103,33 @@ struct State {
   Scratch scratch, scan_scratch;
   std::vector<StageStat> stats;
   std::string last_error;
+
+  // Per-kernel(-family) device timing: CUDA events on `stream` around the launches.
+  size_t timer_begin(const char *name, uint64_t units, uint64_t algo_bytes) {
+    StageStat st;
+    st.name = name;
+    st.units = units;
+    st.algo_bytes = algo_bytes;
+    HUMID_CUDA(cudaEventCreate(&st.e0));
+    HUMID_CUDA(cudaEventCreate(&st.e1));
+    HUMID_CUDA(cudaEventRecord(st.e0, stream));
+    stats.push_back(st);
+    return stats.size() - 1;
+  }
+  void timer_end(size_t idx, uint32_t launches) {
+    stats[idx].launches = launches;
+    HUMID_CUDA(cudaEventRecord(stats[idx].e1, stream));
+  }
+};
+
+// RAII form: `{ Timed t(s, "probe", U, bytes); kernel<<<...>>>(); t.launches = 1; }`
+struct Timed {
+  State &s;
+  size_t idx;
+  uint32_t launches = 1;
+  Timed(State &st, const char *name, uint64_t units, uint64_t algo_bytes)
+      : s(st), idx(st.timer_begin(name, units, algo_bytes)) {}
+  ~Timed() { cudaEventRecord(s.stats[idx].e1, s.stream); s.stats[idx].launches = launches; }
 };
 
 // ---- stage launchers (each returns the number of kernels it launched) --------------------

@@ -67,6 +67,8 @@ int stage_pack(State &s, const uint8_t *d_chars, const uint16_t *d_seg_len, uint
   for (uint32_t i = 0; i < pp.n_segs; i++) pp.take[i] = s.cfg.seg_take[i];
   unsigned grid = grid_for(n, PACK_THREADS);
   size_t smem = (size_t)PACK_THREADS * pp.n;
+  // makeWord: n ASCII bytes in, one 8-byte key out
+  Timed t(s, "pack", n, n * (pp.n + 8));
   pack_words_kernel<<<grid, PACK_THREADS, smem, s.stream>>>(d_chars, d_seg_len, n, pp, s.tuple_key.p + first,
                                                             s.counters.p + 0);
   HUMID_CUDA(cudaGetLastError());
@@ -152,9 +154,14 @@ int stage_build_table(State &s) {
   if (cap > (1ull << 32)) throw CudaError{"word table would exceed 2^32 slots"};
   s.table_cap = cap;
   s.slots.ensure(cap);
-  table_clear_kernel<<<grid_for(cap, 256), 256, 0, s.stream>>>(s.slots.p, cap);
+  {
+    Timed t(s, "table_clear", cap, cap * 16);
+    table_clear_kernel<<<grid_for(cap, 256), 256, 0, s.stream>>>(s.slots.p, cap);
+  }
   k++;
   if (s.n_tuples) {
+    // key in (8) + slot key (8) + count RMW (8) + first RMW (8)
+    Timed t(s, "table_insert", s.n_tuples, s.n_tuples * 8 + s.usable * 24);
     table_insert_kernel<<<grid_for(s.n_tuples, 256), 256, 0, s.stream>>>(s.tuple_key.p, s.n_tuples, s.slots.p,
                                                                         cap - 1);
     k++;
@@ -165,8 +172,11 @@ int stage_build_table(State &s) {
   s.word_slot.ensure(s.usable + 1);
   s.slot_alt.ensure(s.usable + 1);
   HUMID_CUDA(cudaMemsetAsync(s.counters.p + 1, 0, sizeof(unsigned long long), s.stream));
-  table_compact_kernel<<<grid_for(cap, 256), 256, 0, s.stream>>>(s.slots.p, cap, s.word_key.p, s.word_slot.p,
-                                                                 s.counters.p + 1);
+  {
+    Timed t(s, "table_compact", cap, cap * 8 + s.usable * 12);
+    table_compact_kernel<<<grid_for(cap, 256), 256, 0, s.stream>>>(s.slots.p, cap, s.word_key.p, s.word_slot.p,
+                                                                   s.counters.p + 1);
+  }
   k++;
   HUMID_CUDA(cudaMemcpyAsync(&s.unique, s.counters.p + 1, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
   HUMID_CUDA(cudaStreamSynchronize(s.stream));
@@ -174,7 +184,13 @@ int stage_build_table(State &s) {
   uint64_t *kb[2] = {s.word_key.p, s.key_alt.p};
   uint32_t *vb[2] = {s.word_slot.p, s.slot_alt.p};
   int launches = 0;
-  int cur = radix_sort_u64(kb, vb, U, 2 * (int)s.cfg.word_length, s.scratch, s.scan_scratch, s.stream, &launches);
+  int cur;
+  {
+    // keys + slot ids read once and written once (the radix passes are overhead)
+    Timed t(s, "sort_words", U, U * 2 * (8 + 4));
+    cur = radix_sort_u64(kb, vb, U, 2 * (int)s.cfg.word_length, s.scratch, s.scan_scratch, s.stream, &launches);
+    t.launches = launches;
+  }
   k += launches;
   if (cur == 1) {
     std::swap(s.word_key, s.key_alt);
@@ -183,6 +199,7 @@ int stage_build_table(State &s) {
   s.word_count.ensure(U + 1);
   s.word_first.ensure(U + 1);
   if (U) {
+    Timed t(s, "rank_columns", U, U * (4 + 16 + 4 + 4 + 4));
     rank_columns_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.slots.p, s.word_slot.p, U, s.word_count.p,
                                                                 s.word_first.p);
     k++;

@@ -289,3 +289,202 @@ def _records(hdr: np.ndarray, seq: np.ndarray) -> np.ndarray:
     qual = np.full((r, L), ord("I"), dtype=np.uint8)
     return np.ascontiguousarray(np.concatenate(
         [hdr, _const(b"\n", r), seq, _const(b"\n+\n", r), qual, _const(b"\n", r)], axis=1))
+
+
+# ======================================================================================
+# Stateless generator for the large configurations (50 M – 500 M tuples)
+# ======================================================================================
+def _i64(x: int) -> int:
+    """Wrap a Python int into the int64 range (two's complement)."""
+    return ((x + (1 << 63)) % (1 << 64)) - (1 << 63)
+
+
+class HashSynth:
+    """Same read model as `Synth`, but every quantity is a pure function of
+    (seed, tuple index) built from 64-bit integer hashing, evaluated with torch integer ops.
+
+    Consequences: any tuple range can be produced on any device (each rank of a multi-GPU
+    run generates just its own slice, directly in HBM), CPU and CUDA give identical bytes,
+    and no per-tuple state (the 8 B/tuple molecule table of `Synth`) is ever materialised.
+    torch is used here as plumbing for the *workload generator* only; nothing on the
+    deduplication path depends on it.
+
+      molecule of tuple t  : weighted pick; weights 1+Geometric(0.5)… precisely
+                             Geometric(0.5) on {1,2,…} as in `Synth`, arranged in a repeating
+                             pattern of PATTERN molecules so the inverse CDF is a 4096-entry
+                             search; M = R/3 molecules (rounded up to whole patterns)
+      molecule m           : UMI, fragment start, insert size ~ N(300, 30) (Irwin–Hall of 4 bytes)
+      genome               : base(p) = hash(p) & 3 over `glen` positions (never stored)
+      errors               : 0.5 %/base on the first 32 nt of each mate, 1 %/base on the UMI,
+                             at most one indel per mate prefix when cfg.indels, 'N' in 0.1 %
+    """
+
+    PATTERN = 4096
+
+    def __init__(self, cfg: SynthConfig):
+        import torch  # local: the numpy generator above must stay importable without torch
+
+        self.torch = torch
+        self.cfg = cfg
+        R = cfg.n_tuples
+        M = max(1, R // 3)
+        self.n_patterns = (M + self.PATTERN - 1) // self.PATTERN
+        self.M = self.n_patterns * self.PATTERN
+        rng = np.random.Generator(np.random.PCG64(cfg.seed))
+        w = rng.geometric(0.5, size=self.PATTERN).astype(np.int64)
+        self._cdf = np.cumsum(w)  # inclusive
+        self.glen = int(cfg.genome_len if cfg.genome_len < 100_000 else min(cfg.genome_len, max(100_000, 40 * self.M)))
+        s = [int(x) for x in rng.integers(1, 2**62, size=8)]
+        self.k_pick, self.k_umi, self.k_start, self.k_ins, self.k_gen, self.k_err, self.k_n, self.k_indel = s
+        self._cdf_dev = {}
+
+    # splitmix64 finaliser on int64 tensors (wrapping multiply, logical shifts emulated)
+    def _mix(self, x):
+        x = x ^ ((x >> 30) & 0x3FFFFFFFF)
+        x = x * -4658895280553007687  # 0xbf58476d1ce4e5b9
+        x = x ^ ((x >> 27) & 0x1FFFFFFFFF)
+        x = x * -7723592293110705685  # 0x94d049bb133111eb
+        x = x ^ ((x >> 31) & 0x1FFFFFFFF)
+        return x
+
+    def layout(self) -> Tuple[int, List[int]]:
+        cfg = self.cfg
+        hdr = cfg.umi_len if cfg.umi_where == "header" else 0
+        return pre_compute(hdr, cfg.word_length, cfg.n_files)
+
+    def _molecule(self, t):
+        torch = self.torch
+        dev = t.device
+        if dev not in self._cdf_dev:
+            self._cdf_dev[dev] = torch.from_numpy(self._cdf).to(dev)
+        cdf = self._cdf_dev[dev]
+        h = self._mix(t ^ self.k_pick)
+        block = ((h >> 32) & 0xFFFFFFFF) % self.n_patterns
+        slot = (h & 0xFFFFFFFF) % int(self._cdf[-1])
+        idx = torch.searchsorted(cdf, slot, right=True)
+        return block * self.PATTERN + idx
+
+    def _genome(self, p):
+        return self._mix(p ^ self.k_gen) & 3
+
+    def _mates(self, lo: int, hi: int, length: int, device):
+        """Letter codes (0..3, 4 = 'N') umi[r,u], m1[r,length], m2[r,length] as uint8 tensors."""
+        torch = self.torch
+        cfg = self.cfg
+        t = torch.arange(lo, hi, dtype=torch.int64, device=device)
+        m = self._molecule(t)
+        start = (self._mix(m ^ self.k_start) & 0x7FFFFFFFFFFFFFFF) % (self.glen - 600)
+        hb = self._mix(m ^ self.k_ins)
+        ih = (hb & 255) + ((hb >> 8) & 255) + ((hb >> 16) & 255) + ((hb >> 24) & 255)  # mean 510, sd 147.8
+        ins = torch.clamp(300 + ((ih - 510) * 13) // 64, READ_LEN + 10, 500)
+        end = start + ins
+        j = torch.arange(length, dtype=torch.int64, device=device)[None, :]
+        idx1 = start[:, None] + j
+        idx2 = end[:, None] - 1 - j
+        ins1 = ins2 = None
+        if cfg.indels:
+            idx1, ins1 = self._indel(t, idx1, +1, 0)
+            idx2, ins2 = self._indel(t, idx2, -1, 1)
+        m1 = self._genome(idx1)
+        m2 = 3 - self._genome(idx2)
+        if ins1 is not None:
+            for mm, (rows, cols, vals) in ((m1, ins1), (m2, ins2)):
+                ok = cols < length
+                mm[rows[ok], cols[ok]] = vals[ok]
+        span = min(32, length)
+        for which, mm in ((0, m1), (1, m2)):
+            self._subst(t, mm, span, 328, which)  # 328/65536 = 0.5 %
+        u = max(cfg.umi_len, 1)
+        hu = self._mix(m ^ self.k_umi)
+        ju = torch.arange(u, dtype=torch.int64, device=device)[None, :]
+        umi = (hu[:, None] >> (2 * ju)) & 3
+        if cfg.umi_len:
+            self._subst(t, umi, u, 655, 2)  # 655/65536 = 1 %
+        hn = self._mix(t ^ self.k_n)
+        bad = (hn & 0xFFFFF) < int(cfg.n_frac * (1 << 20))
+        if length >= 6:
+            pos = ((hn >> 20) & 0xFFFF) % 6
+            rows = torch.nonzero(bad)[:, 0]
+            m1[rows, pos[rows]] = 4
+        return umi.to(torch.uint8), m1.to(torch.uint8), m2.to(torch.uint8)
+
+    def _subst(self, t, mat, span, thresh, which):
+        """Substitution errors on mat[:, :span]: one 16-bit draw per base, 4 draws per hash."""
+        torch = self.torch
+        for q in range((span + 3) // 4):
+            h = self._mix(t ^ _i64(self.k_err + 0x9E3779B97F4A7C15 * (which * 16 + q + 1)))
+            for k in range(4):
+                col = 4 * q + k
+                if col >= span:
+                    break
+                draw = (h >> (16 * k)) & 0xFFFF
+                err = draw < thresh
+                # a different letter: + (1 + draw % 3)
+                mat[:, col] = torch.where(err, (mat[:, col] + 1 + draw % 3) & 3, mat[:, col])
+
+    def _indel(self, t, idx, step, which):
+        torch = self.torch
+        length = idx.shape[1]
+        span = min(30, length)
+        h = self._mix(t ^ _i64(self.k_indel + which))
+        p_any = 1.0 - (1.0 - 0.002) ** span
+        hit = (h & 0xFFFFF) < int(p_any * (1 << 20))
+        pos = ((h >> 20) & 0xFFFF) % span
+        is_ins = ((h >> 36) & 1) == 1
+        val = (h >> 37) & 3
+        j = torch.arange(length, dtype=torch.int64, device=idx.device)[None, :]
+        dele = (hit & ~is_ins)[:, None] & (j >= pos[:, None])
+        inse = (hit & is_ins)[:, None] & (j > pos[:, None])
+        idx = idx + step * dele.to(torch.int64) - step * inse.to(torch.int64)
+        rows = torch.nonzero(hit & is_ins)[:, 0]
+        return idx, (rows, pos[rows], val[rows])
+
+    _LETTERS = b"ACGTN"
+
+    def word_chars(self, lo: int, hi: int, device="cpu", chunk: int = 2_000_000):
+        """uint8 tensor [hi-lo, word_length] of ASCII word characters on `device`."""
+        torch = self.torch
+        cfg = self.cfg
+        hdr, take = self.layout()
+        need = max(take[0], take[1], 8)
+        table = torch.tensor(list(self._LETTERS), dtype=torch.uint8, device=device)
+        out = torch.empty((hi - lo, cfg.word_length), dtype=torch.uint8, device=device)
+        for a in range(lo, hi, chunk):
+            b = min(hi, a + chunk)
+            umi, m1, m2 = self._mates(a, b, need, device)
+            parts = []
+            if hdr:
+                parts.append(umi[:, :hdr])
+            parts += [m1[:, : take[0]], m2[:, : take[1]]]
+            if cfg.umi_where == "file":
+                uu = umi[:, : take[2]]
+                if uu.shape[1] < take[2]:
+                    pad = torch.full((uu.shape[0], take[2] - uu.shape[1]), 4, dtype=torch.uint8, device=device)
+                    uu = torch.cat([uu, pad], dim=1)
+                parts.append(uu)
+            out[a - lo: b - lo] = table[torch.cat(parts, dim=1).long()]
+        return out
+
+    def write_fastq(self, directory: str, prefix: Optional[str] = None, chunk: int = 250_000) -> List[str]:
+        """FastQ files (CPU) of the whole configuration, for the reference binary."""
+        cfg = self.cfg
+        prefix = prefix or cfg.name
+        os.makedirs(directory, exist_ok=True)
+        names = [os.path.join(directory, f"{prefix}_R{i + 1}.fastq") for i in range(2)]
+        if cfg.umi_where == "file":
+            names.append(os.path.join(directory, f"{prefix}_UMI.fastq"))
+        files = [open(p, "wb") for p in names]
+        letters = np.frombuffer(self._LETTERS, dtype=np.uint8)
+        try:
+            for lo in range(0, cfg.n_tuples, chunk):
+                hi = min(cfg.n_tuples, lo + chunk)
+                umi, m1, m2 = (letters[x.numpy()] for x in self._mates(lo, hi, READ_LEN, "cpu"))
+                ids = np.arange(lo, hi, dtype=np.int64)
+                for fi, seq in enumerate((m1, m2)):
+                    files[fi].write(_records(_headers(cfg, ids, umi, fi + 1), seq).tobytes())
+                if cfg.umi_where == "file":
+                    files[2].write(_records(_headers(cfg, ids, umi, 3), umi[:, : cfg.umi_len]).tobytes())
+        finally:
+            for f in files:
+                f.close()
+        return names

@@ -66,6 +66,10 @@ int humid_gpu_reset(humid_gpu *h);
 /* Message of the last failing call on `h` (or of the last failing create when h == NULL). */
 const char *humid_gpu_last_error(const humid_gpu *h);
 
+/* The cudaStream_t all of h's device work is issued on (so a caller can record its own
+ * events around calls, or order device-resident inputs before humid_gpu_add_batch_device). */
+void *humid_gpu_stream(humid_gpu *h);
+
 /* Pass 1 — replaces `makeWord` + `trie.add` in readData (src/humid.cc:92-99; makeWord
  * src/fastq.cc:146-161, getNucleotides :116-144, makeStringSize_ :57-66, Trie::add
  * lib/trie/src/trieFunctions.tcc:45-59).
