@@ -1,8 +1,330 @@
-// K6 — Levenshtein neighbour search (placeholder until the exact-multiplicity kernel lands).
+// K6 — Levenshtein neighbour search with the reference's exact multiplicities and order.
+//
+// Replaces Trie::asymmetricLevenshtein -> levenshtein_<4,NLeaf,false>
+// (lib/trie/src/trieFunctions.tcc:196-233) as called from findEditNeighbours
+// (src/humid.cc:140-158).  That recursion yields a stored word v once per distinct move
+// sequence (deletion / substitution-or-match / insertion, including "phantom" deletions past
+// the end of the query), every yield != self pushes both directions, and the order of a
+// word's own yields is the depth-first order of the recursion.  Distance 1 is handled by the
+// Hamming-1 kernel (identical result for fixed-length words); this file is d >= 2.
+//
+// Two phases, both exact:
+//   1. candidates: every yielded v satisfies Levenshtein(w, v) <= d (a move sequence is an
+//      edit script of cost <= d), so for each word all same-length words within that distance
+//      are enumerated as variants (substitutions only; one deletion + one insertion + further
+//      substitutions) and looked up through the fingerprint filter + table.  Hits (rank pairs
+//      (q, v), q != v) are sorted and deduplicated.
+//   2. replay: the order of the yields of query q is a function of the move strings only
+//      (deletion < substitution/insertion by child letter < own leaf), so running the
+//      recursion on the tiny trie made of q's candidates alone gives the same yield sequence,
+//      order and multiplicity, as the reference's walk of the whole trie.  One thread per
+//      query walks the implicit trie over its sorted candidate keys with an explicit stack.
+// Own yields are appended in yield order (key = q<<32|q), the mirrored pushes as (v<<32|q);
+// the stable sort of stage_csr then produces list(L) = [pushes by queries q < L] ++ [own
+// yields] ++ [pushes by queries q > L], which is the reference's list order.
 #include "state.cuh"
+
 namespace humid {
-int stage_neighbours_edit(State &s) {
-  (void)s;
-  throw CudaError{"edit distance >= 2 is not implemented yet"};
+
+constexpr int EDIT_MAX_D = 3;  // one deletion+insertion pair plus substitutions
+
+__device__ __forceinline__ void emit_candidate(uint64_t *cand, uint64_t cap, unsigned long long *counter, uint32_t q,
+                                               uint32_t v) {
+  unsigned long long pos = atomicAdd(counter, 1ull);
+  if (pos < cap) cand[pos] = ((uint64_t)q << 32) | v;
 }
+
+// All words obtained from `base` by 0..budget further substitutions (positions strictly
+// increasing, any other letter), each looked up once.
+__device__ void probe_substitutions(uint64_t base, uint32_t n, int budget, uint32_t first_pos, uint64_t self,
+                                    uint32_t q, const Lookup &lk, uint64_t *cand, uint64_t cap,
+                                    unsigned long long *counter, bool probe_base) {
+  if (probe_base && base != self) {
+    uint32_t hit = lookup_rank(lk, base);
+    if (hit != NONE32) emit_candidate(cand, cap, counter, q, hit);
+  }
+  if (budget <= 0) return;
+  uint32_t pos[EDIT_MAX_D];
+  uint32_t add[EDIT_MAX_D];  // letter offset 1..3 applied at pos (mod 4)
+  uint64_t cur = base;
+  int depth = 0;
+  pos[0] = first_pos;
+  add[0] = 0;
+  if (first_pos >= n) return;
+  while (true) {
+    const uint32_t sh = 2 * (n - 1 - pos[depth]);
+    const uint64_t orig = (base >> sh) & 3ull;
+    if (++add[depth] > 3) {
+      cur = (cur & ~(3ull << sh)) | (orig << sh);
+      if (++pos[depth] >= n) {
+        if (depth == 0) break;
+        depth--;
+        continue;
+      }
+      add[depth] = 0;
+      continue;
+    }
+    cur = (cur & ~(3ull << sh)) | (((orig + add[depth]) & 3ull) << sh);
+    if (cur != self) {
+      uint32_t hit = lookup_rank(lk, cur);
+      if (hit != NONE32) emit_candidate(cand, cap, counter, q, hit);
+    }
+    if (depth + 1 < budget && pos[depth] + 1 < n) {
+      depth++;
+      pos[depth] = pos[depth - 1] + 1;
+      add[depth] = 0;
+    }
+  }
+}
+
+// Substitution-only variants: one thread per (word, first substituted position).
+__global__ void __launch_bounds__(128)
+    edit_candidates_subst_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, uint32_t d,
+                                 const Lookup lk, uint64_t *__restrict__ cand, uint64_t cap,
+                                 unsigned long long *__restrict__ counter) {
+  uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  uint64_t r = gid / n;
+  if (r >= U) return;
+  const uint32_t p1 = (uint32_t)(gid - r * n);
+  const uint64_t w = word_key[r];
+  const uint32_t sh = 2 * (n - 1 - p1);
+  const uint64_t orig = (w >> sh) & 3ull;
+  for (uint32_t a = 1; a < 4; a++) {
+    uint64_t v1 = (w & ~(3ull << sh)) | (((orig + a) & 3ull) << sh);
+    probe_substitutions(v1, n, (int)d - 1, p1 + 1, w, (uint32_t)r, lk, cand, cap, counter, true);
+  }
+}
+
+// Deletion of letter i + insertion of letter c so that it lands at position q (a one-letter
+// block shift), then up to d-2 substitutions: one thread per (word, i, q).
+__global__ void __launch_bounds__(128)
+    edit_candidates_shift_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, uint32_t d,
+                                 const Lookup lk, uint64_t *__restrict__ cand, uint64_t cap,
+                                 unsigned long long *__restrict__ counter) {
+  uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t per_word = (uint64_t)n * n;
+  uint64_t r = gid / per_word;
+  if (r >= U) return;
+  uint32_t rem = (uint32_t)(gid - r * per_word);
+  const uint32_t i = rem / n, q = rem - i * n;
+  if (i == q) return;  // a plain substitution (or the word itself): covered by the other kernel
+  const uint64_t w = word_key[r];
+  const uint32_t a = min(i, q), b = max(i, q);  // affected positions [a, b]
+  const uint32_t sh_a = 2 * (n - 1 - a), sh_b = 2 * (n - 1 - b);
+  const uint64_t seg_mask = (sh_a + 2 >= 64 ? ~0ull : ((1ull << (sh_a + 2)) - 1ull)) & ~((1ull << sh_b) - 1ull);
+  const uint64_t seg = w & seg_mask;
+  // q < i: letters q..i-1 move one place to the right; q > i: letters i+1..q move to the left
+  const uint64_t moved = (q < i ? (seg >> 2) : (seg << 2)) & seg_mask;
+  const uint32_t sh_q = 2 * (n - 1 - q);
+  const uint64_t base0 = (w & ~seg_mask) | (moved & ~(3ull << sh_q));
+  for (uint64_t c = 0; c < 4; c++) {
+    uint64_t v = base0 | (c << sh_q);
+    probe_substitutions(v, n, (int)d - 2, 0, w, (uint32_t)r, lk, cand, cap, counter, true);
+  }
+}
+
+// ---- distinct candidates per query -----------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    mark_unique_kernel(const uint64_t *__restrict__ sorted, uint64_t m, uint32_t *__restrict__ flag) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < m) flag[i] = (i == 0 || sorted[i] != sorted[i - 1]) ? 1u : 0u;
+}
+
+__global__ void __launch_bounds__(256)
+    compact_candidates_kernel(const uint64_t *__restrict__ sorted, const uint32_t *__restrict__ flag,
+                              const uint32_t *__restrict__ index, uint64_t m, const uint64_t *__restrict__ word_key,
+                              uint32_t *__restrict__ cand_q, uint32_t *__restrict__ cand_v,
+                              uint64_t *__restrict__ cand_key) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m || !flag[i]) return;
+  uint32_t o = index[i];
+  uint64_t e = sorted[i];
+  cand_q[o] = (uint32_t)(e >> 32);
+  cand_v[o] = (uint32_t)e;
+  cand_key[o] = word_key[(uint32_t)e];
+}
+
+__global__ void __launch_bounds__(256)
+    candidate_rows_kernel(const uint32_t *__restrict__ cand_q, uint64_t m, uint64_t U, uint32_t *__restrict__ row) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i > m) return;
+  uint64_t src = i < m ? cand_q[i] : U;
+  uint64_t prev = i == 0 ? 0 : (uint64_t)cand_q[i - 1] + 1;
+  for (uint64_t r = prev; r <= src; r++) row[r] = (uint32_t)i;
+}
+
+// ---- replay of levenshtein_<4,T,false> on the query's own candidates ---------------------------
+struct Frame {
+  uint32_t lo, hi;   // candidate sub-range == trie node
+  uint8_t depth;     // depth of the node
+  uint8_t pos;       // position in the query word
+  int8_t dist;       // remaining budget
+  uint8_t stage;     // next move to try: 0 deletion, 1+2c substitution by child c, 2+2c insertion, 9 leaf
+};
+constexpr int EDIT_STACK = 48;
+
+__device__ __forceinline__ uint32_t lower_letter(const uint64_t *__restrict__ keys, uint32_t lo, uint32_t hi,
+                                                 uint32_t sh, uint32_t c) {
+  while (lo < hi) {
+    uint32_t mid = (lo + hi) >> 1;
+    if (((uint32_t)(keys[mid] >> sh) & 3u) < c) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+__global__ void __launch_bounds__(128)
+    edit_replay_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, int d,
+                       const uint32_t *__restrict__ cand_row, const uint32_t *__restrict__ cand_v,
+                       const uint64_t *__restrict__ cand_key, uint64_t *__restrict__ entries,
+                       uint32_t *__restrict__ entry_val, uint64_t cap, unsigned long long *__restrict__ counter) {
+  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= U) return;
+  const uint32_t seg = cand_row[r], m = cand_row[r + 1] - seg;
+  if (m == 0) return;
+  const uint64_t w = word_key[r];
+  const uint64_t *keys = cand_key + seg;
+  const uint32_t *ranks = cand_v + seg;
+  Frame stk[EDIT_STACK];
+  int sp = 0;
+  stk[sp++] = Frame{0u, m, 0, 0, (int8_t)d, 0};
+  while (sp > 0) {
+    Frame &f = stk[sp - 1];
+    const uint32_t st = f.stage++;
+    if (st == 0) {  // deletion: same node, next query position (also past the end, :202-203)
+      if (f.dist >= 1) {
+        stk[sp] = Frame{f.lo, f.hi, f.depth, (uint8_t)(f.pos + 1), (int8_t)(f.dist - 1), 0};
+        sp++;
+      }
+    } else if (st <= 8) {
+      const uint32_t c = (st - 1) >> 1;
+      const bool insertion = ((st - 1) & 1u) != 0;
+      if (f.depth >= n) { f.stage = 9; continue; }  // a leaf has no children
+      const uint32_t wl = f.pos < n ? (uint32_t)(w >> (2 * (n - 1 - f.pos))) & 3u : 0u;
+      if (c < wl) { f.stage = (uint8_t)(1 + 2 * wl); continue; }  // children start at word[position]
+      if (!insertion && f.pos >= n) continue;                      // substitution needs a query letter
+      const int nd = insertion ? f.dist - 1 : f.dist - (int)(c != wl);
+      if (nd < 0) continue;
+      const uint32_t sh = 2 * (n - 1 - f.depth);
+      const uint32_t clo = lower_letter(keys, f.lo, f.hi, sh, c);
+      const uint32_t chi = lower_letter(keys, clo, f.hi, sh, c + 1);
+      if (clo >= chi) { if (!insertion) f.stage++; continue; }  // no such child: skip its insertion too
+      stk[sp] = Frame{clo, chi, (uint8_t)(f.depth + 1), (uint8_t)(insertion ? f.pos : f.pos + 1), (int8_t)nd, 0};
+      sp++;
+    } else if (st == 9) {
+      if (f.pos >= n && f.depth == n && f.lo < f.hi) {  // yield node->leaf
+        const uint32_t v = ranks[f.lo];
+        unsigned long long p = atomicAdd(counter, 2ull);
+        if (p + 2 <= cap) {
+          entries[p] = (r << 32) | (uint32_t)r;       // own yield, in yield order
+          entry_val[p] = v;
+          entries[p + 1] = ((uint64_t)v << 32) | (uint32_t)r;  // r.leaf->neighbours.push_back(walk leaf)
+          entry_val[p + 1] = (uint32_t)r;
+        }
+      }
+    } else {
+      sp--;
+    }
+  }
+}
+
+int stage_neighbours_edit(State &s) {
+  const uint64_t U = s.unique;
+  const uint32_t n = s.cfg.word_length, d = s.cfg.distance;
+  s.n_entries = 0;
+  if (U == 0) return 0;
+  if (d > EDIT_MAX_D) throw CudaError{"edit distance > 3 is not supported (two deletion+insertion pairs)"};
+  if (n + d + 2 > EDIT_STACK) throw CudaError{"word too long for the edit replay stack"};
+  int k = 0;
+  const Lookup lk = s.lookup();
+
+  // phase 1: candidate pairs (with duplicates)
+  uint64_t cap = std::max<uint64_t>(s.entries.cap, std::max<uint64_t>(8 * U, 1u << 20));
+  uint64_t n_cand = 0;
+  for (int attempt = 0; attempt < 2; attempt++) {
+    s.entries.ensure(cap);
+    cap = s.entries.cap;
+    HUMID_CUDA(cudaMemsetAsync(s.counters.p + 5, 0, sizeof(unsigned long long), s.stream));
+    {
+      // variants probed per word: substitutions 3n + 9C(n,2) (+27C(n,3)), shifts 4n(n-1)(1 + 3n at d=3)
+      double subs = 3.0 * n + 4.5 * n * (n - 1) + (d >= 3 ? 4.5 * n * (n - 1) * (n - 2) : 0.0);
+      double shifts = 4.0 * n * (n - 1) * (d >= 3 ? 1.0 + 3.0 * n : 1.0);
+      Timed t(s, "edit_candidates", U, (uint64_t)(U * 8.0 * (1.0 + subs + shifts)));
+      edit_candidates_subst_kernel<<<grid_for(U * n, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, d, lk, s.entries.p,
+                                                                              cap, s.counters.p + 5);
+      edit_candidates_shift_kernel<<<grid_for(U * n * n, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, d, lk,
+                                                                                  s.entries.p, cap, s.counters.p + 5);
+      t.launches = 2;
+    }
+    k += 2;
+    HUMID_CUDA(cudaMemcpyAsync(&n_cand, s.counters.p + 5, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    if (n_cand <= cap) break;
+    cap = n_cand;
+  }
+  if (n_cand >= 0xFFFFFFFFull) throw CudaError{"too many edit-distance candidate pairs"};
+
+  // sort + unique -> per-query candidate lists in rank (== lexicographic) order
+  s.work_a.ensure(U + 2);  // cand_row
+  uint64_t n_distinct = 0;
+  if (n_cand) {
+    size_t t_sort = s.timer_begin("edit_candidates_unique", n_cand, n_cand * 28);
+    s.entries_alt.ensure(s.entries.cap);
+    uint64_t *kb[2] = {s.entries.p, s.entries_alt.p};
+    uint32_t *vb[2] = {nullptr, nullptr};
+    int ubits = 1;
+    while ((1ull << ubits) < U) ubits++;
+    int launches = 0;
+    int cur = radix_sort_u64(kb, vb, n_cand, 32 + ubits, s.scratch, s.scan_scratch, s.stream, &launches);
+    if (cur == 1) std::swap(s.entries, s.entries_alt);
+    s.seed_flag.ensure(n_cand);
+    s.seed_index.ensure(n_cand);
+    mark_unique_kernel<<<grid_for(n_cand, 256), 256, 0, s.stream>>>(s.entries.p, n_cand, s.seed_flag.p);
+    uint32_t *total = reinterpret_cast<uint32_t *>(s.counters.p + 6);
+    launches += 1 + exclusive_scan_u32(s.seed_flag.p, s.seed_index.p, n_cand, total, s.scan_scratch, s.stream);
+    uint32_t nd32 = 0;
+    HUMID_CUDA(cudaMemcpyAsync(&nd32, total, sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    n_distinct = nd32;
+    s.work_b.ensure(n_distinct + 1);   // cand_q
+    s.work_c.ensure(n_distinct + 1);   // cand_v
+    s.key_alt.ensure(n_distinct + 1);  // cand_key
+    compact_candidates_kernel<<<grid_for(n_cand, 256), 256, 0, s.stream>>>(
+        s.entries.p, s.seed_flag.p, s.seed_index.p, n_cand, s.word_key.p, s.work_b.p, s.work_c.p, s.key_alt.p);
+    launches++;
+    s.timer_end(t_sort, launches);
+    k += launches;
+  } else {
+    s.work_b.ensure(1);
+    s.work_c.ensure(1);
+    s.key_alt.ensure(1);
+  }
+  candidate_rows_kernel<<<grid_for(n_distinct + 1, 256), 256, 0, s.stream>>>(s.work_b.p, n_distinct, U, s.work_a.p);
+  k++;
+
+  // phase 2: replay
+  uint64_t ecap = std::max<uint64_t>(std::max<uint64_t>(s.entries_alt.cap, s.entry_val.cap),
+                                     std::max<uint64_t>(8 * n_distinct, 1u << 20));
+  for (int attempt = 0; attempt < 2; attempt++) {
+    // entries_alt is free again (the sorted candidates were compacted out of `entries`)
+    s.entries_alt.ensure(ecap);
+    s.entry_val.ensure(ecap);
+    ecap = std::min<uint64_t>(s.entries_alt.cap, s.entry_val.cap);
+    HUMID_CUDA(cudaMemsetAsync(s.counters.p + 2, 0, sizeof(unsigned long long), s.stream));
+    {
+      Timed t(s, "edit_replay", U, n_distinct * 12 + U * 16);
+      edit_replay_kernel<<<grid_for(U, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, (int)d, s.work_a.p, s.work_c.p,
+                                                                 s.key_alt.p, s.entries_alt.p, s.entry_val.p, ecap,
+                                                                 s.counters.p + 2);
+    }
+    k++;
+    HUMID_CUDA(cudaMemcpyAsync(&s.n_entries, s.counters.p + 2, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    if (s.n_entries <= ecap) break;
+    ecap = s.n_entries;
+  }
+  std::swap(s.entries, s.entries_alt);  // stage_csr sorts `entries` / `entry_val`
+  HUMID_CUDA(cudaGetLastError());
+  return k;
+}
+
 }  // namespace humid

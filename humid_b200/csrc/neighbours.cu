@@ -13,17 +13,6 @@
 
 namespace humid {
 
-__device__ __forceinline__ uint32_t table_find(const Slot *__restrict__ slots, uint64_t mask, uint64_t key) {
-  uint64_t idx = mix64(key) & mask;
-  while (true) {
-    uint4 v = __ldg(reinterpret_cast<const uint4 *>(slots + idx));
-    uint64_t k = ((uint64_t)v.y << 32) | v.x;
-    if (k == key) return v.z;  // rank (count field after rank_columns_kernel)
-    if (k == KEY_INVALID) return NONE32;
-    idx = (idx + 1) & mask;
-  }
-}
-
 __device__ __forceinline__ void emit_pair(uint64_t *entries, uint64_t cap, unsigned long long *counter, uint32_t a,
                                           uint32_t b) {
   unsigned long long pos = atomicAdd(counter, 2ull);
@@ -37,7 +26,7 @@ __device__ __forceinline__ void emit_pair(uint64_t *entries, uint64_t cap, unsig
 // be appended with one atomic per warp.
 __global__ void __launch_bounds__(256)
     hamming1_probe_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n,
-                          const Slot *__restrict__ slots, uint64_t mask, uint64_t *__restrict__ entries,
+                          const Lookup lk, uint64_t *__restrict__ entries,
                           uint64_t cap, unsigned long long *__restrict__ counter) {
   uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   uint64_t r = gid / n;
@@ -50,7 +39,7 @@ __global__ void __launch_bounds__(256)
 #pragma unroll
   for (uint32_t c = 1; c < 4; c++) {
     uint32_t hit = NONE32;
-    if (live && c > wl) hit = table_find(slots, mask, w + ((uint64_t)(c - wl) << sh));
+    if (live && c > wl) hit = lookup_rank(lk, w + ((uint64_t)(c - wl) << sh));
     unsigned m = __ballot_sync(0xffffffffu, hit != NONE32);
     if (m) {
       unsigned long long base = 0;
@@ -71,7 +60,7 @@ __global__ void __launch_bounds__(256)
 // d == 2: one thread per (word, first modified position p1).
 __global__ void __launch_bounds__(256)
     hamming2_probe_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n,
-                          const Slot *__restrict__ slots, uint64_t mask, uint64_t *__restrict__ entries,
+                          const Lookup lk, uint64_t *__restrict__ entries,
                           uint64_t cap, unsigned long long *__restrict__ counter) {
   uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   uint64_t r = gid / n;
@@ -82,13 +71,13 @@ __global__ void __launch_bounds__(256)
   uint32_t w1 = (uint32_t)(w >> sh1) & 3u;
   for (uint32_t c1 = w1 + 1; c1 < 4; c1++) {
     uint64_t v1 = w + ((uint64_t)(c1 - w1) << sh1);
-    uint32_t hit = table_find(slots, mask, v1);
+    uint32_t hit = lookup_rank(lk, v1);
     if (hit != NONE32) emit_pair(entries, cap, counter, (uint32_t)r, hit);
     for (uint32_t p2 = p1 + 1; p2 < n; p2++) {
       uint32_t sh2 = 2 * (n - 1 - p2);
       uint32_t w2 = (uint32_t)(w >> sh2) & 3u;
       for (uint32_t c2 = w2 + 1; c2 < 4; c2++) {
-        uint32_t h2 = table_find(slots, mask, v1 + ((uint64_t)(c2 - w2) << sh2));
+        uint32_t h2 = lookup_rank(lk, v1 + ((uint64_t)(c2 - w2) << sh2));
         if (h2 != NONE32) emit_pair(entries, cap, counter, (uint32_t)r, h2);
       }
     }
@@ -100,7 +89,7 @@ __global__ void __launch_bounds__(256)
 constexpr int HAM_MAX_D = 8;
 __global__ void __launch_bounds__(128)
     hammingd_probe_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, uint32_t d,
-                          const Slot *__restrict__ slots, uint64_t mask, uint64_t *__restrict__ entries,
+                          const Lookup lk, uint64_t *__restrict__ entries,
                           uint64_t cap, unsigned long long *__restrict__ counter) {
   uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   uint64_t r = gid / n;
@@ -123,7 +112,7 @@ __global__ void __launch_bounds__(128)
       continue;
     }
     cur = (cur & ~(3ull << sh)) | ((uint64_t)let[depth] << sh);
-    uint32_t hit = table_find(slots, mask, cur);
+    uint32_t hit = lookup_rank(lk, cur);
     if (hit != NONE32) emit_pair(entries, cap, counter, (uint32_t)r, hit);
     if (depth + 1 < (int)d && pos[depth] + 1 < n) {
       depth++;
@@ -152,13 +141,13 @@ int stage_neighbours_hamming(State &s) {
             (uint64_t)(U * 8.0 * (1.0 + probes)));
     if (d == 1)
       hamming1_probe_kernel<<<grid_for(threads, 256), 256, 0, s.stream>>>(
-          s.word_key.p, U, n, s.slots.p, s.table_cap - 1, s.entries.p, cap, s.counters.p + 2);
+          s.word_key.p, U, n, s.lookup(), s.entries.p, cap, s.counters.p + 2);
     else if (d == 2)
       hamming2_probe_kernel<<<grid_for(threads, 256), 256, 0, s.stream>>>(
-          s.word_key.p, U, n, s.slots.p, s.table_cap - 1, s.entries.p, cap, s.counters.p + 2);
+          s.word_key.p, U, n, s.lookup(), s.entries.p, cap, s.counters.p + 2);
     else
       hammingd_probe_kernel<<<grid_for(threads, 128), 128, 0, s.stream>>>(
-          s.word_key.p, U, n, d, s.slots.p, s.table_cap - 1, s.entries.p, cap, s.counters.p + 2);
+          s.word_key.p, U, n, d, s.lookup(), s.entries.p, cap, s.counters.p + 2);
     k++;
     HUMID_CUDA(cudaMemcpyAsync(&s.n_entries, s.counters.p + 2, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));

@@ -74,6 +74,9 @@ struct State {
   // word table
   DevBuf<Slot> slots;
   uint64_t table_cap = 0;  // power of two
+  DevBuf<uint4> filter;    // fingerprint buckets in front of the table (common.cuh)
+  uint32_t filter_buckets = 0;
+  Lookup lookup() const { return Lookup{slots.p, table_cap - 1, filter_buckets ? filter.p : nullptr, filter_buckets}; }
 
   // rank-ordered columns
   DevBuf<uint64_t> word_key, key_alt;
@@ -134,7 +137,7 @@ struct Timed {
 
 // ---- stage launchers (each returns the number of kernels it launched) --------------------
 int stage_pack(State &s, const uint8_t *d_chars, const uint16_t *d_seg_len, uint64_t first, uint64_t n);
-int stage_build_table(State &s);       // insert + compact + sort + rank columns
+int stage_build_table(State &s);       // insert + compact + sort + rank columns + filter
 int stage_neighbours_hamming(State &s);
 int stage_neighbours_edit(State &s);
 int stage_csr(State &s);               // sort entries, row_ptr / col

@@ -2,6 +2,8 @@
 //
 // Replaces makeWord/getNucleotides/makeStringSize_ (reference src/fastq.cc:57-66, :116-161),
 // Trie::add (lib/trie/src/trieFunctions.tcc:45-59) and Trie::walk order (:129-143).
+#include <algorithm>
+
 #include "state.cuh"
 
 namespace humid {
@@ -110,24 +112,44 @@ __global__ void __launch_bounds__(256)
   atomicMin(&slots[idx].first, (uint32_t)t);   // first tuple in input order
 }
 
-// Occupied slots -> (key, slot) pairs, any order (they are sorted next).
+// Occupied slots -> (key, slot) pairs, any order (they are sorted next).  One atomic per CTA:
+// warp ballots -> per-warp counts -> CTA prefix in shared memory.
+constexpr int COMPACT_ITEMS = 8;
 __global__ void __launch_bounds__(256)
     table_compact_kernel(const Slot *__restrict__ slots, uint64_t cap, uint64_t *__restrict__ keys_out,
                          uint32_t *__restrict__ slot_out, unsigned long long *__restrict__ counter) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  uint64_t key = KEY_INVALID;
-  if (i < cap) key = slots[i].key;
-  bool occ = key != KEY_INVALID;
-  unsigned m = __ballot_sync(0xffffffffu, occ);
-  if (m == 0) return;
-  unsigned long long base = 0;
-  int leader = __ffs(m) - 1;
-  if ((int)lane_id() == leader) base = atomicAdd(counter, (unsigned long long)__popc(m));
-  base = __shfl_sync(0xffffffffu, base, leader);
-  if (occ) {
-    uint64_t pos = base + __popc(m & ((1u << lane_id()) - 1u));
-    keys_out[pos] = key;
-    slot_out[pos] = (uint32_t)i;
+  __shared__ uint32_t warp_cnt[COMPACT_ITEMS][8];
+  __shared__ unsigned long long cta_base;
+  const uint64_t base = (uint64_t)blockIdx.x * (256 * COMPACT_ITEMS);
+  const uint32_t lane = lane_id(), w = threadIdx.x >> 5;
+  uint64_t key[COMPACT_ITEMS];
+  unsigned bal[COMPACT_ITEMS];
+#pragma unroll
+  for (int j = 0; j < COMPACT_ITEMS; j++) {
+    uint64_t i = base + (uint64_t)j * 256 + threadIdx.x;
+    key[j] = i < cap ? ld_stream_u64(&slots[i].key) : KEY_INVALID;
+    bal[j] = __ballot_sync(0xffffffffu, key[j] != KEY_INVALID);
+    if (lane == 0) warp_cnt[j][w] = __popc(bal[j]);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t run = 0;
+    for (int j = 0; j < COMPACT_ITEMS; j++)
+      for (int k = 0; k < 8; k++) {
+        uint32_t c = warp_cnt[j][k];
+        warp_cnt[j][k] = run;
+        run += c;
+      }
+    cta_base = run ? atomicAdd(counter, (unsigned long long)run) : 0ull;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < COMPACT_ITEMS; j++) {
+    if (key[j] != KEY_INVALID) {
+      uint64_t pos = cta_base + warp_cnt[j][w] + __popc(bal[j] & ((1u << lane) - 1u));
+      keys_out[pos] = key[j];
+      slot_out[pos] = (uint32_t)(base + (uint64_t)j * 256 + threadIdx.x);
+    }
   }
 }
 
@@ -143,6 +165,47 @@ __global__ void __launch_bounds__(256)
   word_count[r] = v.z;
   word_first[r] = v.w;
   sl->count = (uint32_t)r;
+}
+
+// Fingerprint filter over the distinct words (layout: common.cuh).  One CAS per word into an
+// L2-resident array.
+__global__ void __launch_bounds__(256)
+    filter_build_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t *words, uint32_t n_buckets) {
+  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= U) return;
+  const uint64_t h = mix64(word_key[r]);
+  uint32_t *w = words + 4ull * filter_bucket(h, n_buckets);
+  const uint32_t fp = filter_fp(h);
+  const uint32_t start = (uint32_t)(h >> 20) & 3u;
+  for (uint32_t t = 0; t < 4; t++) {
+    const uint32_t wi = (start + t) & 3u;
+    uint32_t old = *reinterpret_cast<volatile uint32_t *>(w + wi);
+    while (true) {
+      int b = -1;
+      for (int q = wi == 0 ? 1 : 0; q < 4; q++)
+        if (((old >> (8 * q)) & 0xFFu) == 0u) { b = q; break; }
+      if (b < 0) break;  // word full
+      uint32_t prev = atomicCAS(w + wi, old, old | (fp << (8 * b)));
+      if (prev == old) return;
+      old = prev;
+    }
+  }
+  atomicOr(w, 1u);  // bucket overflowed: queries falling here always go to the table
+}
+
+static int stage_build_filter(State &s) {
+  const uint64_t U = s.unique;
+  s.filter_buckets = 0;
+  if (U == 0) return 0;
+  uint64_t nb = std::max<uint64_t>(1024, U / 5 + 1);
+  if (nb > 0xFFFFFFF0ull) return 0;
+  s.filter.ensure(nb);
+  Timed t(s, "filter_build", U, U * 9 + nb * 16);
+  HUMID_CUDA(cudaMemsetAsync(s.filter.p, 0, nb * sizeof(uint4), s.stream));
+  filter_build_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.word_key.p, U, reinterpret_cast<uint32_t *>(s.filter.p),
+                                                              (uint32_t)nb);
+  s.filter_buckets = (uint32_t)nb;
+  return 1;
 }
 
 int stage_build_table(State &s) {
@@ -174,7 +237,7 @@ int stage_build_table(State &s) {
   HUMID_CUDA(cudaMemsetAsync(s.counters.p + 1, 0, sizeof(unsigned long long), s.stream));
   {
     Timed t(s, "table_compact", cap, cap * 8 + s.usable * 12);
-    table_compact_kernel<<<grid_for(cap, 256), 256, 0, s.stream>>>(s.slots.p, cap, s.word_key.p, s.word_slot.p,
+    table_compact_kernel<<<grid_for(cap, 256, COMPACT_ITEMS), 256, 0, s.stream>>>(s.slots.p, cap, s.word_key.p, s.word_slot.p,
                                                                    s.counters.p + 1);
   }
   k++;
@@ -204,6 +267,7 @@ int stage_build_table(State &s) {
                                                                 s.word_first.p);
     k++;
   }
+  k += stage_build_filter(s);
   HUMID_CUDA(cudaGetLastError());
   return k;
 }
