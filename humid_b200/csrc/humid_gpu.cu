@@ -8,33 +8,9 @@
 
 using namespace humid;
 
-struct humid_gpu {
-  State s;
-};
+#include "abi_internal.cuh"
 
-static thread_local std::string g_create_error;
-
-static int fail(humid_gpu *h, int code, const std::string &msg) {
-  if (h) h->s.last_error = msg; else g_create_error = msg;
-  return code;
-}
-
-// Runs `body`, mapping C++ failures onto the C error codes.
-static int guarded(humid_gpu *h, const std::function<void()> &body) {
-  try {
-    body();
-    return HUMID_GPU_OK;
-  } catch (const CudaError &e) {
-    bool oom = e.msg.find("out of memory") != std::string::npos;
-    return fail(h, oom ? HUMID_GPU_ERR_MEMORY : HUMID_GPU_ERR_CUDA, e.msg);
-  } catch (const std::bad_alloc &) {
-    return fail(h, HUMID_GPU_ERR_MEMORY, "host allocation failed");
-  } catch (const std::exception &e) {
-    return fail(h, HUMID_GPU_ERR_CUDA, e.what());
-  }
-}
-
-static void resolve_stats(State &s) {
+void humid::resolve_stats(State &s) {
   for (auto &st : s.stats) {
     if (!st.e0) continue;
     HUMID_CUDA(cudaEventSynchronize(st.e1));
@@ -59,7 +35,7 @@ int humid_gpu_abi_version(void) { return HUMID_GPU_ABI_VERSION; }
 
 void *humid_gpu_stream(humid_gpu *h) { return h ? (void *)h->s.stream : nullptr; }
 
-const char *humid_gpu_last_error(const humid_gpu *h) { return h ? h->s.last_error.c_str() : g_create_error.c_str(); }
+const char *humid_gpu_last_error(const humid_gpu *h) { return h ? h->s.last_error.c_str() : create_error().c_str(); }
 
 int humid_gpu_create(const humid_gpu_config *cfg, humid_gpu **out) {
   if (!cfg || !out) return fail(nullptr, HUMID_GPU_ERR_ARG, "humid_gpu_create: null argument");
@@ -83,13 +59,13 @@ int humid_gpu_create(const humid_gpu_config *cfg, humid_gpu **out) {
     if (cfg->device >= 0) HUMID_CUDA(cudaSetDevice(cfg->device));
     HUMID_CUDA(cudaGetDevice(&s.device));
     HUMID_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
-    s.counters.ensure(16);
-    HUMID_CUDA(cudaMemsetAsync(s.counters.p, 0, 16 * sizeof(unsigned long long), s.stream));
+    s.counters.ensure(64);
+    HUMID_CUDA(cudaMemsetAsync(s.counters.p, 0, 64 * sizeof(unsigned long long), s.stream));
     if (cfg->expected_tuples) s.tuple_key.ensure(cfg->expected_tuples);
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
   });
   if (rc != HUMID_GPU_OK) {
-    g_create_error = h->s.last_error;
+    create_error() = h->s.last_error;
     delete h;
     return rc;
   }
@@ -110,6 +86,7 @@ void humid_gpu_destroy(humid_gpu *h) {
   s.comp.release(); s.label.release(); s.members.release(); s.seg_start.release(); s.seg_end.release();
   s.work_a.release(); s.work_b.release(); s.work_c.release(); s.seed_flag.release(); s.seed_index.release();
   s.seed_size.release(); s.seed_max.release(); s.cluster_size.release(); s.cluster_max.release();
+  s.shard_slots.release(); s.local_word_grank.release(); s.filter.release();
   s.keep_bits.release(); s.out_ids.release(); s.scratch.release(); s.scan_scratch.release();
   if (s.stream) cudaStreamDestroy(s.stream);
   delete h;
@@ -124,8 +101,12 @@ int humid_gpu_reset(humid_gpu *h) {
     clear_stats(s);
     s.n_tuples = s.usable = s.unique = s.n_entries = s.n_clusters = 0;
     s.finalized = false;
+    s.shard_mode = false;
+    s.report_tuples = s.report_usable = s.tuple_base = s.n_local_words = s.n_shard_words = 0;
+    s.part = 0;
+    s.n_parts = 1;
     for (int i = 0; i < 3; i++) s.hist_done[i] = false;
-    HUMID_CUDA(cudaMemsetAsync(s.counters.p, 0, 16 * sizeof(unsigned long long), s.stream));
+    HUMID_CUDA(cudaMemsetAsync(s.counters.p, 0, 64 * sizeof(unsigned long long), s.stream));
   });
 }
 
@@ -179,7 +160,10 @@ int humid_gpu_finalize(humid_gpu *h) {
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
     const bool edit2 = s.cfg.edit && s.cfg.distance >= 2;
+    if (s.shard_mode) throw CudaError{"finalize on a handle that is in shard mode"};
     stage_build_table(s);
+    s.report_tuples = s.n_tuples;
+    s.report_usable = s.usable;
     if (edit2) stage_neighbours_edit(s); else stage_neighbours_hamming(s);
     stage_csr(s);
     stage_cluster(s);
@@ -193,8 +177,8 @@ int humid_gpu_finalize(humid_gpu *h) {
 int humid_gpu_counts(humid_gpu *h, uint64_t *total, uint64_t *usable, uint64_t *unique, uint64_t *clusters) {
   if (!h) return HUMID_GPU_ERR_ARG;
   if (!h->s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "not finalized");
-  if (total) *total = h->s.n_tuples;
-  if (usable) *usable = h->s.usable;
+  if (total) *total = h->s.report_tuples;
+  if (usable) *usable = h->s.report_usable;
   if (unique) *unique = h->s.unique;
   if (clusters) *clusters = h->s.n_clusters;
   return HUMID_GPU_OK;
@@ -226,7 +210,7 @@ int humid_gpu_keep_mask(humid_gpu *h, uint64_t first_tuple, uint64_t n, uint64_t
   if (!h || (n && !bits)) return HUMID_GPU_ERR_ARG;
   State &s = h->s;
   if (!s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "not finalized");
-  if (first_tuple + n > s.n_tuples) return fail(h, HUMID_GPU_ERR_ARG, "tuple range out of bounds");
+  if (first_tuple + n > s.report_tuples) return fail(h, HUMID_GPU_ERR_ARG, "tuple range out of bounds");
   if (first_tuple % 64) return fail(h, HUMID_GPU_ERR_ARG, "first_tuple must be a multiple of 64");
   if (n == 0) return HUMID_GPU_OK;
   return guarded(h, [&] {
@@ -242,6 +226,7 @@ int humid_gpu_cluster_ids(humid_gpu *h, uint64_t first_tuple, uint64_t n, uint32
   if (!h || (n && !ids)) return HUMID_GPU_ERR_ARG;
   State &s = h->s;
   if (!s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "not finalized");
+  if (s.shard_mode) return fail(h, HUMID_GPU_ERR_ARG, "use humid_gpu_shard_cluster_ids in shard mode");
   if (first_tuple + n > s.n_tuples) return fail(h, HUMID_GPU_ERR_ARG, "tuple range out of bounds");
   if (n == 0) return HUMID_GPU_OK;
   return guarded(h, [&] {

@@ -22,7 +22,7 @@ __global__ void __launch_bounds__(256)
 }
 
 int stage_keep(State &s) {
-  uint64_t words = (s.n_tuples + 31) / 32 + 2;  // +2: the D2H view is in 64-bit units
+  uint64_t words = (s.report_tuples + 31) / 32 + 2;  // +2: the D2H view is in 64-bit units
   s.keep_bits.ensure(words);
   HUMID_CUDA(cudaMemsetAsync(s.keep_bits.p, 0, words * sizeof(uint32_t), s.stream));
   if (s.n_clusters == 0) return 0;
@@ -107,7 +107,7 @@ int stage_histogram(State &s, int which) {
                                                              kb[0]);
   k++;
   // counts and cluster sizes are bounded by the number of tuples, list lengths by the entries
-  uint64_t bound = which == HUMID_HIST_NEIGHBOURS ? s.n_entries : s.n_tuples;
+  uint64_t bound = which == HUMID_HIST_NEIGHBOURS ? s.n_entries : s.report_tuples;
   int bits = 1;
   while (bits < 64 && (1ull << bits) <= bound) bits++;
   int launches = 0;

@@ -76,7 +76,26 @@ struct State {
   uint64_t table_cap = 0;  // power of two
   DevBuf<uint4> filter;    // fingerprint buckets in front of the table (common.cuh)
   uint32_t filter_buckets = 0;
-  Lookup lookup() const { return Lookup{slots.p, table_cap - 1, filter_buckets ? filter.p : nullptr, filter_buckets}; }
+  Lookup lookup() const {
+    if (shard_mode) return Lookup{shard_slots.p, shard_cap - 1, filter_buckets ? filter.p : nullptr, filter_buckets};
+    return Lookup{slots.p, table_cap - 1, filter_buckets ? filter.p : nullptr, filter_buckets};
+  }
+
+  // what humid_gpu_counts reports / what keep_bits covers (the whole job in shard mode)
+  uint64_t report_tuples = 0, report_usable = 0;
+
+  // shard mode (include/humid_gpu_shard.h): `slots` stays the table of this rank's own tuples
+  // (key -> local word index), `shard_slots` is the table of the words this shard owns
+  // (key -> shard-local rank); word_key/word_count/word_first switch from the former to the
+  // latter at import_words and to the gathered whole-job columns at import_graph.
+  bool shard_mode = false;
+  uint64_t tuple_base = 0, n_local_words = 0, n_shard_words = 0;
+  DevBuf<Slot> shard_slots;
+  uint64_t shard_cap = 0;
+  DevBuf<uint32_t> local_word_grank;
+  uint32_t part = 0, n_parts = 1;
+  uint64_t splitters[16] = {0};
+  uint64_t bases[17] = {0};
 
   // rank-ordered columns
   DevBuf<uint64_t> word_key, key_alt;
@@ -137,7 +156,8 @@ struct Timed {
 
 // ---- stage launchers (each returns the number of kernels it launched) --------------------
 int stage_pack(State &s, const uint8_t *d_chars, const uint16_t *d_seg_len, uint64_t first, uint64_t n);
-int stage_build_table(State &s);       // insert + compact + sort + rank columns + filter
+int stage_build_table(State &s, bool with_filter = true);  // insert + compact + sort + rank columns (+ filter)
+int stage_build_filter(State &s);      // fingerprint filter over word_key[0..unique)
 int stage_neighbours_hamming(State &s);
 int stage_neighbours_edit(State &s);
 int stage_csr(State &s);               // sort entries, row_ptr / col

@@ -193,7 +193,7 @@ __global__ void __launch_bounds__(256)
   atomicOr(w, 1u);  // bucket overflowed: queries falling here always go to the table
 }
 
-static int stage_build_filter(State &s) {
+int stage_build_filter(State &s) {
   const uint64_t U = s.unique;
   s.filter_buckets = 0;
   if (U == 0) return 0;
@@ -208,7 +208,7 @@ static int stage_build_filter(State &s) {
   return 1;
 }
 
-int stage_build_table(State &s) {
+int stage_build_table(State &s, bool with_filter) {
   int k = 0;
   HUMID_CUDA(cudaMemcpyAsync(&s.usable, s.counters.p + 0, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
   HUMID_CUDA(cudaStreamSynchronize(s.stream));
@@ -267,7 +267,7 @@ int stage_build_table(State &s) {
                                                                 s.word_first.p);
     k++;
   }
-  k += stage_build_filter(s);
+  if (with_filter) k += stage_build_filter(s);
   HUMID_CUDA(cudaGetLastError());
   return k;
 }

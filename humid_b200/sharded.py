@@ -1,0 +1,400 @@
+"""One-process-per-GPU deduplication: the phases of include/humid_gpu_shard.h with the
+exchanges between them done by torch.distributed (NCCL over NVLink on the GPU box, gloo in the
+CPU tests).  DESIGN.md §5 describes the partitioning.
+
+The reference is a single process with one global trie (src/humid.cc:369-409); the bar for
+this module is that every rank ends up with exactly the results the single-GPU path (and the
+reference) gives for the concatenation of all ranks' tuples in rank order.
+
+`ShardedDedup` is the orchestration (splitters, all-to-all-v, all-gather); the per-rank compute
+is an *engine*: `CudaShardEngine` binds the C ABI.  The engine methods take and return torch
+tensors that live on the engine's device, so the same orchestration runs over gloo with a
+CPU engine in tests/ (a checker built on the oracle — not part of the product).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import api
+
+MAX_PARTS = 16
+SAMPLES_PER_RANK = 4096
+NONE32 = 0xFFFFFFFF
+
+
+def _bind(L):
+    if getattr(L, "_shard_bound", False):
+        return L
+    vp, u64, u32 = C.c_void_p, C.c_uint64, C.c_uint32
+    P = C.POINTER
+    L.humid_gpu_shard_local_words.argtypes = [vp, u64, P(u64), P(u64)]
+    L.humid_gpu_shard_sample_keys.argtypes = [vp, u32, vp]
+    L.humid_gpu_shard_split.argtypes = [vp, vp, u32, vp]
+    L.humid_gpu_shard_export_words.argtypes = [vp, vp, vp, vp]
+    L.humid_gpu_shard_import_words.argtypes = [vp, vp, vp, vp, u64, vp, P(u64)]
+    L.humid_gpu_shard_set_layout.argtypes = [vp, u32, u32, vp, vp]
+    L.humid_gpu_shard_set_word_ranks.argtypes = [vp, vp, u64]
+    L.humid_gpu_shard_probe_count.argtypes = [vp, vp]
+    L.humid_gpu_shard_probe.argtypes = [vp, vp, vp, vp]
+    L.humid_gpu_shard_answer.argtypes = [vp, vp, vp, u64, vp]
+    L.humid_gpu_shard_apply_answers.argtypes = [vp, vp, vp, u64]
+    L.humid_gpu_shard_build_rows.argtypes = [vp, P(u64)]
+    L.humid_gpu_shard_export_graph.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.humid_gpu_shard_import_graph.argtypes = [vp, u64, u64, u64, u64, vp, vp, vp, vp, vp]
+    L.humid_gpu_shard_cluster_ids.argtypes = [vp, u64, u64, vp]
+    L._shard_bound = True
+    return L
+
+
+SHARD_EXPORTS = [
+    "humid_gpu_shard_local_words", "humid_gpu_shard_sample_keys", "humid_gpu_shard_split",
+    "humid_gpu_shard_export_words", "humid_gpu_shard_import_words", "humid_gpu_shard_set_layout",
+    "humid_gpu_shard_set_word_ranks", "humid_gpu_shard_probe_count", "humid_gpu_shard_probe",
+    "humid_gpu_shard_answer", "humid_gpu_shard_apply_answers", "humid_gpu_shard_build_rows",
+    "humid_gpu_shard_export_graph", "humid_gpu_shard_import_graph", "humid_gpu_shard_cluster_ids",
+]
+
+
+def _dp(t: Optional[torch.Tensor]):
+    return None if t is None or t.numel() == 0 else C.c_void_p(t.data_ptr())
+
+
+class CudaShardEngine(api.Dedup):
+    """The C ABI (include/humid_gpu.h + include/humid_gpu_shard.h) on one GPU."""
+
+    def __init__(self, device: int = 0, **kw):
+        super().__init__(device=device, **kw)
+        _bind(self._L)
+        self.device = torch.device("cuda", device)
+
+    def _empty(self, n, dtype):
+        return torch.empty(max(int(n), 0), dtype=dtype, device=self.device)
+
+    def _sync(self):
+        """The library works on its own stream: tensors produced by torch / NCCL on torch's
+        current stream must be complete before a call that reads them."""
+        torch.cuda.current_stream(self.device).synchronize()
+
+    # torch has no unsigned 64/32-bit arithmetic: keys travel as int64, ranks/counts as int32
+    def local_words(self, tuple_offset: int) -> Tuple[int, int]:
+        n, u = C.c_uint64(0), C.c_uint64(0)
+        self._check(self._L.humid_gpu_shard_local_words(self._h, tuple_offset, C.byref(n), C.byref(u)), "shard_local_words")
+        self.n_local_words = int(n.value)
+        return int(n.value), int(u.value)
+
+    def sample_keys(self, n: int) -> np.ndarray:
+        out = np.zeros(n, dtype=np.uint64)
+        self._check(self._L.humid_gpu_shard_sample_keys(self._h, n, out.ctypes.data_as(C.c_void_p)), "shard_sample_keys")
+        return out
+
+    def split(self, splitters: np.ndarray, n_parts: int) -> np.ndarray:
+        sp = np.ascontiguousarray(splitters, dtype=np.uint64)
+        out = np.zeros(n_parts, dtype=np.uint64)
+        self._check(self._L.humid_gpu_shard_split(self._h, sp.ctypes.data_as(C.c_void_p), n_parts,
+                                                  out.ctypes.data_as(C.c_void_p)), "shard_split")
+        return out.astype(np.int64)
+
+    def export_words(self):
+        n = self.n_local_words
+        k, c, f = self._empty(n, torch.int64), self._empty(n, torch.int32), self._empty(n, torch.int32)
+        self._check(self._L.humid_gpu_shard_export_words(self._h, _dp(k), _dp(c), _dp(f)), "shard_export_words")
+        return k, c, f
+
+    def import_words(self, keys, counts, first):
+        self._sync()
+        n = keys.numel()
+        lr = self._empty(n, torch.int32)
+        u = C.c_uint64(0)
+        self._check(self._L.humid_gpu_shard_import_words(self._h, _dp(keys), _dp(counts), _dp(first), n, _dp(lr),
+                                                         C.byref(u)), "shard_import_words")
+        self.n_shard_words = int(u.value)
+        return lr, int(u.value)
+
+    def set_layout(self, part: int, n_parts: int, splitters: np.ndarray, bases: np.ndarray):
+        sp = np.ascontiguousarray(splitters, dtype=np.uint64)
+        b = np.ascontiguousarray(bases, dtype=np.uint64)
+        self._check(self._L.humid_gpu_shard_set_layout(self._h, part, n_parts, sp.ctypes.data_as(C.c_void_p),
+                                                       b.ctypes.data_as(C.c_void_p)), "shard_set_layout")
+
+    def set_word_ranks(self, granks):
+        self._sync()
+        self._check(self._L.humid_gpu_shard_set_word_ranks(self._h, _dp(granks), granks.numel()), "shard_set_word_ranks")
+
+    def probe_count(self, n_parts: int) -> np.ndarray:
+        out = np.zeros(MAX_PARTS, dtype=np.uint64)
+        self._check(self._L.humid_gpu_shard_probe_count(self._h, out.ctypes.data_as(C.c_void_p)), "shard_probe_count")
+        return out[:n_parts].astype(np.int64)
+
+    def probe(self, counts: np.ndarray):
+        off = np.zeros(len(counts) + 1, dtype=np.uint64)
+        off[1:] = np.cumsum(counts)
+        n = int(off[-1])
+        qk, qs = self._empty(n, torch.int64), self._empty(n, torch.int32)
+        self._check(self._L.humid_gpu_shard_probe(self._h, _dp(qk), _dp(qs), off.ctypes.data_as(C.c_void_p)), "shard_probe")
+        return qk, qs
+
+    def answer(self, qkeys, qsrc):
+        self._sync()
+        ans = self._empty(qkeys.numel(), torch.int32)
+        self._check(self._L.humid_gpu_shard_answer(self._h, _dp(qkeys), _dp(qsrc), qkeys.numel(), _dp(ans)), "shard_answer")
+        return ans
+
+    def apply_answers(self, qsrc, answers):
+        self._sync()
+        self._check(self._L.humid_gpu_shard_apply_answers(self._h, _dp(qsrc), _dp(answers), qsrc.numel()),
+                    "shard_apply_answers")
+
+    def build_rows(self) -> int:
+        e = C.c_uint64(0)
+        self._check(self._L.humid_gpu_shard_build_rows(self._h, C.byref(e)), "shard_build_rows")
+        self.n_shard_entries = int(e.value)
+        return int(e.value)
+
+    def export_graph(self):
+        u, e = self.n_shard_words, self.n_shard_entries
+        k, c, f, d = (self._empty(u, torch.int64), self._empty(u, torch.int32), self._empty(u, torch.int32),
+                      self._empty(u, torch.int32))
+        col = self._empty(e, torch.int32)
+        self._check(self._L.humid_gpu_shard_export_graph(self._h, _dp(k), _dp(c), _dp(f), _dp(d), _dp(col)),
+                    "shard_export_graph")
+        return k, c, f, d, col
+
+    def import_graph(self, n_tuples: int, n_usable: int, keys, counts, first, degree, col):
+        self._sync()
+        self._check(self._L.humid_gpu_shard_import_graph(self._h, keys.numel(), col.numel(), n_tuples, n_usable, _dp(keys),
+                                                         _dp(counts), _dp(first), _dp(degree), _dp(col)),
+                    "shard_import_graph")
+        self.n_tuples_total = n_tuples
+
+    def local_cluster_ids(self, first: int, n: int) -> np.ndarray:
+        ids = np.zeros(max(n, 1), dtype=np.uint32)
+        self._check(self._L.humid_gpu_shard_cluster_ids(self._h, first, n, ids.ctypes.data_as(C.c_void_p)),
+                    "shard_cluster_ids")
+        return ids[:n]
+
+    def global_keep_bits(self, first: int, n: int) -> np.ndarray:
+        """bool[n] for GLOBAL tuple indices first..first+n."""
+        lo = (first // 64) * 64
+        m = first + n - lo
+        bits = np.zeros((m + 63) // 64 + 1, dtype=np.uint64)
+        self._check(self._L.humid_gpu_keep_mask(self._h, lo, m, bits.ctypes.data_as(C.c_void_p)), "keep_mask")
+        return np.unpackbits(bits.view(np.uint8), bitorder="little")[first - lo: first - lo + n].astype(bool)
+
+
+# ----------------------------------------------------------------------------------------------
+class TorchComm:
+    """The two collectives the path needs, over a torch.distributed process group."""
+
+    def __init__(self, group=None):
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+
+    def all_to_all_single(self, out, inp, out_splits=None, in_splits=None):
+        dist.all_to_all_single(out, inp, output_split_sizes=out_splits, input_split_sizes=in_splits, group=self.group)
+
+    def all_gather_into_tensor(self, out, inp):
+        dist.all_gather_into_tensor(out, inp, group=self.group)
+
+
+class ThreadComm:
+    """Loop-back collectives between `world` threads of ONE process (tests: several logical
+    shards on one GPU run the same orchestration without a process group).  Every engine call
+    synchronises its stream before returning, so no kernel ever waits on another rank."""
+
+    class Shared:
+        def __init__(self, world: int):
+            import threading
+
+            self.world = world
+            self.barrier = threading.Barrier(world)
+            self.slots = [None] * world
+
+    def __init__(self, shared: "ThreadComm.Shared", rank: int):
+        self.sh, self.rank, self.world = shared, rank, shared.world
+
+    def _exchange(self, item):
+        self.sh.slots[self.rank] = item
+        self.sh.barrier.wait()
+        items = list(self.sh.slots)
+        self.sh.barrier.wait()
+        return items
+
+    def all_to_all_single(self, out, inp, out_splits=None, in_splits=None):
+        W = self.world
+        if in_splits is None:
+            in_splits = [inp.numel() // W] * W
+        offs = np.concatenate([[0], np.cumsum(in_splits)])
+        items = self._exchange((inp, offs))
+        parts = [t[int(o[self.rank]): int(o[self.rank + 1])] for (t, o) in items]
+        got = torch.cat(parts) if parts else inp[:0]
+        out.copy_(got.to(out.device))
+        self.sh.barrier.wait()  # senders may reuse their buffers only after everyone copied
+
+    def all_gather_into_tensor(self, out, inp):
+        items = self._exchange(inp)
+        out.copy_(torch.cat([t.to(out.device) for t in items]))
+        self.sh.barrier.wait()
+
+
+def all_to_all_v(comm, t: torch.Tensor, send_counts: Sequence[int]) -> Tuple[torch.Tensor, List[int]]:
+    """t is laid out destination-major; returns (received, recv_counts) source-major."""
+    sc = torch.tensor([int(x) for x in send_counts], dtype=torch.int64, device=t.device)
+    rc = torch.empty(comm.world, dtype=torch.int64, device=t.device)
+    comm.all_to_all_single(rc, sc)
+    recv_counts = [int(x) for x in rc.tolist()]
+    return all_to_all_fixed(comm, t, send_counts, recv_counts), recv_counts
+
+
+def all_to_all_fixed(comm, t: torch.Tensor, send_counts: Sequence[int], recv_counts: Sequence[int]) -> torch.Tensor:
+    out = torch.empty(int(sum(recv_counts)), dtype=t.dtype, device=t.device)
+    comm.all_to_all_single(out, t, [int(x) for x in recv_counts], [int(x) for x in send_counts])
+    return out
+
+
+def all_gather_v(comm, t: torch.Tensor, sizes: Sequence[int]) -> torch.Tensor:
+    """Concatenation of every rank's `t` (sizes[r] elements) in rank order."""
+    m = max(max(sizes), 1)
+    pad = torch.zeros(m, dtype=t.dtype, device=t.device)
+    pad[: t.numel()] = t
+    buf = torch.empty(comm.world * m, dtype=t.dtype, device=t.device)
+    comm.all_gather_into_tensor(buf, pad)
+    return torch.cat([buf[r * m: r * m + sizes[r]] for r in range(comm.world)])
+
+
+class ShardedDedup:
+    """Same call sequence as `api.Dedup` (add_batch* … finalize … results), one instance per
+    rank; rank r's tuples are the r-th contiguous slice of the job's input order."""
+
+    def __init__(self, engine=None, group=None, comm=None, **kw):
+        self.comm = comm if comm is not None else TorchComm(group)
+        self.rank, self.world = self.comm.rank, self.comm.world
+        if self.world > MAX_PARTS:
+            raise api.HumidGpuError(f"at most {MAX_PARTS} shards")
+        self.eng = engine if engine is not None else CudaShardEngine(**kw)
+        self.n_local = 0
+        self.stage_ms: Dict[str, float] = {}
+
+    # -- pass 1 -------------------------------------------------------------------------------
+    @property
+    def stream(self) -> int:
+        return self.eng.stream
+
+    def reset(self):
+        self.eng.reset()
+        self.n_local = 0
+
+    def add_batch(self, chars, seg_len=None):
+        self.eng.add_batch(chars, seg_len)
+        self.n_local = self.eng.n_tuples
+
+    def add_batch_device(self, d_chars: int, n: int, d_seg_len: int = 0):
+        self.eng.add_batch_device(d_chars, n, d_seg_len)
+        self.n_local = self.eng.n_tuples
+
+    def _gather_ints(self, *vals: int) -> np.ndarray:
+        dev = self.eng.device
+        t = torch.tensor(list(vals), dtype=torch.int64, device=dev)
+        out = torch.empty(self.world * len(vals), dtype=torch.int64, device=dev)
+        self.comm.all_gather_into_tensor(out, t)
+        return out.cpu().numpy().reshape(self.world, len(vals))
+
+    # -- everything between readData and the outputs ------------------------------------------------
+    def finalize(self):
+        eng, W, me, g = self.eng, self.world, self.rank, self.comm
+        dev = eng.device
+        # tuple offsets: rank order == input order
+        n_tuples = self._gather_ints(self.n_local)[:, 0]
+        offs = np.concatenate([[0], np.cumsum(n_tuples)])
+        self.tuple_offset, self.n_total = int(offs[me]), int(offs[-1])
+        n_words, usable = eng.local_words(self.tuple_offset)
+
+        # splitters: evenly spaced samples of every rank's sorted words, weighted equally
+        samp = eng.sample_keys(SAMPLES_PER_RANK) if n_words else np.zeros(0, dtype=np.uint64)
+        st = torch.zeros(SAMPLES_PER_RANK + 1, dtype=torch.int64, device=dev)
+        st[0] = len(samp)
+        if len(samp):
+            st[1:] = torch.from_numpy(samp.view(np.int64)).to(dev)
+        allst = torch.empty(W * (SAMPLES_PER_RANK + 1), dtype=torch.int64, device=dev)
+        g.all_gather_into_tensor(allst, st)
+        allst = allst.cpu().numpy().reshape(W, SAMPLES_PER_RANK + 1)
+        pool = np.sort(np.concatenate([allst[r, 1: 1 + allst[r, 0]].view(np.uint64) for r in range(W)]))
+        if len(pool) and W > 1:
+            splitters = pool[[(len(pool) * p) // W for p in range(1, W)]]
+        else:
+            splitters = np.zeros(max(W - 1, 0), dtype=np.uint64)
+        self.splitters = splitters
+
+        # words to their owners
+        send = eng.split(splitters, W)
+        k, c, f = eng.export_words()
+        rk, recv = all_to_all_v(g, k, send)
+        rc_ = all_to_all_fixed(g, c, send, recv)
+        rf = all_to_all_fixed(g, f, send, recv)
+        local_rank, n_shard = eng.import_words(rk, rc_, rf)
+        info = self._gather_ints(n_shard, usable)
+        bases = np.concatenate([[0], np.cumsum(info[:, 0])]).astype(np.uint64)
+        self.n_words_total, self.usable_total = int(bases[-1]), int(info[:, 1].sum())
+        eng.set_layout(me, W, splitters, bases)
+        # owners tell the senders the global rank of every word they sent
+        grank = all_to_all_fixed(g, local_rank + int(bases[me]), recv, send)
+        eng.set_word_ranks(grank)
+
+        # neighbour search: local look-ups + routed queries
+        qcounts = eng.probe_count(W)
+        qk, qs = eng.probe(qcounts)
+        rqk, qrecv = all_to_all_v(g, qk, qcounts)
+        rqs = all_to_all_fixed(g, qs, qcounts, qrecv)
+        ans = eng.answer(rqk, rqs)
+        back = all_to_all_fixed(g, ans, qrecv, qcounts)
+        eng.apply_answers(qs, back)
+        n_entries = eng.build_rows()
+
+        # the neighbour graph everywhere; clusters, keep mask, histograms
+        gk, gc, gf, gd, gcol = eng.export_graph()
+        sizes = self._gather_ints(n_shard, n_entries)
+        wsz, esz = [int(x) for x in sizes[:, 0]], [int(x) for x in sizes[:, 1]]
+        eng.import_graph(self.n_total, self.usable_total, all_gather_v(g, gk, wsz), all_gather_v(g, gc, wsz),
+                         all_gather_v(g, gf, wsz), all_gather_v(g, gd, wsz), all_gather_v(g, gcol, esz))
+        self.queries_sent = int(np.sum(qcounts))
+
+    # -- results (whole job unless stated) -------------------------------------------------------------
+    def counts(self):
+        return self.eng.counts()
+
+    def histogram(self, which: str):
+        return self.eng.histogram(which)
+
+    def stats_text(self):
+        return self.eng.stats_text()
+
+    def keep_mask(self) -> np.ndarray:
+        """bool[n_local]: this rank's tuples that are written to the *_dedup files."""
+        return self.eng.global_keep_bits(self.tuple_offset, self.n_local)
+
+    def keep_bits(self) -> np.ndarray:
+        return np.packbits(self.keep_mask(), bitorder="little")
+
+    def cluster_ids(self) -> np.ndarray:
+        """uint32[n_local]: cluster ids of this rank's tuples."""
+        return self.eng.local_cluster_ids(0, self.n_local)
+
+    def words(self):
+        return self.eng.words()
+
+    def neighbours(self):
+        return self.eng.neighbours()
+
+    def clusters(self):
+        return self.eng.clusters()
+
+    def stage_stats(self):
+        return self.eng.stage_stats()
+
+    def close(self):
+        self.eng.close()

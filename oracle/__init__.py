@@ -66,6 +66,8 @@ def lib() -> C.CDLL:
         L.oracle_trie_query.argtypes = [_u8p, _u32p, C.c_uint64, _u8p, C.c_uint32, C.c_int, C.c_int, _u64p, C.c_uint64]
         L.oracle_cluster_graph.argtypes = [C.c_uint64, _u64p, _u64p, _u32p, C.c_int, _u32p, C.c_uint64,
                                            C.c_void_p, _u32p, _u64p, _u32p]
+        L.oracle_cluster_all.restype = C.c_uint64
+        L.oracle_cluster_all.argtypes = [C.c_uint64, _u64p, _u64p, _u32p, C.c_int, _u32p, _u64p, _u32p]
         L.oracle_max_neighbour.restype = C.c_uint32
         L.oracle_max_neighbour.argtypes = [C.c_uint64, _u64p, _u64p, _u32p, C.c_void_p, C.c_uint32]
         L.oracle_at_least_double.restype = C.c_int
@@ -204,6 +206,19 @@ def cluster_graph(count, adj: Sequence[Sequence[int]], maximum: bool, seeds: Seq
         pa = pa_arr.ctypes.data_as(C.c_void_p)
     lib().oracle_cluster_graph(U, count, row_ptr, col, int(maximum), seeds_a, len(seeds), pa, cl, size, mx)
     return cl, size, mx
+
+
+def cluster_all(count, row_ptr, col, maximum: bool):
+    """findClusters on an explicit graph: (cluster id per word, size per cluster, maxLeaf per cluster)."""
+    count = np.ascontiguousarray(count, dtype=np.uint64)
+    row_ptr = np.ascontiguousarray(row_ptr, dtype=np.uint64)
+    U = count.size
+    col = np.ascontiguousarray(col if len(col) else [0], dtype=np.uint32)
+    cl = np.zeros(max(U, 1), dtype=np.uint32)
+    size = np.zeros(max(U, 1), dtype=np.uint64)
+    mx = np.zeros(max(U, 1), dtype=np.uint32)
+    n = int(lib().oracle_cluster_all(U, count if U else np.zeros(1, np.uint64), row_ptr, col, int(maximum), cl, size, mx))
+    return cl[:U], size[:n], mx[:n]
 
 
 def max_neighbour(count, adj, assigned, leaf: int) -> int:

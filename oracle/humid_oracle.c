@@ -598,3 +598,39 @@ void oracle_expand_word(const uint8_t *chars, const uint16_t *seg_len, uint32_t 
     for (uint32_t q = 0; q < seg_take[s]; q++, p++)
       out[p] = q < seg_len[s] ? chars[p] : (uint8_t)'N';
 }
+
+/* findClusters (src/humid.cc:167-193) on an explicit neighbour graph (counts + neighbour
+ * lists in CSR form, in the reference's list order): walk order seeds, ids from 1.  Used by
+ * the CPU shard engine of tests/ to finish a job whose graph was assembled from shards.
+ * size_out / max_out need room for U entries; returns the number of clusters. */
+uint64_t oracle_cluster_all(uint64_t U, const uint64_t *count, const uint64_t *row_ptr, const uint32_t *col,
+                            int maximum, uint32_t *cluster_out, uint64_t *size_out, uint32_t *max_out) {
+  oracle o;
+  memset(&o, 0, sizeof o);
+  o.U = U;
+  o.count = (uint64_t *)count;
+  o.nbr = (vec32 *)calloc(U ? U : 1, sizeof(vec32));
+  for (uint64_t i = 0; i < U; i++) {
+    o.nbr[i].v = (uint32_t *)(col + row_ptr[i]);
+    o.nbr[i].n = row_ptr[i + 1] - row_ptr[i];
+  }
+  o.cluster = cluster_out;
+  memset(cluster_out, 0, U * sizeof(uint32_t));
+  o.csize = size_out;
+  o.cmax = max_out;
+  memset(size_out, 0, U * sizeof(uint64_t));
+  memset(max_out, 0, U * sizeof(uint32_t));
+  o.cmaxcount = (uint64_t *)calloc(U ? U : 1, sizeof(uint64_t));
+  uint64_t cap = 1024;
+  frame *stk = (frame *)malloc(cap * sizeof(frame));
+  uint32_t id = 1;
+  for (uint64_t r = 0; r < U; r++) {
+    if (!o.cluster[r]) {
+      uint32_t cl = id++;
+      if (maximum) assign_max_cluster(&o, (uint32_t)r, cl, &stk, &cap);
+      else assign_directional_cluster(&o, (uint32_t)r, cl, &stk, &cap);
+    }
+  }
+  free(stk); free(o.nbr); free(o.cmaxcount);
+  return (uint64_t)id - 1;
+}

@@ -18,9 +18,13 @@ def lib():
 
 
 def declared_symbols():
-    text = open(os.path.join(ROOT, "include", "humid_gpu.h")).read()
-    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(humid_gpu_[a-z_]+)\s*\(", text)))
+    import glob
+
+    syms = set()
+    for h in glob.glob(os.path.join(ROOT, "include", "*.h")):
+        text = re.sub(r"/\*.*?\*/", "", open(h).read(), flags=re.S)
+        syms |= set(re.findall(r"\b(humid_gpu_[a-z_0-9]+)\s*\(", text))
+    return sorted(syms)
 
 
 def test_header_symbols_exported(lib):
@@ -28,7 +32,9 @@ def test_header_symbols_exported(lib):
     assert len(syms) >= 16
     for s in syms:
         assert hasattr(lib, s), s
-    assert sorted(api.EXPORTS) == syms
+    from humid_b200 import sharded
+
+    assert sorted(api.EXPORTS + sharded.SHARD_EXPORTS) == syms
 
 
 def test_abi_version(lib):
