@@ -314,7 +314,7 @@ def run_gpu_arm(args):
         "config": {"workload": WORKLOAD, "tuples_per_gpu": R_per, "tuples_total": R_all, "word_length": cfg.word_length,
                    "distance": cfg.distance, "clustering": "maximum" if cfg.maximum else "directional",
                    "l2": "inputs larger than L2 (word characters %.2f GB per GPU)" % (R_per * cfg.word_length / 1e9),
-                   "parallelism": "1 GPU" if world == 1 else f"key-hash sharded over {world} GPUs, NCCL all-to-all",
+                   "parallelism": "1 GPU" if world == 1 else f"words range-partitioned over {world} GPUs, NCCL all-to-all-v (words, variant queries) + all-gather (graph)",
                    "result": counts},
         "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": t_e2e * 1e3,
                 "h2d_bytes_per_step": int(R_per * cfg.word_length), "d2h_bytes_per_step": int(d2h[0])},
