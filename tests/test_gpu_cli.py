@@ -1,0 +1,78 @@
+"""End-to-end: the `humid` executable of this repo (host/humid_main.cc over libhumid_gpu)
+against the UNMODIFIED reference CLI (oracle/_ref/humid, built from the reference's sources;
+the binary travels to the GPU box) on the same FastQ files — every output file byte for byte
+(`.gz` outputs compared after decompression, as the deflate encoders differ)."""
+import filecmp
+import gzip
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle
+from humid_b200 import build
+from humid_b200.synth import Synth, baseline_config
+
+pytestmark = pytest.mark.gpu
+
+CASES = [  # (name, config, tuples, overrides, extra flags, gz inputs)
+    ("c1_max", 0, 20000, {}, ["-a"], False),
+    ("c1_dir_gz", 0, 8000, dict(maximum=False), ["-a"], True),
+    ("c2_umifile", 1, 15000, {}, ["-a"], False),
+    ("c3_ham2", 2, 8000, {}, [], False),
+    ("c4_edit2", 3, 4000, {}, ["-a"], False),
+    ("c5_umi10", 4, 15000, {}, [], False),
+    ("n30", 1, 5000, dict(word_length=30), ["-a"], False),
+    ("no_dedup_output", 0, 3000, {}, ["-q"], False),
+]
+
+
+def read_any(path):
+    return gzip.open(path, "rb").read() if path.endswith(".gz") else open(path, "rb").read()
+
+
+@pytest.fixture(scope="module")
+def humid_bin():
+    return build.build_host()
+
+
+@pytest.mark.parametrize("name,ci,R,kw,flags,gz", CASES, ids=[c[0] for c in CASES])
+def test_cli_matches_reference_binary(tmp_path, humid_bin, name, ci, R, kw, flags, gz):
+    cfg = baseline_config(ci, R, **kw)
+    s = Synth(cfg)
+    files = s.write_fastq(str(tmp_path / "in"), prefix="x", gzip_output=gz)
+    ours = str(tmp_path / "ours" / "nested")
+    cmd = [humid_bin, *cfg.cli_flags(), "-s", *flags, "-d", ours, "-l", str(tmp_path / "ours.log"), *files]
+    subprocess.run(cmd, check=True, timeout=600)
+    log = open(tmp_path / "ours.log").read()
+    assert "Reading data... done." in log and "clusters... done." in log
+
+    if oracle.have_ref():
+        ref = str(tmp_path / "ref")
+        oracle.run_ref_humid(files, ref, cfg.cli_flags() + [f for f in flags if f != "-a"], stats=True,
+                             annotate="-a" in flags)
+        names = sorted(os.listdir(ref))
+        names.remove("humid.log")
+        assert sorted(os.listdir(ours)) == names
+        for f in names:
+            if f.endswith(".gz"):
+                assert read_any(os.path.join(ours, f)) == read_any(os.path.join(ref, f)), f
+            else:
+                assert filecmp.cmp(os.path.join(ours, f), os.path.join(ref, f), shallow=False), f
+    else:  # no reference binary on this machine: the oracle's statistics files
+        hdr, take = s.layout()
+        seg_take = ([hdr] if hdr else []) + take
+        r = oracle.Result(oracle.pack_words(s.word_chars(), seg_take), cfg.word_length, cfg.distance, cfg.edit, cfg.maximum)
+        for f, text in r.stats_text().items():
+            assert open(os.path.join(ours, f)).read() == text, f
+        if "-q" not in flags:
+            kept = read_any(os.path.join(ours, os.path.basename(files[0]).replace(".", "_dedup.", 1))).count(b"\n") // 4
+            assert kept == r.clusters
+
+
+def test_cli_help_and_errors(humid_bin, tmp_path):
+    p = subprocess.run([humid_bin, "-h"], capture_output=True, text=True)
+    assert p.returncode == 0 and "-x" in p.stdout and "word length" in p.stdout
+    p = subprocess.run([humid_bin, str(tmp_path / "missing.fastq")], capture_output=True, text=True)
+    assert p.returncode != 0 and "ERROR" in p.stderr
