@@ -187,7 +187,7 @@ def run_gpu_arm(args):
 
     R_per = args.tuples
     R_all = R_per * world
-    cfg = baseline_config(1, R_all)
+    cfg = baseline_config(args.config, R_all)
     syn = HashSynth(cfg)
     hdr, take = syn.layout()
     seg_take = ([hdr] if hdr else []) + take
@@ -311,7 +311,7 @@ def run_gpu_arm(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": t_dev * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "tuples_per_gpu": R_per, "tuples_total": R_all, "word_length": cfg.word_length,
+        "config": {"workload": WORKLOAD if args.config == 1 else cfg.name, "tuples_per_gpu": R_per, "tuples_total": R_all, "word_length": cfg.word_length,
                    "distance": cfg.distance, "clustering": "maximum" if cfg.maximum else "directional",
                    "l2": "inputs larger than L2 (word characters %.2f GB per GPU)" % (R_per * cfg.word_length / 1e9),
                    "parallelism": "1 GPU" if world == 1 else f"words range-partitioned over {world} GPUs, NCCL all-to-all-v (words, variant queries) + all-gather (graph)",
@@ -336,6 +336,7 @@ def main():
     ap.add_argument("--impl", default="humid_b200", choices=["humid_b200", "reference"])
     ap.add_argument("--tuples", type=int, default=50_000_000, help="read tuples per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--config", type=int, default=1, help="BASELINE.json configs[i] (0-based); the bench line is configs[1]")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":

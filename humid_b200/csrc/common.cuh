@@ -58,25 +58,50 @@ struct Lookup {
   uint32_t n_buckets;
 };
 
-__host__ __device__ __forceinline__ uint32_t filter_bucket(uint64_t h, uint32_t n_buckets) {
-  return (uint32_t)(((h >> 32) * (uint64_t)n_buckets) >> 32);
+// The filter uses its own, cheaper hash: hf(key) = key * FILTER_MUL (Fibonacci hashing, high
+// bits).  It is linear, so the hash of a variant w + delta is hf(w) + delta * FILTER_MUL: one
+// multiply per word, one add per probed variant.  (The slot table keeps the avalanche hash
+// mix64: its index is taken from the LOW bits.)
+constexpr uint64_t FILTER_MUL = 0x9E3779B97F4A7C15ull;
+__host__ __device__ __forceinline__ uint64_t filter_hash(uint64_t key) { return key * FILTER_MUL; }
+__host__ __device__ __forceinline__ uint32_t filter_bucket(uint64_t hf, uint32_t n_buckets) {
+  return (uint32_t)(((hf >> 32) * (uint64_t)n_buckets) >> 32);
 }
-__host__ __device__ __forceinline__ uint32_t filter_fp(uint64_t h) {
-  uint32_t b = (uint32_t)(h >> 24) & 0xFFu;
+__host__ __device__ __forceinline__ uint32_t filter_fp(uint64_t hf) {
+  uint32_t b = (uint32_t)(hf >> 32) & 0xFFu;  // low byte of the high word: not used by the bucket index
   return b < 2u ? b + 2u : b;
 }
 
 #ifdef __CUDACC__
-// rank of `key`, or NONE32.  After rank_columns_kernel the slot's count field holds the rank.
-__device__ __forceinline__ uint32_t lookup_rank(const Lookup &lk, uint64_t key) {
-  const uint64_t h = mix64(key);
-  if (lk.filter) {
-    const uint4 b = __ldg(lk.filter + filter_bucket(h, lk.n_buckets));
-    const uint32_t f4 = filter_fp(h) * 0x01010101u;
-    const uint32_t m = __vcmpeq4(b.x, f4) | __vcmpeq4(b.y, f4) | __vcmpeq4(b.z, f4) | __vcmpeq4(b.w, f4);
-    if (m == 0u && (b.x & 1u) == 0u) return NONE32;
-  }
-  uint64_t idx = h & lk.mask;
+// L2 eviction-priority hints: the filter should stay resident, table sectors and streamed
+// columns should not displace it.
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint4 ld_hint_u128(const void *ptr, uint64_t policy) {
+  uint4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(ptr), "l"(policy));
+  return v;
+}
+
+__device__ __forceinline__ bool filter_match(const uint4 &b, uint64_t hf) {
+  const uint32_t f4 = filter_fp(hf) * 0x01010101u;
+  const uint32_t m = __vcmpeq4(b.x, f4) | __vcmpeq4(b.y, f4) | __vcmpeq4(b.z, f4) | __vcmpeq4(b.w, f4);
+  return m != 0u || (b.x & 1u) != 0u;
+}
+
+// slot table only: rank of `key` or NONE32 (after rank_columns_kernel `count` holds the rank)
+__device__ __forceinline__ uint32_t table_rank(const Lookup &lk, uint64_t key) {
+  uint64_t idx = mix64(key) & lk.mask;
   while (true) {
     const uint4 v = __ldg(reinterpret_cast<const uint4 *>(lk.slots + idx));
     const uint64_t k = ((uint64_t)v.y << 32) | v.x;
@@ -84,6 +109,16 @@ __device__ __forceinline__ uint32_t lookup_rank(const Lookup &lk, uint64_t key) 
     if (k == KEY_INVALID) return NONE32;
     idx = (idx + 1) & lk.mask;
   }
+}
+
+// rank of `key`, or NONE32: filter first, table only on a fingerprint match
+__device__ __forceinline__ uint32_t lookup_rank(const Lookup &lk, uint64_t key) {
+  if (lk.filter) {
+    const uint64_t hf = filter_hash(key);
+    const uint4 b = __ldg(lk.filter + filter_bucket(hf, lk.n_buckets));
+    if (!filter_match(b, hf)) return NONE32;
+  }
+  return table_rank(lk, key);
 }
 #endif
 

@@ -82,7 +82,7 @@ void humid_gpu_destroy(humid_gpu *h) {
   s.tuple_key.release(); s.stage_chars.release(); s.stage_seg_len.release(); s.counters.release();
   s.slots.release(); s.word_key.release(); s.key_alt.release(); s.word_slot.release(); s.slot_alt.release();
   s.word_count.release(); s.word_first.release(); s.entries.release(); s.entries_alt.release();
-  s.entry_val.release(); s.entry_val_alt.release(); s.row_ptr.release(); s.col.release();
+  s.entry_val.release(); s.entry_val_alt.release(); s.row_ptr.release(); s.deg.release(); s.col.release();
   s.comp.release(); s.label.release(); s.members.release(); s.seg_start.release(); s.seg_end.release();
   s.work_a.release(); s.work_b.release(); s.work_c.release(); s.seed_flag.release(); s.seed_index.release();
   s.seed_size.release(); s.seed_max.release(); s.cluster_size.release(); s.cluster_max.release();
@@ -164,8 +164,13 @@ int humid_gpu_finalize(humid_gpu *h) {
     stage_build_table(s);
     s.report_tuples = s.n_tuples;
     s.report_usable = s.usable;
-    if (edit2) stage_neighbours_edit(s); else stage_neighbours_hamming(s);
-    stage_csr(s);
+    if (edit2) {
+      stage_neighbours_edit(s);
+      stage_csr(s);
+    } else {
+      stage_neighbours_hamming(s);
+      stage_csr_pairs(s);
+    }
     stage_cluster(s);
     stage_keep(s);
     HUMID_CUDA(cudaStreamSynchronize(s.stream));

@@ -105,6 +105,8 @@ struct State {
   // neighbour lists
   DevBuf<uint64_t> entries, entries_alt;  // (src rank << 32 | payload), see neighbours.cu
   DevBuf<uint32_t> entry_val, entry_val_alt;
+  DevBuf<uint32_t> deg;                   // [U] list lengths (Hamming mode: counted by the probe kernels)
+  uint64_t n_pairs = 0;                   // undirected pairs in `entries` (Hamming mode)
   DevBuf<uint64_t> row_ptr;               // [U+1]
   DevBuf<uint32_t> col;                   // [n_entries]
 
@@ -160,7 +162,8 @@ int stage_build_table(State &s, bool with_filter = true);  // insert + compact +
 int stage_build_filter(State &s);      // fingerprint filter over word_key[0..unique)
 int stage_neighbours_hamming(State &s);
 int stage_neighbours_edit(State &s);
-int stage_csr(State &s);               // sort entries, row_ptr / col
+int stage_csr(State &s);               // sort directed entries, row_ptr / col (edit and shard modes)
+int stage_csr_pairs(State &s);         // Hamming mode: undirected pairs + degrees -> row_ptr / col
 int stage_cluster(State &s);           // components, replay, ids, sizes, maxLeaf
 int stage_keep(State &s);              // keep bitmap
 int stage_cluster_ids(State &s, uint64_t first, uint64_t n, uint32_t *d_out);

@@ -173,10 +173,10 @@ __global__ void __launch_bounds__(256)
     filter_build_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t *words, uint32_t n_buckets) {
   uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= U) return;
-  const uint64_t h = mix64(word_key[r]);
+  const uint64_t h = filter_hash(word_key[r]);
   uint32_t *w = words + 4ull * filter_bucket(h, n_buckets);
   const uint32_t fp = filter_fp(h);
-  const uint32_t start = (uint32_t)(h >> 20) & 3u;
+  const uint32_t start = (uint32_t)(h >> 40) & 3u;
   for (uint32_t t = 0; t < 4; t++) {
     const uint32_t wi = (start + t) & 3u;
     uint32_t old = *reinterpret_cast<volatile uint32_t *>(w + wi);
