@@ -5,10 +5,15 @@
 // word by recursive traversal of the neighbour lists; the result depends on walk order and
 // on neighbour-list order, but never crosses a connected component of the neighbour graph.
 // So: (1) lock-free union-find gives the components (root = smallest rank = the word the
-// walk meets first); (2) members are grouped per component in rank order; (3) every
-// component is replayed exactly, independently of all others; (4) cluster ids are an
+// walk meets first); (2) the members of a component are needed in rank order: components of
+// up to SMALL_COMP words (virtually all of them) are collected by their root's thread with a
+// breadth-first walk of the lists and sorted in local memory, only the words of larger
+// components go through a global sort; (3) every component is replayed exactly,
+// independently of all others; (4) cluster ids are an
 // exclusive scan over the seed flags in rank order (ids are handed out in walk order of
 // the seeding word, src/humid.cc:180).
+#include <algorithm>
+
 #include "state.cuh"
 
 namespace humid {
@@ -52,83 +57,116 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-__global__ void uf_flatten_kernel(uint32_t *parent, uint32_t *comp, uint64_t U) {
-  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (r < U) comp[r] = uf_find(parent, (uint32_t)r);
-}
+constexpr uint32_t SMALL_COMP = 32;
 
-// ---- (2) members per component -------------------------------------------------------------
-__global__ void member_keys_kernel(const uint32_t *__restrict__ comp, uint64_t U, uint64_t *keys, uint32_t *vals) {
+// comp[r] = root; csize[root] = number of members (singletons are not counted: csize stays 0)
+__global__ void uf_flatten_kernel(uint32_t *parent, uint32_t *comp, uint32_t *csize, uint64_t U) {
   uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (r < U) {
-    keys[r] = comp[r];
-    vals[r] = (uint32_t)r;
+  if (r >= U) return;
+  uint32_t root = uf_find(parent, (uint32_t)r);
+  comp[r] = root;
+  if (root != r) {
+    atomicAdd(csize + root, 1u);  // members besides the root itself
   }
 }
 
-__global__ void segment_bounds_kernel(const uint64_t *__restrict__ sorted_comp, uint64_t U, uint32_t *seg_start,
-                                      uint32_t *seg_end) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= U) return;
-  uint32_t c = (uint32_t)sorted_comp[i];
-  if (i == 0 || (uint32_t)sorted_comp[i - 1] != c) seg_start[c] = (uint32_t)i;
-  if (i + 1 == U || (uint32_t)sorted_comp[i + 1] != c) seg_end[c] = (uint32_t)i + 1;
+// ---- (2) members of the LARGE components, grouped by a global sort ---------------------------
+__global__ void __launch_bounds__(256)
+    big_member_keys_kernel(const uint32_t *__restrict__ comp, const uint32_t *__restrict__ csize, uint64_t U,
+                           uint64_t *__restrict__ keys, unsigned long long *__restrict__ counter) {
+  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  bool big = r < U && csize[comp[r]] + 1u > SMALL_COMP;
+  unsigned m = __ballot_sync(0xffffffffu, big);
+  if (m == 0) return;
+  unsigned long long base = 0;
+  int leader = __ffs(m) - 1;
+  if ((int)lane_id() == leader) base = atomicAdd(counter, (unsigned long long)__popc(m));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (big) keys[base + __popc(m & ((1u << lane_id()) - 1u))] = ((uint64_t)comp[r] << 32) | (uint32_t)r;
 }
 
-// ---- (3) exact replay per component ------------------------------------------------------
+__global__ void big_segments_kernel(const uint64_t *__restrict__ sorted, uint64_t n, uint32_t *__restrict__ members,
+                                    uint32_t *__restrict__ seg_start) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t c = (uint32_t)(sorted[i] >> 32);
+  members[i] = (uint32_t)sorted[i];
+  if (i == 0 || (uint32_t)(sorted[i - 1] >> 32) != c) seg_start[c] = (uint32_t)i;
+}
+
 struct Graph {
   const uint64_t *row_ptr;
   const uint32_t *col;
   const uint32_t *count;
 };
 
+// Members of the component of `root` (m of them) in rank order, collected by a breadth-first
+// walk of the neighbour lists into `arr` (capacity SMALL_COMP) and sorted there.
+__device__ __forceinline__ void gather_small_component(const Graph &g, uint32_t root, uint32_t m, uint32_t *arr) {
+  arr[0] = root;
+  uint32_t cnt = 1;
+  for (uint32_t i = 0; i < cnt && cnt < m; i++) {
+    const uint32_t u = arr[i];
+    for (uint64_t e = g.row_ptr[u], hi = g.row_ptr[u + 1]; e < hi && cnt < m; e++) {
+      const uint32_t v = g.col[e];
+      bool seen = false;
+      for (uint32_t j = 0; j < cnt; j++) seen |= arr[j] == v;
+      if (!seen) arr[cnt++] = v;
+    }
+  }
+  for (uint32_t i = 1; i < cnt; i++) {
+    uint32_t x = arr[i], j = i;
+    while (j > 0 && arr[j - 1] > x) { arr[j] = arr[j - 1]; j--; }
+    arr[j] = x;
+  }
+}
+
+// position of word v inside the sorted member array (the per-member work arrays are indexed by it)
+__device__ __forceinline__ uint32_t member_index(const uint32_t *mem, uint32_t m, uint32_t v) {
+  uint32_t lo = 0, hi = m;
+  while (lo < hi) {
+    uint32_t mid = (lo + hi) >> 1;
+    if (mem[mid] < v) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+// ---- (3) exact replay per component ------------------------------------------------------
 // assignMaxCluster (src/cluster.cc:72-80): cluster == component, size = sum of counts,
 // maxLeaf = first word in DFS pre-order (neighbour-list order) holding the strictly largest
 // count.  The DFS is only replayed when several members tie for the largest count.
-__global__ void __launch_bounds__(128)
-    replay_maximum_kernel(Graph g, uint64_t U, const uint32_t *__restrict__ comp,
-                          const uint32_t *__restrict__ members, const uint32_t *__restrict__ seg_start,
-                          const uint32_t *__restrict__ seg_end, uint32_t *__restrict__ stk_node,
-                          uint32_t *__restrict__ stk_edge_lo, uint32_t *__restrict__ visited,
-                          uint32_t *__restrict__ label, uint32_t *__restrict__ seed_flag,
-                          uint64_t *__restrict__ seed_size, uint32_t *__restrict__ seed_max) {
-  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (r >= U) return;
-  uint32_t root = comp[r];
-  label[r] = root;
-  if (root != r) { seed_flag[r] = 0; return; }
-  seed_flag[r] = 1;
-  const uint32_t s = seg_start[r], e = seg_end[r];
+// mem[0..m) = members in rank order (mem[0] == root); stk_* have room for m frames.
+__device__ void replay_maximum(const Graph &g, const uint32_t *mem, uint32_t m, uint32_t *stk_node,
+                               uint32_t *stk_edge, uint32_t *visited, uint64_t *size_out, uint32_t *max_out) {
+  const uint32_t root = mem[0];
   uint64_t size = 0;
   uint32_t best = 0, best_rank = NONE32, ties = 0;
-  for (uint32_t i = s; i < e; i++) {
-    uint32_t m = members[i];
-    uint32_t c = g.count[m];
+  for (uint32_t i = 0; i < m; i++) {
+    const uint32_t w = mem[i];
+    const uint32_t c = g.count[w];
     size += c;
-    if (c > best) { best = c; best_rank = m; ties = 1; }
+    if (c > best) { best = c; best_rank = w; ties = 1; }
     else if (c == best) ties++;
   }
-  seed_size[r] = size;
   if (ties > 1) {
-    // DFS pre-order from the root until the first word with count == best is entered.
-    // Frames: (node, next edge index relative to row start) in the component's own slice.
-    uint32_t sp = s;
-    visited[r] = 1;
-    if (g.count[r] == best) { best_rank = (uint32_t)r; }
-    else {
-      stk_node[sp] = (uint32_t)r; stk_edge_lo[sp] = 0; sp++;
+    if (g.count[root] == best) {
+      best_rank = root;
+    } else {
+      uint32_t sp = 0;
+      visited[root] = 1;
+      stk_node[sp] = root; stk_edge[sp] = 0; sp++;
       bool found = false;
-      while (sp > s && !found) {
-        uint32_t u = stk_node[sp - 1];
-        uint64_t lo = g.row_ptr[u], hi = g.row_ptr[u + 1];
-        uint64_t j = lo + stk_edge_lo[sp - 1];
+      while (sp > 0 && !found) {
+        const uint32_t u = stk_node[sp - 1];
+        const uint64_t lo = g.row_ptr[u], hi = g.row_ptr[u + 1];
+        const uint64_t j = lo + stk_edge[sp - 1];
         if (j < hi) {
-          stk_edge_lo[sp - 1]++;
-          uint32_t v = g.col[j];
+          stk_edge[sp - 1]++;
+          const uint32_t v = g.col[j];
           if (!visited[v]) {
             visited[v] = 1;
             if (g.count[v] == best) { best_rank = v; found = true; }
-            else { stk_node[sp] = v; stk_edge_lo[sp] = 0; sp++; }
+            else { stk_node[sp] = v; stk_edge[sp] = 0; sp++; }
           }
         } else {
           sp--;
@@ -136,7 +174,8 @@ __global__ void __launch_bounds__(128)
       }
     }
   }
-  seed_max[r] = best_rank;
+  *size_out = size;
+  *max_out = best_rank;
 }
 
 // assignDirectionalCluster (src/cluster.cc:82-87): for every still-unassigned member in rank
@@ -144,24 +183,16 @@ __global__ void __launch_bounds__(128)
 // count >= 2x, restarting the scan after every move; the top word is maxLeaf; then take the
 // closure over unassigned neighbours with count <= half (assignDirectionalCluster_, :58-69;
 // a closure, so breadth-first order gives the same set as the reference's recursion).
-__global__ void __launch_bounds__(128)
-    replay_directional_kernel(Graph g, uint64_t U, const uint32_t *__restrict__ comp,
-                              const uint32_t *__restrict__ members, const uint32_t *__restrict__ seg_start,
-                              const uint32_t *__restrict__ seg_end, uint32_t *__restrict__ queue,
-                              uint32_t *label, uint32_t *__restrict__ seed_flag,
-                              uint64_t *__restrict__ seed_size, uint32_t *__restrict__ seed_max) {
-  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (r >= U) return;
-  if (comp[r] != r) return;
-  const uint32_t s = seg_start[r], e = seg_end[r];
-  for (uint32_t i = s; i < e; i++) {
-    uint32_t seed = members[i];
+__device__ void replay_directional(const Graph &g, const uint32_t *mem, uint32_t m, uint32_t *queue, uint32_t *label,
+                                   uint32_t *seed_flag, uint64_t *seed_size, uint32_t *seed_max) {
+  for (uint32_t i = 0; i < m; i++) {
+    const uint32_t seed = mem[i];
     if (label[seed] != NONE32) continue;
     uint32_t node = seed;
     uint64_t j = g.row_ptr[node], hi = g.row_ptr[node + 1];
     uint64_t cn = g.count[node];
     while (j < hi) {
-      uint32_t nb = g.col[j++];
+      const uint32_t nb = g.col[j++];
       if (label[nb] == NONE32 && (uint64_t)g.count[nb] >= 2 * cn) {
         node = nb;
         j = g.row_ptr[node];
@@ -169,17 +200,17 @@ __global__ void __launch_bounds__(128)
         cn = g.count[node];
       }
     }
-    uint32_t head = s, tail = s;
+    uint32_t head = 0, tail = 0;
     label[node] = seed;
     uint64_t size = cn;
     queue[tail++] = node;
     while (head < tail) {
-      uint32_t u = queue[head++];
-      uint64_t cu = g.count[u];
-      for (uint64_t k = g.row_ptr[u]; k < g.row_ptr[u + 1]; k++) {
-        uint32_t nb = g.col[k];
+      const uint32_t u = queue[head++];
+      const uint64_t cu = g.count[u];
+      for (uint64_t k = g.row_ptr[u], e = g.row_ptr[u + 1]; k < e; k++) {
+        const uint32_t nb = g.col[k];
         if (label[nb] == NONE32) {
-          uint64_t cb = g.count[nb];
+          const uint64_t cb = g.count[nb];
           if (cu >= 2 * cb) {
             label[nb] = seed;
             size += cb;
@@ -191,6 +222,43 @@ __global__ void __launch_bounds__(128)
     seed_flag[seed] = 1;
     seed_size[seed] = size;
     seed_max[seed] = node;
+  }
+}
+
+// One thread per word; only component roots work.  Singletons are closed in place, small
+// components are gathered and replayed in local memory, large ones use the globally sorted
+// member array (big_members / big_start) and global work arrays of the same length.
+template <bool MAXIMUM>
+__global__ void __launch_bounds__(128)
+    replay_kernel(Graph g, uint64_t U, const uint32_t *__restrict__ comp, const uint32_t *__restrict__ csize,
+                  const uint32_t *__restrict__ big_members, const uint32_t *__restrict__ big_start,
+                  uint32_t *__restrict__ big_work_a, uint32_t *__restrict__ big_work_b, uint32_t *visited,
+                  uint32_t *label, uint32_t *__restrict__ seed_flag, uint64_t *__restrict__ seed_size,
+                  uint32_t *__restrict__ seed_max) {
+  const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= U) return;
+  const uint32_t root = comp[r];
+  if (MAXIMUM) {
+    label[r] = root;
+    seed_flag[r] = root == r ? 1u : 0u;
+  }
+  if (root != r) return;
+  const uint32_t m = csize[r] + 1u;
+  if (m == 1) {  // no neighbours: its own cluster
+    if (!MAXIMUM) { label[r] = (uint32_t)r; seed_flag[r] = 1; }
+    seed_size[r] = g.count[r];
+    seed_max[r] = (uint32_t)r;
+    return;
+  }
+  if (m <= SMALL_COMP) {
+    uint32_t mem[SMALL_COMP], wa[SMALL_COMP], wb[SMALL_COMP];
+    gather_small_component(g, (uint32_t)r, m, mem);
+    if (MAXIMUM) replay_maximum(g, mem, m, wa, wb, visited, seed_size + r, seed_max + r);
+    else replay_directional(g, mem, m, wa, label, seed_flag, seed_size, seed_max);
+  } else {
+    const uint32_t s0 = big_start[r];
+    if (MAXIMUM) replay_maximum(g, big_members + s0, m, big_work_a + s0, big_work_b + s0, visited, seed_size + r, seed_max + r);
+    else replay_directional(g, big_members + s0, m, big_work_a + s0, label, seed_flag, seed_size, seed_max);
   }
 }
 
@@ -215,59 +283,67 @@ int stage_cluster(State &s) {
   s.comp.ensure(U);
   s.label.ensure(U);
   s.work_a.ensure(U);
+  s.seg_end.ensure(U);  // csize
+  uint32_t *csize = s.seg_end.p;
   {
     // 8 (entry) + 8 (two parent reads) per entry; 12 per word
     Timed t(s, "union_find", s.n_entries, s.n_entries * 16 + U * 12);
+    HUMID_CUDA(cudaMemsetAsync(csize, 0, U * sizeof(uint32_t), s.stream));
     iota_kernel<<<g256, 256, 0, s.stream>>>(s.work_a.p, U);  // parent
     uf_union_kernel<<<g256, 256, 0, s.stream>>>(s.row_ptr.p, s.col.p, s.n_entries, U, s.work_a.p);
-    uf_flatten_kernel<<<g256, 256, 0, s.stream>>>(s.work_a.p, s.comp.p, U);
+    uf_flatten_kernel<<<g256, 256, 0, s.stream>>>(s.work_a.p, s.comp.p, csize, U);
     t.launches = 3;
   }
   k += 3;
 
-  // members grouped by component (stable sort keeps rank order inside a component)
-  s.key_alt.ensure(U + 1);
-  s.entries_alt.ensure(U + 1);
-  s.members.ensure(U);
-  s.slot_alt.ensure(U + 1);
-  uint64_t *kb[2] = {s.key_alt.p, s.entries_alt.p};
-  uint32_t *vb[2] = {s.members.p, s.slot_alt.p};
-  int ubits = 1;
-  while ((1ull << ubits) < U) ubits++;
-  int launches = 0;
-  int cur;
+  // words of large components, grouped by component in rank order (usually none)
+  uint64_t n_big = 0;
   s.seg_start.ensure(U);
-  s.seg_end.ensure(U);
   {
-    Timed t(s, "group_members", U, U * (4 + 2 * 12 + 8));
-    member_keys_kernel<<<g256, 256, 0, s.stream>>>(s.comp.p, U, kb[0], vb[0]);
-    cur = radix_sort_u64(kb, vb, U, ubits, s.scratch, s.scan_scratch, s.stream, &launches);
-    if (cur == 1) std::swap(s.members, s.slot_alt);
-    segment_bounds_kernel<<<g256, 256, 0, s.stream>>>(kb[cur], U, s.seg_start.p, s.seg_end.p);
-    t.launches = launches + 2;
+    Timed t(s, "group_big_components", U, U * 8);
+    s.key_alt.ensure(U + 1);
+    HUMID_CUDA(cudaMemsetAsync(s.counters.p + 8, 0, sizeof(unsigned long long), s.stream));
+    big_member_keys_kernel<<<g256, 256, 0, s.stream>>>(s.comp.p, csize, U, s.key_alt.p, s.counters.p + 8);
+    HUMID_CUDA(cudaMemcpyAsync(&n_big, s.counters.p + 8, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    int launches = 1;
+    s.members.ensure(n_big + 1);
+    s.work_b.ensure(std::max<uint64_t>(n_big + 1, 1));
+    s.work_c.ensure(std::max<uint64_t>(n_big + 1, U));  // also `visited` in maximum mode
+    if (n_big) {
+      s.entries_alt.ensure(n_big + 1);
+      uint64_t *kb[2] = {s.key_alt.p, s.entries_alt.p};
+      uint32_t *vb[2] = {nullptr, nullptr};
+      int ubits = 1;
+      while ((1ull << ubits) < U) ubits++;
+      int cur = radix_sort_u64(kb, vb, n_big, 32 + ubits, s.scratch, s.scan_scratch, s.stream, &launches);
+      big_segments_kernel<<<grid_for(n_big, 256), 256, 0, s.stream>>>(kb[cur], n_big, s.members.p, s.seg_start.p);
+      launches++;
+    }
+    t.launches = launches;
+    k += launches;
   }
-  k += launches + 2;
 
   s.seed_flag.ensure(U);
   s.seed_index.ensure(U);
   s.seed_size.ensure(U);
   s.seed_max.ensure(U);
-  s.work_b.ensure(U);
-  s.work_c.ensure(U);
   Graph g{s.row_ptr.p, s.col.p, s.word_count.p};
   size_t t_replay = s.timer_begin(s.cfg.maximum ? "replay_maximum" : "replay_directional", U,
                                   s.n_entries * 8 + U * 24);
   if (s.cfg.maximum) {
-    HUMID_CUDA(cudaMemsetAsync(s.work_c.p, 0, U * sizeof(uint32_t), s.stream));  // visited
-    replay_maximum_kernel<<<g128, 128, 0, s.stream>>>(g, U, s.comp.p, s.members.p, s.seg_start.p, s.seg_end.p,
-                                                      s.work_a.p, s.work_b.p, s.work_c.p, s.label.p, s.seed_flag.p,
-                                                      s.seed_size.p, s.seed_max.p);
+    // big components: DFS stack (node, edge) in work_b / slot_alt, visited flags per word in work_c
+    s.slot_alt.ensure(n_big + 1);
+    HUMID_CUDA(cudaMemsetAsync(s.work_c.p, 0, U * sizeof(uint32_t), s.stream));
+    replay_kernel<true><<<g128, 128, 0, s.stream>>>(g, U, s.comp.p, csize, s.members.p, s.seg_start.p, s.work_b.p,
+                                                    s.slot_alt.p, s.work_c.p, s.label.p, s.seed_flag.p, s.seed_size.p,
+                                                    s.seed_max.p);
   } else {
     HUMID_CUDA(cudaMemsetAsync(s.label.p, 0xFF, U * sizeof(uint32_t), s.stream));
     HUMID_CUDA(cudaMemsetAsync(s.seed_flag.p, 0, U * sizeof(uint32_t), s.stream));
-    replay_directional_kernel<<<g128, 128, 0, s.stream>>>(g, U, s.comp.p, s.members.p, s.seg_start.p, s.seg_end.p,
-                                                          s.work_a.p, s.label.p, s.seed_flag.p, s.seed_size.p,
-                                                          s.seed_max.p);
+    replay_kernel<false><<<g128, 128, 0, s.stream>>>(g, U, s.comp.p, csize, s.members.p, s.seg_start.p, s.work_b.p,
+                                                     nullptr, nullptr, s.label.p, s.seed_flag.p, s.seed_size.p,
+                                                     s.seed_max.p);
   }
   s.timer_end(t_replay, 1);
   k++;
