@@ -14,26 +14,37 @@ struct PackParams {
 };
 
 constexpr int PACK_THREADS = 256;
+constexpr int PACK_ROWS = 1024;  // tuples per CTA: 4 x 16-byte loads in flight per thread while staging
 
-// A=0 C=1 G=2 T=3 (src/fastq.cc:12); anything else filters the word (:151-158).
-__device__ __forceinline__ uint32_t nt_code(uint32_t ch, bool &bad) {
-  bad |= !(ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T');
-  uint32_t x = (ch >> 1) & 3u;  // A:0 C:1 G:3 T:2
-  return x ^ (x >> 1);          // A:0 C:1 G:2 T:3
+// Four characters at a time (SIMD inside a 32-bit register).  A=0 C=1 G=2 T=3
+// (src/fastq.cc:12) falls out of bits 1-2 of the ASCII code; a character is valid iff the
+// letter that its code maps back to is the character itself (anything else — N, lower case,
+// padding — filters the word, :151-158).  Returns the four 2-bit codes packed into 8 bits,
+// first character most significant.
+__device__ __forceinline__ uint32_t pack4(uint32_t x, bool &bad) {
+  uint32_t c = (x >> 1) & 0x03030303u;  // A:0 C:1 G:3 T:2
+  c ^= (c >> 1) & 0x01010101u;          // A:0 C:1 G:2 T:3
+  const uint32_t sel = (c & 0x3u) | ((c >> 4) & 0x30u) | ((c >> 8) & 0x300u) | ((c >> 12) & 0x3000u);
+  bad |= __byte_perm(0x54474341u /* "ACGT" */, 0u, sel) != x;
+  return (c * 0x40100401u) >> 24;  // b0<<6 | b1<<4 | b2<<2 | b3
 }
 
-// One CTA packs PACK_THREADS consecutive tuples: the CTA's n*256 characters are staged into
+// One CTA packs PACK_ROWS consecutive tuples: their n*PACK_ROWS characters are staged into
 // shared memory with coalesced 16-byte loads, then thread t encodes tuple t from its row.
+// The cut / pad rule (makeStringSize_, src/fastq.cc:57-66) only decides `filtered`: a segment
+// shorter than its share would be padded with 'N', so the tuple is dropped and its characters
+// no longer matter.
 __global__ void __launch_bounds__(PACK_THREADS)
     pack_words_kernel(const uint8_t *__restrict__ chars, const uint16_t *__restrict__ seg_len, uint64_t n_tuples,
                       PackParams pp, uint64_t *__restrict__ keys_out, unsigned long long *__restrict__ usable) {
   extern __shared__ __align__(16) uint8_t tile[];
-  const uint64_t t0 = (uint64_t)blockIdx.x * PACK_THREADS;
-  const uint32_t rows = (uint32_t)min((uint64_t)PACK_THREADS, n_tuples - t0);
+  const uint64_t t0 = (uint64_t)blockIdx.x * PACK_ROWS;
+  const uint32_t rows = (uint32_t)min((uint64_t)PACK_ROWS, n_tuples - t0);
   const uint32_t bytes = rows * pp.n;
   const uint8_t *src = chars + t0 * pp.n;
   if ((((uintptr_t)src) & 15u) == 0) {
     const uint32_t vecs = bytes >> 4;
+#pragma unroll 6
     for (uint32_t i = threadIdx.x; i < vecs; i += PACK_THREADS)
       reinterpret_cast<uint4 *>(tile)[i] = ld_stream_u128(src + 16ull * i);
     for (uint32_t i = (vecs << 4) + threadIdx.x; i < bytes; i += PACK_THREADS) tile[i] = src[i];
@@ -42,23 +53,35 @@ __global__ void __launch_bounds__(PACK_THREADS)
   }
   __syncthreads();
 
-  bool ok = threadIdx.x < rows;
-  uint64_t key = 0;
-  bool bad = false;
-  if (ok) {
-    const uint8_t *row = tile + threadIdx.x * pp.n;
-    const uint16_t *sl = seg_len ? seg_len + (t0 + threadIdx.x) * pp.n_segs : nullptr;
-    uint32_t p = 0;
-    for (uint32_t s = 0; s < pp.n_segs; s++) {
-      // makeStringSize_: a segment shorter than its share is padded with 'N' => filtered
-      uint32_t have = sl ? sl[s] : pp.take[s];
-      bad |= have < pp.take[s];
-      for (uint32_t q = 0; q < pp.take[s]; q++, p++) key = (key << 2) | nt_code(row[p], bad);
+  uint32_t n_good = 0;
+  for (uint32_t rr = threadIdx.x; rr < rows; rr += PACK_THREADS) {
+    uint64_t key = 0;
+    bool bad = false;
+    const uint8_t *row = tile + rr * pp.n;
+    if (seg_len) {
+      const uint16_t *sl = seg_len + (t0 + rr) * pp.n_segs;
+      for (uint32_t s = 0; s < pp.n_segs; s++) bad |= sl[s] < pp.take[s];
     }
-    keys_out[t0 + threadIdx.x] = bad ? KEY_INVALID : key;
+    const uint32_t full = pp.n & ~3u;
+    if ((pp.n & 3u) == 0) {  // rows are 4-byte aligned in shared memory
+      const uint32_t *row4 = reinterpret_cast<const uint32_t *>(row);
+      for (uint32_t q = 0; q < full; q += 4) key = (key << 8) | pack4(row4[q >> 2], bad);
+    } else {
+      for (uint32_t q = 0; q < full; q += 4) {
+        uint32_t x = row[q] | (row[q + 1] << 8) | (row[q + 2] << 16) | ((uint32_t)row[q + 3] << 24);
+        key = (key << 8) | pack4(x, bad);
+      }
+    }
+    for (uint32_t q = full; q < pp.n; q++) {
+      uint32_t one = pack4(row[q] | 0x41414100u, bad);  // pad with 'A' (code 0, valid)
+      key = (key << 2) | ((one >> 6) & 3u);
+    }
+    keys_out[t0 + rr] = bad ? KEY_INVALID : key;
+    n_good += bad ? 0u : 1u;
   }
-  unsigned good = __ballot_sync(0xffffffffu, ok && !bad);
-  if (lane_id() == 0 && good) atomicAdd(usable, (unsigned long long)__popc(good));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) n_good += __shfl_xor_sync(0xffffffffu, n_good, o);
+  if (lane_id() == 0 && n_good) atomicAdd(usable, (unsigned long long)n_good);
 }
 
 int stage_pack(State &s, const uint8_t *d_chars, const uint16_t *d_seg_len, uint64_t first, uint64_t n) {
@@ -67,8 +90,8 @@ int stage_pack(State &s, const uint8_t *d_chars, const uint16_t *d_seg_len, uint
   pp.n = s.cfg.word_length;
   pp.n_segs = s.cfg.n_segments;
   for (uint32_t i = 0; i < pp.n_segs; i++) pp.take[i] = s.cfg.seg_take[i];
-  unsigned grid = grid_for(n, PACK_THREADS);
-  size_t smem = (size_t)PACK_THREADS * pp.n;
+  unsigned grid = grid_for(n, PACK_ROWS);
+  size_t smem = (size_t)PACK_ROWS * pp.n;
   // makeWord: n ASCII bytes in, one 8-byte key out
   Timed t(s, "pack", n, n * (pp.n + 8));
   pack_words_kernel<<<grid, PACK_THREADS, smem, s.stream>>>(d_chars, d_seg_len, n, pp, s.tuple_key.p + first,
@@ -92,15 +115,23 @@ __global__ void table_clear_kernel(Slot *slots, uint64_t cap) {
 }
 
 __global__ void __launch_bounds__(256)
-    table_insert_kernel(const uint64_t *__restrict__ keys, uint64_t n_tuples, Slot *slots, uint64_t mask) {
+    table_insert_kernel(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ tuple_index,
+                        uint64_t n_tuples, Slot *slots, uint64_t mask) {
   uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n_tuples) return;
   uint64_t key = ld_stream_u64(keys + t);
   if (key == KEY_INVALID) return;
+  // position of the tuple in the job's input order (shard mode: tuples arrive from other ranks)
+  const uint32_t ti = tuple_index ? tuple_index[t] : (uint32_t)t;
   uint64_t idx = mix64(key) & mask;
+  uint32_t seen_first = 0xFFFFFFFFu;
   while (true) {
-    uint64_t cur = *reinterpret_cast<volatile uint64_t *>(&slots[idx].key);
-    if (cur == key) break;
+    uint4 v;
+    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(slots + idx));
+    uint64_t cur = ((uint64_t)v.y << 32) | v.x;
+    if (cur == key) { seen_first = v.w; break; }
     if (cur == KEY_INVALID) {
       unsigned long long prev = atomicCAS(reinterpret_cast<unsigned long long *>(&slots[idx].key),
                                           (unsigned long long)KEY_INVALID, (unsigned long long)key);
@@ -108,8 +139,10 @@ __global__ void __launch_bounds__(256)
     }
     idx = (idx + 1) & mask;
   }
-  atomicAdd(&slots[idx].count, 1u);            // Leaf::count++
-  atomicMin(&slots[idx].first, (uint32_t)t);   // first tuple in input order
+  atomicAdd(&slots[idx].count, 1u);  // Leaf::count++
+  // first tuple in input order; `first` only ever decreases, so a stale larger value read
+  // above merely costs the atomic, a smaller one proves it is not needed
+  if (ti < seen_first) atomicMin(&slots[idx].first, ti);
 }
 
 // Occupied slots -> (key, slot) pairs, any order (they are sorted next).  One atomic per CTA:
@@ -213,7 +246,7 @@ int stage_build_table(State &s, bool with_filter) {
   HUMID_CUDA(cudaMemcpyAsync(&s.usable, s.counters.p + 0, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
   HUMID_CUDA(cudaStreamSynchronize(s.stream));
   uint64_t cap = 1024;
-  while (cap < 2 * s.usable) cap <<= 1;
+  while (4 * cap < 5 * s.usable) cap <<= 1;  // load factor <= 0.8 if every tuple were distinct, ~0.3 typically
   if (cap > (1ull << 32)) throw CudaError{"word table would exceed 2^32 slots"};
   s.table_cap = cap;
   s.slots.ensure(cap);
@@ -225,7 +258,7 @@ int stage_build_table(State &s, bool with_filter) {
   if (s.n_tuples) {
     // key in (8) + slot key (8) + count RMW (8) + first RMW (8)
     Timed t(s, "table_insert", s.n_tuples, s.n_tuples * 8 + s.usable * 24);
-    table_insert_kernel<<<grid_for(s.n_tuples, 256), 256, 0, s.stream>>>(s.tuple_key.p, s.n_tuples, s.slots.p,
+    table_insert_kernel<<<grid_for(s.n_tuples, 256), 256, 0, s.stream>>>(s.tuple_key.p, nullptr, s.n_tuples, s.slots.p,
                                                                         cap - 1);
     k++;
   }
