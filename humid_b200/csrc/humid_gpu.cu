@@ -86,7 +86,7 @@ void humid_gpu_destroy(humid_gpu *h) {
   s.comp.release(); s.label.release(); s.members.release(); s.seg_start.release(); s.seg_end.release();
   s.work_a.release(); s.work_b.release(); s.work_c.release(); s.seed_flag.release(); s.seed_index.release();
   s.seed_size.release(); s.seed_max.release(); s.cluster_size.release(); s.cluster_max.release();
-  s.shard_slots.release(); s.local_word_grank.release(); s.filter.release();
+  s.shard_keys.release(); s.shard_index.release(); s.filter.release();
   s.keep_bits.release(); s.out_ids.release(); s.scratch.release(); s.scan_scratch.release();
   if (s.stream) cudaStreamDestroy(s.stream);
   delete h;
@@ -102,7 +102,9 @@ int humid_gpu_reset(humid_gpu *h) {
     s.n_tuples = s.usable = s.unique = s.n_entries = s.n_clusters = 0;
     s.finalized = false;
     s.shard_mode = false;
-    s.report_tuples = s.report_usable = s.tuple_base = s.n_local_words = s.n_shard_words = 0;
+    s.report_tuples = s.report_usable = s.tuple_base = s.n_shard_words = s.src_n = 0;
+    s.src_keys = nullptr;
+    s.src_index = nullptr;
     s.part = 0;
     s.n_parts = 1;
     for (int i = 0; i < 3; i++) s.hist_done[i] = false;

@@ -289,9 +289,20 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-int stage_csr_pairs(State &s) {
-  const uint64_t U = s.unique, P = s.n_pairs, E = 2 * P;
-  s.n_entries = E;
+// Directed entries (row << 32 | column) with the list lengths already counted in `deg`
+// (shard mode: rows are shard-local ranks, columns global ranks).
+__global__ void __launch_bounds__(256)
+    csr_fill_directed_kernel(const uint64_t *__restrict__ entries, uint64_t E, const uint32_t *__restrict__ excl,
+                             uint32_t *__restrict__ cursor, uint32_t *__restrict__ col) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= E) return;
+  uint64_t e = ld_stream_u64(entries + i);
+  uint32_t a = (uint32_t)(e >> 32);
+  col[excl[a] + atomicAdd(cursor + a, 1u)] = (uint32_t)e;
+}
+
+static int csr_from_degrees(State &s, uint64_t E, bool pairs) {
+  const uint64_t U = s.unique;
   s.row_ptr.ensure(U + 2);
   s.col.ensure(E + 1);
   s.work_a.ensure(U + 1);  // exclusive scan of deg
@@ -301,9 +312,12 @@ int stage_csr_pairs(State &s) {
   if (U) k += exclusive_scan_u32(s.deg.p, s.work_a.p, U, nullptr, s.scan_scratch, s.stream);
   csr_rows_kernel<<<grid_for(U + 1, 256), 256, 0, s.stream>>>(s.work_a.p, U, E, s.row_ptr.p);
   k++;
-  if (P) {
+  if (E) {
     HUMID_CUDA(cudaMemsetAsync(s.work_b.p, 0, U * sizeof(uint32_t), s.stream));
-    csr_fill_kernel<<<grid_for(P, 256), 256, 0, s.stream>>>(s.entries.p, P, s.work_a.p, s.work_b.p, s.col.p);
+    if (pairs)
+      csr_fill_kernel<<<grid_for(E / 2, 256), 256, 0, s.stream>>>(s.entries.p, E / 2, s.work_a.p, s.work_b.p, s.col.p);
+    else
+      csr_fill_directed_kernel<<<grid_for(E, 256), 256, 0, s.stream>>>(s.entries.p, E, s.work_a.p, s.work_b.p, s.col.p);
     HUMID_CUDA(cudaMemsetAsync(s.counters.p + 7, 0, sizeof(unsigned long long), s.stream));
     csr_sort_rows_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.work_a.p, s.deg.p, U, s.col.p, s.work_b.p,
                                                                  s.counters.p + 7);
@@ -320,6 +334,13 @@ int stage_csr_pairs(State &s) {
   t.launches = k;
   return k;
 }
+
+int stage_csr_pairs(State &s) {
+  s.n_entries = 2 * s.n_pairs;
+  return csr_from_degrees(s, s.n_entries, true);
+}
+
+int stage_csr_directed(State &s) { return csr_from_degrees(s, s.n_entries, false); }
 
 // ------------------------------------------------------------------------------------
 // CSR: sort the directed entries by (source rank, order key), then split.

@@ -18,6 +18,7 @@ struct Layout {
   uint32_t part, n_parts;
   uint64_t splitters[HUMID_MAX_PARTS];  // n_parts-1 used
   uint32_t base;                        // global rank of this shard's first word
+  uint64_t hi;                          // first key above this shard's range (upward variants never fall below it)
 };
 
 __device__ __forceinline__ uint32_t owner_of(const Layout &L, uint64_t key) {
@@ -26,79 +27,69 @@ __device__ __forceinline__ uint32_t owner_of(const Layout &L, uint64_t key) {
   return p;
 }
 
-// ---- words ---------------------------------------------------------------------------------
-__global__ void add_offset_kernel(uint32_t *a, uint64_t n, uint32_t off) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) a[i] += off;
-}
-
-__global__ void sample_keys_kernel(const uint64_t *__restrict__ keys, uint64_t U, uint32_t n, uint64_t *out) {
+// ---- tuples to their owners ------------------------------------------------------------------
+// up to n evenly spaced usable tuple keys (tuples are in random order w.r.t. their keys)
+__global__ void sample_tuple_keys_kernel(const uint64_t *__restrict__ keys, uint64_t R, uint32_t n, uint64_t *out,
+                                         unsigned long long *counter) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) out[i] = keys[(uint64_t)(((unsigned __int128)i * U + U / 2) / n) % U];
+  if (i >= n) return;
+  uint64_t k = keys[(uint64_t)(((unsigned __int128)i * R + R / 2) / n) % R];
+  if (k != KEY_INVALID) out[atomicAdd(counter, 1ull)] = k;
 }
 
-__global__ void split_kernel(const uint64_t *__restrict__ keys, uint64_t U, const Layout L, uint64_t *bounds) {
-  uint32_t i = threadIdx.x;  // bounds[i] = first index with key >= splitters[i]
-  if (i + 1 >= L.n_parts) return;
-  uint64_t lo = 0, hi = U;
-  while (lo < hi) {
-    uint64_t mid = (lo + hi) >> 1;
-    if (keys[mid] < L.splitters[i]) lo = mid + 1; else hi = mid;
-  }
-  bounds[i] = lo;
-}
-
-__global__ void iota32_kernel(uint32_t *a, uint64_t n) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) a[i] = (uint32_t)i;
-}
-
-__global__ void mark_heads_kernel(const uint64_t *__restrict__ sorted, uint64_t n, uint32_t *flag) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) flag[i] = (i > 0 && sorted[i] != sorted[i - 1]) ? 1u : 0u;  // inclusive scan => word index
-}
-
-// sorted record i (original position idx[i]) belongs to shard word widx = scan[i] + flag[i]
+// MODE 0: usable tuples per destination part.  MODE 1: scatter {key, global tuple index} into
+// the destination's region (cursors = exclusive prefix of the counts).  One global atomic per
+// CTA and part; positions inside a part are arbitrary (the owner does not depend on them).
+template <int MODE>
 __global__ void __launch_bounds__(256)
-    merge_words_kernel(const uint64_t *__restrict__ sorted, const uint32_t *__restrict__ idx,
-                       const uint32_t *__restrict__ flag, const uint32_t *__restrict__ scan, uint64_t n,
-                       const uint32_t *__restrict__ in_count, const uint32_t *__restrict__ in_first,
-                       uint64_t *__restrict__ word_key, uint32_t *__restrict__ word_count,
-                       uint32_t *__restrict__ word_first, uint32_t *__restrict__ local_rank_out) {
+    partition_tuples_kernel(const uint64_t *__restrict__ keys, uint64_t R, uint32_t tuple_base, const Layout L,
+                            unsigned long long *__restrict__ part_counts, uint64_t *__restrict__ out_keys,
+                            uint32_t *__restrict__ out_index) {
+  __shared__ uint32_t cnt[HUMID_MAX_PARTS];
+  __shared__ unsigned long long base[HUMID_MAX_PARTS];
+  constexpr int ITEMS = 4;
+  if (threadIdx.x < HUMID_MAX_PARTS) cnt[threadIdx.x] = 0;
+  __syncthreads();
+  const uint64_t t0 = (uint64_t)blockIdx.x * (256 * ITEMS);
+  uint64_t key[ITEMS];
+  uint32_t own[ITEMS], slot[ITEMS];
+#pragma unroll
+  for (int j = 0; j < ITEMS; j++) {
+    uint64_t t = t0 + (uint64_t)j * 256 + threadIdx.x;
+    key[j] = t < R ? ld_stream_u64(keys + t) : KEY_INVALID;
+    own[j] = 0;
+    if (key[j] != KEY_INVALID) {
+      own[j] = owner_of(L, key[j]);
+      slot[j] = atomicAdd(&cnt[own[j]], 1u);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < L.n_parts) {
+    uint32_t c = cnt[threadIdx.x];
+    base[threadIdx.x] = c ? atomicAdd(part_counts + threadIdx.x, (unsigned long long)c) : 0ull;
+  }
+  if (MODE == 0) return;
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < ITEMS; j++) {
+    if (key[j] != KEY_INVALID) {
+      unsigned long long pos = base[own[j]] + slot[j];
+      out_keys[pos] = key[j];
+      out_index[pos] = tuple_base + (uint32_t)(t0 + (uint64_t)j * 256 + threadIdx.x);
+    }
+  }
+}
+
+// cluster id of every tuple this shard received (after import_graph: label / seed_index are
+// whole-job columns indexed by global rank)
+__global__ void __launch_bounds__(256)
+    shard_tuple_ids_kernel(const uint64_t *__restrict__ keys, uint64_t n, const Lookup lk, uint32_t base,
+                           const uint32_t *__restrict__ label, const uint32_t *__restrict__ seed_index,
+                           uint32_t *__restrict__ out) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  uint32_t w = scan[i] + flag[i];
-  uint32_t o = idx[i];
-  if (i == 0 || flag[i]) word_key[w] = sorted[i];
-  atomicAdd(word_count + w, in_count[o]);   // Leaf::count summed over the ranks
-  atomicMin(word_first + w, in_first[o]);   // first tuple in global input order
-  local_rank_out[o] = w;
-}
-
-__global__ void __launch_bounds__(256)
-    word_table_insert_kernel(const uint64_t *__restrict__ word_key, uint64_t U, Slot *slots, uint64_t mask) {
-  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (r >= U) return;
-  uint64_t key = word_key[r];
-  uint64_t idx = mix64(key) & mask;
-  while (true) {
-    unsigned long long prev = atomicCAS(reinterpret_cast<unsigned long long *>(&slots[idx].key),
-                                        (unsigned long long)KEY_INVALID, (unsigned long long)key);
-    if (prev == KEY_INVALID) break;  // keys are distinct
-    idx = (idx + 1) & mask;
-  }
-  slots[idx].count = (uint32_t)r;  // rank
-}
-
-__global__ void table_clear2_kernel(Slot *slots, uint64_t cap) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < cap) {
-    uint4 v;
-    v.x = v.y = 0xFFFFFFFFu;
-    v.z = 0u;
-    v.w = 0xFFFFFFFFu;
-    reinterpret_cast<uint4 *>(slots)[i] = v;
-  }
+  uint32_t r = table_rank(lk, keys[i]);  // always present: the tuple was inserted here
+  out[i] = seed_index[label[base + r]] + 1u;
 }
 
 // ---- probe ---------------------------------------------------------------------------------
@@ -141,7 +132,7 @@ __global__ void __launch_bounds__(256)
     shard_probe_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, uint32_t d, const Layout L,
                        const Lookup lk, unsigned long long *__restrict__ part_counts /* MODE 0: totals; MODE 1: cursors */,
                        uint64_t *__restrict__ q_keys, uint32_t *__restrict__ q_src, uint64_t *__restrict__ entries,
-                       uint64_t cap, unsigned long long *__restrict__ entry_counter) {
+                       uint64_t cap, unsigned long long *__restrict__ entry_counter, uint32_t *__restrict__ deg) {
   __shared__ uint32_t cnt[HUMID_MAX_PARTS];
   __shared__ unsigned long long base[HUMID_MAX_PARTS];
   if (threadIdx.x < HUMID_MAX_PARTS) cnt[threadIdx.x] = 0;
@@ -153,8 +144,7 @@ __global__ void __launch_bounds__(256)
   const uint64_t w = live ? word_key[r] : 0ull;
   if (live)
     for_each_upward_variant(w, n, d, p1, [&](uint64_t v) {
-      uint32_t o = owner_of(L, v);
-      if (o != L.part) atomicAdd(&cnt[o], 1u);
+      if (v >= L.hi) atomicAdd(&cnt[owner_of(L, v)], 1u);
     });
   __syncthreads();
   if (threadIdx.x < L.n_parts) {
@@ -167,8 +157,7 @@ __global__ void __launch_bounds__(256)
   if (!live) return;
   const uint32_t me = L.base + (uint32_t)r;
   for_each_upward_variant(w, n, d, p1, [&](uint64_t v) {
-    uint32_t o = owner_of(L, v);
-    if (o == L.part) {
+    if (v < L.hi) {
       uint32_t hit = lookup_rank(lk, v);
       if (hit != NONE32) {
         unsigned long long pos = atomicAdd(entry_counter, 2ull);
@@ -176,9 +165,12 @@ __global__ void __launch_bounds__(256)
           // rows are shard-local, columns global
           entries[pos] = (r << 32) | (uint64_t)(L.base + hit);
           entries[pos + 1] = ((uint64_t)hit << 32) | me;
+          atomicAdd(deg + r, 1u);
+          atomicAdd(deg + hit, 1u);
         }
       }
     } else {
+      const uint32_t o = owner_of(L, v);
       unsigned long long pos = base[o] + atomicAdd(&cnt[o], 1u);
       q_keys[pos] = v;
       q_src[pos] = me;
@@ -186,30 +178,148 @@ __global__ void __launch_bounds__(256)
   });
 }
 
+// d == 1: one thread per word (the single-GPU hamming1_probe_kernel plus routing).  An upward
+// variant is larger than its word, so it is either in this shard's range or in a later one.
+// Remote variants are counted per destination in shared memory, one reservation per CTA and
+// part, then the enumeration is repeated to write them.
+template <int MODE>
+__global__ void __launch_bounds__(128)
+    shard_probe1_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, const Layout L, const Lookup lk,
+                        unsigned long long *__restrict__ part_counts, uint64_t *__restrict__ q_keys,
+                        uint32_t *__restrict__ q_src, uint64_t *__restrict__ entries, uint64_t cap,
+                        unsigned long long *__restrict__ entry_counter, uint32_t *__restrict__ deg) {
+  __shared__ uint32_t cnt[HUMID_MAX_PARTS];
+  __shared__ unsigned long long base[HUMID_MAX_PARTS];
+  if (threadIdx.x < HUMID_MAX_PARTS) cnt[threadIdx.x] = 0;
+  __syncthreads();
+  const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = r < U;
+  const uint64_t w = live ? ld_stream_u64(word_key + r) : 0ull;
+  // variants at position p exceed the range only if w + (3 << sh) can reach hi at all
+  uint32_t p_remote_end = 0;  // positions [0, p_remote_end) may produce remote variants
+  if (live)
+    while (p_remote_end < n && w + (3ull << (2 * (n - 1 - p_remote_end))) >= L.hi) p_remote_end++;
+  for (uint32_t p = 0; p < p_remote_end; p++) {
+    const uint32_t sh = 2 * (n - 1 - p);
+    const uint32_t wl = (uint32_t)(w >> sh) & 3u;
+    for (uint32_t c = 1; wl + c <= 3u; c++) {
+      const uint64_t v = w + ((uint64_t)c << sh);
+      if (v >= L.hi) atomicAdd(&cnt[owner_of(L, v)], 1u);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < L.n_parts) {
+    uint32_t c = cnt[threadIdx.x];
+    base[threadIdx.x] = c ? atomicAdd(part_counts + threadIdx.x, (unsigned long long)c) : 0ull;
+    cnt[threadIdx.x] = 0;
+  }
+  if (MODE == 0) return;
+  __syncthreads();
+  const uint32_t me = L.base + (uint32_t)r;
+  const uint64_t hw = filter_hash(w);
+  const uint64_t pol_keep = l2_policy_evict_last();
+  constexpr int LOCAL_HITS = 6;
+  uint32_t hits[LOCAL_HITS];
+  uint32_t nh = 0;
+  for (uint32_t p = 0; p < n; p++) {
+    const uint32_t sh = 2 * (n - 1 - p);
+    const uint32_t wl = (uint32_t)(w >> sh) & 3u;
+    const uint64_t step = FILTER_MUL << sh;
+    uint4 bkt[3];
+    uint64_t hf[3];
+    bool local[3];
+#pragma unroll
+    for (uint32_t c = 1; c < 4; c++) {
+      hf[c - 1] = hw + step * c;
+      const uint64_t v = w + ((uint64_t)c << sh);
+      const bool valid = live && wl + c <= 3u;
+      local[c - 1] = valid && v < L.hi;
+      if (local[c - 1]) bkt[c - 1] = ld_hint_u128(lk.filter + filter_bucket(hf[c - 1], lk.n_buckets), pol_keep);
+      if (valid && !local[c - 1]) {
+        const uint32_t o = owner_of(L, v);
+        const unsigned long long pos = base[o] + atomicAdd(&cnt[o], 1u);
+        q_keys[pos] = v;
+        q_src[pos] = me;
+      }
+    }
+#pragma unroll
+    for (uint32_t c = 1; c < 4; c++) {
+      if (local[c - 1] && filter_match(bkt[c - 1], hf[c - 1])) {
+        const uint32_t hit = table_rank(lk, w + ((uint64_t)c << sh));
+        if (hit != NONE32) {
+          if (nh == LOCAL_HITS) {
+            unsigned long long pos = atomicAdd(entry_counter, 2ull * nh);
+            if (pos + 2ull * nh <= cap) {
+              for (uint32_t k = 0; k < nh; k++) {
+                entries[pos + 2 * k] = (r << 32) | (uint64_t)(L.base + hits[k]);
+                entries[pos + 2 * k + 1] = ((uint64_t)hits[k] << 32) | me;
+                atomicAdd(deg + hits[k], 1u);
+              }
+              atomicAdd(deg + r, nh);
+            }
+            nh = 0;
+          }
+          hits[nh++] = hit;
+        }
+      }
+    }
+  }
+  const uint32_t lane = lane_id();
+  uint32_t inc = nh;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+    if ((int)lane >= o) inc += t;
+  }
+  const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
+  if (total == 0) return;
+  unsigned long long wbase = 0;
+  if (lane == 31) wbase = atomicAdd(entry_counter, 2ull * total);
+  wbase = __shfl_sync(0xffffffffu, wbase, 31);
+  if (nh) {
+    unsigned long long pos = wbase + 2ull * (inc - nh);
+    if (pos + 2ull * nh <= cap) {
+      for (uint32_t k = 0; k < nh; k++) {
+        entries[pos + 2 * k] = (r << 32) | (uint64_t)(L.base + hits[k]);
+        entries[pos + 2 * k + 1] = ((uint64_t)hits[k] << 32) | me;
+        atomicAdd(deg + hits[k], 1u);
+      }
+      atomicAdd(deg + r, nh);
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256)
     shard_answer_kernel(const uint64_t *__restrict__ q_keys, const uint32_t *__restrict__ q_src, uint64_t n,
                         const Layout L, const Lookup lk, uint32_t *__restrict__ answers,
-                        uint64_t *__restrict__ entries, uint64_t cap, unsigned long long *__restrict__ entry_counter) {
+                        uint64_t *__restrict__ entries, uint64_t cap, unsigned long long *__restrict__ entry_counter,
+                        uint32_t *__restrict__ deg) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   uint32_t hit = lookup_rank(lk, q_keys[i]);
   answers[i] = hit == NONE32 ? NONE32 : L.base + hit;
   if (hit != NONE32) {
     unsigned long long pos = atomicAdd(entry_counter, 1ull);
-    if (pos < cap) entries[pos] = ((uint64_t)hit << 32) | q_src[i];  // result leaf <- walk leaf
+    if (pos < cap) {
+      entries[pos] = ((uint64_t)hit << 32) | q_src[i];  // result leaf <- walk leaf
+      atomicAdd(deg + hit, 1u);
+    }
   }
 }
 
 __global__ void __launch_bounds__(256)
     shard_apply_kernel(const uint32_t *__restrict__ q_src, const uint32_t *__restrict__ answers, uint64_t n,
                        const Layout L, uint64_t *__restrict__ entries, uint64_t cap,
-                       unsigned long long *__restrict__ entry_counter) {
+                       unsigned long long *__restrict__ entry_counter, uint32_t *__restrict__ deg) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   uint32_t a = answers[i];
   if (a != NONE32) {
     unsigned long long pos = atomicAdd(entry_counter, 1ull);
-    if (pos < cap) entries[pos] = ((uint64_t)(q_src[i] - L.base) << 32) | a;  // walk leaf <- result leaf
+    if (pos < cap) {
+      entries[pos] = ((uint64_t)(q_src[i] - L.base) << 32) | a;  // walk leaf <- result leaf
+      atomicAdd(deg + (q_src[i] - L.base), 1u);
+    }
   }
 }
 
@@ -225,33 +335,13 @@ __global__ void widen_rows_kernel(const uint32_t *__restrict__ excl, uint64_t U,
   if (r == U) row_ptr[U] = total;
 }
 
-__global__ void __launch_bounds__(256)
-    shard_cluster_ids_kernel(const uint64_t *__restrict__ tuple_key, uint64_t first, uint64_t n,
-                             const Slot *__restrict__ slots, uint64_t mask, const uint32_t *__restrict__ grank,
-                             const uint32_t *__restrict__ label, const uint32_t *__restrict__ seed_index,
-                             uint32_t *__restrict__ out) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  uint64_t key = tuple_key[first + i];
-  uint32_t id = 0;
-  if (key != KEY_INVALID) {
-    uint64_t idx = mix64(key) & mask;
-    while (true) {
-      uint4 v = __ldg(reinterpret_cast<const uint4 *>(slots + idx));
-      uint64_t k = ((uint64_t)v.y << 32) | v.x;
-      if (k == key) { id = seed_index[label[grank[v.z]]] + 1u; break; }
-      idx = (idx + 1) & mask;
-    }
-  }
-  out[i] = id;
-}
-
 static Layout layout_of(const State &s) {
   Layout L{};
   L.part = s.part;
   L.n_parts = s.n_parts;
   for (uint32_t i = 0; i + 1 < s.n_parts; i++) L.splitters[i] = s.splitters[i];
   L.base = (uint32_t)s.bases[s.part];
+  L.hi = s.part + 1 < s.n_parts ? s.splitters[s.part] : ~0ull;
   return L;
 }
 
@@ -267,138 +357,119 @@ static int require_shard(humid_gpu *h, bool want) {
 
 extern "C" {
 
-int humid_gpu_shard_local_words(humid_gpu *h, uint64_t tuple_offset, uint64_t *n_local_words, uint64_t *n_usable) {
-  if (!h || !n_local_words) return HUMID_GPU_ERR_ARG;
+int humid_gpu_shard_begin(humid_gpu *h, uint64_t tuple_offset, uint64_t *n_usable) {
+  if (!h) return HUMID_GPU_ERR_ARG;
   State &s = h->s;
-  if (s.finalized || s.shard_mode) return fail(h, HUMID_GPU_ERR_ARG, "shard_local_words: wrong call order");
+  if (s.finalized || s.shard_mode) return fail(h, HUMID_GPU_ERR_ARG, "shard_begin: wrong call order");
   if (s.cfg.edit && s.cfg.distance >= 2)
     return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "edit distance >= 2 is not sharded (use one GPU)");
   if (s.cfg.distance > SHARD_MAX_D) return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "distance > 8");
   if (tuple_offset + s.n_tuples >= 0xFFFFFFFFull) return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "more than 2^32-2 tuples");
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
-    stage_build_table(s, /*with_filter=*/false);
-    s.tuple_base = tuple_offset;
-    s.n_local_words = s.unique;
-    if (tuple_offset && s.unique)
-      add_offset_kernel<<<grid_for(s.unique, 256), 256, 0, s.stream>>>(s.word_first.p, s.unique, (uint32_t)tuple_offset);
+    HUMID_CUDA(cudaMemcpyAsync(&s.usable, s.counters.p + 0, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    s.tuple_base = tuple_offset;
     s.shard_mode = true;
-    *n_local_words = s.unique;
     if (n_usable) *n_usable = s.usable;
   });
 }
 
-int humid_gpu_shard_sample_keys(humid_gpu *h, uint32_t n_samples, uint64_t *keys_out) {
+int humid_gpu_shard_sample_keys(humid_gpu *h, uint32_t n_samples, uint64_t *keys_out, uint32_t *n_out) {
   if (int rc = require_shard(h, true)) return rc;
   State &s = h->s;
-  if (!keys_out || n_samples == 0 || s.n_local_words == 0) return fail(h, HUMID_GPU_ERR_ARG, "sample_keys: nothing to sample");
+  if (!keys_out || !n_out) return fail(h, HUMID_GPU_ERR_ARG, "sample_keys: null argument");
+  *n_out = 0;
+  if (n_samples == 0 || s.n_tuples == 0) return HUMID_GPU_OK;
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
     uint64_t *tmp = (uint64_t *)s.scratch.get(n_samples * sizeof(uint64_t));
-    sample_keys_kernel<<<(n_samples + 255) / 256, 256, 0, s.stream>>>(s.word_key.p, s.n_local_words, n_samples, tmp);
-    HUMID_CUDA(cudaMemcpyAsync(keys_out, tmp, n_samples * sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+    HUMID_CUDA(cudaMemsetAsync(s.counters.p + 9, 0, sizeof(unsigned long long), s.stream));
+    sample_tuple_keys_kernel<<<(n_samples + 255) / 256, 256, 0, s.stream>>>(s.tuple_key.p, s.n_tuples, n_samples, tmp,
+                                                                            s.counters.p + 9);
+    uint64_t got = 0;
+    HUMID_CUDA(cudaMemcpyAsync(&got, s.counters.p + 9, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    if (got) HUMID_CUDA(cudaMemcpy(keys_out, tmp, got * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    *n_out = (uint32_t)got;
   });
 }
 
-int humid_gpu_shard_split(humid_gpu *h, const uint64_t *splitters, uint32_t n_parts, uint64_t *counts) {
+static void run_partition(State &s, const uint64_t *splitters, uint32_t n_parts, int mode, const uint64_t *offsets,
+                          uint64_t *d_keys, uint32_t *d_index, uint64_t *counts_out) {
+  Layout L{};
+  L.n_parts = n_parts;
+  for (uint32_t i = 0; i + 1 < n_parts; i++) L.splitters[i] = splitters[i];
+  unsigned long long *pc = s.counters.p + 16;
+  unsigned long long init[HUMID_MAX_PARTS] = {0};
+  if (offsets) for (uint32_t p = 0; p < n_parts; p++) init[p] = offsets[p];
+  HUMID_CUDA(cudaMemcpyAsync(pc, init, sizeof(init), cudaMemcpyHostToDevice, s.stream));
+  if (s.n_tuples) {
+    Timed t(s, mode ? "shard_partition_tuples" : "shard_count_tuples", s.n_tuples, s.n_tuples * (mode ? 20 : 8));
+    unsigned grid = grid_for(s.n_tuples, 256, 4);
+    if (mode)
+      partition_tuples_kernel<1><<<grid, 256, 0, s.stream>>>(s.tuple_key.p, s.n_tuples, (uint32_t)s.tuple_base, L, pc,
+                                                             d_keys, d_index);
+    else
+      partition_tuples_kernel<0><<<grid, 256, 0, s.stream>>>(s.tuple_key.p, s.n_tuples, (uint32_t)s.tuple_base, L, pc,
+                                                             nullptr, nullptr);
+  }
+  HUMID_CUDA(cudaGetLastError());
+  if (counts_out) {
+    unsigned long long host[HUMID_MAX_PARTS];
+    HUMID_CUDA(cudaMemcpyAsync(host, pc, sizeof(host), cudaMemcpyDeviceToHost, s.stream));
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    for (uint32_t p = 0; p < n_parts; p++) counts_out[p] = host[p];
+  } else {
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+  }
+}
+
+int humid_gpu_shard_partition(humid_gpu *h, const uint64_t *splitters, uint32_t n_parts, uint64_t *counts) {
   if (int rc = require_shard(h, true)) return rc;
   State &s = h->s;
   if (!counts || n_parts == 0 || n_parts > HUMID_MAX_PARTS || (n_parts > 1 && !splitters))
-    return fail(h, HUMID_GPU_ERR_ARG, "split: bad arguments");
+    return fail(h, HUMID_GPU_ERR_ARG, "partition: bad arguments");
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
-    Layout L{};
-    L.n_parts = n_parts;
-    for (uint32_t i = 0; i + 1 < n_parts; i++) L.splitters[i] = splitters[i];
-    std::vector<uint64_t> b(n_parts + 1, 0);
-    if (n_parts > 1 && s.n_local_words) {
-      uint64_t *tmp = (uint64_t *)s.scratch.get(HUMID_MAX_PARTS * sizeof(uint64_t));
-      split_kernel<<<1, HUMID_MAX_PARTS, 0, s.stream>>>(s.word_key.p, s.n_local_words, L, tmp);
-      HUMID_CUDA(cudaMemcpyAsync(b.data() + 1, tmp, (n_parts - 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
-      HUMID_CUDA(cudaStreamSynchronize(s.stream));
-    }
-    b[n_parts] = s.n_local_words;
-    for (uint32_t p = 0; p < n_parts; p++) counts[p] = b[p + 1] - b[p];
+    s.n_parts = n_parts;
+    for (uint32_t i = 0; i + 1 < n_parts; i++) s.splitters[i] = splitters[i];
+    run_partition(s, splitters, n_parts, 0, nullptr, nullptr, nullptr, counts);
   });
 }
 
-int humid_gpu_shard_export_words(humid_gpu *h, uint64_t *d_keys, uint32_t *d_counts, uint32_t *d_first) {
+int humid_gpu_shard_export_tuples(humid_gpu *h, const uint64_t *offsets, uint64_t *d_keys, uint32_t *d_index) {
   if (int rc = require_shard(h, true)) return rc;
   State &s = h->s;
-  const uint64_t U = s.n_local_words;
-  if (U && (!d_keys || !d_counts || !d_first)) return fail(h, HUMID_GPU_ERR_ARG, "export_words: null buffer");
+  if (!offsets) return fail(h, HUMID_GPU_ERR_ARG, "export_tuples: null offsets");
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
-    if (U) {
-      Timed t(s, "shard_export_words", U, U * 32);
-      HUMID_CUDA(cudaMemcpyAsync(d_keys, s.word_key.p, U * 8, cudaMemcpyDeviceToDevice, s.stream));
-      HUMID_CUDA(cudaMemcpyAsync(d_counts, s.word_count.p, U * 4, cudaMemcpyDeviceToDevice, s.stream));
-      HUMID_CUDA(cudaMemcpyAsync(d_first, s.word_first.p, U * 4, cudaMemcpyDeviceToDevice, s.stream));
-      t.launches = 0;
-    }
-    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    run_partition(s, s.splitters, s.n_parts, 1, offsets, d_keys, d_index, nullptr);
   });
 }
 
-int humid_gpu_shard_import_words(humid_gpu *h, const uint64_t *d_keys, const uint32_t *d_counts,
-                                 const uint32_t *d_first, uint64_t n, uint32_t *d_local_rank, uint64_t *n_shard_words) {
+int humid_gpu_shard_import_tuples(humid_gpu *h, const uint64_t *d_keys, const uint32_t *d_index, uint64_t n,
+                                  uint64_t *n_shard_words) {
   if (int rc = require_shard(h, true)) return rc;
   State &s = h->s;
-  if (!n_shard_words || (n && (!d_keys || !d_counts || !d_first || !d_local_rank)))
-    return fail(h, HUMID_GPU_ERR_ARG, "import_words: null buffer");
-  if (n >= 0xFFFFFFFFull) return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "too many records");
+  if (!n_shard_words || (n && (!d_keys || !d_index))) return fail(h, HUMID_GPU_ERR_ARG, "import_tuples: null buffer");
+  if (n >= 0xFFFFFFFFull) return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "too many tuples in one shard");
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
-    uint64_t U = 0;
+    // keep the received tuples: they are this shard's share of the job from here on
+    s.shard_keys.ensure(n + 1);
+    s.shard_index.ensure(n + 1);
     if (n) {
-      Timed t(s, "shard_merge_words", n, n * (2 * 12 + 24));
-      s.key_alt.ensure(n + 1);
-      s.entries_alt.ensure(n + 1);
-      s.word_slot.ensure(n + 1);
-      s.slot_alt.ensure(n + 1);
-      HUMID_CUDA(cudaMemcpyAsync(s.key_alt.p, d_keys, n * 8, cudaMemcpyDeviceToDevice, s.stream));
-      iota32_kernel<<<grid_for(n, 256), 256, 0, s.stream>>>(s.word_slot.p, n);
-      uint64_t *kb[2] = {s.key_alt.p, s.entries_alt.p};
-      uint32_t *vb[2] = {s.word_slot.p, s.slot_alt.p};
-      int launches = 2;
-      int cur = radix_sort_u64(kb, vb, n, 2 * (int)s.cfg.word_length, s.scratch, s.scan_scratch, s.stream, &launches);
-      s.seed_flag.ensure(n);
-      s.seed_index.ensure(n);
-      mark_heads_kernel<<<grid_for(n, 256), 256, 0, s.stream>>>(kb[cur], n, s.seed_flag.p);
-      uint32_t *total = reinterpret_cast<uint32_t *>(s.counters.p + 6);
-      launches += 1 + exclusive_scan_u32(s.seed_flag.p, s.seed_index.p, n, total, s.scan_scratch, s.stream);
-      uint32_t heads = 0;
-      HUMID_CUDA(cudaMemcpyAsync(&heads, total, sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
-      HUMID_CUDA(cudaStreamSynchronize(s.stream));
-      U = (uint64_t)heads + 1;
-      s.word_key.ensure(U + 1);
-      s.word_count.ensure(U + 1);
-      s.word_first.ensure(U + 1);
-      HUMID_CUDA(cudaMemsetAsync(s.word_count.p, 0, U * 4, s.stream));
-      HUMID_CUDA(cudaMemsetAsync(s.word_first.p, 0xFF, U * 4, s.stream));
-      merge_words_kernel<<<grid_for(n, 256), 256, 0, s.stream>>>(kb[cur], vb[cur], s.seed_flag.p, s.seed_index.p, n,
-                                                                 d_counts, d_first, s.word_key.p, s.word_count.p,
-                                                                 s.word_first.p, d_local_rank);
-      t.launches = launches + 1;
+      HUMID_CUDA(cudaMemcpyAsync(s.shard_keys.p, d_keys, n * 8, cudaMemcpyDeviceToDevice, s.stream));
+      HUMID_CUDA(cudaMemcpyAsync(s.shard_index.p, d_index, n * 4, cudaMemcpyDeviceToDevice, s.stream));
     }
-    s.unique = s.n_shard_words = U;
-    // table of the shard's words (key -> shard-local rank) + fingerprint filter
-    uint64_t cap = 1024;
-    while (cap < 2 * U) cap <<= 1;
-    s.shard_cap = cap;
-    s.shard_slots.ensure(cap);
-    {
-      Timed t(s, "shard_word_table", U, cap * 16 + U * 24);
-      table_clear2_kernel<<<grid_for(cap, 256), 256, 0, s.stream>>>(s.shard_slots.p, cap);
-      if (U) word_table_insert_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.word_key.p, U, s.shard_slots.p, cap - 1);
-      t.launches = 2;
-    }
-    stage_build_filter(s);
-    HUMID_CUDA(cudaGetLastError());
+    s.src_keys = s.shard_keys.p;
+    s.src_index = s.shard_index.p;
+    s.src_n = n;
+    stage_build_table(s);  // the single-GPU table / sort / rank / filter stages on this key range
+    s.n_shard_words = s.unique;
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
-    *n_shard_words = U;
+    *n_shard_words = s.unique;
   });
 }
 
@@ -416,19 +487,6 @@ int humid_gpu_shard_set_layout(humid_gpu *h, uint32_t part, uint32_t n_parts, co
   return HUMID_GPU_OK;
 }
 
-int humid_gpu_shard_set_word_ranks(humid_gpu *h, const uint32_t *d_global_rank, uint64_t n_local_words) {
-  if (int rc = require_shard(h, true)) return rc;
-  State &s = h->s;
-  if (n_local_words != s.n_local_words) return fail(h, HUMID_GPU_ERR_ARG, "set_word_ranks: wrong count");
-  return guarded(h, [&] {
-    HUMID_CUDA(cudaSetDevice(s.device));
-    s.local_word_grank.ensure(n_local_words + 1);
-    if (n_local_words)
-      HUMID_CUDA(cudaMemcpyAsync(s.local_word_grank.p, d_global_rank, n_local_words * 4, cudaMemcpyDeviceToDevice, s.stream));
-    HUMID_CUDA(cudaStreamSynchronize(s.stream));
-  });
-}
-
 int humid_gpu_shard_probe_count(humid_gpu *h, uint64_t *counts) {
   if (int rc = require_shard(h, true)) return rc;
   State &s = h->s;
@@ -441,8 +499,13 @@ int humid_gpu_shard_probe_count(humid_gpu *h, uint64_t *counts) {
     HUMID_CUDA(cudaMemsetAsync(pc, 0, HUMID_MAX_PARTS * sizeof(unsigned long long), s.stream));
     if (U && d) {
       Timed t(s, "shard_probe_count", U, U * 8);
-      shard_probe_kernel<0><<<grid_for(U * n, 256), 256, 0, s.stream>>>(s.word_key.p, U, n, d, layout_of(s), s.lookup(),
-                                                                        pc, nullptr, nullptr, nullptr, 0, nullptr);
+      if (d == 1 && s.filter_buckets)
+        shard_probe1_kernel<0><<<grid_for(U, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, layout_of(s), s.lookup(), pc,
+                                                                       nullptr, nullptr, nullptr, 0, nullptr, nullptr);
+      else
+        shard_probe_kernel<0><<<grid_for(U * n, 256), 256, 0, s.stream>>>(s.word_key.p, U, n, d, layout_of(s),
+                                                                          s.lookup(), pc, nullptr, nullptr, nullptr, 0,
+                                                                          nullptr, nullptr);
     }
     HUMID_CUDA(cudaGetLastError());
     unsigned long long host[HUMID_MAX_PARTS];
@@ -461,6 +524,8 @@ int humid_gpu_shard_probe(humid_gpu *h, uint64_t *d_query_keys, uint32_t *d_quer
     const uint64_t U = s.n_shard_words;
     const uint32_t n = s.cfg.word_length, d = s.cfg.distance;
     s.n_entries = 0;
+    s.deg.ensure(U + 1);
+    if (U) HUMID_CUDA(cudaMemsetAsync(s.deg.p, 0, U * sizeof(uint32_t), s.stream));
     if (U == 0 || d == 0) return;
     unsigned long long *pc = s.counters.p + 16;
     unsigned long long cursors[HUMID_MAX_PARTS] = {0};
@@ -471,12 +536,18 @@ int humid_gpu_shard_probe(humid_gpu *h, uint64_t *d_query_keys, uint32_t *d_quer
       cap = s.entries.cap;
       HUMID_CUDA(cudaMemcpyAsync(pc, cursors, sizeof(cursors), cudaMemcpyHostToDevice, s.stream));
       HUMID_CUDA(cudaMemsetAsync(s.counters.p + 2, 0, sizeof(unsigned long long), s.stream));
+      HUMID_CUDA(cudaMemsetAsync(s.deg.p, 0, U * sizeof(uint32_t), s.stream));
       {
         double probes = d == 1 ? 1.5 * n : d == 2 ? 1.5 * n + 2.25 * n * (n - 1) / 2.0 : 0.0;
         Timed t(s, "shard_probe", U, (uint64_t)(U * 8.0 * (1.0 + probes)));
-        shard_probe_kernel<1><<<grid_for(U * n, 256), 256, 0, s.stream>>>(s.word_key.p, U, n, d, layout_of(s), s.lookup(),
-                                                                          pc, d_query_keys, d_query_src, s.entries.p, cap,
-                                                                          s.counters.p + 2);
+        if (d == 1 && s.filter_buckets)
+          shard_probe1_kernel<1><<<grid_for(U, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, layout_of(s), s.lookup(), pc,
+                                                                         d_query_keys, d_query_src, s.entries.p, cap,
+                                                                         s.counters.p + 2, s.deg.p);
+        else
+          shard_probe_kernel<1><<<grid_for(U * n, 256), 256, 0, s.stream>>>(s.word_key.p, U, n, d, layout_of(s),
+                                                                            s.lookup(), pc, d_query_keys, d_query_src,
+                                                                            s.entries.p, cap, s.counters.p + 2, s.deg.p);
       }
       HUMID_CUDA(cudaGetLastError());
       HUMID_CUDA(cudaMemcpyAsync(&s.n_entries, s.counters.p + 2, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
@@ -498,7 +569,8 @@ int humid_gpu_shard_answer(humid_gpu *h, const uint64_t *d_query_keys, const uin
     s.entries.grow(s.n_entries + n, s.n_entries, s.stream);
     Timed t(s, "shard_answer", n, n * 16);
     shard_answer_kernel<<<grid_for(n, 256), 256, 0, s.stream>>>(d_query_keys, d_query_src, n, layout_of(s), s.lookup(),
-                                                                d_answers, s.entries.p, s.entries.cap, s.counters.p + 2);
+                                                                d_answers, s.entries.p, s.entries.cap, s.counters.p + 2,
+                                                                s.deg.p);
     HUMID_CUDA(cudaGetLastError());
     HUMID_CUDA(cudaMemcpyAsync(&s.n_entries, s.counters.p + 2, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
@@ -515,7 +587,7 @@ int humid_gpu_shard_apply_answers(humid_gpu *h, const uint32_t *d_query_src, con
     s.entries.grow(s.n_entries + n, s.n_entries, s.stream);
     Timed t(s, "shard_apply_answers", n, n * 8);
     shard_apply_kernel<<<grid_for(n, 256), 256, 0, s.stream>>>(d_query_src, d_answers, n, layout_of(s), s.entries.p,
-                                                               s.entries.cap, s.counters.p + 2);
+                                                               s.entries.cap, s.counters.p + 2, s.deg.p);
     HUMID_CUDA(cudaGetLastError());
     HUMID_CUDA(cudaMemcpyAsync(&s.n_entries, s.counters.p + 2, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
@@ -527,7 +599,7 @@ int humid_gpu_shard_build_rows(humid_gpu *h, uint64_t *n_entries) {
   State &s = h->s;
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
-    stage_csr(s);  // rows: the shard's words; sort key (row << 32 | global column)
+    stage_csr_directed(s);  // rows: the shard's words, columns: global ranks
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     if (n_entries) *n_entries = s.n_entries;
   });
@@ -594,24 +666,21 @@ int humid_gpu_shard_import_graph(humid_gpu *h, uint64_t n_words, uint64_t n_entr
   });
 }
 
-int humid_gpu_shard_cluster_ids(humid_gpu *h, uint64_t first_local_tuple, uint64_t n, uint32_t *ids) {
+int humid_gpu_shard_tuple_ids(humid_gpu *h, uint32_t *d_ids) {
   if (int rc = require_shard(h, true)) return rc;
   State &s = h->s;
   if (!s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "not finalized");
-  if (first_local_tuple + n > s.n_tuples) return fail(h, HUMID_GPU_ERR_ARG, "tuple range out of bounds");
-  if (n == 0) return HUMID_GPU_OK;
-  if (!ids) return HUMID_GPU_ERR_ARG;
+  if (s.src_n == 0) return HUMID_GPU_OK;
+  if (!d_ids) return HUMID_GPU_ERR_ARG;
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
-    s.out_ids.ensure(n);
     {
-      Timed t(s, "cluster_ids", n, n * 40);
-      shard_cluster_ids_kernel<<<grid_for(n, 256), 256, 0, s.stream>>>(s.tuple_key.p, first_local_tuple, n, s.slots.p,
-                                                                       s.table_cap - 1, s.local_word_grank.p, s.label.p,
-                                                                       s.seed_index.p, s.out_ids.p);
+      Timed t(s, "cluster_ids", s.src_n, s.src_n * 36);
+      shard_tuple_ids_kernel<<<grid_for(s.src_n, 256), 256, 0, s.stream>>>(s.shard_keys.p, s.src_n, s.lookup(),
+                                                                           (uint32_t)s.bases[s.part], s.label.p,
+                                                                           s.seed_index.p, d_ids);
     }
     HUMID_CUDA(cudaGetLastError());
-    HUMID_CUDA(cudaMemcpyAsync(ids, s.out_ids.p, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     resolve_stats(s);
   });

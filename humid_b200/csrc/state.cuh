@@ -76,23 +76,22 @@ struct State {
   uint64_t table_cap = 0;  // power of two
   DevBuf<uint4> filter;    // fingerprint buckets in front of the table (common.cuh)
   uint32_t filter_buckets = 0;
-  Lookup lookup() const {
-    if (shard_mode) return Lookup{shard_slots.p, shard_cap - 1, filter_buckets ? filter.p : nullptr, filter_buckets};
-    return Lookup{slots.p, table_cap - 1, filter_buckets ? filter.p : nullptr, filter_buckets};
-  }
+  Lookup lookup() const { return Lookup{slots.p, table_cap - 1, filter_buckets ? filter.p : nullptr, filter_buckets}; }
 
   // what humid_gpu_counts reports / what keep_bits covers (the whole job in shard mode)
   uint64_t report_tuples = 0, report_usable = 0;
 
-  // shard mode (include/humid_gpu_shard.h): `slots` stays the table of this rank's own tuples
-  // (key -> local word index), `shard_slots` is the table of the words this shard owns
-  // (key -> shard-local rank); word_key/word_count/word_first switch from the former to the
-  // latter at import_words and to the gathered whole-job columns at import_graph.
+  // shard mode (include/humid_gpu_shard.h): the table is built from the tuples this shard
+  // RECEIVED (keys of its range from every rank, with their global input positions) instead
+  // of the rank's own tuples; word columns then hold the shard's words, and after import_graph
+  // the gathered whole-job columns.
   bool shard_mode = false;
-  uint64_t tuple_base = 0, n_local_words = 0, n_shard_words = 0;
-  DevBuf<Slot> shard_slots;
-  uint64_t shard_cap = 0;
-  DevBuf<uint32_t> local_word_grank;
+  uint64_t tuple_base = 0, n_shard_words = 0;
+  DevBuf<uint64_t> shard_keys;
+  DevBuf<uint32_t> shard_index;
+  const uint64_t *src_keys = nullptr;   // table input override (nullptr: tuple_key / implicit index)
+  const uint32_t *src_index = nullptr;
+  uint64_t src_n = 0;
   uint32_t part = 0, n_parts = 1;
   uint64_t splitters[16] = {0};
   uint64_t bases[17] = {0};
@@ -164,6 +163,7 @@ int stage_neighbours_hamming(State &s);
 int stage_neighbours_edit(State &s);
 int stage_csr(State &s);               // sort directed entries, row_ptr / col (edit and shard modes)
 int stage_csr_pairs(State &s);         // Hamming mode: undirected pairs + degrees -> row_ptr / col
+int stage_csr_directed(State &s);      // shard mode: directed entries + degrees -> row_ptr / col
 int stage_cluster(State &s);           // components, replay, ids, sizes, maxLeaf
 int stage_keep(State &s);              // keep bitmap
 int stage_cluster_ids(State &s, uint64_t first, uint64_t n, uint32_t *d_out);

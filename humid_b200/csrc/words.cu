@@ -243,8 +243,18 @@ int stage_build_filter(State &s) {
 
 int stage_build_table(State &s, bool with_filter) {
   int k = 0;
-  HUMID_CUDA(cudaMemcpyAsync(&s.usable, s.counters.p + 0, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
-  HUMID_CUDA(cudaStreamSynchronize(s.stream));
+  const uint64_t *keys = s.tuple_key.p;
+  const uint32_t *index = nullptr;
+  uint64_t n_in = s.n_tuples;
+  if (s.src_keys) {  // shard mode: tuples received from all ranks, every one usable
+    keys = s.src_keys;
+    index = s.src_index;
+    n_in = s.src_n;
+    s.usable = n_in;
+  } else {
+    HUMID_CUDA(cudaMemcpyAsync(&s.usable, s.counters.p + 0, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+  }
   uint64_t cap = 1024;
   while (4 * cap < 5 * s.usable) cap <<= 1;  // load factor <= 0.8 if every tuple were distinct, ~0.3 typically
   if (cap > (1ull << 32)) throw CudaError{"word table would exceed 2^32 slots"};
@@ -255,11 +265,10 @@ int stage_build_table(State &s, bool with_filter) {
     table_clear_kernel<<<grid_for(cap, 256), 256, 0, s.stream>>>(s.slots.p, cap);
   }
   k++;
-  if (s.n_tuples) {
+  if (n_in) {
     // key in (8) + slot key (8) + count RMW (8) + first RMW (8)
-    Timed t(s, "table_insert", s.n_tuples, s.n_tuples * 8 + s.usable * 24);
-    table_insert_kernel<<<grid_for(s.n_tuples, 256), 256, 0, s.stream>>>(s.tuple_key.p, nullptr, s.n_tuples, s.slots.p,
-                                                                        cap - 1);
+    Timed t(s, "table_insert", n_in, n_in * 8 + s.usable * 24);
+    table_insert_kernel<<<grid_for(n_in, 256), 256, 0, s.stream>>>(keys, index, n_in, s.slots.p, cap - 1);
     k++;
   }
   // distinct words cannot outnumber usable tuples

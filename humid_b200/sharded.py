@@ -32,13 +32,12 @@ def _bind(L):
         return L
     vp, u64, u32 = C.c_void_p, C.c_uint64, C.c_uint32
     P = C.POINTER
-    L.humid_gpu_shard_local_words.argtypes = [vp, u64, P(u64), P(u64)]
-    L.humid_gpu_shard_sample_keys.argtypes = [vp, u32, vp]
-    L.humid_gpu_shard_split.argtypes = [vp, vp, u32, vp]
-    L.humid_gpu_shard_export_words.argtypes = [vp, vp, vp, vp]
-    L.humid_gpu_shard_import_words.argtypes = [vp, vp, vp, vp, u64, vp, P(u64)]
+    L.humid_gpu_shard_begin.argtypes = [vp, u64, P(u64)]
+    L.humid_gpu_shard_sample_keys.argtypes = [vp, u32, vp, P(u32)]
+    L.humid_gpu_shard_partition.argtypes = [vp, vp, u32, vp]
+    L.humid_gpu_shard_export_tuples.argtypes = [vp, vp, vp, vp]
+    L.humid_gpu_shard_import_tuples.argtypes = [vp, vp, vp, u64, P(u64)]
     L.humid_gpu_shard_set_layout.argtypes = [vp, u32, u32, vp, vp]
-    L.humid_gpu_shard_set_word_ranks.argtypes = [vp, vp, u64]
     L.humid_gpu_shard_probe_count.argtypes = [vp, vp]
     L.humid_gpu_shard_probe.argtypes = [vp, vp, vp, vp]
     L.humid_gpu_shard_answer.argtypes = [vp, vp, vp, u64, vp]
@@ -46,17 +45,17 @@ def _bind(L):
     L.humid_gpu_shard_build_rows.argtypes = [vp, P(u64)]
     L.humid_gpu_shard_export_graph.argtypes = [vp, vp, vp, vp, vp, vp]
     L.humid_gpu_shard_import_graph.argtypes = [vp, u64, u64, u64, u64, vp, vp, vp, vp, vp]
-    L.humid_gpu_shard_cluster_ids.argtypes = [vp, u64, u64, vp]
+    L.humid_gpu_shard_tuple_ids.argtypes = [vp, vp]
     L._shard_bound = True
     return L
 
 
 SHARD_EXPORTS = [
-    "humid_gpu_shard_local_words", "humid_gpu_shard_sample_keys", "humid_gpu_shard_split",
-    "humid_gpu_shard_export_words", "humid_gpu_shard_import_words", "humid_gpu_shard_set_layout",
-    "humid_gpu_shard_set_word_ranks", "humid_gpu_shard_probe_count", "humid_gpu_shard_probe",
-    "humid_gpu_shard_answer", "humid_gpu_shard_apply_answers", "humid_gpu_shard_build_rows",
-    "humid_gpu_shard_export_graph", "humid_gpu_shard_import_graph", "humid_gpu_shard_cluster_ids",
+    "humid_gpu_shard_begin", "humid_gpu_shard_sample_keys", "humid_gpu_shard_partition",
+    "humid_gpu_shard_export_tuples", "humid_gpu_shard_import_tuples", "humid_gpu_shard_set_layout",
+    "humid_gpu_shard_probe_count", "humid_gpu_shard_probe", "humid_gpu_shard_answer",
+    "humid_gpu_shard_apply_answers", "humid_gpu_shard_build_rows", "humid_gpu_shard_export_graph",
+    "humid_gpu_shard_import_graph", "humid_gpu_shard_tuple_ids",
 ]
 
 
@@ -81,49 +80,47 @@ class CudaShardEngine(api.Dedup):
         torch.cuda.current_stream(self.device).synchronize()
 
     # torch has no unsigned 64/32-bit arithmetic: keys travel as int64, ranks/counts as int32
-    def local_words(self, tuple_offset: int) -> Tuple[int, int]:
-        n, u = C.c_uint64(0), C.c_uint64(0)
-        self._check(self._L.humid_gpu_shard_local_words(self._h, tuple_offset, C.byref(n), C.byref(u)), "shard_local_words")
-        self.n_local_words = int(n.value)
-        return int(n.value), int(u.value)
+    def begin(self, tuple_offset: int) -> int:
+        u = C.c_uint64(0)
+        self._check(self._L.humid_gpu_shard_begin(self._h, tuple_offset, C.byref(u)), "shard_begin")
+        return int(u.value)
 
     def sample_keys(self, n: int) -> np.ndarray:
         out = np.zeros(n, dtype=np.uint64)
-        self._check(self._L.humid_gpu_shard_sample_keys(self._h, n, out.ctypes.data_as(C.c_void_p)), "shard_sample_keys")
-        return out
+        got = C.c_uint32(0)
+        self._check(self._L.humid_gpu_shard_sample_keys(self._h, n, out.ctypes.data_as(C.c_void_p), C.byref(got)),
+                    "shard_sample_keys")
+        return out[: got.value]
 
-    def split(self, splitters: np.ndarray, n_parts: int) -> np.ndarray:
+    def partition(self, splitters: np.ndarray, n_parts: int) -> np.ndarray:
         sp = np.ascontiguousarray(splitters, dtype=np.uint64)
         out = np.zeros(n_parts, dtype=np.uint64)
-        self._check(self._L.humid_gpu_shard_split(self._h, sp.ctypes.data_as(C.c_void_p), n_parts,
-                                                  out.ctypes.data_as(C.c_void_p)), "shard_split")
+        self._check(self._L.humid_gpu_shard_partition(self._h, sp.ctypes.data_as(C.c_void_p), n_parts,
+                                                      out.ctypes.data_as(C.c_void_p)), "shard_partition")
         return out.astype(np.int64)
 
-    def export_words(self):
-        n = self.n_local_words
-        k, c, f = self._empty(n, torch.int64), self._empty(n, torch.int32), self._empty(n, torch.int32)
-        self._check(self._L.humid_gpu_shard_export_words(self._h, _dp(k), _dp(c), _dp(f)), "shard_export_words")
-        return k, c, f
+    def export_tuples(self, counts: np.ndarray):
+        off = np.zeros(len(counts) + 1, dtype=np.uint64)
+        off[1:] = np.cumsum(counts)
+        n = int(off[-1])
+        k, ix = self._empty(n, torch.int64), self._empty(n, torch.int32)
+        self._check(self._L.humid_gpu_shard_export_tuples(self._h, off.ctypes.data_as(C.c_void_p), _dp(k), _dp(ix)),
+                    "shard_export_tuples")
+        return k, ix
 
-    def import_words(self, keys, counts, first):
+    def import_tuples(self, keys, index) -> int:
         self._sync()
-        n = keys.numel()
-        lr = self._empty(n, torch.int32)
         u = C.c_uint64(0)
-        self._check(self._L.humid_gpu_shard_import_words(self._h, _dp(keys), _dp(counts), _dp(first), n, _dp(lr),
-                                                         C.byref(u)), "shard_import_words")
-        self.n_shard_words = int(u.value)
-        return lr, int(u.value)
+        self._check(self._L.humid_gpu_shard_import_tuples(self._h, _dp(keys), _dp(index), keys.numel(), C.byref(u)),
+                    "shard_import_tuples")
+        self.n_shard_words, self.n_shard_tuples = int(u.value), keys.numel()
+        return int(u.value)
 
     def set_layout(self, part: int, n_parts: int, splitters: np.ndarray, bases: np.ndarray):
         sp = np.ascontiguousarray(splitters, dtype=np.uint64)
         b = np.ascontiguousarray(bases, dtype=np.uint64)
         self._check(self._L.humid_gpu_shard_set_layout(self._h, part, n_parts, sp.ctypes.data_as(C.c_void_p),
                                                        b.ctypes.data_as(C.c_void_p)), "shard_set_layout")
-
-    def set_word_ranks(self, granks):
-        self._sync()
-        self._check(self._L.humid_gpu_shard_set_word_ranks(self._h, _dp(granks), granks.numel()), "shard_set_word_ranks")
 
     def probe_count(self, n_parts: int) -> np.ndarray:
         out = np.zeros(MAX_PARTS, dtype=np.uint64)
@@ -171,11 +168,11 @@ class CudaShardEngine(api.Dedup):
                     "shard_import_graph")
         self.n_tuples_total = n_tuples
 
-    def local_cluster_ids(self, first: int, n: int) -> np.ndarray:
-        ids = np.zeros(max(n, 1), dtype=np.uint32)
-        self._check(self._L.humid_gpu_shard_cluster_ids(self._h, first, n, ids.ctypes.data_as(C.c_void_p)),
-                    "shard_cluster_ids")
-        return ids[:n]
+    def tuple_ids(self):
+        """int32 tensor: cluster id of every tuple handed to import_tuples, in that order."""
+        ids = self._empty(self.n_shard_tuples, torch.int32)
+        self._check(self._L.humid_gpu_shard_tuple_ids(self._h, _dp(ids)), "shard_tuple_ids")
+        return ids
 
     def global_keep_bits(self, first: int, n: int) -> np.ndarray:
         """bool[n] for GLOBAL tuple indices first..first+n."""
@@ -312,14 +309,14 @@ class ShardedDedup:
         n_tuples = self._gather_ints(self.n_local)[:, 0]
         offs = np.concatenate([[0], np.cumsum(n_tuples)])
         self.tuple_offset, self.n_total = int(offs[me]), int(offs[-1])
-        n_words, usable = eng.local_words(self.tuple_offset)
+        usable = eng.begin(self.tuple_offset)
 
-        # splitters: evenly spaced samples of every rank's sorted words, weighted equally
-        samp = eng.sample_keys(SAMPLES_PER_RANK) if n_words else np.zeros(0, dtype=np.uint64)
+        # splitters: an equal number of evenly spaced tuple keys from every rank
+        samp = eng.sample_keys(SAMPLES_PER_RANK)
         st = torch.zeros(SAMPLES_PER_RANK + 1, dtype=torch.int64, device=dev)
         st[0] = len(samp)
         if len(samp):
-            st[1:] = torch.from_numpy(samp.view(np.int64)).to(dev)
+            st[1: 1 + len(samp)] = torch.from_numpy(samp.view(np.int64).copy()).to(dev)
         allst = torch.empty(W * (SAMPLES_PER_RANK + 1), dtype=torch.int64, device=dev)
         g.all_gather_into_tensor(allst, st)
         allst = allst.cpu().numpy().reshape(W, SAMPLES_PER_RANK + 1)
@@ -330,20 +327,18 @@ class ShardedDedup:
             splitters = np.zeros(max(W - 1, 0), dtype=np.uint64)
         self.splitters = splitters
 
-        # words to their owners
-        send = eng.split(splitters, W)
-        k, c, f = eng.export_words()
+        # tuples to the owners of their key range; each owner then runs the single-GPU word stages
+        send = eng.partition(splitters, W)
+        k, ix = eng.export_tuples(send)
         rk, recv = all_to_all_v(g, k, send)
-        rc_ = all_to_all_fixed(g, c, send, recv)
-        rf = all_to_all_fixed(g, f, send, recv)
-        local_rank, n_shard = eng.import_words(rk, rc_, rf)
+        rix = all_to_all_fixed(g, ix, send, recv)
+        self._sent_index, self._send_counts, self._recv_counts = ix, send, recv
+        n_shard = eng.import_tuples(rk, rix)
+        del k, rk, rix
         info = self._gather_ints(n_shard, usable)
         bases = np.concatenate([[0], np.cumsum(info[:, 0])]).astype(np.uint64)
         self.n_words_total, self.usable_total = int(bases[-1]), int(info[:, 1].sum())
         eng.set_layout(me, W, splitters, bases)
-        # owners tell the senders the global rank of every word they sent
-        grank = all_to_all_fixed(g, local_rank + int(bases[me]), recv, send)
-        eng.set_word_ranks(grank)
 
         # neighbour search: local look-ups + routed queries
         qcounts = eng.probe_count(W)
@@ -381,8 +376,15 @@ class ShardedDedup:
         return np.packbits(self.keep_mask(), bitorder="little")
 
     def cluster_ids(self) -> np.ndarray:
-        """uint32[n_local]: cluster ids of this rank's tuples."""
-        return self.eng.local_cluster_ids(0, self.n_local)
+        """uint32[n_local]: cluster ids of this rank's tuples (collective: the owners of the
+        key ranges look the ids up and send them back along the route the tuples took)."""
+        ids = self.eng.tuple_ids()
+        if hasattr(self.eng, "_sync"):
+            self.eng._sync()
+        back = all_to_all_fixed(self.comm, ids, self._recv_counts, self._send_counts)
+        out = torch.zeros(self.n_local, dtype=torch.int32, device=back.device)
+        out[(self._sent_index.long() & 0xFFFFFFFF) - self.tuple_offset] = back
+        return out.cpu().numpy().view(np.uint32)
 
     def words(self):
         return self.eng.words()

@@ -6,9 +6,9 @@
  * torch.distributed / NCCL) can do the exchanges in between:
  *
  *   add_batch*            each rank packs its own slice of the read tuples          (makeWord)
- *   local_words           per-rank distinct words with counts / first tuple         (Trie::add)
- *   sample / split        splitters for a range partition of the word space
- *   export_words  ==all-to-all-v==>  import_words     owner merges counts, min(first)
+ *   begin / sample_keys   splitters for a range partition of the word space
+ *   partition / export_tuples  ==all-to-all-v==>  import_tuples
+ *                         the owner of a key range counts its words                 (Trie::add)
  *   set_layout            global rank = bases[part] + local rank                    (Trie::walk order)
  *   probe_count / probe   variants owned by this shard are looked up in place, the
  *                         others become queries  ==all-to-all-v==>  answer  ==back==>  apply_answers
@@ -30,26 +30,25 @@ extern "C" {
 
 #define HUMID_MAX_PARTS 16
 
-/* Distinct words of the tuples added so far, in key order.  tuple_offset = global index of
- * this rank's first tuple (the `first` column is global). */
-int humid_gpu_shard_local_words(humid_gpu *h, uint64_t tuple_offset, uint64_t *n_local_words,
-                                uint64_t *n_usable);
-/* n_samples evenly spaced keys of the local words (n_local_words > 0). */
-int humid_gpu_shard_sample_keys(humid_gpu *h, uint32_t n_samples, uint64_t *keys_out);
-/* counts[p] = local words with splitters[p-1] <= key < splitters[p] (n_parts-1 splitters). */
-int humid_gpu_shard_split(humid_gpu *h, const uint64_t *splitters, uint32_t n_parts, uint64_t *counts);
-int humid_gpu_shard_export_words(humid_gpu *h, uint64_t *d_keys, uint32_t *d_counts, uint32_t *d_first);
-/* Merge n received records into this shard's words; d_local_rank[i] = the shard-local rank
- * of record i (returned to its sender so that tuples can be resolved later). */
-int humid_gpu_shard_import_words(humid_gpu *h, const uint64_t *d_keys, const uint32_t *d_counts,
-                                 const uint32_t *d_first, uint64_t n, uint32_t *d_local_rank,
-                                 uint64_t *n_shard_words);
+/* Enter shard mode after the add_batch* calls.  tuple_offset = global input position of this
+ * rank's first tuple (rank order == input order). */
+int humid_gpu_shard_begin(humid_gpu *h, uint64_t tuple_offset, uint64_t *n_usable);
+/* Up to n_samples evenly spaced usable tuple keys (splitter candidates); *n_out of them. */
+int humid_gpu_shard_sample_keys(humid_gpu *h, uint32_t n_samples, uint64_t *keys_out, uint32_t *n_out);
+/* counts[p] = usable local tuples whose key lies in [splitters[p-1], splitters[p])
+ * (n_parts-1 ascending splitters).  The splitters are remembered for export_tuples. */
+int humid_gpu_shard_partition(humid_gpu *h, const uint64_t *splitters, uint32_t n_parts, uint64_t *counts);
+/* {key, global tuple index} of every usable local tuple, grouped by part; offsets (n_parts+1)
+ * = exclusive prefix of the counts; order inside a part is unspecified. */
+int humid_gpu_shard_export_tuples(humid_gpu *h, const uint64_t *offsets, uint64_t *d_keys, uint32_t *d_index);
+/* The tuples of this shard's key range received from all ranks: distinct words with counts
+ * and first (global) tuple, rank order, look-up table and filter — the single-GPU stages
+ * restricted to the range. */
+int humid_gpu_shard_import_tuples(humid_gpu *h, const uint64_t *d_keys, const uint32_t *d_index, uint64_t n,
+                                  uint64_t *n_shard_words);
 /* bases has n_parts+1 entries (exclusive prefix sums of the shard sizes). */
 int humid_gpu_shard_set_layout(humid_gpu *h, uint32_t part, uint32_t n_parts, const uint64_t *splitters,
                                const uint64_t *bases);
-/* d_global_rank[i] = global rank of exported local word i (from the owners' replies). */
-int humid_gpu_shard_set_word_ranks(humid_gpu *h, const uint32_t *d_global_rank, uint64_t n_local_words);
-
 /* Number of variant queries this shard will send to every part (counts[part] = 0). */
 int humid_gpu_shard_probe_count(humid_gpu *h, uint64_t *counts);
 /* Local look-ups + fill of the query buffers; offsets (n_parts+1) = exclusive prefix of counts. */
@@ -67,8 +66,10 @@ int humid_gpu_shard_export_graph(humid_gpu *h, uint64_t *d_keys, uint32_t *d_cou
 int humid_gpu_shard_import_graph(humid_gpu *h, uint64_t n_words, uint64_t n_entries, uint64_t n_tuples,
                                  uint64_t n_usable, const uint64_t *d_keys, const uint32_t *d_counts,
                                  const uint32_t *d_first, const uint32_t *d_degree, const uint32_t *d_col);
-/* Cluster ids of this rank's own tuples (local tuple indices), 0 for filtered tuples. */
-int humid_gpu_shard_cluster_ids(humid_gpu *h, uint64_t first_local_tuple, uint64_t n, uint32_t *ids);
+/* After import_graph: d_ids[i] = cluster id of the i-th tuple handed to import_tuples (the
+ * host routes them back to the ranks the tuples came from; filtered tuples never travelled
+ * and keep id 0). */
+int humid_gpu_shard_tuple_ids(humid_gpu *h, uint32_t *d_ids);
 
 #ifdef __cplusplus
 }

@@ -49,47 +49,44 @@ class CpuShardEngine:
         self._keys.append(oracle.pack_words(chars, self.seg_take, seg_len))
         self.n_tuples += chars.shape[0]
 
-    # ---- words ------------------------------------------------------------------------------
-    def local_words(self, tuple_offset):
+    # ---- tuples to their owners ---------------------------------------------------------------
+    def begin(self, tuple_offset):
         self.tuple_keys = np.concatenate(self._keys) if self._keys else np.zeros(0, np.uint64)
-        ok = self.tuple_keys != oracle.INVALID
-        idx = np.nonzero(ok)[0]
-        k, first, cnt = np.unique(self.tuple_keys[idx], return_index=True, return_counts=True)
-        self.lw_keys, self.lw_counts = k, cnt.astype(np.uint32)
-        self.lw_first = (idx[first] + tuple_offset).astype(np.uint32)
-        self.n_local_words = k.size
-        return k.size, int(ok.sum())
+        self.tuple_offset = tuple_offset
+        return int((self.tuple_keys != oracle.INVALID).sum())
 
     def sample_keys(self, n):
-        U = self.n_local_words
-        return self.lw_keys[[((i * U + U // 2) // n) % U for i in range(n)]]
+        R = self.tuple_keys.size
+        if R == 0:
+            return np.zeros(0, np.uint64)
+        k = self.tuple_keys[[((i * R + R // 2) // n) % R for i in range(n)]]
+        return k[k != oracle.INVALID]
 
-    def split(self, splitters, n_parts):
-        b = np.concatenate([[0], np.searchsorted(self.lw_keys, np.asarray(splitters, np.uint64), "left"),
-                            [self.n_local_words]])
-        return np.diff(b).astype(np.int64)
+    def partition(self, splitters, n_parts):
+        ok = self.tuple_keys != oracle.INVALID
+        self._own = np.searchsorted(np.asarray(splitters, np.uint64), self.tuple_keys, "right")
+        self._own[~ok] = n_parts  # dropped
+        return np.bincount(self._own, minlength=n_parts + 1)[:n_parts].astype(np.int64)
 
-    def export_words(self):
-        return _t64(self.lw_keys), _t32(self.lw_counts), _t32(self.lw_first)
+    def export_tuples(self, counts):
+        order = np.argsort(self._own, kind="stable")[: int(np.sum(counts))]
+        order = order[::-1].copy() if False else order  # any order inside a part is allowed
+        return _t64(self.tuple_keys[order]), _t32((order + self.tuple_offset).astype(np.uint32))
 
-    def import_words(self, keys, counts, first):
-        k, c, f = _u64(keys), _u32(counts), _u32(first)
-        uk, inv = np.unique(k, return_inverse=True)
-        cnt = np.zeros(uk.size, np.uint64)
-        np.add.at(cnt, inv, c)
+    def import_tuples(self, keys, index):
+        k, ix = _u64(keys), _u32(index)
+        self.rk = k.copy()
+        uk, inv, cnt = np.unique(k, return_inverse=True, return_counts=True)
         fst = np.full(uk.size, 0xFFFFFFFF, np.uint32)
-        np.minimum.at(fst, inv, f)
+        np.minimum.at(fst, inv, ix)
         self.sk, self.sc, self.sf = uk, cnt.astype(np.uint32), fst
         self.n_shard_words = uk.size
-        return _t32(inv.astype(np.uint32)), uk.size
+        return uk.size
 
     def set_layout(self, part, n_parts, splitters, bases):
         self.part, self.n_parts = part, n_parts
         self.splitters = np.asarray(splitters, np.uint64)
         self.base = int(bases[part])
-
-    def set_word_ranks(self, granks):
-        self.lw_grank = _u32(granks).copy()
 
     # ---- neighbours ----------------------------------------------------------------------------
     def _variants(self):
@@ -192,13 +189,9 @@ class CpuShardEngine:
     def global_keep_bits(self, first, n):
         return self.keep[first:first + n]
 
-    def local_cluster_ids(self, first, n):
-        k = self.tuple_keys[first:first + n]
-        out = np.zeros(n, np.uint32)
-        ok = k != oracle.INVALID
-        lw = np.searchsorted(self.lw_keys, k[ok])
-        out[ok] = self.g_cluster[self.lw_grank[lw]]
-        return out
+    def tuple_ids(self):
+        lr = np.searchsorted(self.sk, self.rk)
+        return _t32(self.g_cluster[self.base + lr])
 
     def words(self):
         return self.g_keys, self.g_count, self.g_first, self.g_cluster

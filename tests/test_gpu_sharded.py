@@ -40,6 +40,7 @@ def run_sharded(W, chars, seg_take, cfg):
             dd.add_batch(part[:half])
             dd.add_batch(part[half:])
             dd.finalize()
+            dd.ids = dd.cluster_ids()  # collective
             out[r] = dd
         except BaseException as e:  # noqa: BLE001
             err.append(e)
@@ -79,7 +80,7 @@ def test_logical_shards_match_oracle(W, ci, R, kw):
         size, mx = dd.clusters()
         assert np.array_equal(size, ref.cluster_size) and np.array_equal(mx, ref.cluster_max)
         assert np.array_equal(dd.keep_mask(), ref.keep[lo:hi].astype(bool))
-        assert np.array_equal(dd.cluster_ids(), ref.cid[lo:hi])
+        assert np.array_equal(dd.ids, ref.cid[lo:hi])
         assert dd.stats_text() == ref.stats_text()
     if W > 1 and R > 100:
         assert sum(dd.queries_sent for dd in dds) > 0
