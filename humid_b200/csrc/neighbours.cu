@@ -32,19 +32,40 @@ __device__ __forceinline__ void emit_pair(uint64_t *pairs, uint64_t cap, unsigne
 // The filter hash is linear, so a variant costs one 64-bit add.  A thread keeps its hits in
 // registers; the warp appends all of them with one global atomic.
 constexpr int H1_LOCAL_HITS = 6;
+constexpr uint32_t H1_SCAN_CAP = 32;
 __global__ void __launch_bounds__(128)
-    hamming1_probe_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, const Lookup lk,
-                          uint64_t *__restrict__ pairs, uint64_t cap, unsigned long long *__restrict__ counter,
-                          uint32_t *__restrict__ deg) {
+    hamming1_probe_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, uint32_t scan_from,
+                          const Lookup lk, uint64_t *__restrict__ pairs, uint64_t cap,
+                          unsigned long long *__restrict__ counter, uint32_t *__restrict__ deg) {
   const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = r < U;
-  const uint64_t w = live ? ld_stream_u64(word_key + r) : 0ull;
+  const uint64_t w = live ? word_key[r] : 0ull;
   const uint64_t hw = filter_hash(w);
   const uint64_t pol_keep = l2_policy_evict_last();
   uint32_t hits[H1_LOCAL_HITS];
   uint32_t nh = 0;
   const uint32_t lane = lane_id();
-  for (uint32_t p = 0; p < n; p++) {
+  // Variants at positions >= scan_from share the word's first scan_from letters, so in rank
+  // order they sit right behind it: walk forward while the prefix matches (rank == index, no
+  // look-up at all).  Only if that run is unusually long are those positions probed instead.
+  uint32_t probe_end = n;
+  if (live && scan_from < n) {
+    const uint32_t low = 2 * (n - scan_from);
+    const uint64_t prefix = w >> low;
+    probe_end = scan_from;
+    for (uint64_t j = r + 1; j < U; j++) {
+      const uint64_t k = word_key[j];
+      if ((k >> low) != prefix) break;
+      if (j - r > H1_SCAN_CAP) { probe_end = n; break; }
+      const uint64_t x = k ^ w;
+      if (__popcll((x | (x >> 1)) & 0x5555555555555555ull) == 1) {  // one letter differs (and k > w)
+        if (nh == H1_LOCAL_HITS) { probe_end = n; break; }  // nothing emitted yet: safe to start over
+        hits[nh++] = (uint32_t)j;
+      }
+    }
+    if (probe_end == n) nh = 0;  // run too long: everything is found by probing below instead
+  }
+  for (uint32_t p = 0; p < probe_end; p++) {
     const uint32_t sh = 2 * (n - 1 - p);
     const uint32_t wl = (uint32_t)(w >> sh) & 3u;
     const uint64_t step = FILTER_MUL << sh;  // hash of "+1 at position p"
@@ -185,8 +206,8 @@ int stage_neighbours_hamming(State &s) {
       Timed t(s, d == 1 ? "probe_hamming1" : d == 2 ? "probe_hamming2" : "probe_hammingd", U,
               (uint64_t)(U * 8.0 * (1.0 + probes)));
       if (d == 1 && lk.filter)
-        hamming1_probe_kernel<<<grid_for(U, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, lk, s.entries.p, cap,
-                                                                      s.counters.p + 2, s.deg.p);
+        hamming1_probe_kernel<<<grid_for(U, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, scan_from_position(U, n), lk,
+                                                                      s.entries.p, cap, s.counters.p + 2, s.deg.p);
       else if (d == 2)
         hamming2_probe_kernel<<<grid_for(threads, 256), 256, 0, s.stream>>>(s.word_key.p, U, n, lk, s.entries.p, cap,
                                                                             s.counters.p + 2, s.deg.p);

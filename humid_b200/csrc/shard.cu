@@ -184,7 +184,8 @@ __global__ void __launch_bounds__(256)
 // part, then the enumeration is repeated to write them.
 template <int MODE>
 __global__ void __launch_bounds__(128)
-    shard_probe1_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, const Layout L, const Lookup lk,
+    shard_probe1_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, uint32_t scan_from,
+                        const Layout L, const Lookup lk,
                         unsigned long long *__restrict__ part_counts, uint64_t *__restrict__ q_keys,
                         uint32_t *__restrict__ q_src, uint64_t *__restrict__ entries, uint64_t cap,
                         unsigned long long *__restrict__ entry_counter, uint32_t *__restrict__ deg) {
@@ -219,8 +220,24 @@ __global__ void __launch_bounds__(128)
   const uint64_t hw = filter_hash(w);
   const uint64_t pol_keep = l2_policy_evict_last();
   constexpr int LOCAL_HITS = 6;
+  constexpr uint32_t SCAN_CAP = 32;
   uint32_t hits[LOCAL_HITS];
   uint32_t nh = 0;
+  // positions >= scan_from: the shard's own words right behind w in rank order (see
+  // hamming1_probe_kernel); variants beyond the shard's range still travel as queries
+  uint32_t probe_end = n;
+  if (live && scan_from < n) {
+    const uint32_t low = 2 * (n - scan_from);
+    const uint64_t prefix = w >> low;
+    probe_end = scan_from;
+    for (uint64_t j = r + 1; j < U; j++) {
+      const uint64_t k = word_key[j];
+      if ((k >> low) != prefix) break;
+      if (j - r > SCAN_CAP || nh == LOCAL_HITS) { probe_end = n; nh = 0; break; }
+      const uint64_t x = k ^ w;
+      if (__popcll((x | (x >> 1)) & 0x5555555555555555ull) == 1) hits[nh++] = (uint32_t)j;
+    }
+  }
   for (uint32_t p = 0; p < n; p++) {
     const uint32_t sh = 2 * (n - 1 - p);
     const uint32_t wl = (uint32_t)(w >> sh) & 3u;
@@ -233,9 +250,10 @@ __global__ void __launch_bounds__(128)
       hf[c - 1] = hw + step * c;
       const uint64_t v = w + ((uint64_t)c << sh);
       const bool valid = live && wl + c <= 3u;
-      local[c - 1] = valid && v < L.hi;
+      local[c - 1] = valid && v < L.hi && p < probe_end;
+      const bool remote = valid && v >= L.hi;
       if (local[c - 1]) bkt[c - 1] = ld_hint_u128(lk.filter + filter_bucket(hf[c - 1], lk.n_buckets), pol_keep);
-      if (valid && !local[c - 1]) {
+      if (remote) {
         const uint32_t o = owner_of(L, v);
         const unsigned long long pos = base[o] + atomicAdd(&cnt[o], 1u);
         q_keys[pos] = v;
@@ -500,7 +518,8 @@ int humid_gpu_shard_probe_count(humid_gpu *h, uint64_t *counts) {
     if (U && d) {
       Timed t(s, "shard_probe_count", U, U * 8);
       if (d == 1 && s.filter_buckets)
-        shard_probe1_kernel<0><<<grid_for(U, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, layout_of(s), s.lookup(), pc,
+        shard_probe1_kernel<0><<<grid_for(U, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, scan_from_position(U, n),
+                                                                       layout_of(s), s.lookup(), pc,
                                                                        nullptr, nullptr, nullptr, 0, nullptr, nullptr);
       else
         shard_probe_kernel<0><<<grid_for(U * n, 256), 256, 0, s.stream>>>(s.word_key.p, U, n, d, layout_of(s),
@@ -541,7 +560,8 @@ int humid_gpu_shard_probe(humid_gpu *h, uint64_t *d_query_keys, uint32_t *d_quer
         double probes = d == 1 ? 1.5 * n : d == 2 ? 1.5 * n + 2.25 * n * (n - 1) / 2.0 : 0.0;
         Timed t(s, "shard_probe", U, (uint64_t)(U * 8.0 * (1.0 + probes)));
         if (d == 1 && s.filter_buckets)
-          shard_probe1_kernel<1><<<grid_for(U, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, layout_of(s), s.lookup(), pc,
+          shard_probe1_kernel<1><<<grid_for(U, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, scan_from_position(U, n),
+                                                                         layout_of(s), s.lookup(), pc,
                                                                          d_query_keys, d_query_src, s.entries.p, cap,
                                                                          s.counters.p + 2, s.deg.p);
         else

@@ -145,6 +145,14 @@ struct State {
   }
 };
 
+// First position handled by the forward scan of the Hamming-1 probe kernels: the prefix of that
+// many letters should be long enough that few words share it (4^p >= U).
+inline uint32_t scan_from_position(uint64_t U, uint32_t n) {
+  uint32_t p = 1;
+  while (p < n && (1ull << (2 * p)) < U) p++;
+  return p;
+}
+
 // RAII form: `{ Timed t(s, "probe", U, bytes); kernel<<<...>>>(); t.launches = 1; }`
 struct Timed {
   State &s;

@@ -230,7 +230,7 @@ int stage_build_filter(State &s) {
   const uint64_t U = s.unique;
   s.filter_buckets = 0;
   if (U == 0) return 0;
-  uint64_t nb = std::max<uint64_t>(1024, U / 5 + 1);
+  uint64_t nb = std::max<uint64_t>(1024, U / 7 + 1);  // ~7 words per 15-slot bucket: 43 MB at 21 M words
   if (nb > 0xFFFFFFF0ull) return 0;
   s.filter.ensure(nb);
   Timed t(s, "filter_build", U, U * 9 + nb * 16);
