@@ -37,13 +37,17 @@ __device__ __forceinline__ uint32_t uf_find(uint32_t *parent, uint32_t x) {
 
 __global__ void __launch_bounds__(256)
     uf_union_kernel(const uint64_t *__restrict__ row_ptr, const uint32_t *__restrict__ col, uint64_t E, uint64_t U,
-                    uint32_t *parent) {
+                    uint32_t base, uint32_t *__restrict__ open_flag, uint32_t *parent) {
   // one thread per directed entry; the source rank is recovered lazily only for a < b
   // entries via binary search would be wasteful, so sources come from a per-row loop instead
   uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= U) return;
   for (uint64_t e = row_ptr[r]; e < row_ptr[r + 1]; e++) {
-    uint32_t b = col[e];
+    uint32_t b = col[e] - base;
+    if (b >= U) {  // shard mode: the neighbour lives on another shard
+      if (open_flag) open_flag[r] = 1u;
+      continue;
+    }
     if (b <= r) continue;  // every undirected pair is present in both rows; take it once
     uint32_t x = (uint32_t)r, y = b;
     while (true) {
@@ -60,11 +64,13 @@ __global__ void __launch_bounds__(256)
 constexpr uint32_t SMALL_COMP = 32;
 
 // comp[r] = root; csize[root] = number of members (singletons are not counted: csize stays 0)
-__global__ void uf_flatten_kernel(uint32_t *parent, uint32_t *comp, uint32_t *csize, uint64_t U) {
+__global__ void uf_flatten_kernel(uint32_t *parent, uint32_t *comp, uint32_t *csize, uint64_t U,
+                                  const uint32_t *__restrict__ open_flag, uint32_t *__restrict__ comp_open) {
   uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= U) return;
   uint32_t root = uf_find(parent, (uint32_t)r);
   comp[r] = root;
+  if (open_flag && open_flag[r]) comp_open[root] = 1u;
   if (root != r) {
     atomicAdd(csize + root, 1u);  // members besides the root itself
   }
@@ -98,7 +104,9 @@ struct Graph {
   const uint64_t *row_ptr;
   const uint32_t *col;
   const uint32_t *count;
+  uint32_t base;  // columns are stored as rank + base (shard mode: global ranks), rows are 0-based
 };
+__device__ __forceinline__ uint32_t gcol(const Graph &g, uint64_t e) { return g.col[e] - g.base; }
 
 // Members of the component of `root` (m of them) in rank order, collected by a breadth-first
 // walk of the neighbour lists into `arr` (capacity SMALL_COMP) and sorted there.
@@ -108,7 +116,7 @@ __device__ __forceinline__ void gather_small_component(const Graph &g, uint32_t 
   for (uint32_t i = 0; i < cnt && cnt < m; i++) {
     const uint32_t u = arr[i];
     for (uint64_t e = g.row_ptr[u], hi = g.row_ptr[u + 1]; e < hi && cnt < m; e++) {
-      const uint32_t v = g.col[e];
+      const uint32_t v = gcol(g, e);
       bool seen = false;
       for (uint32_t j = 0; j < cnt; j++) seen |= arr[j] == v;
       if (!seen) arr[cnt++] = v;
@@ -162,7 +170,7 @@ __device__ void replay_maximum(const Graph &g, const uint32_t *mem, uint32_t m, 
         const uint64_t j = lo + stk_edge[sp - 1];
         if (j < hi) {
           stk_edge[sp - 1]++;
-          const uint32_t v = g.col[j];
+          const uint32_t v = gcol(g, j);
           if (!visited[v]) {
             visited[v] = 1;
             if (g.count[v] == best) { best_rank = v; found = true; }
@@ -192,7 +200,7 @@ __device__ void replay_directional(const Graph &g, const uint32_t *mem, uint32_t
     uint64_t j = g.row_ptr[node], hi = g.row_ptr[node + 1];
     uint64_t cn = g.count[node];
     while (j < hi) {
-      const uint32_t nb = g.col[j++];
+      const uint32_t nb = gcol(g, j++);
       if (label[nb] == NONE32 && (uint64_t)g.count[nb] >= 2 * cn) {
         node = nb;
         j = g.row_ptr[node];
@@ -208,7 +216,7 @@ __device__ void replay_directional(const Graph &g, const uint32_t *mem, uint32_t
       const uint32_t u = queue[head++];
       const uint64_t cu = g.count[u];
       for (uint64_t k = g.row_ptr[u], e = g.row_ptr[u + 1]; k < e; k++) {
-        const uint32_t nb = g.col[k];
+        const uint32_t nb = gcol(g, k);
         if (label[nb] == NONE32) {
           const uint64_t cb = g.count[nb];
           if (cu >= 2 * cb) {
@@ -234,10 +242,14 @@ __global__ void __launch_bounds__(128)
                   const uint32_t *__restrict__ big_members, const uint32_t *__restrict__ big_start,
                   uint32_t *__restrict__ big_work_a, uint32_t *__restrict__ big_work_b, uint32_t *visited,
                   uint32_t *label, uint32_t *__restrict__ seed_flag, uint64_t *__restrict__ seed_size,
-                  uint32_t *__restrict__ seed_max) {
+                  uint32_t *__restrict__ seed_max, const uint32_t *__restrict__ skip_root) {
   const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= U) return;
   const uint32_t root = comp[r];
+  if (skip_root && skip_root[root]) {  // shard mode: component continues on another shard, replayed later
+    if (MAXIMUM) seed_flag[r] = 0;
+    return;
+  }
   if (MAXIMUM) {
     label[r] = root;
     seed_flag[r] = root == r ? 1u : 0u;
@@ -290,8 +302,17 @@ int stage_cluster(State &s) {
     Timed t(s, "union_find", s.n_entries, s.n_entries * 16 + U * 12);
     HUMID_CUDA(cudaMemsetAsync(csize, 0, U * sizeof(uint32_t), s.stream));
     iota_kernel<<<g256, 256, 0, s.stream>>>(s.work_a.p, U);  // parent
-    uf_union_kernel<<<g256, 256, 0, s.stream>>>(s.row_ptr.p, s.col.p, s.n_entries, U, s.work_a.p);
-    uf_flatten_kernel<<<g256, 256, 0, s.stream>>>(s.work_a.p, s.comp.p, csize, U);
+    uint32_t *open_flag = nullptr;
+    if (s.cluster_skip_open) {
+      s.open_flag.ensure(U);
+      s.comp_open.ensure(U);
+      HUMID_CUDA(cudaMemsetAsync(s.open_flag.p, 0, U * sizeof(uint32_t), s.stream));
+      HUMID_CUDA(cudaMemsetAsync(s.comp_open.p, 0, U * sizeof(uint32_t), s.stream));
+      open_flag = s.open_flag.p;
+    }
+    uf_union_kernel<<<g256, 256, 0, s.stream>>>(s.row_ptr.p, s.col.p, s.n_entries, U, s.cluster_col_base, open_flag,
+                                                s.work_a.p);
+    uf_flatten_kernel<<<g256, 256, 0, s.stream>>>(s.work_a.p, s.comp.p, csize, U, open_flag, s.comp_open.p);
     t.launches = 3;
   }
   k += 3;
@@ -328,7 +349,8 @@ int stage_cluster(State &s) {
   s.seed_index.ensure(U);
   s.seed_size.ensure(U);
   s.seed_max.ensure(U);
-  Graph g{s.row_ptr.p, s.col.p, s.word_count.p};
+  Graph g{s.row_ptr.p, s.col.p, s.word_count.p, s.cluster_col_base};
+  const uint32_t *skip_root = s.cluster_skip_open ? s.comp_open.p : nullptr;
   size_t t_replay = s.timer_begin(s.cfg.maximum ? "replay_maximum" : "replay_directional", U,
                                   s.n_entries * 8 + U * 24);
   if (s.cfg.maximum) {
@@ -337,16 +359,26 @@ int stage_cluster(State &s) {
     HUMID_CUDA(cudaMemsetAsync(s.work_c.p, 0, U * sizeof(uint32_t), s.stream));
     replay_kernel<true><<<g128, 128, 0, s.stream>>>(g, U, s.comp.p, csize, s.members.p, s.seg_start.p, s.work_b.p,
                                                     s.slot_alt.p, s.work_c.p, s.label.p, s.seed_flag.p, s.seed_size.p,
-                                                    s.seed_max.p);
+                                                    s.seed_max.p, skip_root);
   } else {
     HUMID_CUDA(cudaMemsetAsync(s.label.p, 0xFF, U * sizeof(uint32_t), s.stream));
     HUMID_CUDA(cudaMemsetAsync(s.seed_flag.p, 0, U * sizeof(uint32_t), s.stream));
     replay_kernel<false><<<g128, 128, 0, s.stream>>>(g, U, s.comp.p, csize, s.members.p, s.seg_start.p, s.work_b.p,
                                                      nullptr, nullptr, s.label.p, s.seed_flag.p, s.seed_size.p,
-                                                     s.seed_max.p);
+                                                     s.seed_max.p, skip_root);
   }
   s.timer_end(t_replay, 1);
   k++;
+  HUMID_CUDA(cudaGetLastError());
+  if (s.cluster_skip_open) return k;  // shard mode: ids are handed out after the open components are merged in
+  return k + stage_cluster_number(s);
+}
+
+// ids in walk order of the seeding word (src/humid.cc:180): exclusive scan of the seed flags
+int stage_cluster_number(State &s) {
+  const uint64_t U = s.unique;
+  const unsigned g256 = grid_for(U, 256);
+  int k = 0;
   uint32_t *total = reinterpret_cast<uint32_t *>(s.counters.p + 3);
   size_t t_ids = s.timer_begin("cluster_ids_scan", U, U * 8);
   int scan_launches = exclusive_scan_u32(s.seed_flag.p, s.seed_index.p, U, total, s.scan_scratch, s.stream);

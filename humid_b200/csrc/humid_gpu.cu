@@ -88,6 +88,17 @@ void humid_gpu_destroy(humid_gpu *h) {
   s.seed_size.release(); s.seed_max.release(); s.cluster_size.release(); s.cluster_max.release();
   s.shard_keys.release(); s.shard_index.release(); s.filter.release();
   s.keep_bits.release(); s.out_ids.release(); s.scratch.release(); s.scan_scratch.release();
+  if (s.open) {
+    State &o = *s.open;
+    o.counters.release(); o.word_count.release(); o.row_ptr.release(); o.col.release(); o.comp.release();
+    o.label.release(); o.work_a.release(); o.work_b.release(); o.work_c.release(); o.seg_start.release();
+    o.seg_end.release(); o.members.release(); o.key_alt.release(); o.entries_alt.release(); o.slot_alt.release();
+    o.seed_flag.release(); o.seed_index.release(); o.seed_size.release(); o.seed_max.release();
+    o.cluster_size.release(); o.cluster_max.release(); o.scratch.release(); o.scan_scratch.release();
+    delete s.open;
+  }
+  s.is_open.release(); s.open_pos.release(); s.open_ent.release(); s.open_rank.release(); s.open_first.release();
+  s.seed_first.release(); s.cluster_first.release(); s.word_cid.release(); s.open_flag.release(); s.comp_open.release();
   if (s.stream) cudaStreamDestroy(s.stream);
   delete h;
 }
@@ -102,6 +113,8 @@ int humid_gpu_reset(humid_gpu *h) {
     s.n_tuples = s.usable = s.unique = s.n_entries = s.n_clusters = 0;
     s.finalized = false;
     s.shard_mode = false;
+    s.cluster_skip_open = false;
+    s.cluster_col_base = 0;
     s.report_tuples = s.report_usable = s.tuple_base = s.n_shard_words = s.src_n = 0;
     s.src_keys = nullptr;
     s.src_index = nullptr;
@@ -186,8 +199,8 @@ int humid_gpu_counts(humid_gpu *h, uint64_t *total, uint64_t *usable, uint64_t *
   if (!h->s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "not finalized");
   if (total) *total = h->s.report_tuples;
   if (usable) *usable = h->s.report_usable;
-  if (unique) *unique = h->s.unique;
-  if (clusters) *clusters = h->s.n_clusters;
+  if (unique) *unique = h->s.shard_mode ? h->s.report_unique : h->s.unique;
+  if (clusters) *clusters = h->s.shard_mode ? h->s.report_clusters : h->s.n_clusters;
   return HUMID_GPU_OK;
 }
 
@@ -217,6 +230,7 @@ int humid_gpu_keep_mask(humid_gpu *h, uint64_t first_tuple, uint64_t n, uint64_t
   if (!h || (n && !bits)) return HUMID_GPU_ERR_ARG;
   State &s = h->s;
   if (!s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "not finalized");
+  if (s.shard_mode) return fail(h, HUMID_GPU_ERR_ARG, "use humid_gpu_shard_keep_bits in shard mode");
   if (first_tuple + n > s.report_tuples) return fail(h, HUMID_GPU_ERR_ARG, "tuple range out of bounds");
   if (first_tuple % 64) return fail(h, HUMID_GPU_ERR_ARG, "first_tuple must be a multiple of 64");
   if (n == 0) return HUMID_GPU_OK;
@@ -266,7 +280,9 @@ int humid_gpu_debug_words(humid_gpu *h, uint64_t cap, uint64_t *keys, uint32_t *
     if (keys) HUMID_CUDA(cudaMemcpyAsync(keys, s.word_key.p, U * 8, cudaMemcpyDeviceToHost, s.stream));
     if (counts) HUMID_CUDA(cudaMemcpyAsync(counts, s.word_count.p, U * 4, cudaMemcpyDeviceToHost, s.stream));
     if (first_tuple) HUMID_CUDA(cudaMemcpyAsync(first_tuple, s.word_first.p, U * 4, cudaMemcpyDeviceToHost, s.stream));
-    if (cluster_ids) {
+    if (cluster_ids && s.shard_mode) {
+      HUMID_CUDA(cudaMemcpyAsync(cluster_ids, s.word_cid.p, U * 4, cudaMemcpyDeviceToHost, s.stream));
+    } else if (cluster_ids) {
       s.out_ids.ensure(U);
       word_cluster_ids_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.label.p, s.seed_index.p, U, s.out_ids.p);
       HUMID_CUDA(cudaMemcpyAsync(cluster_ids, s.out_ids.p, U * 4, cudaMemcpyDeviceToHost, s.stream));

@@ -80,18 +80,6 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-// cluster id of every tuple this shard received (after import_graph: label / seed_index are
-// whole-job columns indexed by global rank)
-__global__ void __launch_bounds__(256)
-    shard_tuple_ids_kernel(const uint64_t *__restrict__ keys, uint64_t n, const Lookup lk, uint32_t base,
-                           const uint32_t *__restrict__ label, const uint32_t *__restrict__ seed_index,
-                           uint32_t *__restrict__ out) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  uint32_t r = table_rank(lk, keys[i]);  // always present: the tuple was inserted here
-  out[i] = seed_index[label[base + r]] + 1u;
-}
-
 // ---- probe ---------------------------------------------------------------------------------
 // One thread per (word, first modified position); upward variants with at most d modified
 // positions (strictly increasing), exactly the enumeration of hammingd_probe_kernel.
@@ -351,6 +339,126 @@ __global__ void widen_rows_kernel(const uint32_t *__restrict__ excl, uint64_t U,
   uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (r < U) row_ptr[r] = excl[r];
   if (r == U) row_ptr[U] = total;
+}
+
+// ---- clustering across shards ------------------------------------------------------------------
+// A component of the neighbour graph that has no entry pointing outside the shard ("closed") is
+// complete here and is replayed by stage_cluster as on one GPU.  The others ("open") are
+// exported whole — every member with its count, first tuple and list — gathered on all shards
+// and replayed there on a compact copy of that sub-graph; every shard keeps the results for
+// the words it owns.
+__global__ void open_flags_kernel(const uint32_t *__restrict__ comp, const uint32_t *__restrict__ comp_open,
+                                  const uint64_t *__restrict__ row_ptr, uint64_t U, uint32_t *__restrict__ is_open,
+                                  uint32_t *__restrict__ open_deg) {
+  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= U) return;
+  uint32_t o = comp_open[comp[r]];
+  is_open[r] = o;
+  open_deg[r] = o ? (uint32_t)(row_ptr[r + 1] - row_ptr[r]) : 0u;
+}
+
+__global__ void __launch_bounds__(256)
+    export_open_kernel(const uint32_t *__restrict__ is_open, const uint32_t *__restrict__ open_pos,
+                       const uint32_t *__restrict__ open_ent, const uint64_t *__restrict__ row_ptr,
+                       const uint32_t *__restrict__ col, const uint32_t *__restrict__ count,
+                       const uint32_t *__restrict__ first, uint64_t U, uint32_t base, uint32_t *__restrict__ o_rank,
+                       uint32_t *__restrict__ o_count, uint32_t *__restrict__ o_first, uint32_t *__restrict__ o_deg,
+                       uint32_t *__restrict__ o_col) {
+  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= U || !is_open[r]) return;
+  const uint32_t i = open_pos[r];
+  const uint64_t lo = row_ptr[r], hi = row_ptr[r + 1];
+  o_rank[i] = base + (uint32_t)r;
+  o_count[i] = count[r];
+  o_first[i] = first[r];
+  o_deg[i] = (uint32_t)(hi - lo);
+  uint32_t *dst = o_col + open_ent[r];
+  for (uint64_t e = lo; e < hi; e++) dst[e - lo] = col[e];
+}
+
+// columns of the gathered open sub-graph: global rank -> position in the (ascending) rank list
+__global__ void __launch_bounds__(256)
+    remap_open_cols_kernel(const uint32_t *__restrict__ ranks, uint64_t n, const uint32_t *__restrict__ col_in,
+                           uint64_t E, uint32_t *__restrict__ col_out) {
+  uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= E) return;
+  const uint32_t v = col_in[e];
+  uint64_t lo = 0, hi = n;
+  while (lo < hi) {
+    uint64_t mid = (lo + hi) >> 1;
+    if (ranks[mid] < v) lo = mid + 1; else hi = mid;
+  }
+  col_out[e] = (uint32_t)lo;
+}
+
+// closed seeds: maxLeaf as a global rank + its first tuple
+__global__ void closed_seeds_kernel(const uint32_t *__restrict__ seed_flag, uint32_t *__restrict__ seed_max,
+                                    const uint32_t *__restrict__ word_first, uint64_t U, uint32_t base,
+                                    uint32_t *__restrict__ seed_first) {
+  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= U || !seed_flag[r]) return;
+  seed_first[r] = word_first[seed_max[r]];
+  seed_max[r] += base;
+}
+
+// results of the open sub-graph for the words this shard owns (positions [off, off + n))
+__global__ void merge_open_kernel(uint64_t off, uint64_t n, const uint32_t *__restrict__ ranks,
+                                  const uint32_t *__restrict__ firsts, const uint32_t *__restrict__ o_flag,
+                                  const uint64_t *__restrict__ o_size, const uint32_t *__restrict__ o_max, uint32_t base,
+                                  uint32_t *__restrict__ seed_flag, uint64_t *__restrict__ seed_size,
+                                  uint32_t *__restrict__ seed_max, uint32_t *__restrict__ seed_first) {
+  uint64_t k = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const uint64_t i = off + k;
+  const uint32_t r = ranks[i] - base;
+  const uint32_t f = o_flag[i];
+  seed_flag[r] = f;
+  if (f) {
+    seed_size[r] = o_size[i];
+    seed_max[r] = ranks[o_max[i]];
+    seed_first[r] = firsts[o_max[i]];
+  }
+}
+
+__global__ void cluster_first_kernel(const uint32_t *__restrict__ seed_flag, const uint32_t *__restrict__ seed_index,
+                                     const uint32_t *__restrict__ seed_first, uint64_t U,
+                                     uint32_t *__restrict__ cluster_first) {
+  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < U && seed_flag[r]) cluster_first[seed_index[r]] = seed_first[r];
+}
+
+__global__ void open_seed_ids_kernel(uint64_t off, uint64_t n, const uint32_t *__restrict__ ranks,
+                                     const uint32_t *__restrict__ o_flag, const uint32_t *__restrict__ seed_index,
+                                     uint32_t base, uint32_t id_offset, uint32_t *__restrict__ open_ids) {
+  uint64_t k = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const uint64_t i = off + k;
+  if (o_flag[i]) open_ids[i] = id_offset + seed_index[ranks[i] - base] + 1u;
+}
+
+__global__ void word_ids_kernel(uint64_t U, const uint32_t *__restrict__ is_open, const uint32_t *__restrict__ open_pos,
+                                uint64_t off, const uint32_t *__restrict__ o_label,
+                                const uint32_t *__restrict__ open_ids, const uint32_t *__restrict__ label,
+                                const uint32_t *__restrict__ seed_index, uint32_t id_offset,
+                                uint32_t *__restrict__ word_cid) {
+  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= U) return;
+  word_cid[r] = is_open[r] ? open_ids[o_label[off + open_pos[r]]] : id_offset + seed_index[label[r]] + 1u;
+}
+
+__global__ void keep_bits_kernel(const uint32_t *__restrict__ cluster_first, uint64_t C, uint32_t *__restrict__ bits) {
+  uint64_t c = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  uint32_t t = cluster_first[c];
+  atomicOr(bits + (t >> 5), 1u << (t & 31u));
+}
+
+__global__ void __launch_bounds__(256)
+    shard_word_ids_for_tuples_kernel(const uint64_t *__restrict__ keys, uint64_t n, const Lookup lk,
+                                     const uint32_t *__restrict__ word_cid, uint32_t *__restrict__ out) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  out[i] = word_cid[table_rank(lk, keys[i])];  // always present: the tuple was inserted here
 }
 
 static Layout layout_of(const State &s) {
@@ -625,64 +733,182 @@ int humid_gpu_shard_build_rows(humid_gpu *h, uint64_t *n_entries) {
   });
 }
 
-int humid_gpu_shard_export_graph(humid_gpu *h, uint64_t *d_keys, uint32_t *d_counts, uint32_t *d_first,
-                                 uint32_t *d_degree, uint32_t *d_col) {
+int humid_gpu_shard_cluster_local(humid_gpu *h, uint64_t *n_open_words, uint64_t *n_open_entries) {
   if (int rc = require_shard(h, true)) return rc;
   State &s = h->s;
-  const uint64_t U = s.n_shard_words, E = s.n_entries;
+  if (!n_open_words || !n_open_entries) return HUMID_GPU_ERR_ARG;
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
+    const uint64_t U = s.n_shard_words;
+    s.cluster_col_base = (uint32_t)s.bases[s.part];
+    s.cluster_skip_open = true;
+    s.n_open_local = s.n_open_entries_local = 0;
+    stage_cluster(s);  // closed components only, no ids yet
     if (U) {
-      HUMID_CUDA(cudaMemcpyAsync(d_keys, s.word_key.p, U * 8, cudaMemcpyDeviceToDevice, s.stream));
-      HUMID_CUDA(cudaMemcpyAsync(d_counts, s.word_count.p, U * 4, cudaMemcpyDeviceToDevice, s.stream));
-      HUMID_CUDA(cudaMemcpyAsync(d_first, s.word_first.p, U * 4, cudaMemcpyDeviceToDevice, s.stream));
-      degree_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.row_ptr.p, U, d_degree);
+      Timed t(s, "shard_open_words", U, U * 24);
+      s.is_open.ensure(U);
+      s.open_pos.ensure(U + 1);
+      s.open_ent.ensure(U + 1);
+      s.work_c.ensure(U + 1);
+      open_flags_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.comp.p, s.comp_open.p, s.row_ptr.p, U, s.is_open.p,
+                                                                s.work_c.p);
+      uint32_t *tot = reinterpret_cast<uint32_t *>(s.counters.p + 10);
+      int l = exclusive_scan_u32(s.is_open.p, s.open_pos.p, U, tot, s.scan_scratch, s.stream);
+      l += exclusive_scan_u32(s.work_c.p, s.open_ent.p, U, tot + 2, s.scan_scratch, s.stream);
+      uint32_t host[4] = {0, 0, 0, 0};
+      HUMID_CUDA(cudaMemcpyAsync(host, tot, sizeof(host), cudaMemcpyDeviceToHost, s.stream));
+      HUMID_CUDA(cudaStreamSynchronize(s.stream));
+      s.n_open_local = host[0];
+      s.n_open_entries_local = host[2];
+      t.launches = l + 1;
     }
-    if (E) HUMID_CUDA(cudaMemcpyAsync(d_col, s.col.p, E * 4, cudaMemcpyDeviceToDevice, s.stream));
+    *n_open_words = s.n_open_local;
+    *n_open_entries = s.n_open_entries_local;
+  });
+}
+
+int humid_gpu_shard_export_open(humid_gpu *h, uint32_t *d_rank, uint32_t *d_count, uint32_t *d_first, uint32_t *d_deg,
+                                uint32_t *d_col) {
+  if (int rc = require_shard(h, true)) return rc;
+  State &s = h->s;
+  return guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(s.device));
+    const uint64_t U = s.n_shard_words;
+    if (U && s.n_open_local) {
+      Timed t(s, "shard_export_open", s.n_open_local, s.n_open_local * 20 + s.n_open_entries_local * 8);
+      export_open_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.is_open.p, s.open_pos.p, s.open_ent.p, s.row_ptr.p,
+                                                                 s.col.p, s.word_count.p, s.word_first.p, U,
+                                                                 (uint32_t)s.bases[s.part], d_rank, d_count, d_first,
+                                                                 d_deg, d_col);
+    }
     HUMID_CUDA(cudaGetLastError());
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
   });
 }
 
-int humid_gpu_shard_import_graph(humid_gpu *h, uint64_t n_words, uint64_t n_entries, uint64_t n_tuples,
-                                 uint64_t n_usable, const uint64_t *d_keys, const uint32_t *d_counts,
-                                 const uint32_t *d_first, const uint32_t *d_degree, const uint32_t *d_col) {
+int humid_gpu_shard_import_open(humid_gpu *h, uint64_t open_offset, uint64_t n_open, uint64_t n_entries,
+                                const uint32_t *d_rank, const uint32_t *d_count, const uint32_t *d_first,
+                                const uint32_t *d_deg, const uint32_t *d_col, uint64_t *n_clusters_local) {
   if (int rc = require_shard(h, true)) return rc;
   State &s = h->s;
-  if (n_words >= 0xFFFFFFFFull || n_entries >= 0xFFFFFFFFull || n_tuples >= 0xFFFFFFFFull)
-    return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "job too large for 32-bit ranks");
+  if (!n_clusters_local || open_offset + s.n_open_local > n_open) return fail(h, HUMID_GPU_ERR_ARG, "import_open: bad arguments");
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
-    const uint64_t U = n_words, E = n_entries;
-    s.word_key.ensure(U + 1);
-    s.word_count.ensure(U + 1);
-    s.word_first.ensure(U + 1);
-    s.row_ptr.ensure(U + 2);
-    s.col.ensure(E + 1);
-    {
-      Timed t(s, "shard_import_graph", U, U * 28 + E * 8);
-      if (U) {
-        HUMID_CUDA(cudaMemcpyAsync(s.word_key.p, d_keys, U * 8, cudaMemcpyDeviceToDevice, s.stream));
-        HUMID_CUDA(cudaMemcpyAsync(s.word_count.p, d_counts, U * 4, cudaMemcpyDeviceToDevice, s.stream));
-        HUMID_CUDA(cudaMemcpyAsync(s.word_first.p, d_first, U * 4, cudaMemcpyDeviceToDevice, s.stream));
-      }
-      if (E) HUMID_CUDA(cudaMemcpyAsync(s.col.p, d_col, E * 4, cudaMemcpyDeviceToDevice, s.stream));
-      s.seed_index.ensure(U + 1);
-      int launches = 0;
-      if (U) launches += exclusive_scan_u32(d_degree, s.seed_index.p, U, nullptr, s.scan_scratch, s.stream);
-      widen_rows_kernel<<<grid_for(U + 1, 256), 256, 0, s.stream>>>(s.seed_index.p, U, E, s.row_ptr.p);
-      t.launches = launches + 1;
+    const uint64_t U = s.n_shard_words;
+    const uint32_t base = (uint32_t)s.bases[s.part];
+    if (!s.open) {
+      s.open = new State();
+      s.open->cfg = s.cfg;
+      s.open->device = s.device;
+      s.open->stream = s.stream;
+      s.open->counters.ensure(64);
     }
-    s.unique = U;
-    s.n_entries = E;
+    State &o = *s.open;
+    o.stats.clear();
+    o.unique = n_open;
+    o.n_entries = n_entries;
+    s.open_offset = open_offset;
+    s.n_open_total = n_open;
+    s.open_rank.ensure(n_open + 1);
+    s.open_first.ensure(n_open + 1);
+    if (n_open) {
+      Timed t(s, "shard_open_graph", n_open, n_open * 28 + n_entries * 12);
+      HUMID_CUDA(cudaMemcpyAsync(s.open_rank.p, d_rank, n_open * 4, cudaMemcpyDeviceToDevice, s.stream));
+      HUMID_CUDA(cudaMemcpyAsync(s.open_first.p, d_first, n_open * 4, cudaMemcpyDeviceToDevice, s.stream));
+      o.word_count.ensure(n_open + 1);
+      HUMID_CUDA(cudaMemcpyAsync(o.word_count.p, d_count, n_open * 4, cudaMemcpyDeviceToDevice, s.stream));
+      o.row_ptr.ensure(n_open + 2);
+      o.col.ensure(n_entries + 1);
+      o.seed_index.ensure(n_open + 1);
+      int l = exclusive_scan_u32(d_deg, o.seed_index.p, n_open, nullptr, s.scan_scratch, s.stream);
+      widen_rows_kernel<<<grid_for(n_open + 1, 256), 256, 0, s.stream>>>(o.seed_index.p, n_open, n_entries, o.row_ptr.p);
+      if (n_entries)
+        remap_open_cols_kernel<<<grid_for(n_entries, 256), 256, 0, s.stream>>>(s.open_rank.p, n_open, d_col, n_entries,
+                                                                               o.col.p);
+      t.launches = l + 2;
+    }
+    HUMID_CUDA(cudaMemsetAsync(o.counters.p, 0, 64 * sizeof(unsigned long long), s.stream));
+    stage_cluster(o);  // the same replay, on the gathered open components
+    for (auto &st : o.stats) s.stats.push_back(st);
+    o.stats.clear();
+    s.seed_first.ensure(U + 1);
+    if (U) {
+      closed_seeds_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.seed_flag.p, s.seed_max.p, s.word_first.p, U, base,
+                                                                  s.seed_first.p);
+      if (s.n_open_local)
+        merge_open_kernel<<<grid_for(s.n_open_local, 256), 256, 0, s.stream>>>(
+            open_offset, s.n_open_local, s.open_rank.p, s.open_first.p, o.seed_flag.p, o.seed_size.p, o.seed_max.p, base,
+            s.seed_flag.p, s.seed_size.p, s.seed_max.p, s.seed_first.p);
+    }
+    stage_cluster_number(s);  // ids of this shard's seeds, relative to the shard
+    s.cluster_first.ensure(s.n_clusters + 1);
+    if (U)
+      cluster_first_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.seed_flag.p, s.seed_index.p, s.seed_first.p, U,
+                                                                   s.cluster_first.p);
+    HUMID_CUDA(cudaGetLastError());
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    *n_clusters_local = s.n_clusters;
+  });
+}
+
+int humid_gpu_shard_assign_ids(humid_gpu *h, uint64_t id_offset, uint32_t *d_open_ids) {
+  if (int rc = require_shard(h, true)) return rc;
+  State &s = h->s;
+  if (!s.open) return fail(h, HUMID_GPU_ERR_ARG, "assign_ids before import_open");
+  return guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(s.device));
+    s.id_offset = id_offset;
+    if (s.n_open_local)
+      open_seed_ids_kernel<<<grid_for(s.n_open_local, 256), 256, 0, s.stream>>>(
+          s.open_offset, s.n_open_local, s.open_rank.p, s.open->seed_flag.p, s.seed_index.p, (uint32_t)s.bases[s.part],
+          (uint32_t)id_offset, d_open_ids);
+    HUMID_CUDA(cudaGetLastError());
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+  });
+}
+
+int humid_gpu_shard_finish(humid_gpu *h, const uint32_t *d_open_ids, uint64_t n_tuples, uint64_t n_usable,
+                           uint64_t n_words, uint64_t n_clusters) {
+  if (int rc = require_shard(h, true)) return rc;
+  State &s = h->s;
+  if (!s.open) return fail(h, HUMID_GPU_ERR_ARG, "finish before import_open");
+  if (n_tuples >= 0xFFFFFFFFull) return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "more than 2^32-2 tuples");
+  return guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(s.device));
+    const uint64_t U = s.n_shard_words;
+    s.word_cid.ensure(U + 1);
+    if (U) {
+      Timed t(s, "shard_word_ids", U, U * 20);
+      word_ids_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(U, s.is_open.p, s.open_pos.p, s.open_offset,
+                                                              s.open->label.p, d_open_ids, s.label.p, s.seed_index.p,
+                                                              (uint32_t)s.id_offset, s.word_cid.p);
+    }
+    HUMID_CUDA(cudaGetLastError());
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
     s.report_tuples = n_tuples;
     s.report_usable = n_usable;
-    stage_cluster(s);
-    stage_keep(s);
+    s.report_unique = n_words;
+    s.report_clusters = n_clusters;
+    resolve_stats(s);
+    s.finalized = true;
+  });
+}
+
+int humid_gpu_shard_keep_bits(humid_gpu *h, uint32_t *d_bits, uint64_t n_words32) {
+  if (int rc = require_shard(h, true)) return rc;
+  State &s = h->s;
+  if (!s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "not finalized");
+  if (n_words32 * 32 < s.report_tuples) return fail(h, HUMID_GPU_ERR_ARG, "keep_bits: buffer too small");
+  return guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(s.device));
+    HUMID_CUDA(cudaMemsetAsync(d_bits, 0, n_words32 * 4, s.stream));
+    if (s.n_clusters) {
+      Timed t(s, "keep", s.n_clusters, s.n_clusters * 8);
+      keep_bits_kernel<<<grid_for(s.n_clusters, 256), 256, 0, s.stream>>>(s.cluster_first.p, s.n_clusters, d_bits);
+    }
     HUMID_CUDA(cudaGetLastError());
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     resolve_stats(s);
-    s.finalized = true;
   });
 }
 
@@ -696,9 +922,8 @@ int humid_gpu_shard_tuple_ids(humid_gpu *h, uint32_t *d_ids) {
     HUMID_CUDA(cudaSetDevice(s.device));
     {
       Timed t(s, "cluster_ids", s.src_n, s.src_n * 36);
-      shard_tuple_ids_kernel<<<grid_for(s.src_n, 256), 256, 0, s.stream>>>(s.shard_keys.p, s.src_n, s.lookup(),
-                                                                           (uint32_t)s.bases[s.part], s.label.p,
-                                                                           s.seed_index.p, d_ids);
+      shard_word_ids_for_tuples_kernel<<<grid_for(s.src_n, 256), 256, 0, s.stream>>>(s.shard_keys.p, s.src_n, s.lookup(),
+                                                                                     s.word_cid.p, d_ids);
     }
     HUMID_CUDA(cudaGetLastError());
     HUMID_CUDA(cudaStreamSynchronize(s.stream));

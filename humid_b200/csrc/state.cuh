@@ -92,6 +92,14 @@ struct State {
   const uint64_t *src_keys = nullptr;   // table input override (nullptr: tuple_key / implicit index)
   const uint32_t *src_index = nullptr;
   uint64_t src_n = 0;
+  // clustering across shards (shard.cu): open components are replayed in a second State
+  State *open = nullptr;
+  uint64_t n_open_local = 0, n_open_entries_local = 0, open_offset = 0, n_open_total = 0, id_offset = 0;
+  uint64_t report_unique = 0, report_clusters = 0;
+  DevBuf<uint32_t> is_open, open_pos, open_ent, open_rank, open_first, seed_first, cluster_first, word_cid;
+  uint32_t cluster_col_base = 0;     // stage_cluster: columns are rank + base
+  bool cluster_skip_open = false;    // ... and components with a neighbour outside [0, unique) are left for later
+  DevBuf<uint32_t> open_flag, comp_open;
   uint32_t part = 0, n_parts = 1;
   uint64_t splitters[16] = {0};
   uint64_t bases[17] = {0};
@@ -173,6 +181,7 @@ int stage_csr(State &s);               // sort directed entries, row_ptr / col (
 int stage_csr_pairs(State &s);         // Hamming mode: undirected pairs + degrees -> row_ptr / col
 int stage_csr_directed(State &s);      // shard mode: directed entries + degrees -> row_ptr / col
 int stage_cluster(State &s);           // components, replay, ids, sizes, maxLeaf
+int stage_cluster_number(State &s);    // seed flags -> cluster ids, compacted size / maxLeaf
 int stage_keep(State &s);              // keep bitmap
 int stage_cluster_ids(State &s, uint64_t first, uint64_t n, uint32_t *d_out);
 int stage_histogram(State &s, int which);

@@ -43,8 +43,12 @@ def _bind(L):
     L.humid_gpu_shard_answer.argtypes = [vp, vp, vp, u64, vp]
     L.humid_gpu_shard_apply_answers.argtypes = [vp, vp, vp, u64]
     L.humid_gpu_shard_build_rows.argtypes = [vp, P(u64)]
-    L.humid_gpu_shard_export_graph.argtypes = [vp, vp, vp, vp, vp, vp]
-    L.humid_gpu_shard_import_graph.argtypes = [vp, u64, u64, u64, u64, vp, vp, vp, vp, vp]
+    L.humid_gpu_shard_cluster_local.argtypes = [vp, P(u64), P(u64)]
+    L.humid_gpu_shard_export_open.argtypes = [vp, vp, vp, vp, vp, vp]
+    L.humid_gpu_shard_import_open.argtypes = [vp, u64, u64, u64, vp, vp, vp, vp, vp, P(u64)]
+    L.humid_gpu_shard_assign_ids.argtypes = [vp, u64, vp]
+    L.humid_gpu_shard_finish.argtypes = [vp, vp, u64, u64, u64, u64]
+    L.humid_gpu_shard_keep_bits.argtypes = [vp, vp, u64]
     L.humid_gpu_shard_tuple_ids.argtypes = [vp, vp]
     L._shard_bound = True
     return L
@@ -54,8 +58,9 @@ SHARD_EXPORTS = [
     "humid_gpu_shard_begin", "humid_gpu_shard_sample_keys", "humid_gpu_shard_partition",
     "humid_gpu_shard_export_tuples", "humid_gpu_shard_import_tuples", "humid_gpu_shard_set_layout",
     "humid_gpu_shard_probe_count", "humid_gpu_shard_probe", "humid_gpu_shard_answer",
-    "humid_gpu_shard_apply_answers", "humid_gpu_shard_build_rows", "humid_gpu_shard_export_graph",
-    "humid_gpu_shard_import_graph", "humid_gpu_shard_tuple_ids",
+    "humid_gpu_shard_apply_answers", "humid_gpu_shard_build_rows", "humid_gpu_shard_cluster_local",
+    "humid_gpu_shard_export_open", "humid_gpu_shard_import_open", "humid_gpu_shard_assign_ids",
+    "humid_gpu_shard_finish", "humid_gpu_shard_keep_bits", "humid_gpu_shard_tuple_ids",
 ]
 
 
@@ -152,35 +157,76 @@ class CudaShardEngine(api.Dedup):
         self.n_shard_entries = int(e.value)
         return int(e.value)
 
-    def export_graph(self):
-        u, e = self.n_shard_words, self.n_shard_entries
-        k, c, f, d = (self._empty(u, torch.int64), self._empty(u, torch.int32), self._empty(u, torch.int32),
-                      self._empty(u, torch.int32))
-        col = self._empty(e, torch.int32)
-        self._check(self._L.humid_gpu_shard_export_graph(self._h, _dp(k), _dp(c), _dp(f), _dp(d), _dp(col)),
-                    "shard_export_graph")
-        return k, c, f, d, col
+    def cluster_local(self) -> Tuple[int, int]:
+        a, b = C.c_uint64(0), C.c_uint64(0)
+        self._check(self._L.humid_gpu_shard_cluster_local(self._h, C.byref(a), C.byref(b)), "shard_cluster_local")
+        self.n_open, self.n_open_entries = int(a.value), int(b.value)
+        return self.n_open, self.n_open_entries
 
-    def import_graph(self, n_tuples: int, n_usable: int, keys, counts, first, degree, col):
+    def export_open(self):
+        n, e = self.n_open, self.n_open_entries
+        r, c, f, d = (self._empty(n, torch.int32) for _ in range(4))
+        col = self._empty(e, torch.int32)
+        self._check(self._L.humid_gpu_shard_export_open(self._h, _dp(r), _dp(c), _dp(f), _dp(d), _dp(col)),
+                    "shard_export_open")
+        return r, c, f, d, col
+
+    def import_open(self, open_offset: int, rank, count, first, deg, col) -> int:
         self._sync()
-        self._check(self._L.humid_gpu_shard_import_graph(self._h, keys.numel(), col.numel(), n_tuples, n_usable, _dp(keys),
-                                                         _dp(counts), _dp(first), _dp(degree), _dp(col)),
-                    "shard_import_graph")
-        self.n_tuples_total = n_tuples
+        n = C.c_uint64(0)
+        self._check(self._L.humid_gpu_shard_import_open(self._h, open_offset, rank.numel(), col.numel(), _dp(rank),
+                                                        _dp(count), _dp(first), _dp(deg), _dp(col), C.byref(n)),
+                    "shard_import_open")
+        self.n_open_total = rank.numel()
+        return int(n.value)
+
+    def assign_ids(self, id_offset: int):
+        ids = torch.zeros(max(self.n_open_total, 1), dtype=torch.int32, device=self.device)
+        self._sync()
+        self._check(self._L.humid_gpu_shard_assign_ids(self._h, id_offset, C.c_void_p(ids.data_ptr())), "shard_assign_ids")
+        return ids
+
+    def finish(self, open_ids, n_tuples: int, n_usable: int, n_words: int, n_clusters: int):
+        self._sync()
+        self._check(self._L.humid_gpu_shard_finish(self._h, C.c_void_p(open_ids.data_ptr()), n_tuples, n_usable, n_words,
+                                                   n_clusters), "shard_finish")
+
+    def keep_bits32(self, n_tuples: int):
+        """int32 tensor of ceil(n_tuples/32) words: this shard's contribution to the keep mask."""
+        n32 = (n_tuples + 31) // 32 + 1
+        bits = self._empty(n32, torch.int32)
+        self._check(self._L.humid_gpu_shard_keep_bits(self._h, C.c_void_p(bits.data_ptr()), n32), "shard_keep_bits")
+        return bits
+
+    # this shard's part of the results (numpy)
+    def local_words(self):
+        U = self.n_shard_words
+        keys, cnt, first, cid = (np.zeros(max(U, 1), dtype=t) for t in (np.uint64, np.uint32, np.uint32, np.uint32))
+        self._check(self._L.humid_gpu_debug_words(self._h, max(U, 1), api._ptr(keys), api._ptr(cnt), api._ptr(first),
+                                                  api._ptr(cid)), "debug_words")
+        return keys[:U], cnt[:U], first[:U], cid[:U]
+
+    def local_rows(self):
+        U = self.n_shard_words
+        n = C.c_uint64(0)
+        self._check(self._L.humid_gpu_debug_neighbours(self._h, None, None, C.byref(n)), "debug_neighbours")
+        row_ptr = np.zeros(U + 1, dtype=np.uint64)
+        col = np.zeros(max(n.value, 1), dtype=np.uint32)
+        self._check(self._L.humid_gpu_debug_neighbours(self._h, api._ptr(row_ptr), api._ptr(col), C.byref(n)),
+                    "debug_neighbours")
+        return np.diff(row_ptr).astype(np.uint32), col[: n.value]
+
+    def local_clusters(self, n: int):
+        size = np.zeros(max(n, 1), dtype=np.uint64)
+        mx = np.zeros(max(n, 1), dtype=np.uint32)
+        self._check(self._L.humid_gpu_debug_clusters(self._h, max(n, 1), api._ptr(size), api._ptr(mx)), "debug_clusters")
+        return size[:n], mx[:n]
 
     def tuple_ids(self):
         """int32 tensor: cluster id of every tuple handed to import_tuples, in that order."""
         ids = self._empty(self.n_shard_tuples, torch.int32)
         self._check(self._L.humid_gpu_shard_tuple_ids(self._h, _dp(ids)), "shard_tuple_ids")
         return ids
-
-    def global_keep_bits(self, first: int, n: int) -> np.ndarray:
-        """bool[n] for GLOBAL tuple indices first..first+n."""
-        lo = (first // 64) * 64
-        m = first + n - lo
-        bits = np.zeros((m + 63) // 64 + 1, dtype=np.uint64)
-        self._check(self._L.humid_gpu_keep_mask(self._h, lo, m, bits.ctypes.data_as(C.c_void_p)), "keep_mask")
-        return np.unpackbits(bits.view(np.uint8), bitorder="little")[first - lo: first - lo + n].astype(bool)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -197,6 +243,9 @@ class TorchComm:
 
     def all_gather_into_tensor(self, out, inp):
         dist.all_gather_into_tensor(out, inp, group=self.group)
+
+    def all_reduce_sum(self, t):
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
 
 
 class ThreadComm:
@@ -236,6 +285,11 @@ class ThreadComm:
     def all_gather_into_tensor(self, out, inp):
         items = self._exchange(inp)
         out.copy_(torch.cat([t.to(out.device) for t in items]))
+        self.sh.barrier.wait()
+
+    def all_reduce_sum(self, t):
+        items = self._exchange(t.clone())
+        t.copy_(torch.stack(items).sum(dim=0).to(t.dtype))
         self.sh.barrier.wait()
 
 
@@ -350,34 +404,84 @@ class ShardedDedup:
         eng.apply_answers(qs, back)
         n_entries = eng.build_rows()
 
-        # the neighbour graph everywhere; clusters, keep mask, histograms
-        gk, gc, gf, gd, gcol = eng.export_graph()
-        sizes = self._gather_ints(n_shard, n_entries)
-        wsz, esz = [int(x) for x in sizes[:, 0]], [int(x) for x in sizes[:, 1]]
-        eng.import_graph(self.n_total, self.usable_total, all_gather_v(g, gk, wsz), all_gather_v(g, gc, wsz),
-                         all_gather_v(g, gf, wsz), all_gather_v(g, gd, wsz), all_gather_v(g, gcol, esz))
+        # clusters: components inside a shard are finished there; the ones that cross shards
+        # ("open") are gathered whole and replayed identically on every shard
+        n_open, n_open_e = eng.cluster_local()
+        orank, ocount, ofirst, odeg, ocol = eng.export_open()
+        sizes = self._gather_ints(n_open, n_open_e, n_shard)
+        osz, esz = [int(x) for x in sizes[:, 0]], [int(x) for x in sizes[:, 1]]
+        open_off = int(np.sum(sizes[:me, 0]))
+        n_cl = eng.import_open(open_off, all_gather_v(g, orank, osz), all_gather_v(g, ocount, osz),
+                               all_gather_v(g, ofirst, osz), all_gather_v(g, odeg, osz), all_gather_v(g, ocol, esz))
+        ncl = self._gather_ints(n_cl)[:, 0]
+        self.cluster_offsets = np.concatenate([[0], np.cumsum(ncl)])
+        self.n_clusters_local = int(n_cl)
+        ids = eng.assign_ids(int(self.cluster_offsets[me]))
+        if hasattr(eng, "_sync"):
+            eng._sync()
+        g.all_reduce_sum(ids)
+        eng.finish(ids, self.n_total, self.usable_total, self.n_words_total, int(self.cluster_offsets[-1]))
+        self.word_sizes = [int(x) for x in sizes[:, 2]]
         self.queries_sent = int(np.sum(qcounts))
+        self.open_words_total = int(np.sum(sizes[:, 0]))
 
-    # -- results (whole job unless stated) -------------------------------------------------------------
+    # -- results: whole job, identical on every rank, unless stated; all of them are collective -----
     def counts(self):
         return self.eng.counts()
 
+    def _gather_np(self, a: np.ndarray) -> np.ndarray:
+        """Concatenation over the ranks (in rank order) of a 1-d numpy array."""
+        dev = self.eng.device
+        n = self._gather_ints(a.size)[:, 0]
+        if a.dtype.itemsize == 8:
+            t = torch.from_numpy(np.ascontiguousarray(a).view(np.int64).copy()).to(dev)
+        else:
+            t = torch.from_numpy(np.ascontiguousarray(a).view(np.int32).copy()).to(dev)
+        if hasattr(self.eng, "_sync"):
+            self.eng._sync()
+        out = all_gather_v(self.comm, t, [int(x) for x in n]).cpu().numpy()
+        return out.view(a.dtype)
+
     def histogram(self, which: str):
-        return self.eng.histogram(which)
+        """counts.dat / neigh.dat / clusters.dat: every shard histograms its own words / lists /
+        clusters on its GPU, the (key, value) lists are merged here."""
+        k, v = self.eng.histogram(which)
+        ks, vs = self._gather_np(k.astype(np.uint64)), self._gather_np(v.astype(np.uint64))
+        uk, inv = np.unique(ks, return_inverse=True)
+        uv = np.zeros(uk.size, dtype=np.uint64)
+        np.add.at(uv, inv, vs)
+        return uk, uv
 
     def stats_text(self):
-        return self.eng.stats_text()
+        out = {}
+        for name, f in (("counts", "counts.dat"), ("neigh", "neigh.dat"), ("clusters", "clusters.dat")):
+            k, v = self.histogram(name)
+            out[f] = "".join(f"{int(a)} {int(b)}\n" for a, b in zip(k, v))
+        c = self.counts()
+        out["stats.dat"] = (f"total: {c['total']}\nusable: {c['usable']}\nunique: {c['unique']}\n"
+                            f"clusters: {c['clusters']}\n")
+        return out
+
+    def keep_words32(self):
+        """int32 tensor (device): the job's keep mask, bit t of word t//32 = tuple t is written."""
+        bits = self.eng.keep_bits32(self.n_total)
+        if hasattr(self.eng, "_sync"):
+            self.eng._sync()
+        self.comm.all_reduce_sum(bits)  # every tuple is kept by at most one cluster: sum == or
+        return bits
 
     def keep_mask(self) -> np.ndarray:
         """bool[n_local]: this rank's tuples that are written to the *_dedup files."""
-        return self.eng.global_keep_bits(self.tuple_offset, self.n_local)
+        w = self.keep_words32().cpu().numpy().view(np.uint32)
+        lo, hi = self.tuple_offset, self.tuple_offset + self.n_local
+        return np.unpackbits(w[lo // 32: (hi + 31) // 32 + 1].view(np.uint8), bitorder="little")[lo % 32: lo % 32 + self.n_local].astype(bool)
 
     def keep_bits(self) -> np.ndarray:
         return np.packbits(self.keep_mask(), bitorder="little")
 
     def cluster_ids(self) -> np.ndarray:
-        """uint32[n_local]: cluster ids of this rank's tuples (collective: the owners of the
-        key ranges look the ids up and send them back along the route the tuples took)."""
+        """uint32[n_local]: cluster ids of this rank's tuples (the owners of the key ranges look
+        the ids up and send them back along the route the tuples took)."""
         ids = self.eng.tuple_ids()
         if hasattr(self.eng, "_sync"):
             self.eng._sync()
@@ -386,14 +490,18 @@ class ShardedDedup:
         out[(self._sent_index.long() & 0xFFFFFFFF) - self.tuple_offset] = back
         return out.cpu().numpy().view(np.uint32)
 
+    # introspection for the parity tests: the shards' pieces put back together
     def words(self):
-        return self.eng.words()
+        return tuple(self._gather_np(a) for a in self.eng.local_words())
 
     def neighbours(self):
-        return self.eng.neighbours()
+        deg, col = self.eng.local_rows()
+        deg, col = self._gather_np(deg), self._gather_np(col)
+        return np.concatenate([[0], np.cumsum(deg.astype(np.uint64))]).astype(np.uint64), col
 
     def clusters(self):
-        return self.eng.clusters()
+        size, mx = self.eng.local_clusters(self.n_clusters_local)
+        return self._gather_np(size), self._gather_np(mx)
 
     def stage_stats(self):
         return self.eng.stage_stats()

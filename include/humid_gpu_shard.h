@@ -13,7 +13,10 @@
  *   probe_count / probe   variants owned by this shard are looked up in place, the
  *                         others become queries  ==all-to-all-v==>  answer  ==back==>  apply_answers
  *   build_rows            neighbour lists of the shard's words (columns = global ranks)
- *   export_graph  ==all-gather==>  import_graph       clustering, keep mask, histograms
+ *   cluster_local         components inside the shard are clustered in place        (findClusters)
+ *   export_open  ==all-gather==>  import_open   components that cross shards, replayed on every shard
+ *   assign_ids  ==all-reduce==>  finish         cluster ids in global walk order
+ *   keep_bits  ==all-reduce==>                  the job's keep mask
  *
  * All pointers named d_* are device memory of the handle's GPU, allocated by the caller
  * (sizes are known from the preceding call); everything else is host memory.  Same error
@@ -58,15 +61,31 @@ int humid_gpu_shard_answer(humid_gpu *h, const uint64_t *d_query_keys, const uin
                            uint32_t *d_answers);
 int humid_gpu_shard_apply_answers(humid_gpu *h, const uint32_t *d_query_src, const uint32_t *d_answers, uint64_t n);
 int humid_gpu_shard_build_rows(humid_gpu *h, uint64_t *n_entries);
-int humid_gpu_shard_export_graph(humid_gpu *h, uint64_t *d_keys, uint32_t *d_counts, uint32_t *d_first,
-                                 uint32_t *d_degree, uint32_t *d_col);
-/* The gathered graph (all shards concatenated in part order) -> clusters, keep mask,
- * histograms; afterwards the handle answers humid_gpu_counts / histogram / keep_mask /
- * debug_* for the WHOLE job (tuple indices are global). */
-int humid_gpu_shard_import_graph(humid_gpu *h, uint64_t n_words, uint64_t n_entries, uint64_t n_tuples,
-                                 uint64_t n_usable, const uint64_t *d_keys, const uint32_t *d_counts,
-                                 const uint32_t *d_first, const uint32_t *d_degree, const uint32_t *d_col);
-/* After import_graph: d_ids[i] = cluster id of the i-th tuple handed to import_tuples (the
+/* Clusters of the components that lie entirely inside this shard; the others ("open": some
+ * member has a neighbour on another shard) are counted for the export below. */
+int humid_gpu_shard_cluster_local(humid_gpu *h, uint64_t *n_open_words, uint64_t *n_open_entries);
+/* Every word of the open components: global rank, count, first tuple, list length and list
+ * (global ranks), words in rank order. */
+int humid_gpu_shard_export_open(humid_gpu *h, uint32_t *d_rank, uint32_t *d_count, uint32_t *d_first, uint32_t *d_deg,
+                                uint32_t *d_col);
+/* The open words of ALL shards (concatenated in part order == rank order; this shard's own
+ * ones start at open_offset): replays them and merges the result into the shard's clusters.
+ * Returns the number of clusters seeded by words of this shard. */
+int humid_gpu_shard_import_open(humid_gpu *h, uint64_t open_offset, uint64_t n_open, uint64_t n_entries,
+                                const uint32_t *d_rank, const uint32_t *d_count, const uint32_t *d_first,
+                                const uint32_t *d_deg, const uint32_t *d_col, uint64_t *n_clusters_local);
+/* id_offset = clusters seeded on lower parts.  Writes the ids of the open seeds this shard owns
+ * into d_open_ids (n_open entries, zero-initialised by the caller, summed over the shards). */
+int humid_gpu_shard_assign_ids(humid_gpu *h, uint64_t id_offset, uint32_t *d_open_ids);
+/* d_open_ids = the summed array.  The totals are what humid_gpu_counts reports afterwards;
+ * humid_gpu_histogram / debug_* then describe THIS SHARD's words, lists and clusters. */
+int humid_gpu_shard_finish(humid_gpu *h, const uint32_t *d_open_ids, uint64_t n_tuples, uint64_t n_usable,
+                           uint64_t n_words, uint64_t n_clusters);
+/* Bit t of d_bits (n_words32 32-bit words, global tuple positions) is set for the first tuple
+ * of the maxLeaf word of every cluster seeded on this shard; the job's keep mask is the sum /
+ * OR over the shards. */
+int humid_gpu_shard_keep_bits(humid_gpu *h, uint32_t *d_bits, uint64_t n_words32);
+/* After finish: d_ids[i] = cluster id of the i-th tuple handed to import_tuples (the
  * host routes them back to the ranks the tuples came from; filtered tuples never travelled
  * and keep id 0). */
 int humid_gpu_shard_tuple_ids(humid_gpu *h, uint32_t *d_ids);

@@ -153,53 +153,116 @@ class CpuShardEngine:
         self.col = (e & np.uint64(0xFFFFFFFF)).astype(np.uint32)
         return e.size
 
-    def export_graph(self):
-        return _t64(self.sk), _t32(self.sc), _t32(self.sf), _t32(self.deg), _t32(self.col)
+    # ---- clusters ------------------------------------------------------------------------------
+    @staticmethod
+    def _cluster(count, deg, col, maximum):
+        """oracle clustering of a compact graph -> (cluster id per word, seed word per cluster, size, maxLeaf)."""
+        row = np.concatenate([[0], np.cumsum(deg.astype(np.uint64))]).astype(np.uint64)
+        cl, size, mx = oracle.cluster_all(count.astype(np.uint64), row, col.astype(np.uint32), maximum)
+        _, seed = np.unique(cl, return_index=True)  # the seed is the lowest-ranked member, ids follow seed order
+        return cl, seed.astype(np.int64), size, mx
 
-    # ---- whole job ----------------------------------------------------------------------------
-    def import_graph(self, n_tuples, n_usable, keys, counts, first, degree, col):
-        self.g_keys, self.g_count, self.g_first = _u64(keys).copy(), _u32(counts).copy(), _u32(first).copy()
-        deg = _u32(degree).astype(np.uint64)
-        self.g_row = np.concatenate([[0], np.cumsum(deg)]).astype(np.uint64)
-        self.g_col = _u32(col).copy()
-        self.total, self.usable = n_tuples, n_usable
-        self.g_cluster, self.c_size, self.c_max = oracle.cluster_all(self.g_count, self.g_row, self.g_col, self.maximum)
-        self.keep = np.zeros(n_tuples, bool)
-        self.keep[self.g_first[self.c_max]] = True
+    def cluster_local(self):
+        from scipy.sparse import coo_matrix
+        from scipy.sparse.csgraph import connected_components
+
+        U, base = self.n_shard_words, self.base
+        src = np.repeat(np.arange(U), self.deg)
+        loc = (self.col >= base) & (self.col < base + U)
+        if U:
+            gph = coo_matrix((np.ones(int(loc.sum()), np.int8), (src[loc], (self.col[loc] - base).astype(np.int64))), shape=(U, U))
+            _, comp = connected_components(gph, directed=False)
+        else:
+            comp = np.zeros(0, np.int64)
+        comp_open = np.zeros(comp.max() + 1 if U else 0, bool)
+        comp_open[comp[src[~loc]]] = True
+        self.is_open = comp_open[comp] if U else np.zeros(0, bool)
+        closed = np.nonzero(~self.is_open)[0]
+        cmap = np.full(U, -1, np.int64)
+        cmap[closed] = np.arange(closed.size)
+        keep_e = ~self.is_open[src]
+        ccol = cmap[(self.col[keep_e] - base).astype(np.int64)]
+        cl, seed, size, mx = self._cluster(self.sc[closed], self.deg[closed], ccol, self.maximum)
+        # per local word: seed word (local rank) of its cluster; per seed: size, maxLeaf (global), first of maxLeaf
+        self.seed_of = np.full(U, -1, np.int64)
+        self.seed_of[closed] = closed[seed[cl.astype(np.int64) - 1]] if closed.size else []
+        self.seed_info = {int(closed[sd]): (int(size[k]), base + int(closed[mx[k]]), int(self.sf[closed[mx[k]]]))
+                          for k, sd in enumerate(seed)}
+        self.open_words = np.nonzero(self.is_open)[0]
+        self.n_open = self.open_words.size
+        return self.n_open, int(self.deg[self.open_words].sum())
+
+    def export_open(self):
+        ow = self.open_words
+        src = np.repeat(np.arange(self.n_shard_words), self.deg)
+        return (_t32((ow + self.base).astype(np.uint32)), _t32(self.sc[ow]), _t32(self.sf[ow]), _t32(self.deg[ow]),
+                _t32(self.col[self.is_open[src]]))
+
+    def import_open(self, open_offset, rank, count, first, deg, col):
+        rk, cnt, fst, dg, cl_ = _u32(rank), _u32(count), _u32(first), _u32(deg), _u32(col)
+        ccol = np.searchsorted(rk, cl_)
+        cl, seed, size, mx = self._cluster(cnt, dg, ccol, self.maximum)
+        self.open_off, self.n_open_total = open_offset, rk.size
+        self.o_seed_of = seed[cl.astype(np.int64) - 1] if rk.size else np.zeros(0, np.int64)  # compact index of the seed
+        mine = range(open_offset, open_offset + self.n_open)
+        self.o_is_seed = np.zeros(rk.size, bool)
+        self.o_is_seed[seed] = True
+        for k, sd in enumerate(seed):
+            if open_offset <= sd < open_offset + self.n_open:
+                self.seed_info[int(rk[sd]) - self.base] = (int(size[k]), int(rk[mx[k]]), int(fst[mx[k]]))
+        self.local_seeds = np.array(sorted(self.seed_info), dtype=np.int64)
+        self.seed_index = {int(w): i for i, w in enumerate(self.local_seeds)}
+        self.o_rank = rk
+        return self.local_seeds.size
+
+    def assign_ids(self, id_offset):
+        self.id_offset = id_offset
+        ids = np.zeros(max(self.n_open_total, 1), np.uint32)
+        for i in range(self.open_off, self.open_off + self.n_open):
+            if self.o_is_seed[i]:
+                ids[i] = id_offset + self.seed_index[int(self.o_rank[i]) - self.base] + 1
+        return _t32(ids)
+
+    def finish(self, open_ids, n_tuples, n_usable, n_words, n_clusters):
+        ids = _u32(open_ids)
+        U = self.n_shard_words
+        self.word_cid = np.zeros(U, np.uint32)
+        pos = 0
+        for r in range(U):
+            if self.is_open[r]:
+                self.word_cid[r] = ids[self.o_seed_of[self.open_off + pos]]
+                pos += 1
+            else:
+                self.word_cid[r] = self.id_offset + self.seed_index[int(self.seed_of[r])] + 1
+        self.totals = dict(total=int(n_tuples), usable=int(n_usable), unique=int(n_words), clusters=int(n_clusters))
+        info = [self.seed_info[int(w)] for w in self.local_seeds]
+        self.c_size = np.array([x[0] for x in info], np.uint64)
+        self.c_max = np.array([x[1] for x in info], np.uint32)
+        self.c_first = np.array([x[2] for x in info], np.int64)
+
+    def keep_bits32(self, n_tuples):
+        keep = np.zeros(((n_tuples + 31) // 32 + 1) * 32, np.uint8)
+        keep[self.c_first] = 1
+        return _t32(np.packbits(keep, bitorder="little").view(np.uint32))
 
     def counts(self):
-        return dict(total=int(self.total), usable=int(self.usable), unique=int(self.g_keys.size),
-                    clusters=int(self.c_size.size))
+        return dict(self.totals)
 
     def histogram(self, which):
-        v = {"counts": self.g_count.astype(np.uint64), "neigh": np.diff(self.g_row), "clusters": self.c_size}[which]
+        v = {"counts": self.sc.astype(np.uint64), "neigh": self.deg.astype(np.uint64), "clusters": self.c_size}[which]
         k, c = np.unique(v, return_counts=True)
         return k.astype(np.uint64), c.astype(np.uint64)
 
-    def stats_text(self):
-        out = {}
-        for name, f in (("counts", "counts.dat"), ("neigh", "neigh.dat"), ("clusters", "clusters.dat")):
-            k, v = self.histogram(name)
-            out[f] = "".join(f"{int(a)} {int(b)}\n" for a, b in zip(k, v))
-        c = self.counts()
-        out["stats.dat"] = (f"total: {c['total']}\nusable: {c['usable']}\nunique: {c['unique']}\n"
-                            f"clusters: {c['clusters']}\n")
-        return out
-
-    def global_keep_bits(self, first, n):
-        return self.keep[first:first + n]
-
     def tuple_ids(self):
-        lr = np.searchsorted(self.sk, self.rk)
-        return _t32(self.g_cluster[self.base + lr])
+        return _t32(self.word_cid[np.searchsorted(self.sk, self.rk)])
 
-    def words(self):
-        return self.g_keys, self.g_count, self.g_first, self.g_cluster
+    def local_words(self):
+        return self.sk, self.sc, self.sf, self.word_cid
 
-    def neighbours(self):
-        return self.g_row, self.g_col
+    def local_rows(self):
+        return self.deg, self.col
 
-    def clusters(self):
+    def local_clusters(self, n):
         return self.c_size, self.c_max
 
     def stage_stats(self):

@@ -40,7 +40,9 @@ def run_sharded(W, chars, seg_take, cfg):
             dd.add_batch(part[:half])
             dd.add_batch(part[half:])
             dd.finalize()
-            dd.ids = dd.cluster_ids()  # collective
+            # every result accessor is a collective: all shards call them in the same order
+            dd.res = dict(counts=dd.counts(), words=dd.words(), neighbours=dd.neighbours(), clusters=dd.clusters(),
+                          keep=dd.keep_mask(), ids=dd.cluster_ids(), stats=dd.stats_text())
             out[r] = dd
         except BaseException as e:  # noqa: BLE001
             err.append(e)
@@ -68,20 +70,21 @@ def test_logical_shards_match_oracle(W, ci, R, kw):
     dds, cuts = run_sharded(W, chars, seg_take, cfg)
     for r, dd in enumerate(dds):
         lo, hi = cuts[r], cuts[r + 1]
-        c = dd.counts()
+        res = dd.res
+        c = res["counts"]
         assert (c["total"], c["usable"], c["unique"], c["clusters"]) == (ref.total, ref.usable, ref.unique, ref.clusters)
-        keys, cnt, first, cid = dd.words()
+        keys, cnt, first, cid = res["words"]
         assert np.array_equal(keys, ref.keys)
         assert np.array_equal(cnt.astype(np.uint64), ref.count)
         assert np.array_equal(first.astype(np.uint64), ref.first)
         assert np.array_equal(cid, ref.cluster_of)
-        row, col = dd.neighbours()
+        row, col = res["neighbours"]
         assert np.array_equal(row, ref.row_ptr) and np.array_equal(col, ref.col)
-        size, mx = dd.clusters()
+        size, mx = res["clusters"]
         assert np.array_equal(size, ref.cluster_size) and np.array_equal(mx, ref.cluster_max)
-        assert np.array_equal(dd.keep_mask(), ref.keep[lo:hi].astype(bool))
-        assert np.array_equal(dd.ids, ref.cid[lo:hi])
-        assert dd.stats_text() == ref.stats_text()
+        assert np.array_equal(res["keep"], ref.keep[lo:hi].astype(bool))
+        assert np.array_equal(res["ids"], ref.cid[lo:hi])
+        assert res["stats"] == ref.stats_text()
     if W > 1 and R > 100:
         assert sum(dd.queries_sent for dd in dds) > 0
     for dd in dds:
