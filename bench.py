@@ -263,6 +263,8 @@ def run_gpu_arm(args):
     ms_e2e, wall_e2e, (counts_e2e, _) = timed(step_e2e, args.steps)
     clocks = sampler.stop() if sampler else None
     assert counts == counts_e2e, (counts, counts_e2e)
+    if world > 1 and rank == 0 and getattr(dd, "phases", None):
+        sys.stderr.write("phases (ms, last step, rank 0): " + json.dumps([(n, round(t, 3)) for n, t in dd.phases]) + "\n")
 
     if rank != 0:
         if world > 1:
@@ -314,10 +316,10 @@ def run_gpu_arm(args):
         "config": {"workload": WORKLOAD if args.config == 1 else cfg.name, "tuples_per_gpu": R_per, "tuples_total": R_all, "word_length": cfg.word_length,
                    "distance": cfg.distance, "clustering": "maximum" if cfg.maximum else "directional",
                    "l2": "inputs larger than L2 (word characters %.2f GB per GPU)" % (R_per * cfg.word_length / 1e9),
-                   "parallelism": "1 GPU" if world == 1 else f"words range-partitioned over {world} GPUs, NCCL all-to-all-v (words, variant queries) + all-gather (graph)",
+                   "parallelism": "1 GPU" if world == 1 else f"word space range-partitioned over {world} GPUs; NCCL all-to-all-v (tuples, variant queries), all-gather (components that cross shards)",
                    "result": counts},
         "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": t_e2e * 1e3,
-                "h2d_bytes_per_step": int(R_per * cfg.word_length), "d2h_bytes_per_step": int(d2h[0])},
+                "h2d_bytes_per_step": int(R_all * cfg.word_length), "d2h_bytes_per_step": int(d2h[0]) * world},
         "gpu_launches": int(launches_per_step * args.steps),
         "roofline": roofline, "clocks": clocks,
     }

@@ -127,117 +127,212 @@ int exclusive_scan_u32(const uint32_t *in, uint32_t *out, uint64_t n, uint32_t *
 }
 
 // ------------------------------------------------------------------------------------
-// Stable LSD radix sort, 8 bits per pass.  Per pass:
-//   radix_hist_kernel     per-tile digit histogram            hist[digit][tile]
-//   exclusive_scan_u32    over hist in (digit, tile) order    -> global offset of every
-//                                                                (digit, tile) run
-//   radix_scatter_kernel  stable in-tile ranking with warp match + per-warp counters
-// A tile is RS_THREADS*RS_ITEMS consecutive elements; warp w owns a contiguous sub-tile and
-// walks it in strips of 32 consecutive elements, so "element order" == (warp, strip, lane).
+// Stable LSD radix sort, 8 bits per pass, one read and one write of the data per pass:
+//   radix_digit_hist_kernel   ONE pass over the keys: the 256-bin histogram of every digit
+//   radix_digit_bases_kernel  exclusive scan of each histogram -> first output position of a digit
+//   radix_pass_kernel         per digit pass.  A tile (RS_TILE consecutive elements) ranks its
+//                             elements by digit (warp match + per-warp counters), learns how many
+//                             elements of each digit precede it from the tiles before it through a
+//                             chained look-back over `status` (aggregate / inclusive words, tiles
+//                             ordered by a ticket), reorders the tile in shared memory and writes
+//                             every digit run as consecutive addresses.
+// Warp w owns a contiguous sub-tile and walks it in strips of 32 consecutive elements, so
+// "element order" == (warp, strip, lane) and the in-tile ranking is stable.
 // ------------------------------------------------------------------------------------
 constexpr int RS_THREADS = 256;
 constexpr int RS_WARPS = RS_THREADS / 32;
 constexpr int RS_ITEMS = 16;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
 constexpr int RS_BINS = 256;
+constexpr int RS_MAX_PASSES = 8;
+constexpr uint64_t RS_AGGREGATE = 1ull << 62;  // status word: this tile's own count
+constexpr uint64_t RS_INCLUSIVE = 1ull << 63;  // status word: count of this tile and all before it
 
-__global__ void __launch_bounds__(RS_THREADS) radix_hist_kernel(const uint64_t *__restrict__ keys, uint64_t n,
-                                                                int shift, uint32_t *__restrict__ hist,
-                                                                uint32_t n_tiles) {
-  __shared__ uint32_t h[RS_BINS];
-  h[threadIdx.x] = 0;
+__global__ void __launch_bounds__(RS_THREADS) radix_digit_hist_kernel(const uint64_t *__restrict__ keys, uint64_t n,
+                                                                      int passes, uint32_t *__restrict__ hist) {
+  __shared__ uint32_t h[RS_MAX_PASSES][RS_BINS];
+  for (int p = 0; p < passes; p++) h[p][threadIdx.x] = 0;
   __syncthreads();
-  uint64_t base = (uint64_t)blockIdx.x * RS_TILE;
-#pragma unroll
-  for (int j = 0; j < RS_ITEMS; j++) {
-    uint64_t i = base + (uint64_t)j * RS_THREADS + threadIdx.x;
-    if (i < n) atomicAdd(&h[(uint32_t)(ld_stream_u64(keys + i) >> shift) & 255u], 1u);
+  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+  for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride) {
+    uint64_t key = ld_stream_u64(keys + i);
+    for (int p = 0; p < passes; p++) atomicAdd(&h[p][(uint32_t)(key >> (8 * p)) & 255u], 1u);
   }
   __syncthreads();
-  hist[(uint64_t)threadIdx.x * n_tiles + blockIdx.x] = h[threadIdx.x];
+  for (int p = 0; p < passes; p++) {
+    uint32_t c = h[p][threadIdx.x];
+    if (c) atomicAdd(&hist[p * RS_BINS + threadIdx.x], c);
+  }
+}
+
+// exclusive prefix over the 256 values held one per thread
+__device__ __forceinline__ uint32_t block_exclusive_256(uint32_t v, uint32_t *warp_sums) {
+  const uint32_t lane = lane_id();
+  uint32_t inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= (uint32_t)o) inc += t;
+  }
+  if (lane == 31) warp_sums[threadIdx.x >> 5] = inc;
+  __syncthreads();
+  uint32_t before = 0;
+  for (uint32_t k = 0; k < (threadIdx.x >> 5); k++) before += warp_sums[k];
+  return before + inc - v;
+}
+
+__global__ void __launch_bounds__(RS_THREADS) radix_digit_bases_kernel(uint32_t *hist) {
+  __shared__ uint32_t warp_sums[RS_WARPS];
+  uint32_t *h = hist + blockIdx.x * RS_BINS;
+  h[threadIdx.x] = block_exclusive_256(h[threadIdx.x], warp_sums);
 }
 
 template <bool HAS_VALS>
 __global__ void __launch_bounds__(RS_THREADS)
-    radix_scatter_kernel(const uint64_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
-                         uint64_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n, int shift,
-                         const uint32_t *__restrict__ offsets, uint32_t n_tiles) {
+    radix_pass_kernel(const uint64_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
+                      uint64_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n, int shift,
+                      const uint32_t *__restrict__ digit_base, volatile uint64_t *status, uint32_t *ticket) {
   __shared__ uint32_t cnt[RS_WARPS][RS_BINS];
+  __shared__ uint32_t dstart[RS_BINS];  // first tile-local position of a digit
+  __shared__ uint32_t gbase[RS_BINS];   // output position of tile-local position 0 of a digit
+  __shared__ uint64_t stage[RS_TILE];
+  __shared__ uint32_t warp_sums[RS_WARPS];
+  __shared__ uint32_t s_tile;
   const int w = threadIdx.x >> 5;
   const uint32_t lane = lane_id();
   const uint32_t lt = (1u << lane) - 1u;
+  if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);  // tiles start in ticket order: look-back cannot starve
 #pragma unroll
   for (int k = 0; k < RS_WARPS; k++) cnt[k][threadIdx.x] = 0;
   __syncthreads();
+  const uint32_t tile = s_tile;
+  const uint64_t tile_base = (uint64_t)tile * RS_TILE;
+  const uint64_t warp_base = tile_base + (uint64_t)w * (32 * RS_ITEMS);
 
-  const uint64_t warp_base = (uint64_t)blockIdx.x * RS_TILE + (uint64_t)w * (32 * RS_ITEMS);
   uint64_t key[RS_ITEMS];
   uint32_t val[RS_ITEMS];
-  // phase 1: load, per-warp digit totals
+  uint16_t lpos[RS_ITEMS];
 #pragma unroll
   for (int j = 0; j < RS_ITEMS; j++) {
     uint64_t i = warp_base + (uint64_t)j * 32 + lane;
-    bool ok = i < n;
-    key[j] = ok ? ld_stream_u64(keys_in + i) : 0ull;
-    if (HAS_VALS) val[j] = ok ? vals_in[i] : 0u;
+    key[j] = i < n ? ld_stream_u64(keys_in + i) : 0ull;
+  }
+  if (HAS_VALS) {
+#pragma unroll
+    for (int j = 0; j < RS_ITEMS; j++) {
+      uint64_t i = warp_base + (uint64_t)j * 32 + lane;
+      val[j] = i < n ? __ldcs(vals_in + i) : 0u;
+    }
+  }
+  // rank of every element among the elements of its digit in this warp's sub-tile
+#pragma unroll
+  for (int j = 0; j < RS_ITEMS; j++) {
+    bool ok = warp_base + (uint64_t)j * 32 + lane < n;
     uint32_t dig = ok ? ((uint32_t)(key[j] >> shift) & 255u) : 256u;
     uint32_t peers = __match_any_sync(0xffffffffu, dig);
-    if (ok && (peers & lt) == 0) cnt[w][dig] += __popc(peers);  // one leader per digit
+    uint32_t before = ok ? cnt[w][dig] : 0u;
     __syncwarp();
+    if (ok && (peers & lt) == 0) cnt[w][dig] = before + __popc(peers);  // one leader per digit
+    __syncwarp();
+    lpos[j] = (uint16_t)(before + __popc(peers & lt));
   }
   __syncthreads();
-  // per digit: global base of this tile's run, then exclusive prefix over the warps
+  // thread d: digit d of this tile
   {
-    uint32_t d = threadIdx.x;
-    uint32_t run = offsets[(uint64_t)d * n_tiles + blockIdx.x];
+    const uint32_t d = threadIdx.x;
+    uint32_t total = 0;
 #pragma unroll
     for (int k = 0; k < RS_WARPS; k++) {
       uint32_t c = cnt[k][d];
-      cnt[k][d] = run;
-      run += c;
+      cnt[k][d] = total;
+      total += c;
+    }
+    volatile uint64_t *mine = status + (uint64_t)tile * RS_BINS + d;
+    *mine = (tile == 0 ? RS_INCLUSIVE : RS_AGGREGATE) | total;
+    uint32_t local = block_exclusive_256(total, warp_sums);
+    dstart[d] = local;
+    uint32_t preceding = 0;
+    if (tile > 0) {
+      for (uint32_t t = tile - 1;; t--) {
+        uint64_t v;
+        do {
+          v = status[(uint64_t)t * RS_BINS + d];
+        } while (v == 0);
+        preceding += (uint32_t)v;
+        if (v & RS_INCLUSIVE) break;
+      }
+      *mine = RS_INCLUSIVE | (uint64_t)(preceding + total);
+    }
+    gbase[d] = digit_base[d] + preceding - local;
+  }
+  __syncthreads();
+  // reorder in shared memory, then every digit run goes out as consecutive addresses
+#pragma unroll
+  for (int j = 0; j < RS_ITEMS; j++) {
+    bool ok = warp_base + (uint64_t)j * 32 + lane < n;
+    if (ok) {
+      uint32_t dig = (uint32_t)(key[j] >> shift) & 255u;
+      uint32_t p = dstart[dig] + cnt[w][dig] + lpos[j];
+      stage[p] = key[j];
+      lpos[j] = (uint16_t)p;
     }
   }
   __syncthreads();
-  // phase 2: stable rank inside the warp strip, scatter
+  const uint32_t in_tile = (uint32_t)min((uint64_t)RS_TILE, n - tile_base);
+  uint32_t out[RS_ITEMS];
 #pragma unroll
-  for (int j = 0; j < RS_ITEMS; j++) {
-    uint64_t i = warp_base + (uint64_t)j * 32 + lane;
-    bool ok = i < n;
-    uint32_t dig = ok ? ((uint32_t)(key[j] >> shift) & 255u) : 256u;
-    uint32_t peers = __match_any_sync(0xffffffffu, dig);
-    uint32_t rank = __popc(peers & lt);
-    uint32_t pos = 0;
-    if (ok) {
-      pos = cnt[w][dig] + rank;
+  for (int k = 0; k < RS_ITEMS; k++) {
+    uint32_t idx = k * RS_THREADS + threadIdx.x;
+    if (idx < in_tile) {
+      uint64_t kk = stage[idx];
+      out[k] = gbase[(uint32_t)(kk >> shift) & 255u] + idx;
+      keys_out[out[k]] = kk;
     }
-    __syncwarp();
-    if (ok && rank == 0) cnt[w][dig] += __popc(peers);
-    __syncwarp();
-    if (ok) {
-      keys_out[pos] = key[j];
-      if (HAS_VALS) vals_out[pos] = val[j];
+  }
+  if (HAS_VALS) {
+    uint32_t *sv = reinterpret_cast<uint32_t *>(stage);
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < RS_ITEMS; j++)
+      if (warp_base + (uint64_t)j * 32 + lane < n) sv[lpos[j]] = val[j];
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; k++) {
+      uint32_t idx = k * RS_THREADS + threadIdx.x;
+      if (idx < in_tile) vals_out[out[k]] = sv[idx];
     }
   }
 }
 
 int radix_sort_u64(uint64_t *keys[2], uint32_t *vals[2], uint64_t n, int end_bit, Scratch &scratch,
                    Scratch &scan_scratch, cudaStream_t stream, int *launches) {
+  (void)scan_scratch;
   if (n <= 1 || end_bit <= 0) return 0;
   if (n >= 0xFFFFFFFFull) throw CudaError{"radix_sort_u64: more than 2^32-1 elements"};
-  uint32_t n_tiles = (uint32_t)((n + RS_TILE - 1) / RS_TILE);
-  uint64_t hist_n = (uint64_t)RS_BINS * n_tiles;
-  uint32_t *hist = (uint32_t *)scratch.get(hist_n * sizeof(uint32_t));
+  const int passes = (end_bit + 7) / 8;
+  const uint32_t n_tiles = (uint32_t)((n + RS_TILE - 1) / RS_TILE);
+  // scratch: [status: n_tiles*256 u64][tickets: 8 u32 (one per pass)][hist: passes*256 u32]
+  const size_t status_bytes = (size_t)n_tiles * RS_BINS * sizeof(uint64_t);
+  const size_t tail_bytes = (RS_MAX_PASSES + RS_MAX_PASSES * RS_BINS) * sizeof(uint32_t);
+  char *base = (char *)scratch.get(status_bytes + tail_bytes);
+  uint64_t *status = (uint64_t *)base;
+  uint32_t *tickets = (uint32_t *)(base + status_bytes);
+  uint32_t *hist = tickets + RS_MAX_PASSES;
+  HUMID_CUDA(cudaMemsetAsync(tickets, 0, tail_bytes, stream));
+  unsigned hist_grid = (unsigned)std::min<uint64_t>((n + RS_THREADS - 1) / RS_THREADS, 148 * 8);
+  radix_digit_hist_kernel<<<hist_grid, RS_THREADS, 0, stream>>>(keys[0], n, passes, hist);
+  radix_digit_bases_kernel<<<passes, RS_THREADS, 0, stream>>>(hist);
+  *launches += 2;
   int cur = 0;
   const bool has_vals = vals && vals[0];
-  for (int shift = 0; shift < end_bit; shift += 8) {
-    radix_hist_kernel<<<n_tiles, RS_THREADS, 0, stream>>>(keys[cur], n, shift, hist, n_tiles);
-    *launches += 1 + exclusive_scan_u32(hist, hist, hist_n, nullptr, scan_scratch, stream);
+  for (int p = 0; p < passes; p++) {
+    HUMID_CUDA(cudaMemsetAsync(status, 0, status_bytes, stream));
     if (has_vals)
-      radix_scatter_kernel<true><<<n_tiles, RS_THREADS, 0, stream>>>(keys[cur], vals[cur], keys[cur ^ 1],
-                                                                    vals[cur ^ 1], n, shift, hist, n_tiles);
+      radix_pass_kernel<true><<<n_tiles, RS_THREADS, 0, stream>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n,
+                                                                  8 * p, hist + p * RS_BINS, status, tickets + p);
     else
-      radix_scatter_kernel<false><<<n_tiles, RS_THREADS, 0, stream>>>(keys[cur], nullptr, keys[cur ^ 1], nullptr, n,
-                                                                     shift, hist, n_tiles);
+      radix_pass_kernel<false><<<n_tiles, RS_THREADS, 0, stream>>>(keys[cur], nullptr, keys[cur ^ 1], nullptr, n, 8 * p,
+                                                                   hist + p * RS_BINS, status, tickets + p);
     *launches += 1;
     cur ^= 1;
   }

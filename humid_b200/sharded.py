@@ -356,14 +356,32 @@ class ShardedDedup:
         return out.cpu().numpy().reshape(self.world, len(vals))
 
     # -- everything between readData and the outputs ------------------------------------------------
+    def _mark(self, name):
+        """HUMID_SHARD_PHASES=1: wall time per phase with a device synchronize at each mark (diagnostic)."""
+        if not self._phases_on:
+            return
+        import time
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+        now = time.perf_counter()
+        self.phases.append((name, (now - self._t_mark) * 1e3))
+        self._t_mark = time.perf_counter()
+
     def finalize(self):
         eng, W, me, g = self.eng, self.world, self.rank, self.comm
         dev = eng.device
+        import os, time
+        self._phases_on = os.environ.get("HUMID_SHARD_PHASES") == "1"
+        self.phases = []
+        if self._phases_on:
+            torch.cuda.synchronize()
+            self._t_mark = time.perf_counter()
         # tuple offsets: rank order == input order
         n_tuples = self._gather_ints(self.n_local)[:, 0]
         offs = np.concatenate([[0], np.cumsum(n_tuples)])
         self.tuple_offset, self.n_total = int(offs[me]), int(offs[-1])
         usable = eng.begin(self.tuple_offset)
+        self._mark("offsets+begin")
 
         # splitters: an equal number of evenly spaced tuple keys from every rank
         samp = eng.sample_keys(SAMPLES_PER_RANK)
@@ -380,47 +398,61 @@ class ShardedDedup:
         else:
             splitters = np.zeros(max(W - 1, 0), dtype=np.uint64)
         self.splitters = splitters
+        self._mark("splitters")
 
         # tuples to the owners of their key range; each owner then runs the single-GPU word stages
         send = eng.partition(splitters, W)
         k, ix = eng.export_tuples(send)
+        self._mark("partition+export")
         rk, recv = all_to_all_v(g, k, send)
         rix = all_to_all_fixed(g, ix, send, recv)
         self._sent_index, self._send_counts, self._recv_counts = ix, send, recv
+        self._mark("tuples all-to-all")
         n_shard = eng.import_tuples(rk, rix)
+        self._mark("import_tuples")
         del k, rk, rix
         info = self._gather_ints(n_shard, usable)
         bases = np.concatenate([[0], np.cumsum(info[:, 0])]).astype(np.uint64)
         self.n_words_total, self.usable_total = int(bases[-1]), int(info[:, 1].sum())
         eng.set_layout(me, W, splitters, bases)
+        self._mark("layout")
 
         # neighbour search: local look-ups + routed queries
         qcounts = eng.probe_count(W)
         qk, qs = eng.probe(qcounts)
+        self._mark("probe")
         rqk, qrecv = all_to_all_v(g, qk, qcounts)
         rqs = all_to_all_fixed(g, qs, qcounts, qrecv)
+        self._mark("queries all-to-all")
         ans = eng.answer(rqk, rqs)
+        self._mark("answer")
         back = all_to_all_fixed(g, ans, qrecv, qcounts)
+        self._mark("answers all-to-all")
         eng.apply_answers(qs, back)
         n_entries = eng.build_rows()
+        self._mark("apply+rows")
 
         # clusters: components inside a shard are finished there; the ones that cross shards
         # ("open") are gathered whole and replayed identically on every shard
         n_open, n_open_e = eng.cluster_local()
+        self._mark("cluster_local")
         orank, ocount, ofirst, odeg, ocol = eng.export_open()
         sizes = self._gather_ints(n_open, n_open_e, n_shard)
         osz, esz = [int(x) for x in sizes[:, 0]], [int(x) for x in sizes[:, 1]]
         open_off = int(np.sum(sizes[:me, 0]))
+        self._mark("export_open+sizes")
         n_cl = eng.import_open(open_off, all_gather_v(g, orank, osz), all_gather_v(g, ocount, osz),
                                all_gather_v(g, ofirst, osz), all_gather_v(g, odeg, osz), all_gather_v(g, ocol, esz))
         ncl = self._gather_ints(n_cl)[:, 0]
         self.cluster_offsets = np.concatenate([[0], np.cumsum(ncl)])
         self.n_clusters_local = int(n_cl)
+        self._mark("open gather+import")
         ids = eng.assign_ids(int(self.cluster_offsets[me]))
         if hasattr(eng, "_sync"):
             eng._sync()
         g.all_reduce_sum(ids)
         eng.finish(ids, self.n_total, self.usable_total, self.n_words_total, int(self.cluster_offsets[-1]))
+        self._mark("ids+finish")
         self.word_sizes = [int(x) for x in sizes[:, 2]]
         self.queries_sent = int(np.sum(qcounts))
         self.open_words_total = int(np.sum(sizes[:, 0]))

@@ -109,6 +109,18 @@ def test_against_oracle(ci, R, kw):
     assert_same_as_oracle(dd, r, R)
 
 
+def test_against_oracle_millions():
+    """Enough words that the sorts, scans and tables span more tiles than are resident at once."""
+    cfg = baseline_config(1, 4_000_000)
+    s = Synth(cfg)
+    chars = s.word_chars()
+    hdr, take = s.layout()
+    seg_take = ([hdr] if hdr else []) + take
+    r = oracle.Result(oracle.pack_words(chars, seg_take), cfg.word_length, cfg.distance, cfg.edit, cfg.maximum)
+    dd = run_gpu(chars, seg_take, cfg.word_length, cfg.distance, cfg.edit, cfg.maximum, batches=3)
+    assert_same_as_oracle(dd, r, chars.shape[0])
+
+
 def _chars(words):
     return np.frombuffer("".join(words).encode(), dtype=np.uint8).reshape(len(words), -1).copy()
 
