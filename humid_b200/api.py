@@ -36,7 +36,7 @@ class Config(C.Structure):
     _fields_ = [
         ("word_length", C.c_uint32), ("distance", C.c_uint32), ("n_segments", C.c_uint32),
         ("seg_take", C.c_uint32 * MAX_SEGMENTS), ("edit", C.c_uint8), ("maximum", C.c_uint8),
-        ("reserved", C.c_uint8 * 2), ("device", C.c_int32), ("expected_tuples", C.c_uint64),
+        ("defer_table", C.c_uint8), ("reserved", C.c_uint8), ("device", C.c_int32), ("expected_tuples", C.c_uint64),
     ]
 
 
@@ -95,7 +95,8 @@ class Dedup:
     """
 
     def __init__(self, word_length: int = 24, distance: int = 1, seg_take: Sequence[int] = (12, 12),
-                 edit: bool = False, maximum: bool = False, device: int = -1, expected_tuples: int = 0):
+                 edit: bool = False, maximum: bool = False, device: int = -1, expected_tuples: int = 0,
+                 defer_table: bool = False):
         self._L = load_library()
         self._h = C.c_void_p()
         cfg = Config()
@@ -108,6 +109,7 @@ class Dedup:
             cfg.seg_take[i] = t
         cfg.edit, cfg.maximum, cfg.device = int(bool(edit)), int(bool(maximum)), int(device)
         cfg.expected_tuples = int(expected_tuples)
+        cfg.defer_table = 1 if defer_table else 0
         self.word_length, self.n_segments = cfg.word_length, cfg.n_segments
         rc = self._L.humid_gpu_create(C.byref(cfg), C.byref(self._h))
         if rc != 0:

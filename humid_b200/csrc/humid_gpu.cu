@@ -59,6 +59,11 @@ int humid_gpu_create(const humid_gpu_config *cfg, humid_gpu **out) {
     if (cfg->device >= 0) HUMID_CUDA(cudaSetDevice(cfg->device));
     HUMID_CUDA(cudaGetDevice(&s.device));
     HUMID_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    HUMID_CUDA(cudaStreamCreateWithFlags(&s.copy_stream, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; b++) {
+      HUMID_CUDA(cudaEventCreateWithFlags(&s.ev_copied[b], cudaEventDisableTiming));
+      HUMID_CUDA(cudaEventCreateWithFlags(&s.ev_consumed[b], cudaEventDisableTiming));
+    }
     s.counters.ensure(64);
     HUMID_CUDA(cudaMemsetAsync(s.counters.p, 0, 64 * sizeof(unsigned long long), s.stream));
     if (cfg->expected_tuples) s.tuple_key.ensure(cfg->expected_tuples);
@@ -79,7 +84,15 @@ void humid_gpu_destroy(humid_gpu *h) {
   cudaSetDevice(s.device);
   if (s.stream) cudaStreamSynchronize(s.stream);
   clear_stats(s);
-  s.tuple_key.release(); s.stage_chars.release(); s.stage_seg_len.release(); s.counters.release();
+  if (s.copy_stream) cudaStreamSynchronize(s.copy_stream);
+  for (int b = 0; b < 2; b++) {
+    s.stage_chars[b].release();
+    s.stage_seg_len[b].release();
+    if (s.ev_copied[b]) cudaEventDestroy(s.ev_copied[b]);
+    if (s.ev_consumed[b]) cudaEventDestroy(s.ev_consumed[b]);
+  }
+  if (s.copy_stream) cudaStreamDestroy(s.copy_stream);
+  s.tuple_key.release(); s.counters.release();
   s.slots.release(); s.word_key.release(); s.key_alt.release(); s.word_slot.release(); s.slot_alt.release();
   s.word_count.release(); s.word_first.release(); s.entries.release(); s.entries_alt.release();
   s.entry_val.release(); s.entry_val_alt.release(); s.row_ptr.release(); s.deg.release(); s.col.release();
@@ -108,8 +121,12 @@ int humid_gpu_reset(humid_gpu *h) {
   return guarded(h, [&] {
     State &s = h->s;
     HUMID_CUDA(cudaSetDevice(s.device));
+    HUMID_CUDA(cudaStreamSynchronize(s.copy_stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     clear_stats(s);
+    s.early_table = false;
+    s.early_inserted = 0;
+    s.stage_busy[0] = s.stage_busy[1] = false;
     s.n_tuples = s.usable = s.unique = s.n_entries = s.n_clusters = 0;
     s.finalized = false;
     s.shard_mode = false;
@@ -140,21 +157,36 @@ static int add_batch_impl(humid_gpu *h, const uint8_t *chars, const uint16_t *se
     s.tuple_key.grow(s.n_tuples + n, s.n_tuples, s.stream);
     const uint8_t *d_chars = chars;
     const uint16_t *d_len = seg_len;
+    const int b = (int)(s.n_batches & 1);
     if (!on_device) {
-      s.stage_chars.ensure(n * wl);
-      HUMID_CUDA(cudaMemcpyAsync(s.stage_chars.p, chars, n * wl, cudaMemcpyHostToDevice, s.stream));
-      d_chars = s.stage_chars.p;
-      if (seg_len) {
-        s.stage_seg_len.ensure(n * ns);
-        HUMID_CUDA(cudaMemcpyAsync(s.stage_seg_len.p, seg_len, n * ns * sizeof(uint16_t), cudaMemcpyHostToDevice,
-                                   s.stream));
-        d_len = s.stage_seg_len.p;
+      // upload on the copy stream into staging buffer b; the kernels that read that buffer two
+      // batches ago must be done, and this batch's kernels wait for the upload
+      if (s.stage_busy[b]) HUMID_CUDA(cudaStreamWaitEvent(s.copy_stream, s.ev_consumed[b], 0));
+      if (s.stage_chars[b].cap < n * wl || (seg_len && s.stage_seg_len[b].cap < n * ns)) {
+        HUMID_CUDA(cudaStreamSynchronize(s.stream));  // reallocation: nothing may still read the old buffer
+        s.stage_chars[b].ensure(n * wl);
+        if (seg_len) s.stage_seg_len[b].ensure(n * ns);
       }
+      HUMID_CUDA(cudaMemcpyAsync(s.stage_chars[b].p, chars, n * wl, cudaMemcpyHostToDevice, s.copy_stream));
+      d_chars = s.stage_chars[b].p;
+      if (seg_len) {
+        HUMID_CUDA(cudaMemcpyAsync(s.stage_seg_len[b].p, seg_len, n * ns * sizeof(uint16_t), cudaMemcpyHostToDevice,
+                                   s.copy_stream));
+        d_len = s.stage_seg_len[b].p;
+      }
+      HUMID_CUDA(cudaEventRecord(s.ev_copied[b], s.copy_stream));
+      HUMID_CUDA(cudaStreamWaitEvent(s.stream, s.ev_copied[b], 0));
     }
-    // makeWord: n ASCII bytes in, one 8-byte key out
+    // makeWord: n ASCII bytes in, one 8-byte key out; then Trie::add when the table is already sized
     stage_pack(s, d_chars, d_len, first, n);
+    stage_early_insert(s, first, n);
+    if (!on_device) {
+      HUMID_CUDA(cudaEventRecord(s.ev_consumed[b], s.stream));
+      s.stage_busy[b] = true;
+      s.n_batches++;
+    }
     s.n_tuples += n;
-    if (!on_device) HUMID_CUDA(cudaStreamSynchronize(s.stream));  // the caller may reuse its buffers
+    if (!on_device) HUMID_CUDA(cudaEventSynchronize(s.ev_copied[b]));  // the caller may reuse its buffers
   });
 }
 

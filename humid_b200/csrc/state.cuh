@@ -66,8 +66,17 @@ struct State {
   // pass 1
   uint64_t n_tuples = 0;
   DevBuf<uint64_t> tuple_key;
-  DevBuf<uint8_t> stage_chars;     // H2D staging for add_batch
-  DevBuf<uint16_t> stage_seg_len;
+  // H2D staging for add_batch: two buffers, uploads on their own stream so that batch i+1
+  // travels while batch i is packed and counted
+  DevBuf<uint8_t> stage_chars[2];
+  DevBuf<uint16_t> stage_seg_len[2];
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
+  bool stage_busy[2] = {false, false};
+  uint64_t n_batches = 0;
+  // words counted during add_batch (expected_tuples given): tuples [0, early_inserted) are in the table
+  bool early_table = false;
+  uint64_t early_inserted = 0;
   DevBuf<unsigned long long> counters;  // [0] usable, [1] unique, [2] entries, [3..] misc
   uint64_t usable = 0, unique = 0, n_entries = 0, n_clusters = 0;
 
@@ -174,6 +183,7 @@ struct Timed {
 // ---- stage launchers (each returns the number of kernels it launched) --------------------
 int stage_pack(State &s, const uint8_t *d_chars, const uint16_t *d_seg_len, uint64_t first, uint64_t n);
 int stage_build_table(State &s, bool with_filter = true);  // insert + compact + sort + rank columns (+ filter)
+int stage_early_insert(State &s, uint64_t first, uint64_t n);  // add_batch: count tuples [first, first+n)
 int stage_build_filter(State &s);      // fingerprint filter over word_key[0..unique)
 int stage_neighbours_hamming(State &s);
 int stage_neighbours_edit(State &s);

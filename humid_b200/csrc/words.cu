@@ -116,13 +116,13 @@ __global__ void table_clear_kernel(Slot *slots, uint64_t cap) {
 
 __global__ void __launch_bounds__(256)
     table_insert_kernel(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ tuple_index,
-                        uint64_t n_tuples, Slot *slots, uint64_t mask) {
+                        uint64_t n_tuples, Slot *slots, uint64_t mask, uint32_t index_base) {
   uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n_tuples) return;
   uint64_t key = ld_stream_u64(keys + t);
   if (key == KEY_INVALID) return;
   // position of the tuple in the job's input order (shard mode: tuples arrive from other ranks)
-  const uint32_t ti = tuple_index ? tuple_index[t] : (uint32_t)t;
+  const uint32_t ti = tuple_index ? tuple_index[t] : index_base + (uint32_t)t;
   uint64_t idx = mix64(key) & mask;
   uint32_t seen_first = 0xFFFFFFFFu;
   while (true) {
@@ -241,6 +241,42 @@ int stage_build_filter(State &s) {
   return 1;
 }
 
+static uint64_t table_capacity_for(uint64_t tuples) {
+  uint64_t cap = 1024;
+  while (4 * cap < 5 * tuples) cap <<= 1;  // load factor <= 0.8 if every tuple were distinct, ~0.3 typically
+  if (cap > (1ull << 32)) throw CudaError{"word table would exceed 2^32 slots"};
+  return cap;
+}
+
+static int table_clear(State &s, uint64_t cap) {
+  s.table_cap = cap;
+  s.slots.ensure(cap);
+  Timed t(s, "table_clear", cap, cap * 16);
+  table_clear_kernel<<<grid_for(cap, 256), 256, 0, s.stream>>>(s.slots.p, cap);
+  return 1;
+}
+
+int stage_early_insert(State &s, uint64_t first, uint64_t n) {
+  if (s.cfg.defer_table || s.cfg.expected_tuples == 0) return 0;
+  int k = 0;
+  if (first == 0) {
+    k += table_clear(s, table_capacity_for(s.cfg.expected_tuples));
+    s.early_table = true;
+    s.early_inserted = 0;
+  }
+  if (!s.early_table || first != s.early_inserted) return k;
+  if (first + n > s.cfg.expected_tuples) {  // outgrew the hint: finalize recounts into a larger table
+    s.early_table = false;
+    return k;
+  }
+  // key in (8) + slot key (8) + count RMW (8) + first RMW (8)
+  Timed t(s, "table_insert", n, n * 32);
+  table_insert_kernel<<<grid_for(n, 256), 256, 0, s.stream>>>(s.tuple_key.p + first, nullptr, n, s.slots.p,
+                                                              s.table_cap - 1, (uint32_t)first);
+  s.early_inserted = first + n;
+  return k + 1;
+}
+
 int stage_build_table(State &s, bool with_filter) {
   int k = 0;
   const uint64_t *keys = s.tuple_key.p;
@@ -255,22 +291,16 @@ int stage_build_table(State &s, bool with_filter) {
     HUMID_CUDA(cudaMemcpyAsync(&s.usable, s.counters.p + 0, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
   }
-  uint64_t cap = 1024;
-  while (4 * cap < 5 * s.usable) cap <<= 1;  // load factor <= 0.8 if every tuple were distinct, ~0.3 typically
-  if (cap > (1ull << 32)) throw CudaError{"word table would exceed 2^32 slots"};
-  s.table_cap = cap;
-  s.slots.ensure(cap);
-  {
-    Timed t(s, "table_clear", cap, cap * 16);
-    table_clear_kernel<<<grid_for(cap, 256), 256, 0, s.stream>>>(s.slots.p, cap);
+  const bool counted = !s.src_keys && s.early_table && s.early_inserted == s.n_tuples && s.n_tuples > 0;
+  if (!counted) {
+    k += table_clear(s, table_capacity_for(s.usable));
+    if (n_in) {
+      Timed t(s, "table_insert", n_in, n_in * 8 + s.usable * 24);
+      table_insert_kernel<<<grid_for(n_in, 256), 256, 0, s.stream>>>(keys, index, n_in, s.slots.p, s.table_cap - 1, 0u);
+      k++;
+    }
   }
-  k++;
-  if (n_in) {
-    // key in (8) + slot key (8) + count RMW (8) + first RMW (8)
-    Timed t(s, "table_insert", n_in, n_in * 8 + s.usable * 24);
-    table_insert_kernel<<<grid_for(n_in, 256), 256, 0, s.stream>>>(keys, index, n_in, s.slots.p, cap - 1);
-    k++;
-  }
+  const uint64_t cap = s.table_cap;
   // distinct words cannot outnumber usable tuples
   s.word_key.ensure(s.usable + 1);
   s.key_alt.ensure(s.usable + 1);

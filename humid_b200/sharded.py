@@ -72,7 +72,7 @@ class CudaShardEngine(api.Dedup):
     """The C ABI (include/humid_gpu.h + include/humid_gpu_shard.h) on one GPU."""
 
     def __init__(self, device: int = 0, **kw):
-        super().__init__(device=device, **kw)
+        super().__init__(device=device, defer_table=True, **kw)  # words are counted by their owners
         _bind(self._L)
         self.device = torch.device("cuda", device)
 

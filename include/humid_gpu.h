@@ -52,9 +52,14 @@ typedef struct {
   uint32_t seg_take[HUMID_MAX_SEGMENTS];
   uint8_t edit;                          /* -e: Levenshtein instead of Hamming */
   uint8_t maximum;                       /* -x: maximum instead of directional clusters */
-  uint8_t reserved[2];
+  uint8_t defer_table;                   /* 1: never count words during add_batch (shard hosts) */
+  uint8_t reserved;
   int32_t device;                        /* CUDA device ordinal, -1 = current */
-  uint64_t expected_tuples;              /* capacity hint, 0 = grow on demand */
+  uint64_t expected_tuples;              /* capacity hint, 0 = grow on demand.  With a hint the word
+                                            table is sized up front and every batch is counted into it
+                                            as it arrives (Trie::add per read, src/humid.cc:69-77), so
+                                            that work overlaps the next batch's upload; a job that
+                                            outgrows the hint is recounted at finalize. */
 } humid_gpu_config;
 
 int humid_gpu_abi_version(void);

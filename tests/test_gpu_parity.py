@@ -121,6 +121,26 @@ def test_against_oracle_millions():
     assert_same_as_oracle(dd, r, chars.shape[0])
 
 
+@pytest.mark.parametrize("hint", [30000, 100000, 17000, 1])
+def test_words_counted_while_batches_arrive(hint):
+    """expected_tuples sizes the table up front and add_batch counts into it; a job that outgrows
+    the hint (17000, 1) is recounted at finalize.  Same result either way, also after a reset."""
+    cfg = baseline_config(1, 30000)
+    s = Synth(cfg)
+    chars = s.word_chars()
+    hdr, take = s.layout()
+    seg_take = ([hdr] if hdr else []) + take
+    r = oracle.Result(oracle.pack_words(chars, seg_take), cfg.word_length, cfg.distance, cfg.edit, cfg.maximum)
+    dd = api.Dedup(word_length=cfg.word_length, distance=cfg.distance, seg_take=seg_take, edit=cfg.edit,
+                   maximum=cfg.maximum, expected_tuples=hint)
+    for rounds in range(2):
+        for lo in range(0, 30000, 7000):
+            dd.add_batch(chars[lo:lo + 7000])
+        dd.finalize()
+        assert_same_as_oracle(dd, r, 30000)
+        dd.reset()
+
+
 def _chars(words):
     return np.frombuffer("".join(words).encode(), dtype=np.uint8).reshape(len(words), -1).copy()
 
