@@ -187,11 +187,39 @@ __global__ void __launch_bounds__(RS_THREADS) radix_digit_bases_kernel(uint32_t 
   h[threadIdx.x] = block_exclusive_256(h[threadIdx.x], warp_sums);
 }
 
-template <bool HAS_VALS>
+// digit of a key in a sort pass / in the slot partition of the word table (top 8 bits of the home slot)
+struct ShiftDigit {
+  int shift;
+  __device__ __forceinline__ uint32_t operator()(uint64_t key) const { return (uint32_t)(key >> shift) & 255u; }
+};
+struct SlotDigit {
+  uint64_t mask;
+  int shift;
+  __device__ __forceinline__ uint32_t operator()(uint64_t key) const {
+    return (uint32_t)((mix64(key) & mask) >> shift) & 255u;
+  }
+};
+
+template <class Digit>
+__global__ void __launch_bounds__(RS_THREADS) digit_hist_kernel(const uint64_t *__restrict__ keys, uint64_t n,
+                                                                Digit digit_of, uint32_t *__restrict__ hist) {
+  __shared__ uint32_t h[RS_BINS];
+  h[threadIdx.x] = 0;
+  __syncthreads();
+  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+  for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride)
+    atomicAdd(&h[digit_of(ld_stream_u64(keys + i))], 1u);
+  __syncthreads();
+  if (h[threadIdx.x]) atomicAdd(&hist[threadIdx.x], h[threadIdx.x]);
+}
+
+// HAS_VALS with vals_in == nullptr: the value of element i is index_base + i.
+template <bool HAS_VALS, class Digit>
 __global__ void __launch_bounds__(RS_THREADS)
     radix_pass_kernel(const uint64_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
-                      uint64_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n, int shift,
-                      const uint32_t *__restrict__ digit_base, volatile uint64_t *status, uint32_t *ticket) {
+                      uint64_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n, Digit digit_of,
+                      const uint32_t *__restrict__ digit_base, volatile uint64_t *status, uint32_t *ticket,
+                      uint32_t index_base) {
   __shared__ uint32_t cnt[RS_WARPS][RS_BINS];
   __shared__ uint32_t dstart[RS_BINS];  // first tile-local position of a digit
   __shared__ uint32_t gbase[RS_BINS];   // output position of tile-local position 0 of a digit
@@ -221,14 +249,14 @@ __global__ void __launch_bounds__(RS_THREADS)
 #pragma unroll
     for (int j = 0; j < RS_ITEMS; j++) {
       uint64_t i = warp_base + (uint64_t)j * 32 + lane;
-      val[j] = i < n ? __ldcs(vals_in + i) : 0u;
+      val[j] = i >= n ? 0u : vals_in ? __ldcs(vals_in + i) : index_base + (uint32_t)i;
     }
   }
   // rank of every element among the elements of its digit in this warp's sub-tile
 #pragma unroll
   for (int j = 0; j < RS_ITEMS; j++) {
     bool ok = warp_base + (uint64_t)j * 32 + lane < n;
-    uint32_t dig = ok ? ((uint32_t)(key[j] >> shift) & 255u) : 256u;
+    uint32_t dig = ok ? digit_of(key[j]) : 256u;
     uint32_t peers = __match_any_sync(0xffffffffu, dig);
     uint32_t before = ok ? cnt[w][dig] : 0u;
     __syncwarp();
@@ -271,7 +299,7 @@ __global__ void __launch_bounds__(RS_THREADS)
   for (int j = 0; j < RS_ITEMS; j++) {
     bool ok = warp_base + (uint64_t)j * 32 + lane < n;
     if (ok) {
-      uint32_t dig = (uint32_t)(key[j] >> shift) & 255u;
+      uint32_t dig = digit_of(key[j]);
       uint32_t p = dstart[dig] + cnt[w][dig] + lpos[j];
       stage[p] = key[j];
       lpos[j] = (uint16_t)p;
@@ -285,7 +313,7 @@ __global__ void __launch_bounds__(RS_THREADS)
     uint32_t idx = k * RS_THREADS + threadIdx.x;
     if (idx < in_tile) {
       uint64_t kk = stage[idx];
-      out[k] = gbase[(uint32_t)(kk >> shift) & 255u] + idx;
+      out[k] = gbase[digit_of(kk)] + idx;
       keys_out[out[k]] = kk;
     }
   }
@@ -329,15 +357,42 @@ int radix_sort_u64(uint64_t *keys[2], uint32_t *vals[2], uint64_t n, int end_bit
     HUMID_CUDA(cudaMemsetAsync(status, 0, status_bytes, stream));
     if (has_vals)
       radix_pass_kernel<true><<<n_tiles, RS_THREADS, 0, stream>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n,
-                                                                  8 * p, hist + p * RS_BINS, status, tickets + p);
+                                                                  ShiftDigit{8 * p}, hist + p * RS_BINS, status,
+                                                                  tickets + p, 0u);
     else
-      radix_pass_kernel<false><<<n_tiles, RS_THREADS, 0, stream>>>(keys[cur], nullptr, keys[cur ^ 1], nullptr, n, 8 * p,
-                                                                   hist + p * RS_BINS, status, tickets + p);
+      radix_pass_kernel<false><<<n_tiles, RS_THREADS, 0, stream>>>(keys[cur], nullptr, keys[cur ^ 1], nullptr, n,
+                                                                   ShiftDigit{8 * p}, hist + p * RS_BINS, status,
+                                                                   tickets + p, 0u);
     *launches += 1;
     cur ^= 1;
   }
   HUMID_CUDA(cudaGetLastError());
   return cur;
+}
+
+int partition_by_slot_u64(const uint64_t *keys_in, const uint32_t *vals_in, uint32_t index_base, uint64_t *keys_out,
+                          uint32_t *vals_out, uint64_t n, uint64_t slot_mask, Scratch &scratch, cudaStream_t stream,
+                          int *launches) {
+  if (n == 0) return 0;
+  if (n >= 0xFFFFFFFFull) throw CudaError{"partition_by_slot_u64: more than 2^32-1 elements"};
+  int bits = 0;
+  while ((slot_mask >> bits) != 0) bits++;
+  const SlotDigit dg{slot_mask, bits > 8 ? bits - 8 : 0};
+  const uint32_t n_tiles = (uint32_t)((n + RS_TILE - 1) / RS_TILE);
+  const size_t status_bytes = (size_t)n_tiles * RS_BINS * sizeof(uint64_t);
+  const size_t tail_bytes = (RS_MAX_PASSES + RS_BINS) * sizeof(uint32_t);
+  char *base = (char *)scratch.get(status_bytes + tail_bytes);
+  uint32_t *tickets = (uint32_t *)(base + status_bytes);
+  uint32_t *hist = tickets + RS_MAX_PASSES;
+  HUMID_CUDA(cudaMemsetAsync(base, 0, status_bytes + tail_bytes, stream));
+  unsigned hist_grid = (unsigned)std::min<uint64_t>((n + RS_THREADS - 1) / RS_THREADS, 148 * 8);
+  digit_hist_kernel<<<hist_grid, RS_THREADS, 0, stream>>>(keys_in, n, dg, hist);
+  radix_digit_bases_kernel<<<1, RS_THREADS, 0, stream>>>(hist);
+  radix_pass_kernel<true><<<n_tiles, RS_THREADS, 0, stream>>>(keys_in, vals_in, keys_out, vals_out, n, dg, hist,
+                                                              (uint64_t *)base, tickets, index_base);
+  HUMID_CUDA(cudaGetLastError());
+  *launches += 3;
+  return 3;
 }
 
 }  // namespace humid

@@ -42,4 +42,12 @@ int exclusive_scan_u32(const uint32_t *in, uint32_t *out, uint64_t n, uint32_t *
 int radix_sort_u64(uint64_t *keys[2], uint32_t *vals[2], uint64_t n, int end_bit, Scratch &scratch,
                    Scratch &scan_scratch, cudaStream_t stream, int *launches);
 
+// One stable partition pass of (key, value) pairs by the top 8 bits of the key's home slot in an
+// open-addressing table with `slot_mask + 1` slots (slot = mix64(key) & slot_mask): afterwards
+// consecutive elements touch one 1/256 of the table, which then stays in L2 while it is worked on.
+// vals_in == nullptr: the value of element i is index_base + i.
+int partition_by_slot_u64(const uint64_t *keys_in, const uint32_t *vals_in, uint32_t index_base, uint64_t *keys_out,
+                          uint32_t *vals_out, uint64_t n, uint64_t slot_mask, Scratch &scratch, cudaStream_t stream,
+                          int *launches);
+
 }  // namespace humid

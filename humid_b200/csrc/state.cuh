@@ -82,6 +82,8 @@ struct State {
 
   // word table
   DevBuf<Slot> slots;
+  DevBuf<uint64_t> part_key;    // tuples grouped by table region (words.cu: table_insert)
+  DevBuf<uint32_t> part_index;
   uint64_t table_cap = 0;  // power of two
   DevBuf<uint4> filter;    // fingerprint buckets in front of the table (common.cuh)
   uint32_t filter_buckets = 0;

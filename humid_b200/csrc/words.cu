@@ -256,6 +256,29 @@ static int table_clear(State &s, uint64_t cap) {
   return 1;
 }
 
+// Trie::add for n tuples.  Large inputs are first grouped by the 1/256 of the table their home slot
+// lies in, so the random slot updates run against L2 instead of paying one DRAM line fill each.
+constexpr uint64_t PARTITION_MIN_TUPLES = 1ull << 21;
+static int table_insert(State &s, const uint64_t *keys, const uint32_t *index, uint64_t n, uint32_t index_base,
+                        uint64_t algo_bytes) {
+  int k = 0;
+  if (n >= PARTITION_MIN_TUPLES && s.table_cap * sizeof(Slot) > (64ull << 20)) {
+    s.part_key.ensure(n);
+    s.part_index.ensure(n);
+    Timed t(s, "table_partition", n, n * (8 + 12));
+    int launches = 0;
+    partition_by_slot_u64(keys, index, index_base, s.part_key.p, s.part_index.p, n, s.table_cap - 1, s.scratch,
+                          s.stream, &launches);
+    t.launches = launches;
+    k += launches;
+    keys = s.part_key.p;
+    index = s.part_index.p;
+  }
+  Timed t(s, "table_insert", n, algo_bytes);
+  table_insert_kernel<<<grid_for(n, 256), 256, 0, s.stream>>>(keys, index, n, s.slots.p, s.table_cap - 1, index_base);
+  return k + 1;
+}
+
 int stage_early_insert(State &s, uint64_t first, uint64_t n) {
   if (s.cfg.defer_table || s.cfg.expected_tuples == 0) return 0;
   int k = 0;
@@ -270,11 +293,9 @@ int stage_early_insert(State &s, uint64_t first, uint64_t n) {
     return k;
   }
   // key in (8) + slot key (8) + count RMW (8) + first RMW (8)
-  Timed t(s, "table_insert", n, n * 32);
-  table_insert_kernel<<<grid_for(n, 256), 256, 0, s.stream>>>(s.tuple_key.p + first, nullptr, n, s.slots.p,
-                                                              s.table_cap - 1, (uint32_t)first);
+  k += table_insert(s, s.tuple_key.p + first, nullptr, n, (uint32_t)first, n * 32);
   s.early_inserted = first + n;
-  return k + 1;
+  return k;
 }
 
 int stage_build_table(State &s, bool with_filter) {
@@ -294,11 +315,7 @@ int stage_build_table(State &s, bool with_filter) {
   const bool counted = !s.src_keys && s.early_table && s.early_inserted == s.n_tuples && s.n_tuples > 0;
   if (!counted) {
     k += table_clear(s, table_capacity_for(s.usable));
-    if (n_in) {
-      Timed t(s, "table_insert", n_in, n_in * 8 + s.usable * 24);
-      table_insert_kernel<<<grid_for(n_in, 256), 256, 0, s.stream>>>(keys, index, n_in, s.slots.p, s.table_cap - 1, 0u);
-      k++;
-    }
+    if (n_in) k += table_insert(s, keys, index, n_in, 0u, n_in * 8 + s.usable * 24);
   }
   const uint64_t cap = s.table_cap;
   // distinct words cannot outnumber usable tuples
