@@ -125,6 +125,18 @@ __device__ __forceinline__ uint32_t lookup_rank(const Lookup &lk, uint64_t key) 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
 
 // Grid size helper: enough CTAs to fill the 148 SMs a few times over, never more than needed.
+// Reserve `each` consecutive output slots per calling lane at a global cursor.  All lanes that
+// reach the call together share ONE atomic: a cursor is a single address, and returning atomics on
+// one address complete at well under 1 G/s, so a per-thread atomicAdd caps a kernel at that rate.
+__device__ __forceinline__ unsigned long long reserve_slots(unsigned long long *cursor, uint32_t each = 1u) {
+  const unsigned m = __activemask();
+  const uint32_t lane = threadIdx.x & 31u;
+  const int leader = __ffs(m) - 1;
+  unsigned long long base = 0;
+  if ((int)lane == leader) base = atomicAdd(cursor, (unsigned long long)each * __popc(m));
+  return __shfl_sync(m, base, leader) + (unsigned long long)each * __popc(m & ((1u << lane) - 1u));
+}
+
 inline unsigned grid_for(uint64_t items, unsigned block, unsigned per_thread = 1) {
   uint64_t per_block = (uint64_t)block * per_thread;
   uint64_t g = (items + per_block - 1) / per_block;

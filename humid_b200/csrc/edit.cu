@@ -30,7 +30,7 @@ constexpr int EDIT_MAX_D = 3;  // one deletion+insertion pair plus substitutions
 
 __device__ __forceinline__ void emit_candidate(uint64_t *cand, uint64_t cap, unsigned long long *counter, uint32_t q,
                                                uint32_t v) {
-  unsigned long long pos = atomicAdd(counter, 1ull);
+  const unsigned long long pos = reserve_slots(counter);
   if (pos < cap) cand[pos] = ((uint64_t)q << 32) | v;
 }
 
@@ -213,7 +213,7 @@ __global__ void __launch_bounds__(128)
     } else if (st == 9) {
       if (f.pos >= n && f.depth == n && f.lo < f.hi) {  // yield node->leaf
         const uint32_t v = ranks[f.lo];
-        unsigned long long p = atomicAdd(counter, 2ull);
+        const unsigned long long p = reserve_slots(counter, 2u);
         if (p + 2 <= cap) {
           entries[p] = (r << 32) | (uint32_t)r;       // own yield, in yield order
           entry_val[p] = v;
@@ -234,7 +234,7 @@ int stage_neighbours_edit(State &s) {
   if (U == 0) return 0;
   if (d > EDIT_MAX_D) throw CudaError{"edit distance > 3 is not supported (two deletion+insertion pairs)"};
   if (n + d + 2 > EDIT_STACK) throw CudaError{"word too long for the edit replay stack"};
-  int k = 0;
+  int k = stage_ensure_lookup(s);
   const Lookup lk = s.lookup();
 
   // phase 1: candidate pairs (with duplicates)

@@ -92,7 +92,7 @@ void humid_gpu_destroy(humid_gpu *h) {
     if (s.ev_consumed[b]) cudaEventDestroy(s.ev_consumed[b]);
   }
   if (s.copy_stream) cudaStreamDestroy(s.copy_stream);
-  s.tuple_key.release(); s.counters.release(); s.part_key.release(); s.part_index.release();
+  s.tuple_key.release(); s.counters.release(); s.part_key.release(); s.part_index.release(); s.word_flags.release();
   s.slots.release(); s.word_key.release(); s.key_alt.release(); s.word_slot.release(); s.slot_alt.release();
   s.word_count.release(); s.word_first.release(); s.entries.release(); s.entries_alt.release();
   s.entry_val.release(); s.entry_val_alt.release(); s.row_ptr.release(); s.deg.release(); s.col.release();
@@ -208,7 +208,7 @@ int humid_gpu_finalize(humid_gpu *h) {
     HUMID_CUDA(cudaSetDevice(s.device));
     const bool edit2 = s.cfg.edit && s.cfg.distance >= 2;
     if (s.shard_mode) throw CudaError{"finalize on a handle that is in shard mode"};
-    stage_build_table(s);
+    stage_build_table(s, false);  // key -> rank look-ups are set up by the stages that need them
     s.report_tuples = s.n_tuples;
     s.report_usable = s.usable;
     if (edit2) {

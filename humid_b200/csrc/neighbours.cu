@@ -1,24 +1,37 @@
-// K3 — Hamming neighbour search by variant enumeration + hash probe, and CSR construction.
+// K3 — Hamming neighbour search by block join (variant probing only for pathological groups),
+// and CSR construction.
 //
 // Replaces Trie::asymmetricHamming -> hamming_<4,NLeaf,false>
 // (lib/trie/src/trieFunctions.tcc:156-181) as called from findHammingNeighbours
 // (src/humid.cc:113-130).  The asymmetric search of query w yields every stored v with
 // v[p] >= w[p] at EVERY position and ham(w,v) <= d (component-wise dominance, not
-// lexicographic order); the caller links both directions.  So each unordered linked pair is
-// found exactly once, from its dominated member, by enumerating only UPWARD variants
-// (letters greater than w[p]).  list(L) ends up as all linked words in ascending rank
-// (dominated ones are pushed while L is the result of earlier queries, dominating ones by
-// L's own query, each group ascending), without duplicates.
+// lexicographic order); the caller links both directions.  So a pair of words is linked iff
+// they differ in 1..d positions and one of them dominates the other, and list(L) ends up as all
+// linked words in ascending rank, without duplicates.
+//
+// Block join: cut the n letters into d+1 blocks.  Two words that differ in at most d positions
+// agree on at least one whole block, so every linked pair sits inside one group of the words
+// ordered by that block ("first" = lowest block they agree on, which makes the pair unique).
+// Block 0 is the word's prefix: rank order already groups by it.  For every other block the
+// (key, rank) pairs are stably radix-sorted by the block's bits, which keeps rank order inside a
+// group.  One thread per word then walks forward through its group and tests each later member
+// with XOR / popcount.  Nothing is looked up: no hash probes, no false positives.
+//
+// A group larger than the cap (low-complexity data: thousands of words sharing a block) would
+// make the walk quadratic.  Such groups are skipped whole; their members are flagged per block and
+// resolved afterwards by enumerating their upward variants against the word table, keeping only
+// the hits whose first common block is a flagged one — the pair set stays exactly the same.
 #include <algorithm>
+#include <cstdlib>
 
 #include "state.cuh"
 
 namespace humid {
 
-// Undirected pair (a < b in rank: an upward variant is numerically larger) + the two degrees.
+// Undirected pair (a < b in rank) + the two degrees.
 __device__ __forceinline__ void emit_pair(uint64_t *pairs, uint64_t cap, unsigned long long *counter, uint32_t *deg,
                                           uint32_t a, uint32_t b) {
-  unsigned long long pos = atomicAdd(counter, 1ull);
+  const unsigned long long pos = reserve_slots(counter);
   if (pos < cap) {
     pairs[pos] = ((uint64_t)a << 32) | b;
     atomicAdd(deg + a, 1u);
@@ -26,70 +39,89 @@ __device__ __forceinline__ void emit_pair(uint64_t *pairs, uint64_t cap, unsigne
   }
 }
 
-// d == 1: one thread per word, looping over the positions.  Per position the (up to) three
-// filter buckets are fetched back to back (independent L2 requests, evict_last so that the
-// filter stays resident), only fingerprint matches go on to the HBM table (evict_first).
-// The filter hash is linear, so a variant costs one 64-bit add.  A thread keeps its hits in
-// registers; the warp appends all of them with one global atomic.
-constexpr int H1_LOCAL_HITS = 6;
-constexpr uint32_t H1_SCAN_CAP = 32;
-__global__ void __launch_bounds__(128)
-    hamming1_probe_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, uint32_t scan_from,
-                          const Lookup lk, uint64_t *__restrict__ pairs, uint64_t cap,
-                          unsigned long long *__restrict__ counter, uint32_t *__restrict__ deg) {
-  const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const bool live = r < U;
-  const uint64_t w = live ? word_key[r] : 0ull;
-  const uint64_t hw = filter_hash(w);
-  const uint64_t pol_keep = l2_policy_evict_last();
-  uint32_t hits[H1_LOCAL_HITS];
-  uint32_t nh = 0;
+constexpr int HAM_MAX_D = 8;
+constexpr uint64_t LETTER_LOW = 0x5555555555555555ull;
+
+struct Blocks {
+  uint32_t n_blocks;
+  uint64_t mask[HAM_MAX_D + 1];  // bits of block b (block 0 = first letters = highest bits)
+};
+
+// lowest block on which two words (x = a ^ b) agree; n_blocks if none.  Unrolled with constant
+// indices: B is a kernel parameter and must stay in the constant bank, not be copied to the stack.
+__device__ __forceinline__ uint32_t first_common_block(const Blocks &B, uint64_t x) {
+  uint32_t first = B.n_blocks;
+#pragma unroll
+  for (int b = HAM_MAX_D; b >= 0; b--)
+    if ((uint32_t)b < B.n_blocks && (x & B.mask[b]) == 0) first = (uint32_t)b;
+  return first;
+}
+
+// a precedes b in rank, 1..d letters differ: linked iff a[p] <= b[p] wherever they differ
+__device__ __forceinline__ bool linked(uint64_t a, uint64_t b, uint32_t d) {
+  const uint64_t x = a ^ b;
+  const uint64_t diff = (x | (x >> 1)) & LETTER_LOW;
+  if ((uint32_t)__popcll(diff) > d) return false;
+  if (d == 1) return true;  // the only differing letter decides the order, and a < b
+  const uint64_t ah = (a >> 1) & LETTER_LOW, bh = (b >> 1) & LETTER_LOW, al = a & LETTER_LOW, bl = b & LETTER_LOW;
+  const uint64_t a_greater = (ah & ~bh) | (~(ah ^ bh) & al & ~bl);
+  return (a_greater & diff) == 0;
+}
+
+// One thread per position i of the block order.  keys: the words in that order; rank == nullptr
+// means the order IS rank order.  A group is skipped (and its members flagged with bit `block`)
+// iff it has more than group_cap members; every member reaches the same verdict by looking at
+// most group_cap positions back and forth.
+constexpr int JOIN_LOCAL_HITS = 6;
+constexpr int JOIN_THREADS = 512;
+__global__ void __launch_bounds__(JOIN_THREADS)
+    hamming_join_kernel(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ rank, uint64_t U, uint32_t d,
+                        const Blocks B, uint32_t block, uint64_t mask, uint32_t group_cap,
+                        uint64_t *__restrict__ pairs,
+                        uint64_t cap, unsigned long long *__restrict__ counter, uint32_t *__restrict__ deg,
+                        uint32_t *__restrict__ flags, unsigned long long *__restrict__ n_flagged) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = i < U;
+  const uint64_t w = live ? keys[i] : 0ull;
+  const uint64_t g = w & mask;
   const uint32_t lane = lane_id();
-  // Variants at positions >= scan_from share the word's first scan_from letters, so in rank
-  // order they sit right behind it: walk forward while the prefix matches (rank == index, no
-  // look-up at all).  Only if that run is unusually long are those positions probed instead.
-  uint32_t probe_end = n;
-  if (live && scan_from < n) {
-    const uint32_t low = 2 * (n - scan_from);
-    const uint64_t prefix = w >> low;
-    probe_end = scan_from;
-    for (uint64_t j = r + 1; j < U; j++) {
-      const uint64_t k = word_key[j];
-      if ((k >> low) != prefix) break;
-      if (j - r > H1_SCAN_CAP) { probe_end = n; break; }
-      const uint64_t x = k ^ w;
-      if (__popcll((x | (x >> 1)) & 0x5555555555555555ull) == 1) {  // one letter differs (and k > w)
-        if (nh == H1_LOCAL_HITS) { probe_end = n; break; }  // nothing emitted yet: safe to start over
-        hits[nh++] = (uint32_t)j;
-      }
+  // hits stay in registers (offsets inside the group); the warp appends all of them with ONE
+  // atomic on the pair counter — a per-pair atomic on that single address would serialise
+  uint32_t hits[JOIN_LOCAL_HITS];
+  uint32_t nh = 0;
+  uint32_t ri = 0;
+  if (live) {
+    // members before i (stop as soon as the group is known to be too large)
+    uint32_t before = 0;
+    while (before < group_cap && before < i && (keys[i - 1 - before] & mask) == g) before++;
+    uint32_t after = 0;
+    if (before < group_cap) {
+      const uint32_t room = group_cap - before;  // the group fits iff after < room
+      while (after < room && i + 1 + after < U && (keys[i + 1 + after] & mask) == g) after++;
     }
-    if (probe_end == n) nh = 0;  // run too long: everything is found by probing below instead
-  }
-  for (uint32_t p = 0; p < probe_end; p++) {
-    const uint32_t sh = 2 * (n - 1 - p);
-    const uint32_t wl = (uint32_t)(w >> sh) & 3u;
-    const uint64_t step = FILTER_MUL << sh;  // hash of "+1 at position p"
-    uint4 bkt[3];
-    uint64_t hf[3];
+    ri = after || before >= group_cap ? (rank ? rank[i] : (uint32_t)i) : 0u;
+    if (before + after >= group_cap) {
+      atomicOr(flags + ri, 1u << block);
+      atomicAdd(n_flagged, 1ull);
+    } else {
+      for (uint32_t t = 1; t <= after; t++) {
+        const uint64_t v = keys[i + t];
+        if (!linked(w, v, d)) continue;
+        if (first_common_block(B, v ^ w) != block) continue;  // found in an earlier block's order
+        if (nh == JOIN_LOCAL_HITS) {  // rare: local buffer full, append what we have
+          unsigned long long pos = atomicAdd(counter, (unsigned long long)nh);
 #pragma unroll
-    for (uint32_t c = 1; c < 4; c++) {
-      hf[c - 1] = hw + step * c;  // variants with letter wl + c (valid while wl + c <= 3)
-      if (live && wl + c <= 3u) bkt[c - 1] = ld_hint_u128(lk.filter + filter_bucket(hf[c - 1], lk.n_buckets), pol_keep);
-    }
-#pragma unroll
-    for (uint32_t c = 1; c < 4; c++) {
-      if (live && wl + c <= 3u && filter_match(bkt[c - 1], hf[c - 1])) {
-        const uint32_t hit = table_rank(lk, w + ((uint64_t)c << sh));
-        if (hit != NONE32) {
-          if (nh == H1_LOCAL_HITS) {  // rare: local buffer full, spill what we have
-            unsigned long long pos = atomicAdd(counter, (unsigned long long)nh);
-            for (uint32_t k = 0; k < nh; k++, pos++)
-              if (pos < cap) { pairs[pos] = (r << 32) | hits[k]; atomicAdd(deg + hits[k], 1u); }
-            if (pos <= cap) atomicAdd(deg + r, nh);
-            nh = 0;
+          for (int k = 0; k < JOIN_LOCAL_HITS; k++, pos++) {
+            const uint32_t rb = rank ? rank[i + hits[k]] : (uint32_t)(i + hits[k]);
+            if (pos < cap) { pairs[pos] = ((uint64_t)ri << 32) | rb; atomicAdd(deg + rb, 1u); }
           }
-          hits[nh++] = hit;
+          if (pos <= cap) atomicAdd(deg + ri, nh);
+          nh = 0;
         }
+#pragma unroll
+        for (int k = 0; k < JOIN_LOCAL_HITS; k++)  // constant indices keep the buffer in registers
+          if (k == (int)nh) hits[k] = t;
+        nh++;
       }
     }
   }
@@ -99,60 +131,52 @@ __global__ void __launch_bounds__(128)
     uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
     if ((int)lane >= o) inc += t;
   }
-  const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
-  if (total == 0) return;
-  unsigned long long base = 0;
-  if (lane == 31) base = atomicAdd(counter, (unsigned long long)total);
-  base = __shfl_sync(0xffffffffu, base, 31);
+  // ... and the CTA's warps share one: warp totals -> CTA prefix in shared memory
+  __shared__ uint32_t warp_total[JOIN_THREADS / 32];
+  __shared__ unsigned long long cta_base;
+  const uint32_t wid = threadIdx.x >> 5;
+  if (lane == 31) warp_total[wid] = inc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t sum = 0;
+    for (int k = 0; k < JOIN_THREADS / 32; k++) {
+      uint32_t c = warp_total[k];
+      warp_total[k] = sum;
+      sum += c;
+    }
+    cta_base = sum ? atomicAdd(counter, (unsigned long long)sum) : 0ull;
+  }
+  __syncthreads();
   if (nh) {
-    unsigned long long pos = base + (inc - nh);
+    unsigned long long pos = cta_base + warp_total[wid] + (inc - nh);
     if (pos + nh <= cap) {
-      for (uint32_t k = 0; k < nh; k++) {
-        pairs[pos + k] = (r << 32) | hits[k];
-        atomicAdd(deg + hits[k], 1u);
+#pragma unroll
+      for (int k = 0; k < JOIN_LOCAL_HITS; k++) {
+        if (k < (int)nh) {
+          const uint32_t rb = rank ? rank[i + hits[k]] : (uint32_t)(i + hits[k]);
+          pairs[pos + k] = ((uint64_t)ri << 32) | rb;
+          atomicAdd(deg + rb, 1u);
+        }
       }
-      atomicAdd(deg + r, nh);
+      atomicAdd(deg + ri, nh);
     }
   }
 }
 
-// d == 2: one thread per (word, first modified position p1).
-__global__ void __launch_bounds__(256)
-    hamming2_probe_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, const Lookup lk,
-                          uint64_t *__restrict__ pairs, uint64_t cap, unsigned long long *__restrict__ counter,
-                          uint32_t *__restrict__ deg) {
-  uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  uint64_t r = gid / n;
-  if (r >= U) return;
-  uint32_t p1 = (uint32_t)(gid - r * n);
-  uint64_t w = word_key[r];
-  uint32_t sh1 = 2 * (n - 1 - p1);
-  uint32_t w1 = (uint32_t)(w >> sh1) & 3u;
-  for (uint32_t c1 = w1 + 1; c1 < 4; c1++) {
-    uint64_t v1 = w + ((uint64_t)(c1 - w1) << sh1);
-    uint32_t hit = lookup_rank(lk, v1);
-    if (hit != NONE32) emit_pair(pairs, cap, counter, deg, (uint32_t)r, hit);
-    for (uint32_t p2 = p1 + 1; p2 < n; p2++) {
-      uint32_t sh2 = 2 * (n - 1 - p2);
-      uint32_t w2 = (uint32_t)(w >> sh2) & 3u;
-      for (uint32_t c2 = w2 + 1; c2 < 4; c2++) {
-        uint32_t h2 = lookup_rank(lk, v1 + ((uint64_t)(c2 - w2) << sh2));
-        if (h2 != NONE32) emit_pair(pairs, cap, counter, deg, (uint32_t)r, h2);
-      }
-    }
-  }
-}
-
-// any d >= 1: one thread per (word, first modified position); iterative enumeration of the
-// upward variants with at most d modified positions, positions strictly increasing.
-constexpr int HAM_MAX_D = 8;
+// Flagged words only: one thread per (word, first modified position); iterative enumeration of
+// the upward variants with at most d modified positions, positions strictly increasing.  A hit
+// counts iff the first block the two words share is one the word is flagged for (the join
+// skipped exactly those groups).
 __global__ void __launch_bounds__(128)
-    hammingd_probe_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, uint32_t d, const Lookup lk,
-                          uint64_t *__restrict__ pairs, uint64_t cap, unsigned long long *__restrict__ counter,
-                          uint32_t *__restrict__ deg) {
+    hamming_flagged_probe_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, uint32_t d,
+                                 const Blocks B, const uint32_t *__restrict__ flags, const Lookup lk,
+                                 uint64_t *__restrict__ pairs, uint64_t cap, unsigned long long *__restrict__ counter,
+                                 uint32_t *__restrict__ deg) {
   uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   uint64_t r = gid / n;
   if (r >= U) return;
+  const uint32_t fl = flags[r];
+  if (fl == 0) return;
   const uint64_t w = word_key[r];
   uint32_t pos[HAM_MAX_D];
   uint32_t let[HAM_MAX_D];
@@ -171,14 +195,38 @@ __global__ void __launch_bounds__(128)
       continue;
     }
     cur = (cur & ~(3ull << sh)) | ((uint64_t)let[depth] << sh);
-    uint32_t hit = lookup_rank(lk, cur);
-    if (hit != NONE32) emit_pair(pairs, cap, counter, deg, (uint32_t)r, hit);
+    const uint32_t fb = first_common_block(B, cur ^ w);
+    if (fb < B.n_blocks && ((fl >> fb) & 1u)) {
+      uint32_t hit = lookup_rank(lk, cur);
+      if (hit != NONE32) emit_pair(pairs, cap, counter, deg, (uint32_t)r, hit);
+    }
     if (depth + 1 < (int)d && pos[depth] + 1 < n) {
       depth++;
       pos[depth] = pos[depth - 1] + 1;
       let[depth] = (uint32_t)(w >> (2 * (n - 1 - pos[depth]))) & 3u;
     }
   }
+}
+
+static Blocks make_blocks(uint32_t n, uint32_t d, int lo_bit[], int hi_bit[]) {
+  Blocks B{};
+  B.n_blocks = d + 1;
+  for (uint32_t b = 0; b <= d; b++) {
+    const uint32_t p0 = b * n / (d + 1), p1 = (b + 1) * n / (d + 1);  // letters [p0, p1); may be empty if n <= d
+    lo_bit[b] = 2 * (int)(n - p1);
+    hi_bit[b] = 2 * (int)(n - p0);
+    B.mask[b] = p1 > p0 ? ((~0ull >> (64 - 2 * (p1 - p0))) << lo_bit[b]) : 0ull;
+  }
+  return B;
+}
+
+// HUMID_GPU_JOIN_CAP: group size above which the join hands a group to the probe path (testing knob)
+static uint32_t join_group_cap(uint32_t d) {
+  if (const char *e = std::getenv("HUMID_GPU_JOIN_CAP")) {
+    long v = std::strtol(e, nullptr, 10);
+    if (v >= 1) return (uint32_t)v;
+  }
+  return d == 1 ? 64u : 2048u;
 }
 
 int stage_neighbours_hamming(State &s) {
@@ -190,33 +238,59 @@ int stage_neighbours_hamming(State &s) {
     if (U) HUMID_CUDA(cudaMemsetAsync(s.deg.p, 0, U * sizeof(uint32_t), s.stream));
     return 0;
   }
-  if (d > HAM_MAX_D) throw CudaError{"Hamming distance > 8 is not supported by the variant-probe path"};
+  if (d > HAM_MAX_D) throw CudaError{"Hamming distance > 8 is not supported"};
   int k = 0;
+  int lo_bit[HAM_MAX_D + 1], hi_bit[HAM_MAX_D + 1];
+  const Blocks B = make_blocks(n, d, lo_bit, hi_bit);
+  const uint32_t group_cap = join_group_cap(d);
   uint64_t cap = s.entries.cap ? s.entries.cap : std::max<uint64_t>(2 * U, 1u << 20);
-  const Lookup lk = s.lookup();
+  s.word_flags.ensure(U + 1);
+  s.key_alt.ensure(U + 1);
+  s.entries_alt.ensure(U + 1);
+  s.entry_val.ensure(U + 1);
+  s.entry_val_alt.ensure(U + 1);
+  unsigned long long *counter = s.counters.p + 2, *n_flagged = s.counters.p + 40;
   for (int attempt = 0; attempt < 2; attempt++) {
     s.entries.ensure(cap);
     cap = s.entries.cap;
-    HUMID_CUDA(cudaMemsetAsync(s.counters.p + 2, 0, sizeof(unsigned long long), s.stream));
+    HUMID_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned long long), s.stream));
+    HUMID_CUDA(cudaMemsetAsync(n_flagged, 0, sizeof(unsigned long long), s.stream));
     HUMID_CUDA(cudaMemsetAsync(s.deg.p, 0, U * sizeof(uint32_t), s.stream));
-    uint64_t threads = U * n;
-    // 8 B per probed upward variant (expected 1.5 n at d=1, + 2.25 C(n,2) at d=2) + the word
-    double probes = d == 1 ? 1.5 * n : d == 2 ? 1.5 * n + 2.25 * n * (n - 1) / 2.0 : 0.0;
-    {
-      Timed t(s, d == 1 ? "probe_hamming1" : d == 2 ? "probe_hamming2" : "probe_hammingd", U,
-              (uint64_t)(U * 8.0 * (1.0 + probes)));
-      if (d == 1 && lk.filter)
-        hamming1_probe_kernel<<<grid_for(U, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, scan_from_position(U, n), lk,
-                                                                      s.entries.p, cap, s.counters.p + 2, s.deg.p);
-      else if (d == 2)
-        hamming2_probe_kernel<<<grid_for(threads, 256), 256, 0, s.stream>>>(s.word_key.p, U, n, lk, s.entries.p, cap,
-                                                                            s.counters.p + 2, s.deg.p);
-      else
-        hammingd_probe_kernel<<<grid_for(threads, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, d, lk, s.entries.p,
-                                                                            cap, s.counters.p + 2, s.deg.p);
+    HUMID_CUDA(cudaMemsetAsync(s.word_flags.p, 0, U * sizeof(uint32_t), s.stream));
+    for (uint32_t b = 0; b <= d; b++) {
+      const uint64_t *keys = s.word_key.p;
+      const uint32_t *rank = nullptr;
+      if (b > 0 && hi_bit[b] > lo_bit[b]) {
+        uint64_t *kb[2] = {s.key_alt.p, s.entries_alt.p};
+        uint32_t *vb[2] = {s.entry_val.p, s.entry_val_alt.p};
+        int launches = 0;
+        Timed t(s, "join_sort", U, U * (8 + 12));
+        int cur = radix_sort_bits_indexed(s.word_key.p, kb, vb, U, lo_bit[b], hi_bit[b], s.scratch, s.stream, &launches);
+        t.launches = launches;
+        k += launches;
+        keys = kb[cur];
+        rank = vb[cur];
+      }
+      // the word, its successor in the group (the walk ends there for almost every word) and the pair out
+      static const char *const join_names[HAM_MAX_D + 1] = {"join_hamming_b0", "join_hamming_b1", "join_hamming_b2",
+                                                            "join_hamming_b3", "join_hamming_b4", "join_hamming_b5",
+                                                            "join_hamming_b6", "join_hamming_b7", "join_hamming_b8"};
+      Timed t(s, join_names[b], U, U * (8 + 8 + (rank ? 4 : 0)));
+      hamming_join_kernel<<<grid_for(U, JOIN_THREADS), JOIN_THREADS, 0, s.stream>>>(keys, rank, U, d, B, b, B.mask[b], group_cap, s.entries.p, cap,
+                                                                  counter, s.deg.p, s.word_flags.p, n_flagged);
+      k++;
     }
-    k++;
-    HUMID_CUDA(cudaMemcpyAsync(&s.n_pairs, s.counters.p + 2, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+    HUMID_CUDA(cudaMemcpyAsync(&s.n_flagged, n_flagged, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    if (s.n_flagged) {  // rare: groups beyond the cap go through the word table instead
+      k += stage_ensure_lookup(s);
+      Timed t(s, "probe_flagged", s.n_flagged, s.n_flagged * 8);
+      hamming_flagged_probe_kernel<<<grid_for(U * n, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, d, B, s.word_flags.p,
+                                                                              s.lookup(), s.entries.p, cap, counter,
+                                                                              s.deg.p);
+      k++;
+    }
+    HUMID_CUDA(cudaMemcpyAsync(&s.n_pairs, counter, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     if (s.n_pairs <= cap) break;
     cap = s.n_pairs;  // the counter kept counting: exact size is now known, run once more

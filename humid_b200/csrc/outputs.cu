@@ -56,6 +56,7 @@ __global__ void __launch_bounds__(256)
 
 int stage_cluster_ids(State &s, uint64_t first, uint64_t n, uint32_t *d_out) {
   if (n == 0) return 0;
+  if (!s.ranks_in_table) stage_ensure_lookup(s);  // slot.count -> rank
   // K5: key (8) + slot (16) + label (4) + seed index (4) + id out (4)
   Timed t(s, "cluster_ids", n, n * 36);
   cluster_ids_kernel<<<grid_for(n, 256), 256, 0, s.stream>>>(s.tuple_key.p, first, n, s.slots.p, s.table_cap - 1,
@@ -82,7 +83,7 @@ __global__ void __launch_bounds__(256)
   if (i >= m) return;
   uint64_t v = sorted[i];
   if (i == 0 || sorted[i - 1] != v) {
-    unsigned long long pos = atomicAdd(counter, 1ull);
+    const unsigned long long pos = reserve_slots(counter);
     if (pos < cap) {
       run_val[pos] = v;
       run_start[pos] = i;

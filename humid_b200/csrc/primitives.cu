@@ -148,15 +148,22 @@ constexpr int RS_MAX_PASSES = 8;
 constexpr uint64_t RS_AGGREGATE = 1ull << 62;  // status word: this tile's own count
 constexpr uint64_t RS_INCLUSIVE = 1ull << 63;  // status word: count of this tile and all before it
 
+__device__ __forceinline__ uint32_t pass_mask(int begin_bit, int end_bit, int p) {
+  const int left = end_bit - begin_bit - 8 * p;
+  return left >= 8 ? 255u : (1u << left) - 1u;
+}
+
 __global__ void __launch_bounds__(RS_THREADS) radix_digit_hist_kernel(const uint64_t *__restrict__ keys, uint64_t n,
-                                                                      int passes, uint32_t *__restrict__ hist) {
+                                                                      int begin_bit, int end_bit, int passes,
+                                                                      uint32_t *__restrict__ hist) {
   __shared__ uint32_t h[RS_MAX_PASSES][RS_BINS];
   for (int p = 0; p < passes; p++) h[p][threadIdx.x] = 0;
   __syncthreads();
   const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
   for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride) {
     uint64_t key = ld_stream_u64(keys + i);
-    for (int p = 0; p < passes; p++) atomicAdd(&h[p][(uint32_t)(key >> (8 * p)) & 255u], 1u);
+    for (int p = 0; p < passes; p++)
+      atomicAdd(&h[p][(uint32_t)(key >> (begin_bit + 8 * p)) & pass_mask(begin_bit, end_bit, p)], 1u);
   }
   __syncthreads();
   for (int p = 0; p < passes; p++) {
@@ -190,7 +197,8 @@ __global__ void __launch_bounds__(RS_THREADS) radix_digit_bases_kernel(uint32_t 
 // digit of a key in a sort pass / in the slot partition of the word table (top 8 bits of the home slot)
 struct ShiftDigit {
   int shift;
-  __device__ __forceinline__ uint32_t operator()(uint64_t key) const { return (uint32_t)(key >> shift) & 255u; }
+  uint32_t mask;
+  __device__ __forceinline__ uint32_t operator()(uint64_t key) const { return (uint32_t)(key >> shift) & mask; }
 };
 struct SlotDigit {
   uint64_t mask;
@@ -332,12 +340,15 @@ __global__ void __launch_bounds__(RS_THREADS)
   }
 }
 
-int radix_sort_u64(uint64_t *keys[2], uint32_t *vals[2], uint64_t n, int end_bit, Scratch &scratch,
-                   Scratch &scan_scratch, cudaStream_t stream, int *launches) {
-  (void)scan_scratch;
-  if (n <= 1 || end_bit <= 0) return 0;
-  if (n >= 0xFFFFFFFFull) throw CudaError{"radix_sort_u64: more than 2^32-1 elements"};
-  const int passes = (end_bit + 7) / 8;
+// Passes over bits [begin_bit, end_bit).  The first pass reads (in_keys, in_vals) and writes buffer
+// `first_out`; later passes ping-pong between the two buffers.  in_vals == nullptr with value
+// buffers present: the value of input element i is i.  Returns the buffer holding the result.
+static int radix_sort_impl(const uint64_t *in_keys, const uint32_t *in_vals, uint64_t *keys[2], uint32_t *vals[2],
+                           int first_out, uint64_t n, int begin_bit, int end_bit, Scratch &scratch,
+                           cudaStream_t stream, int *launches) {
+  if (n >= 0xFFFFFFFFull) throw CudaError{"radix sort: more than 2^32-1 elements"};
+  const int passes = (end_bit - begin_bit + 7) / 8;
+  if (passes > RS_MAX_PASSES) throw CudaError{"radix sort: more than 64 key bits"};
   const uint32_t n_tiles = (uint32_t)((n + RS_TILE - 1) / RS_TILE);
   // scratch: [status: n_tiles*256 u64][tickets: 8 u32 (one per pass)][hist: passes*256 u32]
   const size_t status_bytes = (size_t)n_tiles * RS_BINS * sizeof(uint64_t);
@@ -348,26 +359,44 @@ int radix_sort_u64(uint64_t *keys[2], uint32_t *vals[2], uint64_t n, int end_bit
   uint32_t *hist = tickets + RS_MAX_PASSES;
   HUMID_CUDA(cudaMemsetAsync(tickets, 0, tail_bytes, stream));
   unsigned hist_grid = (unsigned)std::min<uint64_t>((n + RS_THREADS - 1) / RS_THREADS, 148 * 8);
-  radix_digit_hist_kernel<<<hist_grid, RS_THREADS, 0, stream>>>(keys[0], n, passes, hist);
+  radix_digit_hist_kernel<<<hist_grid, RS_THREADS, 0, stream>>>(in_keys, n, begin_bit, end_bit, passes, hist);
   radix_digit_bases_kernel<<<passes, RS_THREADS, 0, stream>>>(hist);
   *launches += 2;
-  int cur = 0;
   const bool has_vals = vals && vals[0];
+  const uint64_t *src_k = in_keys;
+  const uint32_t *src_v = in_vals;
+  int out = first_out;
   for (int p = 0; p < passes; p++) {
+    const int shift = begin_bit + 8 * p;
+    const int left = end_bit - shift;
+    const ShiftDigit dg{shift, left >= 8 ? 255u : (1u << left) - 1u};
     HUMID_CUDA(cudaMemsetAsync(status, 0, status_bytes, stream));
     if (has_vals)
-      radix_pass_kernel<true><<<n_tiles, RS_THREADS, 0, stream>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n,
-                                                                  ShiftDigit{8 * p}, hist + p * RS_BINS, status,
-                                                                  tickets + p, 0u);
+      radix_pass_kernel<true><<<n_tiles, RS_THREADS, 0, stream>>>(src_k, src_v, keys[out], vals[out], n, dg,
+                                                                  hist + p * RS_BINS, status, tickets + p, 0u);
     else
-      radix_pass_kernel<false><<<n_tiles, RS_THREADS, 0, stream>>>(keys[cur], nullptr, keys[cur ^ 1], nullptr, n,
-                                                                   ShiftDigit{8 * p}, hist + p * RS_BINS, status,
-                                                                   tickets + p, 0u);
+      radix_pass_kernel<false><<<n_tiles, RS_THREADS, 0, stream>>>(src_k, nullptr, keys[out], nullptr, n, dg,
+                                                                   hist + p * RS_BINS, status, tickets + p, 0u);
     *launches += 1;
-    cur ^= 1;
+    src_k = keys[out];
+    src_v = has_vals ? vals[out] : nullptr;
+    out ^= 1;
   }
   HUMID_CUDA(cudaGetLastError());
-  return cur;
+  return out ^ 1;
+}
+
+int radix_sort_u64(uint64_t *keys[2], uint32_t *vals[2], uint64_t n, int end_bit, Scratch &scratch,
+                   Scratch &scan_scratch, cudaStream_t stream, int *launches) {
+  (void)scan_scratch;
+  if (n <= 1 || end_bit <= 0) return 0;
+  return radix_sort_impl(keys[0], vals ? vals[0] : nullptr, keys, vals, 1, n, 0, end_bit, scratch, stream, launches);
+}
+
+int radix_sort_bits_indexed(const uint64_t *keys_in, uint64_t *keys[2], uint32_t *index[2], uint64_t n, int begin_bit,
+                            int end_bit, Scratch &scratch, cudaStream_t stream, int *launches) {
+  if (n == 0 || end_bit <= begin_bit) throw CudaError{"radix_sort_bits_indexed: nothing to sort by"};
+  return radix_sort_impl(keys_in, nullptr, keys, index, 0, n, begin_bit, end_bit, scratch, stream, launches);
 }
 
 int partition_by_slot_u64(const uint64_t *keys_in, const uint32_t *vals_in, uint32_t index_base, uint64_t *keys_out,

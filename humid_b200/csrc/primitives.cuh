@@ -42,6 +42,12 @@ int exclusive_scan_u32(const uint32_t *in, uint32_t *out, uint64_t n, uint32_t *
 int radix_sort_u64(uint64_t *keys[2], uint32_t *vals[2], uint64_t n, int end_bit, Scratch &scratch,
                    Scratch &scan_scratch, cudaStream_t stream, int *launches);
 
+// Stable sort of (key, position) pairs by bits [begin_bit, end_bit) of the key.  keys_in is only
+// read; element i carries the value i.  Returns the index (0 or 1) of the (keys, index) buffer
+// pair holding the result.
+int radix_sort_bits_indexed(const uint64_t *keys_in, uint64_t *keys[2], uint32_t *index[2], uint64_t n, int begin_bit,
+                            int end_bit, Scratch &scratch, cudaStream_t stream, int *launches);
+
 // One stable partition pass of (key, value) pairs by the top 8 bits of the key's home slot in an
 // open-addressing table with `slot_mask + 1` slots (slot = mix64(key) & slot_mask): afterwards
 // consecutive elements touch one 1/256 of the table, which then stays in L2 while it is worked on.

@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(256)
     if (v < L.hi) {
       uint32_t hit = lookup_rank(lk, v);
       if (hit != NONE32) {
-        unsigned long long pos = atomicAdd(entry_counter, 2ull);
+        const unsigned long long pos = reserve_slots(entry_counter, 2u);
         if (pos + 2 <= cap) {
           // rows are shard-local, columns global
           entries[pos] = (r << 32) | (uint64_t)(L.base + hit);
@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(256)
   uint32_t hit = lookup_rank(lk, q_keys[i]);
   answers[i] = hit == NONE32 ? NONE32 : L.base + hit;
   if (hit != NONE32) {
-    unsigned long long pos = atomicAdd(entry_counter, 1ull);
+    const unsigned long long pos = reserve_slots(entry_counter);
     if (pos < cap) {
       entries[pos] = ((uint64_t)hit << 32) | q_src[i];  // result leaf <- walk leaf
       atomicAdd(deg + hit, 1u);
@@ -321,7 +321,7 @@ __global__ void __launch_bounds__(256)
   if (i >= n) return;
   uint32_t a = answers[i];
   if (a != NONE32) {
-    unsigned long long pos = atomicAdd(entry_counter, 1ull);
+    const unsigned long long pos = reserve_slots(entry_counter);
     if (pos < cap) {
       entries[pos] = ((uint64_t)(q_src[i] - L.base) << 32) | a;  // walk leaf <- result leaf
       atomicAdd(deg + (q_src[i] - L.base), 1u);

@@ -87,6 +87,9 @@ struct State {
   uint64_t table_cap = 0;  // power of two
   DevBuf<uint4> filter;    // fingerprint buckets in front of the table (common.cuh)
   uint32_t filter_buckets = 0;
+  DevBuf<uint32_t> word_flags;  // Hamming join: bit b = the word's block-b group was too large to walk
+  uint64_t n_flagged = 0;
+  bool ranks_in_table = false;  // slot.count holds the word's rank (stage_ensure_lookup)
   Lookup lookup() const { return Lookup{slots.p, table_cap - 1, filter_buckets ? filter.p : nullptr, filter_buckets}; }
 
   // what humid_gpu_counts reports / what keep_bits covers (the whole job in shard mode)
@@ -184,7 +187,8 @@ struct Timed {
 
 // ---- stage launchers (each returns the number of kernels it launched) --------------------
 int stage_pack(State &s, const uint8_t *d_chars, const uint16_t *d_seg_len, uint64_t first, uint64_t n);
-int stage_build_table(State &s, bool with_filter = true);  // insert + compact + sort + rank columns (+ filter)
+int stage_build_table(State &s, bool with_lookup = true);  // insert + compact + sort + columns (+ look-up)
+int stage_ensure_lookup(State &s);    // ranks into the table slots + fingerprint filter, once per job
 int stage_early_insert(State &s, uint64_t first, uint64_t n);  // add_batch: count tuples [first, first+n)
 int stage_build_filter(State &s);      // fingerprint filter over word_key[0..unique)
 int stage_neighbours_hamming(State &s);

@@ -187,17 +187,22 @@ __global__ void __launch_bounds__(256)
 }
 
 // Rank-ordered columns; the slot's count field is overwritten with the rank so that one
-// probe of the table answers "which rank is this key".
+// probe of the table answers "which rank is this key" — written only when something will ask
+// (stage_ensure_lookup).
 __global__ void __launch_bounds__(256)
-    rank_columns_kernel(Slot *slots, const uint32_t *__restrict__ word_slot, uint64_t U,
-                        uint32_t *__restrict__ word_count, uint32_t *__restrict__ word_first) {
+    gather_columns_kernel(const Slot *__restrict__ slots, const uint32_t *__restrict__ word_slot, uint64_t U,
+                          uint32_t *__restrict__ word_count, uint32_t *__restrict__ word_first) {
   uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= U) return;
-  Slot *sl = slots + word_slot[r];
-  uint4 v = *reinterpret_cast<const uint4 *>(sl);
+  uint4 v = __ldg(reinterpret_cast<const uint4 *>(slots + word_slot[r]));
   word_count[r] = v.z;
   word_first[r] = v.w;
-  sl->count = (uint32_t)r;
+}
+
+__global__ void __launch_bounds__(256)
+    scatter_ranks_kernel(Slot *slots, const uint32_t *__restrict__ word_slot, uint64_t U) {
+  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < U) slots[word_slot[r]].count = (uint32_t)r;
 }
 
 // Fingerprint filter over the distinct words (layout: common.cuh).  One CAS per word into an
@@ -298,7 +303,7 @@ int stage_early_insert(State &s, uint64_t first, uint64_t n) {
   return k;
 }
 
-int stage_build_table(State &s, bool with_filter) {
+int stage_build_table(State &s, bool with_lookup) {
   int k = 0;
   const uint64_t *keys = s.tuple_key.p;
   const uint32_t *index = nullptr;
@@ -351,12 +356,30 @@ int stage_build_table(State &s, bool with_filter) {
   s.word_count.ensure(U + 1);
   s.word_first.ensure(U + 1);
   if (U) {
-    Timed t(s, "rank_columns", U, U * (4 + 16 + 4 + 4 + 4));
-    rank_columns_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.slots.p, s.word_slot.p, U, s.word_count.p,
-                                                                s.word_first.p);
+    Timed t(s, "rank_columns", U, U * (4 + 16 + 4 + 4));
+    gather_columns_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.slots.p, s.word_slot.p, U, s.word_count.p,
+                                                                  s.word_first.p);
     k++;
   }
-  if (with_filter) k += stage_build_filter(s);
+  s.ranks_in_table = false;
+  s.filter_buckets = 0;
+  if (with_lookup) k += stage_ensure_lookup(s);
+  HUMID_CUDA(cudaGetLastError());
+  return k;
+}
+
+// key -> rank look-ups (Lookup in common.cuh) need the ranks in the table slots and the filter in
+// front of them.  The Hamming block join never asks, so this is done on first use.
+int stage_ensure_lookup(State &s) {
+  int k = 0;
+  const uint64_t U = s.unique;
+  if (!s.ranks_in_table && U) {
+    Timed t(s, "table_ranks", U, U * (4 + 4));
+    scatter_ranks_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.slots.p, s.word_slot.p, U);
+    k++;
+  }
+  s.ranks_in_table = true;
+  if (!s.filter_buckets) k += stage_build_filter(s);
   HUMID_CUDA(cudaGetLastError());
   return k;
 }

@@ -141,6 +141,35 @@ def test_words_counted_while_batches_arrive(hint):
         dd.reset()
 
 
+JOIN_CASES = [  # (config index, tuples, overrides) — dense enough that small caps split the work both ways
+    (0, 20000, dict(word_length=8, genome_len=2000)),
+    (2, 20000, dict(word_length=10, genome_len=3000)),
+    (2, 20000, dict(word_length=10, genome_len=3000, maximum=True)),
+    (2, 3000, dict(distance=3, word_length=9, genome_len=1500)),
+    (1, 30000, {}),
+]
+
+
+@pytest.mark.parametrize("group_cap", [1, 3, 16])
+@pytest.mark.parametrize("ci,R,kw", JOIN_CASES, ids=[f"c{c + 1}_{R}_{'_'.join(f'{k}{v}' for k, v in kw.items())}" for c, R, kw in JOIN_CASES])
+def test_oversized_groups_take_the_probe_path(monkeypatch, ci, R, kw, group_cap):
+    """The block join hands groups above the cap to variant probing; with tiny caps most or all pairs
+    come from that path, with middling ones the two paths share the pairs.  Same lists either way."""
+    monkeypatch.setenv("HUMID_GPU_JOIN_CAP", str(group_cap))
+    cfg = baseline_config(ci, R, **kw)
+    s = Synth(cfg)
+    chars = s.word_chars()
+    hdr, take = s.layout()
+    seg_take = ([hdr] if hdr else []) + take
+    r = oracle.Result(oracle.pack_words(chars, seg_take), cfg.word_length, cfg.distance, cfg.edit, cfg.maximum)
+    dd = run_gpu(chars, seg_take, cfg.word_length, cfg.distance, cfg.edit, cfg.maximum, batches=2)
+    assert_same_as_oracle(dd, r, R)
+    names = {st["name"] for st in dd.stage_stats()}
+    assert "join_hamming_b0" in names
+    if group_cap == 1:
+        assert "probe_flagged" in names
+
+
 def _chars(words):
     return np.frombuffer("".join(words).encode(), dtype=np.uint8).reshape(len(words), -1).copy()
 
