@@ -145,6 +145,7 @@ constexpr int RS_ITEMS = 16;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
 constexpr int RS_BINS = 256;
 constexpr int RS_MAX_PASSES = 8;
+constexpr int RS_LOOK = 8;
 constexpr uint64_t RS_AGGREGATE = 1ull << 62;  // status word: this tile's own count
 constexpr uint64_t RS_INCLUSIVE = 1ull << 63;  // status word: count of this tile and all before it
 
@@ -222,60 +223,89 @@ __global__ void __launch_bounds__(RS_THREADS) digit_hist_kernel(const uint64_t *
 }
 
 // HAS_VALS with vals_in == nullptr: the value of element i is index_base + i.
+// Persistent CTAs taking tiles by ticket.  A CTA draws the ticket of its NEXT tile when it starts
+// on the current one and pulls that tile into L2 meanwhile, which halves the exposed load latency
+// of a kernel that is otherwise a chain of dependent phases (load, rank, look-back, reorder,
+// store).  A ticket is only ever held by a running CTA that works through its (at most two)
+// tickets in order, so every tile a look-back waits for makes progress whatever else shares the
+// GPU.
+// Dynamic shared memory: RS_TILE keys (+ RS_TILE values).
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 template <bool HAS_VALS, class Digit>
 __global__ void __launch_bounds__(RS_THREADS)
     radix_pass_kernel(const uint64_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
-                      uint64_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n, Digit digit_of,
-                      const uint32_t *__restrict__ digit_base, volatile uint64_t *status, uint32_t *ticket,
-                      uint32_t index_base) {
+                      uint64_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n, uint32_t n_tiles,
+                      Digit digit_of, const uint32_t *__restrict__ digit_base, volatile uint64_t *status,
+                      uint32_t *ticket, uint32_t index_base) {
+  extern __shared__ uint64_t stage[];  // [RS_TILE] keys, then [RS_TILE] u32 values
   __shared__ uint32_t cnt[RS_WARPS][RS_BINS];
   __shared__ uint32_t dstart[RS_BINS];  // first tile-local position of a digit
   __shared__ uint32_t gbase[RS_BINS];   // output position of tile-local position 0 of a digit
-  __shared__ uint64_t stage[RS_TILE];
   __shared__ uint32_t warp_sums[RS_WARPS];
-  __shared__ uint32_t s_tile;
+  __shared__ uint32_t s_next;
+  uint32_t *const svals = reinterpret_cast<uint32_t *>(stage + RS_TILE);
   const int w = threadIdx.x >> 5;
   const uint32_t lane = lane_id();
   const uint32_t lt = (1u << lane) - 1u;
-  if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);  // tiles start in ticket order: look-back cannot starve
-#pragma unroll
-  for (int k = 0; k < RS_WARPS; k++) cnt[k][threadIdx.x] = 0;
-  __syncthreads();
-  const uint32_t tile = s_tile;
-  const uint64_t tile_base = (uint64_t)tile * RS_TILE;
-  const uint64_t warp_base = tile_base + (uint64_t)w * (32 * RS_ITEMS);
+  const uint32_t d = threadIdx.x;  // the digit this thread looks after
+  const uint32_t my_base = digit_base[d];
 
-  uint64_t key[RS_ITEMS];
-  uint32_t val[RS_ITEMS];
-  uint16_t lpos[RS_ITEMS];
+  if (threadIdx.x == 0) s_next = atomicAdd(ticket, 1u);
+  __syncthreads();
+  uint32_t tile = s_next;
+  __syncthreads();
+  while (tile < n_tiles) {
+    if (threadIdx.x == 0) s_next = atomicAdd(ticket, 1u);
 #pragma unroll
-  for (int j = 0; j < RS_ITEMS; j++) {
-    uint64_t i = warp_base + (uint64_t)j * 32 + lane;
-    key[j] = i < n ? ld_stream_u64(keys_in + i) : 0ull;
-  }
-  if (HAS_VALS) {
+    for (int k = 0; k < RS_WARPS; k++) cnt[k][threadIdx.x] = 0;
+    const uint64_t tile_base = (uint64_t)tile * RS_TILE;
+    const uint64_t warp_base = tile_base + (uint64_t)w * (32 * RS_ITEMS);
+    uint64_t key[RS_ITEMS];
+    uint32_t val[HAS_VALS ? RS_ITEMS : 1];
+    uint16_t lpos[RS_ITEMS];
 #pragma unroll
     for (int j = 0; j < RS_ITEMS; j++) {
       uint64_t i = warp_base + (uint64_t)j * 32 + lane;
-      val[j] = i >= n ? 0u : vals_in ? __ldcs(vals_in + i) : index_base + (uint32_t)i;
+      key[j] = i < n ? ld_stream_u64(keys_in + i) : 0ull;
     }
-  }
-  // rank of every element among the elements of its digit in this warp's sub-tile
+    if (HAS_VALS) {
 #pragma unroll
-  for (int j = 0; j < RS_ITEMS; j++) {
-    bool ok = warp_base + (uint64_t)j * 32 + lane < n;
-    uint32_t dig = ok ? digit_of(key[j]) : 256u;
-    uint32_t peers = __match_any_sync(0xffffffffu, dig);
-    uint32_t before = ok ? cnt[w][dig] : 0u;
-    __syncwarp();
-    if (ok && (peers & lt) == 0) cnt[w][dig] = before + __popc(peers);  // one leader per digit
-    __syncwarp();
-    lpos[j] = (uint16_t)(before + __popc(peers & lt));
-  }
-  __syncthreads();
-  // thread d: digit d of this tile
-  {
-    const uint32_t d = threadIdx.x;
+      for (int j = 0; j < RS_ITEMS; j++) {
+        uint64_t i = warp_base + (uint64_t)j * 32 + lane;
+        val[j] = i >= n ? 0u : vals_in ? __ldcs(vals_in + i) : index_base + (uint32_t)i;
+      }
+    }
+    __syncthreads();  // counters cleared, next ticket known
+    const uint32_t next_tile = s_next;
+    if (next_tile < n_tiles) {  // -> L2 (128-B lines: 256 of keys, 128 of values)
+      const uint64_t next = (uint64_t)next_tile * RS_TILE;
+      if (next + (uint64_t)threadIdx.x * 16 < n) prefetch_l2(keys_in + next + (uint64_t)threadIdx.x * 16);
+      if (HAS_VALS && vals_in && threadIdx.x < RS_THREADS / 2 && next + (uint64_t)threadIdx.x * 32 < n)
+        prefetch_l2(vals_in + next + (uint64_t)threadIdx.x * 32);
+    }
+    // rank of every element among the elements of its digit in this warp's sub-tile
+#pragma unroll
+    for (int j = 0; j < RS_ITEMS; j++) {
+      bool ok = warp_base + (uint64_t)j * 32 + lane < n;
+      uint32_t dig = ok ? digit_of(key[j]) : 0u;
+      // lanes holding the same digit: eight ballots (match.any is a slow-pipe instruction: the
+      // first version of this kernel was bound by it, ncu r01f)
+      uint32_t peers = __ballot_sync(0xffffffffu, ok);
+#pragma unroll
+      for (int bit = 0; bit < 8; bit++) {
+        const bool one = (dig >> bit) & 1u;
+        const uint32_t m = __ballot_sync(0xffffffffu, one);
+        peers &= one ? m : ~m;
+      }
+      uint32_t before = ok ? cnt[w][dig] : 0u;
+      __syncwarp();
+      if (ok && (peers & lt) == 0) cnt[w][dig] = before + __popc(peers);  // one leader per digit
+      __syncwarp();
+      lpos[j] = (uint16_t)(before + __popc(peers & lt));
+    }
+    __syncthreads();
+    // thread d: digit d of this tile
     uint32_t total = 0;
 #pragma unroll
     for (int k = 0; k < RS_WARPS; k++) {
@@ -285,59 +315,82 @@ __global__ void __launch_bounds__(RS_THREADS)
     }
     volatile uint64_t *mine = status + (uint64_t)tile * RS_BINS + d;
     *mine = (tile == 0 ? RS_INCLUSIVE : RS_AGGREGATE) | total;
-    uint32_t local = block_exclusive_256(total, warp_sums);
+    const uint32_t local = block_exclusive_256(total, warp_sums);
     dstart[d] = local;
-    uint32_t preceding = 0;
-    if (tile > 0) {
-      for (uint32_t t = tile - 1;; t--) {
-        uint64_t v;
-        do {
-          v = status[(uint64_t)t * RS_BINS + d];
-        } while (v == 0);
-        preceding += (uint32_t)v;
-        if (v & RS_INCLUSIVE) break;
+    __syncthreads();
+    // reorder in shared memory: every digit run becomes consecutive
+#pragma unroll
+    for (int j = 0; j < RS_ITEMS; j++) {
+      bool ok = warp_base + (uint64_t)j * 32 + lane < n;
+      if (ok) {
+        uint32_t dig = digit_of(key[j]);
+        uint32_t p = dstart[dig] + cnt[w][dig] + lpos[j];
+        stage[p] = key[j];
+        if (HAS_VALS) svals[p] = val[j];
       }
-      *mine = RS_INCLUSIVE | (uint64_t)(preceding + total);
     }
-    gbase[d] = digit_base[d] + preceding - local;
-  }
-  __syncthreads();
-  // reorder in shared memory, then every digit run goes out as consecutive addresses
+    // how many elements of digit d precede this tile: chained look-back over the earlier tiles,
+    // RS_LOOK status words per step (independent loads)
+    {
+      uint32_t preceding = 0;
+      if (tile > 0) {
+        uint32_t t = tile;  // next tile to examine is t - 1
+        bool done = false;
+        while (!done) {
+          uint64_t v[RS_LOOK];
 #pragma unroll
-  for (int j = 0; j < RS_ITEMS; j++) {
-    bool ok = warp_base + (uint64_t)j * 32 + lane < n;
-    if (ok) {
-      uint32_t dig = digit_of(key[j]);
-      uint32_t p = dstart[dig] + cnt[w][dig] + lpos[j];
-      stage[p] = key[j];
-      lpos[j] = (uint16_t)p;
-    }
-  }
-  __syncthreads();
-  const uint32_t in_tile = (uint32_t)min((uint64_t)RS_TILE, n - tile_base);
-  uint32_t out[RS_ITEMS];
+          for (int q = 0; q < RS_LOOK; q++)
+            v[q] = t > (uint32_t)q ? (uint64_t)status[(uint64_t)(t - 1 - q) * RS_BINS + d] : (1ull << 63);
 #pragma unroll
-  for (int k = 0; k < RS_ITEMS; k++) {
-    uint32_t idx = k * RS_THREADS + threadIdx.x;
-    if (idx < in_tile) {
-      uint64_t kk = stage[idx];
-      out[k] = gbase[digit_of(kk)] + idx;
-      keys_out[out[k]] = kk;
+          for (int q = 0; q < RS_LOOK; q++) {
+            if (done) break;
+            uint64_t x = v[q];
+            while (x == 0) x = status[(uint64_t)(t - 1 - q) * RS_BINS + d];  // not published yet
+            preceding += (uint32_t)x;
+            done = (x & RS_INCLUSIVE) != 0;
+          }
+          t = t > RS_LOOK ? t - RS_LOOK : 0;
+        }
+        *mine = RS_INCLUSIVE | (uint64_t)(preceding + total);
+      }
+      gbase[d] = my_base + preceding - local;
     }
-  }
-  if (HAS_VALS) {
-    uint32_t *sv = reinterpret_cast<uint32_t *>(stage);
     __syncthreads();
-#pragma unroll
-    for (int j = 0; j < RS_ITEMS; j++)
-      if (warp_base + (uint64_t)j * 32 + lane < n) sv[lpos[j]] = val[j];
-    __syncthreads();
+    const uint32_t in_tile = (uint32_t)min((uint64_t)RS_TILE, n - tile_base);
 #pragma unroll
     for (int k = 0; k < RS_ITEMS; k++) {
       uint32_t idx = k * RS_THREADS + threadIdx.x;
-      if (idx < in_tile) vals_out[out[k]] = sv[idx];
+      if (idx < in_tile) {
+        uint64_t kk = stage[idx];
+        uint32_t out = gbase[digit_of(kk)] + idx;
+        keys_out[out] = kk;
+        if (HAS_VALS) vals_out[out] = svals[idx];
+      }
     }
+    __syncthreads();  // stage / gbase / cnt / s_next are reused by the next tile
+    tile = next_tile;
   }
+}
+
+template <bool HAS_VALS, class Digit>
+static void launch_radix_pass(uint32_t n_tiles, cudaStream_t stream, const uint64_t *keys_in, const uint32_t *vals_in,
+                              uint64_t *keys_out, uint32_t *vals_out, uint64_t n, Digit dg, const uint32_t *digit_base,
+                              uint64_t *status, uint32_t *ticket, uint32_t index_base) {
+  const size_t smem = (size_t)RS_TILE * (HAS_VALS ? 12 : 8);
+  static int resident = 0;  // per instantiation: CTAs of this kernel that fit on the device at once
+  if (!resident) {
+    auto *fn = radix_pass_kernel<HAS_VALS, Digit>;
+    HUMID_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int dev = 0, sms = 0, per_sm = 0;
+    HUMID_CUDA(cudaGetDevice(&dev));
+    HUMID_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    HUMID_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, RS_THREADS, smem));
+    if (per_sm < 1) throw CudaError{"radix_pass_kernel does not fit on an SM"};
+    resident = sms * per_sm;
+  }
+  const unsigned grid = std::min<unsigned>(n_tiles, (unsigned)resident);
+  radix_pass_kernel<HAS_VALS, Digit><<<grid, RS_THREADS, smem, stream>>>(keys_in, vals_in, keys_out, vals_out, n, n_tiles,
+                                                                       dg, digit_base, status, ticket, index_base);
 }
 
 // Passes over bits [begin_bit, end_bit).  The first pass reads (in_keys, in_vals) and writes buffer
@@ -372,11 +425,11 @@ static int radix_sort_impl(const uint64_t *in_keys, const uint32_t *in_vals, uin
     const ShiftDigit dg{shift, left >= 8 ? 255u : (1u << left) - 1u};
     HUMID_CUDA(cudaMemsetAsync(status, 0, status_bytes, stream));
     if (has_vals)
-      radix_pass_kernel<true><<<n_tiles, RS_THREADS, 0, stream>>>(src_k, src_v, keys[out], vals[out], n, dg,
-                                                                  hist + p * RS_BINS, status, tickets + p, 0u);
+      launch_radix_pass<true>(n_tiles, stream, src_k, src_v, keys[out], vals[out], n, dg, hist + p * RS_BINS, status,
+                              tickets + p, 0u);
     else
-      radix_pass_kernel<false><<<n_tiles, RS_THREADS, 0, stream>>>(src_k, nullptr, keys[out], nullptr, n, dg,
-                                                                   hist + p * RS_BINS, status, tickets + p, 0u);
+      launch_radix_pass<false>(n_tiles, stream, src_k, nullptr, keys[out], nullptr, n, dg, hist + p * RS_BINS, status,
+                               tickets + p, 0u);
     *launches += 1;
     src_k = keys[out];
     src_v = has_vals ? vals[out] : nullptr;
@@ -417,8 +470,8 @@ int partition_by_slot_u64(const uint64_t *keys_in, const uint32_t *vals_in, uint
   unsigned hist_grid = (unsigned)std::min<uint64_t>((n + RS_THREADS - 1) / RS_THREADS, 148 * 8);
   digit_hist_kernel<<<hist_grid, RS_THREADS, 0, stream>>>(keys_in, n, dg, hist);
   radix_digit_bases_kernel<<<1, RS_THREADS, 0, stream>>>(hist);
-  radix_pass_kernel<true><<<n_tiles, RS_THREADS, 0, stream>>>(keys_in, vals_in, keys_out, vals_out, n, dg, hist,
-                                                              (uint64_t *)base, tickets, index_base);
+  launch_radix_pass<true>(n_tiles, stream, keys_in, vals_in, keys_out, vals_out, n, dg, hist, (uint64_t *)base, tickets,
+                          index_base);
   HUMID_CUDA(cudaGetLastError());
   *launches += 3;
   return 3;
