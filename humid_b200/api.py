@@ -25,6 +25,7 @@ EXPORTS = [
     "humid_gpu_add_batch", "humid_gpu_add_batch_device", "humid_gpu_finalize", "humid_gpu_counts",
     "humid_gpu_histogram", "humid_gpu_keep_mask", "humid_gpu_cluster_ids", "humid_gpu_debug_words",
     "humid_gpu_debug_neighbours", "humid_gpu_debug_clusters", "humid_gpu_stage_stats", "humid_gpu_stream",
+    "humid_gpu_debug_sort_pairs", "humid_gpu_debug_partition",
 ]
 
 
@@ -79,6 +80,8 @@ def load_library() -> C.CDLL:
     L.humid_gpu_stage_stats.argtypes = [vp, P(StageStat), P(u32)]
     L.humid_gpu_stream.argtypes = [vp]
     L.humid_gpu_stream.restype = vp
+    L.humid_gpu_debug_sort_pairs.argtypes = [vp, vp, vp, u64, C.c_int, C.c_int, vp, vp]
+    L.humid_gpu_debug_partition.argtypes = [vp, C.c_int, vp, u64, u64, u32, vp, u32, vp, vp, vp]
     _lib = L
     return L
 
@@ -111,6 +114,7 @@ class Dedup:
         cfg.expected_tuples = int(expected_tuples)
         cfg.defer_table = 1 if defer_table else 0
         self.word_length, self.n_segments = cfg.word_length, cfg.n_segments
+        self.distance = int(distance)
         rc = self._L.humid_gpu_create(C.byref(cfg), C.byref(self._h))
         if rc != 0:
             msg = self._L.humid_gpu_last_error(None).decode()
@@ -144,6 +148,22 @@ class Dedup:
     def stream(self) -> int:
         """Raw cudaStream_t of the handle (e.g. for torch.cuda.ExternalStream)."""
         return int(self._L.humid_gpu_stream(self._h) or 0)
+
+    # -- test hooks for the device primitives (device pointers as ints) --------------------------
+    def debug_sort_pairs(self, d_keys_in: int, d_vals_in: int, n: int, begin_bit: int, end_bit: int, d_keys_out: int,
+                         d_vals_out: int):
+        self._check(self._L.humid_gpu_debug_sort_pairs(self._h, C.c_void_p(d_keys_in), C.c_void_p(d_vals_in or None), n,
+                                                       begin_bit, end_bit, C.c_void_p(d_keys_out), C.c_void_p(d_vals_out)),
+                    "debug_sort_pairs")
+
+    def debug_partition(self, kind: int, d_keys_in: int, n: int, arg: int, n_parts: int, bases, index_base: int,
+                        d_keys_out: int, d_vals_out: int) -> np.ndarray:
+        counts = np.zeros(16, dtype=np.uint64)
+        b = None if bases is None else np.ascontiguousarray(bases, dtype=np.uint64)
+        self._check(self._L.humid_gpu_debug_partition(self._h, kind, C.c_void_p(d_keys_in), n, arg, n_parts, _ptr(b),
+                                                      index_base, C.c_void_p(d_keys_out), C.c_void_p(d_vals_out or None),
+                                                      _ptr(counts)), "debug_partition")
+        return counts[:n_parts]
 
     def reset(self):
         self._check(self._L.humid_gpu_reset(self._h), "reset")

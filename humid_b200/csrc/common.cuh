@@ -65,7 +65,11 @@ struct Lookup {
 constexpr uint64_t FILTER_MUL = 0x9E3779B97F4A7C15ull;
 __host__ __device__ __forceinline__ uint64_t filter_hash(uint64_t key) { return key * FILTER_MUL; }
 __host__ __device__ __forceinline__ uint32_t filter_bucket(uint64_t hf, uint32_t n_buckets) {
+#ifdef __CUDA_ARCH__
+  return __umulhi((uint32_t)(hf >> 32), n_buckets);  // the 64-bit spelling below was once miscompiled (primitives.cu: DestDigit)
+#else
   return (uint32_t)(((hf >> 32) * (uint64_t)n_buckets) >> 32);
+#endif
 }
 __host__ __device__ __forceinline__ uint32_t filter_fp(uint64_t hf) {
   uint32_t b = (uint32_t)(hf >> 32) & 0xFFu;  // low byte of the high word: not used by the bucket index

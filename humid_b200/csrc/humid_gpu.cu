@@ -92,7 +92,7 @@ void humid_gpu_destroy(humid_gpu *h) {
     if (s.ev_consumed[b]) cudaEventDestroy(s.ev_consumed[b]);
   }
   if (s.copy_stream) cudaStreamDestroy(s.copy_stream);
-  s.tuple_key.release(); s.counters.release(); s.part_key.release(); s.part_index.release(); s.word_flags.release();
+  s.tuple_key.release(); s.counters.release(); s.part_key.release(); s.part_index.release(); s.word_flags.release(); s.join_entries.release(); s.join_entries_out.release();
   s.slots.release(); s.word_key.release(); s.key_alt.release(); s.word_slot.release(); s.slot_alt.release();
   s.word_count.release(); s.word_first.release(); s.entries.release(); s.entries_alt.release();
   s.entry_val.release(); s.entry_val_alt.release(); s.row_ptr.release(); s.deg.release(); s.col.release();
@@ -349,6 +349,53 @@ int humid_gpu_debug_clusters(humid_gpu *h, uint64_t cap, uint64_t *sizes, uint32
     if (sizes) HUMID_CUDA(cudaMemcpyAsync(sizes, s.cluster_size.p, s.n_clusters * 8, cudaMemcpyDeviceToHost, s.stream));
     if (max_leaf_rank)
       HUMID_CUDA(cudaMemcpyAsync(max_leaf_rank, s.cluster_max.p, s.n_clusters * 4, cudaMemcpyDeviceToHost, s.stream));
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+  });
+}
+
+int humid_gpu_debug_sort_pairs(humid_gpu *h, const uint64_t *d_keys_in, const uint32_t *d_vals_in, uint64_t n,
+                               int begin_bit, int end_bit, uint64_t *d_keys_out, uint32_t *d_vals_out) {
+  if (!h) return HUMID_GPU_ERR_ARG;
+  State &s = h->s;
+  if (n == 0) return HUMID_GPU_OK;
+  if (!d_keys_in || !d_keys_out || !d_vals_out || end_bit <= begin_bit || end_bit > 64)
+    return fail(h, HUMID_GPU_ERR_ARG, "debug_sort_pairs: bad arguments");
+  return guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(s.device));
+    s.key_alt.ensure(n);
+    s.entries_alt.ensure(n);
+    s.entry_val.ensure(n);
+    s.entry_val_alt.ensure(n);
+    uint64_t *kb[2] = {s.key_alt.p, s.entries_alt.p};
+    uint32_t *vb[2] = {s.entry_val.p, s.entry_val_alt.p};
+    int launches = 0;
+    int cur = d_vals_in ? radix_sort_bits_pairs(d_keys_in, d_vals_in, kb, vb, n, begin_bit, end_bit, s.scratch, s.stream,
+                                                &launches)
+                        : radix_sort_bits_indexed(d_keys_in, kb, vb, n, begin_bit, end_bit, s.scratch, s.stream,
+                                                  &launches);
+    HUMID_CUDA(cudaMemcpyAsync(d_keys_out, kb[cur], n * 8, cudaMemcpyDeviceToDevice, s.stream));
+    HUMID_CUDA(cudaMemcpyAsync(d_vals_out, vb[cur], n * 4, cudaMemcpyDeviceToDevice, s.stream));
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+  });
+}
+
+int humid_gpu_debug_partition(humid_gpu *h, int kind, const uint64_t *d_keys_in, uint64_t n, uint64_t arg,
+                              uint32_t n_parts, const uint64_t *bases, uint32_t index_base, uint64_t *d_keys_out,
+                              uint32_t *d_vals_out, uint64_t *counts) {
+  if (!h) return HUMID_GPU_ERR_ARG;
+  State &s = h->s;
+  if (kind < 0 || kind > 2 || (n && (!d_keys_in || !d_keys_out)) || (kind != 2 && n && !d_vals_out) ||
+      (kind != 0 && (!counts || n_parts == 0 || n_parts > 16)) || (kind == 2 && !bases))
+    return fail(h, HUMID_GPU_ERR_ARG, "debug_partition: bad arguments");
+  return guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(s.device));
+    int launches = 0;
+    if (kind == 0)
+      partition_by_slot_u64(d_keys_in, nullptr, index_base, d_keys_out, d_vals_out, n, arg, s.scratch, s.stream, &launches);
+    else if (kind == 1)
+      partition_by_block_hash(d_keys_in, index_base, d_keys_out, d_vals_out, n, arg, n_parts, counts, s.scratch, s.stream);
+    else
+      partition_by_row_owner(d_keys_in, d_keys_out, n, bases, n_parts, counts, s.scratch, s.stream);
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
   });
 }

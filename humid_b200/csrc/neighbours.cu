@@ -39,13 +39,7 @@ __device__ __forceinline__ void emit_pair(uint64_t *pairs, uint64_t cap, unsigne
   }
 }
 
-constexpr int HAM_MAX_D = 8;
 constexpr uint64_t LETTER_LOW = 0x5555555555555555ull;
-
-struct Blocks {
-  uint32_t n_blocks;
-  uint64_t mask[HAM_MAX_D + 1];  // bits of block b (block 0 = first letters = highest bits)
-};
 
 // lowest block on which two words (x = a ^ b) agree; n_blocks if none.  Unrolled with constant
 // indices: B is a kernel parameter and must stay in the constant bank, not be copied to the stack.
@@ -72,14 +66,33 @@ __device__ __forceinline__ bool linked(uint64_t a, uint64_t b, uint32_t d) {
 // means the order IS rank order.  A group is skipped (and its members flagged with bit `block`)
 // iff it has more than group_cap members; every member reaches the same verdict by looking at
 // most group_cap positions back and forth.
+//
+// EMIT (state.cuh): JOIN_PAIRS_DEG   pairs[k] = a << 32 | b, deg[a]++, deg[b]++        (single GPU)
+//                   JOIN_DIRECTED    out[2k] = a << 32 | (col_base + b), out[2k+1] = b << 32 | (col_base + a),
+//                                    deg (if not null) counted per row                  (shards)
+// group_cap == JOIN_NO_CAP: every group is walked whatever its size, nothing is flagged.
 constexpr int JOIN_LOCAL_HITS = 6;
 constexpr int JOIN_THREADS = 512;
+
+template <int EMIT>
+__device__ __forceinline__ void join_emit(uint64_t *out, uint64_t pos, uint32_t a, uint32_t b, uint32_t col_base,
+                                          uint32_t *deg) {
+  if (EMIT == JOIN_PAIRS_DEG) {
+    out[pos] = ((uint64_t)a << 32) | b;
+  } else {
+    out[2 * pos] = ((uint64_t)a << 32) | (col_base + b);
+    out[2 * pos + 1] = ((uint64_t)b << 32) | (col_base + a);
+  }
+  if (deg) atomicAdd(deg + b, 1u);
+}
+
+template <int EMIT>
 __global__ void __launch_bounds__(JOIN_THREADS)
     hamming_join_kernel(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ rank, uint64_t U, uint32_t d,
                         const Blocks B, uint32_t block, uint64_t mask, uint32_t group_cap,
                         uint64_t *__restrict__ pairs,
                         uint64_t cap, unsigned long long *__restrict__ counter, uint32_t *__restrict__ deg,
-                        uint32_t *__restrict__ flags, unsigned long long *__restrict__ n_flagged) {
+                        uint32_t col_base, uint32_t *__restrict__ flags, unsigned long long *__restrict__ n_flagged) {
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = i < U;
   const uint64_t w = live ? keys[i] : 0ull;
@@ -93,7 +106,8 @@ __global__ void __launch_bounds__(JOIN_THREADS)
   if (live) {
     // members before i (stop as soon as the group is known to be too large)
     uint32_t before = 0;
-    while (before < group_cap && before < i && (keys[i - 1 - before] & mask) == g) before++;
+    if (group_cap != JOIN_NO_CAP)
+      while (before < group_cap && before < i && (keys[i - 1 - before] & mask) == g) before++;
     uint32_t after = 0;
     if (before < group_cap) {
       const uint32_t room = group_cap - before;  // the group fits iff after < room
@@ -113,9 +127,9 @@ __global__ void __launch_bounds__(JOIN_THREADS)
 #pragma unroll
           for (int k = 0; k < JOIN_LOCAL_HITS; k++, pos++) {
             const uint32_t rb = rank ? rank[i + hits[k]] : (uint32_t)(i + hits[k]);
-            if (pos < cap) { pairs[pos] = ((uint64_t)ri << 32) | rb; atomicAdd(deg + rb, 1u); }
+            if (pos < cap) join_emit<EMIT>(pairs, pos, ri, rb, col_base, deg);
           }
-          if (pos <= cap) atomicAdd(deg + ri, nh);
+          if (pos <= cap && deg) atomicAdd(deg + ri, nh);
           nh = 0;
         }
 #pragma unroll
@@ -154,11 +168,10 @@ __global__ void __launch_bounds__(JOIN_THREADS)
       for (int k = 0; k < JOIN_LOCAL_HITS; k++) {
         if (k < (int)nh) {
           const uint32_t rb = rank ? rank[i + hits[k]] : (uint32_t)(i + hits[k]);
-          pairs[pos + k] = ((uint64_t)ri << 32) | rb;
-          atomicAdd(deg + rb, 1u);
+          join_emit<EMIT>(pairs, pos + k, ri, rb, col_base, deg);
         }
       }
-      atomicAdd(deg + ri, nh);
+      if (deg) atomicAdd(deg + ri, nh);
     }
   }
 }
@@ -208,7 +221,20 @@ __global__ void __launch_bounds__(128)
   }
 }
 
-static Blocks make_blocks(uint32_t n, uint32_t d, int lo_bit[], int hi_bit[]) {
+void launch_hamming_join(State &s, int emit, const uint64_t *keys, const uint32_t *rank, uint64_t n_words, const Blocks &B,
+                         uint32_t block, uint32_t group_cap, uint64_t *out, uint64_t cap, unsigned long long *counter,
+                         uint32_t *deg, uint32_t col_base, uint32_t *flags, unsigned long long *n_flagged) {
+  const uint32_t d = s.cfg.distance;
+  const unsigned grid = grid_for(n_words, JOIN_THREADS);
+  if (emit == JOIN_PAIRS_DEG)
+    hamming_join_kernel<JOIN_PAIRS_DEG><<<grid, JOIN_THREADS, 0, s.stream>>>(
+        keys, rank, n_words, d, B, block, B.mask[block], group_cap, out, cap, counter, deg, col_base, flags, n_flagged);
+  else
+    hamming_join_kernel<JOIN_DIRECTED><<<grid, JOIN_THREADS, 0, s.stream>>>(
+        keys, rank, n_words, d, B, block, B.mask[block], group_cap, out, cap, counter, deg, col_base, flags, n_flagged);
+}
+
+Blocks make_blocks(uint32_t n, uint32_t d, int lo_bit[], int hi_bit[]) {
   Blocks B{};
   B.n_blocks = d + 1;
   for (uint32_t b = 0; b <= d; b++) {
@@ -276,8 +302,8 @@ int stage_neighbours_hamming(State &s) {
                                                             "join_hamming_b3", "join_hamming_b4", "join_hamming_b5",
                                                             "join_hamming_b6", "join_hamming_b7", "join_hamming_b8"};
       Timed t(s, join_names[b], U, U * (8 + 8 + (rank ? 4 : 0)));
-      hamming_join_kernel<<<grid_for(U, JOIN_THREADS), JOIN_THREADS, 0, s.stream>>>(keys, rank, U, d, B, b, B.mask[b], group_cap, s.entries.p, cap,
-                                                                  counter, s.deg.p, s.word_flags.p, n_flagged);
+      launch_hamming_join(s, JOIN_PAIRS_DEG, keys, rank, U, B, b, group_cap, s.entries.p, cap, counter, s.deg.p, 0u,
+                          s.word_flags.p, n_flagged);
       k++;
     }
     HUMID_CUDA(cudaMemcpyAsync(&s.n_flagged, n_flagged, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));

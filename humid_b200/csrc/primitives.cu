@@ -233,7 +233,7 @@ __global__ void __launch_bounds__(RS_THREADS) digit_hist_kernel(const uint64_t *
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 template <bool HAS_VALS, class Digit>
-__global__ void __launch_bounds__(RS_THREADS)
+__global__ void __launch_bounds__(RS_THREADS, 3)
     radix_pass_kernel(const uint64_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
                       uint64_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n, uint32_t n_tiles,
                       Digit digit_of, const uint32_t *__restrict__ digit_base, volatile uint64_t *status,
@@ -452,29 +452,94 @@ int radix_sort_bits_indexed(const uint64_t *keys_in, uint64_t *keys[2], uint32_t
   return radix_sort_impl(keys_in, nullptr, keys, index, 0, n, begin_bit, end_bit, scratch, stream, launches);
 }
 
-int partition_by_slot_u64(const uint64_t *keys_in, const uint32_t *vals_in, uint32_t index_base, uint64_t *keys_out,
-                          uint32_t *vals_out, uint64_t n, uint64_t slot_mask, Scratch &scratch, cudaStream_t stream,
-                          int *launches) {
+// digit = destination part of a word in the exchange of one join block: hash of the block's letters
+struct DestDigit {
+  uint64_t mask;
+  uint32_t n_parts;
+  __device__ __forceinline__ uint32_t operator()(uint64_t key) const {
+    // (high word of the hash * n_parts) >> 32.  Written with the intrinsic: nvcc 12.9 folds the
+    // 64-bit form "((h >> 32) * n) >> 32" into the shared-memory address arithmetic of the
+    // histogram kernel as h_hi * (n >> 30), i.e. always part 0 (seen in the SASS and on the device).
+    return __umulhi((uint32_t)(mix64(key & mask) >> 32), n_parts);
+  }
+};
+// digit = owner of the row of a directed entry (row << 32 | column), rows are global ranks
+struct OwnerDigit {
+  uint32_t n_parts;
+  uint32_t bases[17];
+  __device__ __forceinline__ uint32_t operator()(uint64_t entry) const {
+    const uint32_t row = (uint32_t)(entry >> 32);
+    uint32_t p = 0;
+#pragma unroll
+    for (int q = 1; q < 16; q++) p += (q < (int)n_parts && row >= bases[q]) ? 1u : 0u;
+    return p;
+  }
+};
+
+// One stable partition pass by `dg`; host_counts (may be nullptr) receives the size of the first
+// n_counts parts.
+template <bool HAS_VALS, class Digit>
+static int partition_pass(const uint64_t *keys_in, const uint32_t *vals_in, uint32_t index_base, uint64_t *keys_out,
+                          uint32_t *vals_out, uint64_t n, Digit dg, uint64_t *host_counts, uint32_t n_counts,
+                          Scratch &scratch, cudaStream_t stream) {
+  for (uint32_t p = 0; host_counts && p < n_counts; p++) host_counts[p] = 0;
   if (n == 0) return 0;
-  if (n >= 0xFFFFFFFFull) throw CudaError{"partition_by_slot_u64: more than 2^32-1 elements"};
-  int bits = 0;
-  while ((slot_mask >> bits) != 0) bits++;
-  const SlotDigit dg{slot_mask, bits > 8 ? bits - 8 : 0};
+  if (n >= 0xFFFFFFFFull) throw CudaError{"partition: more than 2^32-1 elements"};
   const uint32_t n_tiles = (uint32_t)((n + RS_TILE - 1) / RS_TILE);
   const size_t status_bytes = (size_t)n_tiles * RS_BINS * sizeof(uint64_t);
-  const size_t tail_bytes = (RS_MAX_PASSES + RS_BINS) * sizeof(uint32_t);
+  const size_t tail_bytes = (RS_MAX_PASSES + 2 * RS_BINS) * sizeof(uint32_t);
   char *base = (char *)scratch.get(status_bytes + tail_bytes);
   uint32_t *tickets = (uint32_t *)(base + status_bytes);
   uint32_t *hist = tickets + RS_MAX_PASSES;
+  uint32_t *counts = hist + RS_BINS;
   HUMID_CUDA(cudaMemsetAsync(base, 0, status_bytes + tail_bytes, stream));
   unsigned hist_grid = (unsigned)std::min<uint64_t>((n + RS_THREADS - 1) / RS_THREADS, 148 * 8);
   digit_hist_kernel<<<hist_grid, RS_THREADS, 0, stream>>>(keys_in, n, dg, hist);
+  if (host_counts) HUMID_CUDA(cudaMemcpyAsync(counts, hist, RS_BINS * sizeof(uint32_t), cudaMemcpyDeviceToDevice, stream));
   radix_digit_bases_kernel<<<1, RS_THREADS, 0, stream>>>(hist);
-  launch_radix_pass<true>(n_tiles, stream, keys_in, vals_in, keys_out, vals_out, n, dg, hist, (uint64_t *)base, tickets,
-                          index_base);
+  launch_radix_pass<HAS_VALS>(n_tiles, stream, keys_in, vals_in, keys_out, vals_out, n, dg, hist, (uint64_t *)base,
+                              tickets, index_base);
   HUMID_CUDA(cudaGetLastError());
-  *launches += 3;
+  if (host_counts) {
+    uint32_t hc[RS_BINS];
+    HUMID_CUDA(cudaMemcpyAsync(hc, counts, n_counts * sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+    HUMID_CUDA(cudaStreamSynchronize(stream));
+    for (uint32_t p = 0; p < n_counts; p++) host_counts[p] = hc[p];
+  }
   return 3;
+}
+
+int partition_by_slot_u64(const uint64_t *keys_in, const uint32_t *vals_in, uint32_t index_base, uint64_t *keys_out,
+                          uint32_t *vals_out, uint64_t n, uint64_t slot_mask, Scratch &scratch, cudaStream_t stream,
+                          int *launches) {
+  int bits = 0;
+  while ((slot_mask >> bits) != 0) bits++;
+  const SlotDigit dg{slot_mask, bits > 8 ? bits - 8 : 0};
+  int k = partition_pass<true>(keys_in, vals_in, index_base, keys_out, vals_out, n, dg, nullptr, 0, scratch, stream);
+  *launches += k;
+  return k;
+}
+
+int partition_by_block_hash(const uint64_t *keys_in, uint32_t index_base, uint64_t *keys_out, uint32_t *index_out,
+                            uint64_t n, uint64_t block_mask, uint32_t n_parts, uint64_t *host_counts, Scratch &scratch,
+                            cudaStream_t stream) {
+  return partition_pass<true>(keys_in, nullptr, index_base, keys_out, index_out, n, DestDigit{block_mask, n_parts},
+                              host_counts, n_parts, scratch, stream);
+}
+
+int partition_by_row_owner(const uint64_t *entries_in, uint64_t *entries_out, uint64_t n, const uint64_t *bases,
+                           uint32_t n_parts, uint64_t *host_counts, Scratch &scratch, cudaStream_t stream) {
+  OwnerDigit dg{};
+  dg.n_parts = n_parts;
+  for (uint32_t p = 0; p <= n_parts && p < 17; p++) dg.bases[p] = (uint32_t)bases[p];
+  return partition_pass<false>(entries_in, nullptr, 0u, entries_out, nullptr, n, dg, host_counts, n_parts, scratch,
+                               stream);
+}
+
+int radix_sort_bits_pairs(const uint64_t *keys_in, const uint32_t *vals_in, uint64_t *keys[2], uint32_t *vals[2],
+                          uint64_t n, int begin_bit, int end_bit, Scratch &scratch, cudaStream_t stream, int *launches) {
+  if (n == 0 || end_bit <= begin_bit) throw CudaError{"radix_sort_bits_pairs: nothing to sort by"};
+  return radix_sort_impl(keys_in, vals_in, keys, vals, 0, n, begin_bit, end_bit, scratch, stream, launches);
 }
 
 }  // namespace humid

@@ -56,4 +56,18 @@ int partition_by_slot_u64(const uint64_t *keys_in, const uint32_t *vals_in, uint
                           uint32_t *vals_out, uint64_t n, uint64_t slot_mask, Scratch &scratch, cudaStream_t stream,
                           int *launches);
 
+// Multi-GPU block join (shard.cu).  Stable partition of the words by the part that joins their
+// block (hash of the letters under block_mask): (key, index_base + i) pairs grouped by part,
+// host_counts[p] = words for part p.  Synchronises the stream.
+int partition_by_block_hash(const uint64_t *keys_in, uint32_t index_base, uint64_t *keys_out, uint32_t *index_out,
+                            uint64_t n, uint64_t block_mask, uint32_t n_parts, uint64_t *host_counts, Scratch &scratch,
+                            cudaStream_t stream);
+// Directed entries (row << 32 | column, rows = global ranks) grouped by the part owning the row
+// (bases[p] <= row < bases[p+1]).  Synchronises the stream.
+int partition_by_row_owner(const uint64_t *entries_in, uint64_t *entries_out, uint64_t n, const uint64_t *bases,
+                           uint32_t n_parts, uint64_t *host_counts, Scratch &scratch, cudaStream_t stream);
+// Stable sort of (key, value) pairs by bits [begin_bit, end_bit); inputs are only read.
+int radix_sort_bits_pairs(const uint64_t *keys_in, const uint32_t *vals_in, uint64_t *keys[2], uint32_t *vals[2],
+                          uint64_t n, int begin_bit, int end_bit, Scratch &scratch, cudaStream_t stream, int *launches);
+
 }  // namespace humid

@@ -80,253 +80,23 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-// ---- probe ---------------------------------------------------------------------------------
-// One thread per (word, first modified position); upward variants with at most d modified
-// positions (strictly increasing), exactly the enumeration of hammingd_probe_kernel.
-// MODE 0: count the queries per destination part.  MODE 1: look up the variants this shard
-// owns, append the others to the destination's region of the query buffers.
-constexpr int SHARD_MAX_D = 8;
-
-template <typename F>
-__device__ __forceinline__ void for_each_upward_variant(uint64_t w, uint32_t n, uint32_t d, uint32_t p1, F &&f) {
-  uint32_t pos[SHARD_MAX_D];
-  uint32_t let[SHARD_MAX_D];
-  uint64_t cur = w;
-  int depth = 0;
-  pos[0] = p1;
-  let[0] = (uint32_t)(w >> (2 * (n - 1 - p1))) & 3u;
-  while (true) {
-    uint32_t sh = 2 * (n - 1 - pos[depth]);
-    uint32_t orig = (uint32_t)(w >> sh) & 3u;
-    if (++let[depth] > 3) {
-      cur = (cur & ~(3ull << sh)) | ((uint64_t)orig << sh);
-      if (depth == 0) break;
-      if (++pos[depth] >= n) { depth--; continue; }
-      let[depth] = (uint32_t)(w >> (2 * (n - 1 - pos[depth]))) & 3u;
-      continue;
-    }
-    cur = (cur & ~(3ull << sh)) | ((uint64_t)let[depth] << sh);
-    f(cur);
-    if (depth + 1 < (int)d && pos[depth] + 1 < n) {
-      depth++;
-      pos[depth] = pos[depth - 1] + 1;
-      let[depth] = (uint32_t)(w >> (2 * (n - 1 - pos[depth]))) & 3u;
-    }
-  }
-}
-
-template <int MODE>
+// ---- block join across shards ---------------------------------------------------------------
+// Directed entries (global row << 32 | global column) that arrived for this shard's rows: rows
+// become shard-local, the list lengths are counted.
 __global__ void __launch_bounds__(256)
-    shard_probe_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, uint32_t d, const Layout L,
-                       const Lookup lk, unsigned long long *__restrict__ part_counts /* MODE 0: totals; MODE 1: cursors */,
-                       uint64_t *__restrict__ q_keys, uint32_t *__restrict__ q_src, uint64_t *__restrict__ entries,
-                       uint64_t cap, unsigned long long *__restrict__ entry_counter, uint32_t *__restrict__ deg) {
-  __shared__ uint32_t cnt[HUMID_MAX_PARTS];
-  __shared__ unsigned long long base[HUMID_MAX_PARTS];
-  if (threadIdx.x < HUMID_MAX_PARTS) cnt[threadIdx.x] = 0;
-  __syncthreads();
-  uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  uint64_t r = gid / n;
-  const bool live = r < U;
-  const uint32_t p1 = live ? (uint32_t)(gid - r * n) : 0;
-  const uint64_t w = live ? word_key[r] : 0ull;
-  if (live)
-    for_each_upward_variant(w, n, d, p1, [&](uint64_t v) {
-      if (v >= L.hi) atomicAdd(&cnt[owner_of(L, v)], 1u);
-    });
-  __syncthreads();
-  if (threadIdx.x < L.n_parts) {
-    uint32_t c = cnt[threadIdx.x];
-    base[threadIdx.x] = c ? atomicAdd(part_counts + threadIdx.x, (unsigned long long)c) : 0ull;
-    cnt[threadIdx.x] = 0;
-  }
-  if (MODE == 0) return;
-  __syncthreads();
-  if (!live) return;
-  const uint32_t me = L.base + (uint32_t)r;
-  for_each_upward_variant(w, n, d, p1, [&](uint64_t v) {
-    if (v < L.hi) {
-      uint32_t hit = lookup_rank(lk, v);
-      if (hit != NONE32) {
-        const unsigned long long pos = reserve_slots(entry_counter, 2u);
-        if (pos + 2 <= cap) {
-          // rows are shard-local, columns global
-          entries[pos] = (r << 32) | (uint64_t)(L.base + hit);
-          entries[pos + 1] = ((uint64_t)hit << 32) | me;
-          atomicAdd(deg + r, 1u);
-          atomicAdd(deg + hit, 1u);
-        }
-      }
-    } else {
-      const uint32_t o = owner_of(L, v);
-      unsigned long long pos = base[o] + atomicAdd(&cnt[o], 1u);
-      q_keys[pos] = v;
-      q_src[pos] = me;
-    }
-  });
-}
-
-// d == 1: one thread per word (the single-GPU hamming1_probe_kernel plus routing).  An upward
-// variant is larger than its word, so it is either in this shard's range or in a later one.
-// Remote variants are counted per destination in shared memory, one reservation per CTA and
-// part, then the enumeration is repeated to write them.
-template <int MODE>
-__global__ void __launch_bounds__(128)
-    shard_probe1_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, uint32_t scan_from,
-                        const Layout L, const Lookup lk,
-                        unsigned long long *__restrict__ part_counts, uint64_t *__restrict__ q_keys,
-                        uint32_t *__restrict__ q_src, uint64_t *__restrict__ entries, uint64_t cap,
-                        unsigned long long *__restrict__ entry_counter, uint32_t *__restrict__ deg) {
-  __shared__ uint32_t cnt[HUMID_MAX_PARTS];
-  __shared__ unsigned long long base[HUMID_MAX_PARTS];
-  if (threadIdx.x < HUMID_MAX_PARTS) cnt[threadIdx.x] = 0;
-  __syncthreads();
-  const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const bool live = r < U;
-  const uint64_t w = live ? ld_stream_u64(word_key + r) : 0ull;
-  // variants at position p exceed the range only if w + (3 << sh) can reach hi at all
-  uint32_t p_remote_end = 0;  // positions [0, p_remote_end) may produce remote variants
-  if (live)
-    while (p_remote_end < n && w + (3ull << (2 * (n - 1 - p_remote_end))) >= L.hi) p_remote_end++;
-  for (uint32_t p = 0; p < p_remote_end; p++) {
-    const uint32_t sh = 2 * (n - 1 - p);
-    const uint32_t wl = (uint32_t)(w >> sh) & 3u;
-    for (uint32_t c = 1; wl + c <= 3u; c++) {
-      const uint64_t v = w + ((uint64_t)c << sh);
-      if (v >= L.hi) atomicAdd(&cnt[owner_of(L, v)], 1u);
-    }
-  }
-  __syncthreads();
-  if (threadIdx.x < L.n_parts) {
-    uint32_t c = cnt[threadIdx.x];
-    base[threadIdx.x] = c ? atomicAdd(part_counts + threadIdx.x, (unsigned long long)c) : 0ull;
-    cnt[threadIdx.x] = 0;
-  }
-  if (MODE == 0) return;
-  __syncthreads();
-  const uint32_t me = L.base + (uint32_t)r;
-  const uint64_t hw = filter_hash(w);
-  const uint64_t pol_keep = l2_policy_evict_last();
-  constexpr int LOCAL_HITS = 6;
-  constexpr uint32_t SCAN_CAP = 32;
-  uint32_t hits[LOCAL_HITS];
-  uint32_t nh = 0;
-  // positions >= scan_from: the shard's own words right behind w in rank order (see
-  // hamming1_probe_kernel); variants beyond the shard's range still travel as queries
-  uint32_t probe_end = n;
-  if (live && scan_from < n) {
-    const uint32_t low = 2 * (n - scan_from);
-    const uint64_t prefix = w >> low;
-    probe_end = scan_from;
-    for (uint64_t j = r + 1; j < U; j++) {
-      const uint64_t k = word_key[j];
-      if ((k >> low) != prefix) break;
-      if (j - r > SCAN_CAP || nh == LOCAL_HITS) { probe_end = n; nh = 0; break; }
-      const uint64_t x = k ^ w;
-      if (__popcll((x | (x >> 1)) & 0x5555555555555555ull) == 1) hits[nh++] = (uint32_t)j;
-    }
-  }
-  for (uint32_t p = 0; p < n; p++) {
-    const uint32_t sh = 2 * (n - 1 - p);
-    const uint32_t wl = (uint32_t)(w >> sh) & 3u;
-    const uint64_t step = FILTER_MUL << sh;
-    uint4 bkt[3];
-    uint64_t hf[3];
-    bool local[3];
-#pragma unroll
-    for (uint32_t c = 1; c < 4; c++) {
-      hf[c - 1] = hw + step * c;
-      const uint64_t v = w + ((uint64_t)c << sh);
-      const bool valid = live && wl + c <= 3u;
-      local[c - 1] = valid && v < L.hi && p < probe_end;
-      const bool remote = valid && v >= L.hi;
-      if (local[c - 1]) bkt[c - 1] = ld_hint_u128(lk.filter + filter_bucket(hf[c - 1], lk.n_buckets), pol_keep);
-      if (remote) {
-        const uint32_t o = owner_of(L, v);
-        const unsigned long long pos = base[o] + atomicAdd(&cnt[o], 1u);
-        q_keys[pos] = v;
-        q_src[pos] = me;
-      }
-    }
-#pragma unroll
-    for (uint32_t c = 1; c < 4; c++) {
-      if (local[c - 1] && filter_match(bkt[c - 1], hf[c - 1])) {
-        const uint32_t hit = table_rank(lk, w + ((uint64_t)c << sh));
-        if (hit != NONE32) {
-          if (nh == LOCAL_HITS) {
-            unsigned long long pos = atomicAdd(entry_counter, 2ull * nh);
-            if (pos + 2ull * nh <= cap) {
-              for (uint32_t k = 0; k < nh; k++) {
-                entries[pos + 2 * k] = (r << 32) | (uint64_t)(L.base + hits[k]);
-                entries[pos + 2 * k + 1] = ((uint64_t)hits[k] << 32) | me;
-                atomicAdd(deg + hits[k], 1u);
-              }
-              atomicAdd(deg + r, nh);
-            }
-            nh = 0;
-          }
-          hits[nh++] = hit;
-        }
-      }
-    }
-  }
-  const uint32_t lane = lane_id();
-  uint32_t inc = nh;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-    if ((int)lane >= o) inc += t;
-  }
-  const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
-  if (total == 0) return;
-  unsigned long long wbase = 0;
-  if (lane == 31) wbase = atomicAdd(entry_counter, 2ull * total);
-  wbase = __shfl_sync(0xffffffffu, wbase, 31);
-  if (nh) {
-    unsigned long long pos = wbase + 2ull * (inc - nh);
-    if (pos + 2ull * nh <= cap) {
-      for (uint32_t k = 0; k < nh; k++) {
-        entries[pos + 2 * k] = (r << 32) | (uint64_t)(L.base + hits[k]);
-        entries[pos + 2 * k + 1] = ((uint64_t)hits[k] << 32) | me;
-        atomicAdd(deg + hits[k], 1u);
-      }
-      atomicAdd(deg + r, nh);
-    }
-  }
-}
-
-__global__ void __launch_bounds__(256)
-    shard_answer_kernel(const uint64_t *__restrict__ q_keys, const uint32_t *__restrict__ q_src, uint64_t n,
-                        const Layout L, const Lookup lk, uint32_t *__restrict__ answers,
-                        uint64_t *__restrict__ entries, uint64_t cap, unsigned long long *__restrict__ entry_counter,
-                        uint32_t *__restrict__ deg) {
+    import_entries_kernel(const uint64_t *__restrict__ in, uint64_t n, uint32_t base, uint64_t U,
+                          uint64_t *__restrict__ entries, uint32_t *__restrict__ deg, unsigned long long *misrouted) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  uint32_t hit = lookup_rank(lk, q_keys[i]);
-  answers[i] = hit == NONE32 ? NONE32 : L.base + hit;
-  if (hit != NONE32) {
-    const unsigned long long pos = reserve_slots(entry_counter);
-    if (pos < cap) {
-      entries[pos] = ((uint64_t)hit << 32) | q_src[i];  // result leaf <- walk leaf
-      atomicAdd(deg + hit, 1u);
-    }
+  const uint64_t e = in[i];
+  const uint32_t row = (uint32_t)(e >> 32) - base;
+  if (row >= U) {  // an entry for a row this shard does not own: the host mixed up the exchange
+    atomicAdd(misrouted, 1ull);
+    entries[i] = 0;
+    return;
   }
-}
-
-__global__ void __launch_bounds__(256)
-    shard_apply_kernel(const uint32_t *__restrict__ q_src, const uint32_t *__restrict__ answers, uint64_t n,
-                       const Layout L, uint64_t *__restrict__ entries, uint64_t cap,
-                       unsigned long long *__restrict__ entry_counter, uint32_t *__restrict__ deg) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  uint32_t a = answers[i];
-  if (a != NONE32) {
-    const unsigned long long pos = reserve_slots(entry_counter);
-    if (pos < cap) {
-      entries[pos] = ((uint64_t)(q_src[i] - L.base) << 32) | a;  // walk leaf <- result leaf
-      atomicAdd(deg + (q_src[i] - L.base), 1u);
-    }
-  }
+  entries[i] = ((uint64_t)row << 32) | (uint32_t)e;
+  atomicAdd(deg + row, 1u);
 }
 
 // ---- graph ---------------------------------------------------------------------------------
@@ -489,7 +259,7 @@ int humid_gpu_shard_begin(humid_gpu *h, uint64_t tuple_offset, uint64_t *n_usabl
   if (s.finalized || s.shard_mode) return fail(h, HUMID_GPU_ERR_ARG, "shard_begin: wrong call order");
   if (s.cfg.edit && s.cfg.distance >= 2)
     return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "edit distance >= 2 is not sharded (use one GPU)");
-  if (s.cfg.distance > SHARD_MAX_D) return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "distance > 8");
+  if (s.cfg.distance > (uint32_t)HAM_MAX_D) return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "distance > 8");
   if (tuple_offset + s.n_tuples >= 0xFFFFFFFFull) return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "more than 2^32-2 tuples");
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
@@ -592,7 +362,7 @@ int humid_gpu_shard_import_tuples(humid_gpu *h, const uint64_t *d_keys, const ui
     s.src_keys = s.shard_keys.p;
     s.src_index = s.shard_index.p;
     s.src_n = n;
-    stage_build_table(s);  // the single-GPU table / sort / rank / filter stages on this key range
+    stage_build_table(s, false);  // the single-GPU table / sort / column stages on this key range
     s.n_shard_words = s.unique;
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     *n_shard_words = s.unique;
@@ -613,112 +383,158 @@ int humid_gpu_shard_set_layout(humid_gpu *h, uint32_t part, uint32_t n_parts, co
   return HUMID_GPU_OK;
 }
 
-int humid_gpu_shard_probe_count(humid_gpu *h, uint64_t *counts) {
-  if (int rc = require_shard(h, true)) return rc;
-  State &s = h->s;
-  if (!counts) return HUMID_GPU_ERR_ARG;
-  return guarded(h, [&] {
-    HUMID_CUDA(cudaSetDevice(s.device));
-    const uint64_t U = s.n_shard_words;
-    const uint32_t n = s.cfg.word_length, d = s.cfg.distance;
-    unsigned long long *pc = s.counters.p + 16;
-    HUMID_CUDA(cudaMemsetAsync(pc, 0, HUMID_MAX_PARTS * sizeof(unsigned long long), s.stream));
-    if (U && d) {
-      Timed t(s, "shard_probe_count", U, U * 8);
-      if (d == 1 && s.filter_buckets)
-        shard_probe1_kernel<0><<<grid_for(U, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, scan_from_position(U, n),
-                                                                       layout_of(s), s.lookup(), pc,
-                                                                       nullptr, nullptr, nullptr, 0, nullptr, nullptr);
-      else
-        shard_probe_kernel<0><<<grid_for(U * n, 256), 256, 0, s.stream>>>(s.word_key.p, U, n, d, layout_of(s),
-                                                                          s.lookup(), pc, nullptr, nullptr, nullptr, 0,
-                                                                          nullptr, nullptr);
-    }
-    HUMID_CUDA(cudaGetLastError());
-    unsigned long long host[HUMID_MAX_PARTS];
-    HUMID_CUDA(cudaMemcpyAsync(host, pc, sizeof(host), cudaMemcpyDeviceToHost, s.stream));
-    HUMID_CUDA(cudaStreamSynchronize(s.stream));
-    for (uint32_t p = 0; p < s.n_parts; p++) counts[p] = host[p];
-  });
+// Block geometry of the job (neighbours.cu); in shard mode the joins never cap a group.
+static Blocks shard_blocks(const State &s, int lo_bit[], int hi_bit[]) {
+  return make_blocks(s.cfg.word_length, s.cfg.distance, lo_bit, hi_bit);
 }
 
-int humid_gpu_shard_probe(humid_gpu *h, uint64_t *d_query_keys, uint32_t *d_query_src, const uint64_t *offsets) {
+int humid_gpu_shard_join_local(humid_gpu *h, uint64_t *n_entries) {
   if (int rc = require_shard(h, true)) return rc;
   State &s = h->s;
-  if (!offsets) return HUMID_GPU_ERR_ARG;
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
     const uint64_t U = s.n_shard_words;
-    const uint32_t n = s.cfg.word_length, d = s.cfg.distance;
+    const uint32_t d = s.cfg.distance;
     s.n_entries = 0;
     s.deg.ensure(U + 1);
     if (U) HUMID_CUDA(cudaMemsetAsync(s.deg.p, 0, U * sizeof(uint32_t), s.stream));
+    if (n_entries) *n_entries = 0;
     if (U == 0 || d == 0) return;
-    unsigned long long *pc = s.counters.p + 16;
-    unsigned long long cursors[HUMID_MAX_PARTS] = {0};
-    for (uint32_t p = 0; p < s.n_parts; p++) cursors[p] = offsets[p];
+    if (d > HAM_MAX_D) throw CudaError{"Hamming distance > 8 is not supported"};
+    int lo_bit[HAM_MAX_D + 1], hi_bit[HAM_MAX_D + 1];
+    const Blocks B = shard_blocks(s, lo_bit, hi_bit);
+    unsigned long long *counter = s.counters.p + 2;
     uint64_t cap = std::max<uint64_t>(s.entries.cap, std::max<uint64_t>(4 * U, 1u << 20));
+    uint64_t pairs = 0;
     for (int attempt = 0; attempt < 2; attempt++) {
       s.entries.ensure(cap);
       cap = s.entries.cap;
-      HUMID_CUDA(cudaMemcpyAsync(pc, cursors, sizeof(cursors), cudaMemcpyHostToDevice, s.stream));
-      HUMID_CUDA(cudaMemsetAsync(s.counters.p + 2, 0, sizeof(unsigned long long), s.stream));
+      HUMID_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned long long), s.stream));
       HUMID_CUDA(cudaMemsetAsync(s.deg.p, 0, U * sizeof(uint32_t), s.stream));
       {
-        double probes = d == 1 ? 1.5 * n : d == 2 ? 1.5 * n + 2.25 * n * (n - 1) / 2.0 : 0.0;
-        Timed t(s, "shard_probe", U, (uint64_t)(U * 8.0 * (1.0 + probes)));
-        if (d == 1 && s.filter_buckets)
-          shard_probe1_kernel<1><<<grid_for(U, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, scan_from_position(U, n),
-                                                                         layout_of(s), s.lookup(), pc,
-                                                                         d_query_keys, d_query_src, s.entries.p, cap,
-                                                                         s.counters.p + 2, s.deg.p);
-        else
-          shard_probe_kernel<1><<<grid_for(U * n, 256), 256, 0, s.stream>>>(s.word_key.p, U, n, d, layout_of(s),
-                                                                            s.lookup(), pc, d_query_keys, d_query_src,
-                                                                            s.entries.p, cap, s.counters.p + 2, s.deg.p);
+        Timed t(s, "shard_join_local", U, U * 16);
+        launch_hamming_join(s, JOIN_DIRECTED, s.word_key.p, nullptr, U, B, 0, JOIN_NO_CAP, s.entries.p, cap / 2, counter,
+                            s.deg.p, (uint32_t)s.bases[s.part], nullptr, nullptr);
       }
       HUMID_CUDA(cudaGetLastError());
-      HUMID_CUDA(cudaMemcpyAsync(&s.n_entries, s.counters.p + 2, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+      HUMID_CUDA(cudaMemcpyAsync(&pairs, counter, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
       HUMID_CUDA(cudaStreamSynchronize(s.stream));
-      if (s.n_entries <= cap) break;
-      cap = s.n_entries;
+      if (2 * pairs <= cap) break;
+      cap = 2 * pairs;
     }
+    s.n_entries = 2 * pairs;
+    if (n_entries) *n_entries = s.n_entries;
   });
 }
 
-int humid_gpu_shard_answer(humid_gpu *h, const uint64_t *d_query_keys, const uint32_t *d_query_src, uint64_t n,
-                           uint32_t *d_answers) {
+int humid_gpu_shard_join_export(humid_gpu *h, uint32_t block, uint64_t *counts, uint64_t *d_keys, uint32_t *d_ranks) {
   if (int rc = require_shard(h, true)) return rc;
   State &s = h->s;
-  if (n && (!d_query_keys || !d_query_src || !d_answers)) return fail(h, HUMID_GPU_ERR_ARG, "answer: null buffer");
+  if (!counts || block == 0 || block > s.cfg.distance) return fail(h, HUMID_GPU_ERR_ARG, "join_export: bad arguments");
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
-    if (n == 0) return;
-    s.entries.grow(s.n_entries + n, s.n_entries, s.stream);
-    Timed t(s, "shard_answer", n, n * 16);
-    shard_answer_kernel<<<grid_for(n, 256), 256, 0, s.stream>>>(d_query_keys, d_query_src, n, layout_of(s), s.lookup(),
-                                                                d_answers, s.entries.p, s.entries.cap, s.counters.p + 2,
-                                                                s.deg.p);
-    HUMID_CUDA(cudaGetLastError());
-    HUMID_CUDA(cudaMemcpyAsync(&s.n_entries, s.counters.p + 2, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+    const uint64_t U = s.n_shard_words;
+    for (uint32_t p = 0; p < s.n_parts; p++) counts[p] = 0;
+    if (U == 0) return;
+    if (!d_keys || !d_ranks) throw CudaError{"join_export: null buffer"};
+    int lo_bit[HAM_MAX_D + 1], hi_bit[HAM_MAX_D + 1];
+    const Blocks B = shard_blocks(s, lo_bit, hi_bit);
+    Timed t(s, "shard_join_export", U, U * (8 + 12));
+    t.launches = partition_by_block_hash(s.word_key.p, (uint32_t)s.bases[s.part], d_keys, d_ranks, U, B.mask[block],
+                                         s.n_parts, counts, s.scratch, s.stream);
+  });
+}
+
+int humid_gpu_shard_join_match(humid_gpu *h, uint32_t block, const uint64_t *d_keys, const uint32_t *d_ranks, uint64_t n,
+                               uint64_t *counts) {
+  if (int rc = require_shard(h, true)) return rc;
+  State &s = h->s;
+  if (!counts || block == 0 || block > s.cfg.distance) return fail(h, HUMID_GPU_ERR_ARG, "join_match: bad arguments");
+  if (n >= 0xFFFFFFFFull) return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "too many words in one join");
+  return guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(s.device));
+    for (uint32_t p = 0; p < s.n_parts; p++) counts[p] = 0;
+    s.n_join_entries = 0;
+    if (n < 2) return;
+    if (!d_keys || !d_ranks) throw CudaError{"join_match: null buffer"};
+    int lo_bit[HAM_MAX_D + 1], hi_bit[HAM_MAX_D + 1];
+    const Blocks B = shard_blocks(s, lo_bit, hi_bit);
+    const uint64_t *keys = d_keys;
+    const uint32_t *rank = d_ranks;
+    if (hi_bit[block] > lo_bit[block]) {  // words arrive in rank order: a stable sort keeps that inside a group
+      s.key_alt.ensure(n + 1);
+      s.entries_alt.ensure(n + 1);
+      s.entry_val.ensure(n + 1);
+      s.entry_val_alt.ensure(n + 1);
+      uint64_t *kb[2] = {s.key_alt.p, s.entries_alt.p};
+      uint32_t *vb[2] = {s.entry_val.p, s.entry_val_alt.p};
+      int launches = 0;
+      Timed t(s, "shard_join_sort", n, n * (8 + 4) * 2);
+      int cur = radix_sort_bits_pairs(d_keys, d_ranks, kb, vb, n, lo_bit[block], hi_bit[block], s.scratch, s.stream,
+                                      &launches);
+      t.launches = launches;
+      keys = kb[cur];
+      rank = vb[cur];
+    }
+    unsigned long long *counter = s.counters.p + 41;
+    uint64_t cap = std::max<uint64_t>(s.join_entries.cap, std::max<uint64_t>(n, 1u << 20));
+    uint64_t pairs = 0;
+    for (int attempt = 0; attempt < 2; attempt++) {
+      s.join_entries.ensure(cap);
+      cap = s.join_entries.cap;
+      HUMID_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned long long), s.stream));
+      {
+        Timed t(s, "shard_join_match", n, n * 16);
+        launch_hamming_join(s, JOIN_DIRECTED, keys, rank, n, B, block, JOIN_NO_CAP, s.join_entries.p, cap / 2, counter,
+                            nullptr, 0u, nullptr, nullptr);
+      }
+      HUMID_CUDA(cudaGetLastError());
+      HUMID_CUDA(cudaMemcpyAsync(&pairs, counter, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+      HUMID_CUDA(cudaStreamSynchronize(s.stream));
+      if (2 * pairs <= cap) break;
+      cap = 2 * pairs;
+    }
+    s.n_join_entries = 2 * pairs;
+    if (s.n_join_entries == 0) return;
+    s.join_entries_out.ensure(s.n_join_entries);
+    Timed t(s, "shard_join_route", s.n_join_entries, s.n_join_entries * 16);
+    t.launches = partition_by_row_owner(s.join_entries.p, s.join_entries_out.p, s.n_join_entries, s.bases, s.n_parts,
+                                        counts, s.scratch, s.stream);
+  });
+}
+
+int humid_gpu_shard_join_entries(humid_gpu *h, uint64_t *d_entries) {
+  if (int rc = require_shard(h, true)) return rc;
+  State &s = h->s;
+  return guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(s.device));
+    if (s.n_join_entries == 0) return;
+    if (!d_entries) throw CudaError{"join_entries: null buffer"};
+    HUMID_CUDA(cudaMemcpyAsync(d_entries, s.join_entries_out.p, s.n_join_entries * 8, cudaMemcpyDeviceToDevice, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
   });
 }
 
-int humid_gpu_shard_apply_answers(humid_gpu *h, const uint32_t *d_query_src, const uint32_t *d_answers, uint64_t n) {
+int humid_gpu_shard_join_import(humid_gpu *h, const uint64_t *d_entries, uint64_t n) {
   if (int rc = require_shard(h, true)) return rc;
   State &s = h->s;
-  if (n && (!d_query_src || !d_answers)) return fail(h, HUMID_GPU_ERR_ARG, "apply_answers: null buffer");
+  if (n && !d_entries) return fail(h, HUMID_GPU_ERR_ARG, "join_import: null buffer");
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
     if (n == 0) return;
+    if (s.n_entries + n >= 0xFFFFFFFFull) throw CudaError{"more than 2^32-2 neighbour entries"};
     s.entries.grow(s.n_entries + n, s.n_entries, s.stream);
-    Timed t(s, "shard_apply_answers", n, n * 8);
-    shard_apply_kernel<<<grid_for(n, 256), 256, 0, s.stream>>>(d_query_src, d_answers, n, layout_of(s), s.entries.p,
-                                                               s.entries.cap, s.counters.p + 2, s.deg.p);
+    Timed t(s, "shard_join_import", n, n * 20);
+    unsigned long long *misrouted = s.counters.p + 42;
+    HUMID_CUDA(cudaMemsetAsync(misrouted, 0, sizeof(unsigned long long), s.stream));
+    import_entries_kernel<<<grid_for(n, 256), 256, 0, s.stream>>>(d_entries, n, (uint32_t)s.bases[s.part], s.n_shard_words,
+                                                                  s.entries.p + s.n_entries, s.deg.p, misrouted);
     HUMID_CUDA(cudaGetLastError());
-    HUMID_CUDA(cudaMemcpyAsync(&s.n_entries, s.counters.p + 2, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+    s.n_entries += n;
+    uint64_t bad = 0;
+    HUMID_CUDA(cudaMemcpyAsync(&bad, misrouted, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    if (bad) throw CudaError{"join_import: " + std::to_string(bad) + " entries for rows outside this shard"};
   });
 }
 
@@ -920,6 +736,7 @@ int humid_gpu_shard_tuple_ids(humid_gpu *h, uint32_t *d_ids) {
   if (!d_ids) return HUMID_GPU_ERR_ARG;
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
+    stage_ensure_lookup(s);  // key -> local rank
     {
       Timed t(s, "cluster_ids", s.src_n, s.src_n * 36);
       shard_word_ids_for_tuples_kernel<<<grid_for(s.src_n, 256), 256, 0, s.stream>>>(s.shard_keys.p, s.src_n, s.lookup(),

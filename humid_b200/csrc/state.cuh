@@ -114,6 +114,8 @@ struct State {
   uint32_t cluster_col_base = 0;     // stage_cluster: columns are rank + base
   bool cluster_skip_open = false;    // ... and components with a neighbour outside [0, unique) are left for later
   DevBuf<uint32_t> open_flag, comp_open;
+  DevBuf<uint64_t> join_entries, join_entries_out;  // join_match: directed entries, then grouped by owner
+  uint64_t n_join_entries = 0;
   uint32_t part = 0, n_parts = 1;
   uint64_t splitters[16] = {0};
   uint64_t bases[17] = {0};
@@ -191,6 +193,18 @@ int stage_build_table(State &s, bool with_lookup = true);  // insert + compact +
 int stage_ensure_lookup(State &s);    // ranks into the table slots + fingerprint filter, once per job
 int stage_early_insert(State &s, uint64_t first, uint64_t n);  // add_batch: count tuples [first, first+n)
 int stage_build_filter(State &s);      // fingerprint filter over word_key[0..unique)
+// Hamming block join (neighbours.cu), shared with the shard phases
+constexpr int HAM_MAX_D = 8;
+struct Blocks {
+  uint32_t n_blocks;
+  uint64_t mask[HAM_MAX_D + 1];  // bits of block b (block 0 = first letters = highest bits)
+};
+constexpr int JOIN_PAIRS_DEG = 0, JOIN_DIRECTED = 1;
+constexpr uint32_t JOIN_NO_CAP = 0xFFFFFFFFu;
+Blocks make_blocks(uint32_t n, uint32_t d, int lo_bit[], int hi_bit[]);  // arrays of HAM_MAX_D + 1
+void launch_hamming_join(State &s, int emit, const uint64_t *keys, const uint32_t *rank, uint64_t n_words, const Blocks &B,
+                         uint32_t block, uint32_t group_cap, uint64_t *out, uint64_t cap, unsigned long long *counter,
+                         uint32_t *deg, uint32_t col_base, uint32_t *flags, unsigned long long *n_flagged);
 int stage_neighbours_hamming(State &s);
 int stage_neighbours_edit(State &s);
 int stage_csr(State &s);               // sort directed entries, row_ptr / col (edit and shard modes)

@@ -38,10 +38,11 @@ def _bind(L):
     L.humid_gpu_shard_export_tuples.argtypes = [vp, vp, vp, vp]
     L.humid_gpu_shard_import_tuples.argtypes = [vp, vp, vp, u64, P(u64)]
     L.humid_gpu_shard_set_layout.argtypes = [vp, u32, u32, vp, vp]
-    L.humid_gpu_shard_probe_count.argtypes = [vp, vp]
-    L.humid_gpu_shard_probe.argtypes = [vp, vp, vp, vp]
-    L.humid_gpu_shard_answer.argtypes = [vp, vp, vp, u64, vp]
-    L.humid_gpu_shard_apply_answers.argtypes = [vp, vp, vp, u64]
+    L.humid_gpu_shard_join_local.argtypes = [vp, P(u64)]
+    L.humid_gpu_shard_join_export.argtypes = [vp, u32, vp, vp, vp]
+    L.humid_gpu_shard_join_match.argtypes = [vp, u32, vp, vp, u64, vp]
+    L.humid_gpu_shard_join_entries.argtypes = [vp, vp]
+    L.humid_gpu_shard_join_import.argtypes = [vp, vp, u64]
     L.humid_gpu_shard_build_rows.argtypes = [vp, P(u64)]
     L.humid_gpu_shard_cluster_local.argtypes = [vp, P(u64), P(u64)]
     L.humid_gpu_shard_export_open.argtypes = [vp, vp, vp, vp, vp, vp]
@@ -57,8 +58,9 @@ def _bind(L):
 SHARD_EXPORTS = [
     "humid_gpu_shard_begin", "humid_gpu_shard_sample_keys", "humid_gpu_shard_partition",
     "humid_gpu_shard_export_tuples", "humid_gpu_shard_import_tuples", "humid_gpu_shard_set_layout",
-    "humid_gpu_shard_probe_count", "humid_gpu_shard_probe", "humid_gpu_shard_answer",
-    "humid_gpu_shard_apply_answers", "humid_gpu_shard_build_rows", "humid_gpu_shard_cluster_local",
+    "humid_gpu_shard_join_local", "humid_gpu_shard_join_export", "humid_gpu_shard_join_match",
+    "humid_gpu_shard_join_entries", "humid_gpu_shard_join_import", "humid_gpu_shard_build_rows",
+    "humid_gpu_shard_cluster_local",
     "humid_gpu_shard_export_open", "humid_gpu_shard_import_open", "humid_gpu_shard_assign_ids",
     "humid_gpu_shard_finish", "humid_gpu_shard_keep_bits", "humid_gpu_shard_tuple_ids",
 ]
@@ -127,29 +129,32 @@ class CudaShardEngine(api.Dedup):
         self._check(self._L.humid_gpu_shard_set_layout(self._h, part, n_parts, sp.ctypes.data_as(C.c_void_p),
                                                        b.ctypes.data_as(C.c_void_p)), "shard_set_layout")
 
-    def probe_count(self, n_parts: int) -> np.ndarray:
-        out = np.zeros(MAX_PARTS, dtype=np.uint64)
-        self._check(self._L.humid_gpu_shard_probe_count(self._h, out.ctypes.data_as(C.c_void_p)), "shard_probe_count")
-        return out[:n_parts].astype(np.int64)
+    def join_local(self) -> int:
+        e = C.c_uint64(0)
+        self._check(self._L.humid_gpu_shard_join_local(self._h, C.byref(e)), "shard_join_local")
+        return int(e.value)
 
-    def probe(self, counts: np.ndarray):
-        off = np.zeros(len(counts) + 1, dtype=np.uint64)
-        off[1:] = np.cumsum(counts)
-        n = int(off[-1])
-        qk, qs = self._empty(n, torch.int64), self._empty(n, torch.int32)
-        self._check(self._L.humid_gpu_shard_probe(self._h, _dp(qk), _dp(qs), off.ctypes.data_as(C.c_void_p)), "shard_probe")
-        return qk, qs
+    def join_export(self, block: int, n_parts: int):
+        counts = np.zeros(MAX_PARTS, dtype=np.uint64)
+        k, r = self._empty(self.n_shard_words, torch.int64), self._empty(self.n_shard_words, torch.int32)
+        self._check(self._L.humid_gpu_shard_join_export(self._h, block, counts.ctypes.data_as(C.c_void_p), _dp(k), _dp(r)),
+                    "shard_join_export")
+        return k, r, counts[:n_parts].astype(np.int64)
 
-    def answer(self, qkeys, qsrc):
+    def join_match(self, block: int, keys, ranks, n_parts: int):
+        """-> (entries grouped by the part owning their row, entries per part)"""
         self._sync()
-        ans = self._empty(qkeys.numel(), torch.int32)
-        self._check(self._L.humid_gpu_shard_answer(self._h, _dp(qkeys), _dp(qsrc), qkeys.numel(), _dp(ans)), "shard_answer")
-        return ans
+        counts = np.zeros(MAX_PARTS, dtype=np.uint64)
+        self._check(self._L.humid_gpu_shard_join_match(self._h, block, _dp(keys), _dp(ranks), keys.numel(),
+                                                       counts.ctypes.data_as(C.c_void_p)), "shard_join_match")
+        counts = counts[:n_parts].astype(np.int64)
+        out = self._empty(int(counts.sum()), torch.int64)
+        self._check(self._L.humid_gpu_shard_join_entries(self._h, _dp(out)), "shard_join_entries")
+        return out, counts
 
-    def apply_answers(self, qsrc, answers):
+    def join_import(self, entries):
         self._sync()
-        self._check(self._L.humid_gpu_shard_apply_answers(self._h, _dp(qsrc), _dp(answers), qsrc.numel()),
-                    "shard_apply_answers")
+        self._check(self._L.humid_gpu_shard_join_import(self._h, _dp(entries), entries.numel()), "shard_join_import")
 
     def build_rows(self) -> int:
         e = C.c_uint64(0)
@@ -397,6 +402,12 @@ class ShardedDedup:
             splitters = pool[[(len(pool) * p) // W for p in range(1, W)]]
         else:
             splitters = np.zeros(max(W - 1, 0), dtype=np.uint64)
+        # block 0 of the join (the first word_length // (distance + 1) letters) must not straddle two
+        # shards: clear every letter after it (include/humid_gpu_shard.h: join_local)
+        n, d = int(eng.word_length), int(eng.distance)
+        self.n_blocks = d + 1 if d >= 1 else 1
+        tail_bits = 2 * (n - n // (d + 1))
+        splitters = (splitters >> np.uint64(tail_bits)) << np.uint64(tail_bits) if tail_bits < 64 else splitters * np.uint64(0)
         self.splitters = splitters
         self._mark("splitters")
 
@@ -417,18 +428,24 @@ class ShardedDedup:
         eng.set_layout(me, W, splitters, bases)
         self._mark("layout")
 
-        # neighbour search: local look-ups + routed queries
-        qcounts = eng.probe_count(W)
-        qk, qs = eng.probe(qcounts)
-        self._mark("probe")
-        rqk, qrecv = all_to_all_v(g, qk, qcounts)
-        rqs = all_to_all_fixed(g, qs, qcounts, qrecv)
-        self._mark("queries all-to-all")
-        ans = eng.answer(rqk, rqs)
-        self._mark("answer")
-        back = all_to_all_fixed(g, ans, qrecv, qcounts)
-        self._mark("answers all-to-all")
-        eng.apply_answers(qs, back)
+        # neighbour search: Hamming block join.  Block 0 groups lie inside a shard (aligned splitters);
+        # for every other block the words meet at the part that owns their block value, and the
+        # entries found there travel back to the owners of their rows.
+        eng.join_local()
+        self._mark("join_local")
+        self.words_exchanged = 0
+        for b in range(1, self.n_blocks):
+            bk, br, bcounts = eng.join_export(b, W)
+            rk_, brecv = all_to_all_v(g, bk, bcounts)
+            rr_ = all_to_all_fixed(g, br, bcounts, brecv)
+            self._mark("block words all-to-all")
+            ent, ecounts = eng.join_match(b, rk_, rr_, W)
+            self._mark("join_match")
+            rent, _ = all_to_all_v(g, ent, ecounts)
+            eng.join_import(rent)
+            self._mark("entries all-to-all + import")
+            self.words_exchanged += int(np.sum(bcounts))
+            del bk, br, rk_, rr_, ent, rent
         n_entries = eng.build_rows()
         self._mark("apply+rows")
 
@@ -454,7 +471,6 @@ class ShardedDedup:
         eng.finish(ids, self.n_total, self.usable_total, self.n_words_total, int(self.cluster_offsets[-1]))
         self._mark("ids+finish")
         self.word_sizes = [int(x) for x in sizes[:, 2]]
-        self.queries_sent = int(np.sum(qcounts))
         self.open_words_total = int(np.sum(sizes[:, 0]))
 
     # -- results: whole job, identical on every rank, unless stated; all of them are collective -----

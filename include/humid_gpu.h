@@ -126,6 +126,19 @@ int humid_gpu_debug_words(humid_gpu *h, uint64_t cap, uint64_t *keys, uint32_t *
 int humid_gpu_debug_neighbours(humid_gpu *h, uint64_t *row_ptr, uint32_t *col, uint64_t *n_entries);
 /* Per cluster id (1-based; arrays indexed id-1): Cluster::size and rank of Cluster::maxLeaf. */
 int humid_gpu_debug_clusters(humid_gpu *h, uint64_t cap, uint64_t *sizes, uint32_t *max_leaf_rank);
+/* Test hooks for the device primitives the stages are built from (humid_b200/csrc/primitives.cu);
+ * all pointers are device memory of n elements unless stated, the call synchronises.
+ * sort_pairs: stable radix sort of (key, value) by key bits [begin_bit, end_bit); d_vals_in NULL =
+ * the value of element i is i.
+ * partition: one stable partition pass.  kind 0: by the top 8 bits of the home slot in a table of
+ * arg + 1 slots; kind 1: by the part (of n_parts) joining the letters under mask arg; kind 2: 64-bit
+ * entries by the part owning row = entry >> 32 (host array bases[n_parts + 1]); values as above + index_base;
+ * counts (host, n_parts entries; NULL for kind 0) = elements per part. */
+int humid_gpu_debug_sort_pairs(humid_gpu *h, const uint64_t *d_keys_in, const uint32_t *d_vals_in, uint64_t n,
+                               int begin_bit, int end_bit, uint64_t *d_keys_out, uint32_t *d_vals_out);
+int humid_gpu_debug_partition(humid_gpu *h, int kind, const uint64_t *d_keys_in, uint64_t n, uint64_t arg,
+                              uint32_t n_parts, const uint64_t *bases, uint32_t index_base, uint64_t *d_keys_out,
+                              uint32_t *d_vals_out, uint64_t *counts);
 
 /* Per-stage device timings of the last finalize (CUDA events on the library's stream). */
 typedef struct {

@@ -10,8 +10,9 @@
  *   partition / export_tuples  ==all-to-all-v==>  import_tuples
  *                         the owner of a key range counts its words                 (Trie::add)
  *   set_layout            global rank = bases[part] + local rank                    (Trie::walk order)
- *   probe_count / probe   variants owned by this shard are looked up in place, the
- *                         others become queries  ==all-to-all-v==>  answer  ==back==>  apply_answers
+ *   join_local            block join of block 0 inside the shard     (asymmetricHamming)
+ *   per block b = 1..d:   join_export  ==all-to-all-v==>  join_match (the part that owns a block value joins
+ *                         its group)  /  join_entries  ==all-to-all-v==>  join_import (entries back to the row owners)
  *   build_rows            neighbour lists of the shard's words (columns = global ranks)
  *   cluster_local         components inside the shard are clustered in place        (findClusters)
  *   export_open  ==all-gather==>  import_open   components that cross shards, replayed on every shard
@@ -21,6 +22,7 @@
  * All pointers named d_* are device memory of the handle's GPU, allocated by the caller
  * (sizes are known from the preceding call); everything else is host memory.  Same error
  * conventions as humid_gpu.h.  Only Hamming mode (any -m) and edit distance 1 are sharded.
+ * Groups of the join are walked whatever their size here (no variant-probe fallback across shards).
  */
 #ifndef HUMID_GPU_SHARD_H
 #define HUMID_GPU_SHARD_H
@@ -52,14 +54,24 @@ int humid_gpu_shard_import_tuples(humid_gpu *h, const uint64_t *d_keys, const ui
 /* bases has n_parts+1 entries (exclusive prefix sums of the shard sizes). */
 int humid_gpu_shard_set_layout(humid_gpu *h, uint32_t part, uint32_t n_parts, const uint64_t *splitters,
                                const uint64_t *bases);
-/* Number of variant queries this shard will send to every part (counts[part] = 0). */
-int humid_gpu_shard_probe_count(humid_gpu *h, uint64_t *counts);
-/* Local look-ups + fill of the query buffers; offsets (n_parts+1) = exclusive prefix of counts. */
-int humid_gpu_shard_probe(humid_gpu *h, uint64_t *d_query_keys, uint32_t *d_query_src, const uint64_t *offsets);
-/* d_answers[i] = global rank of query i's word, or 0xFFFFFFFF. */
-int humid_gpu_shard_answer(humid_gpu *h, const uint64_t *d_query_keys, const uint32_t *d_query_src, uint64_t n,
-                           uint32_t *d_answers);
-int humid_gpu_shard_apply_answers(humid_gpu *h, const uint32_t *d_query_src, const uint32_t *d_answers, uint64_t n);
+/* Block 0 (the leading letters) of the Hamming block join, inside the shard: the splitters given to
+ * partition / set_layout MUST be multiples of 4^(word_length - word_length / (distance + 1)), i.e. have all
+ * letters after block 0 equal to 'A', so that no block-0 group straddles two shards.  Starts the
+ * shard's entry list (local row, global column) and list lengths. */
+int humid_gpu_shard_join_local(humid_gpu *h, uint64_t *n_entries);
+/* Block b >= 1: every word of the shard as {key, global rank}, grouped by the part that joins its
+ * block-b value (a hash of those letters); inside a part the words stay in rank order.  d_keys /
+ * d_ranks hold n_shard_words elements; counts (n_parts) = words per part. */
+int humid_gpu_shard_join_export(humid_gpu *h, uint32_t block, uint64_t *counts, uint64_t *d_keys, uint32_t *d_ranks);
+/* The words received for block b from all parts, concatenated in part order (== ascending global
+ * rank): joins them and keeps the directed entries {global row << 32 | global column} grouped by
+ * the part owning the row; counts (n_parts) = entries per part. */
+int humid_gpu_shard_join_match(humid_gpu *h, uint32_t block, const uint64_t *d_keys, const uint32_t *d_ranks, uint64_t n,
+                               uint64_t *counts);
+/* Copies the entries of the last join_match (sum of its counts) to d_entries. */
+int humid_gpu_shard_join_entries(humid_gpu *h, uint64_t *d_entries);
+/* Entries received for this shard's rows: appended to its entry list. */
+int humid_gpu_shard_join_import(humid_gpu *h, const uint64_t *d_entries, uint64_t n);
 int humid_gpu_shard_build_rows(humid_gpu *h, uint64_t *n_entries);
 /* Clusters of the components that lie entirely inside this shard; the others ("open": some
  * member has a neighbour on another shard) are counted for the export below. */

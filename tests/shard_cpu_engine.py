@@ -37,8 +37,9 @@ class CpuShardEngine:
     stream = 0
 
     def __init__(self, word_length, distance, seg_take, edit=False, maximum=False, **_):
-        assert not (edit and distance >= 2) and distance in (0, 1, 2)
+        assert not (edit and distance >= 2)
         self.n, self.d, self.seg_take, self.maximum = word_length, distance, list(seg_take), maximum
+        self.word_length, self.distance = word_length, distance
         self.reset()
 
     def reset(self):
@@ -87,65 +88,78 @@ class CpuShardEngine:
         self.part, self.n_parts = part, n_parts
         self.splitters = np.asarray(splitters, np.uint64)
         self.base = int(bases[part])
+        self.all_bases = np.asarray(bases, np.int64)
 
-    # ---- neighbours ----------------------------------------------------------------------------
-    def _variants(self):
-        """(source shard-local rank, upward variant) for every variant within distance d."""
-        w = self.sk
-        n = self.n
-        src, var = [], []
-        r = np.arange(w.size, dtype=np.uint32)
+    # ---- neighbours: Hamming block join -------------------------------------------
+    def _blocks(self):
+        n, d = self.n, self.d
+        out = []
+        for b in range(d + 1):
+            p0, p1 = b * n // (d + 1), (b + 1) * n // (d + 1)
+            lo = 2 * (n - p1)
+            out.append(np.uint64(((1 << (2 * (p1 - p0))) - 1) << lo) if p1 > p0 else np.uint64(0))
+        return out
 
-        def letter(x, p):
-            return (x >> np.uint64(2 * (n - 1 - p))) & np.uint64(3)
+    def _join(self, keys, ranks, block):
+        """All linked pairs (rank a < rank b) whose FIRST common block is `block`; keys in rank order."""
+        masks = self._blocks()
+        order = np.argsort(keys & masks[block], kind="stable")
+        k, r = keys[order], ranks[order]
+        g = k & masks[block]
+        starts = np.nonzero(np.concatenate([[True], g[1:] != g[:-1]]))[0]
+        ends = np.concatenate([starts[1:], [k.size]])
+        low = np.uint64(0x5555555555555555)
+        pa, pb = [], []
+        for s0, e0 in zip(starts, ends):
+            if e0 - s0 < 2:
+                continue
+            kk, rr = k[s0:e0], r[s0:e0]
+            i, j = np.triu_indices(kk.size, 1)
+            a, c = kk[i], kk[j]
+            x = a ^ c
+            diff = (x | (x >> np.uint64(1))) & low
+            cnt = np.array([bin(int(v)).count("1") for v in diff])
+            ok = (cnt >= 1) & (cnt <= self.d)
+            ah, ch, al, cl = (a >> np.uint64(1)) & low, (c >> np.uint64(1)) & low, a & low, c & low
+            a_gt = (ah & ~ch) | (~(ah ^ ch) & al & ~cl)
+            ok &= (a_gt & diff) == 0
+            for bb in range(block):
+                ok &= (x & masks[bb]) != 0
+            pa.append(rr[i][ok]); pb.append(rr[j][ok])
+        if not pa:
+            return np.zeros(0, np.uint64), np.zeros(0, np.uint64)
+        return np.concatenate(pa).astype(np.uint64), np.concatenate(pb).astype(np.uint64)
 
-        for p1 in range(n):
-            for a in range(1, 4):
-                m1 = letter(w, p1) + np.uint64(a) <= 3
-                v1 = w[m1] + (np.uint64(a) << np.uint64(2 * (n - 1 - p1)))
-                src.append(r[m1]); var.append(v1)
-                if self.d >= 2:
-                    for p2 in range(p1 + 1, n):
-                        for b in range(1, 4):
-                            m2 = letter(v1, p2) + np.uint64(b) <= 3
-                            src.append(r[m1][m2]); var.append(v1[m2] + (np.uint64(b) << np.uint64(2 * (n - 1 - p2))))
-        if not src or self.d == 0:
-            return np.zeros(0, np.uint32), np.zeros(0, np.uint64)
-        return np.concatenate(src), np.concatenate(var)
-
-    def _lookup(self, keys):
-        pos = np.searchsorted(self.sk, keys)
-        pos_c = np.minimum(pos, max(self.sk.size - 1, 0))
-        hit = (self.sk[pos_c] == keys) if self.sk.size else np.zeros(keys.size, bool)
-        return np.where(hit, pos_c, 0xFFFFFFFF).astype(np.uint32)
-
-    def probe_count(self, n_parts):
-        self._src, self._var = self._variants()
-        self._owner = np.searchsorted(self.splitters, self._var, "right") if self.n_parts > 1 else np.zeros(self._var.size, int)
-        return np.bincount(self._owner[self._owner != self.part], minlength=n_parts).astype(np.int64)
-
-    def probe(self, counts):
-        local = self._owner == self.part
-        hit = self._lookup(self._var[local])
-        ok = hit != NONE32
-        a, b = self._src[local][ok].astype(np.uint64), hit[ok].astype(np.uint64)
+    def join_local(self):
+        self.entries = []
+        if self.d == 0 or self.sk.size == 0:
+            return 0
         base = np.uint64(self.base)
+        a, b = self._join(self.sk, np.arange(self.sk.size, dtype=np.uint64), 0)
         self.entries = [(a << np.uint64(32)) | (base + b), (b << np.uint64(32)) | (base + a)]
-        order = np.argsort(self._owner[~local], kind="stable")
-        qk = self._var[~local][order]
-        qs = (self._src[~local][order] + np.uint32(self.base)).astype(np.uint32)
-        return _t64(qk), _t32(qs)
+        return 2 * a.size
 
-    def answer(self, qkeys, qsrc):
-        hit = self._lookup(_u64(qkeys))
-        ok = hit != NONE32
-        self.entries.append((hit[ok].astype(np.uint64) << np.uint64(32)) | _u32(qsrc)[ok].astype(np.uint64))
-        return _t32(np.where(ok, hit + np.uint32(self.base), NONE32))
+    def join_export(self, block, n_parts):
+        import hashlib  # any deterministic function of the block value will do as the meeting point
+        m = self._blocks()[block]
+        v = self.sk & m
+        dest = np.array([int.from_bytes(hashlib.blake2b(int(x).to_bytes(8, "little"), digest_size=4).digest(), "little") % n_parts
+                         for x in v], dtype=np.int64) if v.size else np.zeros(0, np.int64)
+        order = np.argsort(dest, kind="stable")
+        ranks = (np.arange(self.sk.size, dtype=np.uint32) + np.uint32(self.base))[order]
+        return _t64(self.sk[order]), _t32(ranks), np.bincount(dest, minlength=n_parts).astype(np.int64)
 
-    def apply_answers(self, qsrc, answers):
-        a, s = _u32(answers), _u32(qsrc)
-        ok = a != NONE32
-        self.entries.append(((s[ok] - np.uint32(self.base)).astype(np.uint64) << np.uint64(32)) | a[ok].astype(np.uint64))
+    def join_match(self, block, keys, ranks, n_parts):
+        a, b = self._join(_u64(keys), _u32(ranks).astype(np.uint64), block)
+        ent = np.concatenate([(a << np.uint64(32)) | b, (b << np.uint64(32)) | a])
+        rows = (ent >> np.uint64(32)).astype(np.int64)
+        owner = np.searchsorted(self.all_bases[1:], rows, "right")
+        order = np.argsort(owner, kind="stable")
+        return _t64(ent[order]), np.bincount(owner, minlength=n_parts).astype(np.int64)
+
+    def join_import(self, entries):
+        e = _u64(entries)
+        self.entries.append(((e >> np.uint64(32)) - np.uint64(self.base)) << np.uint64(32) | (e & np.uint64(0xFFFFFFFF)))
 
     def build_rows(self):
         e = np.sort(np.concatenate(self.entries)) if self.entries else np.zeros(0, np.uint64)

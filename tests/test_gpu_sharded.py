@@ -86,7 +86,7 @@ def test_logical_shards_match_oracle(W, ci, R, kw):
         assert np.array_equal(res["ids"], ref.cid[lo:hi])
         assert res["stats"] == ref.stats_text()
     if W > 1 and R > 100:
-        assert sum(dd.queries_sent for dd in dds) > 0
+        assert sum(dd.words_exchanged for dd in dds) > 0
     for dd in dds:
         dd.close()
 

@@ -48,7 +48,7 @@ def _worker(rank, world, port, ci, R, kw, q):
         assert np.array_equal(dd.keep_mask(), ref.keep[lo:hi].astype(bool))
         assert np.array_equal(dd.cluster_ids(), ref.cid[lo:hi])
         assert dd.stats_text() == ref.stats_text()
-        q.put((rank, "ok", dd.queries_sent))
+        q.put((rank, "ok", dd.words_exchanged))
     except Exception as e:  # noqa: BLE001
         import traceback
 
