@@ -8,13 +8,15 @@ word construction (pack) -> distinct-word table with counts -> Hamming neighbour
 clustering -> keep mask + the three histograms.  The workload is BASELINE.json configs[1]
 (50 M read pairs, 12 bp UMI in a separate FastQ, word length 24 = 8/8/8 nt, Hamming 1,
 directional clustering), `--tuples` read tuples PER GPU (weak scaling: N GPUs process
-N x that many tuples of one common library, sharded by key hash).
+N x that many tuples of one common library; the word space is range-partitioned over the
+GPUs, humid_b200/sharded.py).
 
   value  whole-job read pairs/s with the word characters already resident in HBM
   e2e    the same through the C ABI with HOST buffers: per step the H2D copy of the word
          characters (pinned memory) and the D2H read of the keep mask, the histograms and
          the stats scalars are inside the timed region
-  roofline      the dominant kernel of the step against the measured HBM copy bandwidth
+  roofline      the stage with the largest device time against the measured HBM copy bandwidth:
+                algorithmic bytes of its launches / CUDA-event time of the stage
   cpu_baseline  the reference `humid` binary (oracle/_ref/humid, built from the reference's
                 own sources) — or the C restatement when that binary is absent — timed on a
                 bounded sample of the same workload on the host cores
@@ -40,6 +42,17 @@ METRIC = "read pairs deduplicated/sec"
 UNIT = "read pairs/s"
 WORKLOAD = "configs[1]: synthetic read pairs, 12bp UMI in separate FastQ, -n 24 (8/8/8), Hamming 1, directional"
 REF_SAMPLE_TUPLES = 250_000
+
+
+# stage (humid_gpu_stage_stats) -> the kernel that does its work
+KERNEL_OF = {
+    "sort_words": "radix_pass_kernel<true, ShiftDigit> (1 histogram + 6 digit passes)",
+    "join_sort": "radix_pass_kernel<true, ShiftDigit> (1 histogram + 3 digit passes)",
+    "table_partition": "radix_pass_kernel<true, SlotDigit>", "table_insert": "table_insert_kernel",
+    "pack": "pack_words_kernel", "rank_columns": "gather_columns_kernel", "join_hamming_b0": "hamming_join_kernel",
+    "join_hamming_b1": "hamming_join_kernel", "join_hamming_b2": "hamming_join_kernel", "csr_build": "csr_fill_kernel",
+    "union_find": "uf_union_kernel", "replay_directional": "replay_kernel<false>", "replay_maximum": "replay_kernel<true>",
+}
 
 
 def peaks():
@@ -161,6 +174,27 @@ def run_reference_arm(args):
     print(json.dumps(line), flush=True)
 
 
+def bind_near_gpu(local):
+    """Run this rank's host threads on the cores next to its GPU (the box's own PCIe / NUMA layout from
+    sysfs), so that the pinned upload buffer lives in that socket's memory.  Returns the NUMA node or None."""
+    try:
+        import torch
+
+        p = torch.cuda.get_device_properties(local)
+        bdf = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        base = "/sys/bus/pci/devices/" + bdf
+        cpus = set()
+        for part in open(base + "/local_cpulist").read().strip().split(","):
+            if part:
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return int(open(base + "/numa_node").read())
+    except Exception:
+        return None
+
+
 # ----------------------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------------------
@@ -179,6 +213,7 @@ def run_gpu_arm(args):
         raise SystemExit("bench.py needs a CUDA device: the deduplication hot path has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = bind_near_gpu(local)  # before the pinned buffer is allocated: first touch decides the node
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     if world != args.gpus:
@@ -298,7 +333,7 @@ def run_gpu_arm(args):
             traffic = json.load(open(tp)).get(name)
         except Exception:
             traffic = None
-    roofline = {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": peak, "unit": "GB/s",
+    roofline = {"bound": "hbm", "kernel": KERNEL_OF.get(name, name), "stage": name, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "kernel_ms": a["ms"] / max(1, a["calls"]), "launches": a["launches"],
                 "algo_bytes_per_launch": a["algo_bytes"] / max(1, a["calls"]),
@@ -317,7 +352,7 @@ def run_gpu_arm(args):
                    "distance": cfg.distance, "clustering": "maximum" if cfg.maximum else "directional",
                    "l2": "inputs larger than L2 (word characters %.2f GB per GPU)" % (R_per * cfg.word_length / 1e9),
                    "parallelism": "1 GPU" if world == 1 else f"word space range-partitioned over {world} GPUs; NCCL all-to-all-v (tuples, variant queries), all-gather (components that cross shards)",
-                   "result": counts},
+                   "host_numa_node": numa, "result": counts},
         "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": t_e2e * 1e3,
                 "h2d_bytes_per_step": int(R_all * cfg.word_length), "d2h_bytes_per_step": int(d2h[0]) * world},
         "gpu_launches": int(launches_per_step * args.steps),

@@ -290,7 +290,8 @@ int stage_neighbours_hamming(State &s) {
         uint64_t *kb[2] = {s.key_alt.p, s.entries_alt.p};
         uint32_t *vb[2] = {s.entry_val.p, s.entry_val_alt.p};
         int launches = 0;
-        Timed t(s, "join_sort", U, U * (8 + 12));
+        const uint64_t passes = (uint64_t)(hi_bit[b] - lo_bit[b] + 7) / 8;  // first pass reads keys only (rank = position)
+        Timed t(s, "join_sort", U, U * (8 + (8 + 12) + (passes - 1) * 24));
         int cur = radix_sort_bits_indexed(s.word_key.p, kb, vb, U, lo_bit[b], hi_bit[b], s.scratch, s.stream, &launches);
         t.launches = launches;
         k += launches;

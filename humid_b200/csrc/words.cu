@@ -270,7 +270,7 @@ static int table_insert(State &s, const uint64_t *keys, const uint32_t *index, u
   if (n >= PARTITION_MIN_TUPLES && s.table_cap * sizeof(Slot) > (64ull << 20)) {
     s.part_key.ensure(n);
     s.part_index.ensure(n);
-    Timed t(s, "table_partition", n, n * (8 + 12));
+    Timed t(s, "table_partition", n, n * (8 + 8 + 12));  // histogram read, pass read, (key, index) written
     int launches = 0;
     partition_by_slot_u64(keys, index, index_base, s.part_key.p, s.part_index.p, n, s.table_cap - 1, s.scratch,
                           s.stream, &launches);
@@ -343,8 +343,9 @@ int stage_build_table(State &s, bool with_lookup) {
   int launches = 0;
   int cur;
   {
-    // keys + slot ids read once and written once (the radix passes are overhead)
-    Timed t(s, "sort_words", U, U * 2 * (8 + 4));
+    // per 8-bit pass the (key, slot) pairs are read once and written once; one more read of the keys for the histograms
+    const uint64_t passes = (2 * (uint64_t)s.cfg.word_length + 7) / 8;
+    Timed t(s, "sort_words", U, U * (8 + passes * 2 * (8 + 4)));
     cur = radix_sort_u64(kb, vb, U, 2 * (int)s.cfg.word_length, s.scratch, s.scan_scratch, s.stream, &launches);
     t.launches = launches;
   }

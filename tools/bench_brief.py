@@ -14,7 +14,7 @@ for line in sys.stdin:
     print(f"n_gpus {d['n_gpus']} ms/step {d['ms_per_step']:.3f} value {d['value'] / 1e9:.3f} G/s e2e "
           f"{d['e2e'].get('ms_per_step', 0):.2f} ms {d['e2e']['value'] / 1e9:.3f} G/s launches {d.get('gpu_launches')}")
     if r:
-        print(f"roofline {r.get('kernel')} {r.get('achieved', 0):.0f}/{r.get('peak', 0):.0f} GB/s frac {r.get('frac', 0):.3f} "
+        print(f"roofline {r.get('stage')} [{r.get('kernel')}] {r.get('achieved', 0):.0f}/{r.get('peak', 0):.0f} GB/s frac {r.get('frac', 0):.3f} "
               f"kernel_ms {r.get('kernel_ms', 0):.3f} traffic {r.get('traffic')}")
         print(" ".join(f"{k}={v}" for k, v in (r.get("stages_ms") or {}).items()))
     if d.get("cpu_baseline"):
