@@ -51,6 +51,18 @@ __device__ __forceinline__ uint32_t first_common_block(const Blocks &B, uint64_t
   return first;
 }
 
+// do two words (x = a ^ b) agree on a block before `block`?  `block` is uniform: the unrolled loop
+// leaves by a uniform branch, so block 0 costs nothing and block 1 one test.
+__device__ __forceinline__ bool shares_earlier_block(const Blocks &B, uint32_t block, uint64_t x) {
+  bool shared = false;
+#pragma unroll
+  for (int b = 0; b < HAM_MAX_D; b++) {
+    if ((uint32_t)b >= block) break;
+    shared |= (x & B.mask[b]) == 0;
+  }
+  return shared;
+}
+
 // a precedes b in rank, 1..d letters differ: linked iff a[p] <= b[p] wherever they differ
 __device__ __forceinline__ bool linked(uint64_t a, uint64_t b, uint32_t d) {
   const uint64_t x = a ^ b;
@@ -121,7 +133,7 @@ __global__ void __launch_bounds__(JOIN_THREADS)
       for (uint32_t t = 1; t <= after; t++) {
         const uint64_t v = keys[i + t];
         if (!linked(w, v, d)) continue;
-        if (first_common_block(B, v ^ w) != block) continue;  // found in an earlier block's order
+        if (shares_earlier_block(B, block, v ^ w)) continue;  // found in an earlier block's order
         if (nh == JOIN_LOCAL_HITS) {  // rare: local buffer full, append what we have
           unsigned long long pos = atomicAdd(counter, (unsigned long long)nh);
 #pragma unroll
