@@ -65,30 +65,36 @@ int stage_cluster_ids(State &s, uint64_t first, uint64_t n, uint32_t *d_out) {
   return 1;
 }
 
-// ---- histograms: sort the values, emit (value, first index) at every run start ------------
-__global__ void hist_values_kernel(int which, uint64_t m, const uint32_t *__restrict__ word_count,
-                                   const uint64_t *__restrict__ row_ptr, const uint64_t *__restrict__ cluster_size,
-                                   uint64_t *__restrict__ out) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= m) return;
-  out[i] = which == HUMID_HIST_COUNTS ? (uint64_t)word_count[i]
-           : which == HUMID_HIST_NEIGHBOURS ? row_ptr[i + 1] - row_ptr[i]
-                                            : cluster_size[i];
-}
-
+// ---- histograms: values below HIST_SMALL are binned in shared memory per CTA, the few larger ones
+// are listed and counted on the host ---------------------------------------------------------
+constexpr uint32_t HIST_SMALL = 4096;
+constexpr int HIST_ITEMS = 16;
 __global__ void __launch_bounds__(256)
-    run_starts_kernel(const uint64_t *__restrict__ sorted, uint64_t m, uint64_t *__restrict__ run_val,
-                      uint64_t *__restrict__ run_start, uint64_t cap, unsigned long long *__restrict__ counter) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= m) return;
-  uint64_t v = sorted[i];
-  if (i == 0 || sorted[i - 1] != v) {
-    const unsigned long long pos = reserve_slots(counter);
-    if (pos < cap) {
-      run_val[pos] = v;
-      run_start[pos] = i;
+    hist_small_kernel(int which, uint64_t m, const uint32_t *__restrict__ word_count,
+                      const uint64_t *__restrict__ row_ptr, const uint64_t *__restrict__ cluster_size,
+                      unsigned long long *__restrict__ bins, uint64_t *__restrict__ large, uint64_t large_cap,
+                      unsigned long long *__restrict__ n_large) {
+  __shared__ uint32_t h[HIST_SMALL];
+  for (uint32_t k = threadIdx.x; k < HIST_SMALL; k += 256) h[k] = 0;
+  __syncthreads();
+  const uint64_t base = (uint64_t)blockIdx.x * (256 * HIST_ITEMS);
+#pragma unroll 4
+  for (int j = 0; j < HIST_ITEMS; j++) {
+    const uint64_t i = base + (uint64_t)j * 256 + threadIdx.x;
+    if (i >= m) break;
+    const uint64_t v = which == HUMID_HIST_COUNTS ? (uint64_t)word_count[i]
+                       : which == HUMID_HIST_NEIGHBOURS ? row_ptr[i + 1] - row_ptr[i]
+                                                        : cluster_size[i];
+    if (v < HIST_SMALL) {
+      atomicAdd(&h[(uint32_t)v], 1u);
+    } else {
+      const unsigned long long pos = reserve_slots(n_large);
+      if (pos < large_cap) large[pos] = v;
     }
   }
+  __syncthreads();
+  for (uint32_t k = threadIdx.x; k < HIST_SMALL; k += 256)
+    if (h[k]) atomicAdd(bins + k, (unsigned long long)h[k]);
 }
 
 int stage_histogram(State &s, int which) {
@@ -99,47 +105,44 @@ int stage_histogram(State &s, int which) {
   if (m == 0) return 0;
   int k = 0;
   static const char *names[3] = {"hist_counts", "hist_neigh", "hist_clusters"};
-  Timed t(s, names[which], m, m * 8);
-  s.key_alt.ensure(m + 1);
-  s.entries_alt.ensure(m + 1);
-  uint64_t *kb[2] = {s.key_alt.p, s.entries_alt.p};
-  uint32_t *vb[2] = {nullptr, nullptr};
-  hist_values_kernel<<<grid_for(m, 256), 256, 0, s.stream>>>(which, m, s.word_count.p, s.row_ptr.p, s.cluster_size.p,
-                                                             kb[0]);
-  k++;
-  // counts and cluster sizes are bounded by the number of tuples, list lengths by the entries
-  uint64_t bound = which == HUMID_HIST_NEIGHBOURS ? s.n_entries : s.report_tuples;
-  int bits = 1;
-  while (bits < 64 && (1ull << bits) <= bound) bits++;
-  int launches = 0;
-  int cur = radix_sort_u64(kb, vb, m, bits, s.scratch, s.scan_scratch, s.stream, &launches);
-  k += launches;
+  Timed t(s, names[which], m, m * (which == HUMID_HIST_COUNTS ? 4 : 8));
+  std::vector<unsigned long long> bins(HIST_SMALL);
+  std::vector<uint64_t> large;
   uint64_t cap = 1 << 16;
-  std::vector<uint64_t> hv, hs;
   for (int attempt = 0; attempt < 2; attempt++) {
-    uint64_t *runs = (uint64_t *)s.scratch.get(2 * cap * sizeof(uint64_t));
+    // scratch: [bins: HIST_SMALL u64][large values: cap u64]
+    unsigned long long *d_bins = (unsigned long long *)s.scratch.get((HIST_SMALL + cap) * sizeof(uint64_t));
+    uint64_t *d_large = (uint64_t *)(d_bins + HIST_SMALL);
+    HUMID_CUDA(cudaMemsetAsync(d_bins, 0, HIST_SMALL * sizeof(uint64_t), s.stream));
     HUMID_CUDA(cudaMemsetAsync(s.counters.p + 4, 0, sizeof(unsigned long long), s.stream));
-    run_starts_kernel<<<grid_for(m, 256), 256, 0, s.stream>>>(kb[cur], m, runs, runs + cap, cap, s.counters.p + 4);
+    hist_small_kernel<<<grid_for(m, 256, HIST_ITEMS), 256, 0, s.stream>>>(which, m, s.word_count.p, s.row_ptr.p,
+                                                                         s.cluster_size.p, d_bins, d_large, cap,
+                                                                         s.counters.p + 4);
     k++;
-    uint64_t n_runs = 0;
-    HUMID_CUDA(cudaMemcpyAsync(&n_runs, s.counters.p + 4, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+    uint64_t n_large = 0;
+    HUMID_CUDA(cudaMemcpyAsync(&n_large, s.counters.p + 4, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+    HUMID_CUDA(cudaMemcpyAsync(bins.data(), d_bins, HIST_SMALL * sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
-    if (n_runs > cap) { cap = n_runs; continue; }
-    hv.resize(n_runs);
-    hs.resize(n_runs);
-    HUMID_CUDA(cudaMemcpyAsync(hv.data(), runs, n_runs * sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
-    HUMID_CUDA(cudaMemcpyAsync(hs.data(), runs + cap, n_runs * sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
-    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    if (n_large > cap) { cap = n_large; continue; }
+    large.resize(n_large);
+    if (n_large) {
+      HUMID_CUDA(cudaMemcpyAsync(large.data(), d_large, n_large * sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+      HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    }
     break;
   }
-  // runs arrive in arbitrary order: order them by start index, lengths are the differences
-  std::vector<size_t> order(hv.size());
-  for (size_t i = 0; i < order.size(); i++) order[i] = i;
-  std::sort(order.begin(), order.end(), [&](size_t a, size_t b) { return hs[a] < hs[b]; });
-  for (size_t j = 0; j < order.size(); j++) {
-    uint64_t end = j + 1 < order.size() ? hs[order[j + 1]] : m;
-    s.hist_k[which].push_back(hv[order[j]]);
-    s.hist_v[which].push_back(end - hs[order[j]]);
+  for (uint32_t v = 0; v < HIST_SMALL; v++)
+    if (bins[v]) {
+      s.hist_k[which].push_back(v);
+      s.hist_v[which].push_back(bins[v]);
+    }
+  std::sort(large.begin(), large.end());
+  for (size_t i = 0; i < large.size();) {
+    size_t j = i;
+    while (j < large.size() && large[j] == large[i]) j++;
+    s.hist_k[which].push_back(large[i]);
+    s.hist_v[which].push_back(j - i);
+    i = j;
   }
   t.launches = k;
   return k;

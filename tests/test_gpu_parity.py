@@ -174,6 +174,19 @@ def _chars(words):
     return np.frombuffer("".join(words).encode(), dtype=np.uint8).reshape(len(words), -1).copy()
 
 
+def test_histogram_values_beyond_the_shared_memory_bins():
+    """Words counted 4096 times and more, and a cluster of > 9000 reads, take the listed-value path of the histograms."""
+    rng = np.random.default_rng(5)
+    words = ["ACGTACGTAC"] * 5000 + ["ACGTACGTAG"] * 4500 + ["TTTTTTTTTT"] * 4096 + ["GGGGGGGGGG"] * 4095
+    words += ["".join(rng.choice(list("ACGT"), 10)) for _ in range(3000)]
+    order = rng.permutation(len(words))
+    chars = _chars([words[i] for i in order])
+    r = oracle.Result(oracle.pack_words(chars, [5, 5]), 10, 1, False, False)
+    dd = run_gpu(chars, [5, 5], 10, 1, False, False, batches=2)
+    assert_same_as_oracle(dd, r, chars.shape[0])
+    assert max(int(x.split()[0]) for x in dd.stats_text()["counts.dat"].splitlines()) == 5000
+
+
 def test_empty_input():
     dd = api.Dedup(word_length=8, distance=1, seg_take=[4, 4])
     dd.finalize()
