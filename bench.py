@@ -339,6 +339,19 @@ def run_gpu_arm(args):
                 "algo_bytes_per_launch": a["algo_bytes"] / max(1, a["calls"]),
                 "stages_ms": {k: round(v["ms"], 3) for k, v in agg.items()}}
 
+    # BASELINE.json's second figure, "neighbour-search GB/s", by SURVEY.md §8(d)'s definition: the bytes of the
+    # variant-probe model (8 B per word and per upward variant, 296 B per word at n = 24, d = 1) over the
+    # time of whatever finds the neighbour lists here (block join: sorts + joins; probe stages if any)
+    ns_ms = sum(v["ms"] for k, v in agg.items()
+                if k.startswith(("join_", "probe_", "shard_join", "edit_candidates", "edit_replay")))
+    n_, d_ = cfg.word_length, cfg.distance
+    variants = 1.5 * n_ + (2.25 * n_ * (n_ - 1) / 2.0 if d_ >= 2 else 0.0)
+    ns_bytes = 8.0 * (1.0 + variants) * counts["unique"] / max(world, 1)
+    neighbour_search = {"ms": round(ns_ms, 3), "model_bytes": ns_bytes, "unit": "GB/s",
+                        "value": ns_bytes / (ns_ms / 1e3) / 1e9 if ns_ms > 0 else None,
+                        "definition": "SURVEY 8(d): 8 B x (1 + upward variants) x distinct words / neighbour-search time; "
+                                      "the block join does not probe, so this is an equivalent rate, not traffic"}
+
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         v, ms, kind, cores, what = cpu_reference_run(1, 0, REF_SAMPLE_TUPLES)
@@ -356,7 +369,7 @@ def run_gpu_arm(args):
         "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": t_e2e * 1e3,
                 "h2d_bytes_per_step": int(R_all * cfg.word_length), "d2h_bytes_per_step": int(d2h[0]) * world},
         "gpu_launches": int(launches_per_step * args.steps),
-        "roofline": roofline, "clocks": clocks,
+        "roofline": roofline, "neighbour_search": neighbour_search, "clocks": clocks,
     }
     if cpu:
         line["cpu_baseline"] = cpu
