@@ -77,33 +77,13 @@ __host__ __device__ __forceinline__ uint32_t filter_fp(uint64_t hf) {
 }
 
 #ifdef __CUDACC__
-// L2 eviction-priority hints: the filter should stay resident, table sectors and streamed
-// columns should not displace it.
-__device__ __forceinline__ uint64_t l2_policy_evict_last() {
-  uint64_t p;
-  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
-  return p;
-}
-__device__ __forceinline__ uint64_t l2_policy_evict_first() {
-  uint64_t p;
-  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
-  return p;
-}
-__device__ __forceinline__ uint4 ld_hint_u128(const void *ptr, uint64_t policy) {
-  uint4 v;
-  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
-               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-               : "l"(ptr), "l"(policy));
-  return v;
-}
-
 __device__ __forceinline__ bool filter_match(const uint4 &b, uint64_t hf) {
   const uint32_t f4 = filter_fp(hf) * 0x01010101u;
   const uint32_t m = __vcmpeq4(b.x, f4) | __vcmpeq4(b.y, f4) | __vcmpeq4(b.z, f4) | __vcmpeq4(b.w, f4);
   return m != 0u || (b.x & 1u) != 0u;
 }
 
-// slot table only: rank of `key` or NONE32 (after rank_columns_kernel `count` holds the rank)
+// slot table only: rank of `key` or NONE32 (after stage_ensure_lookup `count` holds the rank)
 __device__ __forceinline__ uint32_t table_rank(const Lookup &lk, uint64_t key) {
   uint64_t idx = mix64(key) & lk.mask;
   while (true) {

@@ -131,7 +131,7 @@ int exclusive_scan_u32(const uint32_t *in, uint32_t *out, uint64_t n, uint32_t *
 //   radix_digit_hist_kernel   ONE pass over the keys: the 256-bin histogram of every digit
 //   radix_digit_bases_kernel  exclusive scan of each histogram -> first output position of a digit
 //   radix_pass_kernel         per digit pass.  A tile (RS_TILE consecutive elements) ranks its
-//                             elements by digit (warp match + per-warp counters), learns how many
+//                             elements by digit (warp ballots + per-warp counters), learns how many
 //                             elements of each digit precede it from the tiles before it through a
 //                             chained look-back over `status` (aggregate / inclusive words, tiles
 //                             ordered by a ticket), reorders the tile in shared memory and writes

@@ -231,16 +231,6 @@ __global__ void __launch_bounds__(256)
   out[i] = word_cid[table_rank(lk, keys[i])];  // always present: the tuple was inserted here
 }
 
-static Layout layout_of(const State &s) {
-  Layout L{};
-  L.part = s.part;
-  L.n_parts = s.n_parts;
-  for (uint32_t i = 0; i + 1 < s.n_parts; i++) L.splitters[i] = s.splitters[i];
-  L.base = (uint32_t)s.bases[s.part];
-  L.hi = s.part + 1 < s.n_parts ? s.splitters[s.part] : ~0ull;
-  return L;
-}
-
 }  // namespace humid
 
 using namespace humid;

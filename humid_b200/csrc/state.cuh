@@ -97,8 +97,7 @@ struct State {
 
   // shard mode (include/humid_gpu_shard.h): the table is built from the tuples this shard
   // RECEIVED (keys of its range from every rank, with their global input positions) instead
-  // of the rank's own tuples; word columns then hold the shard's words, and after import_graph
-  // the gathered whole-job columns.
+  // of the rank's own tuples; the word columns then hold the shard's words.
   bool shard_mode = false;
   uint64_t tuple_base = 0, n_shard_words = 0;
   DevBuf<uint64_t> shard_keys;
@@ -168,14 +167,6 @@ struct State {
     HUMID_CUDA(cudaEventRecord(stats[idx].e1, stream));
   }
 };
-
-// First position handled by the forward scan of the Hamming-1 probe kernels: the prefix of that
-// many letters should be long enough that few words share it (4^p >= U).
-inline uint32_t scan_from_position(uint64_t U, uint32_t n) {
-  uint32_t p = 1;
-  while (p < n && (1ull << (2 * p)) < U) p++;
-  return p;
-}
 
 // RAII form: `{ Timed t(s, "probe", U, bytes); kernel<<<...>>>(); t.launches = 1; }`
 struct Timed {
