@@ -1,0 +1,151 @@
+// Block-wise FastQ reading for the `humid` executable: SURVEY.md §8(f) item 1, the host ingest in
+// front of the device path.  One BlockReader per input file runs in its own thread
+// (host/humid_main.cc); it reads 16 MiB blocks (plain or gzip), finds line ends with memchr and
+// hands out records as views into its buffer — no allocation and no copy per record.
+//
+// The observable rules are those of host/fastq_io.h's FastqReader (i.e. of fastp's reader as the
+// reference uses it, lib/fastp/src/fastqreader.cpp:206-327):
+//   * lines end at '\n', '\r' or "\r\n";
+//   * before a record, empty lines and lines not starting with '@' are skipped; the name keeps
+//     its '@';
+//   * a record whose sequence and quality lengths differ is reported on stderr and ends the input;
+//   * missing lines at the end of the data read as empty.
+#pragma once
+#include <zlib.h>
+
+#include <cstdio>
+#include <cstring>
+#include <iostream>
+#include <string>
+#include <vector>
+
+#include "fastq_io.h"
+
+namespace humid_host {
+
+struct Span {
+  const char *p = nullptr;
+  size_t n = 0;
+};
+
+struct RecordView {
+  Span name, seq, strand, qual;
+};
+
+class BlockReader {
+ public:
+  explicit BlockReader(const std::string &path, size_t block = 16u << 20) : path_(path), buf_(block) {
+    if (ends_with(path, ".gz")) {
+      gz_ = gzopen(path.c_str(), "rb");
+      if (!gz_) error_exit("Failed to open file: " + path);
+      gzbuffer(gz_, 1u << 20);
+    } else {
+      fp_ = std::fopen(path.c_str(), "rb");
+      if (!fp_) error_exit("Failed to open file: " + path);
+    }
+  }
+  ~BlockReader() {
+    if (gz_) gzclose(gz_);
+    if (fp_) std::fclose(fp_);
+  }
+  BlockReader(const BlockReader &) = delete;
+  BlockReader &operator=(const BlockReader &) = delete;
+
+  // false at end of input (or at a malformed record).  The views stay valid until the next call.
+  bool read(RecordView &r) {
+    while (true) {
+      size_t pos = mark_;
+      int st = parse(pos, r);
+      if (st == kNeedMore) {
+        if (!more()) drained_ = true;  // parse again: lines now end where the data ends
+        continue;
+      }
+      if (st == kEnd) return false;
+      mark_ = pos;
+      if (r.qual.n != r.seq.n) {
+        std::cerr << "ERROR: sequence and quality have different length:\n"
+                  << std::string(r.name.p, r.name.n) << "\n" << std::string(r.seq.p, r.seq.n) << "\n"
+                  << std::string(r.strand.p, r.strand.n) << "\n" << std::string(r.qual.p, r.qual.n) << std::endl;
+        return false;
+      }
+      return true;
+    }
+  }
+
+ private:
+  enum { kOk, kNeedMore, kEnd };
+
+  // One line starting at pos.  kNeedMore: no terminator in the buffer and the file has more.
+  int line(size_t &pos, Span &s) {
+    const char *b = buf_.data() + pos;
+    const size_t avail = end_ - pos;
+    const char *nl = avail ? (const char *)std::memchr(b, '\n', avail) : nullptr;
+    if (!nl && !drained_) return kNeedMore;
+    size_t len = nl ? (size_t)(nl - b) : avail;
+    size_t next = nl ? len + 1 : len;
+    if (const char *cr = len ? (const char *)std::memchr(b, '\r', len) : nullptr) {
+      size_t at = (size_t)(cr - b);
+      if (at + 1 < len || !nl) next = at + 1;  // a lone '\r' ends the line where it stands
+      len = at;                                // ("\r\n" keeps next = behind the '\n')
+    }
+    s.p = b;
+    s.n = len;
+    pos += next;
+    return kOk;
+  }
+
+  int parse(size_t &pos, RecordView &r) {
+    if (pos >= end_ && drained_) return kEnd;
+    // name: skip empty lines while data remains, and lines that do not start with '@'
+    while (true) {
+      if (int st = line(pos, r.name)) return st;
+      bool at_end = pos >= end_ && drained_;
+      if ((r.name.n == 0 && !at_end) || (r.name.n != 0 && r.name.p[0] != '@')) {
+        if (pos >= end_ && !drained_) return kNeedMore;
+        mark_ = pos;  // skipped for good
+        continue;
+      }
+      break;
+    }
+    if (r.name.n == 0) return kEnd;
+    if (int st = line(pos, r.seq)) return st;
+    if (int st = line(pos, r.strand)) return st;
+    if (int st = line(pos, r.qual)) return st;
+    return kOk;
+  }
+
+  // Keep the unconsumed tail [mark_, end_) at the front and read behind it.  false: nothing came.
+  bool more() {
+    if (finished_) return false;
+    if (mark_ > 0) {
+      std::memmove(buf_.data(), buf_.data() + mark_, end_ - mark_);
+      end_ -= mark_;
+      mark_ = 0;
+    }
+    if (end_ == buf_.size()) buf_.resize(buf_.size() * 2);  // one record longer than the block
+    size_t room = buf_.size() - end_;
+    long got;
+    if (gz_) {
+      got = gzread(gz_, buf_.data() + end_, (unsigned)std::min<size_t>(room, 1u << 30));
+      if (got < 0) error_exit("igzip: encountered while decompressing file: " + path_);
+    } else {
+      got = (long)std::fread(buf_.data() + end_, 1, room, fp_);
+    }
+    if (got <= 0) {
+      finished_ = true;
+      return false;
+    }
+    end_ += (size_t)got;
+    return true;
+  }
+
+  std::string path_;
+  std::vector<char> buf_;
+  size_t mark_ = 0, end_ = 0;  // [mark_, end_) = bytes not yet handed out
+  bool finished_ = false;      // the file has no more bytes
+  bool drained_ = false;       // ... and the parser knows: the last line ends at end_
+  gzFile gz_ = nullptr;
+  FILE *fp_ = nullptr;
+};
+
+}  // namespace humid_host

@@ -153,6 +153,17 @@ class Writer {
       error_exit("Failed to write: " + path_);
     }
   }
+  // name + suffix, sequence, strand, quality, each followed by '\n' (Read::toString)
+  template <class SpanT>
+  void write_view(const SpanT &name, const SpanT &seq, const SpanT &strand, const SpanT &qual,
+                  const std::string &name_suffix) {
+    line_.clear();
+    line_.append(name.p, name.n).append(name_suffix).push_back('\n');
+    line_.append(seq.p, seq.n).push_back('\n');
+    line_.append(strand.p, strand.n).push_back('\n');
+    line_.append(qual.p, qual.n).push_back('\n');
+    write(line_.data(), line_.size());
+  }
   void write_record(const Record &r, const std::string &name_suffix = std::string()) {
     line_.clear();
     line_.append(r.name).append(name_suffix).push_back('\n');
@@ -177,19 +188,23 @@ inline bool valid_umi(const char *s, size_t n) {
     if (s[i] != 'A' && s[i] != 'C' && s[i] != 'G' && s[i] != 'T') return false;
   return true;
 }
-inline void extract_umi(const std::string &header, size_t &off, size_t &len) {
-  size_t end = header.find(' ');
-  if (end == std::string::npos) end = header.size();
+inline void extract_umi(const char *header, size_t size, size_t &off, size_t &len) {
+  const char *sp = size ? (const char *)std::memchr(header, ' ', size) : nullptr;
+  const size_t end = sp ? (size_t)(sp - header) : size;
   for (char sep : {'_', ':'}) {
-    size_t last = header.rfind(sep, end ? end - 1 : 0);
-    if (end && last != std::string::npos && last < end && valid_umi(header.data() + last + 1, end - last - 1)) {
-      off = last + 1;
-      len = end - last - 1;
+    size_t last = end;  // position of the last `sep` before `end`, or `end` if there is none
+    while (last > 0 && header[last - 1] != sep) last--;
+    if (last > 0 && valid_umi(header + last, end - last)) {
+      off = last;
+      len = end - last;
       return;
     }
   }
   off = 0;
   len = 0;
+}
+inline void extract_umi(const std::string &header, size_t &off, size_t &len) {
+  extract_umi(header.data(), header.size(), off, len);
 }
 
 }  // namespace humid_host

@@ -10,13 +10,23 @@
 // ABI (include/humid_gpu.h) and runs on the GPU.  There is no CPU implementation of those
 // steps here: if the library reports an error the program prints it and exits like the
 // reference's error_exit does.
+//
+// Ingest: one thread per input file parses its FastQ in blocks
+// (host/fastq_block.h) and writes its share of every word straight into a page-locked batch
+// buffer; the main thread hands full batches to humid_gpu_add_batch, which uploads them while the
+// next batch is being parsed and the previous one is counted on the device.  The output passes
+// run one thread per file as well.
 #include <sys/stat.h>
 
+#include <condition_variable>
 #include <ctime>
 #include <fstream>
 #include <memory>
+#include <mutex>
+#include <thread>
 
 #include "../include/humid_gpu.h"
+#include "fastq_block.h"
 #include "fastq_io.h"
 
 using namespace humid_host;
@@ -124,25 +134,99 @@ Layout pre_compute(const vector<string> &files, size_t word_length) {
   return L;
 }
 
-// lock-step reader over all input files (readFiles / readFastq_, src/fastq.cc:37-47, :96-114):
-// the tuple stream ends as soon as any file runs out.
-class TupleReader {
- public:
-  explicit TupleReader(const vector<string> &files) {
-    for (const string &f : files) readers_.emplace_back(new FastqReader(f));
-    recs.resize(files.size());
-  }
-  bool next() {
-    bool ok = true;
-    for (size_t i = 0; i < readers_.size(); i++)
-      if (!readers_[i]->read(recs[i])) ok = false;
-    return ok;
-  }
-  vector<Record> recs;
+// ---- pass 1: tuples of all files in lock step (readFiles / readFastq_, src/fastq.cc:37-47,
+// :96-114): the tuple stream ends as soon as any file runs out --------------------------------
+constexpr size_t BATCH = 1u << 20;  // tuples per upload
+constexpr int N_SLOTS = 3;
 
- private:
-  vector<std::unique_ptr<FastqReader>> readers_;
+struct Slot {
+  uint8_t *chars = nullptr;     // BATCH x word_length, row-major; file i fills its own columns
+  uint16_t *seg_len = nullptr;  // BATCH x n_segments
+  uint64_t batch = 0;           // which batch this slot is collecting
+  size_t done = 0;              // files that have finished it
+  vector<size_t> rows;          // records each file contributed (< BATCH only at its end)
 };
+
+struct Ingest {
+  std::mutex mu;
+  std::condition_variable cv;
+  Slot slots[N_SLOTS];
+  bool stop = false;
+  size_t n = 0, S = 0;          // word length, segments
+  vector<size_t> seg_off;       // first column of a segment
+  Layout L;
+};
+
+// file i: segment (header UMI ? i + 1 : i); file 0 also fills segment 0 from its headers
+void ingest_file(Ingest &g, const string &path, size_t file) {
+  BlockReader reader(path);
+  RecordView rec;
+  const size_t seg = g.L.header_umi ? file + 1 : file;
+  const size_t take = g.L.nt_to_take[file], off = g.seg_off[seg];
+  bool ended = false;
+  for (uint64_t k = 0; !ended; k++) {
+    Slot &s = g.slots[k % N_SLOTS];
+    {
+      std::unique_lock<std::mutex> lk(g.mu);
+      g.cv.wait(lk, [&] { return g.stop || s.batch == k; });
+      if (g.stop) return;
+    }
+    size_t m = 0;
+    for (; m < BATCH; m++) {
+      if (!reader.read(rec)) { ended = true; break; }
+      // getNucleotides (src/fastq.cc:116-144) WITHOUT the padding / validation: the device applies
+      // makeStringSize_ and the ACGT filter from (chars, seg_len)
+      uint8_t *row = s.chars + m * g.n;
+      uint16_t *sl = s.seg_len + m * g.S;
+      auto put = [&](const char *p, size_t have, size_t want, size_t at, size_t which) {
+        size_t c = have < want ? have : want;
+        std::memcpy(row + at, p, c);
+        std::memset(row + at + c, 'N', want - c);
+        sl[which] = (uint16_t)c;
+      };
+      if (file == 0 && g.L.header_umi) {
+        size_t uo, ul;
+        extract_umi(rec.name.p, rec.name.n, uo, ul);
+        put(rec.name.p + uo, ul, g.L.header_umi, 0, 0);
+      }
+      put(rec.seq.p, rec.seq.n, take, off, seg);
+    }
+    std::lock_guard<std::mutex> lk(g.mu);
+    s.rows[file] = m;
+    s.done++;
+    g.cv.notify_all();
+  }
+}
+
+// ---- pass 2: every file is filtered / annotated by its own thread -----------------------------
+void rewrite_file(const string &in_path, const string &out_path, uint64_t total, const uint64_t *keep,
+                  const uint32_t *ids) {
+  BlockReader reader(in_path);
+  Writer out(out_path);
+  RecordView rec;
+  string suffix;
+  for (uint64_t t = 0; t < total && reader.read(rec); t++) {
+    if (keep && !(keep[t >> 6] >> (t & 63) & 1)) continue;
+    if (ids) suffix = ":" + std::to_string(ids[t]);
+    out.write_view(rec.name, rec.seq, rec.strand, rec.qual, suffix);
+  }
+}
+
+// Capacity hint for the word table (lets the device count batches while the next one uploads): size
+// of the first file / size of its first record, for plain files.  A wrong guess only costs a recount
+// (too small) or memory (too large), never the result.
+uint64_t estimate_tuples(const string &path) {
+  if (ends_with(path, ".gz")) return 0;
+  struct stat st;
+  if (stat(path.c_str(), &st) != 0 || st.st_size <= 0) return 0;
+  BlockReader reader(path, 1u << 16);
+  RecordView r;
+  if (!reader.read(r)) return 0;
+  size_t rec = r.name.n + r.seq.n + r.strand.n + r.qual.n + 4;
+  uint64_t est = (uint64_t)st.st_size / rec;
+  est += est / 16 + 1024;
+  return est < 0xF0000000ull ? est : 0;
+}
 
 void check(humid_gpu *h, int rc, const char *what) {
   if (rc != HUMID_GPU_OK) error_exit(string(what) + ": " + humid_gpu_last_error(h));
@@ -179,45 +263,52 @@ int main(int argc, char **argv) {
   if (seg_take.size() > HUMID_MAX_SEGMENTS) error_exit("too many input files");
   cfg.n_segments = (uint32_t)seg_take.size();
   for (size_t i = 0; i < seg_take.size(); i++) cfg.seg_take[i] = (uint32_t)seg_take[i];
+  cfg.expected_tuples = estimate_tuples(opt.files.front());
   humid_gpu *gpu = nullptr;
   check(nullptr, humid_gpu_create(&cfg, &gpu), "humid_gpu_create");
 
   t0 = start_message(log, "Reading data");
-  const size_t n = opt.word_length, S = seg_take.size(), BATCH = 1u << 20;
-  vector<uint8_t> chars(BATCH * n);
-  vector<uint16_t> seg_len(BATCH * S);
-  uint64_t total = 0, pending = 0, first = 0;
-  auto flush = [&] {
-    if (!pending) return;
-    check(gpu, humid_gpu_add_batch(gpu, chars.data(), seg_len.data(), first, pending), "humid_gpu_add_batch");
-    first += pending;
-    pending = 0;
-  };
+  uint64_t total = 0;
   {
-    TupleReader in(opt.files);
-    while (in.next()) {
-      // getNucleotides (src/fastq.cc:116-144) WITHOUT the padding / validation: the device
-      // applies makeStringSize_ and the ACGT filter from (chars, seg_len)
-      uint8_t *dst = chars.data() + pending * n;
-      uint16_t *sl = seg_len.data() + pending * S;
-      size_t s = 0;
-      auto put = [&](const char *p, size_t have, size_t take) {
-        size_t m = have < take ? have : take;
-        std::memcpy(dst, p, m);
-        std::memset(dst + m, 'N', take - m);
-        dst += take;
-        sl[s++] = (uint16_t)m;
-      };
-      if (L.header_umi) {
-        size_t off, len;
-        extract_umi(in.recs[0].name, off, len);
-        put(in.recs[0].name.data() + off, len, L.header_umi);
-      }
-      for (size_t i = 0; i < F; i++) put(in.recs[i].seq.data(), in.recs[i].seq.size(), L.nt_to_take[i]);
-      total++;
-      if (++pending == BATCH) flush();
+    Ingest g;
+    g.n = opt.word_length;
+    g.S = seg_take.size();
+    g.L = L;
+    size_t at = 0;
+    for (size_t t : seg_take) { g.seg_off.push_back(at); at += t; }
+    for (int j = 0; j < N_SLOTS; j++) {
+      void *c = nullptr, *l = nullptr;
+      check(gpu, humid_gpu_host_alloc(gpu, BATCH * g.n, &c), "humid_gpu_host_alloc");
+      check(gpu, humid_gpu_host_alloc(gpu, BATCH * g.S * sizeof(uint16_t), &l), "humid_gpu_host_alloc");
+      g.slots[j].chars = static_cast<uint8_t *>(c);
+      g.slots[j].seg_len = static_cast<uint16_t *>(l);
+      g.slots[j].batch = (uint64_t)j;
+      g.slots[j].rows.assign(F, 0);
     }
-    flush();
+    vector<std::thread> readers;
+    for (size_t i = 0; i < F; i++) readers.emplace_back(ingest_file, std::ref(g), opt.files[i], i);
+    for (uint64_t k = 0;; k++) {
+      Slot &s = g.slots[k % N_SLOTS];
+      {
+        std::unique_lock<std::mutex> lk(g.mu);
+        g.cv.wait(lk, [&] { return s.done == F; });
+      }
+      size_t m = BATCH;
+      for (size_t r : s.rows) m = r < m ? r : m;
+      if (m) check(gpu, humid_gpu_add_batch(gpu, s.chars, s.seg_len, total, m), "humid_gpu_add_batch");
+      total += m;
+      std::lock_guard<std::mutex> lk(g.mu);
+      if (m < BATCH) g.stop = true;  // some file has ended: so has the tuple stream
+      s.done = 0;
+      s.batch = k + N_SLOTS;
+      g.cv.notify_all();
+      if (g.stop) break;
+    }
+    for (std::thread &t : readers) t.join();
+    for (int j = 0; j < N_SLOTS; j++) {
+      humid_gpu_host_free(gpu, g.slots[j].chars);
+      humid_gpu_host_free(gpu, g.slots[j].seg_len);
+    }
   }
   end_message(log, t0);
 
@@ -232,35 +323,30 @@ int main(int argc, char **argv) {
 
   make_dirs(opt.dir_name);
 
-  // ---- writeFiltered (src/humid.cc:203-241) ---------------------------------------------------
+  // ---- writeFiltered (src/humid.cc:203-241): the keep bit of a tuple decides for all its files --
   if (opt.filter) {
     t0 = start_message(log, "Writing filtered results");
     vector<uint64_t> keep((total + 63) / 64 + 1);
     check(gpu, humid_gpu_keep_mask(gpu, 0, total, keep.data()), "humid_gpu_keep_mask");
-    vector<std::unique_ptr<Writer>> out;
-    for (const string &f : opt.files) out.emplace_back(new Writer(make_file_name(f, opt.dir_name, "dedup")));
-    TupleReader in(opt.files);
-    for (uint64_t t = 0; t < total && in.next(); t++)
-      if (keep[t >> 6] >> (t & 63) & 1)
-        for (size_t i = 0; i < F; i++) out[i]->write_record(in.recs[i]);
+    vector<std::thread> writers;
+    for (const string &f : opt.files)
+      writers.emplace_back(rewrite_file, f, make_file_name(f, opt.dir_name, "dedup"), total, keep.data(), nullptr);
+    for (std::thread &t : writers) t.join();
     end_message(log, t0);
   }
 
   // ---- writeAnnotated (:251-292) ------------------------------------------------------------
   if (opt.annotate) {
     t0 = start_message(log, "Writing annotated results");
-    vector<std::unique_ptr<Writer>> out;
-    for (const string &f : opt.files) out.emplace_back(new Writer(make_file_name(f, opt.dir_name, "annotated")));
-    TupleReader in(opt.files);
-    vector<uint32_t> ids(BATCH);
-    for (uint64_t lo = 0; lo < total; lo += BATCH) {
-      uint64_t m = std::min<uint64_t>(BATCH, total - lo);
-      check(gpu, humid_gpu_cluster_ids(gpu, lo, m, ids.data()), "humid_gpu_cluster_ids");
-      for (uint64_t k = 0; k < m && in.next(); k++) {
-        string suffix = ":" + std::to_string(ids[k]);
-        for (size_t i = 0; i < F; i++) out[i]->write_record(in.recs[i], suffix);
-      }
+    vector<uint32_t> ids(total + 1);
+    for (uint64_t lo = 0; lo < total; lo += 16 * BATCH) {
+      uint64_t m = std::min<uint64_t>(16 * BATCH, total - lo);
+      check(gpu, humid_gpu_cluster_ids(gpu, lo, m, ids.data() + lo), "humid_gpu_cluster_ids");
     }
+    vector<std::thread> writers;
+    for (const string &f : opt.files)
+      writers.emplace_back(rewrite_file, f, make_file_name(f, opt.dir_name, "annotated"), total, nullptr, ids.data());
+    for (std::thread &t : writers) t.join();
     end_message(log, t0);
   }
 

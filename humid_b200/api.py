@@ -25,7 +25,7 @@ EXPORTS = [
     "humid_gpu_add_batch", "humid_gpu_add_batch_device", "humid_gpu_finalize", "humid_gpu_counts",
     "humid_gpu_histogram", "humid_gpu_keep_mask", "humid_gpu_cluster_ids", "humid_gpu_debug_words",
     "humid_gpu_debug_neighbours", "humid_gpu_debug_clusters", "humid_gpu_stage_stats", "humid_gpu_stream",
-    "humid_gpu_debug_sort_pairs", "humid_gpu_debug_partition",
+    "humid_gpu_debug_sort_pairs", "humid_gpu_debug_partition", "humid_gpu_host_alloc", "humid_gpu_host_free",
 ]
 
 
@@ -80,6 +80,8 @@ def load_library() -> C.CDLL:
     L.humid_gpu_stage_stats.argtypes = [vp, P(StageStat), P(u32)]
     L.humid_gpu_stream.argtypes = [vp]
     L.humid_gpu_stream.restype = vp
+    L.humid_gpu_host_alloc.argtypes = [vp, C.c_size_t, P(vp)]
+    L.humid_gpu_host_free.argtypes = [vp, vp]
     L.humid_gpu_debug_sort_pairs.argtypes = [vp, vp, vp, u64, C.c_int, C.c_int, vp, vp]
     L.humid_gpu_debug_partition.argtypes = [vp, C.c_int, vp, u64, u64, u32, vp, u32, vp, vp, vp]
     _lib = L

@@ -61,11 +61,11 @@ def build_host(force: bool = False) -> str:
     """The `humid` executable (host/humid_main.cc): same CLI as the reference, linked against
     libhumid_gpu.so (found next to the binary through $ORIGIN)."""
     root = os.path.dirname(HERE)
-    srcs = [os.path.join(root, "host", f) for f in ("humid_main.cc", "fastq_io.h")] + [os.path.join(root, "include", "humid_gpu.h")]
+    srcs = [os.path.join(root, "host", f) for f in ("humid_main.cc", "fastq_io.h", "fastq_block.h")] + [os.path.join(root, "include", "humid_gpu.h")]
     if not force and os.path.exists(HOST_BIN) and all(os.path.getmtime(s) <= os.path.getmtime(HOST_BIN) for s in srcs):
         return HOST_BIN
     build()
-    cmd = ["g++", "-O2", "-std=c++17", "-Wall", "-o", HOST_BIN, srcs[0], "-L" + HERE, "-lhumid_gpu", "-lz",
+    cmd = ["g++", "-O2", "-std=c++17", "-Wall", "-pthread", "-o", HOST_BIN, srcs[0], "-L" + HERE, "-lhumid_gpu", "-lz",
            "-Wl,-rpath,$ORIGIN"]
     subprocess.run(cmd, check=True)
     return HOST_BIN

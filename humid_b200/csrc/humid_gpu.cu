@@ -142,6 +142,21 @@ int humid_gpu_reset(humid_gpu *h) {
   });
 }
 
+int humid_gpu_host_alloc(humid_gpu *h, size_t bytes, void **out) {
+  if (!h || !out) return HUMID_GPU_ERR_ARG;
+  *out = nullptr;
+  return guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(h->s.device));
+    HUMID_CUDA(cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault));
+  });
+}
+
+int humid_gpu_host_free(humid_gpu *h, void *p) {
+  if (!h) return HUMID_GPU_ERR_ARG;
+  if (!p) return HUMID_GPU_OK;
+  return guarded(h, [&] { HUMID_CUDA(cudaFreeHost(p)); });
+}
+
 static int add_batch_impl(humid_gpu *h, const uint8_t *chars, const uint16_t *seg_len, uint64_t first, uint64_t n,
                           bool on_device) {
   if (!h) return HUMID_GPU_ERR_ARG;

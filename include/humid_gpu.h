@@ -18,6 +18,7 @@
 #ifndef HUMID_GPU_H
 #define HUMID_GPU_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -74,6 +75,12 @@ const char *humid_gpu_last_error(const humid_gpu *h);
 /* The cudaStream_t all of h's device work is issued on (so a caller can record its own
  * events around calls, or order device-resident inputs before humid_gpu_add_batch_device). */
 void *humid_gpu_stream(humid_gpu *h);
+
+/* Page-locked host memory for the buffers handed to humid_gpu_add_batch: uploads from it run at
+ * the full PCIe rate and overlap the device work of the previous batch.  Plain malloc'ed memory
+ * works too, only slower.  Nothing in the reference corresponds to this. */
+int humid_gpu_host_alloc(humid_gpu *h, size_t bytes, void **out);
+int humid_gpu_host_free(humid_gpu *h, void *p);
 
 /* Pass 1 — replaces `makeWord` + `trie.add` in readData (src/humid.cc:92-99; makeWord
  * src/fastq.cc:146-161, getNucleotides :116-144, makeStringSize_ :57-66, Trie::add
