@@ -1,0 +1,60 @@
+"""host/fastq_block.h (block parser of the `humid` executable) against host/fastq_io.h (the line-by-line
+reader whose behaviour was pinned against the reference binary): same records, whatever the line
+endings, junk lines, truncation or block size."""
+import gzip
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+@pytest.fixture(scope="module")
+def checker(tmp_path_factory):
+    exe = str(tmp_path_factory.mktemp("bin") / "host_reader_check")
+    subprocess.run(["g++", "-O1", "-std=c++17", "-o", exe, os.path.join(HERE, "host_reader_check.cc"), "-lz"], check=True)
+    return exe
+
+
+def records(n, rng, eol=b"\n", umi=True):
+    out = []
+    for i in range(n):
+        L = int(rng.integers(0, 40))
+        seq = bytes(rng.choice(list(b"ACGTN"), L).tolist())
+        name = b"@r%d:%d" % (i, rng.integers(0, 99)) + (b"_" + bytes(rng.choice(list(b"ACGT"), 8).tolist()) if umi and i % 3 else b"") + \
+            (b" 1:N:0" if i % 2 else b"")
+        out.append(name + eol + seq + eol + b"+" + eol + b"I" * L + eol)
+    return out
+
+
+CASES = {
+    "plain": lambda rng: b"".join(records(300, rng)),
+    "crlf": lambda rng: b"".join(records(300, rng, b"\r\n")),
+    "lone_cr": lambda rng: b"".join(records(50, rng, b"\r")),
+    "mixed_eol": lambda rng: b"".join(r for k in range(60) for r in records(1, rng, [b"\n", b"\r\n", b"\r"][k % 3])),
+    "no_final_newline": lambda rng: b"".join(records(20, rng))[:-1],
+    "junk_between": lambda rng: b"\n\nhello\n" + b"garbage\n\n".join(records(40, rng)) + b"\n\ntrailing junk",
+    "truncated_record": lambda rng: b"".join(records(10, rng)) + b"@last\nACGT\n+\n",
+    "length_mismatch": lambda rng: b"".join(records(5, rng)) + b"@bad\nACGT\n+\nII\n" + b"".join(records(5, rng)),
+    "empty": lambda rng: b"",
+    "only_newlines": lambda rng: b"\n\n\r\n\n",
+    "long_lines": lambda rng: b"@x\n" + b"A" * 5000 + b"\n+\n" + b"I" * 5000 + b"\n" + b"".join(records(3, rng)),
+}
+
+
+@pytest.mark.parametrize("case", sorted(CASES))
+@pytest.mark.parametrize("gz", [False, True])
+def test_block_reader_matches_line_reader(checker, tmp_path, case, gz):
+    data = CASES[case](np.random.default_rng(len(case)))
+    path = str(tmp_path / ("in.fastq.gz" if gz else "in.fastq"))
+    with (gzip.open(path, "wb") if gz else open(path, "wb")) as f:
+        f.write(data)
+    ref = subprocess.run([checker, "old", path], capture_output=True, check=True)
+    for block in (16, 64, 1000, 1 << 20):
+        got = subprocess.run([checker, "block", path, str(block)], capture_output=True, check=True)
+        assert got.stdout == ref.stdout, (case, block)
+        assert (b"different length" in got.stderr) == (b"different length" in ref.stderr)
+    if case in ("plain", "crlf"):
+        assert ref.stdout.endswith(b"records 300\n")
