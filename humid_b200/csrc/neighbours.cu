@@ -98,22 +98,92 @@ __device__ __forceinline__ void join_emit(uint64_t *out, uint64_t pos, uint32_t 
   if (deg) atomicAdd(deg + b, 1u);
 }
 
+// A thread's hits stay in registers (offsets from its own position); when the buffer is full it is
+// appended at once (rare), at the end the whole CTA appends with ONE atomic on the pair counter — a
+// per-pair or even per-warp atomic on that single address would serialise the kernel.
+struct HitBuf {
+  uint32_t hits[JOIN_LOCAL_HITS];
+  uint32_t nh = 0;
+};
+
+template <int EMIT>
+__device__ __forceinline__ void hit_push(HitBuf &hb, uint32_t t, uint64_t i, uint32_t ri, const uint32_t *rank,
+                                         uint64_t *pairs, uint64_t cap, unsigned long long *counter, uint32_t *deg,
+                                         uint32_t col_base) {
+  if (hb.nh == JOIN_LOCAL_HITS) {
+    unsigned long long pos = atomicAdd(counter, (unsigned long long)hb.nh);
+#pragma unroll
+    for (int k = 0; k < JOIN_LOCAL_HITS; k++, pos++) {
+      const uint32_t rb = rank ? rank[i + hb.hits[k]] : (uint32_t)(i + hb.hits[k]);
+      if (pos < cap) join_emit<EMIT>(pairs, pos, ri, rb, col_base, deg);
+    }
+    if (pos <= cap && deg) atomicAdd(deg + ri, hb.nh);
+    hb.nh = 0;
+  }
+#pragma unroll
+  for (int k = 0; k < JOIN_LOCAL_HITS; k++)  // constant indices keep the buffer in registers
+    if (k == (int)hb.nh) hb.hits[k] = t;
+  hb.nh++;
+}
+
+// every thread of the CTA must call this
+template <int EMIT>
+__device__ __forceinline__ void hits_flush_cta(const HitBuf &hb, uint64_t i, uint32_t ri, const uint32_t *rank,
+                                               uint64_t *pairs, uint64_t cap, unsigned long long *counter,
+                                               uint32_t *deg, uint32_t col_base) {
+  const uint32_t lane = lane_id();
+  uint32_t inc = hb.nh;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+    if ((int)lane >= o) inc += t;
+  }
+  __shared__ uint32_t warp_total[JOIN_THREADS / 32];
+  __shared__ unsigned long long cta_base;
+  const uint32_t wid = threadIdx.x >> 5;
+  if (lane == 31) warp_total[wid] = inc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t sum = 0;
+    for (int k = 0; k < JOIN_THREADS / 32; k++) {
+      uint32_t c = warp_total[k];
+      warp_total[k] = sum;
+      sum += c;
+    }
+    cta_base = sum ? atomicAdd(counter, (unsigned long long)sum) : 0ull;
+  }
+  __syncthreads();
+  if (hb.nh) {
+    unsigned long long pos = cta_base + warp_total[wid] + (inc - hb.nh);
+    if (pos + hb.nh <= cap) {
+#pragma unroll
+      for (int k = 0; k < JOIN_LOCAL_HITS; k++) {
+        if (k < (int)hb.nh) {
+          const uint32_t rb = rank ? rank[i + hb.hits[k]] : (uint32_t)(i + hb.hits[k]);
+          join_emit<EMIT>(pairs, pos + k, ri, rb, col_base, deg);
+        }
+      }
+      if (deg) atomicAdd(deg + ri, hb.nh);
+    }
+  }
+}
+
+// Small groups (a word or two on average, the usual case at d = 1): one thread per position i of the
+// block order walks forward through its group.  A group is skipped (and its members flagged with
+// bit `block`) iff it has more than group_cap members; every member reaches the same verdict by
+// looking at most group_cap positions back and forth.
 template <int EMIT>
 __global__ void __launch_bounds__(JOIN_THREADS)
-    hamming_join_kernel(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ rank, uint64_t U, uint32_t d,
-                        const Blocks B, uint32_t block, uint64_t mask, uint32_t group_cap,
-                        uint64_t *__restrict__ pairs,
-                        uint64_t cap, unsigned long long *__restrict__ counter, uint32_t *__restrict__ deg,
-                        uint32_t col_base, uint32_t *__restrict__ flags, unsigned long long *__restrict__ n_flagged) {
+    hamming_join_walk_kernel(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ rank, uint64_t U,
+                             uint32_t d, const Blocks B, uint32_t block, uint64_t mask, uint32_t group_cap,
+                             uint64_t *__restrict__ pairs, uint64_t cap, unsigned long long *__restrict__ counter,
+                             uint32_t *__restrict__ deg, uint32_t col_base, uint32_t *__restrict__ flags,
+                             unsigned long long *__restrict__ n_flagged) {
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = i < U;
   const uint64_t w = live ? keys[i] : 0ull;
   const uint64_t g = w & mask;
-  const uint32_t lane = lane_id();
-  // hits stay in registers (offsets inside the group); the warp appends all of them with ONE
-  // atomic on the pair counter — a per-pair atomic on that single address would serialise
-  uint32_t hits[JOIN_LOCAL_HITS];
-  uint32_t nh = 0;
+  HitBuf hb;
   uint32_t ri = 0;
   if (live) {
     // members before i (stop as soon as the group is known to be too large)
@@ -134,58 +204,88 @@ __global__ void __launch_bounds__(JOIN_THREADS)
         const uint64_t v = keys[i + t];
         if (!linked(w, v, d)) continue;
         if (shares_earlier_block(B, block, v ^ w)) continue;  // found in an earlier block's order
-        if (nh == JOIN_LOCAL_HITS) {  // rare: local buffer full, append what we have
-          unsigned long long pos = atomicAdd(counter, (unsigned long long)nh);
-#pragma unroll
-          for (int k = 0; k < JOIN_LOCAL_HITS; k++, pos++) {
-            const uint32_t rb = rank ? rank[i + hits[k]] : (uint32_t)(i + hits[k]);
-            if (pos < cap) join_emit<EMIT>(pairs, pos, ri, rb, col_base, deg);
-          }
-          if (pos <= cap && deg) atomicAdd(deg + ri, nh);
-          nh = 0;
-        }
-#pragma unroll
-        for (int k = 0; k < JOIN_LOCAL_HITS; k++)  // constant indices keep the buffer in registers
-          if (k == (int)nh) hits[k] = t;
-        nh++;
+        hit_push<EMIT>(hb, t, i, ri, rank, pairs, cap, counter, deg, col_base);
       }
     }
   }
-  uint32_t inc = nh;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-    if ((int)lane >= o) inc += t;
-  }
-  // ... and the CTA's warps share one: warp totals -> CTA prefix in shared memory
-  __shared__ uint32_t warp_total[JOIN_THREADS / 32];
-  __shared__ unsigned long long cta_base;
-  const uint32_t wid = threadIdx.x >> 5;
-  if (lane == 31) warp_total[wid] = inc;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    uint32_t sum = 0;
-    for (int k = 0; k < JOIN_THREADS / 32; k++) {
-      uint32_t c = warp_total[k];
-      warp_total[k] = sum;
-      sum += c;
+  hits_flush_cta<EMIT>(hb, i, ri, rank, pairs, cap, counter, deg, col_base);
+}
+
+// Large groups: one warp per tile of 32 consecutive positions of the block order; lane L owns position t0 + L.
+// The warp learns the extent of every group that touches its tile (chunked scans backwards from
+// the tile for lane 0's group and forwards for the last lane's, head ballots inside), then streams
+// the keys from the tile onwards in chunks of 32: one coalesced load per chunk, every key
+// broadcast by shuffle, every lane testing it against its own word.  All lanes work whatever the
+// group sizes, and a key is loaded once per tile instead of once per pair.
+template <int EMIT>
+__global__ void __launch_bounds__(JOIN_THREADS)
+    hamming_join_tile_kernel(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ rank, uint64_t U, uint32_t d,
+                        const Blocks B, uint32_t block, uint64_t mask, uint32_t group_cap,
+                        uint64_t *__restrict__ pairs,
+                        uint64_t cap, unsigned long long *__restrict__ counter, uint32_t *__restrict__ deg,
+                        uint32_t col_base, uint32_t *__restrict__ flags, unsigned long long *__restrict__ n_flagged) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t lane = lane_id();
+  const uint64_t t0 = i - lane;
+  const bool live = i < U;
+  const uint64_t w = live ? keys[i] : 0ull;
+  const uint64_t g = w & mask;
+  HitBuf hb;
+  uint32_t ri = 0;
+  if (t0 < U) {  // warp-uniform
+    const uint32_t last = (uint32_t)min((uint64_t)31, U - 1 - t0);
+    const uint64_t g0 = __shfl_sync(0xffffffffu, g, 0), gl = __shfl_sync(0xffffffffu, g, last);
+    const uint64_t reach = group_cap == JOIN_NO_CAP ? ~0ull : (uint64_t)group_cap;
+    // Chunked scans.  The result is exact, or (after `reach` positions) merely known to exceed the cap.
+    uint64_t back = 0;
+    while (true) {
+      const uint64_t off = back + lane + 1;
+      const bool same = off <= t0 && (keys[t0 - off] & mask) == g0;
+      const unsigned b = __ballot_sync(0xffffffffu, same);
+      if (b != 0xffffffffu) { back += __ffs(~b) - 1; break; }
+      back += 32;
+      if (back > reach) break;
     }
-    cta_base = sum ? atomicAdd(counter, (unsigned long long)sum) : 0ull;
-  }
-  __syncthreads();
-  if (nh) {
-    unsigned long long pos = cta_base + warp_total[wid] + (inc - nh);
-    if (pos + nh <= cap) {
+    uint64_t fwd = 0;
+    const uint64_t behind = t0 + last + 1;
+    while (true) {
+      const uint64_t p = behind + fwd + lane;
+      const bool same = p < U && (keys[p] & mask) == gl;
+      const unsigned b = __ballot_sync(0xffffffffu, same);
+      if (b != 0xffffffffu) { fwd += __ffs(~b) - 1; break; }
+      fwd += 32;
+      if (fwd > reach) break;
+    }
+    // this lane's group [start, end)
+    const uint64_t gprev = __shfl_up_sync(0xffffffffu, g, 1);
+    const unsigned heads = __ballot_sync(0xffffffffu, live && (lane == 0 || g != gprev));
+    const int h = 31 - __clz((int)(heads & (0xffffffffu >> (31 - lane))));
+    const unsigned above = lane == 31 ? 0u : (heads & (0xffffffffu << (lane + 1)));
+    const uint64_t start = h <= 0 ? t0 - back : t0 + (uint64_t)h;
+    const uint64_t end = above ? t0 + (uint64_t)(__ffs(above) - 1) : behind + fwd;
+    const bool oversized = live && group_cap != JOIN_NO_CAP && end - start > (uint64_t)group_cap;
+    const bool testing = live && !oversized && end > i + 1;
+    if (testing || oversized) ri = rank ? rank[i] : (uint32_t)i;
+    if (oversized) {
+      atomicOr(flags + ri, 1u << block);
+      atomicAdd(n_flagged, 1ull);
+    }
+    const uint64_t my_end = testing ? end : 0ull;
+    uint64_t max_end = my_end;
 #pragma unroll
-      for (int k = 0; k < JOIN_LOCAL_HITS; k++) {
-        if (k < (int)nh) {
-          const uint32_t rb = rank ? rank[i + hits[k]] : (uint32_t)(i + hits[k]);
-          join_emit<EMIT>(pairs, pos + k, ri, rb, col_base, deg);
-        }
+    for (int o = 16; o > 0; o >>= 1) max_end = max(max_end, __shfl_xor_sync(0xffffffffu, max_end, o));
+    for (uint64_t c = t0; c < max_end; c += 32) {
+      const uint64_t kc = c + lane < U ? keys[c + lane] : 0ull;
+      const int m = (int)min((uint64_t)32, max_end - c);
+      for (int q = 0; q < m; q++) {
+        const uint64_t v = __shfl_sync(0xffffffffu, kc, q);
+        const uint64_t j = c + q;
+        if (j > i && j < my_end && linked(w, v, d) && !shares_earlier_block(B, block, v ^ w))
+          hit_push<EMIT>(hb, (uint32_t)(j - i), i, ri, rank, pairs, cap, counter, deg, col_base);
       }
-      if (deg) atomicAdd(deg + ri, nh);
     }
   }
+  hits_flush_cta<EMIT>(hb, i, ri, rank, pairs, cap, counter, deg, col_base);
 }
 
 // Flagged words only: one thread per (word, first modified position); iterative enumeration of
@@ -238,12 +338,25 @@ void launch_hamming_join(State &s, int emit, const uint64_t *keys, const uint32_
                          uint32_t *deg, uint32_t col_base, uint32_t *flags, unsigned long long *n_flagged) {
   const uint32_t d = s.cfg.distance;
   const unsigned grid = grid_for(n_words, JOIN_THREADS);
-  if (emit == JOIN_PAIRS_DEG)
-    hamming_join_kernel<JOIN_PAIRS_DEG><<<grid, JOIN_THREADS, 0, s.stream>>>(
-        keys, rank, n_words, d, B, block, B.mask[block], group_cap, out, cap, counter, deg, col_base, flags, n_flagged);
-  else
-    hamming_join_kernel<JOIN_DIRECTED><<<grid, JOIN_THREADS, 0, s.stream>>>(
-        keys, rank, n_words, d, B, block, B.mask[block], group_cap, out, cap, counter, deg, col_base, flags, n_flagged);
+  // expected group size if the block values were uniform: words / 4^letters.  Measured: at 1.3 and at 13
+  // words per group the per-thread walks win (0.43 vs 1.06 ms, 9.3 vs 13.5 ms), at 300 the tile kernel
+  // does (5.7 vs 8.9 ms); the switch sits in between.
+  const int letters = __builtin_popcountll(B.mask[block]) / 2;
+  const double expected = letters >= 32 ? 0.0 : (double)n_words / (double)(1ull << (2 * letters));
+  bool tile = expected >= 48.0;
+  if (const char *e = std::getenv("HUMID_GPU_JOIN_KERNEL"))  // testing knob: "tile" or "walk"
+    tile = e[0] == 't';
+#define HUMID_JOIN(KERNEL, MODE)                                                                              \
+  KERNEL<MODE><<<grid, JOIN_THREADS, 0, s.stream>>>(keys, rank, n_words, d, B, block, B.mask[block], group_cap, out, \
+                                                    cap, counter, deg, col_base, flags, n_flagged)
+  if (emit == JOIN_PAIRS_DEG) {
+    if (tile) HUMID_JOIN(hamming_join_tile_kernel, JOIN_PAIRS_DEG);
+    else HUMID_JOIN(hamming_join_walk_kernel, JOIN_PAIRS_DEG);
+  } else {
+    if (tile) HUMID_JOIN(hamming_join_tile_kernel, JOIN_DIRECTED);
+    else HUMID_JOIN(hamming_join_walk_kernel, JOIN_DIRECTED);
+  }
+#undef HUMID_JOIN
 }
 
 Blocks make_blocks(uint32_t n, uint32_t d, int lo_bit[], int hi_bit[]) {

@@ -150,12 +150,14 @@ JOIN_CASES = [  # (config index, tuples, overrides) — dense enough that small 
 ]
 
 
-@pytest.mark.parametrize("group_cap", [1, 3, 16])
+@pytest.mark.parametrize("kernel", ["walk", "tile"])
+@pytest.mark.parametrize("group_cap", [1, 3, 16, 100000])
 @pytest.mark.parametrize("ci,R,kw", JOIN_CASES, ids=[f"c{c + 1}_{R}_{'_'.join(f'{k}{v}' for k, v in kw.items())}" for c, R, kw in JOIN_CASES])
-def test_oversized_groups_take_the_probe_path(monkeypatch, ci, R, kw, group_cap):
+def test_oversized_groups_take_the_probe_path(monkeypatch, ci, R, kw, group_cap, kernel):
     """The block join hands groups above the cap to variant probing; with tiny caps most or all pairs
     come from that path, with middling ones the two paths share the pairs.  Same lists either way."""
     monkeypatch.setenv("HUMID_GPU_JOIN_CAP", str(group_cap))
+    monkeypatch.setenv("HUMID_GPU_JOIN_KERNEL", kernel)  # both group-walk kernels, whatever the group sizes
     cfg = baseline_config(ci, R, **kw)
     s = Synth(cfg)
     chars = s.word_chars()
