@@ -77,24 +77,6 @@ __device__ void probe_substitutions(uint64_t base, uint32_t n, int budget, uint3
   }
 }
 
-// Substitution-only variants: one thread per (word, first substituted position).
-__global__ void __launch_bounds__(128)
-    edit_candidates_subst_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, uint32_t d,
-                                 const Lookup lk, uint64_t *__restrict__ cand, uint64_t cap,
-                                 unsigned long long *__restrict__ counter) {
-  uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  uint64_t r = gid / n;
-  if (r >= U) return;
-  const uint32_t p1 = (uint32_t)(gid - r * n);
-  const uint64_t w = word_key[r];
-  const uint32_t sh = 2 * (n - 1 - p1);
-  const uint64_t orig = (w >> sh) & 3ull;
-  for (uint32_t a = 1; a < 4; a++) {
-    uint64_t v1 = (w & ~(3ull << sh)) | (((orig + a) & 3ull) << sh);
-    probe_substitutions(v1, n, (int)d - 1, p1 + 1, w, (uint32_t)r, lk, cand, cap, counter, true);
-  }
-}
-
 // Deletion of letter i + insertion of letter c so that it lands at position q (a one-letter
 // block shift), then up to d-2 substitutions: one thread per (word, i, q).
 __global__ void __launch_bounds__(128)
@@ -240,27 +222,67 @@ int stage_neighbours_edit(State &s) {
   // phase 1: candidate pairs (with duplicates)
   uint64_t cap = std::max<uint64_t>(s.entries.cap, std::max<uint64_t>(8 * U, 1u << 20));
   uint64_t n_cand = 0;
-  for (int attempt = 0; attempt < 2; attempt++) {
+  for (int attempt = 0; attempt < 4; attempt++) {
     s.entries.ensure(cap);
     cap = s.entries.cap;
-    HUMID_CUDA(cudaMemsetAsync(s.counters.p + 5, 0, sizeof(unsigned long long), s.stream));
+    unsigned long long *counter = s.counters.p + 5;
+    HUMID_CUDA(cudaMemsetAsync(counter, 0, sizeof(unsigned long long), s.stream));
+    // (a) substitutions only = every pair within Hamming distance d: block join without the
+    //     dominance rule (neighbours.cu), both directions of a pair become candidates
     {
-      // variants probed per word: substitutions 3n + 9C(n,2) (+27C(n,3)), shifts 4n(n-1)(1 + 3n at d=3)
-      double subs = 3.0 * n + 4.5 * n * (n - 1) + (d >= 3 ? 4.5 * n * (n - 1) * (n - 2) : 0.0);
-      double shifts = 4.0 * n * (n - 1) * (d >= 3 ? 1.0 + 3.0 * n : 1.0);
-      Timed t(s, "edit_candidates", U, (uint64_t)(U * 8.0 * (1.0 + subs + shifts)));
-      edit_candidates_subst_kernel<<<grid_for(U * n, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, d, lk, s.entries.p,
-                                                                              cap, s.counters.p + 5);
-      edit_candidates_shift_kernel<<<grid_for(U * n * n, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, d, lk,
-                                                                                  s.entries.p, cap, s.counters.p + 5);
-      t.launches = 2;
+      int lo_bit[HAM_MAX_D + 1], hi_bit[HAM_MAX_D + 1];
+      const Blocks B = make_blocks(n, d, lo_bit, hi_bit);
+      s.key_alt.ensure(U + 1);
+      s.entries_alt.ensure(U + 1);
+      s.entry_val.ensure(U + 1);
+      s.entry_val_alt.ensure(U + 1);
+      for (uint32_t b = 0; b <= d; b++) {
+        const uint64_t *keys = s.word_key.p;
+        const uint32_t *rank = nullptr;
+        if (b > 0 && hi_bit[b] > lo_bit[b]) {
+          uint64_t *kb[2] = {s.key_alt.p, s.entries_alt.p};
+          uint32_t *vb[2] = {s.entry_val.p, s.entry_val_alt.p};
+          int launches = 0;
+          const uint64_t passes = (uint64_t)(hi_bit[b] - lo_bit[b] + 7) / 8;
+          Timed t(s, "join_sort", U, U * (8 + (8 + 12) + (passes - 1) * 24));
+          int cur = radix_sort_bits_indexed(s.word_key.p, kb, vb, U, lo_bit[b], hi_bit[b], s.scratch, s.stream, &launches);
+          t.launches = launches;
+          k += launches;
+          keys = kb[cur];
+          rank = vb[cur];
+        }
+        Timed t(s, "edit_candidates_join", U, U * (8 + 8 + (rank ? 4 : 0)));
+        launch_hamming_join(s, JOIN_CANDIDATES, keys, rank, U, B, b, JOIN_NO_CAP, s.entries.p, cap / 2, counter, nullptr,
+                            0u, nullptr, nullptr);
+        k++;
+      }
+      uint64_t pairs = 0;
+      HUMID_CUDA(cudaMemcpyAsync(&pairs, counter, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+      HUMID_CUDA(cudaStreamSynchronize(s.stream));
+      if (2 * pairs > cap) {  // the counter kept counting: come back with room for these and as many again
+        cap = 4 * pairs;
+        n_cand = cap + 1;
+        continue;
+      }
+      pairs *= 2;  // from here on the cursor counts candidates
+      HUMID_CUDA(cudaMemcpyAsync(counter, &pairs, sizeof(uint64_t), cudaMemcpyHostToDevice, s.stream));
+      HUMID_CUDA(cudaStreamSynchronize(s.stream));
     }
-    k += 2;
+    // (b) one deletion + one insertion (a one-letter block shift) and up to d-2 substitutions: variants
+    //     probed against the word table, 4 n (n-1) (1 + 3 n at d = 3) per word
+    {
+      double shifts = 4.0 * n * (n - 1) * (d >= 3 ? 1.0 + 3.0 * n : 1.0);
+      Timed t(s, "edit_candidates", U, (uint64_t)(U * 8.0 * (1.0 + shifts)));
+      edit_candidates_shift_kernel<<<grid_for(U * n * n, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, d, lk,
+                                                                                  s.entries.p, cap, counter);
+    }
+    k++;
     HUMID_CUDA(cudaMemcpyAsync(&n_cand, s.counters.p + 5, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     if (n_cand <= cap) break;
     cap = n_cand;
   }
+  if (n_cand > cap) throw CudaError{"edit-distance candidates: the list kept outgrowing its buffer"};
   if (n_cand >= 0xFFFFFFFFull) throw CudaError{"too many edit-distance candidate pairs"};
 
   // sort + unique -> per-query candidate lists in rank (== lexicographic) order

@@ -64,11 +64,13 @@ __device__ __forceinline__ bool shares_earlier_block(const Blocks &B, uint32_t b
 }
 
 // a precedes b in rank, 1..d letters differ: linked iff a[p] <= b[p] wherever they differ
+// DOMINANCE false: any pair within Hamming distance d (candidates of the edit-distance search)
+template <bool DOMINANCE>
 __device__ __forceinline__ bool linked(uint64_t a, uint64_t b, uint32_t d) {
   const uint64_t x = a ^ b;
   const uint64_t diff = (x | (x >> 1)) & LETTER_LOW;
   if ((uint32_t)__popcll(diff) > d) return false;
-  if (d == 1) return true;  // the only differing letter decides the order, and a < b
+  if (!DOMINANCE || d == 1) return true;  // d == 1: the only differing letter decides the order, and a < b
   const uint64_t ah = (a >> 1) & LETTER_LOW, bh = (b >> 1) & LETTER_LOW, al = a & LETTER_LOW, bl = b & LETTER_LOW;
   const uint64_t a_greater = (ah & ~bh) | (~(ah ^ bh) & al & ~bl);
   return (a_greater & diff) == 0;
@@ -82,6 +84,8 @@ __device__ __forceinline__ bool linked(uint64_t a, uint64_t b, uint32_t d) {
 // EMIT (state.cuh): JOIN_PAIRS_DEG   pairs[k] = a << 32 | b, deg[a]++, deg[b]++        (single GPU)
 //                   JOIN_DIRECTED    out[2k] = a << 32 | (col_base + b), out[2k+1] = b << 32 | (col_base + a),
 //                                    deg (if not null) counted per row                  (shards)
+//                   JOIN_CANDIDATES  as JOIN_DIRECTED, but every pair within Hamming distance d counts
+//                                    (no dominance rule)                                 (edit-distance candidates)
 // group_cap == JOIN_NO_CAP: every group is walked whatever its size, nothing is flagged.
 constexpr int JOIN_LOCAL_HITS = 6;
 constexpr int JOIN_THREADS = 512;
@@ -202,7 +206,7 @@ __global__ void __launch_bounds__(JOIN_THREADS)
     } else {
       for (uint32_t t = 1; t <= after; t++) {
         const uint64_t v = keys[i + t];
-        if (!linked(w, v, d)) continue;
+        if (!linked<EMIT != JOIN_CANDIDATES>(w, v, d)) continue;
         if (shares_earlier_block(B, block, v ^ w)) continue;  // found in an earlier block's order
         hit_push<EMIT>(hb, t, i, ri, rank, pairs, cap, counter, deg, col_base);
       }
@@ -280,7 +284,7 @@ __global__ void __launch_bounds__(JOIN_THREADS)
       for (int q = 0; q < m; q++) {
         const uint64_t v = __shfl_sync(0xffffffffu, kc, q);
         const uint64_t j = c + q;
-        if (j > i && j < my_end && linked(w, v, d) && !shares_earlier_block(B, block, v ^ w))
+        if (j > i && j < my_end && linked<EMIT != JOIN_CANDIDATES>(w, v, d) && !shares_earlier_block(B, block, v ^ w))
           hit_push<EMIT>(hb, (uint32_t)(j - i), i, ri, rank, pairs, cap, counter, deg, col_base);
       }
     }
@@ -352,9 +356,12 @@ void launch_hamming_join(State &s, int emit, const uint64_t *keys, const uint32_
   if (emit == JOIN_PAIRS_DEG) {
     if (tile) HUMID_JOIN(hamming_join_tile_kernel, JOIN_PAIRS_DEG);
     else HUMID_JOIN(hamming_join_walk_kernel, JOIN_PAIRS_DEG);
-  } else {
+  } else if (emit == JOIN_DIRECTED) {
     if (tile) HUMID_JOIN(hamming_join_tile_kernel, JOIN_DIRECTED);
     else HUMID_JOIN(hamming_join_walk_kernel, JOIN_DIRECTED);
+  } else {
+    if (tile) HUMID_JOIN(hamming_join_tile_kernel, JOIN_CANDIDATES);
+    else HUMID_JOIN(hamming_join_walk_kernel, JOIN_CANDIDATES);
   }
 #undef HUMID_JOIN
 }

@@ -190,7 +190,7 @@ struct Blocks {
   uint32_t n_blocks;
   uint64_t mask[HAM_MAX_D + 1];  // bits of block b (block 0 = first letters = highest bits)
 };
-constexpr int JOIN_PAIRS_DEG = 0, JOIN_DIRECTED = 1;
+constexpr int JOIN_PAIRS_DEG = 0, JOIN_DIRECTED = 1, JOIN_CANDIDATES = 2;
 constexpr uint32_t JOIN_NO_CAP = 0xFFFFFFFFu;
 Blocks make_blocks(uint32_t n, uint32_t d, int lo_bit[], int hi_bit[]);  // arrays of HAM_MAX_D + 1
 void launch_hamming_join(State &s, int emit, const uint64_t *keys, const uint32_t *rank, uint64_t n_words, const Blocks &B,
