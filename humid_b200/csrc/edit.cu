@@ -154,18 +154,105 @@ __device__ __forceinline__ uint32_t lower_letter(const uint64_t *__restrict__ ke
   return lo;
 }
 
+// Number of times levenshtein_ yields `v` for query `w` when v is the only other word on its paths:
+// the number of move sequences (frames of the recursion) that arrive at v's leaf with the query used
+// up.  State = (letters of v consumed t, query position p, budget k); p - t stays within +-d, so a
+// level is a (2 D + 1) x (D + 1) band of counters.  Moves exactly as in the replay below: deletion
+// (t, p+1, k-1) with no bound on p; the child v[t] only if v[t] >= w[p] (w[p] = 0 past the end);
+// match / substitution (t+1, p+1, k - [v[t] != w[p]]) needs p < n; insertion (t+1, p, k-1).
+constexpr int DPD = 3;  // EDIT_MAX_D
+__device__ uint32_t single_candidate_yields(uint64_t w, uint64_t v, uint32_t n, int d) {
+  uint32_t cur[2 * DPD + 1][DPD + 1];
+#pragma unroll
+  for (int o = 0; o <= 2 * DPD; o++)
+#pragma unroll
+    for (int k = 0; k <= DPD; k++) cur[o][k] = 0;
+#pragma unroll
+  for (int k = 0; k <= DPD; k++)
+    if (k == d) cur[DPD][k] = 1;
+  for (uint32_t t = 0;; t++) {
+    // deletions inside the level, in increasing p so that chains are counted
+#pragma unroll
+    for (int o = 0; o < 2 * DPD; o++)
+#pragma unroll
+      for (int k = 1; k <= DPD; k++) cur[o + 1][k - 1] += cur[o][k];
+    if (t == n) break;
+    const uint32_t c = (uint32_t)(v >> (2 * (n - 1 - t))) & 3u;
+    uint32_t nxt[2 * DPD + 1][DPD + 1];
+#pragma unroll
+    for (int o = 0; o <= 2 * DPD; o++)
+#pragma unroll
+      for (int k = 0; k <= DPD; k++) nxt[o][k] = 0;
+#pragma unroll
+    for (int o = 0; o <= 2 * DPD; o++) {
+      const int p = (int)t + o - DPD;
+      if (p < 0) continue;
+      const bool inside = (uint32_t)p < n;
+      const uint32_t wl = inside ? (uint32_t)(w >> (2 * (n - 1 - (uint32_t)p))) & 3u : 0u;
+      if (c < wl) continue;
+      const int cost = c != wl ? 1 : 0;
+#pragma unroll
+      for (int k = 0; k <= DPD; k++) {
+        const uint32_t ways = cur[o][k];
+        if (inside) {  // match / substitution: same p - t (constant indices keep the band in registers)
+          if (cost == 0) nxt[o][k] += ways;
+          else if (k >= 1) nxt[o][k - 1] += ways;
+        }
+        if (k >= 1 && o >= 1) nxt[o - 1][k - 1] += ways;         // insertion: p stays, t advances
+      }
+    }
+#pragma unroll
+    for (int o = 0; o <= 2 * DPD; o++)
+#pragma unroll
+      for (int k = 0; k <= DPD; k++) cur[o][k] = nxt[o][k];
+  }
+  uint32_t yields = 0;  // level n, p >= n
+#pragma unroll
+  for (int o = DPD; o <= 2 * DPD; o++)
+#pragma unroll
+    for (int k = 0; k <= DPD; k++) yields += cur[o][k];
+  return yields;
+}
+
 __global__ void __launch_bounds__(128)
     edit_replay_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, int d,
                        const uint32_t *__restrict__ cand_row, const uint32_t *__restrict__ cand_v,
                        const uint64_t *__restrict__ cand_key, uint64_t *__restrict__ entries,
                        uint32_t *__restrict__ entry_val, uint64_t cap, unsigned long long *__restrict__ counter) {
   uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (r >= U) return;
-  const uint32_t seg = cand_row[r], m = cand_row[r + 1] - seg;
-  if (m == 0) return;
-  const uint64_t w = word_key[r];
+  const bool live = r < U;
+  const uint32_t seg = live ? cand_row[r] : 0u, m = live ? cand_row[r + 1] - seg : 0u;
+  const uint64_t w = live ? word_key[r] : 0ull;
   const uint64_t *keys = cand_key + seg;
   const uint32_t *ranks = cand_v + seg;
+  // One candidate (most queries): every yield is that word, only their number matters — counted by
+  // the path-counting recurrence instead of walking the paths.  The warp reserves its output once.
+  {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t yields = m == 1 ? single_candidate_yields(w, keys[0], n, d) : 0u;
+    uint32_t inc = yields;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+      if ((int)lane >= o) inc += t;
+    }
+    const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
+    if (total) {
+      unsigned long long base = 0;
+      if (lane == 31) base = atomicAdd(counter, 2ull * total);
+      base = __shfl_sync(0xffffffffu, base, 31) + 2ull * (inc - yields);
+      if (yields && base + 2ull * yields <= cap) {
+        const uint32_t v = ranks[0];
+        for (uint32_t y = 0; y < yields; y++, base += 2) {
+          entries[base] = (r << 32) | (uint32_t)r;
+          entry_val[base] = v;
+          entries[base + 1] = ((uint64_t)v << 32) | (uint32_t)r;
+          entry_val[base + 1] = (uint32_t)r;
+        }
+      }
+    }
+  }
+  if (m < 2) return;
   Frame stk[EDIT_STACK];
   int sp = 0;
   stk[sp++] = Frame{0u, m, 0, 0, (int8_t)d, 0};
