@@ -214,45 +214,65 @@ __device__ uint32_t single_candidate_yields(uint64_t w, uint64_t v, uint32_t n, 
   return yields;
 }
 
+// Queries with one candidate are finished here; those with more are listed for the walk below, so
+// that its warps are full of work.
 __global__ void __launch_bounds__(128)
-    edit_replay_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, int d,
-                       const uint32_t *__restrict__ cand_row, const uint32_t *__restrict__ cand_v,
-                       const uint64_t *__restrict__ cand_key, uint64_t *__restrict__ entries,
-                       uint32_t *__restrict__ entry_val, uint64_t cap, unsigned long long *__restrict__ counter) {
+    edit_replay_single_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, int d,
+                              const uint32_t *__restrict__ cand_row, const uint32_t *__restrict__ cand_v,
+                              const uint64_t *__restrict__ cand_key, uint64_t *__restrict__ entries,
+                              uint32_t *__restrict__ entry_val, uint64_t cap, unsigned long long *__restrict__ counter,
+                              uint32_t *__restrict__ multi_list, unsigned long long *__restrict__ n_multi) {
   uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = r < U;
   const uint32_t seg = live ? cand_row[r] : 0u, m = live ? cand_row[r + 1] - seg : 0u;
   const uint64_t w = live ? word_key[r] : 0ull;
-  const uint64_t *keys = cand_key + seg;
-  const uint32_t *ranks = cand_v + seg;
   // One candidate (most queries): every yield is that word, only their number matters — counted by
   // the path-counting recurrence instead of walking the paths.  The warp reserves its output once.
-  {
-    const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t yields = m == 1 ? single_candidate_yields(w, keys[0], n, d) : 0u;
-    uint32_t inc = yields;
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t yields = m == 1 ? single_candidate_yields(w, cand_key[seg], n, d) : 0u;
+  uint32_t inc = yields;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-      if ((int)lane >= o) inc += t;
-    }
-    const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
-    if (total) {
-      unsigned long long base = 0;
-      if (lane == 31) base = atomicAdd(counter, 2ull * total);
-      base = __shfl_sync(0xffffffffu, base, 31) + 2ull * (inc - yields);
-      if (yields && base + 2ull * yields <= cap) {
-        const uint32_t v = ranks[0];
-        for (uint32_t y = 0; y < yields; y++, base += 2) {
-          entries[base] = (r << 32) | (uint32_t)r;
-          entry_val[base] = v;
-          entries[base + 1] = ((uint64_t)v << 32) | (uint32_t)r;
-          entry_val[base + 1] = (uint32_t)r;
-        }
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+    if ((int)lane >= o) inc += t;
+  }
+  const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
+  if (total) {
+    unsigned long long base = 0;
+    if (lane == 31) base = atomicAdd(counter, 2ull * total);
+    base = __shfl_sync(0xffffffffu, base, 31) + 2ull * (inc - yields);
+    if (yields && base + 2ull * yields <= cap) {
+      const uint32_t v = cand_v[seg];
+      for (uint32_t y = 0; y < yields; y++, base += 2) {
+        entries[base] = (r << 32) | (uint32_t)r;
+        entry_val[base] = v;
+        entries[base + 1] = ((uint64_t)v << 32) | (uint32_t)r;
+        entry_val[base + 1] = (uint32_t)r;
       }
     }
   }
-  if (m < 2) return;
+  const unsigned many = __ballot_sync(0xffffffffu, m >= 2);
+  if (many) {
+    unsigned long long at = 0;
+    const int leader = __ffs(many) - 1;
+    if ((int)lane == leader) at = atomicAdd(n_multi, (unsigned long long)__popc(many));
+    at = __shfl_sync(0xffffffffu, at, leader);
+    if (m >= 2) multi_list[at + __popc(many & ((1u << lane) - 1u))] = (uint32_t)r;
+  }
+}
+
+__global__ void __launch_bounds__(128)
+    edit_replay_kernel(const uint64_t *__restrict__ word_key, const uint32_t *__restrict__ multi_list, uint64_t n_multi,
+                       uint32_t n, int d, const uint32_t *__restrict__ cand_row, const uint32_t *__restrict__ cand_v,
+                       const uint64_t *__restrict__ cand_key, uint64_t *__restrict__ entries,
+                       uint32_t *__restrict__ entry_val, uint64_t cap, unsigned long long *__restrict__ counter) {
+  const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= n_multi) return;
+  const uint64_t r = multi_list[gid];
+  const uint32_t seg = cand_row[r], m = cand_row[r + 1] - seg;
+  const uint64_t w = word_key[r];
+  const uint64_t *keys = cand_key + seg;
+  const uint32_t *ranks = cand_v + seg;
   Frame stk[EDIT_STACK];
   int sp = 0;
   stk[sp++] = Frame{0u, m, 0, 0, (int8_t)d, 0};
@@ -419,13 +439,26 @@ int stage_neighbours_edit(State &s) {
     s.entry_val.ensure(ecap);
     ecap = std::min<uint64_t>(s.entries_alt.cap, s.entry_val.cap);
     HUMID_CUDA(cudaMemsetAsync(s.counters.p + 2, 0, sizeof(unsigned long long), s.stream));
+    HUMID_CUDA(cudaMemsetAsync(s.counters.p + 43, 0, sizeof(unsigned long long), s.stream));
+    s.word_flags.ensure(U + 1);  // list of the queries with two or more candidates
+    uint64_t n_multi = 0;
     {
-      Timed t(s, "edit_replay", U, n_distinct * 12 + U * 16);
-      edit_replay_kernel<<<grid_for(U, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, (int)d, s.work_a.p, s.work_c.p,
-                                                                 s.key_alt.p, s.entries_alt.p, s.entry_val.p, ecap,
-                                                                 s.counters.p + 2);
+      Timed t(s, "edit_replay_single", U, U * 16 + n_distinct * 12);
+      edit_replay_single_kernel<<<grid_for(U, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, (int)d, s.work_a.p, s.work_c.p,
+                                                                        s.key_alt.p, s.entries_alt.p, s.entry_val.p, ecap,
+                                                                        s.counters.p + 2, s.word_flags.p,
+                                                                        s.counters.p + 43);
     }
-    k++;
+    HUMID_CUDA(cudaMemcpyAsync(&n_multi, s.counters.p + 43, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    if (n_multi) {
+      Timed t(s, "edit_replay", n_multi, n_distinct * 12 + n_multi * 16);
+      edit_replay_kernel<<<grid_for(n_multi, 128), 128, 0, s.stream>>>(s.word_key.p, s.word_flags.p, n_multi, n, (int)d,
+                                                                       s.work_a.p, s.work_c.p, s.key_alt.p,
+                                                                       s.entries_alt.p, s.entry_val.p, ecap,
+                                                                       s.counters.p + 2);
+    }
+    k += 2;
     HUMID_CUDA(cudaMemcpyAsync(&s.n_entries, s.counters.p + 2, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     if (s.n_entries <= ecap) break;
