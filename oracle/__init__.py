@@ -20,6 +20,7 @@ REF_HUMID = os.path.join(HERE, "_ref", "humid")
 REF_PROBE = os.path.join(HERE, "_ref", "trie_probe")
 REFERENCE_ROOT = "/root/reference"
 INVALID = np.uint64(0xFFFFFFFFFFFFFFFF)
+MAX_NARROW = 31  # longest word held in one uint64 (the spare top bit keeps INVALID unambiguous)
 
 _u8p = np.ctypeslib.ndpointer(np.uint8, flags="C")
 _u16p = np.ctypeslib.ndpointer(np.uint16, flags="C")
@@ -59,6 +60,11 @@ def lib() -> C.CDLL:
         L.oracle_histogram.restype = C.c_uint64
         L.oracle_histogram.argtypes = [C.c_void_p, C.c_int, _u64p, _u64p, C.c_uint64]
         L.oracle_pack_words.argtypes = [_u8p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, _u32p, _u64p]
+        L.oracle_pack_words_wide.argtypes = [_u8p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, _u32p, _u64p, _u64p]
+        L.oracle_run_wide.restype = C.c_void_p
+        L.oracle_run_wide.argtypes = [_u64p, _u64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int]
+        L.oracle_keys_hi.restype = C.c_void_p
+        L.oracle_keys_hi.argtypes = [C.c_void_p]
         L.oracle_nt_from_file.argtypes = [C.c_uint64, C.c_uint64, _u64p]
         L.oracle_pre_compute.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), _u64p]
         L.oracle_extract_umi.argtypes = [C.c_char_p, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
@@ -104,8 +110,9 @@ def extract_umi(header: str) -> str:
     return b[off.value: off.value + ln.value].decode()
 
 
-def pack_words(chars: np.ndarray, seg_take: Sequence[int], seg_len: Optional[np.ndarray] = None) -> np.ndarray:
-    """chars uint8[R, n] -> packed keys uint64[R] (INVALID where filtered)."""
+def pack_words(chars: np.ndarray, seg_take: Sequence[int], seg_len: Optional[np.ndarray] = None):
+    """chars uint8[R, n] -> packed keys uint64[R] (INVALID where filtered); for n > 31 a pair
+    (lo, hi) of uint64[R] (word = hi << 64 | lo, both INVALID where filtered)."""
     chars = np.ascontiguousarray(chars, dtype=np.uint8)
     R, n = chars.shape
     take = np.asarray(seg_take, dtype=np.uint32)
@@ -116,6 +123,10 @@ def pack_words(chars: np.ndarray, seg_take: Sequence[int], seg_len: Optional[np.
         seg_len = np.ascontiguousarray(seg_len, dtype=np.uint16)
         assert seg_len.shape == (R, take.size)
         sl = seg_len.ctypes.data_as(C.c_void_p)
+    if n > MAX_NARROW:
+        hi = np.zeros(R, dtype=np.uint64)
+        lib().oracle_pack_words_wide(chars, sl, R, n, take.size, take, out, hi)
+        return out, hi
     lib().oracle_pack_words(chars, sl, R, n, take.size, take, out)
     return out
 
@@ -124,16 +135,22 @@ def pack_words(chars: np.ndarray, seg_take: Sequence[int], seg_len: Optional[np.
 class Result:
     """Everything the reference computes between readData and writeStatistics."""
 
-    def __init__(self, keys: np.ndarray, n: int, d: int, edit: bool, maximum: bool, stop_after: int = 0):
-        keys = np.ascontiguousarray(keys, dtype=np.uint64)
+    def __init__(self, keys, n: int, d: int, edit: bool, maximum: bool, stop_after: int = 0):
+        """keys: uint64[R], or for words longer than 31 letters a (lo, hi) pair of uint64[R]."""
         L = lib()
-        h = L.oracle_run(keys, keys.size, n, d, int(edit), int(maximum), stop_after)
+        if isinstance(keys, tuple):
+            keys, keys_hi = (np.ascontiguousarray(k, dtype=np.uint64) for k in keys)
+            h = L.oracle_run_wide(keys, keys_hi, keys.size, n, d, int(edit), int(maximum), stop_after)
+        else:
+            keys = np.ascontiguousarray(keys, dtype=np.uint64)
+            h = L.oracle_run(keys, keys.size, n, d, int(edit), int(maximum), stop_after)
         try:
             self.total = L.oracle_total(h)
             self.usable = L.oracle_usable(h)
             self.unique = U = L.oracle_unique(h)
             self.clusters = Cn = L.oracle_clusters(h)
             self.keys = _view(L.oracle_keys(h), U, np.uint64)
+            self.keys_hi = _view(L.oracle_keys_hi(h), U, np.uint64)
             self.count = _view(L.oracle_count(h), U, np.uint64)
             self.first = _view(L.oracle_first(h), U, np.uint64)
             self.cluster_of = _view(L.oracle_cluster_of(h), U, np.uint32)

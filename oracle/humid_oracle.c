@@ -10,10 +10,11 @@
  *   (3) oracle/_ref/humid (the unmodified reference binary) on synthetic FastQ files,
  *       byte-for-byte on all output files; golden copies live in tests/golden/.
  *
- * Representation: a word of n nucleotides is one uint64_t, 2 bits per nucleotide
+ * Representation: a word of n nucleotides is one 128-bit integer (okey), 2 bits per nucleotide
  * (A=0,C=1,G=2,T=3, src/fastq.cc:12), first nucleotide in the most significant used bits,
  * so unsigned key order == trie pre-order walk order (lib/trie/src/trieFunctions.tcc:129-143).
- * n <= 31 here.  The pointer trie is restated as an *implicit trie over the sorted array
+ * n <= 63 here; the entry points take either one uint64_t per word (n <= 31, the external form
+ * of the one-key library path) or a (lo, hi) pair of uint64_t (n <= 63).  The pointer trie is restated as an *implicit trie over the sorted array
  * of distinct keys*: the node reached by a prefix of `depth` letters is the index range
  * [lo,hi) of keys carrying that prefix, child c is the sub-range whose next letter is c
  * (binary search).  With that substitution the recursions below are line-for-line
@@ -25,6 +26,9 @@
 #include <string.h>
 
 #define ORACLE_INVALID UINT64_MAX
+typedef unsigned __int128 okey;
+#define OKEY_INVALID (~(okey)0)
+#define ORACLE_MAX_N 63u
 
 typedef struct {
   uint32_t *v;
@@ -43,8 +47,9 @@ typedef struct oracle {
   uint32_t n, d;
   int edit, maximum;
   uint64_t R, usable, U, C;
-  uint64_t *keys;    /* [U] sorted distinct words (right-aligned, the external form) */
-  uint64_t *lk;      /* [U] same words left-aligned (internal trie form)             */
+  okey *keys;        /* [U] sorted distinct words (right-aligned, the external form) */
+  uint64_t *keys_lo, *keys_hi; /* [U] the same, split for the getters               */
+  okey *lk;          /* [U] same words left-aligned (internal trie form)             */
   uint8_t *len;      /* [U] word lengths (all n in the pipeline)                     */
   uint64_t *count;   /* [U] Leaf::count (lib/trie/src/node.tcc:14-16)               */
   uint64_t *first;   /* [U] first tuple index carrying the word (visited logic)     */
@@ -115,19 +120,18 @@ void oracle_extract_umi(const char *header, uint64_t len, uint64_t *off, uint64_
  * NULL = all full) holds min(actual length, take) per (tuple, segment).  Bytes beyond
  * seg_len are padding 'N' (makeStringSize_, :57-66) => the word is filtered, like any byte
  * outside ACGT (:151-158).  Filtered => ORACLE_INVALID. */
-void oracle_pack_words(const uint8_t *chars, const uint16_t *seg_len, uint64_t n_tuples,
-                       uint32_t n, uint32_t n_segs, const uint32_t *seg_take,
-                       uint64_t *keys_out) {
+static void pack_words128(const uint8_t *chars, const uint16_t *seg_len, uint64_t n_tuples,
+                          uint32_t n, uint32_t n_segs, const uint32_t *seg_take, okey *keys_out) {
   for (uint64_t t = 0; t < n_tuples; t++) {
     const uint8_t *c = chars + t * n;
-    uint64_t key = 0;
+    okey key = 0;
     int filtered = 0;
     uint32_t p = 0;
     for (uint32_t s = 0; s < n_segs; s++) {
       uint32_t have = seg_len ? seg_len[t * n_segs + s] : seg_take[s];
       for (uint32_t q = 0; q < seg_take[s]; q++, p++) {
         char ch = q < have ? (char)c[p] : 'N';
-        uint64_t code;
+        okey code;
         switch (ch) {
           case 'A': code = 0; break;
           case 'C': code = 1; break;
@@ -138,22 +142,39 @@ void oracle_pack_words(const uint8_t *chars, const uint16_t *seg_len, uint64_t n
         key = (key << 2) | code;
       }
     }
-    keys_out[t] = filtered ? ORACLE_INVALID : key;
+    keys_out[t] = filtered ? OKEY_INVALID : key;
   }
+}
+void oracle_pack_words(const uint8_t *chars, const uint16_t *seg_len, uint64_t n_tuples,
+                       uint32_t n, uint32_t n_segs, const uint32_t *seg_take,
+                       uint64_t *keys_out) { /* n <= 31 */
+  okey *k = (okey *)malloc((n_tuples ? n_tuples : 1) * sizeof(okey));
+  pack_words128(chars, seg_len, n_tuples, n, n_segs, seg_take, k);
+  for (uint64_t t = 0; t < n_tuples; t++) keys_out[t] = (uint64_t)k[t];
+  free(k);
+}
+/* n <= 63: lo = the last 32 letters, hi = the letters before them; filtered => both all-ones */
+void oracle_pack_words_wide(const uint8_t *chars, const uint16_t *seg_len, uint64_t n_tuples,
+                            uint32_t n, uint32_t n_segs, const uint32_t *seg_take,
+                            uint64_t *lo_out, uint64_t *hi_out) {
+  okey *k = (okey *)malloc((n_tuples ? n_tuples : 1) * sizeof(okey));
+  pack_words128(chars, seg_len, n_tuples, n, n_segs, seg_take, k);
+  for (uint64_t t = 0; t < n_tuples; t++) { lo_out[t] = (uint64_t)k[t]; hi_out[t] = (uint64_t)(k[t] >> 64); }
+  free(k);
 }
 
 /* ------------------------------------------------------------------------------------
  * Implicit trie over the sorted distinct keys
  *
- * Internally words are LEFT-aligned (letter p at bits 61-2p..60-2p, p <= 30) with an
+ * Internally words are LEFT-aligned (letter p at bits 125-2p..124-2p, p <= 62) with an
  * explicit length, sorted by (left-aligned key, length), i.e. lexicographically with a
  * word before its extensions == walk_ order (lib/trie/src/trieFunctions.tcc:129-143).
  * HUMID only ever stores words of one length n; variable lengths are supported so that the
  * mixed-length golden vectors of lib/trie/tests/test_trie.cc:129-191 can pin the recursion.
  * ---------------------------------------------------------------------------------- */
 
-static inline uint32_t letter_at(uint64_t lkey, uint32_t p) {
-  return (uint32_t)(lkey >> (2 * (30 - p))) & 3u;
+static inline uint32_t letter_at(okey lkey, uint32_t p) {
+  return (uint32_t)(lkey >> (2 * (ORACLE_MAX_N - 1 - p))) & 3u;
 }
 
 /* node->leaf: the (single) word of the range whose length equals the node depth. */
@@ -178,7 +199,7 @@ static int child_of(const oracle *o, uint64_t lo, uint64_t hi, uint32_t depth, u
                     uint64_t *clo, uint64_t *chi) {
   uint64_t leaf;
   if (leaf_of(o, lo, hi, depth, &leaf)) lo++; /* the node's own leaf is not below a child */
-  if (lo >= hi || depth > 30) return 0;
+  if (lo >= hi || depth > ORACLE_MAX_N - 1) return 0;
   *clo = lower_letter(o, lo, hi, depth, c);
   *chi = lower_letter(o, *clo, hi, depth, c + 1);
   return *clo < *chi;
@@ -189,7 +210,7 @@ typedef void (*yield_fn)(oracle *o, void *ctx, uint64_t leaf);
 /* hamming_<4,T,full>, lib/trie/src/trieFunctions.tcc:156-181.  (The reference yields a
  * Result with a null leaf when the path ends on an inner node; with HUMID's fixed-length
  * words that never happens and such results are skipped here.) */
-static void hamming_rec(oracle *o, uint64_t lo, uint64_t hi, uint64_t word, uint32_t wlen,
+static void hamming_rec(oracle *o, uint64_t lo, uint64_t hi, okey word, uint32_t wlen,
                         uint32_t position, int distance, int full, yield_fn yield, void *ctx) {
   if (distance >= 0) {
     if (position < wlen) {
@@ -209,7 +230,7 @@ static void hamming_rec(oracle *o, uint64_t lo, uint64_t hi, uint64_t word, uint
 
 /* levenshtein_<4,T,full>, lib/trie/src/trieFunctions.tcc:196-233.  `depth` is the depth of
  * `node` in the trie (implicit in the reference's node pointer). */
-static void levenshtein_rec(oracle *o, uint64_t lo, uint64_t hi, uint32_t depth, uint64_t word,
+static void levenshtein_rec(oracle *o, uint64_t lo, uint64_t hi, uint32_t depth, okey word,
                             uint32_t wlen, uint32_t position, int distance, int full,
                             yield_fn yield, void *ctx) {
   if (distance >= 0) {
@@ -332,7 +353,12 @@ static int cmp_u64(const void *a, const void *b) {
   return x < y ? -1 : x > y;
 }
 
-static uint64_t rank_of(const oracle *o, uint64_t key) { /* Trie::find, :109-119 */
+static int cmp_okey(const void *a, const void *b) {
+  okey x = *(const okey *)a, y = *(const okey *)b;
+  return x < y ? -1 : x > y;
+}
+
+static uint64_t rank_of(const oracle *o, okey key) { /* Trie::find, :109-119 */
   uint64_t lo = 0, hi = o->U;
   while (lo < hi) {
     uint64_t mid = lo + (hi - lo) / 2;
@@ -344,7 +370,7 @@ static uint64_t rank_of(const oracle *o, uint64_t key) { /* Trie::find, :109-119
 void oracle_free(oracle *o) {
   if (!o) return;
   if (o->nbr) for (uint64_t i = 0; i < o->U; i++) free(o->nbr[i].v);
-  free(o->nbr); free(o->keys); free(o->lk); free(o->len); free(o->count); free(o->first); free(o->cluster);
+  free(o->nbr); free(o->keys); free(o->keys_lo); free(o->keys_hi); free(o->lk); free(o->len); free(o->count); free(o->first); free(o->cluster);
   free(o->csize); free(o->cmax); free(o->cmaxcount); free(o->keep); free(o->cid);
   free(o);
 }
@@ -352,17 +378,17 @@ void oracle_free(oracle *o) {
 /* keys[t] = packed word of input tuple t, or ORACLE_INVALID when filtered.
  * stop_after: 0 = everything, 1 = stop after the word table (readData),
  *             2 = stop after neighbours. */
-oracle *oracle_run(const uint64_t *keys, uint64_t R, uint32_t n, uint32_t d, int edit,
-                   int maximum, int stop_after) {
+static oracle *oracle_run128(const okey *keys, uint64_t R, uint32_t n, uint32_t d, int edit,
+                             int maximum, int stop_after) {
   oracle *o = (oracle *)calloc(1, sizeof(oracle));
   o->n = n; o->d = d; o->edit = edit; o->maximum = maximum; o->R = R;
 
   /* readData, src/humid.cc:92-99: total++, usable++ and trie.add for unfiltered tuples */
-  uint64_t *tmp = (uint64_t *)malloc((R ? R : 1) * sizeof(uint64_t));
+  okey *tmp = (okey *)malloc((R ? R : 1) * sizeof(okey));
   for (uint64_t t = 0; t < R; t++)
-    if (keys[t] != ORACLE_INVALID) tmp[o->usable++] = keys[t];
-  qsort(tmp, o->usable, sizeof(uint64_t), cmp_u64);
-  o->keys = (uint64_t *)malloc((o->usable ? o->usable : 1) * sizeof(uint64_t));
+    if (keys[t] != OKEY_INVALID) tmp[o->usable++] = keys[t];
+  qsort(tmp, o->usable, sizeof(okey), cmp_okey);
+  o->keys = (okey *)malloc((o->usable ? o->usable : 1) * sizeof(okey));
   o->count = (uint64_t *)calloc(o->usable ? o->usable : 1, sizeof(uint64_t));
   for (uint64_t i = 0; i < o->usable; i++) {
     if (o->U == 0 || o->keys[o->U - 1] != tmp[i]) o->keys[o->U++] = tmp[i];
@@ -373,13 +399,20 @@ oracle *oracle_run(const uint64_t *keys, uint64_t R, uint32_t n, uint32_t d, int
   o->first = (uint64_t *)malloc((U ? U : 1) * sizeof(uint64_t));
   for (uint64_t i = 0; i < U; i++) o->first[i] = UINT64_MAX;
   for (uint64_t t = 0; t < R; t++)
-    if (keys[t] != ORACLE_INVALID) {
+    if (keys[t] != OKEY_INVALID) {
       uint64_t r = rank_of(o, keys[t]);
       if (o->first[r] == UINT64_MAX) o->first[r] = t;
     }
-  o->lk = (uint64_t *)malloc((U ? U : 1) * sizeof(uint64_t));
+  o->lk = (okey *)malloc((U ? U : 1) * sizeof(okey));
   o->len = (uint8_t *)malloc(U ? U : 1);
-  for (uint64_t i = 0; i < U; i++) { o->lk[i] = o->keys[i] << (2 * (31 - n)); o->len[i] = (uint8_t)n; }
+  o->keys_lo = (uint64_t *)malloc((U ? U : 1) * sizeof(uint64_t));
+  o->keys_hi = (uint64_t *)malloc((U ? U : 1) * sizeof(uint64_t));
+  for (uint64_t i = 0; i < U; i++) {
+    o->lk[i] = o->keys[i] << (2 * (ORACLE_MAX_N - n));
+    o->len[i] = (uint8_t)n;
+    o->keys_lo[i] = (uint64_t)o->keys[i];
+    o->keys_hi[i] = (uint64_t)(o->keys[i] >> 64);
+  }
   o->nbr = (vec32 *)calloc(U ? U : 1, sizeof(vec32));
   o->cluster = (uint32_t *)calloc(U ? U : 1, sizeof(uint32_t));
   o->keep = (uint8_t *)calloc(R ? R : 1, 1);
@@ -414,7 +447,7 @@ oracle *oracle_run(const uint64_t *keys, uint64_t R, uint32_t n, uint32_t d, int
   /* writeFiltered :220-234 (visited / maxLeaf test) and writeAnnotated :268-285 */
   uint8_t *visited = (uint8_t *)calloc(o->C ? o->C : 1, 1);
   for (uint64_t t = 0; t < R; t++) {
-    if (keys[t] == ORACLE_INVALID) continue; /* cid stays 0 */
+    if (keys[t] == OKEY_INVALID) continue; /* cid stays 0 */
     uint64_t r = rank_of(o, keys[t]);
     uint32_t cl = o->cluster[r];
     o->cid[t] = cl;
@@ -427,12 +460,31 @@ oracle *oracle_run(const uint64_t *keys, uint64_t R, uint32_t n, uint32_t d, int
   return o;
 }
 
+oracle *oracle_run(const uint64_t *keys, uint64_t R, uint32_t n, uint32_t d, int edit,
+                   int maximum, int stop_after) { /* n <= 31, one uint64_t per word */
+  okey *k = (okey *)malloc((R ? R : 1) * sizeof(okey));
+  for (uint64_t t = 0; t < R; t++) k[t] = keys[t] == ORACLE_INVALID ? OKEY_INVALID : (okey)keys[t];
+  oracle *o = oracle_run128(k, R, n, d, edit, maximum, stop_after);
+  free(k);
+  return o;
+}
+/* n <= 63: word = hi << 64 | lo; hi == UINT64_MAX marks a filtered tuple */
+oracle *oracle_run_wide(const uint64_t *lo, const uint64_t *hi, uint64_t R, uint32_t n, uint32_t d,
+                        int edit, int maximum, int stop_after) {
+  okey *k = (okey *)malloc((R ? R : 1) * sizeof(okey));
+  for (uint64_t t = 0; t < R; t++) k[t] = hi[t] == ORACLE_INVALID ? OKEY_INVALID : ((okey)hi[t] << 64) | lo[t];
+  oracle *o = oracle_run128(k, R, n, d, edit, maximum, stop_after);
+  free(k);
+  return o;
+}
+
 /* ---- getters (ctypes) ---- */
 uint64_t oracle_total(const oracle *o) { return o->R; }
 uint64_t oracle_usable(const oracle *o) { return o->usable; }
 uint64_t oracle_unique(const oracle *o) { return o->U; }
 uint64_t oracle_clusters(const oracle *o) { return o->C; }
-const uint64_t *oracle_keys(const oracle *o) { return o->keys; }
+const uint64_t *oracle_keys(const oracle *o) { return o->keys_lo; }
+const uint64_t *oracle_keys_hi(const oracle *o) { return o->keys_hi; }
 const uint64_t *oracle_count(const oracle *o) { return o->count; }
 const uint64_t *oracle_first(const oracle *o) { return o->first; }
 const uint32_t *oracle_cluster_of(const oracle *o) { return o->cluster; }
@@ -493,15 +545,15 @@ static void q_yield(oracle *o, void *ctx, uint64_t leaf) {
   if (q->n < q->cap) q->out[q->n] = q->orig[leaf];
   q->n++;
 }
-typedef struct { uint64_t lk; uint8_t len; uint64_t orig; } qword;
+typedef struct { okey lk; uint8_t len; uint64_t orig; } qword;
 static int cmp_qword(const void *a, const void *b) {
   const qword *x = (const qword *)a, *y = (const qword *)b;
   if (x->lk != y->lk) return x->lk < y->lk ? -1 : 1;
   return (int)x->len - (int)y->len;
 }
-static uint64_t left_pack(const uint8_t *letters, uint32_t len) {
-  uint64_t k = 0;
-  for (uint32_t p = 0; p < len; p++) k |= (uint64_t)(letters[p] & 3) << (2 * (30 - p));
+static okey left_pack(const uint8_t *letters, uint32_t len) {
+  okey k = 0;
+  for (uint32_t p = 0; p < len; p++) k |= (okey)(letters[p] & 3) << (2 * (ORACLE_MAX_N - 1 - p));
   return k;
 }
 uint64_t oracle_trie_query(const uint8_t *letters, const uint32_t *lens, uint64_t n_words,
@@ -519,12 +571,12 @@ uint64_t oracle_trie_query(const uint8_t *letters, const uint32_t *lens, uint64_
   oracle o;
   memset(&o, 0, sizeof o);
   o.U = n_words;
-  o.lk = (uint64_t *)malloc((n_words ? n_words : 1) * sizeof(uint64_t));
+  o.lk = (okey *)malloc((n_words ? n_words : 1) * sizeof(okey));
   o.len = (uint8_t *)malloc(n_words ? n_words : 1);
   uint64_t *orig = (uint64_t *)malloc((n_words ? n_words : 1) * sizeof(uint64_t));
   for (uint64_t i = 0; i < n_words; i++) { o.lk[i] = w[i].lk; o.len[i] = w[i].len; orig[i] = w[i].orig; }
   qctx q = {out, 0, cap, orig};
-  uint64_t qk = left_pack(query, qlen);
+  okey qk = left_pack(query, qlen);
   if (kind < 2) hamming_rec(&o, 0, n_words, qk, qlen, 0, distance, kind == 0, q_yield, &q);
   else levenshtein_rec(&o, 0, n_words, 0, qk, qlen, 0, distance, kind == 2, q_yield, &q);
   free(o.lk); free(o.len); free(orig); free(w);

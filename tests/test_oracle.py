@@ -211,3 +211,45 @@ def test_reference_query_vectors():
     words = ["ACG", "ACT", "AGG", "AGT", "CCG"]
     _, _, q = oracle.run_ref_probe(words, [1] * 5, False, 1, True, [("h", 1, "ACT"), ("H", 1, "ACT")])
     assert q == [["ACG", "ACT", "AGT"], ["ACT", "AGT"]]
+
+
+def _wide_keys(words):
+    ks = [oracle.word_to_key(w) for w in words]
+    lo = np.array([k & 0xFFFFFFFFFFFFFFFF for k in ks], dtype=np.uint64)
+    hi = np.array([k >> 64 for k in ks], dtype=np.uint64)
+    return lo, hi
+
+
+@ref
+@pytest.mark.parametrize("edit,d", [(False, 1), (False, 2), (True, 1), (True, 2)])
+@pytest.mark.parametrize("maximum", [True, False])
+def test_wide_words_against_reference_trie(edit, d, maximum):
+    """Words of 32..63 letters (two 64-bit halves, `-n 36` of docs/usage.rst:18-20 and beyond)."""
+    rng = np.random.default_rng(7000 + 100 * d + 10 * edit + maximum)
+    for n, m, alpha in [(32, 300, 4), (36, 500, 4), (40, 400, 2), (63, 300, 4)]:
+        if edit and d == 2 and n > 40:
+            continue  # the reference's recursion takes minutes there
+        words = _random_words(rng, n, m, alpha)
+        leaves, clusters, _ = oracle.run_ref_probe(words, [1] * len(words), edit, d, maximum)
+        r = oracle.Result(_wide_keys(words), n, d, edit, maximum)
+        assert r.unique == len(leaves)
+        for lf in leaves:
+            i = lf["rank"]
+            assert oracle.key_to_word((int(r.keys_hi[i]) << 64) | int(r.keys[i]), n) == lf["word"]
+            assert int(r.count[i]) == lf["count"]
+            assert list(r.neighbours(i)) == lf["neighbours"], (n, i)
+            assert int(r.cluster_of[i]) == lf["cluster"]
+        assert r.clusters == len(clusters)
+        for c in clusters:
+            assert int(r.cluster_size[c["id"] - 1]) == c["size"]
+            assert int(r.cluster_max[c["id"] - 1]) == c["max_leaf"]
+
+
+def test_wide_pack_words():
+    """makeWord on 36 letters: halves split 4 | 32, filtered tuples are all-ones in both halves."""
+    w = "ACGT" * 9
+    chars = np.frombuffer((w + w[:35] + "N").encode(), dtype=np.uint8).reshape(2, 36)
+    lo, hi = oracle.pack_words(chars, [12, 12, 12])
+    k = oracle.word_to_key(w)
+    assert int(lo[0]) == k & 0xFFFFFFFFFFFFFFFF and int(hi[0]) == k >> 64
+    assert lo[1] == oracle.INVALID and hi[1] == oracle.INVALID
