@@ -115,12 +115,12 @@ class ClockSampler:
 # ----------------------------------------------------------------------------------------
 # CPU arm: the reference binary on a bounded sample
 # ----------------------------------------------------------------------------------------
-def cpu_reference_run(steps: int, warmup: int, sample: int):
+def cpu_reference_run(steps: int, warmup: int, sample: int, word_length: int = 0):
     """Returns (pairs/s, ms per step, kind, cores, sample description)."""
     import oracle
     from humid_b200.synth import HashSynth, baseline_config
 
-    cfg = baseline_config(1, sample)
+    cfg = baseline_config(1, sample, **({"word_length": word_length} if word_length else {}))
     syn = HashSynth(cfg)
     if os.access(oracle.REF_HUMID, os.X_OK):
         tmp = tempfile.mkdtemp(prefix="humid_ref_")
@@ -137,7 +137,7 @@ def cpu_reference_run(steps: int, warmup: int, sample: int):
             shutil.rmtree(tmp, ignore_errors=True)
         kind = "reference"
         what = (f"{sample} read tuples of the same library model (3 FastQ files, 2x150 nt + 12 nt UMI), whole "
-                f"`humid -n 24 -m 1 -s` process wall time incl. FastQ parsing and writing the dedup files")
+                f"`humid -n {cfg.word_length} -m 1 -s` process wall time incl. FastQ parsing and writing the dedup files")
     else:
         import numpy as np
 
@@ -161,7 +161,7 @@ def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    val, ms, kind, cores, what = cpu_reference_run(args.steps, args.warmup, REF_SAMPLE_TUPLES)
+    val, ms, kind, cores, what = cpu_reference_run(args.steps, args.warmup, REF_SAMPLE_TUPLES, args.word_length)
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -222,7 +222,7 @@ def run_gpu_arm(args):
 
     R_per = args.tuples
     R_all = R_per * world
-    cfg = baseline_config(args.config, R_all)
+    cfg = baseline_config(args.config, R_all, **({"word_length": args.word_length} if args.word_length else {}))
     syn = HashSynth(cfg)
     hdr, take = syn.layout()
     seg_take = ([hdr] if hdr else []) + take
@@ -354,14 +354,14 @@ def run_gpu_arm(args):
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        v, ms, kind, cores, what = cpu_reference_run(1, 0, REF_SAMPLE_TUPLES)
+        v, ms, kind, cores, what = cpu_reference_run(1, 0, REF_SAMPLE_TUPLES, args.word_length)
         cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": what, "host_cores": os.cpu_count()}
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": t_dev * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u64", "data": "synthetic",
-        "config": {"workload": WORKLOAD if args.config == 1 else cfg.name, "tuples_per_gpu": R_per, "tuples_total": R_all, "word_length": cfg.word_length,
+        "config": {"workload": WORKLOAD if args.config == 1 and not args.word_length else cfg.name, "tuples_per_gpu": R_per, "tuples_total": R_all, "word_length": cfg.word_length,
                    "distance": cfg.distance, "clustering": "maximum" if cfg.maximum else "directional",
                    "l2": "inputs larger than L2 (word characters %.2f GB per GPU)" % (R_per * cfg.word_length / 1e9),
                    "parallelism": "1 GPU" if world == 1 else f"word space range-partitioned over {world} GPUs; NCCL all-to-all-v (tuples, variant queries), all-gather (components that cross shards)",
@@ -387,6 +387,7 @@ def main():
     ap.add_argument("--tuples", type=int, default=50_000_000, help="read tuples per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--config", type=int, default=1, help="BASELINE.json configs[i] (0-based); the bench line is configs[1]")
+    ap.add_argument("--word-length", type=int, default=0, help="override -n (e.g. 36: all 12 UMI letters of configs[1])")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":

@@ -17,7 +17,8 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libhumid_gpu.so")
 MAX_SEGMENTS = 16
-MAX_WORD_LENGTH = 31
+MAX_WORD_LENGTH = 63
+MAX_NARROW_WORD_LENGTH = 31  # longer words: two 64-bit keys, Hamming / edit distance 1, one GPU
 HIST = {"counts": 0, "neigh": 1, "clusters": 2}
 
 EXPORTS = [
@@ -26,6 +27,7 @@ EXPORTS = [
     "humid_gpu_histogram", "humid_gpu_keep_mask", "humid_gpu_cluster_ids", "humid_gpu_debug_words",
     "humid_gpu_debug_neighbours", "humid_gpu_debug_clusters", "humid_gpu_stage_stats", "humid_gpu_stream",
     "humid_gpu_debug_sort_pairs", "humid_gpu_debug_partition", "humid_gpu_host_alloc", "humid_gpu_host_free",
+    "humid_gpu_debug_words_hi",
 ]
 
 
@@ -75,6 +77,7 @@ def load_library() -> C.CDLL:
     L.humid_gpu_keep_mask.argtypes = [vp, u64, u64, vp]
     L.humid_gpu_cluster_ids.argtypes = [vp, u64, u64, vp]
     L.humid_gpu_debug_words.argtypes = [vp, u64, vp, vp, vp, vp]
+    L.humid_gpu_debug_words_hi.argtypes = [vp, u64, vp]
     L.humid_gpu_debug_neighbours.argtypes = [vp, vp, vp, P(u64)]
     L.humid_gpu_debug_clusters.argtypes = [vp, u64, vp, vp]
     L.humid_gpu_stage_stats.argtypes = [vp, P(StageStat), P(u32)]
@@ -250,6 +253,13 @@ class Dedup:
         self._check(self._L.humid_gpu_debug_words(self._h, max(U, 1), _ptr(keys), _ptr(cnt), _ptr(first), _ptr(cid)),
                     "debug_words")
         return keys[:U], cnt[:U], first[:U], cid[:U]
+
+    def words_hi(self) -> np.ndarray:
+        """Bits 64.. of every word in rank order (all zero up to 31 letters; `words()` has the low 64)."""
+        U = self.counts()["unique"]
+        hi = np.zeros(max(U, 1), dtype=np.uint64)
+        self._check(self._L.humid_gpu_debug_words_hi(self._h, max(U, 1), _ptr(hi)), "debug_words_hi")
+        return hi[:U]
 
     def neighbours(self) -> Tuple[np.ndarray, np.ndarray]:
         U = self.counts()["unique"]

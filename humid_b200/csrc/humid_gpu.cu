@@ -42,7 +42,10 @@ int humid_gpu_create(const humid_gpu_config *cfg, humid_gpu **out) {
   *out = nullptr;
   if (cfg->word_length == 0 || cfg->word_length > HUMID_MAX_WORD_LENGTH)
     return fail(nullptr, HUMID_GPU_ERR_UNSUPPORTED,
-                "word length must be 1.." + std::to_string(HUMID_MAX_WORD_LENGTH) + " (one 64-bit key per word)");
+                "word length must be 1.." + std::to_string(HUMID_MAX_WORD_LENGTH) + " (at most two 64-bit keys per word)");
+  if (cfg->word_length > HUMID_MAX_NARROW_WORD_LENGTH && cfg->edit && cfg->distance >= 2)
+    return fail(nullptr, HUMID_GPU_ERR_UNSUPPORTED,
+                "edit distance >= 2 needs a word length of at most " + std::to_string(HUMID_MAX_NARROW_WORD_LENGTH));
   if (cfg->n_segments == 0 || cfg->n_segments > HUMID_MAX_SEGMENTS)
     return fail(nullptr, HUMID_GPU_ERR_ARG, "n_segments out of range");
   uint64_t sum = 0;
@@ -67,6 +70,7 @@ int humid_gpu_create(const humid_gpu_config *cfg, humid_gpu **out) {
     s.counters.ensure(64);
     HUMID_CUDA(cudaMemsetAsync(s.counters.p, 0, 64 * sizeof(unsigned long long), s.stream));
     if (cfg->expected_tuples) s.tuple_key.ensure(cfg->expected_tuples);
+    if (cfg->expected_tuples && s.wide()) s.tuple_hi.ensure(cfg->expected_tuples);
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
   });
   if (rc != HUMID_GPU_OK) {
@@ -92,6 +96,8 @@ void humid_gpu_destroy(humid_gpu *h) {
     if (s.ev_consumed[b]) cudaEventDestroy(s.ev_consumed[b]);
   }
   if (s.copy_stream) cudaStreamDestroy(s.copy_stream);
+  s.tuple_hi.release(); s.word_hi.release(); s.wide_k0.release(); s.wide_k1.release(); s.wide_k2.release();
+  s.tuple_rank.release(); s.wide_v0.release(); s.wide_v1.release();
   s.tuple_key.release(); s.counters.release(); s.part_key.release(); s.part_index.release(); s.word_flags.release(); s.join_entries.release(); s.join_entries_out.release();
   s.slots.release(); s.word_key.release(); s.key_alt.release(); s.word_slot.release(); s.slot_alt.release();
   s.word_count.release(); s.word_first.release(); s.entries.release(); s.entries_alt.release();
@@ -170,6 +176,7 @@ static int add_batch_impl(humid_gpu *h, const uint8_t *chars, const uint16_t *se
     HUMID_CUDA(cudaSetDevice(s.device));
     const uint32_t wl = s.cfg.word_length, ns = s.cfg.n_segments;
     s.tuple_key.grow(s.n_tuples + n, s.n_tuples, s.stream);
+    if (s.wide()) s.tuple_hi.grow(s.n_tuples + n, s.n_tuples, s.stream);
     const uint8_t *d_chars = chars;
     const uint16_t *d_len = seg_len;
     const int b = (int)(s.n_batches & 1);
@@ -223,10 +230,14 @@ int humid_gpu_finalize(humid_gpu *h) {
     HUMID_CUDA(cudaSetDevice(s.device));
     const bool edit2 = s.cfg.edit && s.cfg.distance >= 2;
     if (s.shard_mode) throw CudaError{"finalize on a handle that is in shard mode"};
-    stage_build_table(s, false);  // key -> rank look-ups are set up by the stages that need them
+    if (s.wide()) stage_build_words_wide(s);
+    else stage_build_table(s, false);  // key -> rank look-ups are set up by the stages that need them
     s.report_tuples = s.n_tuples;
     s.report_usable = s.usable;
-    if (edit2) {
+    if (s.wide()) {
+      stage_neighbours_hamming_wide(s);
+      stage_csr_pairs(s);
+    } else if (edit2) {
       stage_neighbours_edit(s);
       stage_csr(s);
     } else {
@@ -301,7 +312,8 @@ int humid_gpu_cluster_ids(humid_gpu *h, uint64_t first_tuple, uint64_t n, uint32
     HUMID_CUDA(cudaSetDevice(s.device));
     s.out_ids.ensure(n);
     // K5: key (8) + slot (16) + label (4) + seed index (4) + id out (4)
-    stage_cluster_ids(s, first_tuple, n, s.out_ids.p);
+    if (s.wide()) stage_cluster_ids_wide(s, first_tuple, n, s.out_ids.p);
+    else stage_cluster_ids(s, first_tuple, n, s.out_ids.p);
     HUMID_CUDA(cudaMemcpyAsync(ids, s.out_ids.p, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     resolve_stats(s);
@@ -334,6 +346,24 @@ int humid_gpu_debug_words(humid_gpu *h, uint64_t cap, uint64_t *keys, uint32_t *
       word_cluster_ids_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.label.p, s.seed_index.p, U, s.out_ids.p);
       HUMID_CUDA(cudaMemcpyAsync(cluster_ids, s.out_ids.p, U * 4, cudaMemcpyDeviceToHost, s.stream));
     }
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+  });
+}
+
+int humid_gpu_debug_words_hi(humid_gpu *h, uint64_t cap, uint64_t *keys_hi) {
+  if (!h || !keys_hi) return HUMID_GPU_ERR_ARG;
+  State &s = h->s;
+  if (!s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "not finalized");
+  if (cap < s.unique) return fail(h, HUMID_GPU_ERR_ARG, "buffers too small");
+  const uint64_t U = s.unique;
+  if (U == 0) return HUMID_GPU_OK;
+  if (!s.wide()) {
+    std::memset(keys_hi, 0, U * sizeof(uint64_t));
+    return HUMID_GPU_OK;
+  }
+  return guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(s.device));
+    HUMID_CUDA(cudaMemcpyAsync(keys_hi, s.word_hi.p, U * 8, cudaMemcpyDeviceToHost, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
   });
 }

@@ -337,6 +337,67 @@ __global__ void __launch_bounds__(128)
   }
 }
 
+// ---- words of 32..63 letters: the same join on (hi, lo) key halves ---------------------------
+// Same group walk as hamming_join_walk_kernel, every group walked whatever its size (blocks are at
+// least 16 letters long here, so groups are tiny unless the data is degenerate); pairs + degrees out.
+template <bool DOMINANCE>
+__device__ __forceinline__ bool linked_wide(uint64_t a_hi, uint64_t a_lo, uint64_t b_hi, uint64_t b_lo, uint32_t d) {
+  const uint64_t xh = a_hi ^ b_hi, xl = a_lo ^ b_lo;
+  const uint64_t dh = (xh | (xh >> 1)) & LETTER_LOW, dl = (xl | (xl >> 1)) & LETTER_LOW;
+  if ((uint32_t)(__popcll(dh) + __popcll(dl)) > d) return false;
+  if (!DOMINANCE || d == 1) return true;
+  const uint64_t ahh = (a_hi >> 1) & LETTER_LOW, bhh = (b_hi >> 1) & LETTER_LOW, ahl = a_hi & LETTER_LOW,
+                 bhl = b_hi & LETTER_LOW;
+  const uint64_t alh = (a_lo >> 1) & LETTER_LOW, blh = (b_lo >> 1) & LETTER_LOW, all_ = a_lo & LETTER_LOW,
+                 bll = b_lo & LETTER_LOW;
+  const uint64_t gh = (ahh & ~bhh) | (~(ahh ^ bhh) & ahl & ~bhl);
+  const uint64_t gl = (alh & ~blh) | (~(alh ^ blh) & all_ & ~bll);
+  return ((gh & dh) | (gl & dl)) == 0;
+}
+
+__device__ __forceinline__ bool shares_earlier_block_wide(const WideBlocks &B, uint32_t block, uint64_t xh, uint64_t xl) {
+  bool shared = false;
+#pragma unroll
+  for (int b = 0; b < HAM_MAX_D; b++) {
+    if ((uint32_t)b >= block) break;
+    shared |= ((xh & B.mask_hi[b]) | (xl & B.mask_lo[b])) == 0;
+  }
+  return shared;
+}
+
+__global__ void __launch_bounds__(JOIN_THREADS)
+    hamming_join_wide_kernel(const uint64_t *__restrict__ keys_hi, const uint64_t *__restrict__ keys_lo,
+                             const uint32_t *__restrict__ rank, uint64_t U, uint32_t d, const WideBlocks B, uint32_t block,
+                             uint64_t *__restrict__ pairs, uint64_t cap, unsigned long long *__restrict__ counter,
+                             uint32_t *__restrict__ deg) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = i < U;
+  const uint64_t mh = B.mask_hi[block], ml = B.mask_lo[block];
+  const uint64_t wh = live ? keys_hi[i] : 0ull, wl = live ? keys_lo[i] : 0ull;
+  const uint64_t gh = wh & mh, gl = wl & ml;
+  HitBuf hb;
+  uint32_t ri = 0;
+  if (live) {
+    bool have_rank = false;
+    for (uint64_t j = i + 1; j < U; j++) {
+      const uint64_t vh = keys_hi[j], vl = keys_lo[j];
+      if ((vh & mh) != gh || (vl & ml) != gl) break;
+      if (!linked_wide<true>(wh, wl, vh, vl, d)) continue;
+      if (shares_earlier_block_wide(B, block, vh ^ wh, vl ^ wl)) continue;  // found in an earlier block's order
+      if (!have_rank) { ri = rank ? rank[i] : (uint32_t)i; have_rank = true; }
+      hit_push<JOIN_PAIRS_DEG>(hb, (uint32_t)(j - i), i, ri, rank, pairs, cap, counter, deg, 0u);
+    }
+  }
+  hits_flush_cta<JOIN_PAIRS_DEG>(hb, i, ri, rank, pairs, cap, counter, deg, 0u);
+}
+
+void launch_hamming_join_wide(State &s, const uint64_t *keys_hi, const uint64_t *keys_lo, const uint32_t *rank,
+                              uint64_t n_words, const WideBlocks &B, uint32_t block, uint64_t *out, uint64_t cap,
+                              unsigned long long *counter, uint32_t *deg) {
+  hamming_join_wide_kernel<<<grid_for(n_words, JOIN_THREADS), JOIN_THREADS, 0, s.stream>>>(
+      keys_hi, keys_lo, rank, n_words, s.cfg.distance, B, block, out, cap, counter, deg);
+}
+
 void launch_hamming_join(State &s, int emit, const uint64_t *keys, const uint32_t *rank, uint64_t n_words, const Blocks &B,
                          uint32_t block, uint32_t group_cap, uint64_t *out, uint64_t cap, unsigned long long *counter,
                          uint32_t *deg, uint32_t col_base, uint32_t *flags, unsigned long long *n_flagged) {

@@ -250,6 +250,7 @@ int humid_gpu_shard_begin(humid_gpu *h, uint64_t tuple_offset, uint64_t *n_usabl
   if (s.cfg.edit && s.cfg.distance >= 2)
     return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "edit distance >= 2 is not sharded (use one GPU)");
   if (s.cfg.distance > (uint32_t)HAM_MAX_D) return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "distance > 8");
+  if (s.wide()) return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "words of more than 31 letters are not sharded (use one GPU)");
   if (tuple_offset + s.n_tuples >= 0xFFFFFFFFull) return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "more than 2^32-2 tuples");
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));

@@ -66,6 +66,11 @@ struct State {
   // pass 1
   uint64_t n_tuples = 0;
   DevBuf<uint64_t> tuple_key;
+  // words of 32..63 letters (wide.cu): key = hi << 64 | lo, lo in tuple_key / word_key, hi here;
+  // the word of a tuple is remembered by rank (there is no table to ask)
+  bool wide() const { return cfg.word_length > HUMID_MAX_NARROW_WORD_LENGTH; }
+  DevBuf<uint64_t> tuple_hi, word_hi, wide_k0, wide_k1, wide_k2;
+  DevBuf<uint32_t> tuple_rank, wide_v0, wide_v1;
   // H2D staging for add_batch: two buffers, uploads on their own stream so that batch i+1
   // travels while batch i is packed and counted
   DevBuf<uint8_t> stage_chars[2];
@@ -197,6 +202,18 @@ void launch_hamming_join(State &s, int emit, const uint64_t *keys, const uint32_
                          uint32_t block, uint32_t group_cap, uint64_t *out, uint64_t cap, unsigned long long *counter,
                          uint32_t *deg, uint32_t col_base, uint32_t *flags, unsigned long long *n_flagged);
 int stage_neighbours_hamming(State &s);
+// words of 32..63 letters: bits of block b in the two key halves (block 0 = first letters)
+struct WideBlocks {
+  uint32_t n_blocks;
+  uint64_t mask_hi[HAM_MAX_D + 1], mask_lo[HAM_MAX_D + 1];
+};
+void launch_hamming_join_wide(State &s, const uint64_t *keys_hi, const uint64_t *keys_lo, const uint32_t *rank,
+                              uint64_t n_words, const WideBlocks &B, uint32_t block, uint64_t *out, uint64_t cap,
+                              unsigned long long *counter, uint32_t *deg);
+// wide.cu — the same stages for words of 32..63 letters
+int stage_build_words_wide(State &s);        // distinct words, counts, first tuples, tuple -> rank (by sorting)
+int stage_neighbours_hamming_wide(State &s);
+int stage_cluster_ids_wide(State &s, uint64_t first, uint64_t n, uint32_t *d_out);
 int stage_neighbours_edit(State &s);
 int stage_csr(State &s);               // sort directed entries, row_ptr / col (edit and shard modes)
 int stage_csr_pairs(State &s);         // Hamming mode: undirected pairs + degrees -> row_ptr / col

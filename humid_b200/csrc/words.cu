@@ -15,6 +15,7 @@ struct PackParams {
 
 constexpr int PACK_THREADS = 256;
 constexpr int PACK_ROWS = 1024;  // tuples per CTA: 4 x 16-byte loads in flight per thread while staging
+constexpr int PACK_ROWS_WIDE = 512;  // words of 32..63 letters: the tile still fits 48 KB of shared memory
 
 // Four characters at a time (SIMD inside a 32-bit register).  A=0 C=1 G=2 T=3
 // (src/fastq.cc:12) falls out of bits 1-2 of the ASCII code; a character is valid iff the
@@ -34,12 +35,15 @@ __device__ __forceinline__ uint32_t pack4(uint32_t x, bool &bad) {
 // The cut / pad rule (makeStringSize_, src/fastq.cc:57-66) only decides `filtered`: a segment
 // shorter than its share would be padded with 'N', so the tuple is dropped and its characters
 // no longer matter.
+// WIDE: the word is hi << 64 | lo (its last 32 letters in lo); a filtered tuple is all-ones in both.
+template <bool WIDE, int ROWS>
 __global__ void __launch_bounds__(PACK_THREADS)
     pack_words_kernel(const uint8_t *__restrict__ chars, const uint16_t *__restrict__ seg_len, uint64_t n_tuples,
-                      PackParams pp, uint64_t *__restrict__ keys_out, unsigned long long *__restrict__ usable) {
+                      PackParams pp, uint64_t *__restrict__ keys_out, uint64_t *__restrict__ keys_hi_out,
+                      unsigned long long *__restrict__ usable) {
   extern __shared__ __align__(16) uint8_t tile[];
-  const uint64_t t0 = (uint64_t)blockIdx.x * PACK_ROWS;
-  const uint32_t rows = (uint32_t)min((uint64_t)PACK_ROWS, n_tuples - t0);
+  const uint64_t t0 = (uint64_t)blockIdx.x * ROWS;
+  const uint32_t rows = (uint32_t)min((uint64_t)ROWS, n_tuples - t0);
   const uint32_t bytes = rows * pp.n;
   const uint8_t *src = chars + t0 * pp.n;
   if ((((uintptr_t)src) & 15u) == 0) {
@@ -55,7 +59,7 @@ __global__ void __launch_bounds__(PACK_THREADS)
 
   uint32_t n_good = 0;
   for (uint32_t rr = threadIdx.x; rr < rows; rr += PACK_THREADS) {
-    uint64_t key = 0;
+    uint64_t key = 0, key_hi = 0;
     bool bad = false;
     const uint8_t *row = tile + rr * pp.n;
     if (seg_len) {
@@ -65,18 +69,24 @@ __global__ void __launch_bounds__(PACK_THREADS)
     const uint32_t full = pp.n & ~3u;
     if ((pp.n & 3u) == 0) {  // rows are 4-byte aligned in shared memory
       const uint32_t *row4 = reinterpret_cast<const uint32_t *>(row);
-      for (uint32_t q = 0; q < full; q += 4) key = (key << 8) | pack4(row4[q >> 2], bad);
+      for (uint32_t q = 0; q < full; q += 4) {
+        if (WIDE) key_hi = (key_hi << 8) | (key >> 56);
+        key = (key << 8) | pack4(row4[q >> 2], bad);
+      }
     } else {
       for (uint32_t q = 0; q < full; q += 4) {
         uint32_t x = row[q] | (row[q + 1] << 8) | (row[q + 2] << 16) | ((uint32_t)row[q + 3] << 24);
+        if (WIDE) key_hi = (key_hi << 8) | (key >> 56);
         key = (key << 8) | pack4(x, bad);
       }
     }
     for (uint32_t q = full; q < pp.n; q++) {
       uint32_t one = pack4(row[q] | 0x41414100u, bad);  // pad with 'A' (code 0, valid)
+      if (WIDE) key_hi = (key_hi << 2) | (key >> 62);
       key = (key << 2) | ((one >> 6) & 3u);
     }
     keys_out[t0 + rr] = bad ? KEY_INVALID : key;
+    if (WIDE) keys_hi_out[t0 + rr] = bad ? KEY_INVALID : key_hi;
     n_good += bad ? 0u : 1u;
   }
 #pragma unroll
@@ -90,12 +100,15 @@ int stage_pack(State &s, const uint8_t *d_chars, const uint16_t *d_seg_len, uint
   pp.n = s.cfg.word_length;
   pp.n_segs = s.cfg.n_segments;
   for (uint32_t i = 0; i < pp.n_segs; i++) pp.take[i] = s.cfg.seg_take[i];
-  unsigned grid = grid_for(n, PACK_ROWS);
-  size_t smem = (size_t)PACK_ROWS * pp.n;
-  // makeWord: n ASCII bytes in, one 8-byte key out
-  Timed t(s, "pack", n, n * (pp.n + 8));
-  pack_words_kernel<<<grid, PACK_THREADS, smem, s.stream>>>(d_chars, d_seg_len, n, pp, s.tuple_key.p + first,
-                                                            s.counters.p + 0);
+  // makeWord: n ASCII bytes in, one 8-byte key (two for a word of more than 31 letters) out
+  Timed t(s, "pack", n, n * (pp.n + (s.wide() ? 16 : 8)));
+  if (s.wide())
+    pack_words_kernel<true, PACK_ROWS_WIDE><<<grid_for(n, PACK_ROWS_WIDE), PACK_THREADS, (size_t)PACK_ROWS_WIDE * pp.n,
+                                              s.stream>>>(d_chars, d_seg_len, n, pp, s.tuple_key.p + first,
+                                                          s.tuple_hi.p + first, s.counters.p + 0);
+  else
+    pack_words_kernel<false, PACK_ROWS><<<grid_for(n, PACK_ROWS), PACK_THREADS, (size_t)PACK_ROWS * pp.n, s.stream>>>(
+        d_chars, d_seg_len, n, pp, s.tuple_key.p + first, nullptr, s.counters.p + 0);
   HUMID_CUDA(cudaGetLastError());
   return 1;
 }
@@ -285,7 +298,7 @@ static int table_insert(State &s, const uint64_t *keys, const uint32_t *index, u
 }
 
 int stage_early_insert(State &s, uint64_t first, uint64_t n) {
-  if (s.cfg.defer_table || s.cfg.expected_tuples == 0) return 0;
+  if (s.cfg.defer_table || s.cfg.expected_tuples == 0 || s.wide()) return 0;
   int k = 0;
   if (first == 0) {
     k += table_clear(s, table_capacity_for(s.cfg.expected_tuples));

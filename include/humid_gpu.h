@@ -27,7 +27,9 @@ extern "C" {
 
 #define HUMID_GPU_ABI_VERSION 1
 #define HUMID_MAX_SEGMENTS 16 /* header UMI + up to 15 input files */
-#define HUMID_MAX_WORD_LENGTH 31 /* one 64-bit key per word (2 bits/nt + a spare sentinel bit) */
+#define HUMID_MAX_NARROW_WORD_LENGTH 31 /* one 64-bit key per word (2 bits/nt + a spare sentinel bit) */
+#define HUMID_MAX_WORD_LENGTH 63 /* longer words take two 64-bit keys: Hamming (and edit distance 1) only,
+                                    one GPU only; everything else about the calls is the same */
 
 enum {
   HUMID_GPU_OK = 0,
@@ -127,6 +129,9 @@ int humid_gpu_cluster_ids(humid_gpu *h, uint64_t first_tuple, uint64_t n, uint32
  * Words in rank order; any output pointer may be NULL.  `cap` = capacity of each array. */
 int humid_gpu_debug_words(humid_gpu *h, uint64_t cap, uint64_t *keys, uint32_t *counts,
                           uint32_t *first_tuple, uint32_t *cluster_ids);
+/* Words of more than HUMID_MAX_NARROW_WORD_LENGTH letters: humid_gpu_debug_words returns the low 64
+ * bits of each word (its last 32 letters), this call the bits above them. */
+int humid_gpu_debug_words_hi(humid_gpu *h, uint64_t cap, uint64_t *keys_hi);
 /* Neighbour lists (NLeaf::neighbours, src/leaf.h:6-9) as CSR over ranks, in the
  * reference's list order and multiplicity.  row_ptr has unique+1 entries; call with
  * col == NULL to obtain *n_entries first. */

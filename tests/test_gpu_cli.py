@@ -24,6 +24,8 @@ CASES = [  # (name, config, tuples, overrides, extra flags, gz inputs)
     ("c4_edit2", 3, 4000, {}, ["-a"], False),
     ("c5_umi10", 4, 15000, {}, [], False),
     ("n30", 1, 5000, dict(word_length=30), ["-a"], False),
+    ("n36_umifile", 1, 15000, dict(word_length=36), ["-a"], False),  # all 12 UMI letters used (docs/usage.rst:18-20)
+    ("n50_ham2_max", 2, 6000, dict(word_length=50, distance=2, maximum=True), ["-a"], False),
     ("no_dedup_output", 0, 3000, {}, ["-q"], False),
 ]
 

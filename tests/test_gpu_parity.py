@@ -48,6 +48,7 @@ def assert_same_as_oracle(dd, r, R):
     assert (c["total"], c["usable"], c["unique"], c["clusters"]) == (r.total, r.usable, r.unique, r.clusters)
     keys, cnt, first, cid = dd.words()
     assert np.array_equal(keys, r.keys)
+    assert np.array_equal(dd.words_hi(), r.keys_hi)
     assert np.array_equal(cnt.astype(np.uint64), r.count)
     assert np.array_equal(first.astype(np.uint64), r.first)
     row_ptr, col = dd.neighbours()
@@ -107,6 +108,77 @@ def test_against_oracle(ci, R, kw):
     r = oracle.Result(keys, cfg.word_length, cfg.distance, cfg.edit, cfg.maximum)
     dd = run_gpu(chars, seg_take, cfg.word_length, cfg.distance, cfg.edit, cfg.maximum, batches=2)
     assert_same_as_oracle(dd, r, R)
+
+
+WIDE_CASES = [  # words of 32..63 letters: two key halves (config 2 at `-n 36`)
+    (1, 30000, dict(word_length=36)),
+    (1, 30000, dict(word_length=36, maximum=True)),
+    (1, 20000, dict(word_length=36, distance=2)),
+    (1, 20000, dict(word_length=32)),
+    (1, 20000, dict(word_length=33, distance=2, maximum=True)),
+    (2, 20000, dict(word_length=48, distance=3)),
+    (2, 20000, dict(word_length=63, distance=2)),
+    (0, 20000, dict(word_length=40, maximum=False)),
+    (3, 8000, dict(word_length=36, distance=1)),  # edit distance 1 == Hamming 1
+    (2, 20000, dict(word_length=34, genome_len=3000, distance=2)),  # few distinct fragments: long groups
+]
+
+
+@pytest.mark.parametrize("ci,R,kw", WIDE_CASES,
+                         ids=[f"c{c + 1}_{R}_{'_'.join(f'{k}{v}' for k, v in kw.items())}" for c, R, kw in WIDE_CASES])
+def test_wide_words_against_oracle(ci, R, kw):
+    cfg = baseline_config(ci, R, **kw)
+    s = Synth(cfg)
+    chars = s.word_chars()
+    hdr, take = s.layout()
+    seg_take = ([hdr] if hdr else []) + take
+    keys = oracle.pack_words(chars, seg_take)
+    assert isinstance(keys, tuple)
+    r = oracle.Result(keys, cfg.word_length, cfg.distance, cfg.edit, cfg.maximum)
+    dd = run_gpu(chars, seg_take, cfg.word_length, cfg.distance, cfg.edit, cfg.maximum, batches=3)
+    assert_same_as_oracle(dd, r, R)
+
+
+def test_wide_words_edge_cases():
+    """Empty input, everything filtered, short segments, and a handle reused after reset."""
+    n, take = 36, [12, 12, 12]
+    dd = api.Dedup(word_length=n, distance=1, seg_take=take)
+    dd.finalize()
+    assert dd.counts() == dict(total=0, usable=0, unique=0, clusters=0)
+    dd.reset()
+    chars = np.full((100, n), ord("N"), dtype=np.uint8)
+    dd.add_batch(chars)
+    dd.finalize()
+    assert dd.counts() == dict(total=100, usable=0, unique=0, clusters=0)
+    assert not dd.keep_mask().any() and not dd.cluster_ids().any()
+    dd.reset()
+    rng = np.random.default_rng(5)
+    chars = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, size=(5000, n))]
+    chars[rng.integers(0, 5000, 60), rng.integers(0, n, 60)] = ord("N")
+    chars[1000:2000] = chars[:1000]  # duplicates
+    seg_len = np.tile(np.array(take, dtype=np.uint16), (5000, 1))
+    seg_len[rng.integers(0, 5000, 50), rng.integers(0, 3, 50)] = 11  # short segment: padded with N => filtered
+    dd.add_batch(chars[:3000], seg_len[:3000])
+    dd.add_batch(chars[3000:], seg_len[3000:])
+    dd.finalize()
+    r = oracle.Result(oracle.pack_words(chars, take, seg_len), n, 1, False, False)
+    assert_same_as_oracle(dd, r, 5000)
+    with pytest.raises(api.HumidGpuError):
+        api.Dedup(word_length=36, distance=2, seg_take=take, edit=True)
+    with pytest.raises(api.HumidGpuError):
+        api.Dedup(word_length=64, distance=1, seg_take=[32, 32])
+
+
+def test_wide_words_million():
+    """1 M tuples at -n 36 (configs[1] shape): the two-sort word construction over many tiles."""
+    cfg = baseline_config(1, 1_000_000, word_length=36)
+    s = Synth(cfg)
+    chars = s.word_chars()
+    hdr, take = s.layout()
+    seg_take = ([hdr] if hdr else []) + take
+    r = oracle.Result(oracle.pack_words(chars, seg_take), cfg.word_length, cfg.distance, cfg.edit, cfg.maximum)
+    dd = run_gpu(chars, seg_take, cfg.word_length, cfg.distance, cfg.edit, cfg.maximum, batches=3)
+    assert_same_as_oracle(dd, r, 1_000_000)
 
 
 def test_against_oracle_millions():
@@ -256,4 +328,4 @@ def test_call_order_errors():
     with pytest.raises(api.HumidGpuError):
         dd.add_batch(_chars(["ACGT"]))
     with pytest.raises(api.HumidGpuError):
-        api.Dedup(word_length=40, distance=1, seg_take=[40])
+        api.Dedup(word_length=64, distance=1, seg_take=[64])  # longer than two 64-bit keys

@@ -1,12 +1,16 @@
-"""Per-stage device times of one configuration: python tools/stage_table.py <config index> <tuples> [steps]."""
+"""Per-stage device times of one configuration: python tools/stage_table.py <config index> <tuples> [steps] [word length]."""
+import os
 import sys
+
 import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from humid_b200 import api
 from humid_b200.synth import HashSynth, baseline_config
 
 ci, R = int(sys.argv[1]), int(sys.argv[2])
 steps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
-cfg = baseline_config(ci, R)
+cfg = baseline_config(ci, R, **({"word_length": int(sys.argv[4])} if len(sys.argv) > 4 else {}))
 syn = HashSynth(cfg)
 hdr, take = syn.layout()
 seg_take = ([hdr] if hdr else []) + take
