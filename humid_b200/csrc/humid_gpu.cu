@@ -86,40 +86,18 @@ void humid_gpu_destroy(humid_gpu *h) {
   if (!h) return;
   State &s = h->s;
   cudaSetDevice(s.device);
+  if (s.copy_stream) cudaStreamSynchronize(s.copy_stream);
   if (s.stream) cudaStreamSynchronize(s.stream);
   clear_stats(s);
-  if (s.copy_stream) cudaStreamSynchronize(s.copy_stream);
+  if (s.open) clear_stats(*s.open);
   for (int b = 0; b < 2; b++) {
-    s.stage_chars[b].release();
-    s.stage_seg_len[b].release();
     if (s.ev_copied[b]) cudaEventDestroy(s.ev_copied[b]);
     if (s.ev_consumed[b]) cudaEventDestroy(s.ev_consumed[b]);
   }
-  if (s.copy_stream) cudaStreamDestroy(s.copy_stream);
-  s.tuple_hi.release(); s.word_hi.release(); s.wide_k0.release(); s.wide_k1.release(); s.wide_k2.release();
-  s.tuple_rank.release(); s.wide_v0.release(); s.wide_v1.release();
-  s.tuple_key.release(); s.counters.release(); s.part_key.release(); s.part_index.release(); s.word_flags.release(); s.join_entries.release(); s.join_entries_out.release();
-  s.slots.release(); s.word_key.release(); s.key_alt.release(); s.word_slot.release(); s.slot_alt.release();
-  s.word_count.release(); s.word_first.release(); s.entries.release(); s.entries_alt.release();
-  s.entry_val.release(); s.entry_val_alt.release(); s.row_ptr.release(); s.deg.release(); s.col.release();
-  s.comp.release(); s.label.release(); s.members.release(); s.seg_start.release(); s.seg_end.release();
-  s.work_a.release(); s.work_b.release(); s.work_c.release(); s.seed_flag.release(); s.seed_index.release();
-  s.seed_size.release(); s.seed_max.release(); s.cluster_size.release(); s.cluster_max.release();
-  s.shard_keys.release(); s.shard_index.release(); s.filter.release();
-  s.keep_bits.release(); s.out_ids.release(); s.scratch.release(); s.scan_scratch.release();
-  if (s.open) {
-    State &o = *s.open;
-    o.counters.release(); o.word_count.release(); o.row_ptr.release(); o.col.release(); o.comp.release();
-    o.label.release(); o.work_a.release(); o.work_b.release(); o.work_c.release(); o.seg_start.release();
-    o.seg_end.release(); o.members.release(); o.key_alt.release(); o.entries_alt.release(); o.slot_alt.release();
-    o.seed_flag.release(); o.seed_index.release(); o.seed_size.release(); o.seed_max.release();
-    o.cluster_size.release(); o.cluster_max.release(); o.scratch.release(); o.scan_scratch.release();
-    delete s.open;
-  }
-  s.is_open.release(); s.open_pos.release(); s.open_ent.release(); s.open_rank.release(); s.open_first.release();
-  s.seed_first.release(); s.cluster_first.release(); s.word_cid.release(); s.open_flag.release(); s.comp_open.release();
-  if (s.stream) cudaStreamDestroy(s.stream);
-  delete h;
+  cudaStream_t stream = s.stream, copy_stream = s.copy_stream;
+  delete h;  // device memory: every DevBuf / Scratch of the State (and of its open-component State) frees itself
+  if (copy_stream) cudaStreamDestroy(copy_stream);
+  if (stream) cudaStreamDestroy(stream);
 }
 
 int humid_gpu_reset(humid_gpu *h) {

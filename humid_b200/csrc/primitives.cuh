@@ -10,6 +10,10 @@ namespace humid {
 struct Scratch {
   void *ptr = nullptr;
   size_t bytes = 0;
+  Scratch() = default;
+  Scratch(const Scratch &) = delete;
+  Scratch &operator=(const Scratch &) = delete;
+  ~Scratch() { release(); }
   void *get(size_t need) {
     if (need > bytes) {
       if (ptr) cudaFree(ptr);

@@ -14,10 +14,27 @@
 
 namespace humid {
 
+// Device array owned by the handle: freed when the handle goes away, movable (std::swap of two
+// columns), never copied.
 template <typename T>
 struct DevBuf {
   T *p = nullptr;
   size_t cap = 0;  // elements
+  DevBuf() = default;
+  DevBuf(const DevBuf &) = delete;
+  DevBuf &operator=(const DevBuf &) = delete;
+  DevBuf(DevBuf &&o) noexcept : p(o.p), cap(o.cap) { o.p = nullptr; o.cap = 0; }
+  DevBuf &operator=(DevBuf &&o) noexcept {
+    if (this != &o) {
+      release();
+      p = o.p;
+      cap = o.cap;
+      o.p = nullptr;
+      o.cap = 0;
+    }
+    return *this;
+  }
+  ~DevBuf() { release(); }
   // Make room for n elements; contents are NOT preserved when reallocating.
   T *ensure(size_t n) {
     if (n > cap) {
@@ -71,6 +88,8 @@ struct State {
   bool wide() const { return cfg.word_length > HUMID_MAX_NARROW_WORD_LENGTH; }
   DevBuf<uint64_t> tuple_hi, word_hi, wide_k0, wide_k1, wide_k2;
   DevBuf<uint32_t> tuple_rank, wide_v0, wide_v1;
+  const uint32_t *wide_sorted_index = nullptr, *wide_pos_rank = nullptr;  // inside wide_v0 / wide_v1
+  bool wide_ranks_ready = false;                                         // tuple_rank has been filled for this job
   // H2D staging for add_batch: two buffers, uploads on their own stream so that batch i+1
   // travels while batch i is packed and counted
   DevBuf<uint8_t> stage_chars[2];
@@ -154,6 +173,11 @@ struct State {
   Scratch scratch, scan_scratch;
   std::vector<StageStat> stats;
   std::string last_error;
+
+  State() = default;
+  State(const State &) = delete;
+  State &operator=(const State &) = delete;
+  ~State() { delete open; }  // every DevBuf / Scratch member frees itself; streams and events belong to the ABI layer
 
   // Per-kernel(-family) device timing: CUDA events on `stream` around the launches.
   size_t timer_begin(const char *name, uint64_t units, uint64_t algo_bytes) {

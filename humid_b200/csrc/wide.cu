@@ -7,8 +7,9 @@
 // of method: there is no 128-bit word table.  The tuples are sorted by (hi, lo) with the stable
 // radix sort (two key halves = two sorts, the tuple index rides along), runs of equal keys are the
 // distinct words: run length = Leaf::count, first element of the run = the first tuple in input
-// order (stability), run number = rank.  Every tuple remembers the rank of its word, which is what
-// the table look-up of the narrow path answers later (cluster ids).  The neighbour search is the
+// order (stability), run number = rank.  The sorted tuple indices and the rank of every sorted
+// position are kept: scattered into a tuple -> rank column on demand, they answer what the table
+// look-up of the narrow path answers (cluster ids).  The neighbour search is the
 // same block join; a block other than the prefix is extracted into a 64-bit column, the (value,
 // rank) pairs are sorted and the key halves gathered into that order.
 #include <algorithm>
@@ -33,29 +34,34 @@ __global__ void __launch_bounds__(256)
   head[i] = i == 0 || hi[i] != hi[i - 1] || lo[i] != lo[i - 1];
 }
 
-// rank of position i = heads before it (+ its own) - 1.  Heads write the word columns and where their run starts.
+// rank of position i = heads before it (+ its own) - 1; it replaces the head flag in place.  Heads write the
+// word columns and where their run starts.
 __global__ void __launch_bounds__(256)
     wide_words_kernel(const uint64_t *__restrict__ hi, const uint64_t *__restrict__ lo, const uint32_t *__restrict__ index,
-                      const uint32_t *__restrict__ head, const uint32_t *__restrict__ head_scan, uint64_t usable,
-                      uint64_t n_tuples, uint64_t *__restrict__ word_hi, uint64_t *__restrict__ word_lo,
-                      uint32_t *__restrict__ word_first, uint32_t *__restrict__ run_start,
-                      uint32_t *__restrict__ tuple_rank) {
+                      uint32_t *__restrict__ head_then_rank, const uint32_t *__restrict__ head_scan, uint64_t usable,
+                      uint64_t *__restrict__ word_hi, uint64_t *__restrict__ word_lo, uint32_t *__restrict__ word_first,
+                      uint32_t *__restrict__ run_start) {
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_tuples) return;
-  const uint32_t t = index[i];
-  if (i >= usable) {
-    tuple_rank[t] = NONE32;
-    return;
-  }
-  const uint32_t h = head[i];
+  if (i >= usable) return;
+  const uint32_t h = head_then_rank[i];
   const uint32_t r = head_scan[i] + h - 1u;
-  tuple_rank[t] = r;
+  head_then_rank[i] = r;
   if (h) {
     word_hi[r] = hi[i];
     word_lo[r] = lo[i];
-    word_first[r] = t;
+    word_first[r] = index[i];
     run_start[r] = (uint32_t)i;
   }
+}
+
+// tuple -> rank of its word (NONE32 for the filtered tuples, which sort behind the usable ones): only
+// humid_gpu_cluster_ids asks, so the scatter waits for the first such call
+__global__ void __launch_bounds__(256)
+    wide_tuple_ranks_kernel(const uint32_t *__restrict__ index, const uint32_t *__restrict__ pos_rank, uint64_t usable,
+                            uint64_t n_tuples, uint32_t *__restrict__ tuple_rank) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_tuples) return;
+  tuple_rank[index[i]] = i < usable ? pos_rank[i] : NONE32;
 }
 
 __global__ void __launch_bounds__(256)
@@ -80,7 +86,7 @@ int stage_build_words_wide(State &s) {
   s.word_hi.ensure(s.usable + 1);
   s.word_count.ensure(s.usable + 1);
   s.word_first.ensure(s.usable + 1);
-  s.tuple_rank.ensure(R + 1);
+  s.wide_ranks_ready = false;
   if (R == 0) return 0;
   s.wide_k0.ensure(R);
   s.wide_k1.ensure(R);
@@ -115,7 +121,7 @@ int stage_build_words_wide(State &s) {
   const uint32_t *index = v2[c2];
   uint32_t *head = v2[1 - c2];
   {
-    Timed t(s, "word_runs", R, s.usable * (16 + 4 + 4 + 4) + R * (4 + 4));
+    Timed t(s, "word_runs", s.usable, s.usable * (16 + 4 + 4 + 4 + 4));
     s.work_a.ensure(s.usable + 1);  // scan of the heads
     s.work_b.ensure(s.usable + 1);  // where each run starts
     uint32_t *total = reinterpret_cast<uint32_t *>(s.counters.p + 1);
@@ -125,9 +131,13 @@ int stage_build_words_wide(State &s) {
       wide_heads_kernel<<<grid_for(s.usable, 256), 256, 0, s.stream>>>(hi, lo, s.usable, head);
       launches += 1 + exclusive_scan_u32(head, s.work_a.p, s.usable, total, s.scan_scratch, s.stream);
     }
-    wide_words_kernel<<<gR, 256, 0, s.stream>>>(hi, lo, index, head, s.work_a.p, s.usable, R, s.word_hi.p, s.word_key.p,
-                                                s.word_first.p, s.work_b.p, s.tuple_rank.p);
-    launches++;
+    if (s.usable) {
+      wide_words_kernel<<<grid_for(s.usable, 256), 256, 0, s.stream>>>(hi, lo, index, head, s.work_a.p, s.usable,
+                                                                      s.word_hi.p, s.word_key.p, s.word_first.p, s.work_b.p);
+      launches++;
+    }
+    s.wide_sorted_index = index;  // both stay in wide_v0 / wide_v1 until the next job
+    s.wide_pos_rank = head;
     HUMID_CUDA(cudaMemcpyAsync(&s.unique, s.counters.p + 1, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     if (s.unique) {
@@ -261,6 +271,14 @@ __global__ void __launch_bounds__(256)
 
 int stage_cluster_ids_wide(State &s, uint64_t first, uint64_t n, uint32_t *d_out) {
   if (n == 0) return 0;
+  if (!s.wide_ranks_ready) {
+    const uint64_t R = s.n_tuples;
+    s.tuple_rank.ensure(R + 1);
+    Timed t(s, "tuple_ranks", R, R * (4 + 4 + 4));
+    wide_tuple_ranks_kernel<<<grid_for(R, 256), 256, 0, s.stream>>>(s.wide_sorted_index, s.wide_pos_rank, s.usable, R,
+                                                                    s.tuple_rank.p);
+    s.wide_ranks_ready = true;
+  }
   Timed t(s, "cluster_ids", n, n * (4 + 4 + 4 + 4));
   cluster_ids_by_rank_kernel<<<grid_for(n, 256), 256, 0, s.stream>>>(s.tuple_rank.p, first, n, s.label.p, s.seed_index.p,
                                                                      d_out);
