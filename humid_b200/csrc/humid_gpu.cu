@@ -224,6 +224,11 @@ int humid_gpu_finalize(humid_gpu *h) {
     }
     stage_cluster(s);
     stage_keep(s);
+    // writeFiltered asks for the whole bitmap next: it travels while the stream drains
+    s.keep_host_words = (s.report_tuples + 31) / 32 + 2;
+    s.keep_host.ensure(s.keep_host_words);
+    HUMID_CUDA(cudaMemcpyAsync(s.keep_host.p, s.keep_bits.p, s.keep_host_words * sizeof(uint32_t), cudaMemcpyDeviceToHost,
+                               s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     resolve_stats(s);
     s.finalized = true;
@@ -270,13 +275,10 @@ int humid_gpu_keep_mask(humid_gpu *h, uint64_t first_tuple, uint64_t n, uint64_t
   if (first_tuple + n > s.report_tuples) return fail(h, HUMID_GPU_ERR_ARG, "tuple range out of bounds");
   if (first_tuple % 64) return fail(h, HUMID_GPU_ERR_ARG, "first_tuple must be a multiple of 64");
   if (n == 0) return HUMID_GPU_OK;
-  return guarded(h, [&] {
-    HUMID_CUDA(cudaSetDevice(s.device));
-    uint64_t words = (n + 63) / 64;
-    HUMID_CUDA(cudaMemcpyAsync(bits, s.keep_bits.p + first_tuple / 32, words * 8, cudaMemcpyDeviceToHost, s.stream));
-    HUMID_CUDA(cudaStreamSynchronize(s.stream));
-    if (n % 64) bits[words - 1] &= (~0ull) >> (64 - n % 64);
-  });
+  const uint64_t words = (n + 63) / 64;
+  std::memcpy(bits, s.keep_host.p + first_tuple / 32, words * 8);  // copied to the host by finalize
+  if (n % 64) bits[words - 1] &= (~0ull) >> (64 - n % 64);
+  return HUMID_GPU_OK;
 }
 
 int humid_gpu_cluster_ids(humid_gpu *h, uint64_t first_tuple, uint64_t n, uint32_t *ids) {

@@ -66,6 +66,27 @@ struct DevBuf {
   }
 };
 
+// Page-locked host array owned by the handle (results that the host will read right after finalize).
+template <typename T>
+struct HostBuf {
+  T *p = nullptr;
+  size_t cap = 0;
+  HostBuf() = default;
+  HostBuf(const HostBuf &) = delete;
+  HostBuf &operator=(const HostBuf &) = delete;
+  ~HostBuf() { if (p) cudaFreeHost(p); }
+  T *ensure(size_t n) {
+    if (n > cap) {
+      if (p) cudaFreeHost(p);
+      p = nullptr;
+      cap = 0;
+      HUMID_CUDA(cudaHostAlloc((void **)&p, (n + n / 8 + 64) * sizeof(T), cudaHostAllocDefault));
+      cap = n + n / 8 + 64;
+    }
+    return p;
+  }
+};
+
 struct StageStat {
   const char *name;
   float ms = 0.f;
@@ -166,6 +187,8 @@ struct State {
 
   // outputs
   DevBuf<uint32_t> keep_bits;  // ceil(R/32) words
+  HostBuf<uint32_t> keep_host; // the same bitmap, copied at the end of finalize (page-locked: full PCIe rate)
+  uint64_t keep_host_words = 0;
   DevBuf<uint32_t> out_ids;
   std::vector<uint64_t> hist_k[3], hist_v[3];
   bool hist_done[3] = {false, false, false};

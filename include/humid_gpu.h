@@ -119,7 +119,7 @@ int humid_gpu_histogram(humid_gpu *h, int which, uint64_t *keys, uint64_t *vals,
 /* Pass 2 — replaces `trie.find` + the visited/maxLeaf test of writeFiltered
  * (src/humid.cc:220-234): bit (t - first_tuple) of `bits` (LSB-first inside each
  * uint64_t) is set iff tuple t is written to the *_dedup files.  `bits` holds
- * ceil(n/64) words. */
+ * ceil(n/64) words.  (finalize has already brought the bitmap to the host: no device work here.) */
 int humid_gpu_keep_mask(humid_gpu *h, uint64_t first_tuple, uint64_t n, uint64_t *bits);
 /* … and of writeAnnotated (:268-285): the cluster id appended to each header, 0 for
  * filtered tuples. */
