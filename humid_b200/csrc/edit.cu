@@ -28,10 +28,14 @@ namespace humid {
 
 constexpr int EDIT_MAX_D = 3;  // one deletion+insertion pair plus substitutions
 
+// v is a candidate of query q and q one of query v (the relation is enumerated from one side only)
 __device__ __forceinline__ void emit_candidate(uint64_t *cand, uint64_t cap, unsigned long long *counter, uint32_t q,
                                                uint32_t v) {
-  const unsigned long long pos = reserve_slots(counter);
-  if (pos < cap) cand[pos] = ((uint64_t)q << 32) | v;
+  const unsigned long long pos = reserve_slots(counter, 2u);
+  if (pos + 1 < cap) {
+    cand[pos] = ((uint64_t)q << 32) | v;
+    cand[pos + 1] = ((uint64_t)v << 32) | q;
+  }
 }
 
 // All words obtained from `base` by 0..budget further substitutions (positions strictly
@@ -78,26 +82,29 @@ __device__ void probe_substitutions(uint64_t base, uint32_t n, int budget, uint3
 }
 
 // Deletion of letter i + insertion of letter c so that it lands at position q (a one-letter
-// block shift), then up to d-2 substitutions: one thread per (word, i, q).
+// block shift), then up to d-2 substitutions: one thread per (word, i, q) with q < i.  Only these
+// "right" shifts are enumerated: v is a right shift of w exactly when w is a left shift of v (undo
+// the insertion, redo the deletion), so every hit is recorded in both directions and the other half
+// of the (i, q) square is never probed.
 __global__ void __launch_bounds__(128)
     edit_candidates_shift_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, uint32_t d,
                                  const Lookup lk, uint64_t *__restrict__ cand, uint64_t cap,
                                  unsigned long long *__restrict__ counter) {
   uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const uint64_t per_word = (uint64_t)n * n;
+  const uint64_t per_word = (uint64_t)n * (n - 1) / 2;
+  if (per_word == 0) return;
   uint64_t r = gid / per_word;
   if (r >= U) return;
-  uint32_t rem = (uint32_t)(gid - r * per_word);
-  const uint32_t i = rem / n, q = rem - i * n;
-  if (i == q) return;  // a plain substitution (or the word itself): covered by the other kernel
+  const uint32_t rem = (uint32_t)(gid - r * per_word);  // = i (i - 1) / 2 + q, 0 <= q < i < n
+  uint32_t i = (uint32_t)((1.0f + sqrtf(1.0f + 8.0f * (float)rem)) * 0.5f);
+  while (i * (i - 1) / 2 > rem) i--;
+  while ((i + 1) * i / 2 <= rem) i++;
+  const uint32_t q = rem - i * (i - 1) / 2;
   const uint64_t w = word_key[r];
-  const uint32_t a = min(i, q), b = max(i, q);  // affected positions [a, b]
-  const uint32_t sh_a = 2 * (n - 1 - a), sh_b = 2 * (n - 1 - b);
-  const uint64_t seg_mask = (sh_a + 2 >= 64 ? ~0ull : ((1ull << (sh_a + 2)) - 1ull)) & ~((1ull << sh_b) - 1ull);
-  const uint64_t seg = w & seg_mask;
-  // q < i: letters q..i-1 move one place to the right; q > i: letters i+1..q move to the left
-  const uint64_t moved = (q < i ? (seg >> 2) : (seg << 2)) & seg_mask;
-  const uint32_t sh_q = 2 * (n - 1 - q);
+  // affected positions [q, i]: letters q..i-1 move one place to the right, the new letter lands at q
+  const uint32_t sh_q = 2 * (n - 1 - q), sh_i = 2 * (n - 1 - i);
+  const uint64_t seg_mask = (sh_q + 2 >= 64 ? ~0ull : ((1ull << (sh_q + 2)) - 1ull)) & ~((1ull << sh_i) - 1ull);
+  const uint64_t moved = ((w & seg_mask) >> 2) & seg_mask;
   const uint64_t base0 = (w & ~seg_mask) | (moved & ~(3ull << sh_q));
   for (uint64_t c = 0; c < 4; c++) {
     uint64_t v = base0 | (c << sh_q);
@@ -376,11 +383,11 @@ int stage_neighbours_edit(State &s) {
       HUMID_CUDA(cudaStreamSynchronize(s.stream));
     }
     // (b) one deletion + one insertion (a one-letter block shift) and up to d-2 substitutions: variants
-    //     probed against the word table, 4 n (n-1) (1 + 3 n at d = 3) per word
+    //     probed against the word table, 2 n (n-1) (1 + 3 n at d = 3) per word (one direction of the shift only)
     {
-      double shifts = 4.0 * n * (n - 1) * (d >= 3 ? 1.0 + 3.0 * n : 1.0);
+      double shifts = 2.0 * n * (n - 1) * (d >= 3 ? 1.0 + 3.0 * n : 1.0);
       Timed t(s, "edit_candidates", U, (uint64_t)(U * 8.0 * (1.0 + shifts)));
-      edit_candidates_shift_kernel<<<grid_for(U * n * n, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, d, lk,
+      edit_candidates_shift_kernel<<<grid_for(U * (n * (n - 1) / 2), 128), 128, 0, s.stream>>>(s.word_key.p, U, n, d, lk,
                                                                                   s.entries.p, cap, counter);
     }
     k++;

@@ -202,8 +202,12 @@ int stage_neighbours_hamming_wide(State &s) {
   WideBlocks B{};
   B.n_blocks = d + 1;
   int lo_bit[HAM_MAX_D + 1], hi_bit[HAM_MAX_D + 1];
+  // Any cut of the letters into d+1 blocks finds every pair.  The prefix block costs nothing (rank order
+  // groups by it), every other block one sort of its bits: those get at most 12 letters each (16 beyond
+  // 64 M words) — enough for groups of a word or two — and the prefix takes the rest.
+  const uint32_t other = std::min<uint32_t>(n / (d + 1), U > (64ull << 20) ? 16u : 12u);
   for (uint32_t b = 0; b <= d; b++) {
-    const uint32_t p0 = b * n / (d + 1), p1 = (b + 1) * n / (d + 1);  // letters [p0, p1)
+    const uint32_t p0 = b == 0 ? 0u : n - (d + 1 - b) * other, p1 = n - (d - b) * other;  // letters [p0, p1)
     lo_bit[b] = 2 * (int)(n - p1);
     hi_bit[b] = 2 * (int)(n - p0);
     wide_mask(lo_bit[b], hi_bit[b], B.mask_hi[b], B.mask_lo[b]);
@@ -225,7 +229,7 @@ int stage_neighbours_hamming_wide(State &s) {
     for (uint32_t b = 0; b <= d; b++) {
       const uint64_t *keys_hi = s.word_hi.p, *keys_lo = s.word_key.p;
       const uint32_t *rank = nullptr;
-      if (b > 0) {  // blocks are at least 16 letters long here, never empty
+      if (b > 0) {  // never empty: n >= 32 and d <= 8
         const int width = hi_bit[b] - lo_bit[b];
         const uint64_t passes = (uint64_t)(width + 7) / 8;
         Timed t(s, "join_sort", U, U * (16 + 8 + 8 + (8 + 12) + (passes - 1) * 24 + 4 + 32));
