@@ -22,6 +22,9 @@
 // Own yields are appended in yield order (key = q<<32|q), the mirrored pushes as (v<<32|q);
 // the stable sort of stage_csr then produces list(L) = [pushes by queries q < L] ++ [own
 // yields] ++ [pushes by queries q > L], which is the reference's list order.
+#include <algorithm>
+#include <cstdlib>
+
 #include "state.cuh"
 
 namespace humid {
@@ -167,17 +170,18 @@ __device__ __forceinline__ uint32_t lower_letter(const uint64_t *__restrict__ ke
 // level is a (2 D + 1) x (D + 1) band of counters.  Moves exactly as in the replay below: deletion
 // (t, p+1, k-1) with no bound on p; the child v[t] only if v[t] >= w[p] (w[p] = 0 past the end);
 // match / substitution (t+1, p+1, k - [v[t] != w[p]]) needs p < n; insertion (t+1, p, k-1).
+// The count can start anywhere: from the frame (t0 letters of v consumed, query position p0, budget
+// k0) it is the number of yields of the subtree of the recursion below that frame, which is what the
+// replay needs once a node of the candidate trie holds a single word.
 constexpr int DPD = 3;  // EDIT_MAX_D
-__device__ uint32_t single_candidate_yields(uint64_t w, uint64_t v, uint32_t n, int d) {
+__device__ uint32_t candidate_yields_from(uint64_t w, uint64_t v, uint32_t n, uint32_t t0, uint32_t p0, int k0) {
   uint32_t cur[2 * DPD + 1][DPD + 1];
+  const int o0 = (int)p0 - (int)t0 + DPD;  // |p - t| never exceeds the budget spent: 0 <= o0 <= 2 DPD
 #pragma unroll
   for (int o = 0; o <= 2 * DPD; o++)
 #pragma unroll
-    for (int k = 0; k <= DPD; k++) cur[o][k] = 0;
-#pragma unroll
-  for (int k = 0; k <= DPD; k++)
-    if (k == d) cur[DPD][k] = 1;
-  for (uint32_t t = 0;; t++) {
+    for (int k = 0; k <= DPD; k++) cur[o][k] = (o == o0 && k == k0) ? 1u : 0u;
+  for (uint32_t t = t0;; t++) {
     // deletions inside the level, in increasing p so that chains are counted
 #pragma unroll
     for (int o = 0; o < 2 * DPD; o++)
@@ -221,6 +225,10 @@ __device__ uint32_t single_candidate_yields(uint64_t w, uint64_t v, uint32_t n, 
   return yields;
 }
 
+__device__ __forceinline__ uint32_t single_candidate_yields(uint64_t w, uint64_t v, uint32_t n, int d) {
+  return candidate_yields_from(w, v, n, 0u, 0u, d);
+}
+
 // Queries with one candidate are finished here; those with more are listed for the walk below, so
 // that its warps are full of work.
 __global__ void __launch_bounds__(128)
@@ -228,7 +236,9 @@ __global__ void __launch_bounds__(128)
                               const uint32_t *__restrict__ cand_row, const uint32_t *__restrict__ cand_v,
                               const uint64_t *__restrict__ cand_key, uint64_t *__restrict__ entries,
                               uint32_t *__restrict__ entry_val, uint64_t cap, unsigned long long *__restrict__ counter,
-                              uint32_t *__restrict__ multi_list, unsigned long long *__restrict__ n_multi) {
+                              uint32_t *__restrict__ multi_list, unsigned long long *__restrict__ n_multi,
+                              uint32_t heavy_from, uint32_t *__restrict__ heavy_list,
+                              unsigned long long *__restrict__ n_heavy) {
   uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = r < U;
   const uint32_t seg = live ? cand_row[r] : 0u, m = live ? cand_row[r + 1] - seg : 0u;
@@ -258,38 +268,93 @@ __global__ void __launch_bounds__(128)
       }
     }
   }
-  const unsigned many = __ballot_sync(0xffffffffu, m >= 2);
+  // two lists: queries with many candidates (heavy_from and more) are walked first, so that the longest
+  // walks start when the replay does and not at its end
+  const bool is_heavy = m >= 2 && m >= heavy_from, is_multi = m >= 2 && !is_heavy;
+  const unsigned many = __ballot_sync(0xffffffffu, is_multi);
   if (many) {
     unsigned long long at = 0;
     const int leader = __ffs(many) - 1;
     if ((int)lane == leader) at = atomicAdd(n_multi, (unsigned long long)__popc(many));
     at = __shfl_sync(0xffffffffu, at, leader);
-    if (m >= 2) multi_list[at + __popc(many & ((1u << lane) - 1u))] = (uint32_t)r;
+    if (is_multi) multi_list[at + __popc(many & ((1u << lane) - 1u))] = (uint32_t)r;
+  }
+  const unsigned heavy = __ballot_sync(0xffffffffu, is_heavy);
+  if (heavy) {
+    unsigned long long at = 0;
+    const int leader = __ffs(heavy) - 1;
+    if ((int)lane == leader) at = atomicAdd(n_heavy, (unsigned long long)__popc(heavy));
+    at = __shfl_sync(0xffffffffu, at, leader);
+    if (is_heavy) heavy_list[at + __popc(heavy & ((1u << lane) - 1u))] = (uint32_t)r;
   }
 }
 
-__global__ void __launch_bounds__(128)
-    edit_replay_kernel(const uint64_t *__restrict__ word_key, const uint32_t *__restrict__ multi_list, uint64_t n_multi,
-                       uint32_t n, int d, const uint32_t *__restrict__ cand_row, const uint32_t *__restrict__ cand_v,
-                       const uint64_t *__restrict__ cand_key, uint64_t *__restrict__ entries,
-                       uint32_t *__restrict__ entry_val, uint64_t cap, unsigned long long *__restrict__ counter) {
-  const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (gid >= n_multi) return;
-  const uint64_t r = multi_list[gid];
+// Two exact shortcuts of the recursion, shared by both replay kernels.
+//
+// frame_alive: can the frame (t letters of the stored word consumed, query position p, budget k) still
+// reach a yield?  Every stored word has the query's length n.  A substitution / match needs p < n and the
+// yield needs p >= n at t = n.  So a frame behind the diagonal (p < t) takes t - p deletions, and before the
+// leaf the n - t letters still to come take an insertion each except for the min(n - t, n - p) that a
+// substitution / match can cover — every one of these moves costs one unit of budget.
+// (Checked exhaustively against the recursion for short words: every frame with a yield below it is alive.)
+__device__ __forceinline__ bool frame_alive(uint32_t n, uint32_t t, uint32_t p, int k) {
+  if (p < t) return k >= (int)(t - p);
+  if (t < n) {
+    const uint32_t rem = n - t, subs = p < n ? min(rem, n - p) : 0u;
+    return k >= (int)(rem - subs);
+  }
+  return true;
+}
+// A live frame without budget (so p == t before the leaf) can only match letter by letter: it yields the one
+// word of its range [lo, hi) whose remaining letters are the query's, once — or nothing.  Returns that
+// candidate's index or NONE32.  (The words of the range share their first t letters.)
+__device__ __forceinline__ uint32_t zero_budget_match(const uint64_t *__restrict__ keys, uint32_t lo, uint32_t hi,
+                                                      uint64_t w, uint32_t n, uint32_t t) {
+  if (t >= n) return lo;  // a leaf: the range is one word, the query is used up (frame_alive)
+  const uint32_t end = hi;
+  const uint64_t low = (1ull << (2 * (n - t))) - 1ull;
+  const uint64_t target = (keys[lo] & ~low) | (w & low);
+  while (lo < hi) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (keys[mid] < target) lo = mid + 1; else hi = mid;
+  }
+  return lo < end && keys[lo] == target ? lo : NONE32;
+}
+
+// The recursion of one query, walked frame by frame with an explicit stack.
+__device__ __forceinline__ void edit_walk_query(const uint64_t r, const uint64_t *__restrict__ word_key, uint32_t n, int d,
+                                                const uint32_t *__restrict__ cand_row, const uint32_t *__restrict__ cand_v,
+                                                const uint64_t *__restrict__ cand_key, uint64_t *__restrict__ entries,
+                                                uint32_t *__restrict__ entry_val, uint64_t cap,
+                                                unsigned long long *__restrict__ counter) {
   const uint32_t seg = cand_row[r], m = cand_row[r + 1] - seg;
   const uint64_t w = word_key[r];
   const uint64_t *keys = cand_key + seg;
   const uint32_t *ranks = cand_v + seg;
   Frame stk[EDIT_STACK];
   int sp = 0;
+  auto yield = [&](uint32_t v) {
+    const unsigned long long p = reserve_slots(counter, 2u);
+    if (p + 2 <= cap) {
+      entries[p] = (r << 32) | (uint32_t)r;       // own yield, in yield order
+      entry_val[p] = v;
+      entries[p + 1] = ((uint64_t)v << 32) | (uint32_t)r;  // r.leaf->neighbours.push_back(walk leaf)
+      entry_val[p + 1] = (uint32_t)r;
+    }
+  };
   stk[sp++] = Frame{0u, m, 0, 0, (int8_t)d, 0};
   while (sp > 0) {
     Frame &f = stk[sp - 1];
     const uint32_t st = f.stage++;
     if (st == 0) {  // deletion: same node, next query position (also past the end, :202-203)
-      if (f.dist >= 1) {
-        stk[sp] = Frame{f.lo, f.hi, f.depth, (uint8_t)(f.pos + 1), (int8_t)(f.dist - 1), 0};
-        sp++;
+      if (f.dist >= 1 && frame_alive(n, f.depth, f.pos + 1u, f.dist - 1)) {
+        if (f.dist == 1) {  // no budget left below: at most one word, once
+          const uint32_t ci = zero_budget_match(keys, f.lo, f.hi, w, n, f.depth);
+          if (ci != NONE32) yield(ranks[ci]);
+        } else {
+          stk[sp] = Frame{f.lo, f.hi, f.depth, (uint8_t)(f.pos + 1), (int8_t)(f.dist - 1), 0};
+          sp++;
+        }
       }
     } else if (st <= 8) {
       const uint32_t c = (st - 1) >> 1;
@@ -300,25 +365,167 @@ __global__ void __launch_bounds__(128)
       if (!insertion && f.pos >= n) continue;                      // substitution needs a query letter
       const int nd = insertion ? f.dist - 1 : f.dist - (int)(c != wl);
       if (nd < 0) continue;
+      const uint32_t npos = insertion ? f.pos : f.pos + 1u;
+      if (!frame_alive(n, f.depth + 1u, npos, nd)) continue;
       const uint32_t sh = 2 * (n - 1 - f.depth);
       const uint32_t clo = lower_letter(keys, f.lo, f.hi, sh, c);
       const uint32_t chi = lower_letter(keys, clo, f.hi, sh, c + 1);
       if (clo >= chi) { if (!insertion) f.stage++; continue; }  // no such child: skip its insertion too
-      stk[sp] = Frame{clo, chi, (uint8_t)(f.depth + 1), (uint8_t)(insertion ? f.pos : f.pos + 1), (int8_t)nd, 0};
+      if (nd == 0) {
+        const uint32_t ci = zero_budget_match(keys, clo, chi, w, n, f.depth + 1u);
+        if (ci != NONE32) yield(ranks[ci]);
+        continue;
+      }
+      stk[sp] = Frame{clo, chi, (uint8_t)(f.depth + 1), (uint8_t)npos, (int8_t)nd, 0};
       sp++;
     } else if (st == 9) {
-      if (f.pos >= n && f.depth == n && f.lo < f.hi) {  // yield node->leaf
-        const uint32_t v = ranks[f.lo];
-        const unsigned long long p = reserve_slots(counter, 2u);
-        if (p + 2 <= cap) {
-          entries[p] = (r << 32) | (uint32_t)r;       // own yield, in yield order
-          entry_val[p] = v;
-          entries[p + 1] = ((uint64_t)v << 32) | (uint32_t)r;  // r.leaf->neighbours.push_back(walk leaf)
-          entry_val[p + 1] = (uint32_t)r;
-        }
-      }
+      if (f.pos >= n && f.depth == n && f.lo < f.hi) yield(ranks[f.lo]);  // yield node->leaf
     } else {
       sp--;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(128)
+    edit_replay_kernel(const uint64_t *__restrict__ word_key, const uint32_t *__restrict__ multi_list, uint64_t n_multi,
+                       uint32_t n, int d, const uint32_t *__restrict__ cand_row, const uint32_t *__restrict__ cand_v,
+                       const uint64_t *__restrict__ cand_key, uint64_t *__restrict__ entries,
+                       uint32_t *__restrict__ entry_val, uint64_t cap, unsigned long long *__restrict__ counter) {
+  const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid < n_multi) edit_walk_query(multi_list[gid], word_key, n, d, cand_row, cand_v, cand_key, entries, entry_val, cap, counter);
+}
+
+// Queries with two or more candidates, in two converged phases instead of one divergent walk.
+// Phase A walks the recursion only through the nodes of the candidate trie that still hold two or more
+// words; a child holding ONE word v is not entered: all yields below it are v, they are consecutive in
+// the depth-first order, and their number is the path count from that frame — so the frame is noted as a
+// task (candidate, depth, query position, budget), in order.  Phase B runs the recurrence for task j of
+// every lane side by side, then the warp reserves its output with one atomic and every lane writes
+// its runs.  A query with more tasks than the list holds (or more than 1023 candidates) is left to the
+// walking kernel above; queries with many candidates are walked by the first blocks of this one.
+constexpr int EDIT_TASKS = 96;
+constexpr uint32_t EDIT_HEAVY = 16;
+__global__ void __launch_bounds__(128)
+    edit_replay_tasks_kernel(const uint64_t *__restrict__ word_key, const uint32_t *__restrict__ multi_list,
+                             uint64_t n_multi, uint32_t n, int d, uint32_t task_cap, const uint32_t *__restrict__ cand_row,
+                             const uint32_t *__restrict__ cand_v, const uint64_t *__restrict__ cand_key,
+                             uint64_t *__restrict__ entries, uint32_t *__restrict__ entry_val, uint64_t cap,
+                             unsigned long long *__restrict__ counter, uint32_t *__restrict__ walk_list,
+                             unsigned long long *__restrict__ n_walk, const uint32_t *__restrict__ heavy_list,
+                             uint32_t n_heavy) {
+  // the first blocks walk the queries with many candidates (block-uniform branch)
+  const uint32_t heavy_blocks = (n_heavy + blockDim.x - 1) / blockDim.x;
+  if (blockIdx.x < heavy_blocks) {
+    const uint32_t h = blockIdx.x * blockDim.x + threadIdx.x;
+    if (h < n_heavy) edit_walk_query(heavy_list[h], word_key, n, d, cand_row, cand_v, cand_key, entries, entry_val, cap, counter);
+    return;
+  }
+  const uint64_t gid = (uint64_t)(blockIdx.x - heavy_blocks) * blockDim.x + threadIdx.x;
+  const bool live = gid < n_multi;
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint64_t r = live ? multi_list[gid] : 0ull;
+  const uint32_t seg = live ? cand_row[r] : 0u, m = live ? cand_row[r + 1] - seg : 0u;
+  const uint64_t w = live ? word_key[r] : 0ull;
+  const uint64_t *keys = cand_key + seg;
+  const uint32_t *ranks = cand_v + seg;
+  uint32_t tasks[EDIT_TASKS];   // candidate << 14 | depth << 8 | position << 2 | budget
+  uint32_t counts[EDIT_TASKS];
+  uint32_t nt = 0;
+  bool over = live && m > 1023u;
+  if (live && !over) {
+    Frame stk[EDIT_STACK];
+    int sp = 0;
+    stk[sp++] = Frame{0u, m, 0, 0, (int8_t)d, 0};
+    while (sp > 0) {
+      Frame &f = stk[sp - 1];
+      const uint32_t st = f.stage++;
+      if (st == 0) {  // deletion
+        if (f.dist >= 1 && frame_alive(n, f.depth, f.pos + 1u, f.dist - 1)) {
+          if (f.dist == 1) {  // no budget left below: at most one word, once
+            const uint32_t ci = zero_budget_match(keys, f.lo, f.hi, w, n, f.depth);
+            if (ci != NONE32) {
+              if (nt == task_cap) { over = true; break; }
+              tasks[nt++] = (ci << 14) | ((uint32_t)f.depth << 8) | ((f.pos + 1u) << 2);
+            }
+          } else {
+            stk[sp] = Frame{f.lo, f.hi, f.depth, (uint8_t)(f.pos + 1), (int8_t)(f.dist - 1), 0};
+            sp++;
+          }
+        }
+      } else if (st <= 8) {
+        const uint32_t c = (st - 1) >> 1;
+        const bool insertion = ((st - 1) & 1u) != 0;
+        if (f.depth >= n) { f.stage = 9; continue; }
+        const uint32_t wl = f.pos < n ? (uint32_t)(w >> (2 * (n - 1 - f.pos))) & 3u : 0u;
+        if (c < wl) { f.stage = (uint8_t)(1 + 2 * wl); continue; }
+        if (!insertion && f.pos >= n) continue;
+        const int nd = insertion ? f.dist - 1 : f.dist - (int)(c != wl);
+        if (nd < 0) continue;
+        const uint32_t npos = insertion ? f.pos : f.pos + 1u;
+        if (!frame_alive(n, f.depth + 1u, npos, nd)) continue;
+        const uint32_t sh = 2 * (n - 1 - f.depth);
+        const uint32_t clo = lower_letter(keys, f.lo, f.hi, sh, c);
+        const uint32_t chi = lower_letter(keys, clo, f.hi, sh, c + 1);
+        if (clo >= chi) { if (!insertion) f.stage++; continue; }
+        if (nd == 0) {
+          const uint32_t ci = zero_budget_match(keys, clo, chi, w, n, f.depth + 1u);
+          if (ci != NONE32) {
+            if (nt == task_cap) { over = true; break; }
+            tasks[nt++] = (ci << 14) | ((uint32_t)(f.depth + 1) << 8) | (npos << 2);
+          }
+        } else if (chi - clo == 1u) {  // a single word below: count instead of walking
+          if (nt == task_cap) { over = true; break; }
+          tasks[nt++] = (clo << 14) | ((uint32_t)(f.depth + 1) << 8) | (npos << 2) | (uint32_t)nd;
+        } else {
+          stk[sp] = Frame{clo, chi, (uint8_t)(f.depth + 1), (uint8_t)npos, (int8_t)nd, 0};
+          sp++;
+        }
+      } else {
+        sp--;  // (a node holding two words is never a leaf: the candidates are distinct)
+      }
+    }
+  }
+  {  // queries handed to the walking kernel
+    const unsigned ov = __ballot_sync(0xffffffffu, over);
+    if (ov) {
+      unsigned long long at = 0;
+      const int leader = __ffs(ov) - 1;
+      if ((int)lane == leader) at = atomicAdd(n_walk, (unsigned long long)__popc(ov));
+      at = __shfl_sync(0xffffffffu, at, leader);
+      if (over) walk_list[at + __popc(ov & ((1u << lane) - 1u))] = (uint32_t)r;
+    }
+    if (over) nt = 0;
+  }
+  uint32_t total = 0;
+  for (uint32_t j = 0; j < nt; j++) {
+    const uint32_t tk = tasks[j];
+    // a task without budget was matched when it was noted: one yield
+    const uint32_t c = (tk & 3u) == 0u ? 1u
+                                       : candidate_yields_from(w, keys[tk >> 14], n, (tk >> 8) & 63u, (tk >> 2) & 63u,
+                                                               (int)(tk & 3u));
+    counts[j] = c;
+    total += c;
+  }
+  uint32_t inc = total;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+    if ((int)lane >= o) inc += t;
+  }
+  const uint32_t warp_total = __shfl_sync(0xffffffffu, inc, 31);
+  if (warp_total == 0) return;
+  unsigned long long base = 0;
+  if (lane == 31) base = atomicAdd(counter, 2ull * warp_total);
+  base = __shfl_sync(0xffffffffu, base, 31) + 2ull * (inc - total);
+  if (total && base + 2ull * total <= cap) {
+    for (uint32_t j = 0; j < nt; j++) {
+      const uint32_t v = ranks[tasks[j] >> 14];
+      for (uint32_t y = 0; y < counts[j]; y++, base += 2) {
+        entries[base] = (r << 32) | (uint32_t)r;  // own yield, in yield order
+        entry_val[base] = v;
+        entries[base + 1] = ((uint64_t)v << 32) | (uint32_t)r;  // r.leaf->neighbours.push_back(walk leaf)
+        entry_val[base + 1] = (uint32_t)r;
+      }
     }
   }
 }
@@ -446,24 +653,52 @@ int stage_neighbours_edit(State &s) {
     s.entry_val.ensure(ecap);
     ecap = std::min<uint64_t>(s.entries_alt.cap, s.entry_val.cap);
     HUMID_CUDA(cudaMemsetAsync(s.counters.p + 2, 0, sizeof(unsigned long long), s.stream));
-    HUMID_CUDA(cudaMemsetAsync(s.counters.p + 43, 0, sizeof(unsigned long long), s.stream));
+    HUMID_CUDA(cudaMemsetAsync(s.counters.p + 43, 0, 3 * sizeof(unsigned long long), s.stream));  // 43, 44, 45
     s.word_flags.ensure(U + 1);  // list of the queries with two or more candidates
-    uint64_t n_multi = 0;
+    s.seed_index.ensure(U + 1);  // ... and of those with EDIT_HEAVY or more
+    // testing knobs.  HUMID_GPU_EDIT_TASKS: task list length of the counting replay, 0 = walk every query;
+    // HUMID_GPU_EDIT_HEAVY: number of candidates from which a query is walked straight away
+    uint32_t task_cap = EDIT_TASKS, heavy_from = EDIT_HEAVY;
+    if (const char *e = std::getenv("HUMID_GPU_EDIT_TASKS"))
+      task_cap = (uint32_t)std::min<long>(std::max<long>(std::strtol(e, nullptr, 10), 0), EDIT_TASKS);
+    if (const char *e = std::getenv("HUMID_GPU_EDIT_HEAVY"))
+      heavy_from = (uint32_t)std::max<long>(std::strtol(e, nullptr, 10), 2);
+    if (task_cap == 0) heavy_from = 0xFFFFFFFFu;  // one list, walked
+    uint64_t n_multi = 0, n_heavy = 0;
     {
       Timed t(s, "edit_replay_single", U, U * 16 + n_distinct * 12);
       edit_replay_single_kernel<<<grid_for(U, 128), 128, 0, s.stream>>>(s.word_key.p, U, n, (int)d, s.work_a.p, s.work_c.p,
                                                                         s.key_alt.p, s.entries_alt.p, s.entry_val.p, ecap,
                                                                         s.counters.p + 2, s.word_flags.p,
-                                                                        s.counters.p + 43);
+                                                                        s.counters.p + 43, heavy_from, s.seed_index.p,
+                                                                        s.counters.p + 45);
     }
     HUMID_CUDA(cudaMemcpyAsync(&n_multi, s.counters.p + 43, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+    HUMID_CUDA(cudaMemcpyAsync(&n_heavy, s.counters.p + 45, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
-    if (n_multi) {
-      Timed t(s, "edit_replay", n_multi, n_distinct * 12 + n_multi * 16);
-      edit_replay_kernel<<<grid_for(n_multi, 128), 128, 0, s.stream>>>(s.word_key.p, s.word_flags.p, n_multi, n, (int)d,
-                                                                       s.work_a.p, s.work_c.p, s.key_alt.p,
-                                                                       s.entries_alt.p, s.entry_val.p, ecap,
-                                                                       s.counters.p + 2);
+    const uint32_t *walk_list = s.word_flags.p;
+    uint64_t n_walk = n_multi;
+    if ((n_multi || n_heavy) && task_cap) {
+      s.seed_flag.ensure(n_multi + 1);  // the queries left to the walk
+      HUMID_CUDA(cudaMemsetAsync(s.counters.p + 44, 0, sizeof(unsigned long long), s.stream));
+      {
+        Timed t(s, "edit_replay_count", n_multi + n_heavy, n_distinct * 12 + (n_multi + n_heavy) * 16);
+        const unsigned blocks = (unsigned)((n_heavy + 127) / 128 + (n_multi + 127) / 128);
+        edit_replay_tasks_kernel<<<blocks, 128, 0, s.stream>>>(
+            s.word_key.p, s.word_flags.p, n_multi, n, (int)d, task_cap, s.work_a.p, s.work_c.p, s.key_alt.p, s.entries_alt.p,
+            s.entry_val.p, ecap, s.counters.p + 2, s.seed_flag.p, s.counters.p + 44, s.seed_index.p, (uint32_t)n_heavy);
+      }
+      k++;
+      HUMID_CUDA(cudaMemcpyAsync(&n_walk, s.counters.p + 44, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+      HUMID_CUDA(cudaStreamSynchronize(s.stream));
+      walk_list = s.seed_flag.p;
+    }
+    if (n_walk) {
+      Timed t(s, "edit_replay", n_walk, n_walk * 16);
+      edit_replay_kernel<<<grid_for(n_walk, 128), 128, 0, s.stream>>>(s.word_key.p, walk_list, n_walk, n, (int)d,
+                                                                      s.work_a.p, s.work_c.p, s.key_alt.p,
+                                                                      s.entries_alt.p, s.entry_val.p, ecap,
+                                                                      s.counters.p + 2);
     }
     k += 2;
     HUMID_CUDA(cudaMemcpyAsync(&s.n_entries, s.counters.p + 2, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));

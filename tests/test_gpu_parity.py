@@ -244,6 +244,38 @@ def test_oversized_groups_take_the_probe_path(monkeypatch, ci, R, kw, group_cap,
         assert "probe_flagged" in names
 
 
+EDIT_REPLAY_CASES = [
+    (3, 8000, {}),
+    (3, 8000, dict(maximum=True)),
+    (3, 4000, dict(word_length=10, genome_len=3000)),  # many candidates per query
+    (3, 1500, dict(distance=3, word_length=12, genome_len=3000)),
+]
+
+
+@pytest.mark.parametrize("heavy_from", [3, 16])
+@pytest.mark.parametrize("task_cap", [0, 2, 7, 96])
+@pytest.mark.parametrize("ci,R,kw", EDIT_REPLAY_CASES,
+                         ids=[f"c{c + 1}_{R}_{'_'.join(f'{k}{v}' for k, v in kw.items())}" for c, R, kw in EDIT_REPLAY_CASES])
+def test_edit_replay_by_counting_and_by_walking(monkeypatch, ci, R, kw, task_cap, heavy_from):
+    """Queries with several candidates: subtrees holding one word are counted (task list), queries whose
+    list overflows or that have `heavy_from` candidates or more are walked.  0 walks everything, tiny lists
+    mix the kernels.  Same lists, same order."""
+    monkeypatch.setenv("HUMID_GPU_EDIT_TASKS", str(task_cap))
+    monkeypatch.setenv("HUMID_GPU_EDIT_HEAVY", str(heavy_from))
+    cfg = baseline_config(ci, R, **kw)
+    s = Synth(cfg)
+    chars = s.word_chars()
+    hdr, take = s.layout()
+    seg_take = ([hdr] if hdr else []) + take
+    r = oracle.Result(oracle.pack_words(chars, seg_take), cfg.word_length, cfg.distance, cfg.edit, cfg.maximum)
+    dd = run_gpu(chars, seg_take, cfg.word_length, cfg.distance, cfg.edit, cfg.maximum, batches=2)
+    assert_same_as_oracle(dd, r, R)
+    names = {st["name"] for st in dd.stage_stats()}
+    assert ("edit_replay_count" in names) == (task_cap > 0)
+    if task_cap == 0 or (task_cap == 2 and heavy_from == 16):
+        assert "edit_replay" in names
+
+
 def _chars(words):
     return np.frombuffer("".join(words).encode(), dtype=np.uint8).reshape(len(words), -1).copy()
 
