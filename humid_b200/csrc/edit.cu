@@ -103,14 +103,23 @@ __global__ void __launch_bounds__(128)
   while (i * (i - 1) / 2 > rem) i--;
   while ((i + 1) * i / 2 <= rem) i++;
   const uint32_t q = rem - i * (i - 1) / 2;
+  // A shift by one letter changes two positions; with the d-2 substitutions still allowed that is within
+  // Hamming distance d: the block join has that pair already.
+  if (i - q < 2) return;
   const uint64_t w = word_key[r];
-  // affected positions [q, i]: letters q..i-1 move one place to the right, the new letter lands at q
   const uint32_t sh_q = 2 * (n - 1 - q), sh_i = 2 * (n - 1 - i);
+  // Deleting any letter of a run of equal letters gives the same word: only the last letter of a run is deleted.
+  if (i + 1 < n && ((w >> sh_i) & 3ull) == ((w >> (sh_i - 2)) & 3ull)) return;
+  // affected positions [q, i]: letters q..i-1 move one place to the right, the new letter lands at q
   const uint64_t seg_mask = (sh_q + 2 >= 64 ? ~0ull : ((1ull << (sh_q + 2)) - 1ull)) & ~((1ull << sh_i) - 1ull);
   const uint64_t moved = ((w & seg_mask) >> 2) & seg_mask;
   const uint64_t base0 = (w & ~seg_mask) | (moved & ~(3ull << sh_q));
-  for (uint64_t c = 0; c < 4; c++) {
-    uint64_t v = base0 | (c << sh_q);
+  // the letter w[q] in front of w[q] is the same word as behind it: that is the shift (i, q + 1), or, when
+  // q + 1 == i, a word the block join has — so only the three other letters are inserted
+  const uint64_t wq = (w >> sh_q) & 3ull;
+#pragma unroll
+  for (uint64_t k = 1; k < 4; k++) {
+    const uint64_t v = base0 | (((wq + k) & 3ull) << sh_q);
     probe_substitutions(v, n, (int)d - 2, 0, w, (uint32_t)r, lk, cand, cap, counter, true);
   }
 }
