@@ -439,6 +439,67 @@ Blocks make_blocks(uint32_t n, uint32_t d, int lo_bit[], int hi_bit[]) {
   return B;
 }
 
+// What the single-GPU Hamming search joins on.  Entry e: the words are grouped by the letters under
+// B.mask[e] (obtained from rank order by up to two stable sorts over contiguous bit ranges, least significant
+// range first; a group inside the prefix needs none), and a pair is reported by the first entry both words
+// agree on.
+//   * d + 1 blocks (make_blocks): one block per entry.
+//   * d == 2: FOUR blocks, and an entry per pair of blocks — two words within distance 2 agree on at least two
+//     of four blocks.  Six entries instead of three, but a group is now the words sharing half of their letters
+//     (about one word at 20 M words of 24 letters) instead of a third (about 300): at 50 M tuples of
+//     configs[2] the three joins took 5.7 ms each.  A pair of blocks that contains the prefix block only
+//     needs the other block sorted: inside a group of that block, rank order keeps equal prefixes together.
+struct JoinPlan {
+  Blocks B;
+  int n_sorts[HAM_MAX_D + 1];
+  int lo_bit[HAM_MAX_D + 1][2], hi_bit[HAM_MAX_D + 1][2];
+};
+
+static JoinPlan make_join_plan(uint32_t n, uint32_t d) {
+  JoinPlan P{};
+  bool combos = d == 2 && n >= 8;
+  if (const char *e = std::getenv("HUMID_GPU_JOIN_SCHEME"))  // testing knob: "blocks" or "combos"
+    combos = combos && e[0] == 'c';
+  if (!combos) {
+    int lo[HAM_MAX_D + 1], hi[HAM_MAX_D + 1];
+    P.B = make_blocks(n, d, lo, hi);
+    for (uint32_t b = 0; b <= d; b++) {
+      P.n_sorts[b] = b > 0 && hi[b] > lo[b] ? 1 : 0;
+      P.lo_bit[b][0] = lo[b];
+      P.hi_bit[b][0] = hi[b];
+    }
+    return P;
+  }
+  int lo[4], hi[4];
+  uint64_t mask[4];
+  for (uint32_t b = 0; b < 4; b++) {
+    const uint32_t p0 = b * n / 4, p1 = (b + 1) * n / 4;  // letters [p0, p1), never empty (n >= 8)
+    lo[b] = 2 * (int)(n - p1);
+    hi[b] = 2 * (int)(n - p0);
+    mask[b] = (~0ull >> (64 - 2 * (p1 - p0))) << lo[b];
+  }
+  uint32_t e = 0;
+  for (int a = 0; a < 4; a++)
+    for (int b = a + 1; b < 4; b++, e++) {
+      P.B.mask[e] = mask[a] | mask[b];
+      if (a == 0 && b == 1) {
+        P.n_sorts[e] = 0;  // the prefix: rank order
+      } else if (a == 0 || b == a + 1) {  // the prefix block + one other, or two adjacent blocks: one bit range
+        P.n_sorts[e] = 1;
+        P.lo_bit[e][0] = lo[b];
+        P.hi_bit[e][0] = a == 0 ? hi[b] : hi[a];
+      } else {  // two separate ranges: the less significant one first
+        P.n_sorts[e] = 2;
+        P.lo_bit[e][0] = lo[b];
+        P.hi_bit[e][0] = hi[b];
+        P.lo_bit[e][1] = lo[a];
+        P.hi_bit[e][1] = hi[a];
+      }
+    }
+  P.B.n_blocks = e;  // 6
+  return P;
+}
+
 // HUMID_GPU_JOIN_CAP: group size above which the join hands a group to the probe path (testing knob)
 static uint32_t join_group_cap(uint32_t d) {
   if (const char *e = std::getenv("HUMID_GPU_JOIN_CAP")) {
@@ -459,8 +520,8 @@ int stage_neighbours_hamming(State &s) {
   }
   if (d > HAM_MAX_D) throw CudaError{"Hamming distance > 8 is not supported"};
   int k = 0;
-  int lo_bit[HAM_MAX_D + 1], hi_bit[HAM_MAX_D + 1];
-  const Blocks B = make_blocks(n, d, lo_bit, hi_bit);
+  const JoinPlan P = make_join_plan(n, d);
+  const Blocks &B = P.B;
   const uint32_t group_cap = join_group_cap(d);
   uint64_t cap = s.entries.cap ? s.entries.cap : std::max<uint64_t>(2 * U, 1u << 20);
   s.word_flags.ensure(U + 1);
@@ -476,20 +537,31 @@ int stage_neighbours_hamming(State &s) {
     HUMID_CUDA(cudaMemsetAsync(n_flagged, 0, sizeof(unsigned long long), s.stream));
     HUMID_CUDA(cudaMemsetAsync(s.deg.p, 0, U * sizeof(uint32_t), s.stream));
     HUMID_CUDA(cudaMemsetAsync(s.word_flags.p, 0, U * sizeof(uint32_t), s.stream));
-    for (uint32_t b = 0; b <= d; b++) {
+    for (uint32_t b = 0; b < B.n_blocks; b++) {
       const uint64_t *keys = s.word_key.p;
       const uint32_t *rank = nullptr;
-      if (b > 0 && hi_bit[b] > lo_bit[b]) {
+      if (P.n_sorts[b] > 0) {
         uint64_t *kb[2] = {s.key_alt.p, s.entries_alt.p};
         uint32_t *vb[2] = {s.entry_val.p, s.entry_val_alt.p};
         int launches = 0;
-        const uint64_t passes = (uint64_t)(hi_bit[b] - lo_bit[b] + 7) / 8;  // first pass reads keys only (rank = position)
+        uint64_t passes = (uint64_t)(P.hi_bit[b][0] - P.lo_bit[b][0] + 7) / 8;  // first pass reads keys only (rank = position)
+        if (P.n_sorts[b] > 1) passes += (uint64_t)(P.hi_bit[b][1] - P.lo_bit[b][1] + 7) / 8 + 1;  // + its own histogram read
         Timed t(s, "join_sort", U, U * (8 + (8 + 12) + (passes - 1) * 24));
-        int cur = radix_sort_bits_indexed(s.word_key.p, kb, vb, U, lo_bit[b], hi_bit[b], s.scratch, s.stream, &launches);
+        int cur = radix_sort_bits_indexed(s.word_key.p, kb, vb, U, P.lo_bit[b][0], P.hi_bit[b][0], s.scratch, s.stream,
+                                          &launches);
+        if (P.n_sorts[b] > 1) {  // then, stably, by the more significant range: the first pass writes the free pair
+          uint64_t *kb2[2] = {kb[1 - cur], kb[cur]};
+          uint32_t *vb2[2] = {vb[1 - cur], vb[cur]};
+          const int cur2 = radix_sort_bits_pairs(kb[cur], vb[cur], kb2, vb2, U, P.lo_bit[b][1], P.hi_bit[b][1], s.scratch,
+                                                 s.stream, &launches);
+          keys = kb2[cur2];
+          rank = vb2[cur2];
+        } else {
+          keys = kb[cur];
+          rank = vb[cur];
+        }
         t.launches = launches;
         k += launches;
-        keys = kb[cur];
-        rank = vb[cur];
       }
       // the word, its successor in the group (the walk ends there for almost every word) and the pair out
       static const char *const join_names[HAM_MAX_D + 1] = {"join_hamming_b0", "join_hamming_b1", "join_hamming_b2",

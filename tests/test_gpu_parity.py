@@ -244,6 +244,36 @@ def test_oversized_groups_take_the_probe_path(monkeypatch, ci, R, kw, group_cap,
         assert "probe_flagged" in names
 
 
+SCHEME_CASES = [
+    (2, 30000, {}),
+    (2, 30000, dict(maximum=True)),
+    (2, 20000, dict(word_length=10, genome_len=3000)),           # long groups
+    (2, 20000, dict(word_length=9, genome_len=3000, maximum=True)),  # blocks of 2-3 letters
+    (1, 30000, dict(distance=2)),
+    (0, 20000, dict(distance=2, word_length=31)),
+]
+
+
+@pytest.mark.parametrize("group_cap", [2, 100000])
+@pytest.mark.parametrize("scheme", ["blocks", "combos"])
+@pytest.mark.parametrize("ci,R,kw", SCHEME_CASES, ids=[f"c{c + 1}_{R}_{'_'.join(f'{k}{v}' for k, v in kw.items())}" for c, R, kw in SCHEME_CASES])
+def test_distance_two_by_blocks_and_by_block_pairs(monkeypatch, ci, R, kw, scheme, group_cap):
+    """Hamming distance 2: three blocks (agree on one) or four blocks taken in pairs (agree on two) — the
+    same pairs either way, also when oversized groups go through variant probing."""
+    monkeypatch.setenv("HUMID_GPU_JOIN_SCHEME", scheme)
+    monkeypatch.setenv("HUMID_GPU_JOIN_CAP", str(group_cap))
+    cfg = baseline_config(ci, R, **kw)
+    s = Synth(cfg)
+    chars = s.word_chars()
+    hdr, take = s.layout()
+    seg_take = ([hdr] if hdr else []) + take
+    r = oracle.Result(oracle.pack_words(chars, seg_take), cfg.word_length, cfg.distance, cfg.edit, cfg.maximum)
+    dd = run_gpu(chars, seg_take, cfg.word_length, cfg.distance, cfg.edit, cfg.maximum, batches=2)
+    assert_same_as_oracle(dd, r, R)
+    names = {st["name"] for st in dd.stage_stats()}
+    assert ("join_hamming_b5" in names) == (scheme == "combos")
+
+
 EDIT_REPLAY_CASES = [
     (3, 8000, {}),
     (3, 8000, dict(maximum=True)),
