@@ -56,7 +56,12 @@ struct Lookup {
   uint64_t mask;
   const uint4 *filter;  // may be nullptr (table only)
   uint32_t n_buckets;
+  // optional first level for searches that ask for thousands of variants per word (edit distance): one bit per
+  // hash value, ~3 % of them set, L2-resident — a miss costs one 4-byte load and a handful of instructions
+  const uint32_t *bitmap;  // may be nullptr
+  int bitmap_shift;        // bit index = (key * BITMAP_MUL) >> bitmap_shift
 };
+constexpr uint64_t BITMAP_MUL = 0xD6E8FEB86659FD93ull;
 
 // The filter uses its own, cheaper hash: hf(key) = key * FILTER_MUL (Fibonacci hashing, high
 // bits).  It is linear, so the hash of a variant w + delta is hf(w) + delta * FILTER_MUL: one
@@ -97,6 +102,10 @@ __device__ __forceinline__ uint32_t table_rank(const Lookup &lk, uint64_t key) {
 
 // rank of `key`, or NONE32: filter first, table only on a fingerprint match
 __device__ __forceinline__ uint32_t lookup_rank(const Lookup &lk, uint64_t key) {
+  if (lk.bitmap) {
+    const uint64_t bit = (key * BITMAP_MUL) >> lk.bitmap_shift;
+    if (((__ldg(lk.bitmap + (bit >> 5)) >> (bit & 31u)) & 1u) == 0u) return NONE32;
+  }
   if (lk.filter) {
     const uint64_t hf = filter_hash(key);
     const uint4 b = __ldg(lk.filter + filter_bucket(hf, lk.n_buckets));

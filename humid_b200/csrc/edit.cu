@@ -124,6 +124,15 @@ __global__ void __launch_bounds__(128)
   }
 }
 
+// One bit per hash value of a stored word (Lookup::bitmap)
+__global__ void __launch_bounds__(256)
+    bitmap_build_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t *__restrict__ bits, int shift) {
+  const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= U) return;
+  const uint64_t bit = (word_key[r] * BITMAP_MUL) >> shift;
+  atomicOr(bits + (bit >> 5), 1u << (bit & 31u));
+}
+
 // ---- distinct candidates per query -----------------------------------------------------------
 __global__ void __launch_bounds__(256)
     mark_unique_kernel(const uint64_t *__restrict__ sorted, uint64_t m, uint32_t *__restrict__ flag) {
@@ -547,7 +556,19 @@ int stage_neighbours_edit(State &s) {
   if (d > EDIT_MAX_D) throw CudaError{"edit distance > 3 is not supported (two deletion+insertion pairs)"};
   if (n + d + 2 > EDIT_STACK) throw CudaError{"word too long for the edit replay stack"};
   int k = stage_ensure_lookup(s);
-  const Lookup lk = s.lookup();
+  Lookup lk = s.lookup();
+  {  // first-level bitmap: 16 to 32 bits per word, a power of two
+    int log2_bits = 20;
+    while (log2_bits < 33 && (1ull << log2_bits) < 16 * U) log2_bits++;
+    const uint64_t words32 = (1ull << log2_bits) / 32;
+    s.comp.ensure(words32);  // free until the clustering stage
+    Timed t(s, "edit_bitmap", U, U * 12 + words32 * 4);
+    HUMID_CUDA(cudaMemsetAsync(s.comp.p, 0, words32 * sizeof(uint32_t), s.stream));
+    bitmap_build_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.word_key.p, U, s.comp.p, 64 - log2_bits);
+    lk.bitmap = s.comp.p;
+    lk.bitmap_shift = 64 - log2_bits;
+    k++;
+  }
 
   // phase 1: candidate pairs (with duplicates)
   uint64_t cap = std::max<uint64_t>(s.entries.cap, std::max<uint64_t>(8 * U, 1u << 20));

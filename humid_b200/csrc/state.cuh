@@ -135,7 +135,9 @@ struct State {
   DevBuf<uint32_t> word_flags;  // Hamming join: bit b = the word's block-b group was too large to walk
   uint64_t n_flagged = 0;
   bool ranks_in_table = false;  // slot.count holds the word's rank (stage_ensure_lookup)
-  Lookup lookup() const { return Lookup{slots.p, table_cap - 1, filter_buckets ? filter.p : nullptr, filter_buckets}; }
+  Lookup lookup() const {
+    return Lookup{slots.p, table_cap - 1, filter_buckets ? filter.p : nullptr, filter_buckets, nullptr, 0};
+  }
 
   // what humid_gpu_counts reports / what keep_bits covers (the whole job in shard mode)
   uint64_t report_tuples = 0, report_usable = 0;
