@@ -85,42 +85,125 @@ __device__ void probe_substitutions(uint64_t base, uint32_t n, int budget, uint3
 }
 
 // Deletion of letter i + insertion of letter c so that it lands at position q (a one-letter
-// block shift), then up to d-2 substitutions: one thread per (word, i, q) with q < i.  Only these
-// "right" shifts are enumerated: v is a right shift of w exactly when w is a left shift of v (undo
-// the insertion, redo the deletion), so every hit is recorded in both directions and the other half
-// of the (i, q) square is never probed.
-__global__ void __launch_bounds__(128)
+// block shift), then up to d-2 substitutions.  Only "right" shifts (q < i) are enumerated: v is a right
+// shift of w exactly when w is a left shift of v (undo the insertion, redo the deletion), so every hit
+// is recorded in both directions and the other half of the (i, q) square is never probed.  Left out as
+// well, because another probe or the block join finds the same word:
+//   * i - q == 1: the shift changes two positions; with the d-2 substitutions still allowed that is
+//     within Hamming distance d, and the block join has every such pair;
+//   * a deleted letter that is followed by an equal letter: deleting any letter of a run gives the
+//     same word, only the last letter of a run is deleted;
+//   * inserting the letter w[q]: in front of w[q] it is the same word as behind it, i.e. the shift
+//     (i, q + 1), or a word within Hamming distance d when q + 1 == i - 1.
+// One CTA takes SHIFT_WPB words.  The (i, q) pairs come from a table in shared memory; the live (word,
+// pair) combinations are first compacted into a shared work list, so that the probing loop runs with
+// full warps whatever the words look like.
+constexpr int SHIFT_WPB = 32;
+constexpr int SHIFT_THREADS = 256;
+constexpr int SHIFT_MAX_PAIRS = 30 * 29 / 2;  // n <= 31: (n - 1)(n - 2) / 2 pairs with i - q >= 2
+template <bool D2>  // D2: d == 2 and the bitmap is there — nothing but the shift itself, probed inline
+__global__ void __launch_bounds__(SHIFT_THREADS)
     edit_candidates_shift_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, uint32_t d,
                                  const Lookup lk, uint64_t *__restrict__ cand, uint64_t cap,
-                                 unsigned long long *__restrict__ counter) {
-  uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const uint64_t per_word = (uint64_t)n * (n - 1) / 2;
-  if (per_word == 0) return;
-  uint64_t r = gid / per_word;
-  if (r >= U) return;
-  const uint32_t rem = (uint32_t)(gid - r * per_word);  // = i (i - 1) / 2 + q, 0 <= q < i < n
-  uint32_t i = (uint32_t)((1.0f + sqrtf(1.0f + 8.0f * (float)rem)) * 0.5f);
-  while (i * (i - 1) / 2 > rem) i--;
-  while ((i + 1) * i / 2 <= rem) i++;
-  const uint32_t q = rem - i * (i - 1) / 2;
-  // A shift by one letter changes two positions; with the d-2 substitutions still allowed that is within
-  // Hamming distance d: the block join has that pair already.
-  if (i - q < 2) return;
-  const uint64_t w = word_key[r];
-  const uint32_t sh_q = 2 * (n - 1 - q), sh_i = 2 * (n - 1 - i);
-  // Deleting any letter of a run of equal letters gives the same word: only the last letter of a run is deleted.
-  if (i + 1 < n && ((w >> sh_i) & 3ull) == ((w >> (sh_i - 2)) & 3ull)) return;
-  // affected positions [q, i]: letters q..i-1 move one place to the right, the new letter lands at q
-  const uint64_t seg_mask = (sh_q + 2 >= 64 ? ~0ull : ((1ull << (sh_q + 2)) - 1ull)) & ~((1ull << sh_i) - 1ull);
-  const uint64_t moved = ((w & seg_mask) >> 2) & seg_mask;
-  const uint64_t base0 = (w & ~seg_mask) | (moved & ~(3ull << sh_q));
-  // the letter w[q] in front of w[q] is the same word as behind it: that is the shift (i, q + 1), or, when
-  // q + 1 == i, a word the block join has — so only the three other letters are inserted
-  const uint64_t wq = (w >> sh_q) & 3ull;
+                                 unsigned long long *__restrict__ counter, uint32_t n_pairs, uint32_t inv_pairs) {
+  __shared__ uint16_t pair_tab[SHIFT_MAX_PAIRS];             // i << 8 | q
+  __shared__ uint16_t work[SHIFT_WPB * SHIFT_MAX_PAIRS];     // word in the CTA << 9 | pair
+  __shared__ uint64_t words[SHIFT_WPB];
+  __shared__ uint32_t n_work;
+  const uint64_t first = (uint64_t)blockIdx.x * SHIFT_WPB;
+  const uint32_t n_words = (uint32_t)min((uint64_t)SHIFT_WPB, U - first);
+  const uint32_t lane = threadIdx.x & 31u;
+  if (threadIdx.x == 0) n_work = 0;
+  if (threadIdx.x < n_words) words[threadIdx.x] = word_key[first + threadIdx.x];
+  for (uint32_t t = threadIdx.x; t < n_pairs; t += SHIFT_THREADS) {  // t = j (j - 1) / 2 + q with j = i - 1, q < j
+    uint32_t j = (uint32_t)((1.0f + sqrtf(1.0f + 8.0f * (float)t)) * 0.5f);
+    while (j * (j - 1) / 2 > t) j--;
+    while ((j + 1) * j / 2 <= t) j++;
+    pair_tab[t] = (uint16_t)(((j + 1) << 8) | (t - j * (j - 1) / 2));
+  }
+  __syncthreads();
+  const uint32_t slots = n_words * n_pairs;
+  for (uint32_t base = 0; base < slots; base += SHIFT_THREADS) {
+    const uint32_t t = base + threadIdx.x;
+    bool live = t < slots;
+    uint32_t wl = 0, pi = 0;
+    if (live) {
+      wl = __umulhi(t, inv_pairs);  // t / n_pairs (exact: t < 2^16)
+      pi = t - wl * n_pairs;
+      const uint32_t i = pair_tab[pi] >> 8;
+      const uint64_t w = words[wl];
+      const uint32_t sh_i = 2 * (n - 1 - i);
+      live = !(i + 1 < n && ((w >> sh_i) & 3ull) == ((w >> (sh_i - 2)) & 3ull));  // only the last letter of a run
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, live);
+    uint32_t at = 0;
+    if (lane == 0 && m) at = atomicAdd(&n_work, (uint32_t)__popc(m));
+    at = __shfl_sync(0xffffffffu, at, 0);
+    if (live) work[at + __popc(m & ((1u << lane) - 1u))] = (uint16_t)((wl << 9) | pi);
+  }
+  __syncthreads();
+  const uint32_t total = n_work;
+  Lookup table_only = lk;  // for the words that passed the bitmap here
+  table_only.bitmap = nullptr;
+  if (D2) {
+    // two work items per turn: six independent bitmap loads in flight per thread (the loop waits on L2)
+    for (uint32_t k0 = threadIdx.x; k0 < total; k0 += 2 * SHIFT_THREADS) {
+      uint64_t base0[2], hb0[2], wq[2];
+      uint32_t sh_q[2], r[2];
+      bool have[2];
 #pragma unroll
-  for (uint64_t k = 1; k < 4; k++) {
-    const uint64_t v = base0 | (((wq + k) & 3ull) << sh_q);
-    probe_substitutions(v, n, (int)d - 2, 0, w, (uint32_t)r, lk, cand, cap, counter, true);
+      for (int u = 0; u < 2; u++) {
+        const uint32_t k = k0 + u * SHIFT_THREADS;
+        have[u] = k < total;
+        const uint32_t e = have[u] ? work[k] : 0u;
+        const uint32_t wl = e >> 9, pr = pair_tab[e & 511u];
+        const uint32_t i = pr >> 8, q = pr & 255u;
+        const uint64_t w = words[wl];
+        r[u] = (uint32_t)(first + wl);
+        // affected positions [q, i]: letters q..i-1 move one place to the right, the new letter lands at q
+        sh_q[u] = 2 * (n - 1 - q);
+        const uint32_t sh_i = 2 * (n - 1 - i);
+        const uint64_t seg_mask = (sh_q[u] + 2 >= 64 ? ~0ull : ((1ull << (sh_q[u] + 2)) - 1ull)) & ~((1ull << sh_i) - 1ull);
+        const uint64_t moved = ((w & seg_mask) >> 2) & seg_mask;
+        base0[u] = (w & ~seg_mask) | (moved & ~(3ull << sh_q[u]));
+        wq[u] = (w >> sh_q[u]) & 3ull;
+        hb0[u] = base0[u] * BITMAP_MUL;  // the hash is linear: one multiply per shift, one add per letter
+      }
+      uint32_t bits[2][3];
+#pragma unroll
+      for (int u = 0; u < 2; u++)
+#pragma unroll
+        for (uint64_t c = 1; c < 4; c++) {
+          const uint64_t bit = (hb0[u] + ((wq[u] + c) & 3ull) * (BITMAP_MUL << sh_q[u])) >> lk.bitmap_shift;
+          bits[u][c - 1] = (__ldg(lk.bitmap + (bit >> 5)) >> (bit & 31u)) & 1u;
+        }
+#pragma unroll
+      for (int u = 0; u < 2; u++)
+#pragma unroll
+        for (uint64_t c = 1; c < 4; c++) {
+          if (!have[u] || bits[u][c - 1] == 0u) continue;
+          const uint32_t hit = lookup_rank(table_only, base0[u] | (((wq[u] + c) & 3ull) << sh_q[u]));
+          if (hit != NONE32) emit_candidate(cand, cap, counter, r[u], hit);
+        }
+    }
+  } else {
+    for (uint32_t k = threadIdx.x; k < total; k += SHIFT_THREADS) {
+      const uint32_t e = work[k];
+      const uint32_t wl = e >> 9, pr = pair_tab[e & 511u];
+      const uint32_t i = pr >> 8, q = pr & 255u;
+      const uint64_t w = words[wl];
+      const uint32_t r = (uint32_t)(first + wl);
+      const uint32_t sh_q = 2 * (n - 1 - q), sh_i = 2 * (n - 1 - i);
+      const uint64_t seg_mask = (sh_q + 2 >= 64 ? ~0ull : ((1ull << (sh_q + 2)) - 1ull)) & ~((1ull << sh_i) - 1ull);
+      const uint64_t moved = ((w & seg_mask) >> 2) & seg_mask;
+      const uint64_t base0 = (w & ~seg_mask) | (moved & ~(3ull << sh_q));
+      const uint64_t wq = (w >> sh_q) & 3ull;
+#pragma unroll
+      for (uint64_t c = 1; c < 4; c++) {
+        const uint64_t v = base0 | (((wq + c) & 3ull) << sh_q);
+        probe_substitutions(v, n, (int)d - 2, 0, w, r, lk, cand, cap, counter, true);
+      }
+    }
   }
 }
 
@@ -624,8 +707,14 @@ int stage_neighbours_edit(State &s) {
     {
       double shifts = 2.0 * n * (n - 1) * (d >= 3 ? 1.0 + 3.0 * n : 1.0);
       Timed t(s, "edit_candidates", U, (uint64_t)(U * 8.0 * (1.0 + shifts)));
-      edit_candidates_shift_kernel<<<grid_for(U * (n * (n - 1) / 2), 128), 128, 0, s.stream>>>(s.word_key.p, U, n, d, lk,
-                                                                                  s.entries.p, cap, counter);
+      const uint32_t n_pairs = n >= 3 ? (n - 1) * (n - 2) / 2 : 0u;  // (i, q) with i - q >= 2
+      const uint32_t inv_pairs = n_pairs ? (uint32_t)((1ull << 32) / n_pairs + 1) : 0u;
+      if (n_pairs && d == 2 && lk.bitmap)
+        edit_candidates_shift_kernel<true><<<grid_for(U, SHIFT_WPB), SHIFT_THREADS, 0, s.stream>>>(
+            s.word_key.p, U, n, d, lk, s.entries.p, cap, counter, n_pairs, inv_pairs);
+      else if (n_pairs)
+        edit_candidates_shift_kernel<false><<<grid_for(U, SHIFT_WPB), SHIFT_THREADS, 0, s.stream>>>(
+            s.word_key.p, U, n, d, lk, s.entries.p, cap, counter, n_pairs, inv_pairs);
     }
     k++;
     HUMID_CUDA(cudaMemcpyAsync(&n_cand, s.counters.p + 5, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
