@@ -66,13 +66,16 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs.  The process is
+    started before the warm-up steps (its start-up takes the driver's locks for a while, which stretched the
+    first timed steps of host-synchronising paths several times over); mark() drops the samples taken so far."""
 
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index: int):
         self.rows = []
+        self.start = 0
         self.proc = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
@@ -87,6 +90,13 @@ class ClockSampler:
         for ln in self.proc.stdout:
             self.rows.append([x.strip() for x in ln.split(",")])
 
+    def mark(self):
+        """The timed region starts now (waits for the first sample if nvidia-smi is still starting up)."""
+        t0 = time.time()
+        while self.proc and not self.rows and time.time() - t0 < 5.0:
+            time.sleep(0.02)
+        self.start = len(self.rows)
+
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
@@ -98,7 +108,7 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], 0.0, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        for r in self.rows[self.start:]:
             try:
                 sm.append(float(r[0]))
                 mx = max(mx, float(r[1]))
@@ -287,9 +297,11 @@ def run_gpu_arm(args):
             ms, wall = float(t[0]), float(t[1]) / 1e3
         return ms, wall, out
 
+    sampler = ClockSampler(local) if rank == 0 else None
     for _ in range(args.warmup):
         step_device()
-    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.mark()
     ms_dev, wall_dev, counts = timed(step_device, args.steps)
     stages = dd.stage_stats()
     launches_per_step = sum(s["launches"] for s in stages)

@@ -631,6 +631,69 @@ __global__ void __launch_bounds__(128)
   }
 }
 
+// ---- d == 2: the shift candidates by a join on deletion variants --------------------------------
+// v is one deletion + one insertion away from w exactly when the two words share a word of n - 1 letters
+// obtained by deleting one letter from each.  So every word lists its distinct deletion variants (one per
+// run of equal letters: deleting any letter of a run gives the same variant), the list is sorted by a
+// 32-bit hash of the variant, and words meeting in a group — with truly equal variants — are candidates
+// of each other.  No look-ups: ~n entries per word are written, sorted in four radix passes and read once,
+// against 3 (n-1)(n-2)/2 probes per word through L2 (23 ms -> see DESIGN.md).  A group also holds the pairs
+// that differ by one substitution; they are candidates as well (the block join lists them too, and the
+// list is deduplicated afterwards).
+// entry = (position of the deleted letter << 27 | rank) << 32 | hash of the variant
+constexpr uint32_t DELJOIN_MAX_WORDS = 1u << 27;
+
+__device__ __forceinline__ uint64_t delete_letter(uint64_t w, uint32_t n, uint32_t p) {
+  const uint32_t sh = 2 * (n - 1 - p);
+  return ((w >> (sh + 2)) << sh) | (w & ((1ull << sh) - 1ull));
+}
+__device__ __forceinline__ bool run_ends_at(uint64_t w, uint32_t n, uint32_t p) {
+  return p + 1 == n || (((w >> (2 * (n - 1 - p))) ^ (w >> (2 * (n - 2 - p)))) & 3ull) != 0ull;
+}
+
+__global__ void __launch_bounds__(256)
+    deletion_counts_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n, uint32_t *__restrict__ count) {
+  const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= U) return;
+  const uint64_t w = word_key[r];
+  uint32_t c = 0;
+  for (uint32_t p = 0; p < n; p++) c += run_ends_at(w, n, p) ? 1u : 0u;
+  count[r] = c;
+}
+
+__global__ void __launch_bounds__(256)
+    deletion_variants_kernel(const uint64_t *__restrict__ word_key, uint64_t U, uint32_t n,
+                             const uint32_t *__restrict__ offset, uint64_t *__restrict__ out) {
+  const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= U) return;
+  const uint64_t w = word_key[r];
+  uint64_t o = offset[r];
+  for (uint32_t p = 0; p < n; p++)
+    if (run_ends_at(w, n, p))
+      out[o++] = ((uint64_t)((p << 27) | (uint32_t)r) << 32) | (mix64(delete_letter(w, n, p)) >> 32);
+}
+
+// one thread per sorted entry: forward through the entries with the same hash
+__global__ void __launch_bounds__(256)
+    deletion_join_kernel(const uint64_t *__restrict__ sorted, uint64_t D, const uint64_t *__restrict__ word_key, uint32_t n,
+                         uint64_t *__restrict__ cand, uint64_t cap, unsigned long long *__restrict__ counter) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i + 1 >= D) return;
+  const uint64_t e = ld_stream_u64(sorted + i);
+  const uint32_t h = (uint32_t)e;
+  uint64_t f = sorted[i + 1];
+  if ((uint32_t)f != h) return;  // almost every entry: alone with its hash
+  const uint32_t ra = (uint32_t)(e >> 32) & (DELJOIN_MAX_WORDS - 1u);
+  const uint64_t va = delete_letter(word_key[ra], n, (uint32_t)(e >> 59));
+  for (uint64_t j = i + 1;;) {
+    const uint32_t rb = (uint32_t)(f >> 32) & (DELJOIN_MAX_WORDS - 1u);
+    if (rb != ra && delete_letter(word_key[rb], n, (uint32_t)(f >> 59)) == va) emit_candidate(cand, cap, counter, ra, rb);
+    if (++j >= D) break;
+    f = sorted[j];
+    if ((uint32_t)f != h) break;
+  }
+}
+
 int stage_neighbours_edit(State &s) {
   const uint64_t U = s.unique;
   const uint32_t n = s.cfg.word_length, d = s.cfg.distance;
@@ -638,9 +701,16 @@ int stage_neighbours_edit(State &s) {
   if (U == 0) return 0;
   if (d > EDIT_MAX_D) throw CudaError{"edit distance > 3 is not supported (two deletion+insertion pairs)"};
   if (n + d + 2 > EDIT_STACK) throw CudaError{"word too long for the edit replay stack"};
-  int k = stage_ensure_lookup(s);
-  Lookup lk = s.lookup();
-  {  // first-level bitmap: 16 to 32 bits per word, a power of two
+  // the shift candidates (b) come from a join on deletion variants at d == 2, from variant probing otherwise
+  // (or when the entries would not fit their 27 + 5 bit payload / 2^32 entries)
+  bool by_join = d == 2 && U < DELJOIN_MAX_WORDS && (uint64_t)U * n < 0xFFFFFFFFull && n >= 2;
+  if (const char *e = std::getenv("HUMID_GPU_EDIT_SHIFTS"))  // testing knob: "probe" or "join"
+    by_join = by_join && e[0] == 'j';
+  int k = 0;
+  Lookup lk{};
+  if (!by_join) {  // key -> rank look-ups: table + fingerprint filter + a first-level bitmap of 16 to 32 bits per word
+    k += stage_ensure_lookup(s);
+    lk = s.lookup();
     int log2_bits = 20;
     while (log2_bits < 33 && (1ull << log2_bits) < 16 * U) log2_bits++;
     const uint64_t words32 = (1ull << log2_bits) / 32;
@@ -702,10 +772,39 @@ int stage_neighbours_edit(State &s) {
       HUMID_CUDA(cudaMemcpyAsync(counter, &pairs, sizeof(uint64_t), cudaMemcpyHostToDevice, s.stream));
       HUMID_CUDA(cudaStreamSynchronize(s.stream));
     }
-    // (b) one deletion + one insertion (a one-letter block shift) and up to d-2 substitutions: variants
-    //     probed against the word table, 2 n (n-1) (1 + 3 n at d = 3) per word (one direction of the shift only)
-    {
-      double shifts = 2.0 * n * (n - 1) * (d >= 3 ? 1.0 + 3.0 * n : 1.0);
+    // (b) one deletion + one insertion (a one-letter block shift) and up to d-2 substitutions: join on deletion
+    //     variants, or variants probed against the word table, 3 (n-1)(n-2)/2 (x (1 + 3 n) at d = 3) per word
+    if (by_join) {
+      s.seed_flag.ensure(U + 1);   // variants per word
+      s.seed_index.ensure(U + 1);  // ... and where they go
+      uint32_t *total = reinterpret_cast<uint32_t *>(s.counters.p + 46);
+      HUMID_CUDA(cudaMemsetAsync(s.counters.p + 46, 0, sizeof(unsigned long long), s.stream));
+      size_t t_gen = s.timer_begin("edit_deletion_variants", U, U * (8 + 4 + 4) + U * (uint64_t)n * 8);
+      deletion_counts_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.word_key.p, U, n, s.seed_flag.p);
+      int launches = 1 + exclusive_scan_u32(s.seed_flag.p, s.seed_index.p, U, total, s.scan_scratch, s.stream);
+      uint64_t D = 0;
+      HUMID_CUDA(cudaMemcpyAsync(&D, s.counters.p + 46, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+      HUMID_CUDA(cudaStreamSynchronize(s.stream));
+      s.join_entries.ensure(D + 1);
+      s.join_entries_out.ensure(D + 1);
+      deletion_variants_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.word_key.p, U, n, s.seed_index.p, s.join_entries.p);
+      s.timer_end(t_gen, launches + 1);
+      k += launches + 1;
+      uint64_t *kb[2] = {s.join_entries.p, s.join_entries_out.p};
+      uint32_t *vb[2] = {nullptr, nullptr};
+      int cur;
+      {
+        Timed t(s, "edit_deletion_sort", D, D * (8 + 4 * 16));
+        launches = 0;
+        cur = radix_sort_u64(kb, vb, D, 32, s.scratch, s.scan_scratch, s.stream, &launches);
+        t.launches = launches;
+        k += launches;
+      }
+      Timed t(s, "edit_deletion_join", D, D * 8);
+      if (D > 1)
+        deletion_join_kernel<<<grid_for(D, 256), 256, 0, s.stream>>>(kb[cur], D, s.word_key.p, n, s.entries.p, cap, counter);
+    } else {
+      double shifts = 1.5 * (n - 1) * (n - 2) * (d >= 3 ? 1.0 + 3.0 * n : 1.0);
       Timed t(s, "edit_candidates", U, (uint64_t)(U * 8.0 * (1.0 + shifts)));
       const uint32_t n_pairs = n >= 3 ? (n - 1) * (n - 2) / 2 : 0u;  // (i, q) with i - q >= 2
       const uint32_t inv_pairs = n_pairs ? (uint32_t)((1ull << 32) / n_pairs + 1) : 0u;

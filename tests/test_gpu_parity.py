@@ -282,6 +282,26 @@ EDIT_REPLAY_CASES = [
 ]
 
 
+@pytest.mark.parametrize("shifts", ["probe", "join"])
+@pytest.mark.parametrize("ci,R,kw", EDIT_REPLAY_CASES,
+                         ids=[f"c{c + 1}_{R}_{'_'.join(f'{k}{v}' for k, v in kw.items())}" for c, R, kw in EDIT_REPLAY_CASES])
+def test_edit_shift_candidates_by_probing_and_by_deletion_join(monkeypatch, ci, R, kw, shifts):
+    """One deletion + one insertion: variants probed through the word table, or (distance 2) words joined on
+    their deletion variants.  Same candidate sets, same lists."""
+    monkeypatch.setenv("HUMID_GPU_EDIT_SHIFTS", shifts)
+    cfg = baseline_config(ci, R, **kw)
+    s = Synth(cfg)
+    chars = s.word_chars()
+    hdr, take = s.layout()
+    seg_take = ([hdr] if hdr else []) + take
+    r = oracle.Result(oracle.pack_words(chars, seg_take), cfg.word_length, cfg.distance, cfg.edit, cfg.maximum)
+    dd = run_gpu(chars, seg_take, cfg.word_length, cfg.distance, cfg.edit, cfg.maximum, batches=2)
+    assert_same_as_oracle(dd, r, R)
+    names = {st["name"] for st in dd.stage_stats()}
+    assert ("edit_deletion_join" in names) == (shifts == "join" and cfg.distance == 2)
+    assert ("edit_candidates" in names) == (shifts == "probe" or cfg.distance != 2)
+
+
 @pytest.mark.parametrize("heavy_from", [3, 16])
 @pytest.mark.parametrize("task_cap", [0, 2, 7, 96])
 @pytest.mark.parametrize("ci,R,kw", EDIT_REPLAY_CASES,
