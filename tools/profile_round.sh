@@ -16,7 +16,7 @@ ncu --set full --clock-control none --import-source on \
 echo full rc=$?
 # the other paths: edit distance 2 (configs[3]), Hamming 2 by block pairs (configs[2]), words of 36 letters
 python tools/stage_table.py 3 20000000 1 > gpurun_out/${tag}_stages_c4.log 2>&1 || exit 1
-ncu --set full --clock-control none --import-source on -k "regex:^(edit_replay_tasks|edit_candidates_shift|edit_replay_single)" -c 3 \
+ncu --set full --clock-control none --import-source on -k "regex:^(edit_replay_tasks|deletion_join|deletion_variants|edit_replay_single)" -c 4 \
     -o gpurun_out/${tag}_edit python tools/stage_table.py 3 20000000 1 > gpurun_out/${tag}_ncu3.log 2>&1
 echo edit rc=$?
 python tools/stage_table.py 1 50000000 1 36 > gpurun_out/${tag}_stages_n36.log 2>&1 || exit 1
