@@ -734,29 +734,17 @@ int stage_neighbours_edit(State &s) {
     // (a) substitutions only = every pair within Hamming distance d: block join without the
     //     dominance rule (neighbours.cu), both directions of a pair become candidates
     {
-      int lo_bit[HAM_MAX_D + 1], hi_bit[HAM_MAX_D + 1];
-      const Blocks B = make_blocks(n, d, lo_bit, hi_bit);
+      const JoinPlan P = make_join_plan(n, d);  // d + 1 blocks, or pairs of four blocks at d == 2
       s.key_alt.ensure(U + 1);
       s.entries_alt.ensure(U + 1);
       s.entry_val.ensure(U + 1);
       s.entry_val_alt.ensure(U + 1);
-      for (uint32_t b = 0; b <= d; b++) {
-        const uint64_t *keys = s.word_key.p;
-        const uint32_t *rank = nullptr;
-        if (b > 0 && hi_bit[b] > lo_bit[b]) {
-          uint64_t *kb[2] = {s.key_alt.p, s.entries_alt.p};
-          uint32_t *vb[2] = {s.entry_val.p, s.entry_val_alt.p};
-          int launches = 0;
-          const uint64_t passes = (uint64_t)(hi_bit[b] - lo_bit[b] + 7) / 8;
-          Timed t(s, "join_sort", U, U * (8 + (8 + 12) + (passes - 1) * 24));
-          int cur = radix_sort_bits_indexed(s.word_key.p, kb, vb, U, lo_bit[b], hi_bit[b], s.scratch, s.stream, &launches);
-          t.launches = launches;
-          k += launches;
-          keys = kb[cur];
-          rank = vb[cur];
-        }
+      for (uint32_t b = 0; b < P.B.n_blocks; b++) {
+        const uint64_t *keys;
+        const uint32_t *rank;
+        k += join_plan_order(s, P, b, U, keys, rank);
         Timed t(s, "edit_candidates_join", U, U * (8 + 8 + (rank ? 4 : 0)));
-        launch_hamming_join(s, JOIN_CANDIDATES, keys, rank, U, B, b, JOIN_NO_CAP, s.entries.p, cap / 2, counter, nullptr,
+        launch_hamming_join(s, JOIN_CANDIDATES, keys, rank, U, P.B, b, JOIN_NO_CAP, s.entries.p, cap / 2, counter, nullptr,
                             0u, nullptr, nullptr);
         k++;
       }

@@ -449,13 +449,7 @@ Blocks make_blocks(uint32_t n, uint32_t d, int lo_bit[], int hi_bit[]) {
 //     (about one word at 20 M words of 24 letters) instead of a third (about 300): at 50 M tuples of
 //     configs[2] the three joins took 5.7 ms each.  A pair of blocks that contains the prefix block only
 //     needs the other block sorted: inside a group of that block, rank order keeps equal prefixes together.
-struct JoinPlan {
-  Blocks B;
-  int n_sorts[HAM_MAX_D + 1];
-  int lo_bit[HAM_MAX_D + 1][2], hi_bit[HAM_MAX_D + 1][2];
-};
-
-static JoinPlan make_join_plan(uint32_t n, uint32_t d) {
+JoinPlan make_join_plan(uint32_t n, uint32_t d) {
   JoinPlan P{};
   bool combos = d == 2 && n >= 8;
   if (const char *e = std::getenv("HUMID_GPU_JOIN_SCHEME"))  // testing knob: "blocks" or "combos"
@@ -500,6 +494,34 @@ static JoinPlan make_join_plan(uint32_t n, uint32_t d) {
   return P;
 }
 
+// The words in the order of entry b of the plan: keys (and their ranks; nullptr = the order is rank order).
+// Uses key_alt / entries_alt / entry_val / entry_val_alt (U + 1 elements each, ensured by the caller).
+int join_plan_order(State &s, const JoinPlan &P, uint32_t b, uint64_t U, const uint64_t *&keys, const uint32_t *&rank) {
+  keys = s.word_key.p;
+  rank = nullptr;
+  if (P.n_sorts[b] == 0) return 0;
+  uint64_t *kb[2] = {s.key_alt.p, s.entries_alt.p};
+  uint32_t *vb[2] = {s.entry_val.p, s.entry_val_alt.p};
+  int launches = 0;
+  uint64_t passes = (uint64_t)(P.hi_bit[b][0] - P.lo_bit[b][0] + 7) / 8;  // first pass reads keys only (rank = position)
+  if (P.n_sorts[b] > 1) passes += (uint64_t)(P.hi_bit[b][1] - P.lo_bit[b][1] + 7) / 8 + 1;  // + its own histogram read
+  Timed t(s, "join_sort", U, U * (8 + (8 + 12) + (passes - 1) * 24));
+  const int cur = radix_sort_bits_indexed(s.word_key.p, kb, vb, U, P.lo_bit[b][0], P.hi_bit[b][0], s.scratch, s.stream,
+                                          &launches);
+  keys = kb[cur];
+  rank = vb[cur];
+  if (P.n_sorts[b] > 1) {  // then, stably, by the more significant range: the first pass writes the free pair
+    uint64_t *kb2[2] = {kb[1 - cur], kb[cur]};
+    uint32_t *vb2[2] = {vb[1 - cur], vb[cur]};
+    const int cur2 = radix_sort_bits_pairs(kb[cur], vb[cur], kb2, vb2, U, P.lo_bit[b][1], P.hi_bit[b][1], s.scratch,
+                                           s.stream, &launches);
+    keys = kb2[cur2];
+    rank = vb2[cur2];
+  }
+  t.launches = launches;
+  return launches;
+}
+
 // HUMID_GPU_JOIN_CAP: group size above which the join hands a group to the probe path (testing knob)
 static uint32_t join_group_cap(uint32_t d) {
   if (const char *e = std::getenv("HUMID_GPU_JOIN_CAP")) {
@@ -538,31 +560,9 @@ int stage_neighbours_hamming(State &s) {
     HUMID_CUDA(cudaMemsetAsync(s.deg.p, 0, U * sizeof(uint32_t), s.stream));
     HUMID_CUDA(cudaMemsetAsync(s.word_flags.p, 0, U * sizeof(uint32_t), s.stream));
     for (uint32_t b = 0; b < B.n_blocks; b++) {
-      const uint64_t *keys = s.word_key.p;
-      const uint32_t *rank = nullptr;
-      if (P.n_sorts[b] > 0) {
-        uint64_t *kb[2] = {s.key_alt.p, s.entries_alt.p};
-        uint32_t *vb[2] = {s.entry_val.p, s.entry_val_alt.p};
-        int launches = 0;
-        uint64_t passes = (uint64_t)(P.hi_bit[b][0] - P.lo_bit[b][0] + 7) / 8;  // first pass reads keys only (rank = position)
-        if (P.n_sorts[b] > 1) passes += (uint64_t)(P.hi_bit[b][1] - P.lo_bit[b][1] + 7) / 8 + 1;  // + its own histogram read
-        Timed t(s, "join_sort", U, U * (8 + (8 + 12) + (passes - 1) * 24));
-        int cur = radix_sort_bits_indexed(s.word_key.p, kb, vb, U, P.lo_bit[b][0], P.hi_bit[b][0], s.scratch, s.stream,
-                                          &launches);
-        if (P.n_sorts[b] > 1) {  // then, stably, by the more significant range: the first pass writes the free pair
-          uint64_t *kb2[2] = {kb[1 - cur], kb[cur]};
-          uint32_t *vb2[2] = {vb[1 - cur], vb[cur]};
-          const int cur2 = radix_sort_bits_pairs(kb[cur], vb[cur], kb2, vb2, U, P.lo_bit[b][1], P.hi_bit[b][1], s.scratch,
-                                                 s.stream, &launches);
-          keys = kb2[cur2];
-          rank = vb2[cur2];
-        } else {
-          keys = kb[cur];
-          rank = vb[cur];
-        }
-        t.launches = launches;
-        k += launches;
-      }
+      const uint64_t *keys;
+      const uint32_t *rank;
+      k += join_plan_order(s, P, b, U, keys, rank);
       // the word, its successor in the group (the walk ends there for almost every word) and the pair out
       static const char *const join_names[HAM_MAX_D + 1] = {"join_hamming_b0", "join_hamming_b1", "join_hamming_b2",
                                                             "join_hamming_b3", "join_hamming_b4", "join_hamming_b5",

@@ -244,6 +244,15 @@ struct Blocks {
   uint32_t n_blocks;
   uint64_t mask[HAM_MAX_D + 1];  // bits of block b (block 0 = first letters = highest bits)
 };
+// what the single-GPU searches join on (neighbours.cu: make_join_plan)
+struct JoinPlan {
+  Blocks B;
+  int n_sorts[HAM_MAX_D + 1];
+  int lo_bit[HAM_MAX_D + 1][2], hi_bit[HAM_MAX_D + 1][2];
+};
+
+JoinPlan make_join_plan(uint32_t n, uint32_t d);
+int join_plan_order(State &s, const JoinPlan &P, uint32_t b, uint64_t U, const uint64_t *&keys, const uint32_t *&rank);
 constexpr int JOIN_PAIRS_DEG = 0, JOIN_DIRECTED = 1, JOIN_CANDIDATES = 2;
 constexpr uint32_t JOIN_NO_CAP = 0xFFFFFFFFu;
 Blocks make_blocks(uint32_t n, uint32_t d, int lo_bit[], int hi_bit[]);  // arrays of HAM_MAX_D + 1
