@@ -1,5 +1,5 @@
-"""BASELINE.json sizes (configs[1] and configs[2] at 50 M tuples): too large for the oracle, so the
-result is checked through properties that hold at any size."""
+"""BASELINE.json sizes (configs[1] — also at -n 36 — and configs[2] at 50 M tuples, configs[3] at 20 M): too
+large for the oracle, so the result is checked through properties that hold at any size."""
 import numpy as np
 import pytest
 import torch
@@ -9,7 +9,7 @@ from humid_b200.synth import HashSynth, baseline_config
 
 pytestmark = pytest.mark.gpu
 
-R = 50_000_000
+CASES = [(1, 50_000_000, {}), (2, 50_000_000, {}), (1, 50_000_000, dict(word_length=36)), (3, 20_000_000, {})]
 
 
 def run(cfg, chars, batches, expected=0):
@@ -31,9 +31,9 @@ def hist_dict(dd, which):
     return k.astype(np.int64), v.astype(np.int64)
 
 
-@pytest.mark.parametrize("ci", [1, 2])
-def test_properties_at_full_size(ci):
-    cfg = baseline_config(ci, R)
+@pytest.mark.parametrize("ci,R,kw", CASES, ids=["c2", "c3", "c2_n36", "c4_edit2"])
+def test_properties_at_full_size(ci, R, kw):
+    cfg = baseline_config(ci, R, **kw)
     chars = HashSynth(cfg).word_chars(0, R, device=torch.device("cuda", 0))
     dd = run(cfg, chars, batches=1, expected=R)
     c = dd.counts()
@@ -63,3 +63,29 @@ def test_properties_at_full_size(ci):
     assert dd2.stats_text() == dd.stats_text()
     dd.close()
     dd2.close()
+
+
+ALTERNATIVES = [  # (config, tuples, environment of the second run)
+    (2, 50_000_000, dict(HUMID_GPU_JOIN_SCHEME="blocks")),                       # three blocks instead of block pairs
+    (3, 20_000_000, dict(HUMID_GPU_EDIT_SHIFTS="probe", HUMID_GPU_EDIT_TASKS="0",  # variant probing + plain walk of the
+                         HUMID_GPU_JOIN_SCHEME="blocks")),                          # recursion instead of joins + counting
+]
+
+
+@pytest.mark.parametrize("ci,R,env", ALTERNATIVES, ids=["c3_blocks_vs_pairs", "c4_probe_walk_vs_join_count"])
+def test_independent_paths_agree_at_full_size(monkeypatch, ci, R, env):
+    """Every search has two implementations (forced through the testing knobs); at BASELINE.json's sizes, where
+    the oracle cannot follow, they must produce the same reads, ids and statistics files."""
+    cfg = baseline_config(ci, R)
+    chars = HashSynth(cfg).word_chars(0, R, device=torch.device("cuda", 0))
+    dd = run(cfg, chars, batches=1, expected=R)
+    ref = (dd.counts(), dd.keep_mask().copy(), dd.cluster_ids().copy(), dd.stats_text())
+    dd.close()
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    dd = run(cfg, chars, batches=3)
+    assert dd.counts() == ref[0]
+    assert np.array_equal(dd.keep_mask(), ref[1])
+    assert np.array_equal(dd.cluster_ids(), ref[2])
+    assert dd.stats_text() == ref[3]
+    dd.close()
