@@ -13,6 +13,7 @@
 #pragma once
 #include <zlib.h>
 
+#include <cstdint>
 #include <cstdio>
 #include <cstring>
 #include <iostream>
@@ -34,14 +35,18 @@ struct RecordView {
 
 class BlockReader {
  public:
-  explicit BlockReader(const std::string &path, size_t block = 16u << 20) : path_(path), buf_(block) {
+  // start: byte offset to begin at (plain files only; it must be the start of a line)
+  explicit BlockReader(const std::string &path, size_t block = 16u << 20, uint64_t start = 0)
+      : path_(path), buf_(block), base_(start) {
     if (ends_with(path, ".gz")) {
+      if (start) error_exit("cannot seek in a compressed file: " + path);
       gz_ = gzopen(path.c_str(), "rb");
       if (!gz_) error_exit("Failed to open file: " + path);
       gzbuffer(gz_, 1u << 20);
     } else {
       fp_ = std::fopen(path.c_str(), "rb");
       if (!fp_) error_exit("Failed to open file: " + path);
+      if (start && fseeko(fp_, (off_t)start, SEEK_SET) != 0) error_exit("Failed to seek in file: " + path);
     }
   }
   ~BlockReader() {
@@ -50,6 +55,10 @@ class BlockReader {
   }
   BlockReader(const BlockReader &) = delete;
   BlockReader &operator=(const BlockReader &) = delete;
+
+  // Byte offset (in the uncompressed data) of the name line of the record read last: a reader started
+  // there sees the same records from that one on.
+  uint64_t offset_of(const RecordView &r) const { return base_ + (uint64_t)(r.name.p - buf_.data()); }
 
   // false at end of input (or at a malformed record).  The views stay valid until the next call.
   bool read(RecordView &r) {
@@ -120,6 +129,7 @@ class BlockReader {
     if (mark_ > 0) {
       std::memmove(buf_.data(), buf_.data() + mark_, end_ - mark_);
       end_ -= mark_;
+      base_ += mark_;
       mark_ = 0;
     }
     if (end_ == buf_.size()) buf_.resize(buf_.size() * 2);  // one record longer than the block
@@ -141,6 +151,7 @@ class BlockReader {
 
   std::string path_;
   std::vector<char> buf_;
+  uint64_t base_ = 0;          // offset of buf_[0] in the (uncompressed) data
   size_t mark_ = 0, end_ = 0;  // [mark_, end_) = bytes not yet handed out
   bool finished_ = false;      // the file has no more bytes
   bool drained_ = false;       // ... and the parser knows: the last line ends at end_

@@ -15,10 +15,13 @@
 // (host/fastq_block.h) and writes its share of every word straight into a page-locked batch
 // buffer; the main thread hands full batches to humid_gpu_add_batch, which uploads them while the
 // next batch is being parsed and the previous one is counted on the device.  The output passes
-// run one thread per file as well.
+// (host/fastq_rewrite.h) cut every plain file into chunks at record offsets noted
+// during ingest and parse / write them with several threads per file.
 #include <sys/stat.h>
 
+#include <chrono>
 #include <condition_variable>
+#include <cstdlib>
 #include <ctime>
 #include <fstream>
 #include <memory>
@@ -28,6 +31,7 @@
 #include "../include/humid_gpu.h"
 #include "fastq_block.h"
 #include "fastq_io.h"
+#include "fastq_rewrite.h"
 
 using namespace humid_host;
 using std::string;
@@ -78,12 +82,20 @@ bool parse(int argc, char **argv, Options &o) {
   return !o.files.empty();
 }
 
+// HUMID_TIMING=1: phase times in milliseconds on stderr (the log keeps the reference's whole seconds)
+std::chrono::steady_clock::time_point phase_start;
+const char *phase_name = "";
 time_t start_message(std::ofstream &log, const char *msg) {  // src/log.cc:4-9
   log << msg << "... ";
   log.flush();
+  phase_name = msg;
+  phase_start = std::chrono::steady_clock::now();
   return time(nullptr);
 }
 void end_message(std::ofstream &log, time_t start) {  // src/log.cc:11-15
+  if (std::getenv("HUMID_TIMING"))
+    std::cerr << phase_name << ": "
+              << std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - phase_start).count() << " ms\n";
   time_t s = static_cast<time_t>(difftime(time(nullptr), start));
   log << "done. (" << s / 60 << 'm' << s % 60 << "s)\n";
   log.flush();
@@ -137,7 +149,7 @@ Layout pre_compute(const vector<string> &files, size_t word_length) {
 // ---- pass 1: tuples of all files in lock step (readFiles / readFastq_, src/fastq.cc:37-47,
 // :96-114): the tuple stream ends as soon as any file runs out --------------------------------
 constexpr size_t BATCH = 1u << 20;  // tuples per upload
-constexpr int N_SLOTS = 3;
+constexpr int N_SLOTS = 8;  // batches the readers may run ahead: they start while the device is still being brought up
 
 struct Slot {
   uint8_t *chars = nullptr;     // BATCH x word_length, row-major; file i fills its own columns
@@ -155,6 +167,7 @@ struct Ingest {
   size_t n = 0, S = 0;          // word length, segments
   vector<size_t> seg_off;       // first column of a segment
   Layout L;
+  vector<vector<uint64_t>> chunk_offset;  // per file: byte offset of every REWRITE_CHUNK-th record (pass 2 starts there)
 };
 
 // file i: segment (header UMI ? i + 1 : i); file 0 also fills segment 0 from its headers
@@ -174,6 +187,7 @@ void ingest_file(Ingest &g, const string &path, size_t file) {
     size_t m = 0;
     for (; m < BATCH; m++) {
       if (!reader.read(rec)) { ended = true; break; }
+      if (m % REWRITE_CHUNK == 0) g.chunk_offset[file].push_back(reader.offset_of(rec));  // BATCH is a multiple of it
       // getNucleotides (src/fastq.cc:116-144) WITHOUT the padding / validation: the device applies
       // makeStringSize_ and the ACGT filter from (chars, seg_len)
       uint8_t *row = s.chars + m * g.n;
@@ -195,20 +209,6 @@ void ingest_file(Ingest &g, const string &path, size_t file) {
     s.rows[file] = m;
     s.done++;
     g.cv.notify_all();
-  }
-}
-
-// ---- pass 2: every file is filtered / annotated by its own thread -----------------------------
-void rewrite_file(const string &in_path, const string &out_path, uint64_t total, const uint64_t *keep,
-                  const uint32_t *ids) {
-  BlockReader reader(in_path);
-  Writer out(out_path);
-  RecordView rec;
-  string suffix;
-  for (uint64_t t = 0; t < total && reader.read(rec); t++) {
-    if (keep && !(keep[t >> 6] >> (t & 63) & 1)) continue;
-    if (ids) suffix = ":" + std::to_string(ids[t]);
-    out.write_view(rec.name, rec.seq, rec.strand, rec.qual, suffix);
   }
 }
 
@@ -264,24 +264,37 @@ int main(int argc, char **argv) {
   cfg.n_segments = (uint32_t)seg_take.size();
   for (size_t i = 0; i < seg_take.size(); i++) cfg.seg_take[i] = (uint32_t)seg_take[i];
   cfg.expected_tuples = estimate_tuples(opt.files.front());
+  // Bringing the device up (CUDA context, first allocations) takes about a second: it runs beside the readers,
+  // which fill ordinary page-aligned buffers meanwhile; the buffers are page-locked once the handle exists.
   humid_gpu *gpu = nullptr;
-  check(nullptr, humid_gpu_create(&cfg, &gpu), "humid_gpu_create");
+  int create_rc = HUMID_GPU_OK;
+  std::thread creator([&] {
+    const auto c0 = std::chrono::steady_clock::now();
+    create_rc = humid_gpu_create(&cfg, &gpu);
+    if (std::getenv("HUMID_TIMING"))
+      std::cerr << "humid_gpu_create (CUDA context, beside the readers): "
+                << std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - c0).count() << " ms\n";
+  });
 
   t0 = start_message(log, "Reading data");
   uint64_t total = 0;
+  vector<vector<uint64_t>> chunk_offset;
   {
     Ingest g;
+    g.chunk_offset.assign(F, {});
     g.n = opt.word_length;
     g.S = seg_take.size();
     g.L = L;
     size_t at = 0;
     for (size_t t : seg_take) { g.seg_off.push_back(at); at += t; }
+    auto page_aligned = [](size_t bytes) {
+      void *p = nullptr;
+      if (posix_memalign(&p, 4096, (bytes + 4095) / 4096 * 4096) != 0) error_exit("out of memory");
+      return p;
+    };
     for (int j = 0; j < N_SLOTS; j++) {
-      void *c = nullptr, *l = nullptr;
-      check(gpu, humid_gpu_host_alloc(gpu, BATCH * g.n, &c), "humid_gpu_host_alloc");
-      check(gpu, humid_gpu_host_alloc(gpu, BATCH * g.S * sizeof(uint16_t), &l), "humid_gpu_host_alloc");
-      g.slots[j].chars = static_cast<uint8_t *>(c);
-      g.slots[j].seg_len = static_cast<uint16_t *>(l);
+      g.slots[j].chars = static_cast<uint8_t *>(page_aligned(BATCH * g.n));
+      g.slots[j].seg_len = static_cast<uint16_t *>(page_aligned(BATCH * g.S * sizeof(uint16_t)));
       g.slots[j].batch = (uint64_t)j;
       g.slots[j].rows.assign(F, 0);
     }
@@ -292,6 +305,14 @@ int main(int argc, char **argv) {
       {
         std::unique_lock<std::mutex> lk(g.mu);
         g.cv.wait(lk, [&] { return s.done == F; });
+      }
+      if (creator.joinable()) {  // first batch: the device must be there now
+        creator.join();
+        check(nullptr, create_rc, "humid_gpu_create");
+        for (int j = 0; j < N_SLOTS; j++) {
+          check(gpu, humid_gpu_host_register(gpu, g.slots[j].chars, BATCH * g.n), "humid_gpu_host_register");
+          check(gpu, humid_gpu_host_register(gpu, g.slots[j].seg_len, BATCH * g.S * sizeof(uint16_t)), "humid_gpu_host_register");
+        }
       }
       size_t m = BATCH;
       for (size_t r : s.rows) m = r < m ? r : m;
@@ -305,9 +326,12 @@ int main(int argc, char **argv) {
       if (g.stop) break;
     }
     for (std::thread &t : readers) t.join();
+    chunk_offset.swap(g.chunk_offset);
     for (int j = 0; j < N_SLOTS; j++) {
-      humid_gpu_host_free(gpu, g.slots[j].chars);
-      humid_gpu_host_free(gpu, g.slots[j].seg_len);
+      humid_gpu_host_unregister(gpu, g.slots[j].chars);
+      humid_gpu_host_unregister(gpu, g.slots[j].seg_len);
+      std::free(g.slots[j].chars);
+      std::free(g.slots[j].seg_len);
     }
   }
   end_message(log, t0);
@@ -322,6 +346,9 @@ int main(int argc, char **argv) {
   end_message(log, t0);
 
   make_dirs(opt.dir_name);
+  // pass 2 (host/fastq_rewrite.h): one writer per file, each with its share of the host's threads
+  const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+  const unsigned threads_per_file = std::max(1u, std::min(8u, hw / (unsigned)F));
 
   // ---- writeFiltered (src/humid.cc:203-241): the keep bit of a tuple decides for all its files --
   if (opt.filter) {
@@ -329,8 +356,9 @@ int main(int argc, char **argv) {
     vector<uint64_t> keep((total + 63) / 64 + 1);
     check(gpu, humid_gpu_keep_mask(gpu, 0, total, keep.data()), "humid_gpu_keep_mask");
     vector<std::thread> writers;
-    for (const string &f : opt.files)
-      writers.emplace_back(rewrite_file, f, make_file_name(f, opt.dir_name, "dedup"), total, keep.data(), nullptr);
+    for (size_t i = 0; i < F; i++)
+      writers.emplace_back(rewrite_file_parallel, opt.files[i], make_file_name(opt.files[i], opt.dir_name, "dedup"), total,
+                           keep.data(), nullptr, std::cref(chunk_offset[i]), threads_per_file);
     for (std::thread &t : writers) t.join();
     end_message(log, t0);
   }
@@ -344,8 +372,9 @@ int main(int argc, char **argv) {
       check(gpu, humid_gpu_cluster_ids(gpu, lo, m, ids.data() + lo), "humid_gpu_cluster_ids");
     }
     vector<std::thread> writers;
-    for (const string &f : opt.files)
-      writers.emplace_back(rewrite_file, f, make_file_name(f, opt.dir_name, "annotated"), total, nullptr, ids.data());
+    for (size_t i = 0; i < F; i++)
+      writers.emplace_back(rewrite_file_parallel, opt.files[i], make_file_name(opt.files[i], opt.dir_name, "annotated"),
+                           total, nullptr, ids.data(), std::cref(chunk_offset[i]), threads_per_file);
     for (std::thread &t : writers) t.join();
     end_message(log, t0);
   }
@@ -377,6 +406,10 @@ int main(int argc, char **argv) {
   }
 
   log.close();
+  phase_start = std::chrono::steady_clock::now();
   humid_gpu_destroy(gpu);
+  if (std::getenv("HUMID_TIMING"))
+    std::cerr << "humid_gpu_destroy: "
+              << std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - phase_start).count() << " ms\n";
   return 0;
 }

@@ -27,7 +27,7 @@ EXPORTS = [
     "humid_gpu_histogram", "humid_gpu_keep_mask", "humid_gpu_cluster_ids", "humid_gpu_debug_words",
     "humid_gpu_debug_neighbours", "humid_gpu_debug_clusters", "humid_gpu_stage_stats", "humid_gpu_stream",
     "humid_gpu_debug_sort_pairs", "humid_gpu_debug_partition", "humid_gpu_host_alloc", "humid_gpu_host_free",
-    "humid_gpu_debug_words_hi",
+    "humid_gpu_debug_words_hi", "humid_gpu_host_register", "humid_gpu_host_unregister",
 ]
 
 
@@ -85,6 +85,8 @@ def load_library() -> C.CDLL:
     L.humid_gpu_stream.restype = vp
     L.humid_gpu_host_alloc.argtypes = [vp, C.c_size_t, P(vp)]
     L.humid_gpu_host_free.argtypes = [vp, vp]
+    L.humid_gpu_host_register.argtypes = [vp, vp, C.c_size_t]
+    L.humid_gpu_host_unregister.argtypes = [vp, vp]
     L.humid_gpu_debug_sort_pairs.argtypes = [vp, vp, vp, u64, C.c_int, C.c_int, vp, vp]
     L.humid_gpu_debug_partition.argtypes = [vp, C.c_int, vp, u64, u64, u32, vp, u32, vp, vp, vp]
     _lib = L

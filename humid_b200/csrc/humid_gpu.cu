@@ -141,6 +141,20 @@ int humid_gpu_host_free(humid_gpu *h, void *p) {
   return guarded(h, [&] { HUMID_CUDA(cudaFreeHost(p)); });
 }
 
+int humid_gpu_host_register(humid_gpu *h, void *p, size_t bytes) {
+  if (!h || !p) return HUMID_GPU_ERR_ARG;
+  return guarded(h, [&] {
+    HUMID_CUDA(cudaSetDevice(h->s.device));
+    HUMID_CUDA(cudaHostRegister(p, bytes, cudaHostRegisterDefault));
+  });
+}
+
+int humid_gpu_host_unregister(humid_gpu *h, void *p) {
+  if (!h) return HUMID_GPU_ERR_ARG;
+  if (!p) return HUMID_GPU_OK;
+  return guarded(h, [&] { HUMID_CUDA(cudaHostUnregister(p)); });
+}
+
 static int add_batch_impl(humid_gpu *h, const uint8_t *chars, const uint16_t *seg_len, uint64_t first, uint64_t n,
                           bool on_device) {
   if (!h) return HUMID_GPU_ERR_ARG;

@@ -83,6 +83,10 @@ void *humid_gpu_stream(humid_gpu *h);
  * works too, only slower.  Nothing in the reference corresponds to this. */
 int humid_gpu_host_alloc(humid_gpu *h, size_t bytes, void **out);
 int humid_gpu_host_free(humid_gpu *h, void *p);
+/* The same for memory the caller already owns (page-aligned): page-locks it in place, so a host can fill its
+ * buffers while humid_gpu_create is still bringing the device up and lock them afterwards. */
+int humid_gpu_host_register(humid_gpu *h, void *p, size_t bytes);
+int humid_gpu_host_unregister(humid_gpu *h, void *p);
 
 /* Pass 1 — replaces `makeWord` + `trie.add` in readData (src/humid.cc:92-99; makeWord
  * src/fastq.cc:146-161, getNucleotides :116-144, makeStringSize_ :57-66, Trie::add

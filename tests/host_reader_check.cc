@@ -5,6 +5,7 @@
 #include <iostream>
 
 #include "../host/fastq_block.h"
+#include "../host/fastq_rewrite.h"
 
 using namespace humid_host;
 
@@ -12,6 +13,33 @@ int main(int argc, char **argv) {
   if (argc < 3) return 2;
   std::string mode = argv[1], path = argv[2];
   size_t n = 0;
+  if (mode == "rewrite") {  // rewrite <in> <out one thread> <out threads> <seed> <annotate 0|1> <threads>
+    // pass 1 as the executable does it: count the records, note the offset of every REWRITE_CHUNK-th
+    std::vector<uint64_t> offsets;
+    uint64_t total = 0;
+    {
+      BlockReader reader(path, 64);
+      RecordView r;
+      while (reader.read(r)) {
+        if (total % REWRITE_CHUNK == 0) offsets.push_back(reader.offset_of(r));
+        total++;
+      }
+    }
+    uint64_t x = std::strtoull(argv[5], nullptr, 10) * 0x9E3779B97F4A7C15ull + 1;
+    std::vector<uint64_t> keep((total + 63) / 64 + 1);
+    std::vector<uint32_t> ids(total + 1);
+    for (uint64_t t = 0; t < total; t++) {
+      x ^= x << 13; x ^= x >> 7; x ^= x << 17;
+      if (x % 3 == 0) keep[t >> 6] |= 1ull << (t & 63);
+      ids[t] = (uint32_t)(x >> 40);
+    }
+    const bool annotate = std::atoi(argv[6]) != 0;
+    rewrite_file(path, argv[3], total, annotate ? nullptr : keep.data(), annotate ? ids.data() : nullptr);
+    rewrite_file_parallel(path, argv[4], total, annotate ? nullptr : keep.data(), annotate ? ids.data() : nullptr, offsets,
+                          (unsigned)std::atoi(argv[7]));
+    std::cout << "records " << total << " chunks " << offsets.size() << "\n";
+    return 0;
+  }
   if (mode == "old") {
     FastqReader reader(path);
     Record r;

@@ -14,7 +14,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 @pytest.fixture(scope="module")
 def checker(tmp_path_factory):
     exe = str(tmp_path_factory.mktemp("bin") / "host_reader_check")
-    subprocess.run(["g++", "-O1", "-std=c++17", "-o", exe, os.path.join(HERE, "host_reader_check.cc"), "-lz"], check=True)
+    subprocess.run(["g++", "-O1", "-std=c++17", "-pthread", "-DHUMID_REWRITE_CHUNK=7", "-o", exe,
+                    os.path.join(HERE, "host_reader_check.cc"), "-lz"], check=True)
     return exe
 
 
@@ -58,3 +59,21 @@ def test_block_reader_matches_line_reader(checker, tmp_path, case, gz):
         assert (b"different length" in got.stderr) == (b"different length" in ref.stderr)
     if case in ("plain", "crlf"):
         assert ref.stdout.endswith(b"records 300\n")
+
+
+@pytest.mark.parametrize("case", ["plain", "crlf", "mixed_eol", "junk_between", "no_final_newline", "long_lines", "empty",
+                                  "truncated_record"])
+@pytest.mark.parametrize("annotate", [0, 1])
+def test_parallel_rewrite_matches_one_thread(checker, tmp_path, case, annotate):
+    """Pass 2 cut into chunks of 7 records over 1..5 threads writes the bytes of the one-thread pass
+    (host/fastq_rewrite.h), whatever the line endings and junk between records."""
+    data = CASES[case](np.random.default_rng(len(case) + 3))
+    path = str(tmp_path / "in.fastq")
+    with open(path, "wb") as f:
+        f.write(data)
+    for threads in (1, 2, 5):
+        a, b = str(tmp_path / "one.fastq"), str(tmp_path / f"par{threads}.fastq")
+        subprocess.run([checker, "rewrite", path, a, b, str(threads + 10 * annotate), str(annotate), str(threads)], check=True)
+        assert open(a, "rb").read() == open(b, "rb").read(), (case, threads)
+    if case == "plain" and annotate:
+        assert open(a, "rb").read().count(b"\n") == 4 * 300  # every record, with ":id" behind its name

@@ -3,6 +3,8 @@ python tools/cli_bench.py <config index> <tuples> [extra humid args...]"""
 import os
 import subprocess
 import sys
+
+sys.path.insert(0, __import__("os").path.dirname(__import__("os").path.dirname(__import__("os").path.abspath(__file__))))
 import tempfile
 import time
 

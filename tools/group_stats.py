@@ -1,5 +1,7 @@
 """Group-size statistics of the Hamming block join on the bench workload (diagnostic)."""
 import sys
+
+sys.path.insert(0, __import__("os").path.dirname(__import__("os").path.dirname(__import__("os").path.abspath(__file__))))
 import numpy as np
 import torch
 from humid_b200 import api
