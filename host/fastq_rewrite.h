@@ -7,13 +7,21 @@
 // into those chunks and several threads per file parse them side by side, each into its own buffer.  A
 // chunk's place in the output is known as soon as the chunks before it have been parsed, so the buffers
 // are written with pwrite concurrently.  The bytes written are those of the one-thread pass (same parser,
-// same serialisation); compressed inputs (no seeking) and compressed outputs keep the one-thread pass.
+// same serialisation).
+//
+// Compressed files: a .gz input cannot be entered in the middle, so one thread inflates and parses it and hands
+// the text of every chunk to the pool; a .gz output is written as one gzip member per chunk (the reference's
+// writer produces multi-member files too, lib/fastp/src/writer.cpp:105-128), the members deflated side by
+// side at the reference's level 4 — the inflated bytes are those of the one-thread pass.
 #pragma once
 #include <fcntl.h>
 #include <unistd.h>
 
+#include <zlib.h>
+
 #include <atomic>
 #include <condition_variable>
+#include <deque>
 #include <mutex>
 #include <thread>
 
@@ -51,24 +59,156 @@ inline void rewrite_file(const std::string &in_path, const std::string &out_path
   }
 }
 
+// One gzip member holding `in` (level 4: lib/fastp/src/options.cpp:15).
+inline void gzip_member(const std::string &in, std::string &out) {
+  z_stream zs{};
+  if (deflateInit2(&zs, 4, Z_DEFLATED, 15 + 16, 8, Z_DEFAULT_STRATEGY) != Z_OK) error_exit("deflateInit2 failed");
+  out.resize(deflateBound(&zs, in.size()) + 32);
+  zs.next_in = reinterpret_cast<Bytef *>(const_cast<char *>(in.data()));
+  zs.avail_in = (uInt)in.size();
+  zs.next_out = reinterpret_cast<Bytef *>(&out[0]);
+  zs.avail_out = (uInt)out.size();
+  if (deflate(&zs, Z_FINISH) != Z_STREAM_END) error_exit("deflate failed");
+  out.resize(zs.total_out);
+  deflateEnd(&zs);
+}
+
+// Output file whose pieces arrive from several threads: piece c goes behind pieces [0, c).  A piece's place is
+// known once the pieces before it have been placed, so only the bookkeeping is ordered, not the writes.
+class OrderedOutput {
+ public:
+  explicit OrderedOutput(const std::string &path) : path_(path), gz_(ends_with(path, ".gz")) {
+    fd_ = open(path.c_str(), O_WRONLY | O_CREAT | O_TRUNC, 0666);
+    if (fd_ < 0) error_exit("Failed to write: " + path);
+  }
+  OrderedOutput(const OrderedOutput &) = delete;
+  OrderedOutput &operator=(const OrderedOutput &) = delete;
+  // text of piece c (deflated here when the file is a .gz); `scratch` is the caller's reusable buffer
+  void put(uint64_t c, const std::string &text, std::string &scratch) {
+    const std::string *data = &text;
+    if (gz_) {
+      if (text.empty()) scratch.clear();  // no empty members in the middle of the file
+      else gzip_member(text, scratch);
+      data = &scratch;
+    }
+    uint64_t at;
+    {
+      std::unique_lock<std::mutex> lk(mu_);
+      cv_.wait(lk, [&] { return placed_ == c; });
+      at = end_;
+      end_ += data->size();
+      placed_ = c + 1;
+    }
+    cv_.notify_all();
+    write_at(*data, at);
+  }
+  void finish() {  // after every put() has returned
+    if (gz_ && end_ == 0) {  // an empty .gz is one empty member, as gzclose would leave it
+      std::string member;
+      gzip_member(std::string(), member);
+      write_at(member, 0);
+    }
+    if (close(fd_) != 0) error_exit("Failed to write: " + path_);
+  }
+
+ private:
+  void write_at(const std::string &data, uint64_t at) {
+    for (size_t done = 0; done < data.size();) {
+      const ssize_t w = pwrite(fd_, data.data() + done, data.size() - done, (off_t)(at + done));
+      if (w <= 0) error_exit("Failed to write: " + path_);
+      done += (size_t)w;
+    }
+  }
+  std::string path_;
+  bool gz_;
+  int fd_;
+  std::mutex mu_;
+  std::condition_variable cv_;
+  uint64_t placed_ = 0, end_ = 0;  // pieces [0, placed_) have their place; the next one starts at end_
+};
+
+// A .gz on either side.  Seekable input: the chunk workers below parse and deflate.  .gz input: this thread
+// inflates + parses, the pool deflates (or just writes) the chunks it is handed; at most 2 chunks per pool
+// thread are in flight.
+inline void rewrite_file_piped(const std::string &in_path, const std::string &out_path, uint64_t total,
+                               const uint64_t *keep, const uint32_t *ids, unsigned n_threads) {
+  OrderedOutput out(out_path);
+  std::mutex mu;
+  std::condition_variable cv;
+  std::deque<std::pair<uint64_t, std::string>> queue;
+  std::vector<std::string> spare;
+  bool closed = false;
+  const size_t max_queued = 2 * n_threads;
+  auto worker = [&] {
+    std::string scratch;
+    while (true) {
+      std::pair<uint64_t, std::string> job;
+      {
+        std::unique_lock<std::mutex> lk(mu);
+        cv.wait(lk, [&] { return closed || !queue.empty(); });
+        if (queue.empty()) return;
+        job = std::move(queue.front());
+        queue.pop_front();
+      }
+      cv.notify_all();
+      out.put(job.first, job.second, scratch);
+      job.second.clear();
+      std::lock_guard<std::mutex> lk(mu);
+      spare.push_back(std::move(job.second));  // keeps its capacity for a later chunk
+    }
+  };
+  std::vector<std::thread> pool;
+  for (unsigned i = 0; i < n_threads; i++) pool.emplace_back(worker);
+  {
+    BlockReader reader(in_path);
+    RecordView rec;
+    std::string buf;
+    uint64_t c = 0;
+    auto hand_over = [&] {
+      std::unique_lock<std::mutex> lk(mu);
+      cv.wait(lk, [&] { return queue.size() < max_queued; });
+      queue.emplace_back(c++, std::move(buf));
+      if (!spare.empty()) {
+        buf = std::move(spare.back());
+        spare.pop_back();
+      } else {
+        buf = std::string();
+      }
+      lk.unlock();
+      cv.notify_all();
+    };
+    for (uint64_t t = 0; t < total && reader.read(rec); t++) {
+      if (!keep || (keep[t >> 6] >> (t & 63) & 1)) append_record(buf, rec, ids, t);
+      if ((t + 1) % REWRITE_CHUNK == 0) hand_over();
+    }
+    if (!buf.empty()) hand_over();
+  }
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    closed = true;
+  }
+  cv.notify_all();
+  for (std::thread &t : pool) t.join();
+  out.finish();
+}
+
 // Several threads: offsets[c] = byte offset of record c * REWRITE_CHUNK (noted in pass 1).
 inline void rewrite_file_parallel(const std::string &in_path, const std::string &out_path, uint64_t total,
                                   const uint64_t *keep, const uint32_t *ids, const std::vector<uint64_t> &offsets,
                                   unsigned n_threads) {
   const uint64_t n_chunks = (total + REWRITE_CHUNK - 1) / REWRITE_CHUNK;
-  if (ends_with(in_path, ".gz") || ends_with(out_path, ".gz") || n_threads < 2 || n_chunks < 2 ||
-      offsets.size() < n_chunks) {
+  if (n_threads < 2 || n_chunks < 2) {
     rewrite_file(in_path, out_path, total, keep, ids);
     return;
   }
-  const int fd = open(out_path.c_str(), O_WRONLY | O_CREAT | O_TRUNC, 0666);
-  if (fd < 0) error_exit("Failed to write: " + out_path);
+  if (ends_with(in_path, ".gz") || offsets.size() < n_chunks) {
+    rewrite_file_piped(in_path, out_path, total, keep, ids, n_threads);
+    return;
+  }
+  OrderedOutput out(out_path);
   std::atomic<uint64_t> next{0};
-  std::mutex mu;
-  std::condition_variable cv;
-  uint64_t parsed = 0, out_end = 0;  // chunks [0, parsed) have their place; the next one starts at out_end
   auto worker = [&] {
-    std::string buf;
+    std::string buf, scratch;
     RecordView rec;
     while (true) {
       const uint64_t c = next.fetch_add(1);
@@ -82,26 +222,13 @@ inline void rewrite_file_parallel(const std::string &in_path, const std::string 
           append_record(buf, rec, ids, t);
         }
       }
-      uint64_t at;
-      {
-        std::unique_lock<std::mutex> lk(mu);
-        cv.wait(lk, [&] { return parsed == c; });
-        at = out_end;
-        out_end += buf.size();
-        parsed = c + 1;
-      }
-      cv.notify_all();
-      for (size_t done = 0; done < buf.size();) {
-        const ssize_t w = pwrite(fd, buf.data() + done, buf.size() - done, (off_t)(at + done));
-        if (w <= 0) error_exit("Failed to write: " + out_path);
-        done += (size_t)w;
-      }
+      out.put(c, buf, scratch);
     }
   };
   std::vector<std::thread> pool;
   for (unsigned i = 0; i < n_threads; i++) pool.emplace_back(worker);
   for (std::thread &t : pool) t.join();
-  if (close(fd) != 0) error_exit("Failed to write: " + out_path);
+  out.finish();
 }
 
 }  // namespace humid_host

@@ -77,3 +77,25 @@ def test_parallel_rewrite_matches_one_thread(checker, tmp_path, case, annotate):
         assert open(a, "rb").read() == open(b, "rb").read(), (case, threads)
     if case == "plain" and annotate:
         assert open(a, "rb").read().count(b"\n") == 4 * 300  # every record, with ":id" behind its name
+
+
+@pytest.mark.parametrize("case", ["plain", "mixed_eol", "empty", "truncated_record"])
+@pytest.mark.parametrize("gz_in,gz_out", [(False, True), (True, False), (True, True)])
+def test_parallel_rewrite_of_compressed_files(checker, tmp_path, case, gz_in, gz_out):
+    """A .gz on either side of pass 2: one thread inflates + parses a .gz input, the pool deflates a .gz output as
+    one gzip member per chunk of 7 records — the inflated bytes are those of the one-thread pass."""
+    data = CASES[case](np.random.default_rng(len(case) + 5))
+    path = str(tmp_path / ("in.fastq.gz" if gz_in else "in.fastq"))
+    with (gzip.open(path, "wb") if gz_in else open(path, "wb")) as f:
+        f.write(data)
+    ext = ".fastq.gz" if gz_out else ".fastq"
+    read = (lambda p: gzip.open(p, "rb").read()) if gz_out else (lambda p: open(p, "rb").read())
+    for annotate in (0, 1):
+        for threads in (2, 4):
+            a, b = str(tmp_path / ("one" + ext)), str(tmp_path / (f"par{threads}" + ext))
+            subprocess.run([checker, "rewrite", path, a, b, str(threads + 10 * annotate), str(annotate), str(threads)],
+                           check=True)
+            assert read(a) == read(b), (case, annotate, threads)
+            if gz_out and case == "plain":
+                raw = open(b, "rb").read()
+                assert raw.count(b"\x1f\x8b\x08") >= 300 * (1 if annotate else 0) // 7  # several members
