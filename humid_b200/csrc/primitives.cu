@@ -1,4 +1,5 @@
 // Exclusive scan + stable LSD radix sort (see primitives.cuh).
+#include <cstdlib>
 #include "primitives.cuh"
 
 namespace humid {
@@ -232,6 +233,158 @@ __global__ void __launch_bounds__(RS_THREADS) digit_hist_kernel(const uint64_t *
 // Dynamic shared memory: RS_TILE keys (+ RS_TILE values).
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
+// Shared memory of one CTA of radix_pass_kernel (behind the dynamic part: RS_TILE keys + RS_TILE values).
+struct RadixShared {
+  uint32_t cnt[RS_WARPS][RS_BINS];
+  uint32_t gbase[RS_BINS];   // output position of tile-local position 0 of a digit
+  uint32_t warp_sums[RS_WARPS];
+  uint32_t next;
+};
+
+// Lanes of the (converged) warp whose `dig` agrees with this lane's in the bit `mask`.  Written out in PTX so that the
+// bit test, the ballot and the complement for lanes holding a 0 share one predicate: four instructions per bit
+// (test, VOTE, SEL, LOP3) where the compiler made six of the C++ form.
+__device__ __forceinline__ uint32_t same_bit_lanes(uint32_t dig, uint32_t mask) {
+  uint32_t m, flip;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      ".reg .b32 t;\n\t"
+      "and.b32 t, %2, %3;\n\t"
+      "setp.ne.u32 p, t, 0;\n\t"
+      "vote.sync.ballot.b32 %0, p, 0xffffffff;\n\t"
+      "selp.b32 %1, 0, 0xffffffff, p;\n\t"
+      "}"
+      : "=r"(m), "=r"(flip)
+      : "r"(dig), "r"(mask));
+  return m ^ flip;
+}
+
+// One tile.  FULL: all RS_TILE elements exist (every tile but the last), no bounds tests in the loops.
+template <bool HAS_VALS, bool FULL, class Digit>
+__device__ __forceinline__ uint32_t radix_tile(const uint64_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
+                                               uint64_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out,
+                                               uint64_t n, uint32_t n_tiles, const Digit &digit_of, uint32_t my_base,
+                                               volatile uint64_t *status, uint32_t *ticket, uint32_t index_base,
+                                               uint32_t tile, uint64_t *stage, uint32_t *svals, RadixShared &sh) {
+  const int w = threadIdx.x >> 5;
+  const uint32_t lane = lane_id();
+  const uint32_t lt = (1u << lane) - 1u;
+  const uint32_t d = threadIdx.x;  // the digit this thread looks after
+  if (threadIdx.x == 0) sh.next = atomicAdd(ticket, 1u);
+#pragma unroll
+  for (int k = 0; k < RS_WARPS; k++) sh.cnt[k][threadIdx.x] = 0;
+  const uint64_t tile_base = (uint64_t)tile * RS_TILE;
+  const uint32_t in_tile = FULL ? (uint32_t)RS_TILE : (uint32_t)(n - tile_base);
+  const uint32_t warp_first = (uint32_t)w * (32 * RS_ITEMS) + lane;  // tile-local index of this lane's first element
+  const uint64_t *kin = keys_in + tile_base + warp_first;
+  uint64_t key[RS_ITEMS];
+  uint32_t val[HAS_VALS ? RS_ITEMS : 1];
+  uint16_t lpos[RS_ITEMS];
+#pragma unroll
+  for (int j = 0; j < RS_ITEMS; j++) key[j] = (FULL || warp_first + j * 32 < in_tile) ? ld_stream_u64(kin + j * 32) : 0ull;
+  if (HAS_VALS) {
+    if (vals_in) {
+      const uint32_t *vin = vals_in + tile_base + warp_first;
+#pragma unroll
+      for (int j = 0; j < RS_ITEMS; j++) val[j] = (FULL || warp_first + j * 32 < in_tile) ? __ldcs(vin + j * 32) : 0u;
+    } else {
+      const uint32_t v0 = index_base + (uint32_t)tile_base + warp_first;
+#pragma unroll
+      for (int j = 0; j < RS_ITEMS; j++) val[j] = v0 + j * 32;
+    }
+  }
+  __syncthreads();  // counters cleared, next ticket known
+  const uint32_t next_tile = sh.next;
+  if (next_tile < n_tiles) {  // -> L2 (128-B lines: 256 of keys, 128 of values)
+    const uint64_t next = (uint64_t)next_tile * RS_TILE;
+    if (next + (uint64_t)threadIdx.x * 16 < n) prefetch_l2(keys_in + next + (uint64_t)threadIdx.x * 16);
+    if (HAS_VALS && vals_in && threadIdx.x < RS_THREADS / 2 && next + (uint64_t)threadIdx.x * 32 < n)
+      prefetch_l2(vals_in + next + (uint64_t)threadIdx.x * 32);
+  }
+  // rank of every element among the elements of its digit in this warp's sub-tile
+  uint32_t *const my_cnt = sh.cnt[w];
+#pragma unroll
+  for (int j = 0; j < RS_ITEMS; j++) {
+    const bool ok = FULL || warp_first + j * 32 < in_tile;
+    const uint32_t dig = ok ? digit_of(key[j]) : 0u;
+    // lanes holding the same digit: eight ballots (match.any is a slow-pipe instruction: the
+    // first version of this kernel was bound by it, ncu r01f)
+    uint32_t peers = FULL ? 0xffffffffu : __ballot_sync(0xffffffffu, ok);
+#pragma unroll
+    for (int bit = 0; bit < 8; bit++) peers &= same_bit_lanes(dig, 1u << bit);
+    const uint32_t before = ok ? my_cnt[dig] : 0u;
+    __syncwarp();
+    if (ok && (peers & lt) == 0) my_cnt[dig] = before + __popc(peers);  // one leader per digit
+    __syncwarp();
+    lpos[j] = (uint16_t)(before + __popc(peers & lt));
+  }
+  __syncthreads();
+  // thread d: digit d of this tile
+  uint32_t total = 0;
+#pragma unroll
+  for (int k = 0; k < RS_WARPS; k++) {
+    uint32_t c = sh.cnt[k][d];
+    sh.cnt[k][d] = total;
+    total += c;
+  }
+  volatile uint64_t *mine = status + (uint64_t)tile * RS_BINS + d;
+  *mine = (tile == 0 ? RS_INCLUSIVE : RS_AGGREGATE) | total;
+  const uint32_t local = block_exclusive_256(total, sh.warp_sums);  // first tile-local position of digit d
+#pragma unroll
+  for (int k = 0; k < RS_WARPS; k++) sh.cnt[k][d] += local;  // -> tile-local position of warp k's first element of d
+  __syncthreads();
+  // reorder in shared memory: every digit run becomes consecutive
+#pragma unroll
+  for (int j = 0; j < RS_ITEMS; j++) {
+    if (FULL || warp_first + j * 32 < in_tile) {
+      uint32_t dig = digit_of(key[j]);
+      uint32_t p = my_cnt[dig] + lpos[j];
+      stage[p] = key[j];
+      if (HAS_VALS) svals[p] = val[j];
+    }
+  }
+  // how many elements of digit d precede this tile: chained look-back over the earlier tiles,
+  // RS_LOOK status words per step (independent loads)
+  {
+    uint32_t preceding = 0;
+    if (tile > 0) {
+      uint32_t t = tile;  // next tile to examine is t - 1
+      bool done = false;
+      while (!done) {
+        uint64_t v[RS_LOOK];
+#pragma unroll
+        for (int q = 0; q < RS_LOOK; q++)
+          v[q] = t > (uint32_t)q ? (uint64_t)status[(uint64_t)(t - 1 - q) * RS_BINS + d] : (1ull << 63);
+#pragma unroll
+        for (int q = 0; q < RS_LOOK; q++) {
+          if (done) break;
+          uint64_t x = v[q];
+          while (x == 0) x = status[(uint64_t)(t - 1 - q) * RS_BINS + d];  // not published yet
+          preceding += (uint32_t)x;
+          done = (x & RS_INCLUSIVE) != 0;
+        }
+        t = t > RS_LOOK ? t - RS_LOOK : 0;
+      }
+      *mine = RS_INCLUSIVE | (uint64_t)(preceding + total);
+    }
+    sh.gbase[d] = my_base + preceding - local;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < RS_ITEMS; k++) {
+    const uint32_t idx = k * RS_THREADS + threadIdx.x;
+    if (FULL || idx < in_tile) {
+      const uint64_t kk = stage[idx];
+      const uint32_t out = sh.gbase[digit_of(kk)] + idx;
+      keys_out[out] = kk;
+      if (HAS_VALS) vals_out[out] = svals[idx];
+    }
+  }
+  __syncthreads();  // stage / gbase / cnt / next are reused by the next tile
+  return next_tile;
+}
+
 template <bool HAS_VALS, class Digit>
 __global__ void __launch_bounds__(RS_THREADS, 3)
     radix_pass_kernel(const uint64_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
@@ -239,136 +392,21 @@ __global__ void __launch_bounds__(RS_THREADS, 3)
                       Digit digit_of, const uint32_t *__restrict__ digit_base, volatile uint64_t *status,
                       uint32_t *ticket, uint32_t index_base) {
   extern __shared__ uint64_t stage[];  // [RS_TILE] keys, then [RS_TILE] u32 values
-  __shared__ uint32_t cnt[RS_WARPS][RS_BINS];
-  __shared__ uint32_t dstart[RS_BINS];  // first tile-local position of a digit
-  __shared__ uint32_t gbase[RS_BINS];   // output position of tile-local position 0 of a digit
-  __shared__ uint32_t warp_sums[RS_WARPS];
-  __shared__ uint32_t s_next;
+  __shared__ RadixShared sh;
   uint32_t *const svals = reinterpret_cast<uint32_t *>(stage + RS_TILE);
-  const int w = threadIdx.x >> 5;
-  const uint32_t lane = lane_id();
-  const uint32_t lt = (1u << lane) - 1u;
-  const uint32_t d = threadIdx.x;  // the digit this thread looks after
-  const uint32_t my_base = digit_base[d];
+  const uint32_t my_base = digit_base[threadIdx.x];
 
-  if (threadIdx.x == 0) s_next = atomicAdd(ticket, 1u);
+  if (threadIdx.x == 0) sh.next = atomicAdd(ticket, 1u);
   __syncthreads();
-  uint32_t tile = s_next;
+  uint32_t tile = sh.next;
   __syncthreads();
   while (tile < n_tiles) {
-    if (threadIdx.x == 0) s_next = atomicAdd(ticket, 1u);
-#pragma unroll
-    for (int k = 0; k < RS_WARPS; k++) cnt[k][threadIdx.x] = 0;
-    const uint64_t tile_base = (uint64_t)tile * RS_TILE;
-    const uint64_t warp_base = tile_base + (uint64_t)w * (32 * RS_ITEMS);
-    uint64_t key[RS_ITEMS];
-    uint32_t val[HAS_VALS ? RS_ITEMS : 1];
-    uint16_t lpos[RS_ITEMS];
-#pragma unroll
-    for (int j = 0; j < RS_ITEMS; j++) {
-      uint64_t i = warp_base + (uint64_t)j * 32 + lane;
-      key[j] = i < n ? ld_stream_u64(keys_in + i) : 0ull;
-    }
-    if (HAS_VALS) {
-#pragma unroll
-      for (int j = 0; j < RS_ITEMS; j++) {
-        uint64_t i = warp_base + (uint64_t)j * 32 + lane;
-        val[j] = i >= n ? 0u : vals_in ? __ldcs(vals_in + i) : index_base + (uint32_t)i;
-      }
-    }
-    __syncthreads();  // counters cleared, next ticket known
-    const uint32_t next_tile = s_next;
-    if (next_tile < n_tiles) {  // -> L2 (128-B lines: 256 of keys, 128 of values)
-      const uint64_t next = (uint64_t)next_tile * RS_TILE;
-      if (next + (uint64_t)threadIdx.x * 16 < n) prefetch_l2(keys_in + next + (uint64_t)threadIdx.x * 16);
-      if (HAS_VALS && vals_in && threadIdx.x < RS_THREADS / 2 && next + (uint64_t)threadIdx.x * 32 < n)
-        prefetch_l2(vals_in + next + (uint64_t)threadIdx.x * 32);
-    }
-    // rank of every element among the elements of its digit in this warp's sub-tile
-#pragma unroll
-    for (int j = 0; j < RS_ITEMS; j++) {
-      bool ok = warp_base + (uint64_t)j * 32 + lane < n;
-      uint32_t dig = ok ? digit_of(key[j]) : 0u;
-      // lanes holding the same digit: eight ballots (match.any is a slow-pipe instruction: the
-      // first version of this kernel was bound by it, ncu r01f)
-      uint32_t peers = __ballot_sync(0xffffffffu, ok);
-#pragma unroll
-      for (int bit = 0; bit < 8; bit++) {
-        const bool one = (dig >> bit) & 1u;
-        const uint32_t m = __ballot_sync(0xffffffffu, one);
-        peers &= one ? m : ~m;
-      }
-      uint32_t before = ok ? cnt[w][dig] : 0u;
-      __syncwarp();
-      if (ok && (peers & lt) == 0) cnt[w][dig] = before + __popc(peers);  // one leader per digit
-      __syncwarp();
-      lpos[j] = (uint16_t)(before + __popc(peers & lt));
-    }
-    __syncthreads();
-    // thread d: digit d of this tile
-    uint32_t total = 0;
-#pragma unroll
-    for (int k = 0; k < RS_WARPS; k++) {
-      uint32_t c = cnt[k][d];
-      cnt[k][d] = total;
-      total += c;
-    }
-    volatile uint64_t *mine = status + (uint64_t)tile * RS_BINS + d;
-    *mine = (tile == 0 ? RS_INCLUSIVE : RS_AGGREGATE) | total;
-    const uint32_t local = block_exclusive_256(total, warp_sums);
-    dstart[d] = local;
-    __syncthreads();
-    // reorder in shared memory: every digit run becomes consecutive
-#pragma unroll
-    for (int j = 0; j < RS_ITEMS; j++) {
-      bool ok = warp_base + (uint64_t)j * 32 + lane < n;
-      if (ok) {
-        uint32_t dig = digit_of(key[j]);
-        uint32_t p = dstart[dig] + cnt[w][dig] + lpos[j];
-        stage[p] = key[j];
-        if (HAS_VALS) svals[p] = val[j];
-      }
-    }
-    // how many elements of digit d precede this tile: chained look-back over the earlier tiles,
-    // RS_LOOK status words per step (independent loads)
-    {
-      uint32_t preceding = 0;
-      if (tile > 0) {
-        uint32_t t = tile;  // next tile to examine is t - 1
-        bool done = false;
-        while (!done) {
-          uint64_t v[RS_LOOK];
-#pragma unroll
-          for (int q = 0; q < RS_LOOK; q++)
-            v[q] = t > (uint32_t)q ? (uint64_t)status[(uint64_t)(t - 1 - q) * RS_BINS + d] : (1ull << 63);
-#pragma unroll
-          for (int q = 0; q < RS_LOOK; q++) {
-            if (done) break;
-            uint64_t x = v[q];
-            while (x == 0) x = status[(uint64_t)(t - 1 - q) * RS_BINS + d];  // not published yet
-            preceding += (uint32_t)x;
-            done = (x & RS_INCLUSIVE) != 0;
-          }
-          t = t > RS_LOOK ? t - RS_LOOK : 0;
-        }
-        *mine = RS_INCLUSIVE | (uint64_t)(preceding + total);
-      }
-      gbase[d] = my_base + preceding - local;
-    }
-    __syncthreads();
-    const uint32_t in_tile = (uint32_t)min((uint64_t)RS_TILE, n - tile_base);
-#pragma unroll
-    for (int k = 0; k < RS_ITEMS; k++) {
-      uint32_t idx = k * RS_THREADS + threadIdx.x;
-      if (idx < in_tile) {
-        uint64_t kk = stage[idx];
-        uint32_t out = gbase[digit_of(kk)] + idx;
-        keys_out[out] = kk;
-        if (HAS_VALS) vals_out[out] = svals[idx];
-      }
-    }
-    __syncthreads();  // stage / gbase / cnt / s_next are reused by the next tile
-    tile = next_tile;
+    if ((uint64_t)(tile + 1) * RS_TILE <= n)
+      tile = radix_tile<HAS_VALS, true>(keys_in, vals_in, keys_out, vals_out, n, n_tiles, digit_of, my_base, status,
+                                        ticket, index_base, tile, stage, svals, sh);
+    else
+      tile = radix_tile<HAS_VALS, false>(keys_in, vals_in, keys_out, vals_out, n, n_tiles, digit_of, my_base, status,
+                                         ticket, index_base, tile, stage, svals, sh);
   }
 }
 

