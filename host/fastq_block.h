@@ -1,6 +1,6 @@
 // Block-wise FastQ reading for the `humid` executable: SURVEY.md §8(f) item 1, the host ingest in
 // front of the device path.  One BlockReader per input file runs in its own thread
-// (host/humid_main.cc); it reads 16 MiB blocks (plain or gzip), finds line ends with memchr and
+// (host/humid_main.cc); it reads 16 MiB blocks (plain, gzip, or BGZF inflated by several threads: host/bgzf.h), finds line ends with memchr and
 // hands out records as views into its buffer — no allocation and no copy per record.
 //
 // The observable rules are those of host/fastq_io.h's FastqReader (i.e. of fastp's reader as the
@@ -15,14 +15,25 @@
 
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <iostream>
+#include <memory>
 #include <string>
+#include <thread>
 #include <vector>
 
+#include "bgzf.h"
 #include "fastq_io.h"
 
 namespace humid_host {
+
+// Inflate threads of one BGZF input (HUMID_INFLATE_THREADS overrides; 1 = the one-stream path).
+inline unsigned default_inflate_threads() {
+  if (const char *e = std::getenv("HUMID_INFLATE_THREADS")) return (unsigned)std::max(1, std::atoi(e));
+  const unsigned hw = std::thread::hardware_concurrency();
+  return std::max(1u, std::min(4u, hw / 4));
+}
 
 struct Span {
   const char *p = nullptr;
@@ -36,9 +47,13 @@ struct RecordView {
 class BlockReader {
  public:
   // start: byte offset to begin at (plain files only; it must be the start of a line)
-  explicit BlockReader(const std::string &path, size_t block = 16u << 20, uint64_t start = 0)
+  // inflate_threads > 1: a .gz that is BGZF is inflated by that many threads (host/bgzf.h)
+  explicit BlockReader(const std::string &path, size_t block = 16u << 20, uint64_t start = 0,
+                       unsigned inflate_threads = default_inflate_threads())
       : path_(path), buf_(block), base_(start) {
-    if (ends_with(path, ".gz")) {
+    if (ends_with(path, ".gz") && inflate_threads > 1 && !start && is_bgzf(path)) {
+      bgzf_.reset(new BgzfInflater(path, inflate_threads));
+    } else if (ends_with(path, ".gz")) {
       if (start) error_exit("cannot seek in a compressed file: " + path);
       gz_ = gzopen(path.c_str(), "rb");
       if (!gz_) error_exit("Failed to open file: " + path);
@@ -135,7 +150,9 @@ class BlockReader {
     if (end_ == buf_.size()) buf_.resize(buf_.size() * 2);  // one record longer than the block
     size_t room = buf_.size() - end_;
     long got;
-    if (gz_) {
+    if (bgzf_) {
+      got = bgzf_->read(buf_.data() + end_, room);
+    } else if (gz_) {
       got = gzread(gz_, buf_.data() + end_, (unsigned)std::min<size_t>(room, 1u << 30));
       if (got < 0) error_exit("igzip: encountered while decompressing file: " + path_);
     } else {
@@ -157,6 +174,7 @@ class BlockReader {
   bool drained_ = false;       // ... and the parser knows: the last line ends at end_
   gzFile gz_ = nullptr;
   FILE *fp_ = nullptr;
+  std::unique_ptr<BgzfInflater> bgzf_;
 };
 
 }  // namespace humid_host

@@ -3,7 +3,9 @@ reader whose behaviour was pinned against the reference binary): same records, w
 endings, junk lines, truncation or block size."""
 import gzip
 import os
+import struct
 import subprocess
+import zlib
 
 import numpy as np
 import pytest
@@ -99,3 +101,50 @@ def test_parallel_rewrite_of_compressed_files(checker, tmp_path, case, gz_in, gz
             if gz_out and case == "plain":
                 raw = open(b, "rb").read()
                 assert raw.count(b"\x1f\x8b\x08") >= 300 * (1 if annotate else 0) // 7  # several members
+
+
+def bgzf_bytes(data, block=700):
+    """`data` as a BGZF file (the layout bgzip writes): gzip members with a 'BC' extra field holding the member size,
+    at most `block` inflated bytes each, and the empty end-of-file member."""
+    out = []
+    for a in list(range(0, len(data), block)) + [None]:
+        chunk = b"" if a is None else data[a:a + block]
+        c = zlib.compressobj(6, zlib.DEFLATED, -15)
+        body = c.compress(chunk) + c.flush()
+        bsize = 12 + 6 + len(body) + 8 - 1
+        out.append(b"\x1f\x8b\x08\x04" + b"\0" * 4 + b"\x00\xff" + struct.pack("<H", 6) + b"BC" + struct.pack("<HH", 2, bsize) +
+                   body + struct.pack("<II", zlib.crc32(chunk), len(chunk)))
+    return b"".join(out)
+
+
+@pytest.mark.parametrize("case", ["plain", "mixed_eol", "junk_between", "long_lines", "empty", "truncated_record"])
+def test_bgzf_inflated_by_several_threads(checker, tmp_path, case):
+    """A BGZF input (host/bgzf.h: members inflated side by side) reads as the same records as the same bytes through
+    the one-stream path, with 2..5 inflate threads and jobs of one or many members."""
+    data = CASES[case](np.random.default_rng(len(case) + 11))
+    if case == "plain":
+        data = data * 40  # several jobs' worth of members
+    path = str(tmp_path / "in.fastq.gz")
+    with open(path, "wb") as f:
+        f.write(bgzf_bytes(data, 700 if case != "plain" else 60000))
+    assert gzip.open(path, "rb").read() == data  # a valid multi-member gzip
+    env = dict(os.environ, HUMID_INFLATE_THREADS="1")
+    ref = subprocess.run([checker, "block", path, "4096"], capture_output=True, check=True, env=env)
+    old = subprocess.run([checker, "old", path], capture_output=True, check=True, env=env)
+    assert ref.stdout == old.stdout
+    for threads in (2, 3, 5):
+        env = dict(os.environ, HUMID_INFLATE_THREADS=str(threads))
+        got = subprocess.run([checker, "block", path, "4096"], capture_output=True, check=True, env=env)
+        assert got.stdout == ref.stdout, (case, threads)
+
+
+def test_bgzf_damage_is_an_error(checker, tmp_path):
+    data = CASES["plain"](np.random.default_rng(5))
+    raw = bytearray(bgzf_bytes(data, 700))
+    raw[len(raw) // 2] ^= 0x55  # somewhere inside a member
+    path = str(tmp_path / "in.fastq.gz")
+    with open(path, "wb") as f:
+        f.write(bytes(raw))
+    env = dict(os.environ, HUMID_INFLATE_THREADS="3")
+    got = subprocess.run([checker, "block", path, "4096"], capture_output=True, env=env)
+    assert got.returncode != 0 and b"decompressing" in got.stderr
