@@ -15,7 +15,7 @@ from typing import Dict, List, Optional, Sequence, Tuple
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libhumid_gpu.so")
+LIB_PATH = os.environ.get("HUMID_GPU_LIB") or os.path.join(HERE, "libhumid_gpu.so")  # (override: A/B runs of two builds)
 MAX_SEGMENTS = 16
 MAX_WORD_LENGTH = 63
 MAX_NARROW_WORD_LENGTH = 31  # longer words: two 64-bit keys, Hamming / edit distance 1, one GPU

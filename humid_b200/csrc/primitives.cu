@@ -142,8 +142,22 @@ int exclusive_scan_u32(const uint32_t *in, uint32_t *out, uint64_t n, uint32_t *
 // ------------------------------------------------------------------------------------
 constexpr int RS_THREADS = 256;
 constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_ITEMS = 16;
-constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
+// Tile shape (A/B builds override these).  Measured on sort_words, 21.3 M (key, value) pairs, 6 passes: 256 threads x 16
+// elements x 3 CTAs per SM 1.09-1.12 ms; 256 x 24 x 2 1.03-1.07 (longer digit runs per tile, fewer look-backs);
+// 256 x 12 x 4 1.22; 256 x 32 x 1 1.18; 512 x 16 x 1 1.08; 512 x 12 x 2 1.17; 1024 x 8 x 1 1.17; 1024 x 6 x 1 1.24.
+#ifndef HUMID_RS_ITEMS
+#define HUMID_RS_ITEMS 24
+#endif
+#ifndef HUMID_RS_CTAS
+#define HUMID_RS_CTAS 2
+#endif
+constexpr int RS_ITEMS = HUMID_RS_ITEMS;
+#ifndef HUMID_RS_THREADS
+#define HUMID_RS_THREADS 256
+#endif
+constexpr int RS_PASS_THREADS = HUMID_RS_THREADS;  // threads of a radix_pass_kernel CTA (the histogram kernels keep RS_THREADS)
+constexpr int RS_PASS_WARPS = RS_PASS_THREADS / 32;
+constexpr int RS_TILE = RS_PASS_THREADS * RS_ITEMS;
 constexpr int RS_BINS = 256;
 constexpr int RS_MAX_PASSES = 8;
 constexpr int RS_LOOK = 8;
@@ -235,9 +249,9 @@ __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefe
 
 // Shared memory of one CTA of radix_pass_kernel (behind the dynamic part: RS_TILE keys + RS_TILE values).
 struct RadixShared {
-  uint32_t cnt[RS_WARPS][RS_BINS];
+  uint32_t cnt[RS_PASS_WARPS][RS_BINS];
   uint32_t gbase[RS_BINS];   // output position of tile-local position 0 of a digit
-  uint32_t warp_sums[RS_WARPS];
+  uint32_t warp_sums[RS_PASS_WARPS];
   uint32_t next;
 };
 
@@ -273,7 +287,7 @@ __device__ __forceinline__ uint32_t radix_tile(const uint64_t *__restrict__ keys
   const uint32_t d = threadIdx.x;  // the digit this thread looks after
   if (threadIdx.x == 0) sh.next = atomicAdd(ticket, 1u);
 #pragma unroll
-  for (int k = 0; k < RS_WARPS; k++) sh.cnt[k][threadIdx.x] = 0;
+  for (int i = 0; i < RS_PASS_WARPS * RS_BINS / RS_PASS_THREADS; i++) (&sh.cnt[0][0])[i * RS_PASS_THREADS + threadIdx.x] = 0;
   const uint64_t tile_base = (uint64_t)tile * RS_TILE;
   const uint32_t in_tile = FULL ? (uint32_t)RS_TILE : (uint32_t)(n - tile_base);
   const uint32_t warp_first = (uint32_t)w * (32 * RS_ITEMS) + lane;  // tile-local index of this lane's first element
@@ -298,9 +312,14 @@ __device__ __forceinline__ uint32_t radix_tile(const uint64_t *__restrict__ keys
   const uint32_t next_tile = sh.next;
   if (next_tile < n_tiles) {  // -> L2 (128-B lines: 256 of keys, 128 of values)
     const uint64_t next = (uint64_t)next_tile * RS_TILE;
-    if (next + (uint64_t)threadIdx.x * 16 < n) prefetch_l2(keys_in + next + (uint64_t)threadIdx.x * 16);
-    if (HAS_VALS && vals_in && threadIdx.x < RS_THREADS / 2 && next + (uint64_t)threadIdx.x * 32 < n)
-      prefetch_l2(vals_in + next + (uint64_t)threadIdx.x * 32);
+#pragma unroll
+    for (uint32_t l = threadIdx.x; l < RS_TILE / 16; l += RS_PASS_THREADS)
+      if (next + (uint64_t)l * 16 < n) prefetch_l2(keys_in + next + (uint64_t)l * 16);
+    if (HAS_VALS && vals_in) {
+#pragma unroll
+      for (uint32_t l = threadIdx.x; l < RS_TILE / 32; l += RS_PASS_THREADS)
+        if (next + (uint64_t)l * 32 < n) prefetch_l2(vals_in + next + (uint64_t)l * 32);
+    }
   }
   // rank of every element among the elements of its digit in this warp's sub-tile
   uint32_t *const my_cnt = sh.cnt[w];
@@ -320,19 +339,25 @@ __device__ __forceinline__ uint32_t radix_tile(const uint64_t *__restrict__ keys
     lpos[j] = (uint16_t)(before + __popc(peers & lt));
   }
   __syncthreads();
-  // thread d: digit d of this tile
+  // thread d (of the first RS_BINS threads): digit d of this tile
+  const bool digit_thread = RS_PASS_THREADS == RS_BINS || threadIdx.x < RS_BINS;
   uint32_t total = 0;
+  volatile uint64_t *mine = nullptr;
+  if (digit_thread) {
 #pragma unroll
-  for (int k = 0; k < RS_WARPS; k++) {
-    uint32_t c = sh.cnt[k][d];
-    sh.cnt[k][d] = total;
-    total += c;
+    for (int k = 0; k < RS_PASS_WARPS; k++) {
+      uint32_t c = sh.cnt[k][d];
+      sh.cnt[k][d] = total;
+      total += c;
+    }
+    mine = status + (uint64_t)tile * RS_BINS + d;
+    *mine = (tile == 0 ? RS_INCLUSIVE : RS_AGGREGATE) | total;
   }
-  volatile uint64_t *mine = status + (uint64_t)tile * RS_BINS + d;
-  *mine = (tile == 0 ? RS_INCLUSIVE : RS_AGGREGATE) | total;
   const uint32_t local = block_exclusive_256(total, sh.warp_sums);  // first tile-local position of digit d
+  if (digit_thread) {
 #pragma unroll
-  for (int k = 0; k < RS_WARPS; k++) sh.cnt[k][d] += local;  // -> tile-local position of warp k's first element of d
+    for (int k = 0; k < RS_PASS_WARPS; k++) sh.cnt[k][d] += local;  // -> tile-local position of warp k's first element of d
+  }
   __syncthreads();
   // reorder in shared memory: every digit run becomes consecutive
 #pragma unroll
@@ -346,7 +371,7 @@ __device__ __forceinline__ uint32_t radix_tile(const uint64_t *__restrict__ keys
   }
   // how many elements of digit d precede this tile: chained look-back over the earlier tiles,
   // RS_LOOK status words per step (independent loads)
-  {
+  if (digit_thread) {
     uint32_t preceding = 0;
     if (tile > 0) {
       uint32_t t = tile;  // next tile to examine is t - 1
@@ -373,7 +398,7 @@ __device__ __forceinline__ uint32_t radix_tile(const uint64_t *__restrict__ keys
   __syncthreads();
 #pragma unroll
   for (int k = 0; k < RS_ITEMS; k++) {
-    const uint32_t idx = k * RS_THREADS + threadIdx.x;
+    const uint32_t idx = k * RS_PASS_THREADS + threadIdx.x;
     if (FULL || idx < in_tile) {
       const uint64_t kk = stage[idx];
       const uint32_t out = sh.gbase[digit_of(kk)] + idx;
@@ -386,7 +411,7 @@ __device__ __forceinline__ uint32_t radix_tile(const uint64_t *__restrict__ keys
 }
 
 template <bool HAS_VALS, class Digit>
-__global__ void __launch_bounds__(RS_THREADS, 3)
+__global__ void __launch_bounds__(RS_PASS_THREADS, HUMID_RS_CTAS)
     radix_pass_kernel(const uint64_t *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
                       uint64_t *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n, uint32_t n_tiles,
                       Digit digit_of, const uint32_t *__restrict__ digit_base, volatile uint64_t *status,
@@ -394,7 +419,7 @@ __global__ void __launch_bounds__(RS_THREADS, 3)
   extern __shared__ uint64_t stage[];  // [RS_TILE] keys, then [RS_TILE] u32 values
   __shared__ RadixShared sh;
   uint32_t *const svals = reinterpret_cast<uint32_t *>(stage + RS_TILE);
-  const uint32_t my_base = digit_base[threadIdx.x];
+  const uint32_t my_base = threadIdx.x < RS_BINS ? digit_base[threadIdx.x] : 0u;
 
   if (threadIdx.x == 0) sh.next = atomicAdd(ticket, 1u);
   __syncthreads();
@@ -422,12 +447,12 @@ static void launch_radix_pass(uint32_t n_tiles, cudaStream_t stream, const uint6
     int dev = 0, sms = 0, per_sm = 0;
     HUMID_CUDA(cudaGetDevice(&dev));
     HUMID_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    HUMID_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, RS_THREADS, smem));
+    HUMID_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, RS_PASS_THREADS, smem));
     if (per_sm < 1) throw CudaError{"radix_pass_kernel does not fit on an SM"};
     resident = sms * per_sm;
   }
   const unsigned grid = std::min<unsigned>(n_tiles, (unsigned)resident);
-  radix_pass_kernel<HAS_VALS, Digit><<<grid, RS_THREADS, smem, stream>>>(keys_in, vals_in, keys_out, vals_out, n, n_tiles,
+  radix_pass_kernel<HAS_VALS, Digit><<<grid, RS_PASS_THREADS, smem, stream>>>(keys_in, vals_in, keys_out, vals_out, n, n_tiles,
                                                                        dg, digit_base, status, ticket, index_base);
 }
 

@@ -26,7 +26,11 @@ constexpr int PACK_ROWS_WIDE = 512;  // words of 32..63 letters: the tile still 
 __device__ __forceinline__ uint32_t pack4(uint32_t x, bool &bad) {
   uint32_t c = (x >> 1) & 0x03030303u;  // A:0 C:1 G:3 T:2
   c ^= (c >> 1) & 0x01010101u;          // A:0 C:1 G:2 T:3
+#ifdef HUMID_PACK4_PRMT
+  const uint32_t sel = __byte_perm(c | (c >> 4), 0u, 0x4420u);
+#else
   const uint32_t sel = (c & 0x3u) | ((c >> 4) & 0x30u) | ((c >> 8) & 0x300u) | ((c >> 12) & 0x3000u);
+#endif
   bad |= __byte_perm(0x54474341u /* "ACGT" */, 0u, sel) != x;
   return (c * 0x40100401u) >> 24;  // b0<<6 | b1<<4 | b2<<2 | b3
 }

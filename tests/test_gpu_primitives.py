@@ -33,7 +33,7 @@ def dev(a, dtype):
     return torch.from_numpy(a.view(dtype)).cuda()
 
 
-SIZES = [1, 2, 31, 4096, 4097, 50_000, 3_000_001]
+SIZES = [1, 2, 31, 4096, 4097, 6144, 6145, 50_000, 3_000_001]  # 6144 = one radix tile, 4096 = one scan tile
 
 
 @pytest.mark.parametrize("n", SIZES)
