@@ -237,7 +237,10 @@ __device__ void replay_directional(const Graph &g, const uint32_t *mem, uint32_t
 // components are gathered and replayed in local memory, large ones use the globally sorted
 // member array (big_members / big_start) and global work arrays of the same length.
 template <bool MAXIMUM>
-__global__ void __launch_bounds__(128)
+#ifndef HUMID_REPLAY_THREADS
+#define HUMID_REPLAY_THREADS 128
+#endif
+__global__ void __launch_bounds__(HUMID_REPLAY_THREADS)
     replay_kernel(Graph g, uint64_t U, const uint32_t *__restrict__ comp, const uint32_t *__restrict__ csize,
                   const uint32_t *__restrict__ big_members, const uint32_t *__restrict__ big_start,
                   uint32_t *__restrict__ big_work_a, uint32_t *__restrict__ big_work_b, uint32_t *visited,
@@ -291,7 +294,7 @@ int stage_cluster(State &s) {
   s.n_clusters = 0;
   if (U == 0) return 0;
   int k = 0;
-  const unsigned g256 = grid_for(U, 256), g128 = grid_for(U, 128);
+  const unsigned g256 = grid_for(U, 256), g128 = grid_for(U, HUMID_REPLAY_THREADS);
   s.comp.ensure(U);
   s.label.ensure(U);
   s.work_a.ensure(U);
@@ -357,13 +360,13 @@ int stage_cluster(State &s) {
     // big components: DFS stack (node, edge) in work_b / slot_alt, visited flags per word in work_c
     s.slot_alt.ensure(n_big + 1);
     HUMID_CUDA(cudaMemsetAsync(s.work_c.p, 0, U * sizeof(uint32_t), s.stream));
-    replay_kernel<true><<<g128, 128, 0, s.stream>>>(g, U, s.comp.p, csize, s.members.p, s.seg_start.p, s.work_b.p,
+    replay_kernel<true><<<g128, HUMID_REPLAY_THREADS, 0, s.stream>>>(g, U, s.comp.p, csize, s.members.p, s.seg_start.p, s.work_b.p,
                                                     s.slot_alt.p, s.work_c.p, s.label.p, s.seed_flag.p, s.seed_size.p,
                                                     s.seed_max.p, skip_root);
   } else {
     HUMID_CUDA(cudaMemsetAsync(s.label.p, 0xFF, U * sizeof(uint32_t), s.stream));
     HUMID_CUDA(cudaMemsetAsync(s.seed_flag.p, 0, U * sizeof(uint32_t), s.stream));
-    replay_kernel<false><<<g128, 128, 0, s.stream>>>(g, U, s.comp.p, csize, s.members.p, s.seg_start.p, s.work_b.p,
+    replay_kernel<false><<<g128, HUMID_REPLAY_THREADS, 0, s.stream>>>(g, U, s.comp.p, csize, s.members.p, s.seg_start.p, s.work_b.p,
                                                      nullptr, nullptr, s.label.p, s.seed_flag.p, s.seed_size.p,
                                                      s.seed_max.p, skip_root);
   }

@@ -88,7 +88,10 @@ __device__ __forceinline__ bool linked(uint64_t a, uint64_t b, uint32_t d) {
 //                                    (no dominance rule)                                 (edit-distance candidates)
 // group_cap == JOIN_NO_CAP: every group is walked whatever its size, nothing is flagged.
 constexpr int JOIN_LOCAL_HITS = 6;
-constexpr int JOIN_THREADS = 512;
+#ifndef HUMID_JOIN_THREADS
+#define HUMID_JOIN_THREADS 512
+#endif
+constexpr int JOIN_THREADS = HUMID_JOIN_THREADS;
 
 template <int EMIT>
 __device__ __forceinline__ void join_emit(uint64_t *out, uint64_t pos, uint32_t a, uint32_t b, uint32_t col_base,

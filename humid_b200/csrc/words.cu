@@ -15,7 +15,14 @@ struct PackParams {
 };
 
 constexpr int PACK_THREADS = 256;
-constexpr int PACK_ROWS = 1024;  // tuples per CTA: 4 x 16-byte loads in flight per thread while staging
+#ifndef HUMID_PACK_ROWS
+#define HUMID_PACK_ROWS 1024
+#endif
+constexpr int PACK_ROWS = HUMID_PACK_ROWS;
+#ifndef HUMID_PACK_LOADS
+#define HUMID_PACK_LOADS 6
+#endif
+constexpr int PACK_LOADS = HUMID_PACK_LOADS;  // tuples per CTA: 4 x 16-byte loads in flight per thread while staging
 constexpr int PACK_ROWS_WIDE = 512;  // words of 32..63 letters: the tile still fits 48 KB of shared memory
 
 // Four characters at a time (SIMD inside a 32-bit register).  A=0 C=1 G=2 T=3
@@ -52,10 +59,22 @@ __global__ void __launch_bounds__(PACK_THREADS)
   const uint32_t bytes = rows * pp.n;
   const uint8_t *src = chars + t0 * pp.n;
   if ((((uintptr_t)src) & 15u) == 0) {
+    // PACK_LOADS 16-byte loads in flight per thread whatever the tile holds (a plain unrolled loop leaves the
+    // last vecs % (PACK_LOADS * PACK_THREADS) to a one-load-at-a-time remainder: 2x the time when that is all of them)
     const uint32_t vecs = bytes >> 4;
-#pragma unroll 6
-    for (uint32_t i = threadIdx.x; i < vecs; i += PACK_THREADS)
-      reinterpret_cast<uint4 *>(tile)[i] = ld_stream_u128(src + 16ull * i);
+    for (uint32_t base = 0; base < vecs; base += PACK_LOADS * PACK_THREADS) {
+      uint4 v[PACK_LOADS];
+#pragma unroll
+      for (int k = 0; k < PACK_LOADS; k++) {
+        const uint32_t i = base + k * PACK_THREADS + threadIdx.x;
+        if (i < vecs) v[k] = ld_stream_u128(src + 16ull * i);
+      }
+#pragma unroll
+      for (int k = 0; k < PACK_LOADS; k++) {
+        const uint32_t i = base + k * PACK_THREADS + threadIdx.x;
+        if (i < vecs) reinterpret_cast<uint4 *>(tile)[i] = v[k];
+      }
+    }
     for (uint32_t i = (vecs << 4) + threadIdx.x; i < bytes; i += PACK_THREADS) tile[i] = src[i];
   } else {
     for (uint32_t i = threadIdx.x; i < bytes; i += PACK_THREADS) tile[i] = src[i];
@@ -151,7 +170,10 @@ __device__ __forceinline__ void slot_cas(Slot *p, uint64_t cmp_lo, uint64_t cmp_
 // Trie::add of one tuple per thread.  The whole-slot CAS against the empty pattern either claims the slot (key, count 1,
 // first = this tuple: one L2 operation for a new word, where reading the slot, claiming the key and two more atomics
 // for count and first took four: 1.17 -> 0.93 ms at 50 M tuples) or returns what the slot holds.
-__global__ void __launch_bounds__(256)
+#ifndef HUMID_INSERT_THREADS
+#define HUMID_INSERT_THREADS 128  // 0.887 ms at 50 M tuples; 256: 0.934, 512: 1.044, 64: 0.889
+#endif
+__global__ void __launch_bounds__(HUMID_INSERT_THREADS)
     table_insert_kernel(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ tuple_index,
                         uint64_t n_tuples, Slot *slots, uint64_t mask, uint32_t index_base) {
   uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -311,7 +333,7 @@ static int table_insert(State &s, const uint64_t *keys, const uint32_t *index, u
     index = s.part_index.p;
   }
   Timed t(s, "table_insert", n, algo_bytes);
-  table_insert_kernel<<<grid_for(n, 256), 256, 0, s.stream>>>(keys, index, n, s.slots.p, s.table_cap - 1, index_base);
+  table_insert_kernel<<<grid_for(n, HUMID_INSERT_THREADS), HUMID_INSERT_THREADS, 0, s.stream>>>(keys, index, n, s.slots.p, s.table_cap - 1, index_base);
   return k + 1;
 }
 
