@@ -61,7 +61,10 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-constexpr uint32_t SMALL_COMP = 32;
+#ifndef HUMID_SMALL_COMP
+#define HUMID_SMALL_COMP 32
+#endif
+constexpr uint32_t SMALL_COMP = HUMID_SMALL_COMP;
 
 // comp[r] = root; csize[root] = number of members (singletons are not counted: csize stays 0)
 __global__ void uf_flatten_kernel(uint32_t *parent, uint32_t *comp, uint32_t *csize, uint64_t U,

@@ -87,7 +87,13 @@ __device__ __forceinline__ bool linked(uint64_t a, uint64_t b, uint32_t d) {
 //                   JOIN_CANDIDATES  as JOIN_DIRECTED, but every pair within Hamming distance d counts
 //                                    (no dominance rule)                                 (edit-distance candidates)
 // group_cap == JOIN_NO_CAP: every group is walked whatever its size, nothing is flagged.
-constexpr int JOIN_LOCAL_HITS = 6;
+#ifndef HUMID_JOIN_HITS
+#define HUMID_JOIN_HITS 4
+#endif
+#ifndef HUMID_JOIN_CTAS
+#define HUMID_JOIN_CTAS 4  // walk kernel at 32 registers: 4 CTAs of 512 per SM (0.44 + 0.47 -> 0.39 + 0.40 ms on the bench workload)
+#endif
+constexpr int JOIN_LOCAL_HITS = HUMID_JOIN_HITS;
 #ifndef HUMID_JOIN_THREADS
 #define HUMID_JOIN_THREADS 512
 #endif
@@ -180,7 +186,7 @@ __device__ __forceinline__ void hits_flush_cta(const HitBuf &hb, uint64_t i, uin
 // bit `block`) iff it has more than group_cap members; every member reaches the same verdict by
 // looking at most group_cap positions back and forth.
 template <int EMIT>
-__global__ void __launch_bounds__(JOIN_THREADS)
+__global__ void __launch_bounds__(JOIN_THREADS, HUMID_JOIN_CTAS)
     hamming_join_walk_kernel(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ rank, uint64_t U,
                              uint32_t d, const Blocks B, uint32_t block, uint64_t mask, uint32_t group_cap,
                              uint64_t *__restrict__ pairs, uint64_t cap, unsigned long long *__restrict__ counter,
