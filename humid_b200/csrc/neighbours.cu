@@ -93,6 +93,9 @@ __device__ __forceinline__ bool linked(uint64_t a, uint64_t b, uint32_t d) {
 #ifndef HUMID_JOIN_CTAS
 #define HUMID_JOIN_CTAS 4  // walk kernel at 32 registers: 4 CTAs of 512 per SM (0.44 + 0.47 -> 0.39 + 0.40 ms on the bench workload)
 #endif
+#ifndef HUMID_JOIN_WIDE_CTAS
+#define HUMID_JOIN_WIDE_CTAS 3  // 40 registers instead of 64: 0.46 + 0.67 -> 0.36 + 0.52 ms at -n 36 on the bench workload
+#endif
 constexpr int JOIN_LOCAL_HITS = HUMID_JOIN_HITS;
 #ifndef HUMID_JOIN_THREADS
 #define HUMID_JOIN_THREADS 512
@@ -374,7 +377,7 @@ __device__ __forceinline__ bool shares_earlier_block_wide(const WideBlocks &B, u
   return shared;
 }
 
-__global__ void __launch_bounds__(JOIN_THREADS)
+__global__ void __launch_bounds__(JOIN_THREADS, HUMID_JOIN_WIDE_CTAS)
     hamming_join_wide_kernel(const uint64_t *__restrict__ keys_hi, const uint64_t *__restrict__ keys_lo,
                              const uint32_t *__restrict__ rank, uint64_t U, uint32_t d, const WideBlocks B, uint32_t block,
                              uint64_t *__restrict__ pairs, uint64_t cap, unsigned long long *__restrict__ counter,
