@@ -309,10 +309,12 @@ int main(int argc, char **argv) {
       if (creator.joinable()) {  // first batch: the device must be there now
         creator.join();
         check(nullptr, create_rc, "humid_gpu_create");
+        bool locked = true;  // page-locking is an optimisation: without it the uploads are staged by the driver
         for (int j = 0; j < N_SLOTS; j++) {
-          check(gpu, humid_gpu_host_register(gpu, g.slots[j].chars, BATCH * g.n), "humid_gpu_host_register");
-          check(gpu, humid_gpu_host_register(gpu, g.slots[j].seg_len, BATCH * g.S * sizeof(uint16_t)), "humid_gpu_host_register");
+          locked &= humid_gpu_host_register(gpu, g.slots[j].chars, BATCH * g.n) == HUMID_GPU_OK;
+          locked &= humid_gpu_host_register(gpu, g.slots[j].seg_len, BATCH * g.S * sizeof(uint16_t)) == HUMID_GPU_OK;
         }
+        if (!locked && std::getenv("HUMID_TIMING")) std::cerr << "batch buffers could not be page-locked: " << humid_gpu_last_error(gpu) << "\n";
       }
       size_t m = BATCH;
       for (size_t r : s.rows) m = r < m ? r : m;
