@@ -1,0 +1,62 @@
+"""The HOST side of the `humid` executable (host/humid_main.cc: FastQ block parsing, .gz / BGZF input, batch assembly
+across files, the parallel output pass, file names, statistics files) against the UNMODIFIED reference binary, on a
+machine without a GPU: the executable is linked against tests/stub_humid_gpu.c, a test-only stand-in for libhumid_gpu
+that answers the C ABI from the CPU oracle.  The device path is checked by tests/test_gpu_cli.py through the real
+library; this file only makes the host logic part of the CPU suite."""
+import os
+import subprocess
+
+import pytest
+
+import oracle
+import test_gpu_cli as G
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CPU_CASES = [c for c in G.CASES if c[0] in ("c1_max", "c1_dir_gz", "c2_umifile", "c4_edit2", "n36_umifile", "no_dedup_output",
+                                            "c2_bgzf")]
+
+
+@pytest.fixture(scope="module")
+def humid_cpu(tmp_path_factory):
+    d = str(tmp_path_factory.mktemp("cpu_cli"))
+    lib = os.path.join(d, "libhumid_gpu.so")
+    subprocess.run(["gcc", "-O2", "-shared", "-fPIC", "-w", "-o", lib, os.path.join(ROOT, "tests", "stub_humid_gpu.c"),
+                    os.path.join(ROOT, "oracle", "humid_oracle.c")], check=True)
+    exe = os.path.join(d, "humid_cpu")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-pthread", "-o", exe, os.path.join(ROOT, "host", "humid_main.cc"),
+                    "-L" + d, "-lhumid_gpu", "-lz", "-Wl,-rpath," + d], check=True)
+    return exe
+
+
+@pytest.mark.skipif(not oracle.have_ref(), reason="reference binary not built on this machine")
+@pytest.mark.parametrize("name,ci,R,kw,flags,gz", CPU_CASES, ids=[c[0] for c in CPU_CASES])
+def test_host_side_matches_reference_binary(tmp_path, humid_cpu, name, ci, R, kw, flags, gz):
+    G.test_cli_matches_reference_binary(tmp_path, humid_cpu, name, ci, R, kw, flags, gz)
+
+
+def test_host_side_with_many_inflate_and_writer_threads(tmp_path, humid_cpu, monkeypatch):
+    """Batches of 2^20 tuples and output chunks of 2^16 records only show with a larger input: 150 000 tuples in BGZF
+    files, 3 inflate threads per file, against the same input as plain files."""
+    from humid_b200.synth import Synth, baseline_config
+    from test_host_reader import bgzf_bytes
+    cfg = baseline_config(1, 150_000)
+    files = list(Synth(cfg).write_fastq(str(tmp_path / "in"), prefix="x", gzip_output=False))
+    outs = {}
+    for kind in ("plain", "bgzf"):
+        use = files
+        if kind == "bgzf":
+            use = []
+            for f in files:
+                with open(f + ".gz", "wb") as out:
+                    out.write(bgzf_bytes(open(f, "rb").read(), 65000))
+                use.append(f + ".gz")
+            monkeypatch.setenv("HUMID_INFLATE_THREADS", "3")
+        d = str(tmp_path / kind)
+        subprocess.run([humid_cpu, *cfg.cli_flags(), "-s", "-a", "-d", d, "-l", str(tmp_path / (kind + ".log")), *use],
+                       check=True, timeout=600)
+        outs[kind] = {f.replace(".gz", ""): G.read_any(os.path.join(d, f)) for f in sorted(os.listdir(d))}
+    assert outs["plain"].keys() == outs["bgzf"].keys() and len(outs["plain"]) == 4 + 2 * len(files)
+    for f in outs["plain"]:
+        assert outs["plain"][f] == outs["bgzf"][f], f
+    dedup = [f for f in outs["plain"] if "_dedup" in f][0]
+    assert 0 < outs["plain"][dedup].count(b"\n") // 4 < 150_000
