@@ -148,7 +148,11 @@ Layout pre_compute(const vector<string> &files, size_t word_length) {
 
 // ---- pass 1: tuples of all files in lock step (readFiles / readFastq_, src/fastq.cc:37-47,
 // :96-114): the tuple stream ends as soon as any file runs out --------------------------------
-constexpr size_t BATCH = 1u << 20;  // tuples per upload
+#ifndef HUMID_BATCH
+#define HUMID_BATCH (1u << 20)
+#endif
+constexpr size_t BATCH = HUMID_BATCH;  // tuples per upload (a multiple of REWRITE_CHUNK; the tests build with a small one)
+static_assert(BATCH % REWRITE_CHUNK == 0, "a batch must hold whole output chunks");
 constexpr int N_SLOTS = 8;  // batches the readers may run ahead: they start while the device is still being brought up
 
 struct Slot {

@@ -23,7 +23,8 @@ def humid_cpu(tmp_path_factory):
     subprocess.run(["gcc", "-O2", "-shared", "-fPIC", "-w", "-o", lib, os.path.join(ROOT, "tests", "stub_humid_gpu.c"),
                     os.path.join(ROOT, "oracle", "humid_oracle.c")], check=True)
     exe = os.path.join(d, "humid_cpu")
-    subprocess.run(["g++", "-O2", "-std=c++17", "-pthread", "-o", exe, os.path.join(ROOT, "host", "humid_main.cc"),
+    # small batches and output chunks: every case runs over several of both
+    subprocess.run(["g++", "-O2", "-std=c++17", "-pthread", "-DHUMID_BATCH=2048", "-DHUMID_REWRITE_CHUNK=512", "-o", exe, os.path.join(ROOT, "host", "humid_main.cc"),
                     "-L" + d, "-lhumid_gpu", "-lz", "-Wl,-rpath," + d], check=True)
     return exe
 
@@ -35,8 +36,8 @@ def test_host_side_matches_reference_binary(tmp_path, humid_cpu, name, ci, R, kw
 
 
 def test_host_side_with_many_inflate_and_writer_threads(tmp_path, humid_cpu, monkeypatch):
-    """Batches of 2^20 tuples and output chunks of 2^16 records only show with a larger input: 150 000 tuples in BGZF
-    files, 3 inflate threads per file, against the same input as plain files."""
+    """150 000 tuples (73 batches of 2048, 293 output chunks of 512 in this build) in BGZF files with 3 inflate threads per
+    file, against the same input as plain files."""
     from humid_b200.synth import Synth, baseline_config
     from test_host_reader import bgzf_bytes
     cfg = baseline_config(1, 150_000)
