@@ -103,3 +103,45 @@ def test_odd_fastq_files_like_the_reference_binary(tmp_path, humid_cpu, case, gz
     assert sorted(os.listdir(ours)) == names
     for f in names:
         assert G.read_any(os.path.join(ours, f)) == G.read_any(os.path.join(ref, f)), f
+
+
+LAYOUTS = [  # (name, records per file, drop the first record (so that the first header carries a UMI), flags)
+    ("one_file", [200], False, ["-n", "12"]),
+    ("one_file_header_umi", [200], True, ["-n", "14"]),
+    ("two_files_m2", [200, 200], True, ["-n", "16", "-m", "2"]),
+    ("three_files_third_shorter_max", [150, 150, 90], True, ["-n", "21", "-x"]),
+    ("two_files_edit", [150, 150], False, ["-n", "10", "-e"]),
+    ("two_files_edit2_header_umi", [120, 120], True, ["-n", "13", "-e", "-m", "2"]),
+    ("wide_header_umi", [150, 150], True, ["-n", "40"]),
+    ("distance_zero", [200], False, ["-n", "8", "-m", "0"]),
+    ("umi_longer_than_word", [100, 100], True, ["-n", "5"]),
+    ("annotate_only", [100, 100], False, ["-n", "12", "-q"]),
+]
+
+
+@pytest.mark.skipif(not oracle.have_ref(), reason="reference binary not built on this machine")
+@pytest.mark.parametrize("name,counts,drop_first,flags", LAYOUTS, ids=[c[0] for c in LAYOUTS])
+def test_word_layouts_like_the_reference_binary(tmp_path, humid_cpu, name, counts, drop_first, flags):
+    """preCompute's split of the word over header UMI and files (remainder to the last file), header UMI found or
+    not, files of different lengths (the tuple stream ends with the shortest), reads shorter than their share and
+    reads with N (filtered): every output file as the reference binary writes it."""
+    import numpy as np
+    from test_host_reader import records
+
+    rng = np.random.default_rng(len(name))
+    files = []
+    for i, n in enumerate(counts):
+        f = str(tmp_path / f"r{i + 1}.fastq")
+        with open(f, "wb") as fh:
+            fh.write(b"".join(records(n + 1, rng)[1 if drop_first else 0:][:n]))
+        files.append(f)
+    ours, ref = str(tmp_path / "ours"), str(tmp_path / "ref")
+    os.makedirs(ref)
+    subprocess.run([humid_cpu, *flags, "-s", "-a", "-d", ours, "-l", str(tmp_path / "ours.log"), *files], check=True, timeout=300)
+    subprocess.run([oracle.REF_HUMID, *flags, "-s", "-a", "-d", ref, "-l", os.path.join(ref, "humid.log"), *files], check=True,
+                   timeout=300)
+    names = sorted(os.listdir(ref))
+    names.remove("humid.log")
+    assert sorted(os.listdir(ours)) == names
+    for f in names:
+        assert open(os.path.join(ours, f), "rb").read() == open(os.path.join(ref, f), "rb").read(), f
