@@ -145,3 +145,29 @@ def test_word_layouts_like_the_reference_binary(tmp_path, humid_cpu, name, count
     assert sorted(os.listdir(ours)) == names
     for f in names:
         assert open(os.path.join(ours, f), "rb").read() == open(os.path.join(ref, f), "rb").read(), f
+
+
+@pytest.mark.skipif(not oracle.have_ref(), reason="reference binary not built on this machine")
+@pytest.mark.parametrize("fname,outdir", [("sample.R1.fastq", "out/"), ("a.b.c.fq", "deep/er/dir"), (".hidden.fastq", "out")])
+def test_output_file_names_like_the_reference_binary(tmp_path, humid_cpu, fname, outdir):
+    """makeFileName (src/fastq.cc:170-181): the suffix goes in front of the FIRST dot of the base name; the output
+    directory is created with its parents.  (A name without any dot makes the reference throw std::out_of_range from
+    substr; this executable writes <name>_dedup there — not compared.)"""
+    import numpy as np
+    from test_host_reader import records
+
+    src = tmp_path / "in"
+    src.mkdir()
+    f = str(src / fname)
+    with open(f, "wb") as fh:
+        fh.write(b"".join(records(60, np.random.default_rng(4))))
+    listing = {}
+    for who, exe in (("ours", humid_cpu), ("ref", oracle.REF_HUMID)):
+        top = tmp_path / who
+        top.mkdir()
+        subprocess.run([exe, "-n", "10", "-s", "-a", "-d", outdir, "-l", "run.log", f], check=True, timeout=120, cwd=str(top))
+        listing[who] = sorted(os.path.relpath(os.path.join(d, x), str(top)) for d, _, fs in os.walk(str(top)) for x in fs)
+    assert listing["ours"] == listing["ref"]
+    for rel in listing["ref"]:
+        if not rel.endswith("run.log"):
+            assert open(tmp_path / "ours" / rel, "rb").read() == open(tmp_path / "ref" / rel, "rb").read(), rel
