@@ -273,6 +273,12 @@ class Dedup:
                     "debug_neighbours")
         return row_ptr, col[: n.value]
 
+    def n_entries(self) -> int:
+        """Directed neighbour-list entries (sum of NLeaf::neighbours sizes)."""
+        n = C.c_uint64(0)
+        self._check(self._L.humid_gpu_debug_neighbours(self._h, None, None, C.byref(n)), "debug_neighbours")
+        return int(n.value)
+
     def clusters(self) -> Tuple[np.ndarray, np.ndarray]:
         Cn = self.counts()["clusters"]
         size = np.zeros(max(Cn, 1), dtype=np.uint64)

@@ -23,11 +23,28 @@ def sources():
     return sorted(glob.glob(os.path.join(CSRC, "*.cu")))
 
 
+STAMP = os.path.join(HERE, "build", "flags.stamp")
+
+
+def extra_flags():
+    """A/B builds: HUMID_NVCC_EXTRA="-DHUMID_RS_ITEMS=16 ..." — part of the staleness check below."""
+    return os.environ.get("HUMID_NVCC_EXTRA", "").split()
+
+
+def flags_signature() -> str:
+    return " ".join(NVCC_FLAGS + extra_flags())
+
+
 def needs_build() -> bool:
     if not os.path.exists(LIB):
         return True
+    try:
+        if open(STAMP).read() != flags_signature():
+            return True
+    except OSError:
+        return True
     t = os.path.getmtime(LIB)
-    deps = sources() + glob.glob(os.path.join(CSRC, "*.cuh")) + [os.path.join(HERE, "..", "include", "humid_gpu.h")]
+    deps = sources() + glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(HERE, "..", "include", "*.h"))
     return any(os.path.getmtime(d) > t for d in deps)
 
 
@@ -41,7 +58,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     for src in sources():
         obj = os.path.join(objdir, os.path.basename(src)[:-3] + ".o")
         objs.append(obj)
-        cmd = [nvcc, *NVCC_FLAGS, "-c", src, "-o", obj] + (["-Xptxas", "-v"] if verbose else [])
+        cmd = [nvcc, *NVCC_FLAGS, *extra_flags(), "-c", src, "-o", obj] + (["-Xptxas", "-v"] if verbose else [])
         procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     for cmd, p in procs:
         out, _ = p.communicate()
@@ -51,6 +68,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
             raise RuntimeError("nvcc failed: " + " ".join(cmd))
     cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB, *objs, "-cudart", "static"]
     subprocess.run(cmd, check=True)
+    with open(STAMP, "w") as f:
+        f.write(flags_signature())
     return LIB
 
 

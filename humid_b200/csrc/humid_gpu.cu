@@ -122,6 +122,7 @@ int humid_gpu_reset(humid_gpu *h) {
     s.part = 0;
     s.n_parts = 1;
     for (int i = 0; i < 3; i++) s.hist_done[i] = false;
+    s.hist_pending = false;
     HUMID_CUDA(cudaMemsetAsync(s.counters.p, 0, 64 * sizeof(unsigned long long), s.stream));
   });
 }
@@ -238,12 +239,14 @@ int humid_gpu_finalize(humid_gpu *h) {
     }
     stage_cluster(s);
     stage_keep(s);
+    stage_histograms_enqueue(s);  // runStatistics / clusterStats (src/humid.cc:301-315, src/cluster.cc:89-95)
     // writeFiltered asks for the whole bitmap next: it travels while the stream drains
     s.keep_host_words = (s.report_tuples + 31) / 32 + 2;
     s.keep_host.ensure(s.keep_host_words);
     HUMID_CUDA(cudaMemcpyAsync(s.keep_host.p, s.keep_bits.p, s.keep_host_words * sizeof(uint32_t), cudaMemcpyDeviceToHost,
                                s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    stage_histograms_collect(s);
     resolve_stats(s);
     s.finalized = true;
   });

@@ -97,6 +97,70 @@ __global__ void __launch_bounds__(256)
     if (h[k]) atomicAdd(bins + k, (unsigned long long)h[k]);
 }
 
+// bins + listed large values of the three histograms -> host vectors in ascending key order (std::map order of the
+// reference, src/humid.cc:328-349)
+static void hist_to_vectors(State &s, int which, const unsigned long long *bins, uint64_t *large, uint64_t n_large) {
+  s.hist_k[which].clear();
+  s.hist_v[which].clear();
+  for (uint32_t v = 0; v < HIST_SMALL; v++)
+    if (bins[v]) {
+      s.hist_k[which].push_back(v);
+      s.hist_v[which].push_back(bins[v]);
+    }
+  std::sort(large, large + n_large);
+  for (uint64_t i = 0; i < n_large;) {
+    uint64_t j = i;
+    while (j < n_large && large[j] == large[i]) j++;
+    s.hist_k[which].push_back(large[i]);
+    s.hist_v[which].push_back(j - i);
+    i = j;
+  }
+  s.hist_done[which] = true;
+}
+
+static const char *const HIST_NAMES[3] = {"hist_counts", "hist_neigh", "hist_clusters"};
+
+// runStatistics + clusterStats as part of finalize: the three kernels are enqueued behind the clustering, their bins
+// (and up to HIST_EAGER_LARGE listed values each) travel to page-locked host memory with the keep bitmap, and
+// stage_histograms_collect turns them into the (key, value) lists once finalize has synchronised — no extra host
+// round trip.  A histogram with more large values than that is recomputed on demand (stage_histogram).
+constexpr uint64_t HIST_EAGER_LARGE = 1 << 13;
+constexpr uint64_t HIST_EAGER_STRIDE = HIST_SMALL + HIST_EAGER_LARGE + 1;  // bins, n_large, large values
+
+int stage_histograms_enqueue(State &s) {
+  int k = 0;
+  s.hist_dev.ensure(3 * HIST_EAGER_STRIDE);
+  s.hist_host.ensure(3 * HIST_EAGER_STRIDE);
+  HUMID_CUDA(cudaMemsetAsync(s.hist_dev.p, 0, 3 * HIST_EAGER_STRIDE * sizeof(unsigned long long), s.stream));
+  for (int which = 0; which < 3; which++) {
+    s.hist_done[which] = false;
+    const uint64_t m = which == HUMID_HIST_CLUSTERS ? s.n_clusters : s.unique;
+    if (m == 0) continue;
+    unsigned long long *d = s.hist_dev.p + which * HIST_EAGER_STRIDE;
+    Timed t(s, HIST_NAMES[which], m, m * (which == HUMID_HIST_COUNTS ? 4 : 8));
+    hist_small_kernel<<<grid_for(m, 256, HIST_ITEMS), 256, 0, s.stream>>>(
+        which, m, s.word_count.p, s.row_ptr.p, s.cluster_size.p, d, reinterpret_cast<uint64_t *>(d + HIST_SMALL + 1),
+        HIST_EAGER_LARGE, d + HIST_SMALL);
+    k++;
+  }
+  HUMID_CUDA(cudaGetLastError());
+  HUMID_CUDA(cudaMemcpyAsync(s.hist_host.p, s.hist_dev.p, 3 * HIST_EAGER_STRIDE * sizeof(unsigned long long),
+                             cudaMemcpyDeviceToHost, s.stream));
+  s.hist_pending = true;
+  return k;
+}
+
+void stage_histograms_collect(State &s) {
+  if (!s.hist_pending) return;
+  s.hist_pending = false;
+  for (int which = 0; which < 3; which++) {
+    unsigned long long *hst = s.hist_host.p + which * HIST_EAGER_STRIDE;
+    const uint64_t n_large = hst[HIST_SMALL];
+    if (n_large > HIST_EAGER_LARGE) continue;  // stays !hist_done: recomputed when asked for
+    hist_to_vectors(s, which, hst, reinterpret_cast<uint64_t *>(hst + HIST_SMALL + 1), n_large);
+  }
+}
+
 int stage_histogram(State &s, int which) {
   const uint64_t m = which == HUMID_HIST_CLUSTERS ? s.n_clusters : s.unique;
   s.hist_k[which].clear();
@@ -104,8 +168,7 @@ int stage_histogram(State &s, int which) {
   s.hist_done[which] = true;
   if (m == 0) return 0;
   int k = 0;
-  static const char *names[3] = {"hist_counts", "hist_neigh", "hist_clusters"};
-  Timed t(s, names[which], m, m * (which == HUMID_HIST_COUNTS ? 4 : 8));
+  Timed t(s, HIST_NAMES[which], m, m * (which == HUMID_HIST_COUNTS ? 4 : 8));
   std::vector<unsigned long long> bins(HIST_SMALL);
   std::vector<uint64_t> large;
   uint64_t cap = 1 << 16;
@@ -131,19 +194,7 @@ int stage_histogram(State &s, int which) {
     }
     break;
   }
-  for (uint32_t v = 0; v < HIST_SMALL; v++)
-    if (bins[v]) {
-      s.hist_k[which].push_back(v);
-      s.hist_v[which].push_back(bins[v]);
-    }
-  std::sort(large.begin(), large.end());
-  for (size_t i = 0; i < large.size();) {
-    size_t j = i;
-    while (j < large.size() && large[j] == large[i]) j++;
-    s.hist_k[which].push_back(large[i]);
-    s.hist_v[which].push_back(j - i);
-    i = j;
-  }
+  hist_to_vectors(s, which, bins.data(), large.data(), large.size());
   t.launches = k;
   return k;
 }

@@ -194,6 +194,9 @@ struct State {
   DevBuf<uint32_t> out_ids;
   std::vector<uint64_t> hist_k[3], hist_v[3];
   bool hist_done[3] = {false, false, false};
+  DevBuf<unsigned long long> hist_dev;    // finalize: bins + listed large values of the three histograms
+  HostBuf<unsigned long long> hist_host;  // ... on their way to the host with the keep bitmap
+  bool hist_pending = false;
 
   Scratch scratch, scan_scratch;
   std::vector<StageStat> stats;
@@ -280,6 +283,8 @@ int stage_cluster(State &s);           // components, replay, ids, sizes, maxLea
 int stage_cluster_number(State &s);    // seed flags -> cluster ids, compacted size / maxLeaf
 int stage_keep(State &s);              // keep bitmap
 int stage_cluster_ids(State &s, uint64_t first, uint64_t n, uint32_t *d_out);
-int stage_histogram(State &s, int which);
+int stage_histogram(State &s, int which);        // one histogram, synchronously (shard mode, overflow of the eager form)
+int stage_histograms_enqueue(State &s);          // all three behind the clustering, results to page-locked host memory
+void stage_histograms_collect(State &s);         // ... turned into (key, value) lists after the stream has been synchronised
 
 }  // namespace humid

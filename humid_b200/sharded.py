@@ -323,7 +323,13 @@ def all_gather_v(comm, t: torch.Tensor, sizes: Sequence[int]) -> torch.Tensor:
     return torch.cat([buf[r * m: r * m + sizes[r]] for r in range(comm.world)])
 
 
+def make_sharded(**kw):
+    """The multi-GPU path bench.py and the tests use: one instance per rank (torch.distributed already initialised)."""
+    return ShardedDedup(**kw)
+
+
 class ShardedDedup:
+    transport = "NCCL all-to-all-v / all-gather (torch.distributed)"
     """Same call sequence as `api.Dedup` (add_batch* … finalize … results), one instance per
     rank; rank r's tuples are the r-th contiguous slice of the job's input order."""
 

@@ -465,8 +465,9 @@ class HashSynth:
             out[a - lo: b - lo] = table[torch.cat(parts, dim=1).long()]
         return out
 
-    def write_fastq(self, directory: str, prefix: Optional[str] = None, chunk: int = 250_000) -> List[str]:
-        """FastQ files (CPU) of the whole configuration, for the reference binary."""
+    def write_fastq(self, directory: str, prefix: Optional[str] = None, chunk: int = 250_000, device="cpu") -> List[str]:
+        """FastQ files of the whole configuration, for the executables (the same bytes whatever `device` the
+        letters are drawn on)."""
         cfg = self.cfg
         prefix = prefix or cfg.name
         os.makedirs(directory, exist_ok=True)
@@ -478,7 +479,7 @@ class HashSynth:
         try:
             for lo in range(0, cfg.n_tuples, chunk):
                 hi = min(cfg.n_tuples, lo + chunk)
-                umi, m1, m2 = (letters[x.numpy()] for x in self._mates(lo, hi, READ_LEN, "cpu"))
+                umi, m1, m2 = (letters[x.cpu().numpy()] for x in self._mates(lo, hi, READ_LEN, device))
                 ids = np.arange(lo, hi, dtype=np.int64)
                 for fi, seq in enumerate((m1, m2)):
                     files[fi].write(_records(_headers(cfg, ids, umi, fi + 1), seq).tobytes())

@@ -18,6 +18,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "_build", "liboracle.so")
 REF_HUMID = os.path.join(HERE, "_ref", "humid")
 REF_PROBE = os.path.join(HERE, "_ref", "trie_probe")
+REF_HOTPATH = os.path.join(HERE, "_ref", "hotpath_probe")
 REFERENCE_ROOT = "/root/reference"
 INVALID = np.uint64(0xFFFFFFFFFFFFFFFF)
 MAX_NARROW = 31  # longest word held in one uint64 (the spare top bit keeps INVALID unambiguous)
@@ -316,6 +317,41 @@ def run_ref_humid(files: Sequence[str], out_dir: str, flags: Sequence[str], stat
     t0 = time.monotonic()
     subprocess.run(cmd, check=True, preexec_fn=pre, timeout=timeout)
     return {"wall_s": time.monotonic() - t0}
+
+
+def run_ref_hotpath(chars: np.ndarray, header_umi: int, nt_to_take: Sequence[int], distance: int, edit: bool,
+                    maximum: bool, work_dir: str, timeout: Optional[float] = None) -> Dict:
+    """The reference's hot path from host memory (oracle/_ref/hotpath_probe = oracle/ref_hotpath.cc around the
+    unmodified src/humid.cc): word characters in the C ABI's layout in, counts / keep mask / statistics files and
+    seconds per phase out.  Returns the probe's JSON plus 'keep' (bool[n]), 'stats' ({file: text}) and 'wall_s'."""
+    import json
+    import resource
+    import time
+
+    chars = np.ascontiguousarray(chars, dtype=np.uint8)
+    n, wl = chars.shape
+    os.makedirs(work_dir, exist_ok=True)
+    path = os.path.join(work_dir, "chars.bin")
+    chars.tofile(path)
+    prefix = os.path.join(work_dir, "ref")
+    cmd = [REF_HOTPATH, path, str(n), str(wl), str(distance), str(int(edit)), str(int(maximum)), str(header_umi), prefix,
+           *[str(int(t)) for t in nt_to_take]]
+
+    def pre():
+        try:
+            resource.setrlimit(resource.RLIMIT_STACK, (resource.RLIM_INFINITY, resource.RLIM_INFINITY))
+        except (ValueError, OSError):
+            pass
+
+    t0 = time.monotonic()
+    p = subprocess.run(cmd, check=True, preexec_fn=pre, timeout=timeout, capture_output=True, text=True)
+    out = json.loads(p.stdout.strip().splitlines()[-1])
+    out["wall_s"] = time.monotonic() - t0
+    out["keep"] = np.unpackbits(np.fromfile(prefix + ".keep", dtype=np.uint8), bitorder="little")[:n].astype(bool)
+    out["stats"] = {f: open(prefix + "." + f).read() for f in ("counts.dat", "neigh.dat", "clusters.dat")}
+    out["stats"]["stats.dat"] = (f"total: {out['total']}\nusable: {out['usable']}\nunique: {out['unique']}\n"
+                                 f"clusters: {out['clusters']}\n")
+    return out
 
 
 def get_nucleotides(header: str, seqs: Sequence[str], nt_to_take: Sequence[int], header_umi_size: int) -> str:

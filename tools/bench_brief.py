@@ -19,4 +19,12 @@ for line in sys.stdin:
         print(" ".join(f"{k}={v}" for k, v in (r.get("stages_ms") or {}).items()))
     if d.get("cpu_baseline"):
         print("cpu", d["cpu_baseline"])
-    print("clocks", d.get("clocks"), "result", d["config"].get("result"))
+    print("clocks", d.get("clocks"), "result", (d.get("detail") or d["config"]).get("result"))
+    if r.get("kernels_8d"):
+        print("8(d) families:", {k: (v["ms"], round(v["frac"], 3) if v["frac"] else None) for k, v in r["kernels_8d"].items()})
+        print("pass_frac", round(r.get("pass_frac", 0), 3), "traffic_ratio", r.get("traffic_ratio"), "step", r.get("step"))
+    if d.get("parity"):
+        print("parity", d["parity"])
+    for leg in d.get("cli_e2e") or []:
+        print("cli", leg["config"], leg["tuples"], leg["seconds"], "s", round(leg["pairs_per_s"]), "pairs/s", leg["breakdown_s"],
+              leg["outputs_sha256"][:12], leg.get("identical_to_other_arm"))
