@@ -266,9 +266,9 @@ def cli_leg(kind, ci, R, device="cpu", reps=1):
                         breakdown[nm.strip()] = round(float(rest[:-3]) / 1e3, 3)
                     except ValueError:
                         pass
-        times.append(t)
-    times.sort()
-    sec = times[len(times) // 2]
+        times.append((t, breakdown))
+    times.sort(key=lambda x: x[0])
+    sec, breakdown = times[len(times) // 2]
     digest, per = output_digest(out, out_names)
     shutil.rmtree(out, ignore_errors=True)
     leg = {"config": cfg.name, "flags": " ".join(flags + ["-s"]), "tuples": R, "fastq_bytes": size, "seconds": round(sec, 3),

@@ -13,8 +13,9 @@
 // exclusive scan over the seed flags in rank order (ids are handed out in walk order of
 // the seeding word, src/humid.cc:180).
 #include <algorithm>
+#include <cstdlib>
 
-#include "state.cuh"
+#include "cluster.cuh"
 
 namespace humid {
 
@@ -61,10 +62,22 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-#ifndef HUMID_SMALL_COMP
-#define HUMID_SMALL_COMP 32
-#endif
-constexpr uint32_t SMALL_COMP = HUMID_SMALL_COMP;
+// The same over the undirected pair list the Hamming join leaves behind (one thread per pair: every lane has an
+// edge, where the row form above keeps a lane per word and two words in three have no neighbour).
+__global__ void __launch_bounds__(256)
+    uf_union_pairs_kernel(const uint64_t *__restrict__ pairs, uint64_t P, uint32_t *parent) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P) return;
+  const uint64_t e = ld_stream_u64(pairs + i);
+  uint32_t x = (uint32_t)(e >> 32), y = (uint32_t)e;
+  while (true) {
+    x = uf_find(parent, x);
+    y = uf_find(parent, y);
+    if (x == y) break;
+    if (x > y) { uint32_t t = x; x = y; y = t; }
+    if (atomicCAS(parent + y, y, x) == y) break;
+  }
+}
 
 // comp[r] = root; csize[root] = number of members (singletons are not counted: csize stays 0)
 __global__ void uf_flatten_kernel(uint32_t *parent, uint32_t *comp, uint32_t *csize, uint64_t U,
@@ -79,19 +92,57 @@ __global__ void uf_flatten_kernel(uint32_t *parent, uint32_t *comp, uint32_t *cs
   }
 }
 
-// ---- (2) members of the LARGE components, grouped by a global sort ---------------------------
+// ---- (2) every word by the size of its component ---------------------------------------------
+// singletons are closed in place; the roots of components of 2..SMALL_COMP words go to a dense list (one busy thread
+// per lane in the replay, where one thread per WORD left 27 of 32 lanes idle); the words of larger components are
+// listed as (root, rank) keys and grouped by a sort.
+template <bool MAXIMUM>
 __global__ void __launch_bounds__(256)
-    big_member_keys_kernel(const uint32_t *__restrict__ comp, const uint32_t *__restrict__ csize, uint64_t U,
-                           uint64_t *__restrict__ keys, unsigned long long *__restrict__ counter) {
-  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  bool big = r < U && csize[comp[r]] + 1u > SMALL_COMP;
-  unsigned m = __ballot_sync(0xffffffffu, big);
-  if (m == 0) return;
-  unsigned long long base = 0;
-  int leader = __ffs(m) - 1;
-  if ((int)lane_id() == leader) base = atomicAdd(counter, (unsigned long long)__popc(m));
-  base = __shfl_sync(0xffffffffu, base, leader);
-  if (big) keys[base + __popc(m & ((1u << lane_id()) - 1u))] = ((uint64_t)comp[r] << 32) | (uint32_t)r;
+    classify_words_kernel(const uint32_t *__restrict__ comp, const uint32_t *__restrict__ csize,
+                          const uint32_t *__restrict__ count, uint64_t U, uint32_t small_max,
+                          const uint32_t *__restrict__ skip_root, uint32_t *__restrict__ label, uint32_t *__restrict__ seed_flag, uint64_t *__restrict__ seed_size,
+                          uint32_t *__restrict__ seed_max, uint32_t *__restrict__ small_roots,
+                          unsigned long long *__restrict__ n_small, uint64_t *__restrict__ big_keys,
+                          unsigned long long *__restrict__ n_big) {
+  const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  bool small = false, big = false;
+  uint32_t root = 0;
+  if (r < U) {
+    root = comp[r];
+    const bool skipped = skip_root && skip_root[root];  // shard mode: the component continues on another shard
+    if (MAXIMUM) {
+      label[r] = root;
+      seed_flag[r] = (!skipped && root == r) ? 1u : 0u;
+    }
+    if (!skipped) {
+      const uint32_t m = csize[root] + 1u;
+      if (m == 1) {  // no neighbours: its own cluster
+        if (!MAXIMUM) { label[r] = (uint32_t)r; seed_flag[r] = 1; }
+        seed_size[r] = count[r];
+        seed_max[r] = (uint32_t)r;
+      } else if (m <= small_max) {
+        small = root == r;
+      } else {
+        big = true;
+      }
+    }
+  }
+  const uint32_t lane = lane_id(), lt = (1u << lane) - 1u;
+  const unsigned ms = __ballot_sync(0xffffffffu, small), mb = __ballot_sync(0xffffffffu, big);
+  if (ms) {
+    unsigned long long base = 0;
+    const int leader = __ffs(ms) - 1;
+    if ((int)lane == leader) base = atomicAdd(n_small, (unsigned long long)__popc(ms));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (small) small_roots[base + __popc(ms & lt)] = (uint32_t)r;
+  }
+  if (mb) {
+    unsigned long long base = 0;
+    const int leader = __ffs(mb) - 1;
+    if ((int)lane == leader) base = atomicAdd(n_big, (unsigned long long)__popc(mb));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (big) big_keys[base + __popc(mb & lt)] = ((uint64_t)root << 32) | (uint32_t)r;
+  }
 }
 
 __global__ void big_segments_kernel(const uint64_t *__restrict__ sorted, uint64_t n, uint32_t *__restrict__ members,
@@ -102,14 +153,6 @@ __global__ void big_segments_kernel(const uint64_t *__restrict__ sorted, uint64_
   members[i] = (uint32_t)sorted[i];
   if (i == 0 || (uint32_t)(sorted[i - 1] >> 32) != c) seg_start[c] = (uint32_t)i;
 }
-
-struct Graph {
-  const uint64_t *row_ptr;
-  const uint32_t *col;
-  const uint32_t *count;
-  uint32_t base;  // columns are stored as rank + base (shard mode: global ranks), rows are 0-based
-};
-__device__ __forceinline__ uint32_t gcol(const Graph &g, uint64_t e) { return g.col[e] - g.base; }
 
 // Members of the component of `root` (m of them) in rank order, collected by a breadth-first
 // walk of the neighbour lists into `arr` (capacity SMALL_COMP) and sorted there.
@@ -236,48 +279,24 @@ __device__ void replay_directional(const Graph &g, const uint32_t *mem, uint32_t
   }
 }
 
-// One thread per word; only component roots work.  Singletons are closed in place, small
-// components are gathered and replayed in local memory, large ones use the globally sorted
-// member array (big_members / big_start) and global work arrays of the same length.
+// One thread per component of 2..SMALL_COMP words (dense list of their roots): members gathered and replayed in
+// local memory.
 template <bool MAXIMUM>
 #ifndef HUMID_REPLAY_THREADS
 #define HUMID_REPLAY_THREADS 128
 #endif
 __global__ void __launch_bounds__(HUMID_REPLAY_THREADS)
-    replay_kernel(Graph g, uint64_t U, const uint32_t *__restrict__ comp, const uint32_t *__restrict__ csize,
-                  const uint32_t *__restrict__ big_members, const uint32_t *__restrict__ big_start,
-                  uint32_t *__restrict__ big_work_a, uint32_t *__restrict__ big_work_b, uint32_t *visited,
-                  uint32_t *label, uint32_t *__restrict__ seed_flag, uint64_t *__restrict__ seed_size,
-                  uint32_t *__restrict__ seed_max, const uint32_t *__restrict__ skip_root) {
-  const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (r >= U) return;
-  const uint32_t root = comp[r];
-  if (skip_root && skip_root[root]) {  // shard mode: component continues on another shard, replayed later
-    if (MAXIMUM) seed_flag[r] = 0;
-    return;
-  }
-  if (MAXIMUM) {
-    label[r] = root;
-    seed_flag[r] = root == r ? 1u : 0u;
-  }
-  if (root != r) return;
+    replay_small_kernel(Graph g, const uint32_t *__restrict__ roots, uint64_t n_roots, const uint32_t *__restrict__ csize,
+                        uint32_t *visited, uint32_t *label, uint32_t *__restrict__ seed_flag,
+                        uint64_t *__restrict__ seed_size, uint32_t *__restrict__ seed_max) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_roots) return;
+  const uint32_t r = roots[i];
   const uint32_t m = csize[r] + 1u;
-  if (m == 1) {  // no neighbours: its own cluster
-    if (!MAXIMUM) { label[r] = (uint32_t)r; seed_flag[r] = 1; }
-    seed_size[r] = g.count[r];
-    seed_max[r] = (uint32_t)r;
-    return;
-  }
-  if (m <= SMALL_COMP) {
-    uint32_t mem[SMALL_COMP], wa[SMALL_COMP], wb[SMALL_COMP];
-    gather_small_component(g, (uint32_t)r, m, mem);
-    if (MAXIMUM) replay_maximum(g, mem, m, wa, wb, visited, seed_size + r, seed_max + r);
-    else replay_directional(g, mem, m, wa, label, seed_flag, seed_size, seed_max);
-  } else {
-    const uint32_t s0 = big_start[r];
-    if (MAXIMUM) replay_maximum(g, big_members + s0, m, big_work_a + s0, big_work_b + s0, visited, seed_size + r, seed_max + r);
-    else replay_directional(g, big_members + s0, m, big_work_a + s0, label, seed_flag, seed_size, seed_max);
-  }
+  uint32_t mem[SMALL_COMP], wa[SMALL_COMP], wb[SMALL_COMP];
+  gather_small_component(g, r, m, mem);
+  if (MAXIMUM) replay_maximum(g, mem, m, wa, wb, visited, seed_size + r, seed_max + r);
+  else replay_directional(g, mem, m, wa, label, seed_flag, seed_size, seed_max);
 }
 
 // ---- (4) ids ----------------------------------------------------------------------------
@@ -297,7 +316,7 @@ int stage_cluster(State &s) {
   s.n_clusters = 0;
   if (U == 0) return 0;
   int k = 0;
-  const unsigned g256 = grid_for(U, 256), g128 = grid_for(U, HUMID_REPLAY_THREADS);
+  const unsigned g256 = grid_for(U, 256);
   s.comp.ensure(U);
   s.label.ensure(U);
   s.work_a.ensure(U);
@@ -316,28 +335,76 @@ int stage_cluster(State &s) {
       HUMID_CUDA(cudaMemsetAsync(s.comp_open.p, 0, U * sizeof(uint32_t), s.stream));
       open_flag = s.open_flag.p;
     }
-    uf_union_kernel<<<g256, 256, 0, s.stream>>>(s.row_ptr.p, s.col.p, s.n_entries, U, s.cluster_col_base, open_flag,
-                                                s.work_a.p);
+    if (s.cluster_pairs && !s.cluster_skip_open && s.cluster_col_base == 0) {
+      if (s.n_cluster_pairs)
+        uf_union_pairs_kernel<<<grid_for(s.n_cluster_pairs, 256), 256, 0, s.stream>>>(s.cluster_pairs, s.n_cluster_pairs,
+                                                                                       s.work_a.p);
+    } else {
+      uf_union_kernel<<<g256, 256, 0, s.stream>>>(s.row_ptr.p, s.col.p, s.n_entries, U, s.cluster_col_base, open_flag,
+                                                  s.work_a.p);
+    }
     uf_flatten_kernel<<<g256, 256, 0, s.stream>>>(s.work_a.p, s.comp.p, csize, U, open_flag, s.comp_open.p);
     t.launches = 3;
   }
   k += 3;
 
-  // words of large components, grouped by component in rank order (usually none)
-  uint64_t n_big = 0;
+  s.seed_flag.ensure(U);
+  s.seed_index.ensure(U);
+  s.seed_size.ensure(U);
+  s.seed_max.ensure(U);
   s.seg_start.ensure(U);
+  s.key_alt.ensure(U + 1);
+  s.work_b.ensure(U + 1);  // roots of the small components
+  Graph g{s.row_ptr.p, s.col.p, s.word_count.p, s.cluster_col_base};
+  const uint32_t *skip_root = s.cluster_skip_open ? s.comp_open.p : nullptr;
+  // components of up to SMALL_COMP words are replayed by one thread each; HUMID_GPU_SMALL_COMP lowers the limit (tests:
+  // 1 sends every component through cluster_big.cu)
+  uint32_t small_max = SMALL_COMP;
+  if (const char *e = std::getenv("HUMID_GPU_SMALL_COMP")) small_max = std::min<uint32_t>(SMALL_COMP, std::max(1, atoi(e)));
+  uint64_t host_n[2] = {0, 0};  // large-component words, small-component roots
   {
-    Timed t(s, "group_big_components", U, U * 8);
-    s.key_alt.ensure(U + 1);
-    HUMID_CUDA(cudaMemsetAsync(s.counters.p + 8, 0, sizeof(unsigned long long), s.stream));
-    big_member_keys_kernel<<<g256, 256, 0, s.stream>>>(s.comp.p, csize, U, s.key_alt.p, s.counters.p + 8);
-    HUMID_CUDA(cudaMemcpyAsync(&n_big, s.counters.p + 8, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+    Timed t(s, "classify_components", U, U * 16);
+    HUMID_CUDA(cudaMemsetAsync(s.counters.p + 8, 0, 2 * sizeof(unsigned long long), s.stream));
+    if (s.cfg.maximum) {
+      classify_words_kernel<true><<<g256, 256, 0, s.stream>>>(s.comp.p, csize, s.word_count.p, U, small_max, skip_root, s.label.p,
+                                                              s.seed_flag.p, s.seed_size.p, s.seed_max.p, s.work_b.p,
+                                                              s.counters.p + 9, s.key_alt.p, s.counters.p + 8);
+    } else {
+      HUMID_CUDA(cudaMemsetAsync(s.label.p, 0xFF, U * sizeof(uint32_t), s.stream));
+      HUMID_CUDA(cudaMemsetAsync(s.seed_flag.p, 0, U * sizeof(uint32_t), s.stream));
+      classify_words_kernel<false><<<g256, 256, 0, s.stream>>>(s.comp.p, csize, s.word_count.p, U, small_max, skip_root, s.label.p,
+                                                               s.seed_flag.p, s.seed_size.p, s.seed_max.p, s.work_b.p,
+                                                               s.counters.p + 9, s.key_alt.p, s.counters.p + 8);
+    }
+    HUMID_CUDA(cudaMemcpyAsync(host_n, s.counters.p + 8, sizeof(host_n), cudaMemcpyDeviceToHost, s.stream));
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
-    int launches = 1;
-    s.members.ensure(n_big + 1);
-    s.work_b.ensure(std::max<uint64_t>(n_big + 1, 1));
-    s.work_c.ensure(std::max<uint64_t>(n_big + 1, U));  // also `visited` in maximum mode
-    if (n_big) {
+  }
+  k++;
+  const uint64_t n_big = host_n[0], n_small = host_n[1];
+
+  if (n_small) {
+    Timed t(s, s.cfg.maximum ? "replay_maximum" : "replay_directional", n_small, s.n_entries * 8 + U * 24);
+    const unsigned gs = grid_for(n_small, HUMID_REPLAY_THREADS);
+    if (s.cfg.maximum) {
+      s.work_c.ensure(U);  // visited flags of the depth-first search (only when counts tie)
+      HUMID_CUDA(cudaMemsetAsync(s.work_c.p, 0, U * sizeof(uint32_t), s.stream));
+      replay_small_kernel<true><<<gs, HUMID_REPLAY_THREADS, 0, s.stream>>>(g, s.work_b.p, n_small, csize, s.work_c.p,
+                                                                           s.label.p, s.seed_flag.p, s.seed_size.p,
+                                                                           s.seed_max.p);
+    } else {
+      replay_small_kernel<false><<<gs, HUMID_REPLAY_THREADS, 0, s.stream>>>(g, s.work_b.p, n_small, csize, nullptr,
+                                                                            s.label.p, s.seed_flag.p, s.seed_size.p,
+                                                                            s.seed_max.p);
+    }
+    k++;
+  }
+
+  // words of large components: grouped by component in rank order, then clustered all at once (cluster_big.cu)
+  if (n_big) {
+    int launches = 0;
+    {
+      Timed t(s, "group_big_components", n_big, n_big * 40);
+      s.members.ensure(n_big + 1);
       s.entries_alt.ensure(n_big + 1);
       uint64_t *kb[2] = {s.key_alt.p, s.entries_alt.p};
       uint32_t *vb[2] = {nullptr, nullptr};
@@ -346,35 +413,11 @@ int stage_cluster(State &s) {
       int cur = radix_sort_u64(kb, vb, n_big, 32 + ubits, s.scratch, s.scan_scratch, s.stream, &launches);
       big_segments_kernel<<<grid_for(n_big, 256), 256, 0, s.stream>>>(kb[cur], n_big, s.members.p, s.seg_start.p);
       launches++;
+      t.launches = launches;
     }
-    t.launches = launches;
     k += launches;
+    k += s.cfg.maximum ? stage_big_maximum(s, g, n_big) : stage_big_directional(s, g, n_big);
   }
-
-  s.seed_flag.ensure(U);
-  s.seed_index.ensure(U);
-  s.seed_size.ensure(U);
-  s.seed_max.ensure(U);
-  Graph g{s.row_ptr.p, s.col.p, s.word_count.p, s.cluster_col_base};
-  const uint32_t *skip_root = s.cluster_skip_open ? s.comp_open.p : nullptr;
-  size_t t_replay = s.timer_begin(s.cfg.maximum ? "replay_maximum" : "replay_directional", U,
-                                  s.n_entries * 8 + U * 24);
-  if (s.cfg.maximum) {
-    // big components: DFS stack (node, edge) in work_b / slot_alt, visited flags per word in work_c
-    s.slot_alt.ensure(n_big + 1);
-    HUMID_CUDA(cudaMemsetAsync(s.work_c.p, 0, U * sizeof(uint32_t), s.stream));
-    replay_kernel<true><<<g128, HUMID_REPLAY_THREADS, 0, s.stream>>>(g, U, s.comp.p, csize, s.members.p, s.seg_start.p, s.work_b.p,
-                                                    s.slot_alt.p, s.work_c.p, s.label.p, s.seed_flag.p, s.seed_size.p,
-                                                    s.seed_max.p, skip_root);
-  } else {
-    HUMID_CUDA(cudaMemsetAsync(s.label.p, 0xFF, U * sizeof(uint32_t), s.stream));
-    HUMID_CUDA(cudaMemsetAsync(s.seed_flag.p, 0, U * sizeof(uint32_t), s.stream));
-    replay_kernel<false><<<g128, HUMID_REPLAY_THREADS, 0, s.stream>>>(g, U, s.comp.p, csize, s.members.p, s.seg_start.p, s.work_b.p,
-                                                     nullptr, nullptr, s.label.p, s.seed_flag.p, s.seed_size.p,
-                                                     s.seed_max.p, skip_root);
-  }
-  s.timer_end(t_replay, 1);
-  k++;
   HUMID_CUDA(cudaGetLastError());
   if (s.cluster_skip_open) return k;  // shard mode: ids are handed out after the open components are merged in
   return k + stage_cluster_number(s);

@@ -736,10 +736,15 @@ static int csr_from_degrees(State &s, uint64_t E, bool pairs) {
 
 int stage_csr_pairs(State &s) {
   s.n_entries = 2 * s.n_pairs;
+  s.cluster_pairs = s.entries.p;  // the union-find takes the pairs as they are
+  s.n_cluster_pairs = s.n_pairs;
   return csr_from_degrees(s, s.n_entries, true);
 }
 
-int stage_csr_directed(State &s) { return csr_from_degrees(s, s.n_entries, false); }
+int stage_csr_directed(State &s) {
+  s.cluster_pairs = nullptr;
+  return csr_from_degrees(s, s.n_entries, false);
+}
 
 // ------------------------------------------------------------------------------------
 // CSR: sort the directed entries by (source rank, order key), then split.
@@ -758,6 +763,7 @@ __global__ void __launch_bounds__(256)
 
 int stage_csr(State &s) {
   const uint64_t U = s.unique, E = s.n_entries;
+  s.cluster_pairs = nullptr;
   int k = 0;
   s.row_ptr.ensure(U + 2);
   s.col.ensure(E + 1);
