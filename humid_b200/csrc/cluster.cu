@@ -100,32 +100,33 @@ template <bool MAXIMUM>
 __global__ void __launch_bounds__(256)
     classify_words_kernel(const uint32_t *__restrict__ comp, const uint32_t *__restrict__ csize,
                           const uint32_t *__restrict__ count, uint64_t U, uint32_t small_max,
-                          const uint32_t *__restrict__ skip_root, uint32_t *__restrict__ label, uint32_t *__restrict__ seed_flag, uint64_t *__restrict__ seed_size,
+                          const uint32_t *__restrict__ skip_root, uint32_t *__restrict__ label,
+                          uint32_t *__restrict__ seed_flag, uint64_t *__restrict__ seed_size,
                           uint32_t *__restrict__ seed_max, uint32_t *__restrict__ small_roots,
-                          unsigned long long *__restrict__ n_small, uint64_t *__restrict__ big_keys,
-                          unsigned long long *__restrict__ n_big) {
+                          unsigned long long *__restrict__ n_small, unsigned long long *__restrict__ n_big_roots) {
   const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   bool small = false, big = false;
-  uint32_t root = 0;
   if (r < U) {
-    root = comp[r];
-    const bool skipped = skip_root && skip_root[root];  // shard mode: the component continues on another shard
-    if (MAXIMUM) {
-      label[r] = root;
-      seed_flag[r] = (!skipped && root == r) ? 1u : 0u;
-    }
-    if (!skipped) {
-      const uint32_t m = csize[root] + 1u;
+    const uint32_t root = comp[r];
+    // only roots look at their component (csize[r]: coalesced); the other words are listed later, and only when
+    // some component is large
+    uint32_t lab = MAXIMUM ? root : NONE32, flag = 0;
+    if (root == r && !(skip_root && skip_root[root])) {  // skip: (shard mode) the component continues on another shard
+      const uint32_t m = csize[r] + 1u;
+      if (MAXIMUM) flag = 1;
       if (m == 1) {  // no neighbours: its own cluster
-        if (!MAXIMUM) { label[r] = (uint32_t)r; seed_flag[r] = 1; }
+        lab = (uint32_t)r;
+        flag = 1;
         seed_size[r] = count[r];
         seed_max[r] = (uint32_t)r;
       } else if (m <= small_max) {
-        small = root == r;
+        small = true;
       } else {
         big = true;
       }
     }
+    label[r] = lab;
+    seed_flag[r] = flag;
   }
   const uint32_t lane = lane_id(), lt = (1u << lane) - 1u;
   const unsigned ms = __ballot_sync(0xffffffffu, small), mb = __ballot_sync(0xffffffffu, big);
@@ -136,13 +137,28 @@ __global__ void __launch_bounds__(256)
     base = __shfl_sync(0xffffffffu, base, leader);
     if (small) small_roots[base + __popc(ms & lt)] = (uint32_t)r;
   }
-  if (mb) {
-    unsigned long long base = 0;
-    const int leader = __ffs(mb) - 1;
-    if ((int)lane == leader) base = atomicAdd(n_big, (unsigned long long)__popc(mb));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (big) big_keys[base + __popc(mb & lt)] = ((uint64_t)root << 32) | (uint32_t)r;
+  if (mb && lane == 0) atomicAdd(n_big_roots, (unsigned long long)__popc(mb));
+}
+
+// (root, rank) keys of the words of the large components (run only when there is one)
+__global__ void __launch_bounds__(256)
+    big_member_keys_kernel(const uint32_t *__restrict__ comp, const uint32_t *__restrict__ csize, uint64_t U,
+                           uint32_t small_max, const uint32_t *__restrict__ skip_root, uint64_t *__restrict__ keys,
+                           unsigned long long *__restrict__ counter) {
+  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  bool big = false;
+  uint32_t root = 0;
+  if (r < U) {
+    root = comp[r];
+    big = csize[root] + 1u > small_max && !(skip_root && skip_root[root]);
   }
+  unsigned m = __ballot_sync(0xffffffffu, big);
+  if (m == 0) return;
+  unsigned long long base = 0;
+  int leader = __ffs(m) - 1;
+  if ((int)lane_id() == leader) base = atomicAdd(counter, (unsigned long long)__popc(m));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (big) keys[base + __popc(m & ((1u << lane_id()) - 1u))] = ((uint64_t)root << 32) | (uint32_t)r;
 }
 
 __global__ void big_segments_kernel(const uint64_t *__restrict__ sorted, uint64_t n, uint32_t *__restrict__ members,
@@ -361,26 +377,32 @@ int stage_cluster(State &s) {
   // 1 sends every component through cluster_big.cu)
   uint32_t small_max = SMALL_COMP;
   if (const char *e = std::getenv("HUMID_GPU_SMALL_COMP")) small_max = std::min<uint32_t>(SMALL_COMP, std::max(1, atoi(e)));
-  uint64_t host_n[2] = {0, 0};  // large-component words, small-component roots
+  uint64_t host_n[2] = {0, 0};  // roots of large components, roots of small components
   {
     Timed t(s, "classify_components", U, U * 16);
     HUMID_CUDA(cudaMemsetAsync(s.counters.p + 8, 0, 2 * sizeof(unsigned long long), s.stream));
-    if (s.cfg.maximum) {
-      classify_words_kernel<true><<<g256, 256, 0, s.stream>>>(s.comp.p, csize, s.word_count.p, U, small_max, skip_root, s.label.p,
-                                                              s.seed_flag.p, s.seed_size.p, s.seed_max.p, s.work_b.p,
-                                                              s.counters.p + 9, s.key_alt.p, s.counters.p + 8);
-    } else {
-      HUMID_CUDA(cudaMemsetAsync(s.label.p, 0xFF, U * sizeof(uint32_t), s.stream));
-      HUMID_CUDA(cudaMemsetAsync(s.seed_flag.p, 0, U * sizeof(uint32_t), s.stream));
-      classify_words_kernel<false><<<g256, 256, 0, s.stream>>>(s.comp.p, csize, s.word_count.p, U, small_max, skip_root, s.label.p,
-                                                               s.seed_flag.p, s.seed_size.p, s.seed_max.p, s.work_b.p,
-                                                               s.counters.p + 9, s.key_alt.p, s.counters.p + 8);
-    }
-    HUMID_CUDA(cudaMemcpyAsync(host_n, s.counters.p + 8, sizeof(host_n), cudaMemcpyDeviceToHost, s.stream));
-    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    if (s.cfg.maximum)
+      classify_words_kernel<true><<<g256, 256, 0, s.stream>>>(s.comp.p, csize, s.word_count.p, U, small_max, skip_root,
+                                                              s.label.p, s.seed_flag.p, s.seed_size.p, s.seed_max.p,
+                                                              s.work_b.p, s.counters.p + 9, s.counters.p + 8);
+    else
+      classify_words_kernel<false><<<g256, 256, 0, s.stream>>>(s.comp.p, csize, s.word_count.p, U, small_max, skip_root,
+                                                               s.label.p, s.seed_flag.p, s.seed_size.p, s.seed_max.p,
+                                                               s.work_b.p, s.counters.p + 9, s.counters.p + 8);
   }
+  HUMID_CUDA(cudaMemcpyAsync(host_n, s.counters.p + 8, sizeof(host_n), cudaMemcpyDeviceToHost, s.stream));
+  HUMID_CUDA(cudaStreamSynchronize(s.stream));
   k++;
-  const uint64_t n_big = host_n[0], n_small = host_n[1];
+  const uint64_t n_small = host_n[1];
+  uint64_t n_big = 0;
+  if (host_n[0]) {  // some component is large: list the words of all of them
+    HUMID_CUDA(cudaMemsetAsync(s.counters.p + 8, 0, sizeof(unsigned long long), s.stream));
+    big_member_keys_kernel<<<g256, 256, 0, s.stream>>>(s.comp.p, csize, U, small_max, skip_root, s.key_alt.p,
+                                                       s.counters.p + 8);
+    HUMID_CUDA(cudaMemcpyAsync(&n_big, s.counters.p + 8, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    k++;
+  }
 
   if (n_small) {
     Timed t(s, s.cfg.maximum ? "replay_maximum" : "replay_directional", n_small, s.n_entries * 8 + U * 24);
