@@ -28,7 +28,9 @@ EXPORTS = [
     "humid_gpu_debug_neighbours", "humid_gpu_debug_clusters", "humid_gpu_stage_stats", "humid_gpu_stream",
     "humid_gpu_debug_sort_pairs", "humid_gpu_debug_partition", "humid_gpu_host_alloc", "humid_gpu_host_free",
     "humid_gpu_debug_words_hi", "humid_gpu_host_register", "humid_gpu_host_unregister",
+    "humid_gpu_partition_by_slot_noalloc",
 ]
+NOALLOC_MAX_ELEMENTS = 1 << 22  # HUMID_NOALLOC_MAX_ELEMENTS
 
 
 class HumidGpuError(RuntimeError):
@@ -89,6 +91,7 @@ def load_library() -> C.CDLL:
     L.humid_gpu_host_unregister.argtypes = [vp, vp]
     L.humid_gpu_debug_sort_pairs.argtypes = [vp, vp, vp, u64, C.c_int, C.c_int, vp, vp]
     L.humid_gpu_debug_partition.argtypes = [vp, C.c_int, vp, u64, u64, u32, vp, u32, vp, vp, vp]
+    L.humid_gpu_partition_by_slot_noalloc.argtypes = [vp, vp, u64, u64, u32, vp, vp]
     _lib = L
     return L
 
@@ -171,6 +174,14 @@ class Dedup:
                                                       index_base, C.c_void_p(d_keys_out), C.c_void_p(d_vals_out or None),
                                                       _ptr(counts)), "debug_partition")
         return counts[:n_parts]
+
+    def partition_by_slot_noalloc(self, d_keys_in: int, n: int, slot_mask: int, index_base: int, d_keys_out: int,
+                                  d_vals_out: int):
+        """debug_partition(kind 0) without any allocation (static scratch, at most NOALLOC_MAX_ELEMENTS elements);
+        enqueued on the handle's stream, NOT synchronised."""
+        self._check(self._L.humid_gpu_partition_by_slot_noalloc(self._h, C.c_void_p(d_keys_in), n, slot_mask, index_base,
+                                                                C.c_void_p(d_keys_out), C.c_void_p(d_vals_out)),
+                    "partition_by_slot_noalloc")
 
     def reset(self):
         self._check(self._L.humid_gpu_reset(self._h), "reset")

@@ -444,6 +444,27 @@ int humid_gpu_debug_partition(humid_gpu *h, int kind, const uint64_t *d_keys_in,
   });
 }
 
+// No counterpart in the reference (include/humid_gpu.h).  Nothing on
+// this path allocates: no DevBuf / Scratch / HostBuf is touched, failures are reported through the handle's message.
+int humid_gpu_partition_by_slot_noalloc(humid_gpu *h, const uint64_t *d_keys_in, uint64_t n, uint64_t slot_mask,
+                                        uint32_t index_base, uint64_t *d_keys_out, uint32_t *d_vals_out) {
+  if (!h) return HUMID_GPU_ERR_ARG;
+  State &s = h->s;
+  if (n == 0) return HUMID_GPU_OK;
+  if (!d_keys_in || !d_keys_out || !d_vals_out) return fail(h, HUMID_GPU_ERR_ARG, "partition_by_slot_noalloc: null buffer");
+  if (n > HUMID_NOALLOC_MAX_ELEMENTS)
+    return fail(h, HUMID_GPU_ERR_UNSUPPORTED,
+                "partition_by_slot_noalloc: " + std::to_string(n) + " elements, the static scratch holds at most " +
+                    std::to_string(HUMID_NOALLOC_MAX_ELEMENTS) + " (use humid_gpu_debug_partition, which may allocate)");
+  try {
+    HUMID_CUDA(cudaSetDevice(s.device));
+    partition_by_slot_u64_noalloc(d_keys_in, index_base, d_keys_out, d_vals_out, n, slot_mask, s.stream);
+    return HUMID_GPU_OK;
+  } catch (const CudaError &e) {
+    return fail(h, HUMID_GPU_ERR_CUDA, e.msg);
+  }
+}
+
 int humid_gpu_stage_stats(humid_gpu *h, humid_gpu_stage_stat *out, uint32_t *n) {
   if (!h || !n) return HUMID_GPU_ERR_ARG;
   State &s = h->s;

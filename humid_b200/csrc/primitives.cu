@@ -1,5 +1,8 @@
 // Exclusive scan + stable LSD radix sort (see primitives.cuh).
 #include <cstdlib>
+#include <mutex>
+
+#include "../../include/humid_gpu.h"
 #include "primitives.cuh"
 
 namespace humid {
@@ -603,6 +606,64 @@ int radix_sort_bits_pairs(const uint64_t *keys_in, const uint32_t *vals_in, uint
                           uint64_t n, int begin_bit, int end_bit, Scratch &scratch, cudaStream_t stream, int *launches) {
   if (n == 0 || end_bit <= begin_bit) throw CudaError{"radix_sort_bits_pairs: nothing to sort by"};
   return radix_sort_impl(keys_in, vals_in, keys, vals, 0, n, begin_bit, end_bit, scratch, stream, launches);
+}
+
+// ------------------------------------------------------------------------------------
+// The slot partition for callers that must not allocate (include/humid_gpu.h: humid_gpu_partition_by_slot_noalloc;
+// no counterpart in the reference).  Same kernels, same result as
+// partition_by_slot_u64; the scratch (tile status words, ticket, histogram) lives in a file-scope device array
+// instead of the handle's growable arena, so nothing here can reach cudaMalloc / cudaFree.  Every GPU that loads the
+// library holds the array until the process exits.  All calls on a device share it and it keeps the last call's
+// contents: the part a call uses is cleared on its stream first, and two calls that overlap on the GPU race.
+// ------------------------------------------------------------------------------------
+constexpr uint64_t NOALLOC_MAX_TILES = (HUMID_NOALLOC_MAX_ELEMENTS + RS_TILE - 1) / RS_TILE;
+constexpr size_t NOALLOC_TAIL_BYTES = (RS_MAX_PASSES + 2 * RS_BINS) * sizeof(uint32_t);
+constexpr size_t NOALLOC_SCRATCH_BYTES = NOALLOC_MAX_TILES * RS_BINS * sizeof(uint64_t) + NOALLOC_TAIL_BYTES;
+static __device__ __align__(256) unsigned char noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+// In host code `noalloc_scratch` is only a stand-in for the symbol, not a device address: the address is asked for
+// once per device, with that device current, and cached.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static std::mutex noalloc_mutex;
+static void *noalloc_address[NOALLOC_MAX_DEVICES] = {};
+
+static void *noalloc_scratch_on_current_device() {
+  int device = -1;
+  HUMID_CUDA(cudaGetDevice(&device));
+  if (device < 0 || device >= NOALLOC_MAX_DEVICES) throw CudaError{"no-allocation scratch: device ordinal out of range"};
+  std::lock_guard<std::mutex> lock(noalloc_mutex);
+  if (!noalloc_address[device]) {
+    void *p = nullptr;
+    HUMID_CUDA(cudaGetSymbolAddress(&p, noalloc_scratch));
+    if (!p) throw CudaError{"no-allocation scratch: cudaGetSymbolAddress returned a null address"};
+    noalloc_address[device] = p;
+  }
+  return noalloc_address[device];
+}
+
+size_t partition_noalloc_scratch_bytes() { return NOALLOC_SCRATCH_BYTES; }
+
+int partition_by_slot_u64_noalloc(const uint64_t *keys_in, uint32_t index_base, uint64_t *keys_out, uint32_t *vals_out,
+                                  uint64_t n, uint64_t slot_mask, cudaStream_t stream) {
+  if (n == 0) return 0;
+  if (n > HUMID_NOALLOC_MAX_ELEMENTS) throw CudaError{"no-allocation partition: more elements than the static scratch holds"};
+  int bits = 0;
+  while ((slot_mask >> bits) != 0) bits++;
+  const SlotDigit dg{slot_mask, bits > 8 ? bits - 8 : 0};
+  const uint32_t n_tiles = (uint32_t)((n + RS_TILE - 1) / RS_TILE);
+  // [status: n_tiles * 256 u64][tickets: 8 u32][hist: 256 u32][unused: 256 u32] — the layout of partition_pass
+  const size_t status_bytes = (size_t)n_tiles * RS_BINS * sizeof(uint64_t);
+  char *base = static_cast<char *>(noalloc_scratch_on_current_device());
+  uint32_t *tickets = reinterpret_cast<uint32_t *>(base + status_bytes);
+  uint32_t *hist = tickets + RS_MAX_PASSES;
+  HUMID_CUDA(cudaMemsetAsync(base, 0, status_bytes + NOALLOC_TAIL_BYTES, stream));  // the last call's contents
+  const unsigned hist_grid = (unsigned)std::min<uint64_t>((n + RS_THREADS - 1) / RS_THREADS, 148 * 8);
+  digit_hist_kernel<<<hist_grid, RS_THREADS, 0, stream>>>(keys_in, n, dg, hist);
+  radix_digit_bases_kernel<<<1, RS_THREADS, 0, stream>>>(hist);
+  launch_radix_pass<true>(n_tiles, stream, keys_in, nullptr, keys_out, vals_out, n, dg, hist,
+                          reinterpret_cast<uint64_t *>(base), tickets, index_base);
+  HUMID_CUDA(cudaGetLastError());
+  return 3;
 }
 
 }  // namespace humid

@@ -74,4 +74,11 @@ int partition_by_row_owner(const uint64_t *entries_in, uint64_t *entries_out, ui
 int radix_sort_bits_pairs(const uint64_t *keys_in, const uint32_t *vals_in, uint64_t *keys[2], uint32_t *vals[2],
                           uint64_t n, int begin_bit, int end_bit, Scratch &scratch, cudaStream_t stream, int *launches);
 
+// partition_by_slot_u64 (values = index_base + i) with its scratch in a file-scope device array of primitives.cu: no
+// allocation of any kind, at most HUMID_NOALLOC_MAX_ELEMENTS (include/humid_gpu.h) elements, enqueued on `stream`
+// without synchronising.  Calls on one device share the scratch: they must not overlap on the GPU.
+int partition_by_slot_u64_noalloc(const uint64_t *keys_in, uint32_t index_base, uint64_t *keys_out, uint32_t *vals_out,
+                                  uint64_t n, uint64_t slot_mask, cudaStream_t stream);
+size_t partition_noalloc_scratch_bytes();
+
 }  // namespace humid

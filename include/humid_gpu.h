@@ -156,6 +156,25 @@ int humid_gpu_debug_partition(humid_gpu *h, int kind, const uint64_t *d_keys_in,
                               uint32_t n_parts, const uint64_t *bases, uint32_t index_base, uint64_t *d_keys_out,
                               uint32_t *d_vals_out, uint64_t *counts);
 
+/* The slot partition of humid_gpu_debug_partition (kind 0) for callers that cannot allocate: code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc.  NO COUNTERPART IN THE
+ * REFERENCE.
+ *   d_keys_in   n keys (device memory of h's device), only read
+ *   d_keys_out  n keys, d_vals_out n values: the (key, index_base + i) pairs of the input stably grouped by the top 8
+ *               bits of the key's home slot in a table of slot_mask + 1 slots — element for element what
+ *               humid_gpu_debug_partition(h, 0, d_keys_in, n, slot_mask, 0, NULL, index_base, ...) writes.
+ * The call allocates nothing, neither device nor page-locked memory, on any path: the scratch of the pass (tile status
+ * words, ticket, digit histogram) is a static device array inside the library, sized for at most
+ * HUMID_NOALLOC_MAX_ELEMENTS elements (about 1.4 MB, held by every GPU that loads the library until the process
+ * exits).  n > HUMID_NOALLOC_MAX_ELEMENTS fails with HUMID_GPU_ERR_UNSUPPORTED and a message.  The work is ENQUEUED on
+ * humid_gpu_stream(h) and the call returns without synchronising.  All calls on one device, whatever the handle,
+ * share the one scratch array; it keeps the last call's contents and the part a call uses is cleared first on the
+ * call's stream, so calls that follow each other on a stream are independent — but two calls that overlap on the GPU
+ * (different handles / streams) race and give undefined results: order them yourself. */
+#define HUMID_NOALLOC_MAX_ELEMENTS (1u << 22)
+int humid_gpu_partition_by_slot_noalloc(humid_gpu *h, const uint64_t *d_keys_in, uint64_t n, uint64_t slot_mask,
+                                        uint32_t index_base, uint64_t *d_keys_out, uint32_t *d_vals_out);
+
 /* Per-stage device timings of the last finalize (CUDA events on the library's stream). */
 typedef struct {
   char name[32];
