@@ -28,7 +28,7 @@ EXPORTS = [
     "humid_gpu_debug_neighbours", "humid_gpu_debug_clusters", "humid_gpu_stage_stats", "humid_gpu_stream",
     "humid_gpu_debug_sort_pairs", "humid_gpu_debug_partition", "humid_gpu_host_alloc", "humid_gpu_host_free",
     "humid_gpu_debug_words_hi", "humid_gpu_host_register", "humid_gpu_host_unregister",
-    "humid_gpu_partition_by_slot_noalloc",
+    "humid_gpu_partition_by_slot_noalloc", "humid_gpu_add_batch_packed4",
 ]
 NOALLOC_MAX_ELEMENTS = 1 << 22  # HUMID_NOALLOC_MAX_ELEMENTS
 
@@ -73,6 +73,7 @@ def load_library() -> C.CDLL:
     L.humid_gpu_last_error.restype = C.c_char_p
     L.humid_gpu_add_batch.argtypes = [vp, vp, vp, u64, u64]
     L.humid_gpu_add_batch_device.argtypes = [vp, vp, vp, u64, u64]
+    L.humid_gpu_add_batch_packed4.argtypes = [vp, vp, vp, u64, u64]
     L.humid_gpu_finalize.argtypes = [vp]
     L.humid_gpu_counts.argtypes = [vp, P(u64), P(u64), P(u64), P(u64)]
     L.humid_gpu_histogram.argtypes = [vp, C.c_int, vp, vp, P(u64)]
@@ -94,6 +95,23 @@ def load_library() -> C.CDLL:
     L.humid_gpu_partition_by_slot_noalloc.argtypes = [vp, vp, u64, u64, u32, vp, vp]
     _lib = L
     return L
+
+
+NIBBLE_OTHER = 4  # HUMID_NIBBLE_OTHER
+_NIBBLE_OF = np.full(256, NIBBLE_OTHER, dtype=np.uint8)
+_NIBBLE_OF[[ord(c) for c in "ACGT"]] = [0, 1, 2, 3]
+
+
+def pack_nibbles(chars: np.ndarray) -> np.ndarray:
+    """The host side of the 4-bit wire format (include/humid_gpu.h: humid_gpu_add_batch_packed4): uint8[n, word_length]
+    ASCII -> uint8[n, (word_length + 1) // 2], character q in the high nibble of byte q // 2 when q is even.  A table
+    look-up per byte; no validation, no cut / pad rule — those stay on the device."""
+    chars = np.ascontiguousarray(chars, dtype=np.uint8)
+    n, wl = chars.shape
+    code = _NIBBLE_OF[chars]
+    if wl & 1:
+        code = np.concatenate([code, np.zeros((n, 1), dtype=np.uint8)], axis=1)
+    return np.ascontiguousarray((code[:, 0::2] << 4) | code[:, 1::2])
 
 
 def _ptr(a: Optional[np.ndarray]):
@@ -199,6 +217,20 @@ class Dedup:
             if seg_len.shape != (n, self.n_segments):
                 raise HumidGpuError("seg_len must be [n_tuples, n_segments]")
         self._check(self._L.humid_gpu_add_batch(self._h, _ptr(chars), _ptr(seg_len), self.n_tuples, n), "add_batch")
+        self.n_tuples += n
+
+    def add_batch_packed4(self, nibbles: np.ndarray, seg_len: Optional[np.ndarray] = None):
+        """nibbles: uint8[n, (word_length + 1) // 2] from pack_nibbles(); half the bytes of add_batch on the wire."""
+        nibbles = np.ascontiguousarray(nibbles, dtype=np.uint8)
+        n = nibbles.shape[0]
+        if nibbles.ndim != 2 or nibbles.shape[1] != (self.word_length + 1) // 2:
+            raise HumidGpuError("nibbles must be [n_tuples, (word_length + 1) // 2]")
+        if seg_len is not None:
+            seg_len = np.ascontiguousarray(seg_len, dtype=np.uint16)
+            if seg_len.shape != (n, self.n_segments):
+                raise HumidGpuError("seg_len must be [n_tuples, n_segments]")
+        self._check(self._L.humid_gpu_add_batch_packed4(self._h, _ptr(nibbles), _ptr(seg_len), self.n_tuples, n),
+                    "add_batch_packed4")
         self.n_tuples += n
 
     def add_batch_device(self, d_chars: int, n: int, d_seg_len: int = 0):

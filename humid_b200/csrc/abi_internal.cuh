@@ -39,4 +39,12 @@ inline int guarded(humid_gpu *h, const std::function<void()> &body) {
 
 namespace humid {
 void resolve_stats(State &s);
+// group.cu: what the single-handle entry points need to know about a handle that is a rank of a group
+void group_release_handle(State &s);
+bool group_active(const State &s);
+bool group_batches_numbering(const State &s);
+void group_note_batch(State &s, uint64_t local, uint64_t global, uint64_t n);
+void group_reset(State &s);
+uint64_t group_result_tuples(const State &s);
+const uint32_t *group_result_ids(const State &s);
 }

@@ -8,6 +8,7 @@
 
 using namespace humid;
 
+#include "../../include/humid_gpu_shard.h"
 #include "abi_internal.cuh"
 
 void humid::resolve_stats(State &s) {
@@ -90,6 +91,7 @@ void humid_gpu_destroy(humid_gpu *h) {
   if (s.stream) cudaStreamSynchronize(s.stream);
   clear_stats(s);
   if (s.open) clear_stats(*s.open);
+  group_release_handle(s);
   for (int b = 0; b < 2; b++) {
     if (s.ev_copied[b]) cudaEventDestroy(s.ev_copied[b]);
     if (s.ev_consumed[b]) cudaEventDestroy(s.ev_consumed[b]);
@@ -125,6 +127,7 @@ int humid_gpu_reset(humid_gpu *h) {
     s.n_parts = 1;
     for (int i = 0; i < 3; i++) s.hist_done[i] = false;
     s.hist_pending = false;
+    group_reset(s);
     HUMID_CUDA(cudaMemsetAsync(s.counters.p, 0, 64 * sizeof(unsigned long long), s.stream));
   });
 }
@@ -159,17 +162,22 @@ int humid_gpu_host_unregister(humid_gpu *h, void *p) {
 }
 
 static int add_batch_impl(humid_gpu *h, const uint8_t *chars, const uint16_t *seg_len, uint64_t first, uint64_t n,
-                          bool on_device) {
+                          bool on_device, bool packed4 = false) {
   if (!h) return HUMID_GPU_ERR_ARG;
   State &s = h->s;
   if (s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "add_batch after finalize (call humid_gpu_reset first)");
+  // HUMID_GROUP_BATCHES: `first` is the batch's position in the JOB; this rank stores it behind its earlier batches
+  const bool global_first = group_batches_numbering(s);
+  const uint64_t global_pos = first;
+  if (global_first) first = s.n_tuples;
   if (first != s.n_tuples) return fail(h, HUMID_GPU_ERR_ARG, "batches must be added in input order, without gaps");
   if (n && !chars) return fail(h, HUMID_GPU_ERR_ARG, "chars is null");
   if (s.n_tuples + n >= 0xFFFFFFFFull) return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "more than 2^32-2 tuples");
   if (n == 0) return HUMID_GPU_OK;
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
-    const uint32_t wl = s.cfg.word_length, ns = s.cfg.n_segments;
+    // bytes of one tuple on the wire: one per character, or two characters per byte
+    const uint32_t wl = packed4 ? (s.cfg.word_length + 1) / 2 : s.cfg.word_length, ns = s.cfg.n_segments;
     s.tuple_key.grow(s.n_tuples + n, s.n_tuples, s.stream);
     if (s.wide()) s.tuple_hi.grow(s.n_tuples + n, s.n_tuples, s.stream);
     const uint8_t *d_chars = chars;
@@ -195,13 +203,15 @@ static int add_batch_impl(humid_gpu *h, const uint8_t *chars, const uint16_t *se
       HUMID_CUDA(cudaStreamWaitEvent(s.stream, s.ev_copied[b], 0));
     }
     // makeWord: n ASCII bytes in, one 8-byte key out; then Trie::add when the table is already sized
-    stage_pack(s, d_chars, d_len, first, n);
+    if (packed4) stage_pack4(s, d_chars, d_len, first, n);
+    else stage_pack(s, d_chars, d_len, first, n);
     stage_early_insert(s, first, n);
     if (!on_device) {
       HUMID_CUDA(cudaEventRecord(s.ev_consumed[b], s.stream));
       s.stage_busy[b] = true;
       s.n_batches++;
     }
+    if (global_first) group_note_batch(s, s.n_tuples, global_pos, n);
     s.n_tuples += n;
     if (!on_device) HUMID_CUDA(cudaEventSynchronize(s.ev_copied[b]));  // the caller may reuse its buffers
   });
@@ -210,6 +220,11 @@ static int add_batch_impl(humid_gpu *h, const uint8_t *chars, const uint16_t *se
 int humid_gpu_add_batch(humid_gpu *h, const uint8_t *chars, const uint16_t *seg_len, uint64_t first_tuple_index,
                         uint64_t n_tuples) {
   return add_batch_impl(h, chars, seg_len, first_tuple_index, n_tuples, false);
+}
+
+int humid_gpu_add_batch_packed4(humid_gpu *h, const uint8_t *nibbles, const uint16_t *seg_len, uint64_t first_tuple_index,
+                                uint64_t n_tuples) {
+  return add_batch_impl(h, nibbles, seg_len, first_tuple_index, n_tuples, false, true);
 }
 
 int humid_gpu_add_batch_device(humid_gpu *h, const uint8_t *d_chars, const uint16_t *d_seg_len,
@@ -221,6 +236,7 @@ int humid_gpu_finalize(humid_gpu *h) {
   if (!h) return HUMID_GPU_ERR_ARG;
   State &s = h->s;
   if (s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "finalize called twice");
+  if (group_active(s)) return humid_gpu_group_finalize(h);  // a rank of a group: the collective form
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
     const bool edit2 = s.cfg.edit && s.cfg.distance >= 2;
@@ -290,8 +306,9 @@ int humid_gpu_keep_mask(humid_gpu *h, uint64_t first_tuple, uint64_t n, uint64_t
   if (!h || (n && !bits)) return HUMID_GPU_ERR_ARG;
   State &s = h->s;
   if (!s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "not finalized");
-  if (s.shard_mode) return fail(h, HUMID_GPU_ERR_ARG, "use humid_gpu_shard_keep_bits in shard mode");
-  if (first_tuple + n > s.report_tuples) return fail(h, HUMID_GPU_ERR_ARG, "tuple range out of bounds");
+  if (s.shard_mode && !group_active(s)) return fail(h, HUMID_GPU_ERR_ARG, "use humid_gpu_shard_keep_bits in shard mode");
+  if (first_tuple + n > (group_active(s) ? group_result_tuples(s) : s.report_tuples))
+    return fail(h, HUMID_GPU_ERR_ARG, "tuple range out of bounds");
   if (first_tuple % 64) return fail(h, HUMID_GPU_ERR_ARG, "first_tuple must be a multiple of 64");
   if (n == 0) return HUMID_GPU_OK;
   const uint64_t words = (n + 63) / 64;
@@ -304,6 +321,17 @@ int humid_gpu_cluster_ids(humid_gpu *h, uint64_t first_tuple, uint64_t n, uint32
   if (!h || (n && !ids)) return HUMID_GPU_ERR_ARG;
   State &s = h->s;
   if (!s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "not finalized");
+  if (group_active(s)) {  // the ids of this rank's tuples were sent here by the owners of their words
+    const uint32_t *d_ids = group_result_ids(s);
+    if (!d_ids) return fail(h, HUMID_GPU_ERR_ARG, "call humid_gpu_group_collect_ids first (collective)");
+    if (first_tuple + n > group_result_tuples(s)) return fail(h, HUMID_GPU_ERR_ARG, "tuple range out of bounds");
+    if (n == 0) return HUMID_GPU_OK;
+    return guarded(h, [&] {
+      HUMID_CUDA(cudaSetDevice(s.device));
+      HUMID_CUDA(cudaMemcpyAsync(ids, d_ids + first_tuple, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s.stream));
+      HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    });
+  }
   if (s.shard_mode) return fail(h, HUMID_GPU_ERR_ARG, "use humid_gpu_shard_cluster_ids in shard mode");
   if (first_tuple + n > s.n_tuples) return fail(h, HUMID_GPU_ERR_ARG, "tuple range out of bounds");
   if (n == 0) return HUMID_GPU_OK;

@@ -344,14 +344,19 @@ int humid_gpu_shard_import_tuples(humid_gpu *h, const uint64_t *d_keys, const ui
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
     // keep the received tuples: they are this shard's share of the job from here on
-    s.shard_keys.ensure(n + 1);
-    s.shard_index.ensure(n + 1);
-    if (n) {
-      HUMID_CUDA(cudaMemcpyAsync(s.shard_keys.p, d_keys, n * 8, cudaMemcpyDeviceToDevice, s.stream));
-      HUMID_CUDA(cudaMemcpyAsync(s.shard_index.p, d_index, n * 4, cudaMemcpyDeviceToDevice, s.stream));
+    if (s.alias_imports) {  // group mode: the tuples arrived in a buffer of the handle that stays as it is
+      s.src_keys = d_keys;
+      s.src_index = d_index;
+    } else {
+      s.shard_keys.ensure(n + 1);
+      s.shard_index.ensure(n + 1);
+      if (n) {
+        HUMID_CUDA(cudaMemcpyAsync(s.shard_keys.p, d_keys, n * 8, cudaMemcpyDeviceToDevice, s.stream));
+        HUMID_CUDA(cudaMemcpyAsync(s.shard_index.p, d_index, n * 4, cudaMemcpyDeviceToDevice, s.stream));
+      }
+      s.src_keys = s.shard_keys.p;
+      s.src_index = s.shard_index.p;
     }
-    s.src_keys = s.shard_keys.p;
-    s.src_index = s.shard_index.p;
     s.src_n = n;
     stage_build_table(s, false);  // the single-GPU table / sort / column stages on this key range
     s.n_shard_words = s.unique;
@@ -730,7 +735,7 @@ int humid_gpu_shard_tuple_ids(humid_gpu *h, uint32_t *d_ids) {
     stage_ensure_lookup(s);  // key -> local rank
     {
       Timed t(s, "cluster_ids", s.src_n, s.src_n * 36);
-      shard_word_ids_for_tuples_kernel<<<grid_for(s.src_n, 256), 256, 0, s.stream>>>(s.shard_keys.p, s.src_n, s.lookup(),
+      shard_word_ids_for_tuples_kernel<<<grid_for(s.src_n, 256), 256, 0, s.stream>>>(s.src_keys, s.src_n, s.lookup(),
                                                                                      s.word_cid.p, d_ids);
     }
     HUMID_CUDA(cudaGetLastError());

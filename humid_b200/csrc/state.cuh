@@ -149,6 +149,8 @@ struct State {
   uint64_t tuple_base = 0, n_shard_words = 0;
   DevBuf<uint64_t> shard_keys;
   DevBuf<uint32_t> shard_index;
+  bool alias_imports = false;           // import_tuples keeps the caller's buffers instead of copying them
+  struct GroupLink *group = nullptr;    // group.cu: the handle is one rank of a multi-GPU job run by the library
   const uint64_t *src_keys = nullptr;   // table input override (nullptr: tuple_key / implicit index)
   const uint32_t *src_index = nullptr;
   uint64_t src_n = 0;
@@ -241,6 +243,7 @@ struct Timed {
 
 // ---- stage launchers (each returns the number of kernels it launched) --------------------
 int stage_pack(State &s, const uint8_t *d_chars, const uint16_t *d_seg_len, uint64_t first, uint64_t n);
+int stage_pack4(State &s, const uint8_t *d_nibbles, const uint16_t *d_seg_len, uint64_t first, uint64_t n);  // 4-bit wire format
 int stage_build_table(State &s, bool with_lookup = true);  // insert + compact + sort + columns (+ look-up)
 int stage_ensure_lookup(State &s);    // ranks into the table slots + fingerprint filter, once per job
 int stage_early_insert(State &s, uint64_t first, uint64_t n);  // add_batch: count tuples [first, first+n)

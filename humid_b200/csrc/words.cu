@@ -137,6 +137,79 @@ int stage_pack(State &s, const uint8_t *d_chars, const uint16_t *d_seg_len, uint
   return 1;
 }
 
+// ---- the 4-bit wire format (humid_gpu_add_batch_packed4) ---------------------------------------------------------
+// Half the bytes of the ASCII form on the host -> device link: one nibble per character, 0..3 = A C G T
+// (src/fastq.cc:12), anything else = not a nucleotide; two characters per byte, the earlier one in the HIGH nibble;
+// (word_length + 1) / 2 bytes per tuple.  The cut / pad rule and the filter still run here (makeStringSize_,
+// makeWord): a short segment or a nibble above 3 filters the tuple.
+// Eight characters at a time: one little-endian u32 = bytes 0..3 = characters 0..7.
+__device__ __forceinline__ uint32_t pack8_nibbles(uint32_t x, bool &bad) {
+  x = __byte_perm(x, 0u, 0x0123);                             // character 0 into bits 31..28
+  bad |= (x & 0xCCCCCCCCu) != 0u;                             // a code above 3
+  x = ((x >> 2) & 0x0C0C0C0Cu) | (x & 0x03030303u);           // per byte: two characters in bits 3..0
+  x = ((x >> 4) & 0x00F000F0u) | (x & 0x000F000Fu);           // per half: four characters in bits 7..0
+  return ((x >> 8) & 0xFF00u) | (x & 0xFFu);                  // eight characters, the first most significant
+}
+
+// One thread per tuple: the 12 bytes of a 24-letter word are three u32 loads, a warp reads 384 consecutive bytes.
+template <bool WIDE>
+__global__ void __launch_bounds__(256)
+    pack_words4_kernel(const uint8_t *__restrict__ nibbles, const uint16_t *__restrict__ seg_len, uint64_t n_tuples,
+                       PackParams pp, uint64_t *__restrict__ keys_out, uint64_t *__restrict__ keys_hi_out,
+                       unsigned long long *__restrict__ usable) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t row_bytes = (pp.n + 1u) >> 1;
+  bool bad = false;
+  uint64_t key = 0, key_hi = 0;
+  if (t < n_tuples) {
+    if (seg_len) {
+      const uint16_t *sl = seg_len + t * pp.n_segs;
+      for (uint32_t s = 0; s < pp.n_segs; s++) bad |= sl[s] < pp.take[s];
+    }
+    const uint8_t *row = nibbles + t * row_bytes;
+    uint32_t q = 0;
+    if ((row_bytes & 3u) == 0u && (((uintptr_t)nibbles) & 3u) == 0u) {  // rows are 4-byte aligned
+      const uint32_t *row4 = reinterpret_cast<const uint32_t *>(row);
+      for (; q + 8 <= pp.n; q += 8) {
+        const uint32_t v = pack8_nibbles(__ldg(row4 + (q >> 3)), bad);
+        if (WIDE) key_hi = (key_hi << 16) | (key >> 48);
+        key = (key << 16) | v;
+      }
+    }
+    for (; q < pp.n; q++) {
+      const uint32_t b = row[q >> 1];
+      const uint32_t v = (q & 1u) ? (b & 15u) : (b >> 4);
+      bad |= v > 3u;
+      if (WIDE) key_hi = (key_hi << 2) | (key >> 62);
+      key = (key << 2) | (v & 3u);
+    }
+    keys_out[t] = bad ? KEY_INVALID : key;
+    if (WIDE) keys_hi_out[t] = bad ? KEY_INVALID : key_hi;
+  }
+  uint32_t n_good = (t < n_tuples && !bad) ? 1u : 0u;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) n_good += __shfl_xor_sync(0xffffffffu, n_good, o);
+  if (lane_id() == 0 && n_good) atomicAdd(usable, (unsigned long long)n_good);
+}
+
+int stage_pack4(State &s, const uint8_t *d_nibbles, const uint16_t *d_seg_len, uint64_t first, uint64_t n) {
+  if (n == 0) return 0;
+  PackParams pp{};
+  pp.n = s.cfg.word_length;
+  pp.n_segs = s.cfg.n_segments;
+  for (uint32_t i = 0; i < pp.n_segs; i++) pp.take[i] = s.cfg.seg_take[i];
+  // makeWord from the 4-bit form: (n + 1) / 2 bytes in, one 8-byte key (two for a word of more than 31 letters) out
+  Timed t(s, "pack", n, n * ((pp.n + 1) / 2 + (s.wide() ? 16 : 8)));
+  if (s.wide())
+    pack_words4_kernel<true><<<grid_for(n, 256), 256, 0, s.stream>>>(d_nibbles, d_seg_len, n, pp, s.tuple_key.p + first,
+                                                                      s.tuple_hi.p + first, s.counters.p + 0);
+  else
+    pack_words4_kernel<false><<<grid_for(n, 256), 256, 0, s.stream>>>(d_nibbles, d_seg_len, n, pp, s.tuple_key.p + first,
+                                                                       nullptr, s.counters.p + 0);
+  HUMID_CUDA(cudaGetLastError());
+  return 1;
+}
+
 // ------------------------------------------------------------------------------------
 // Distinct-word table: open addressing, linear probing, 16-B slots (two per 32-B sector).
 // ------------------------------------------------------------------------------------

@@ -323,8 +323,107 @@ def all_gather_v(comm, t: torch.Tensor, sizes: Sequence[int]) -> torch.Tensor:
     return torch.cat([buf[r * m: r * m + sizes[r]] for r in range(comm.world)])
 
 
+GROUP_EXPORTS = [
+    "humid_gpu_group_create", "humid_gpu_group_destroy", "humid_gpu_group_join", "humid_gpu_group_finalize",
+    "humid_gpu_group_collect_ids", "humid_gpu_group_phases",
+]
+GROUP_SLICES, GROUP_BATCHES = 0, 1
+
+
+def _bind_group(L):
+    if getattr(L, "_group_bound", False):
+        return L
+    vp, u32 = C.c_void_p, C.c_uint32
+    L.humid_gpu_group_create.argtypes = [u32]
+    L.humid_gpu_group_create.restype = vp
+    L.humid_gpu_group_destroy.argtypes = [vp]
+    L.humid_gpu_group_destroy.restype = None
+    L.humid_gpu_group_join.argtypes = [vp, vp, C.c_char_p, u32, u32, C.c_int]
+    L.humid_gpu_group_finalize.argtypes = [vp]
+    L.humid_gpu_group_collect_ids.argtypes = [vp]
+    L.humid_gpu_group_phases.argtypes = [vp, C.POINTER(C.c_char_p), C.POINTER(C.c_float), C.POINTER(u32)]
+    L._group_bound = True
+    return L
+
+
+class GroupDedup(api.Dedup):
+    """One rank of a multi-GPU job run by the library itself (include/humid_gpu_shard.h, "Groups"): the exchanges are
+    stores / copies into the peers' buffers over NVLink, issued from C++ — no NCCL, no Python between the phases.
+    Same call sequence as `api.Dedup`; rank r's tuples are the r-th contiguous slice of the job's input order and the
+    per-tuple results (keep mask, cluster ids) are this rank's slice; counts and statistics are the whole job's.
+
+    group: handle from `new_group(world)` when the ranks are threads of one process, else None and `shm_name` names
+    the POSIX shared memory segment the ranks (processes) meet in."""
+
+    transport = "peer memory (CUDA IPC mappings / peer access over NVLink), stores from the producing kernels; no NCCL"
+
+    def __init__(self, rank: int, world: int, group=None, shm_name: Optional[str] = None, device: int = 0, **kw):
+        kw.pop("defer_table", None)
+        super().__init__(device=device, defer_table=True, **kw)  # words are counted by their owners
+        _bind_group(self._L)
+        self.rank, self.world = rank, world
+        self.phases: List[Tuple[str, float]] = []
+        rc = self._L.humid_gpu_group_join(self._h, group, (shm_name or "").encode() or None, rank, world, GROUP_SLICES)
+        if rc != 0:
+            msg = self._L.humid_gpu_last_error(self._h).decode()
+            self.close()
+            raise api.HumidGpuError(f"humid_gpu_group_join failed ({rc}): {msg}")
+
+    def finalize(self):
+        self._check(self._L.humid_gpu_group_finalize(self._h), "group_finalize")
+        n = C.c_uint32(64)
+        names, ms = (C.c_char_p * 64)(), (C.c_float * 64)()
+        if self._L.humid_gpu_group_phases(self._h, names, ms, C.byref(n)) == 0:
+            self.phases = [(names[i].decode(), float(ms[i])) for i in range(n.value)]
+
+    def cluster_ids(self, first: int = 0, n: Optional[int] = None) -> np.ndarray:
+        self._check(self._L.humid_gpu_group_collect_ids(self._h), "group_collect_ids")  # collective
+        return super().cluster_ids(first, n)
+
+
+def new_group(world: int):
+    """In-process group object (ranks = threads of this process); free with free_group()."""
+    L = _bind_group(api.load_library())
+    g = L.humid_gpu_group_create(world)
+    if not g:
+        raise api.HumidGpuError("humid_gpu_group_create failed")
+    return C.c_void_p(g)
+
+
+def free_group(g):
+    _bind_group(api.load_library()).humid_gpu_group_destroy(g)
+
+
+_group_serial = [0]
+
+
 def make_sharded(**kw):
-    """The multi-GPU path bench.py and the tests use: one instance per rank (torch.distributed already initialised)."""
+    """The multi-GPU path bench.py and the tests use: one instance per rank (torch.distributed already initialised).
+    On CUDA the ranks form a group of the library (peer-memory exchanges); HUMID_SHARD_TRANSPORT=nccl selects the
+    torch.distributed / NCCL orchestration (`ShardedDedup`), which is also the fallback when the group cannot be
+    formed (no CUDA IPC between the ranks)."""
+    import os
+    import sys
+
+    world, rank = dist.get_world_size(), dist.get_rank()
+    if os.environ.get("HUMID_SHARD_TRANSPORT", "peer") != "nccl" and torch.cuda.is_available() and world <= MAX_PARTS:
+        name = [None]
+        if rank == 0:
+            _group_serial[0] += 1
+            name[0] = "/humid_%d_%d_%s" % (os.getpid(), _group_serial[0], os.urandom(4).hex())
+        dist.broadcast_object_list(name, src=0)
+        ok, dd = 1, None
+        try:
+            dd = GroupDedup(rank, world, None, name[0], **kw)
+        except api.HumidGpuError as e:
+            ok = 0
+            sys.stderr.write(f"rank {rank}: no peer-memory group ({e}); falling back to NCCL\n")
+        oks = [None] * world
+        dist.all_gather_object(oks, ok)
+        if all(oks):
+            return dd
+        if dd is not None:
+            dd.close()
     return ShardedDedup(**kw)
 
 

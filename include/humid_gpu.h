@@ -107,6 +107,18 @@ int humid_gpu_add_batch(humid_gpu *h, const uint8_t *chars, const uint16_t *seg_
 int humid_gpu_add_batch_device(humid_gpu *h, const uint8_t *d_chars, const uint16_t *d_seg_len,
                                uint64_t first_tuple_index, uint64_t n_tuples);
 
+/* humid_gpu_add_batch with the characters in the 4-bit wire format — half the bytes on the host -> device link,
+ * which is what bounds the path end to end.  Same reference call sites as humid_gpu_add_batch (makeWord + trie.add,
+ * src/humid.cc:92-99); the cut / pad rule, the ACGT-only filter and the 2-bit packing still run on the device.
+ *   nibbles  n_tuples x ((word_length + 1) / 2) bytes, tuple-major; character q of a tuple (same order and segment
+ *            layout as `chars` above) is the HIGH nibble of byte q / 2 when q is even, the low nibble when odd;
+ *            code 0..3 = A C G T (src/fastq.cc:12), any other code (HUMID_NIBBLE_OTHER) = any other byte; the unused
+ *            low nibble of the last byte of an odd-length word is ignored.
+ *   seg_len  as for humid_gpu_add_batch. */
+#define HUMID_NIBBLE_OTHER 4
+int humid_gpu_add_batch_packed4(humid_gpu *h, const uint8_t *nibbles, const uint16_t *seg_len,
+                                uint64_t first_tuple_index, uint64_t n_tuples);
+
 /* Replaces findHammingNeighbours / findEditNeighbours (src/humid.cc:113-158; hamming_ /
  * levenshtein_ lib/trie/src/trieFunctions.tcc:156-233), findClusters (:167-193;
  * src/cluster.cc), runStatistics (:301-315) and clusterStats (src/cluster.cc:89-95). */

@@ -102,6 +102,41 @@ int humid_gpu_shard_keep_bits(humid_gpu *h, uint32_t *d_bits, uint64_t n_words32
  * and keep id 0). */
 int humid_gpu_shard_tuple_ids(humid_gpu *h, uint32_t *d_ids);
 
+/* ---- Groups: the same phases run by the library itself, exchanges over peer memory -------------------------
+ *
+ * Every rank of a job — one GPU each; host threads of one process or processes of one node — creates its handle,
+ * joins the group, adds its share of the read tuples and then calls humid_gpu_group_finalize(): a COLLECTIVE call that
+ * runs everything between readData and the outputs (the phases above) with the exchanges done by the kernels
+ * themselves: a rank's partition pass stores its tuples straight into the owners' buffers, words and entries of the
+ * join and the open components travel as device-to-device copies, keep bits and cluster ids are scattered into the
+ * buffer of the rank that fed the tuple — all through peer mappings (cudaDeviceEnablePeerAccess inside a process,
+ * CUDA IPC handles between processes) over NVLink, with counts, splitters and barriers in a small shared host
+ * segment.  No NCCL on the data path, no Python between the phases.
+ *
+ * Tuple numbering: with HUMID_GROUP_SLICES rank r's tuples are the r-th contiguous slice of the job's input order
+ * (add_batch numbers them from 0 on every rank; the library adds the offsets); with HUMID_GROUP_BATCHES
+ * first_tuple_index of humid_gpu_add_batch is the GLOBAL position of the batch (any rank may take any batch, as
+ * long as a rank's own batches ascend) and the per-tuple results of the whole job are collected on rank 0. */
+enum { HUMID_GROUP_SLICES = 0, HUMID_GROUP_BATCHES = 1 };
+
+typedef struct humid_gpu_group humid_gpu_group; /* ranks that are threads of one process share this object */
+humid_gpu_group *humid_gpu_group_create(uint32_t world);
+void humid_gpu_group_destroy(humid_gpu_group *g);
+
+/* g != NULL: in-process group (shm_name ignored).  g == NULL: ranks are processes; shm_name names a POSIX shared
+ * memory segment (e.g. "/humid_<job id>") that rank 0 creates and the others attach to.  Collective. */
+int humid_gpu_group_join(humid_gpu *h, humid_gpu_group *g, const char *shm_name, uint32_t rank, uint32_t world,
+                         int tuple_numbering);
+/* Collective; replaces humid_gpu_finalize.  Afterwards humid_gpu_counts reports the whole job; humid_gpu_keep_mask
+ * and humid_gpu_cluster_ids answer for this rank's own tuples (HUMID_GROUP_SLICES: positions relative to the rank's
+ * first tuple; HUMID_GROUP_BATCHES: global positions, on rank 0); humid_gpu_histogram returns the merged histograms. */
+int humid_gpu_group_finalize(humid_gpu *h);
+/* Collective: prepares humid_gpu_cluster_ids (the owners of the words send every tuple's id to the rank that fed it). */
+int humid_gpu_group_collect_ids(humid_gpu *h);
+/* Milliseconds of the phases of the last humid_gpu_group_finalize on this rank (host clock around each phase, device
+ * synchronised): names[i] / ms[i], *n in: capacity, out: count. */
+int humid_gpu_group_phases(humid_gpu *h, const char **names, float *ms, uint32_t *n);
+
 #ifdef __cplusplus
 }
 #endif

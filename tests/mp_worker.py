@@ -19,8 +19,16 @@ from humid_b200.synth import Synth, baseline_config  # noqa: E402
 out_path = sys.argv[1]
 cases = json.loads(sys.argv[2])
 rank, world, local = (int(os.environ[k]) for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"))
+# HUMID_TEST_ONE_DEVICE=1: all ranks on device 0 (CUDA IPC between processes works on one device too; NCCL does not
+# take two ranks on one GPU, so the rendezvous is gloo and only the library's own peer-memory transport can run)
+one_device = os.environ.get("HUMID_TEST_ONE_DEVICE") == "1"
+if one_device:
+    local = 0
 torch.cuda.set_device(local)
-dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+if one_device:
+    dist.init_process_group("gloo")
+else:
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 problems = []
 for ci, R, kw in cases:
     cfg = baseline_config(ci, R, **kw)
@@ -32,6 +40,8 @@ for ci, R, kw in cases:
     dd = sharded.make_sharded(word_length=cfg.word_length, distance=cfg.distance, seg_take=seg_take, edit=cfg.edit,
                               maximum=cfg.maximum, device=local)
     for step in range(2):  # twice through one handle: reset must leave nothing behind
+        if one_device:
+            assert isinstance(dd, sharded.GroupDedup), "the peer-memory group could not be formed"
         dd.reset()
         half = (hi - lo) // 2
         dd.add_batch(chars[lo:lo + half])

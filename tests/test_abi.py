@@ -34,7 +34,7 @@ def test_header_symbols_exported(lib):
         assert hasattr(lib, s), s
     from humid_b200 import sharded
 
-    assert sorted(api.EXPORTS + sharded.SHARD_EXPORTS) == syms
+    assert sorted(api.EXPORTS + sharded.SHARD_EXPORTS + sharded.GROUP_EXPORTS) == syms
 
 
 def test_abi_version(lib):

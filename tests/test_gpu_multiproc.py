@@ -34,3 +34,19 @@ def test_ranks_match_oracle(world, tmp_path):
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
     assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-3000:]
     assert out.read_text().strip() == "ok", out.read_text()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_processes_on_one_device_use_peer_memory(world, tmp_path):
+    """The library's own transport between PROCESSES (shared host segment + CUDA IPC mappings), on whatever single GPU
+    the box has."""
+    if visible_gpus() < 1:
+        pytest.skip("needs a GPU")
+    out = tmp_path / "result.txt"
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(29650 + world), os.path.join(HERE, "mp_worker.py"), str(out),
+           json.dumps(CASES[:3])]
+    env = dict(os.environ, HUMID_TEST_ONE_DEVICE="1")
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env)
+    assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-3000:]
+    assert out.read_text().strip() == "ok", out.read_text()
