@@ -435,6 +435,14 @@ def run_gpu_arm(args):
     h_chars.copy_(d_chars)
     torch.cuda.synchronize()
     h_np = h_chars.numpy()
+    # the 4-bit wire format of humid_gpu_add_batch_packed4 (two characters per byte), packed once outside the timed
+    # region the way the executable's parser writes it as it goes; page-locked like the ASCII buffer
+    wire = args.wire
+    row_bytes = (cfg.word_length + 1) // 2
+    h_nib = torch.empty((R_per, row_bytes), dtype=torch.uint8, pin_memory=True)
+    h_nib_np = h_nib.numpy()
+    for a in range(0, R_per, 4_000_000):
+        h_nib_np[a:a + 4_000_000] = api.pack_nibbles(h_np[a:a + 4_000_000])
 
     kw = dict(word_length=cfg.word_length, distance=cfg.distance, seg_take=seg_take, edit=cfg.edit, maximum=cfg.maximum,
               device=local)
@@ -456,10 +464,14 @@ def run_gpu_arm(args):
 
     d2h = [0]
 
-    def step_e2e():
+    def step_e2e(packed=None):
+        packed = (wire == "packed4") if packed is None else packed
         dd.reset()
         for a in range(0, R_per, BATCH):
-            dd.add_batch(h_np[a:a + BATCH])
+            if packed:
+                dd.add_batch_packed4(h_nib_np[a:a + BATCH])
+            else:
+                dd.add_batch(h_np[a:a + BATCH])
         dd.finalize()
         bits = dd.keep_bits()
         n = bits.nbytes
@@ -504,10 +516,17 @@ def run_gpu_arm(args):
     for _ in range(max(1, min(args.warmup, 2))):
         step_e2e()
     ms_e2e, wall_e2e, (counts_e2e, _) = timed(step_e2e, args.steps)
+    # the other wire format beside it (a few steps): what the bytes on the host link cost
+    other = (lambda: step_e2e(wire != "packed4"))
+    other()
+    ms_alt, wall_alt, (counts_alt, _) = timed(other, max(2, args.steps // 2))
+    t_alt = max(ms_alt / 1e3, wall_alt) / max(2, args.steps // 2)
+    assert counts_alt == counts_e2e, (counts_alt, counts_e2e)
     clocks = sampler.stop() if sampler else None
     assert counts == counts_e2e, (counts, counts_e2e)
-    if world > 1 and rank == 0 and getattr(dd, "phases", None):
-        sys.stderr.write("phases (ms, last step, rank 0): " + json.dumps([(n, round(t, 3)) for n, t in dd.phases]) + "\n")
+    phases = [(n, round(t, 3)) for n, t in (getattr(dd, "phases", None) or [])] if world > 1 else None
+    if phases and rank == 0:
+        sys.stderr.write("phases (ms, last step, rank 0): " + json.dumps(phases) + "\n")
 
     # ---- N > 1: the same total job on ONE GPU (outside the timed region) must give identical results ----
     parity = None
@@ -652,7 +671,12 @@ def run_gpu_arm(args):
                    "parallelism": "1 GPU" if world == 1 else
                    f"word space range-partitioned over {world} GPUs, one process per GPU; exchanges: {transport}"},
         "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": t_e2e * 1e3,
-                "h2d_bytes_per_step": int(R_all * cfg.word_length), "d2h_bytes_per_step": int(d2h[0]) * world,
+                "h2d_bytes_per_step": int(R_all * (row_bytes if wire == "packed4" else cfg.word_length)),
+                "d2h_bytes_per_step": int(d2h[0]) * world,
+                "wire_format": "4 bits per character (humid_gpu_add_batch_packed4)" if wire == "packed4" else "ASCII (humid_gpu_add_batch)",
+                "other_wire_format": {"format": "ASCII" if wire == "packed4" else "4 bits per character", "ms_per_step": t_alt * 1e3,
+                                      "value": R_all / t_alt,
+                                      "h2d_bytes_per_step": int(R_all * (cfg.word_length if wire == "packed4" else row_bytes))},
                 "scope": "C ABI with host buffers: word characters in pinned host memory in, keep mask + histograms + "
                          "counts on the host out; compare with the reference arm's `value` (same scope, bounded sample)"},
         "gpu_launches": int(launches_per_step * args.steps),
@@ -662,6 +686,8 @@ def run_gpu_arm(args):
         line["cpu_baseline"] = cpu
     if parity:
         line["parity"] = parity
+    if phases:
+        line["detail"]["phases_ms_rank0_last_e2e_step"] = phases
     if world == 1 and not args.no_cli:
         dd.close()
         del d_chars
@@ -687,6 +713,8 @@ def main():
     ap.add_argument("--no-cli", action="store_true", help="skip the whole-program legs (cli_e2e)")
     ap.add_argument("--cli-scale", type=float, default=float(os.environ.get("HUMID_BENCH_CLI_SCALE", "1.0")),
                     help="scale the tuple counts of the whole-program legs")
+    ap.add_argument("--wire", default="packed4", choices=["packed4", "ascii"],
+                    help="host -> device format of the e2e leg: 4 bits per character (default) or ASCII")
     ap.add_argument("--ref-sample", type=int, default=REF_SAMPLE_TUPLES, help="tuples of the CPU arm's bounded sample")
     ap.add_argument("--config", type=int, default=1, help="BASELINE.json configs[i] (0-based); the bench line is configs[1]")
     ap.add_argument("--word-length", type=int, default=0, help="override -n (e.g. 36: all 12 UMI letters of configs[1])")

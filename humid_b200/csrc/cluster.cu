@@ -79,6 +79,29 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// The same over a list of DIRECTED entries (local row << 32 | column + base): shard mode, where a column outside
+// [0, U) belongs to a word of another shard and marks the row's component as open.
+__global__ void __launch_bounds__(256)
+    uf_union_entries_kernel(const uint64_t *__restrict__ entries, uint64_t E, uint64_t U, uint32_t base,
+                            uint32_t *__restrict__ open_flag, uint32_t *parent) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= E) return;
+  const uint64_t e = ld_stream_u64(entries + i);
+  uint32_t x = (uint32_t)(e >> 32), y = (uint32_t)e - base;
+  if (y >= U) {
+    if (open_flag) open_flag[x] = 1u;
+    return;
+  }
+  if (y <= x) return;  // every undirected pair is present in both directions; take it once
+  while (true) {
+    x = uf_find(parent, x);
+    y = uf_find(parent, y);
+    if (x == y) break;
+    if (x > y) { uint32_t t = x; x = y; y = t; }
+    if (atomicCAS(parent + y, y, x) == y) break;
+  }
+}
+
 // comp[r] = root; csize[root] = number of members (singletons are not counted: csize stays 0)
 __global__ void uf_flatten_kernel(uint32_t *parent, uint32_t *comp, uint32_t *csize, uint64_t U,
                                   const uint32_t *__restrict__ open_flag, uint32_t *__restrict__ comp_open) {
@@ -128,16 +151,30 @@ __global__ void __launch_bounds__(256)
     label[r] = lab;
     seed_flag[r] = flag;
   }
-  const uint32_t lane = lane_id(), lt = (1u << lane) - 1u;
+  // dense list of the small components' roots: one cursor bump per CTA (a cursor is one address, and returning
+  // atomics on one address complete at well under 1 G/s: one per warp made this kernel 0.5 ms long)
+  __shared__ uint32_t warp_small[8], warp_big[8];
+  __shared__ unsigned long long cta_base;
+  const uint32_t lane = lane_id(), lt = (1u << lane) - 1u, w = threadIdx.x >> 5;
   const unsigned ms = __ballot_sync(0xffffffffu, small), mb = __ballot_sync(0xffffffffu, big);
-  if (ms) {
-    unsigned long long base = 0;
-    const int leader = __ffs(ms) - 1;
-    if ((int)lane == leader) base = atomicAdd(n_small, (unsigned long long)__popc(ms));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (small) small_roots[base + __popc(ms & lt)] = (uint32_t)r;
+  if (lane == 0) {
+    warp_small[w] = __popc(ms);
+    warp_big[w] = __popc(mb);
   }
-  if (mb && lane == 0) atomicAdd(n_big_roots, (unsigned long long)__popc(mb));
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t run = 0, nb = 0;
+    for (int k = 0; k < 8; k++) {
+      const uint32_t c = warp_small[k];
+      warp_small[k] = run;
+      run += c;
+      nb += warp_big[k];
+    }
+    cta_base = run ? atomicAdd(n_small, (unsigned long long)run) : 0ull;
+    if (nb) atomicAdd(n_big_roots, (unsigned long long)nb);
+  }
+  __syncthreads();
+  if (small) small_roots[cta_base + warp_small[w] + __popc(ms & lt)] = (uint32_t)r;
 }
 
 // (root, rank) keys of the words of the large components (run only when there is one)
@@ -355,6 +392,10 @@ int stage_cluster(State &s) {
       if (s.n_cluster_pairs)
         uf_union_pairs_kernel<<<grid_for(s.n_cluster_pairs, 256), 256, 0, s.stream>>>(s.cluster_pairs, s.n_cluster_pairs,
                                                                                        s.work_a.p);
+    } else if (s.cluster_entries) {
+      if (s.n_cluster_entries)
+        uf_union_entries_kernel<<<grid_for(s.n_cluster_entries, 256), 256, 0, s.stream>>>(
+            s.cluster_entries, s.n_cluster_entries, U, s.cluster_col_base, open_flag, s.work_a.p);
     } else {
       uf_union_kernel<<<g256, 256, 0, s.stream>>>(s.row_ptr.p, s.col.p, s.n_entries, U, s.cluster_col_base, open_flag,
                                                   s.work_a.p);

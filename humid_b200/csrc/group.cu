@@ -226,16 +226,35 @@ __device__ __forceinline__ uint32_t result_range(const ResultTable &T, uint32_t 
   return q;
 }
 
-// writeFiltered's decision (src/humid.cc:223-231): one bit per cluster seeded here, set in the bitmap of the rank
-// that fed the first tuple of the cluster's maxLeaf word
+// writeFiltered's decision (src/humid.cc:223-231): one bit per cluster seeded here, for the first tuple of the
+// cluster's maxLeaf word.  The bits are set in LOCAL bitmaps, one per result range (bit t - start[q] of the bitmap
+// at range_off[q]: the layout of the rank that holds the range), which then travel to those ranks as plain copies and
+// are OR-ed there — scattering single bits into a peer's memory costs a remote atomic each (0.33 ms for 8 M clusters).
+struct LocalBits {
+  uint32_t n;
+  uint64_t start[G_MAX + 1];
+  uint64_t range_off[G_MAX];  // in 32-bit words
+};
 __global__ void __launch_bounds__(256)
-    push_keep_bits_kernel(const uint32_t *__restrict__ cluster_first, uint64_t C, const ResultTable T) {
+    local_keep_bits_kernel(const uint32_t *__restrict__ cluster_first, uint64_t C, const LocalBits L,
+                           uint32_t *__restrict__ bits) {
   const uint64_t c = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const uint32_t t = cluster_first[c];
-  const uint32_t q = result_range(T, t);
-  const uint32_t l = t - (uint32_t)T.start[q];
-  atomicOr(T.bits[q] + (l >> 5), 1u << (l & 31u));
+  uint32_t q = 0;
+  for (uint32_t i = 1; i < L.n; i++) q += (t >= L.start[i]) ? 1u : 0u;
+  const uint32_t l = t - (uint32_t)L.start[q];
+  atomicOr(bits + L.range_off[q] + (l >> 5), 1u << (l & 31u));
+}
+
+__global__ void __launch_bounds__(256)
+    or_slices_kernel(const uint32_t *__restrict__ slices, uint32_t n_slices, uint64_t words, uint64_t stride_words,
+                     uint32_t *__restrict__ out) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= words) return;
+  uint32_t v = 0;
+  for (uint32_t k = 0; k < n_slices; k++) v |= slices[k * stride_words + i];
+  out[i] = v;
 }
 
 // writeAnnotated's id (src/humid.cc:276-277) of every tuple this shard counted, stored where its feeder reads it
@@ -352,10 +371,9 @@ static void group_finalize_body(humid_gpu *h) {
   for (uint32_t r = 0; r < W; r++) need[r] = 256;
   for (uint32_t q = 0; q < g.n_res; q++) {
     const uint64_t m = g.res_start[q + 1] - g.res_start[q];
-    need[g.res_rank[q]] = bits_bytes(m) + m * 4 + 256;
+    need[g.res_rank[q]] = bits_bytes(m) + align_up(m * 4) + (uint64_t)W * bits_bytes(m) + 256;  // bits, ids, W slices
   }
   group_ensure(s, g, BUF_RESULT, need);
-  HUMID_CUDA(cudaMemsetAsync(g.buf[BUF_RESULT].p, 0, g.my_bits_bytes, s.stream));
 
   // splitters: quantiles of the pooled samples, cut back to a boundary of block 0 of the join (no group of that
   // block may straddle two shards, include/humid_gpu_shard.h: join_local)
@@ -527,13 +545,36 @@ static void group_finalize_body(humid_gpu *h) {
   }
 
   // ---- outputs: keep bits to the ranks that fed the tuples, histograms merged --------------------------------
-  const ResultTable RT = result_table(g);
-  if (s.n_clusters) {
-    Timed t(s, "keep", s.n_clusters, s.n_clusters * 8);
-    push_keep_bits_kernel<<<grid_for(s.n_clusters, 256), 256, 0, s.stream>>>(s.cluster_first.p, s.n_clusters, RT);
-    HUMID_CUDA(cudaGetLastError());
+  {
+    LocalBits L{};
+    L.n = g.n_res;
+    uint64_t off_words = 0;
+    for (uint32_t q = 0; q < g.n_res; q++) {
+      L.start[q] = g.res_start[q];
+      L.range_off[q] = off_words;
+      off_words += bits_bytes(g.res_start[q + 1] - g.res_start[q]) / 4;
+    }
+    L.start[g.n_res] = g.res_start[g.n_res];
+    s.keep_bits.ensure(off_words + 2);
+    HUMID_CUDA(cudaMemsetAsync(s.keep_bits.p, 0, off_words * 4, s.stream));
+    if (s.n_clusters) {
+      Timed t(s, "keep", s.n_clusters, s.n_clusters * 8);
+      local_keep_bits_kernel<<<grid_for(s.n_clusters, 256), 256, 0, s.stream>>>(s.cluster_first.p, s.n_clusters, L,
+                                                                              s.keep_bits.p);
+      HUMID_CUDA(cudaGetLastError());
+    }
+    for (uint32_t q = 0; q < g.n_res; q++) {  // my bitmap of range q -> slice `me` in the result buffer of its holder
+      const uint64_t m = g.res_start[q + 1] - g.res_start[q];
+      const size_t bb = bits_bytes(m);
+      char *dst = reinterpret_cast<char *>(g.peer[BUF_RESULT][g.res_rank[q]]) + bb + align_up(m * 4) + (size_t)me * bb;
+      d2d(dst, s.keep_bits.p + L.range_off[q], bb, s.stream);
+    }
   }
-  for (int w = 0; w < 3; w++) stage_histogram(s, w);  // this shard's words / lists / clusters
+  stage_histograms_enqueue(s);  // this shard's words / lists / clusters, on their way to page-locked memory
+  HUMID_CUDA(cudaStreamSynchronize(s.stream));
+  stage_histograms_collect(s);
+  for (int w = 0; w < 3; w++)
+    if (!s.hist_done[w]) stage_histogram(s, w);  // more large values than the eager form lists
   for (int w = 0; w < 3; w++) {
     const size_t m = s.hist_k[w].size();
     if (m > G_HIST_CAP) throw CudaError{"a histogram of one shard has more than " + std::to_string(G_HIST_CAP) + " keys"};
@@ -541,11 +582,20 @@ static void group_finalize_body(humid_gpu *h) {
     std::copy(s.hist_k[w].begin(), s.hist_k[w].end(), mine.hist_k[w]);
     std::copy(s.hist_v[w].begin(), s.hist_v[w].end(), mine.hist_v[w]);
   }
-  HUMID_CUDA(cudaStreamSynchronize(s.stream));
-  group_barrier(g);  // every keep bit has landed, every histogram is in the segment
-  s.keep_host_words = (g.my_res_n + 31) / 32 + 2;
-  s.keep_host.ensure(s.keep_host_words);
-  HUMID_CUDA(cudaMemcpyAsync(s.keep_host.p, g.buf[BUF_RESULT].p, s.keep_host_words * 4, cudaMemcpyDeviceToHost, s.stream));
+  group_barrier(g);  // every slice has landed, every histogram is in the segment
+  {
+    const size_t bb = g.my_bits_bytes;
+    char *rb = reinterpret_cast<char *>(g.buf[BUF_RESULT].p);
+    if (g.my_res_n)
+      or_slices_kernel<<<grid_for(bb / 4, 256), 256, 0, s.stream>>>(
+          reinterpret_cast<const uint32_t *>(rb + bb + align_up(g.my_res_n * 4)), W, bb / 4, bb / 4,
+          reinterpret_cast<uint32_t *>(rb));
+    HUMID_CUDA(cudaGetLastError());
+    s.keep_host_words = (g.my_res_n + 31) / 32 + 2;
+    s.keep_host.ensure(s.keep_host_words);
+    if (g.my_res_n)
+      HUMID_CUDA(cudaMemcpyAsync(s.keep_host.p, rb, s.keep_host_words * 4, cudaMemcpyDeviceToHost, s.stream));
+  }
   for (int w = 0; w < 3; w++) {
     std::map<uint64_t, uint64_t> merged;
     for (uint32_t r = 0; r < W; r++)
@@ -559,7 +609,7 @@ static void group_finalize_body(humid_gpu *h) {
     s.hist_done[w] = true;
   }
   HUMID_CUDA(cudaStreamSynchronize(s.stream));
-  group_barrier(g);  // the segment may be written again
+  group_barrier(g);  // the segment and the slices may be written again
   resolve_stats(s);
   clock.mark("keep bits + histograms");
 }

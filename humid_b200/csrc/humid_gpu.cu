@@ -120,6 +120,8 @@ int humid_gpu_reset(humid_gpu *h) {
     s.cluster_col_base = 0;
     s.cluster_pairs = nullptr;
     s.n_cluster_pairs = 0;
+    s.cluster_entries = nullptr;
+    s.n_cluster_entries = 0;
     s.report_tuples = s.report_usable = s.tuple_base = s.n_shard_words = s.src_n = 0;
     s.src_keys = nullptr;
     s.src_index = nullptr;

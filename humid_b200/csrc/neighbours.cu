@@ -738,11 +738,14 @@ int stage_csr_pairs(State &s) {
   s.n_entries = 2 * s.n_pairs;
   s.cluster_pairs = s.entries.p;  // the union-find takes the pairs as they are
   s.n_cluster_pairs = s.n_pairs;
+  s.cluster_entries = nullptr;
   return csr_from_degrees(s, s.n_entries, true);
 }
 
 int stage_csr_directed(State &s) {
   s.cluster_pairs = nullptr;
+  s.cluster_entries = s.entries.p;  // csr_fill_directed_kernel only reads them
+  s.n_cluster_entries = s.n_entries;
   return csr_from_degrees(s, s.n_entries, false);
 }
 
@@ -764,6 +767,7 @@ __global__ void __launch_bounds__(256)
 int stage_csr(State &s) {
   const uint64_t U = s.unique, E = s.n_entries;
   s.cluster_pairs = nullptr;
+  s.cluster_entries = nullptr;
   int k = 0;
   s.row_ptr.ensure(U + 2);
   s.col.ensure(E + 1);

@@ -184,6 +184,8 @@ struct State {
   // clustering
   const uint64_t *cluster_pairs = nullptr;  // undirected pairs (rank << 32 | rank) behind the CSR, when the search left them
   uint64_t n_cluster_pairs = 0;
+  const uint64_t *cluster_entries = nullptr;  // directed entries (local row << 32 | column + base) behind the CSR (shard mode)
+  uint64_t n_cluster_entries = 0;
   DevBuf<uint32_t> big_up, big_t, big_cursor, big_lo, big_hi, big_src, big_level;  // cluster_big.cu
   DevBuf<uint64_t> big_keys, big_keys_alt;
   DevBuf<uint32_t> comp, label, members, seg_start, seg_end, work_a, work_b, work_c;

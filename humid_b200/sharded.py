@@ -458,6 +458,10 @@ class ShardedDedup:
         self.eng.add_batch_device(d_chars, n, d_seg_len)
         self.n_local = self.eng.n_tuples
 
+    def add_batch_packed4(self, nibbles, seg_len=None):
+        self.eng.add_batch_packed4(nibbles, seg_len)
+        self.n_local = self.eng.n_tuples
+
     def _gather_ints(self, *vals: int) -> np.ndarray:
         dev = self.eng.device
         t = torch.tensor(list(vals), dtype=torch.int64, device=dev)
