@@ -171,47 +171,122 @@ struct PushTable {
 
 // The exchange of the read tuples fused into the partition pass: a tuple's {key, global position} is stored
 // straight into the arena of the rank that owns its key range (peer memory over NVLink), at a cursor that starts
-// where this rank's share of that arena begins.  One global atomic per CTA and part; order inside a share is
-// arbitrary (Trie::add does not depend on it: counts add up, the first tuple is a minimum).
-__global__ void __launch_bounds__(256)
+// where this rank's share of that arena begins.  A CTA first groups its PUSH_TILE tuples by destination in shared
+// memory, so that what crosses NVLink are runs of consecutive addresses written by consecutive threads (the first
+// version stored every tuple where its thread happened to be: 8-byte stores scattered over eight peers took 2.6 ms
+// for 50 M tuples on 8 GPUs).  One global atomic per CTA and part; order inside a share is arbitrary (Trie::add does
+// not depend on it: counts add up, the first tuple is a minimum).
+constexpr int PUSH_THREADS = 256, PUSH_ITEMS = 8, PUSH_TILE = PUSH_THREADS * PUSH_ITEMS;
+__global__ void __launch_bounds__(PUSH_THREADS)
     push_tuples_kernel(const uint64_t *__restrict__ keys, uint64_t R, uint32_t tuple_base, const PushTable T,
                        unsigned long long *__restrict__ cursors) {
-  __shared__ uint32_t cnt[G_MAX];
-  __shared__ unsigned long long base[G_MAX];
-  constexpr int ITEMS = 4;
-  if (threadIdx.x < G_MAX) cnt[threadIdx.x] = 0;
+  __shared__ uint64_t skey[PUSH_TILE];
+  __shared__ uint32_t sidx[PUSH_TILE];
+  __shared__ uint32_t cnt[G_MAX + 1], loff[G_MAX + 1];
+  __shared__ unsigned long long gbase[G_MAX];
+  if (threadIdx.x <= G_MAX) cnt[threadIdx.x] = 0;
   __syncthreads();
-  const uint64_t t0 = (uint64_t)blockIdx.x * (256 * ITEMS);
-  uint64_t key[ITEMS];
-  uint32_t own[ITEMS], slot[ITEMS];
+  const uint64_t t0 = (uint64_t)blockIdx.x * PUSH_TILE;
+  const uint32_t lane = lane_id(), lt = (1u << lane) - 1u;
+  uint64_t key[PUSH_ITEMS];
+  uint32_t own[PUSH_ITEMS], slot[PUSH_ITEMS];
 #pragma unroll
-  for (int j = 0; j < ITEMS; j++) {
-    const uint64_t t = t0 + (uint64_t)j * 256 + threadIdx.x;
+  for (int j = 0; j < PUSH_ITEMS; j++) {
+    const uint64_t t = t0 + (uint64_t)j * PUSH_THREADS + threadIdx.x;
     key[j] = t < R ? ld_stream_u64(keys + t) : KEY_INVALID;
-    own[j] = 0;
-    slot[j] = 0;
+    uint32_t p = T.n_parts;  // filtered tuples do not travel
     if (key[j] != KEY_INVALID) {
-      uint32_t p = 0;
+      p = 0;
       for (uint32_t i = 0; i + 1 < T.n_parts; i++) p += (key[j] >= T.splitters[i]) ? 1u : 0u;
-      own[j] = p;
-      slot[j] = atomicAdd(&cnt[p], 1u);
     }
+    own[j] = p;
+    // lanes with the same destination share one shared-memory atomic
+    const uint32_t peers = __match_any_sync(0xffffffffu, p);
+    const int leader = __ffs(peers) - 1;
+    uint32_t first = 0;
+    if ((int)lane == leader) first = atomicAdd(&cnt[p], (uint32_t)__popc(peers));
+    slot[j] = __shfl_sync(0xffffffffu, first, leader) + __popc(peers & lt);
   }
   __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t run = 0;
+    for (uint32_t p = 0; p < T.n_parts; p++) {
+      loff[p] = run;
+      run += cnt[p];
+    }
+    loff[T.n_parts] = run;
+  }
   if (threadIdx.x < T.n_parts) {
     const uint32_t c = cnt[threadIdx.x];
-    base[threadIdx.x] = c ? atomicAdd(cursors + threadIdx.x, (unsigned long long)c) : 0ull;
+    gbase[threadIdx.x] = c ? atomicAdd(cursors + threadIdx.x, (unsigned long long)c) : 0ull;
   }
   __syncthreads();
 #pragma unroll
-  for (int j = 0; j < ITEMS; j++) {
-    if (key[j] != KEY_INVALID) {
-      const unsigned long long pos = base[own[j]] + slot[j];
-      T.keys[own[j]][pos] = key[j];
-      T.index[own[j]][pos] = tuple_base + (uint32_t)(t0 + (uint64_t)j * 256 + threadIdx.x);
+  for (int j = 0; j < PUSH_ITEMS; j++) {
+    if (own[j] < T.n_parts) {
+      const uint32_t at = loff[own[j]] + slot[j];
+      skey[at] = key[j];
+      sidx[at] = tuple_base + (uint32_t)(t0 + (uint64_t)j * PUSH_THREADS + threadIdx.x);
     }
   }
+  __syncthreads();
+  const uint32_t total = loff[T.n_parts];
+  for (uint32_t i = threadIdx.x; i < total; i += PUSH_THREADS) {
+    uint32_t p = 0;
+    while (i >= loff[p + 1]) p++;
+    const unsigned long long pos = gbase[p] + (i - loff[p]);
+    T.keys[p][pos] = skey[i];
+    T.index[p][pos] = sidx[i];
+  }
 }
+
+// Several device-to-device copies (to other ranks' buffers as well as local) as ONE kernel: blockIdx.y picks the
+// segment.  A dozen small cudaMemcpyAsync peer copies cost their launch + copy-engine latency each (35 of them made the
+// gathering of the open components 1.2 ms long on 8 GPUs); stores from the SMs go over NVLink at full width when
+// consecutive threads write consecutive 16-byte units.  Sizes and addresses are multiples of 4 bytes.
+constexpr int COPY_MAX_SEGMENTS = 96;
+struct CopySegments {
+  uint32_t n;
+  void *dst[COPY_MAX_SEGMENTS];
+  const void *src[COPY_MAX_SEGMENTS];
+  uint64_t bytes[COPY_MAX_SEGMENTS];
+};
+__global__ void __launch_bounds__(256) multi_copy_kernel(const CopySegments S) {
+  const uint32_t k = blockIdx.y;
+  const uint64_t bytes = S.bytes[k];
+  char *dst = static_cast<char *>(S.dst[k]);
+  const char *src = static_cast<const char *>(S.src[k]);
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x, tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (((((uintptr_t)dst) | ((uintptr_t)src)) & 15u) == 0) {
+    const uint64_t n16 = bytes >> 4;
+    for (uint64_t i = tid; i < n16; i += stride) reinterpret_cast<uint4 *>(dst)[i] = reinterpret_cast<const uint4 *>(src)[i];
+    for (uint64_t i = (n16 << 2) + tid; i < (bytes >> 2); i += stride)
+      reinterpret_cast<uint32_t *>(dst)[i] = reinterpret_cast<const uint32_t *>(src)[i];
+  } else {
+    for (uint64_t i = tid; i < (bytes >> 2); i += stride)
+      reinterpret_cast<uint32_t *>(dst)[i] = reinterpret_cast<const uint32_t *>(src)[i];
+  }
+}
+
+struct CopyList {
+  CopySegments S{};
+  uint64_t largest = 0;
+  void add(void *dst, const void *src, size_t bytes) {
+    if (!bytes) return;
+    if (S.n == COPY_MAX_SEGMENTS) throw CudaError{"group: too many copy segments"};
+    S.dst[S.n] = dst;
+    S.src[S.n] = src;
+    S.bytes[S.n] = bytes;
+    S.n++;
+    largest = std::max<uint64_t>(largest, bytes);
+  }
+  void run(cudaStream_t st) {
+    if (!S.n) return;
+    const unsigned gx = (unsigned)std::min<uint64_t>(std::max<uint64_t>((largest / 16 + 255) / 256, 1), 148 * 4);
+    multi_copy_kernel<<<dim3(gx, S.n), 256, 0, st>>>(S);
+    HUMID_CUDA(cudaGetLastError());
+  }
+};
 
 struct ResultTable {
   uint32_t n;
@@ -295,10 +370,6 @@ static void exchange_counts(GroupLink &g, const uint64_t counts[], uint64_t recv
       recv[dst] += sh.r[src].slot[8 + dst];
     }
   }
-}
-
-static void d2d(void *dst, const void *src, size_t bytes, cudaStream_t st) {
-  if (bytes) HUMID_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, st));
 }
 
 static size_t bits_bytes(uint64_t tuples) { return align_up(((tuples + 31) / 32 + 2) * 4); }
@@ -413,13 +484,13 @@ static void group_finalize_body(humid_gpu *h) {
     Timed t(s, "group_push_tuples", s.n_tuples, s.n_tuples * 20);
     uint32_t launches = 0;
     if (g.numbering == HUMID_GROUP_SLICES) {
-      push_tuples_kernel<<<grid_for(s.n_tuples, 256, 4), 256, 0, s.stream>>>(s.tuple_key.p, s.n_tuples,
-                                                                             (uint32_t)g.tuple_off[me], T, cursors);
+      push_tuples_kernel<<<grid_for(s.n_tuples, PUSH_TILE), PUSH_THREADS, 0, s.stream>>>(s.tuple_key.p, s.n_tuples,
+                                                                                         (uint32_t)g.tuple_off[me], T, cursors);
       launches = 1;
     } else {
       for (const auto &b : g.batches) {
-        push_tuples_kernel<<<grid_for(b.n, 256, 4), 256, 0, s.stream>>>(s.tuple_key.p + b.local, b.n, (uint32_t)b.global,
-                                                                       T, cursors);
+        push_tuples_kernel<<<grid_for(b.n, PUSH_TILE), PUSH_THREADS, 0, s.stream>>>(s.tuple_key.p + b.local, b.n,
+                                                                                   (uint32_t)b.global, T, cursors);
         launches++;
       }
     }
@@ -456,12 +527,14 @@ static void group_finalize_body(humid_gpu *h) {
     for (uint32_t r = 0; r < W; r++) need[r] = align_up(recv[r] * 8) + recv[r] * 4 + 256;
     group_ensure(s, g, BUF_XFER, need);
     uint64_t seg = 0;
+    CopyList words;
     for (uint32_t p = 0; p < W; p++) {
       char *dst = reinterpret_cast<char *>(g.peer[BUF_XFER][p]);
-      d2d(dst + off_at[p] * 8, g.exp_keys.p + seg, counts[p] * 8, s.stream);
-      d2d(dst + align_up(recv[p] * 8) + off_at[p] * 4, g.exp_ranks.p + seg, counts[p] * 4, s.stream);
+      words.add(dst + off_at[p] * 8, g.exp_keys.p + seg, counts[p] * 8);
+      words.add(dst + align_up(recv[p] * 8) + off_at[p] * 4, g.exp_ranks.p + seg, counts[p] * 4);
       seg += counts[p];
     }
+    words.run(s.stream);
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     group_barrier(g);
     clock.mark("join: words to block owners");
@@ -475,10 +548,12 @@ static void group_finalize_body(humid_gpu *h) {
     for (uint32_t r = 0; r < W; r++) need[r] = erecv[r] * 8 + 256;
     group_ensure(s, g, BUF_XFER, need);
     seg = 0;
+    CopyList ents;
     for (uint32_t p = 0; p < W; p++) {
-      d2d(reinterpret_cast<char *>(g.peer[BUF_XFER][p]) + eoff[p] * 8, s.join_entries_out.p + seg, ecounts[p] * 8, s.stream);
+      ents.add(reinterpret_cast<char *>(g.peer[BUF_XFER][p]) + eoff[p] * 8, s.join_entries_out.p + seg, ecounts[p] * 8);
       seg += ecounts[p];
     }
+    ents.run(s.stream);
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     group_barrier(g);
     ck(humid_gpu_shard_join_import(h, reinterpret_cast<uint64_t *>(g.buf[BUF_XFER].p), erecv[me]));
@@ -512,12 +587,14 @@ static void group_finalize_body(humid_gpu *h) {
                                    u32(o_deg) + open_off, u32(o_col) + eo_off));
     HUMID_CUDA(cudaMemsetAsync(base + o_ids, 0, col4, s.stream));
     const size_t cols[4] = {o_rank, o_count, o_first, o_deg};
+    CopyList open;
     for (uint32_t p = 0; p < W; p++) {
       if (p == me) continue;
       char *dst = reinterpret_cast<char *>(g.peer[BUF_XFER][p]);
-      for (size_t off : cols) d2d(dst + off + open_off * 4, base + off + open_off * 4, n_open * 4, s.stream);
-      d2d(dst + o_col + eo_off * 4, base + o_col + eo_off * 4, n_open_e * 4, s.stream);
+      for (size_t off : cols) open.add(dst + off + open_off * 4, base + off + open_off * 4, n_open * 4);
+      open.add(dst + o_col + eo_off * 4, base + o_col + eo_off * 4, n_open_e * 4);
     }
+    open.run(s.stream);
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     group_barrier(g);
     clock.mark("open components gathered");
@@ -534,10 +611,11 @@ static void group_finalize_body(humid_gpu *h) {
     clock.mark("open components clustered");
     // ids of the open seeds: every rank fills in the ones it owns, in every rank's copy
     ck(humid_gpu_shard_assign_ids(h, id_off, u32(o_ids)));
+    CopyList ids;
     for (uint32_t p = 0; p < W; p++)
       if (p != me)
-        d2d(reinterpret_cast<char *>(g.peer[BUF_XFER][p]) + o_ids + open_off * 4, base + o_ids + open_off * 4, n_open * 4,
-            s.stream);
+        ids.add(reinterpret_cast<char *>(g.peer[BUF_XFER][p]) + o_ids + open_off * 4, base + o_ids + open_off * 4, n_open * 4);
+    ids.run(s.stream);
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     group_barrier(g);
     ck(humid_gpu_shard_finish(h, u32(o_ids), g.n_total, usable_total, bases[W], clusters_total));
@@ -563,12 +641,14 @@ static void group_finalize_body(humid_gpu *h) {
                                                                               s.keep_bits.p);
       HUMID_CUDA(cudaGetLastError());
     }
+    CopyList slices;
     for (uint32_t q = 0; q < g.n_res; q++) {  // my bitmap of range q -> slice `me` in the result buffer of its holder
       const uint64_t m = g.res_start[q + 1] - g.res_start[q];
       const size_t bb = bits_bytes(m);
       char *dst = reinterpret_cast<char *>(g.peer[BUF_RESULT][g.res_rank[q]]) + bb + align_up(m * 4) + (size_t)me * bb;
-      d2d(dst, s.keep_bits.p + L.range_off[q], bb, s.stream);
+      slices.add(dst, s.keep_bits.p + L.range_off[q], bb);
     }
+    slices.run(s.stream);
   }
   stage_histograms_enqueue(s);  // this shard's words / lists / clusters, on their way to page-locked memory
   HUMID_CUDA(cudaStreamSynchronize(s.stream));
