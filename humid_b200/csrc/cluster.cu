@@ -119,11 +119,21 @@ __global__ void uf_flatten_kernel(uint32_t *parent, uint32_t *comp, uint32_t *cs
 // singletons are closed in place; the roots of components of 2..SMALL_COMP words go to a dense list (one busy thread
 // per lane in the replay, where one thread per WORD left 27 of 32 lanes idle); the words of larger components are
 // listed as (root, rank) keys and grouped by a sort.
+// Components this pass leaves alone: (shard mode) those that continue on another shard, and — when the open components
+// are shared out among the ranks of a group — those whose root another rank owns (root mod `mod` != `me`).
+struct RootSkip {
+  const uint32_t *flags;
+  uint32_t mod, me;
+  __device__ __forceinline__ bool operator()(uint32_t root) const {
+    return (flags && flags[root]) || (mod && root % mod != me);
+  }
+};
+
 template <bool MAXIMUM>
 __global__ void __launch_bounds__(256)
     classify_words_kernel(const uint32_t *__restrict__ comp, const uint32_t *__restrict__ csize,
                           const uint32_t *__restrict__ count, uint64_t U, uint32_t small_max,
-                          const uint32_t *__restrict__ skip_root, uint32_t *__restrict__ label,
+                          const RootSkip skip_root, uint32_t *__restrict__ label,
                           uint32_t *__restrict__ seed_flag, uint64_t *__restrict__ seed_size,
                           uint32_t *__restrict__ seed_max, uint32_t *__restrict__ small_roots,
                           unsigned long long *__restrict__ n_small, unsigned long long *__restrict__ n_big_roots) {
@@ -134,7 +144,7 @@ __global__ void __launch_bounds__(256)
     // only roots look at their component (csize[r]: coalesced); the other words are listed later, and only when
     // some component is large
     uint32_t lab = MAXIMUM ? root : NONE32, flag = 0;
-    if (root == r && !(skip_root && skip_root[root])) {  // skip: (shard mode) the component continues on another shard
+    if (root == r && !skip_root(root)) {
       const uint32_t m = csize[r] + 1u;
       if (MAXIMUM) flag = 1;
       if (m == 1) {  // no neighbours: its own cluster
@@ -180,14 +190,14 @@ __global__ void __launch_bounds__(256)
 // (root, rank) keys of the words of the large components (run only when there is one)
 __global__ void __launch_bounds__(256)
     big_member_keys_kernel(const uint32_t *__restrict__ comp, const uint32_t *__restrict__ csize, uint64_t U,
-                           uint32_t small_max, const uint32_t *__restrict__ skip_root, uint64_t *__restrict__ keys,
+                           uint32_t small_max, const RootSkip skip_root, uint64_t *__restrict__ keys,
                            unsigned long long *__restrict__ counter) {
   uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   bool big = false;
   uint32_t root = 0;
   if (r < U) {
     root = comp[r];
-    big = csize[root] + 1u > small_max && !(skip_root && skip_root[root]);
+    big = csize[root] + 1u > small_max && !skip_root(root);
   }
   unsigned m = __ballot_sync(0xffffffffu, big);
   if (m == 0) return;
@@ -413,7 +423,7 @@ int stage_cluster(State &s) {
   s.key_alt.ensure(U + 1);
   s.work_b.ensure(U + 1);  // roots of the small components
   Graph g{s.row_ptr.p, s.col.p, s.word_count.p, s.cluster_col_base};
-  const uint32_t *skip_root = s.cluster_skip_open ? s.comp_open.p : nullptr;
+  const RootSkip skip_root{s.cluster_skip_open ? s.comp_open.p : nullptr, s.cluster_owner_mod, s.cluster_owner_me};
   // components of up to SMALL_COMP words are replayed by one thread each; HUMID_GPU_SMALL_COMP lowers the limit (tests:
   // 1 sends every component through cluster_big.cu)
   uint32_t small_max = SMALL_COMP;
@@ -482,7 +492,7 @@ int stage_cluster(State &s) {
     k += s.cfg.maximum ? stage_big_maximum(s, g, n_big) : stage_big_directional(s, g, n_big);
   }
   HUMID_CUDA(cudaGetLastError());
-  if (s.cluster_skip_open) return k;  // shard mode: ids are handed out after the open components are merged in
+  if (s.cluster_skip_open || s.cluster_no_ids) return k;  // shard mode: ids are handed out after the open components are merged in
   return k + stage_cluster_number(s);
 }
 

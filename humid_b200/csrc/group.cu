@@ -71,6 +71,7 @@ struct GroupLink {
   struct Batch { uint64_t local, global, n; };  // HUMID_GROUP_BATCHES
   std::vector<Batch> batches;
   std::vector<std::pair<const char *, float>> phases;
+  double wait_ms = 0.0;  // time spent inside barriers since the last phase mark (waiting for the slowest rank)
 };
 
 }  // namespace humid
@@ -84,6 +85,11 @@ namespace humid {
 static void group_barrier(GroupLink &g) {
   GroupShared &sh = *g.sh;
   if (g.world == 1) return;
+  struct Waited {
+    GroupLink &g;
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    ~Waited() { g.wait_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); }
+  } waited{g};
   const uint32_t gen = sh.generation.load(std::memory_order_acquire);
   if (sh.arrived.fetch_add(1, std::memory_order_acq_rel) + 1 == g.world) {
     sh.arrived.store(0, std::memory_order_relaxed);
@@ -344,14 +350,42 @@ __global__ void __launch_bounds__(256)
   T.ids[q][t - (uint32_t)T.start[q]] = id;
 }
 
+// Results of the open components a rank has clustered (those with root % mod == me), stored where the rank that owns
+// each word reads them: position i of the gathered open list belongs to rank d with off[d] <= i < off[d + 1].
+struct OpenResults {
+  uint32_t n;
+  uint64_t off[G_MAX + 1];
+  uint32_t *label[G_MAX], *flag[G_MAX], *mx[G_MAX];
+  uint64_t *size[G_MAX];
+};
+__global__ void __launch_bounds__(256)
+    scatter_open_results_kernel(const uint32_t *__restrict__ comp, const uint32_t *__restrict__ label,
+                                const uint32_t *__restrict__ flag, const uint64_t *__restrict__ size,
+                                const uint32_t *__restrict__ mx, uint64_t n_open, uint32_t mod, uint32_t me,
+                                const OpenResults R) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_open || comp[i] % mod != me) return;
+  uint32_t d = 0;
+  for (uint32_t k = 1; k < R.n; k++) d += (i >= R.off[k]) ? 1u : 0u;
+  R.label[d][i] = label[i];
+  R.flag[d][i] = flag[i];
+  R.mx[d][i] = mx[i];
+  R.size[d][i] = size[i];
+}
+
 // ---- helpers of the collective finalize ---------------------------------------------------------------------
 struct PhaseClock {
   GroupLink &g;
   std::chrono::steady_clock::time_point t;
-  explicit PhaseClock(GroupLink &gl) : g(gl), t(std::chrono::steady_clock::now()) { g.phases.clear(); }
+  explicit PhaseClock(GroupLink &gl) : g(gl), t(std::chrono::steady_clock::now()) {
+    g.phases.clear();
+    g.wait_ms = 0.0;
+  }
   void mark(const char *name) {  // called where the stream has just been synchronised
     const auto now = std::chrono::steady_clock::now();
     g.phases.emplace_back(name, std::chrono::duration<float, std::milli>(now - t).count());
+    if (g.wait_ms > 0.005) g.phases.emplace_back("  of which waiting at barriers", (float)g.wait_ms);
+    g.wait_ms = 0.0;
     t = now;
   }
 };
@@ -577,8 +611,9 @@ static void group_finalize_body(humid_gpu *h) {
   }
   const size_t col4 = align_up(NO * 4);
   const size_t o_rank = 0, o_count = col4, o_first = 2 * col4, o_deg = 3 * col4, o_col = 4 * col4,
-               o_ids = 4 * col4 + align_up(EO * 4);
-  for (uint32_t r = 0; r < W; r++) need[r] = o_ids + col4 + 256;
+               o_ids = 4 * col4 + align_up(EO * 4), r_label = o_ids + col4, r_flag = r_label + col4, r_max = r_flag + col4,
+               r_size = r_max + col4;
+  for (uint32_t r = 0; r < W; r++) need[r] = r_size + align_up(NO * 8) + 256;
   group_ensure(s, g, BUF_XFER, need);
   {
     char *base = reinterpret_cast<char *>(g.buf[BUF_XFER].p);
@@ -598,6 +633,38 @@ static void group_finalize_body(humid_gpu *h) {
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     group_barrier(g);
     clock.mark("open components gathered");
+    // every open component is clustered by ONE rank (root mod W); its words' results go to the ranks that own them
+    s.open_owner_mod = W;
+    s.open_owner_me = me;
+    s.after_open_cluster = [&](State &o) {
+      if (NO) {
+        OpenResults R{};
+        R.n = W;
+        for (uint32_t r = 0; r < W; r++) R.off[r + 1] = R.off[r] + sh.r[r].slot[3];
+        for (uint32_t p = 0; p < W; p++) {
+          char *xb = reinterpret_cast<char *>(g.peer[BUF_XFER][p]);
+          R.label[p] = reinterpret_cast<uint32_t *>(xb + r_label);
+          R.flag[p] = reinterpret_cast<uint32_t *>(xb + r_flag);
+          R.mx[p] = reinterpret_cast<uint32_t *>(xb + r_max);
+          R.size[p] = reinterpret_cast<uint64_t *>(xb + r_size);
+        }
+        scatter_open_results_kernel<<<grid_for(NO, 256), 256, 0, s.stream>>>(o.comp.p, o.label.p, o.seed_flag.p,
+                                                                            o.seed_size.p, o.seed_max.p, NO, W, me, R);
+        HUMID_CUDA(cudaGetLastError());
+      }
+      HUMID_CUDA(cudaStreamSynchronize(s.stream));
+      group_barrier(g);
+      CopyList back;  // this rank's own words: what their components' owners found
+      back.add(o.label.p + open_off, base + r_label + open_off * 4, n_open * 4);
+      back.add(o.seed_flag.p + open_off, base + r_flag + open_off * 4, n_open * 4);
+      back.add(o.seed_max.p + open_off, base + r_max + open_off * 4, n_open * 4);
+      back.add(o.seed_size.p + open_off, base + r_size + open_off * 8, n_open * 8);
+      back.run(s.stream);
+    };
+    struct ClearHook {
+      State &s;
+      ~ClearHook() { s.after_open_cluster = nullptr; }
+    } clear_hook{s};
     uint64_t n_cl = 0;
     ck(humid_gpu_shard_import_open(h, open_off, NO, EO, u32(o_rank), u32(o_count), u32(o_first), u32(o_deg), u32(o_col),
                                    &n_cl));

@@ -640,7 +640,11 @@ int humid_gpu_shard_import_open(humid_gpu *h, uint64_t open_offset, uint64_t n_o
       t.launches = l + 2;
     }
     HUMID_CUDA(cudaMemsetAsync(o.counters.p, 0, 64 * sizeof(unsigned long long), s.stream));
+    o.cluster_no_ids = true;  // only flags / sizes / maxLeaf per seed are merged below
+    o.cluster_owner_mod = s.open_owner_mod;  // a group shares the open components out among its ranks
+    o.cluster_owner_me = s.open_owner_me;
     stage_cluster(o);  // the same replay, on the gathered open components
+    if (s.after_open_cluster) s.after_open_cluster(o);  // results of the components other ranks own arrive here
     for (auto &st : o.stats) s.stats.push_back(st);
     o.stats.clear();
     s.seed_first.ensure(U + 1);

@@ -7,6 +7,7 @@
 //   per entry:      col[e]                           neighbour rank                    4 B
 //   per cluster:    indexed by seed rank (sparse) then compacted by id
 #pragma once
+#include <functional>
 #include <vector>
 
 #include "../../include/humid_gpu.h"
@@ -184,6 +185,10 @@ struct State {
   // clustering
   const uint64_t *cluster_pairs = nullptr;  // undirected pairs (rank << 32 | rank) behind the CSR, when the search left them
   uint64_t n_cluster_pairs = 0;
+  bool cluster_no_ids = false;  // stage_cluster stops before numbering the clusters (the gathered open components)
+  uint32_t cluster_owner_mod = 0, cluster_owner_me = 0;  // != 0: only components with root % mod == me are clustered here
+  uint32_t open_owner_mod = 0, open_owner_me = 0;        // shard mode: the same for the gathered open components ...
+  std::function<void(State &)> after_open_cluster;       // ... whose results the group then exchanges (group.cu)
   const uint64_t *cluster_entries = nullptr;  // directed entries (local row << 32 | column + base) behind the CSR (shard mode)
   uint64_t n_cluster_entries = 0;
   DevBuf<uint32_t> big_up, big_t, big_cursor, big_lo, big_hi, big_src, big_level;  // cluster_big.cu
