@@ -525,8 +525,17 @@ def run_gpu_arm(args):
     clocks = sampler.stop() if sampler else None
     assert counts == counts_e2e, (counts, counts_e2e)
     phases = [(n, round(t, 3)) for n, t in (getattr(dd, "phases", None) or [])] if world > 1 else None
+    if world > 1:  # every rank's phases of its last step: what the slowest rank spends where (diagnostic, untimed)
+        allp = [None] * world
+        dist.all_gather_object(allp, phases)
+        if rank == 0 and phases and all(a and len(a) == len(phases) for a in allp):
+            spread = []
+            for i, (nm, _) in enumerate(phases):
+                vals = [a[i][1] for a in allp]
+                spread.append((nm, min(vals), max(vals), int(np.argmax(vals))))
+            phases = [{"phase": nm, "min_ms": lo, "max_ms": hi, "slowest_rank": r} for nm, lo, hi, r in spread]
     if phases and rank == 0:
-        sys.stderr.write("phases (ms, last step, rank 0): " + json.dumps(phases) + "\n")
+        sys.stderr.write("phases (ms, last step): " + json.dumps(phases) + "\n")
 
     # ---- N > 1: the same total job on ONE GPU (outside the timed region) must give identical results ----
     parity = None
@@ -687,7 +696,7 @@ def run_gpu_arm(args):
     if parity:
         line["parity"] = parity
     if phases:
-        line["detail"]["phases_ms_rank0_last_e2e_step"] = phases
+        line["detail"]["phases_ms_last_e2e_step"] = phases
     if world == 1 and not args.no_cli:
         dd.close()
         del d_chars
