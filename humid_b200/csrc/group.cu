@@ -384,7 +384,7 @@ struct PhaseClock {
   void mark(const char *name) {  // called where the stream has just been synchronised
     const auto now = std::chrono::steady_clock::now();
     g.phases.emplace_back(name, std::chrono::duration<float, std::milli>(now - t).count());
-    if (g.wait_ms > 0.005) g.phases.emplace_back("  of which waiting at barriers", (float)g.wait_ms);
+    g.phases.emplace_back("  of which waiting at barriers", (float)g.wait_ms);
     g.wait_ms = 0.0;
     t = now;
   }
