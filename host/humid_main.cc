@@ -24,11 +24,13 @@
 #include <cstdlib>
 #include <ctime>
 #include <fstream>
+#include <functional>
 #include <memory>
 #include <mutex>
 #include <thread>
 
 #include "../include/humid_gpu.h"
+#include "../include/humid_gpu_shard.h"
 #include "fastq_block.h"
 #include "fastq_io.h"
 #include "fastq_rewrite.h"
@@ -43,6 +45,7 @@ struct Options {
   size_t word_length = 24, distance = 1;
   string log_name = "/dev/stderr", dir_name = ".";
   bool stats = false, filter = true, annotate = false, edit = false, maximum = false;
+  size_t gpus = 0;  // 0: $HUMID_GPUS, else 1
   vector<string> files;
 };
 
@@ -59,7 +62,10 @@ void usage(const char *prog) {
             << "  -q\t\twrite deduplicated FastQ files (default: on; the flag switches it off)\n"
             << "  -a\t\twrite annotated FastQ files\n"
             << "  -e\t\tuse edit distance\n"
-            << "  -x\t\tuse maximum clustering method\n";
+            << "  -x\t\tuse maximum clustering method\n"
+            << "\nnot in the reference:\n"
+            << "  -g\t\tnumber of GPUs to share the word table over (default: $HUMID_GPUS, else 1);\n"
+            << "    \t\twords of more than 31 letters and edit distances above 1 run on one GPU\n";
 }
 
 bool parse(int argc, char **argv, Options &o) {
@@ -70,6 +76,7 @@ bool parse(int argc, char **argv, Options &o) {
     if (a == "-h" || a == "--help") return false;
     else if (a == "-n") { value(v); o.word_length = std::strtoull(v.c_str(), nullptr, 10); }
     else if (a == "-m") { value(v); o.distance = std::strtoull(v.c_str(), nullptr, 10); }
+    else if (a == "-g") { value(v); o.gpus = std::strtoull(v.c_str(), nullptr, 10); }
     else if (a == "-l") value(o.log_name);
     else if (a == "-d") value(o.dir_name);
     else if (a == "-s") o.stats = !o.stats;
@@ -270,11 +277,52 @@ int main(int argc, char **argv) {
   cfg.expected_tuples = estimate_tuples(opt.files.front());
   // Bringing the device up (CUDA context, first allocations) takes about a second: it runs beside the readers,
   // which fill ordinary page-aligned buffers meanwhile; the buffers are page-locked once the handle exists.
-  humid_gpu *gpu = nullptr;
+  // Several GPUs (not in the reference: `-g N` / $HUMID_GPUS; $HUMID_GPU_DEVICES = "0,1,..." picks the ordinals, the same
+  // one may be named twice): one handle per GPU, joined into a group of the library (include/humid_gpu_shard.h).  Batches
+  // go to the handles in turn under their position in the job; the word table is range-partitioned over the GPUs by
+  // humid_gpu_finalize, and the per-read results of the whole job come back through the first handle.
+  size_t n_gpus = opt.gpus ? opt.gpus : (std::getenv("HUMID_GPUS") ? std::strtoull(std::getenv("HUMID_GPUS"), nullptr, 10) : 1);
+  if (n_gpus < 1) n_gpus = 1;
+  if (n_gpus > HUMID_MAX_PARTS) error_exit("at most " + std::to_string(HUMID_MAX_PARTS) + " GPUs");
+  if (n_gpus > 1 && (opt.word_length > HUMID_MAX_NARROW_WORD_LENGTH || (opt.edit && opt.distance >= 2))) n_gpus = 1;
+  vector<int> devices;
+  if (const char *list = std::getenv("HUMID_GPU_DEVICES")) {
+    for (const char *p = list; *p;) {
+      devices.push_back((int)std::strtol(p, const_cast<char **>(&p), 10));
+      while (*p == ',' || *p == ' ') p++;
+    }
+  }
+  vector<humid_gpu *> gpus(n_gpus, nullptr);
+  humid_gpu *&gpu = gpus[0];  // counts, histograms and (in a group) every per-read result
+  humid_gpu_group *group = n_gpus > 1 ? humid_gpu_group_create((uint32_t)n_gpus) : nullptr;
+  if (n_gpus > 1 && !group) error_exit("humid_gpu_group_create failed");
   int create_rc = HUMID_GPU_OK;
+  string create_msg;
+  std::mutex create_mu;
+  // run `body(rank)` on one thread per GPU (the group's calls are collective) and wait for all of them
+  auto on_every_gpu = [&](const std::function<void(size_t)> &body) {
+    if (n_gpus == 1) { body(0); return; }
+    vector<std::thread> th;
+    for (size_t r = 0; r < n_gpus; r++) th.emplace_back(body, r);
+    for (std::thread &t : th) t.join();
+  };
   std::thread creator([&] {
     const auto c0 = std::chrono::steady_clock::now();
-    create_rc = humid_gpu_create(&cfg, &gpu);
+    on_every_gpu([&](size_t r) {
+      humid_gpu_config c = cfg;
+      if (n_gpus > 1) {
+        c.device = !devices.empty() ? devices[r % devices.size()] : (int)r;
+        c.expected_tuples = 0;  // words are counted by the owners of their key range
+      }
+      int rc = humid_gpu_create(&c, &gpus[r]);
+      if (rc == HUMID_GPU_OK && group)
+        rc = humid_gpu_group_join(gpus[r], group, nullptr, (uint32_t)r, (uint32_t)n_gpus, HUMID_GROUP_BATCHES);
+      if (rc != HUMID_GPU_OK) {
+        std::lock_guard<std::mutex> lk(create_mu);
+        create_rc = rc;
+        create_msg = humid_gpu_last_error(gpus[r]);
+      }
+    });
     if (std::getenv("HUMID_TIMING"))
       std::cerr << "humid_gpu_create (CUDA context, beside the readers): "
                 << std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - c0).count() << " ms\n";
@@ -312,7 +360,7 @@ int main(int argc, char **argv) {
       }
       if (creator.joinable()) {  // first batch: the device must be there now
         creator.join();
-        check(nullptr, create_rc, "humid_gpu_create");
+        if (create_rc != HUMID_GPU_OK) error_exit("humid_gpu_create: " + create_msg);
         bool locked = true;  // page-locking is an optimisation: without it the uploads are staged by the driver
         for (int j = 0; j < N_SLOTS; j++) {
           locked &= humid_gpu_host_register(gpu, g.slots[j].chars, BATCH * g.n) == HUMID_GPU_OK;
@@ -322,7 +370,8 @@ int main(int argc, char **argv) {
       }
       size_t m = BATCH;
       for (size_t r : s.rows) m = r < m ? r : m;
-      if (m) check(gpu, humid_gpu_add_batch(gpu, s.chars, s.seg_len, total, m), "humid_gpu_add_batch");
+      humid_gpu *dst = gpus[k % n_gpus];  // in a group `total` is the batch's position in the job
+      if (m) check(dst, humid_gpu_add_batch(dst, s.chars, s.seg_len, total, m), "humid_gpu_add_batch");
       total += m;
       std::lock_guard<std::mutex> lk(g.mu);
       if (m < BATCH) g.stop = true;  // some file has ended: so has the tuple stream
@@ -346,7 +395,7 @@ int main(int argc, char **argv) {
   // The device computes both in one call; the two phase lines are kept for log compatibility.
   t0 = start_message(log, opt.edit ? "Calculating neighbours using Levenshtein distance"
                                    : "Calculating neighbours using Hamming distance");
-  check(gpu, humid_gpu_finalize(gpu), "humid_gpu_finalize");
+  on_every_gpu([&](size_t r) { check(gpus[r], humid_gpu_finalize(gpus[r]), "humid_gpu_finalize"); });
   end_message(log, t0);
   t0 = start_message(log, opt.maximum ? "Calculating maximum clusters" : "Calculating directional clusters");
   end_message(log, t0);
@@ -373,6 +422,8 @@ int main(int argc, char **argv) {
   if (opt.annotate) {
     t0 = start_message(log, "Writing annotated results");
     vector<uint32_t> ids(total + 1);
+    if (group)  // the owners of the words send every read's id to the first handle
+      on_every_gpu([&](size_t r) { check(gpus[r], humid_gpu_group_collect_ids(gpus[r]), "humid_gpu_group_collect_ids"); });
     for (uint64_t lo = 0; lo < total; lo += 16 * BATCH) {
       uint64_t m = std::min<uint64_t>(16 * BATCH, total - lo);
       check(gpu, humid_gpu_cluster_ids(gpu, lo, m, ids.data() + lo), "humid_gpu_cluster_ids");
@@ -413,7 +464,8 @@ int main(int argc, char **argv) {
 
   log.close();
   phase_start = std::chrono::steady_clock::now();
-  humid_gpu_destroy(gpu);
+  for (humid_gpu *g : gpus) humid_gpu_destroy(g);
+  if (group) humid_gpu_group_destroy(group);
   if (std::getenv("HUMID_TIMING"))
     std::cerr << "humid_gpu_destroy: "
               << std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - phase_start).count() << " ms\n";

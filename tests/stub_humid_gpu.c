@@ -111,3 +111,13 @@ int humid_gpu_cluster_ids(humid_gpu *h, uint64_t first, uint64_t n, uint32_t *id
   memcpy(ids, oracle_cid(h->o) + first, n * sizeof(uint32_t));
   return HUMID_GPU_OK;
 }
+
+/* Groups (include/humid_gpu_shard.h) need real GPUs: the stand-in refuses them, so `humid -g 2` fails loudly here. */
+struct humid_gpu_group;
+struct humid_gpu_group *humid_gpu_group_create(uint32_t world) { (void)world; return NULL; }
+void humid_gpu_group_destroy(struct humid_gpu_group *g) { (void)g; }
+int humid_gpu_group_join(humid_gpu *h, struct humid_gpu_group *g, const char *shm, uint32_t rank, uint32_t world, int numbering) {
+  (void)h; (void)g; (void)shm; (void)rank; (void)world; (void)numbering;
+  return HUMID_GPU_ERR_UNSUPPORTED;
+}
+int humid_gpu_group_collect_ids(humid_gpu *h) { (void)h; return HUMID_GPU_ERR_UNSUPPORTED; }

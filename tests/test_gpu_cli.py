@@ -60,8 +60,14 @@ def test_cli_matches_reference_binary(tmp_path, humid_bin, name, ci, R, kw, flag
 
     if oracle.have_ref():
         ref = str(tmp_path / "ref")
-        oracle.run_ref_humid(files, ref, cfg.cli_flags() + [f for f in flags if f != "-a"], stats=True,
-                             annotate="-a" in flags)
+        ref_flags, skip = [], False
+        for f in flags:  # `-g N` is not an option of the reference
+            if skip or f == "-g":
+                skip = f == "-g"
+                continue
+            if f != "-a":
+                ref_flags.append(f)
+        oracle.run_ref_humid(files, ref, cfg.cli_flags() + ref_flags, stats=True, annotate="-a" in flags)
         names = sorted(os.listdir(ref))
         names.remove("humid.log")
         assert sorted(os.listdir(ours)) == names
@@ -86,3 +92,43 @@ def test_cli_help_and_errors(humid_bin, tmp_path):
     assert p.returncode == 0 and "-x" in p.stdout and "word length" in p.stdout
     p = subprocess.run([humid_bin, str(tmp_path / "missing.fastq")], capture_output=True, text=True)
     assert p.returncode != 0 and "ERROR" in p.stderr
+
+
+# ---- several GPUs behind the same executable (`-g N` / $HUMID_GPUS; not in the reference) --------------------------
+@pytest.fixture(scope="module")
+def humid_small_batches(tmp_path_factory):
+    """The executable built with batches of 2048 tuples (and output chunks of 512 records), so that a job of a few
+    thousand tuples is dealt out over all the GPUs of a group."""
+    build.build_host()
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib_dir = os.path.join(root, "humid_b200")
+    exe = os.path.join(str(tmp_path_factory.mktemp("cli_small")), "humid_small")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-pthread", "-DHUMID_BATCH=2048", "-DHUMID_REWRITE_CHUNK=512", "-o", exe,
+                    os.path.join(root, "host", "humid_main.cc"), "-L" + lib_dir, "-lhumid_gpu", "-lz",
+                    "-Wl,-rpath," + lib_dir], check=True)
+    return exe
+
+
+MULTI_CASES = [c for c in CASES if c[0] in ("c1_max", "c2_umifile", "c3_ham2", "c5_umi10", "c1_dir_gz", "n36_umifile", "c4_edit2")]
+
+
+@pytest.mark.parametrize("n_gpus", [2, 3])
+@pytest.mark.parametrize("name,ci,R,kw,flags,gz", MULTI_CASES, ids=[c[0] for c in MULTI_CASES])
+def test_cli_on_several_gpus_matches_reference_binary(tmp_path, humid_small_batches, monkeypatch, name, ci, R, kw, flags, gz,
+                                                      n_gpus):
+    """Same files, same outputs, with the word table shared over `n_gpus` handles: distinct GPUs when the box has them,
+    else all on device 0 (the group's exchanges work through one device's memory just the same).  Words of more than 31
+    letters and edit distance 2 fall back to one GPU inside the executable."""
+    import torch
+
+    have = torch.cuda.device_count()
+    monkeypatch.setenv("HUMID_GPUS", str(n_gpus))
+    monkeypatch.setenv("HUMID_GPU_DEVICES", ",".join(str(i % max(have, 1)) for i in range(n_gpus)))
+    test_cli_matches_reference_binary(tmp_path, humid_small_batches, name, ci, R, kw, flags, gz)
+
+
+def test_cli_gpu_option(tmp_path, humid_small_batches, monkeypatch):
+    """`-g 2` on the command line does what $HUMID_GPUS does."""
+    monkeypatch.setenv("HUMID_GPU_DEVICES", "0,0")
+    name, ci, R, kw, flags, gz = CASES[2]
+    test_cli_matches_reference_binary(tmp_path, humid_small_batches, name, ci, R, kw, ["-g", "2"] + flags, gz)

@@ -31,7 +31,7 @@ seg_take = ([hdr] if hdr else []) + take
 lo, hi = args.tuples * rank // world, args.tuples * (rank + 1) // world
 kw = dict(word_length=cfg.word_length, distance=cfg.distance, seg_take=seg_take, edit=cfg.edit, maximum=cfg.maximum,
           device=local, expected_tuples=hi - lo)
-dd = sharded.ShardedDedup(**kw) if world > 1 else api.Dedup(**kw)
+dd = sharded.make_sharded(**kw) if world > 1 else api.Dedup(**kw)  # peer-memory group (HUMID_SHARD_TRANSPORT=nccl: the NCCL path)
 CH = 50_000_000
 t_gen = 0.0
 torch.cuda.synchronize()
