@@ -4,6 +4,7 @@
 // Trie::add (lib/trie/src/trieFunctions.tcc:45-59) and Trie::walk order (:129-143).
 #include <cstdlib>
 #include <algorithm>
+#include <string>
 
 #include "state.cuh"
 
@@ -23,6 +24,9 @@ constexpr int PACK_ROWS = HUMID_PACK_ROWS;
 #define HUMID_PACK_LOADS 6
 #endif
 constexpr int PACK_LOADS = HUMID_PACK_LOADS;  // tuples per CTA: 4 x 16-byte loads in flight per thread while staging
+#ifndef HUMID_PACK_DEFAULT_BULK
+#define HUMID_PACK_DEFAULT_BULK 0
+#endif
 constexpr int PACK_ROWS_WIDE = 512;  // words of 32..63 letters: the tile still fits 48 KB of shared memory
 
 // Four characters at a time (SIMD inside a 32-bit register).  A=0 C=1 G=2 T=3
@@ -40,6 +44,41 @@ __device__ __forceinline__ uint32_t pack4(uint32_t x, bool &bad) {
 #endif
   bad |= __byte_perm(0x54474341u /* "ACGT" */, 0u, sel) != x;
   return (c * 0x40100401u) >> 24;  // b0<<6 | b1<<4 | b2<<2 | b3
+}
+
+// makeWord for one tuple whose n characters lie at `row` in shared memory; returns 1 when the tuple is usable.
+template <bool WIDE>
+__device__ __forceinline__ uint32_t pack_row(const uint8_t *row, const uint16_t *__restrict__ seg_len, uint64_t t,
+                                             const PackParams &pp, uint64_t *__restrict__ keys_out,
+                                             uint64_t *__restrict__ keys_hi_out) {
+  uint64_t key = 0, key_hi = 0;
+  bool bad = false;
+  if (seg_len) {
+    const uint16_t *sl = seg_len + t * pp.n_segs;
+    for (uint32_t s = 0; s < pp.n_segs; s++) bad |= sl[s] < pp.take[s];
+  }
+  const uint32_t full = pp.n & ~3u;
+  if ((pp.n & 3u) == 0) {  // rows are 4-byte aligned in shared memory
+    const uint32_t *row4 = reinterpret_cast<const uint32_t *>(row);
+    for (uint32_t q = 0; q < full; q += 4) {
+      if (WIDE) key_hi = (key_hi << 8) | (key >> 56);
+      key = (key << 8) | pack4(row4[q >> 2], bad);
+    }
+  } else {
+    for (uint32_t q = 0; q < full; q += 4) {
+      uint32_t x = row[q] | (row[q + 1] << 8) | (row[q + 2] << 16) | ((uint32_t)row[q + 3] << 24);
+      if (WIDE) key_hi = (key_hi << 8) | (key >> 56);
+      key = (key << 8) | pack4(x, bad);
+    }
+  }
+  for (uint32_t q = full; q < pp.n; q++) {
+    uint32_t one = pack4(row[q] | 0x41414100u, bad);  // pad with 'A' (code 0, valid)
+    if (WIDE) key_hi = (key_hi << 2) | (key >> 62);
+    key = (key << 2) | ((one >> 6) & 3u);
+  }
+  keys_out[t] = bad ? KEY_INVALID : key;
+  if (WIDE) keys_hi_out[t] = bad ? KEY_INVALID : key_hi;
+  return bad ? 0u : 1u;
 }
 
 // One CTA packs PACK_ROWS consecutive tuples: their n*PACK_ROWS characters are staged into
@@ -82,40 +121,116 @@ __global__ void __launch_bounds__(PACK_THREADS)
   __syncthreads();
 
   uint32_t n_good = 0;
-  for (uint32_t rr = threadIdx.x; rr < rows; rr += PACK_THREADS) {
-    uint64_t key = 0, key_hi = 0;
-    bool bad = false;
-    const uint8_t *row = tile + rr * pp.n;
-    if (seg_len) {
-      const uint16_t *sl = seg_len + (t0 + rr) * pp.n_segs;
-      for (uint32_t s = 0; s < pp.n_segs; s++) bad |= sl[s] < pp.take[s];
-    }
-    const uint32_t full = pp.n & ~3u;
-    if ((pp.n & 3u) == 0) {  // rows are 4-byte aligned in shared memory
-      const uint32_t *row4 = reinterpret_cast<const uint32_t *>(row);
-      for (uint32_t q = 0; q < full; q += 4) {
-        if (WIDE) key_hi = (key_hi << 8) | (key >> 56);
-        key = (key << 8) | pack4(row4[q >> 2], bad);
-      }
+  for (uint32_t rr = threadIdx.x; rr < rows; rr += PACK_THREADS)
+    n_good += pack_row<WIDE>(tile + rr * pp.n, seg_len, t0 + rr, pp, keys_out, keys_hi_out);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) n_good += __shfl_xor_sync(0xffffffffu, n_good, o);
+  if (lane_id() == 0 && n_good) atomicAdd(usable, (unsigned long long)n_good);
+}
+
+// ---- the same with the tile brought in by the bulk-copy engine (sm_90+: cp.async.bulk, UBLKCP in SASS) -----------
+// One elected thread asks for a whole tile (ROWS x n bytes, one contiguous piece of the input) with ONE instruction;
+// the bytes land in shared memory without passing through registers and complete an mbarrier's transaction count.
+// Persistent CTAs, two stages: the next tile of a CTA is in flight while the current one is encoded.
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(done)
+        : "r"(smem_addr(bar)), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+// bytes: a multiple of 16; both addresses 16-byte aligned
+__device__ __forceinline__ void bulk_load(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_addr(bar))
+               : "memory");
+}
+
+template <bool WIDE, int ROWS>
+__global__ void __launch_bounds__(PACK_THREADS)
+    pack_words_bulk_kernel(const uint8_t *__restrict__ chars, const uint16_t *__restrict__ seg_len, uint64_t n_tuples,
+                           uint32_t n_tiles, uint32_t stage_bytes, PackParams pp, uint64_t *__restrict__ keys_out,
+                           uint64_t *__restrict__ keys_hi_out, unsigned long long *__restrict__ usable) {
+  extern __shared__ __align__(128) uint8_t stages[];  // 2 x stage_bytes
+  __shared__ __align__(8) uint64_t full[2];
+  if (threadIdx.x == 0) {
+    mbar_init(&full[0], 1);
+    mbar_init(&full[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  // tile `tl` -> stage `st`: the part that is a multiple of 16 bytes by the copy engine, a last tile's odd tail by hand
+  auto issue = [&](uint32_t tl, uint32_t st) {
+    const uint64_t t0 = (uint64_t)tl * ROWS;
+    const uint32_t bytes = (uint32_t)min((uint64_t)ROWS, n_tuples - t0) * pp.n;
+    const uint32_t bulk = bytes & ~15u;
+    uint8_t *dst = stages + (size_t)st * stage_bytes;
+    const uint8_t *src = chars + t0 * pp.n;
+    if (bulk) {
+      mbar_expect_tx(&full[st], bulk);
+      bulk_load(dst, src, bulk, &full[st]);
     } else {
-      for (uint32_t q = 0; q < full; q += 4) {
-        uint32_t x = row[q] | (row[q + 1] << 8) | (row[q + 2] << 16) | ((uint32_t)row[q + 3] << 24);
-        if (WIDE) key_hi = (key_hi << 8) | (key >> 56);
-        key = (key << 8) | pack4(x, bad);
-      }
+      asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_addr(&full[st])) : "memory");
     }
-    for (uint32_t q = full; q < pp.n; q++) {
-      uint32_t one = pack4(row[q] | 0x41414100u, bad);  // pad with 'A' (code 0, valid)
-      if (WIDE) key_hi = (key_hi << 2) | (key >> 62);
-      key = (key << 2) | ((one >> 6) & 3u);
-    }
-    keys_out[t0 + rr] = bad ? KEY_INVALID : key;
-    if (WIDE) keys_hi_out[t0 + rr] = bad ? KEY_INVALID : key_hi;
-    n_good += bad ? 0u : 1u;
+    for (uint32_t i = bulk; i < bytes; i++) dst[i] = src[i];
+  };
+  uint32_t tile = blockIdx.x, it = 0, n_good = 0;
+  if (threadIdx.x == 0 && tile < n_tiles) issue(tile, 0);
+  for (; tile < n_tiles; tile += gridDim.x, it++) {
+    const uint32_t st = it & 1u, next = tile + gridDim.x;
+    // stage st ^ 1 was read in the previous iteration, which ended with a __syncthreads
+    if (threadIdx.x == 0 && next < n_tiles) issue(next, st ^ 1u);
+    mbar_wait(&full[st], (it >> 1) & 1u);
+    __syncthreads();  // the hand-copied tail of a last tile (written by thread 0) is visible to all
+    const uint64_t t0 = (uint64_t)tile * ROWS;
+    const uint32_t rows = (uint32_t)min((uint64_t)ROWS, n_tuples - t0);
+    const uint8_t *src = stages + (size_t)st * stage_bytes;
+    for (uint32_t rr = threadIdx.x; rr < rows; rr += PACK_THREADS)
+      n_good += pack_row<WIDE>(src + rr * pp.n, seg_len, t0 + rr, pp, keys_out, keys_hi_out);
+    __syncthreads();
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) n_good += __shfl_xor_sync(0xffffffffu, n_good, o);
   if (lane_id() == 0 && n_good) atomicAdd(usable, (unsigned long long)n_good);
+}
+
+template <bool WIDE, int ROWS>
+static void launch_pack_bulk(State &s, const uint8_t *d_chars, const uint16_t *d_seg_len, uint64_t first, uint64_t n,
+                             const PackParams &pp) {
+  const uint32_t stage_bytes = ((uint32_t)ROWS * pp.n + 127u) & ~127u;
+  const size_t smem = 2 * (size_t)stage_bytes;
+  static int per_sm = 0;
+  auto *fn = pack_words_bulk_kernel<WIDE, ROWS>;
+  if (!per_sm) {
+    HUMID_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * (((int)ROWS * 64 + 127) & ~127)));
+    per_sm = 3;
+  }
+  const uint32_t n_tiles = (uint32_t)((n + ROWS - 1) / ROWS);
+  const unsigned grid = std::min<unsigned>(n_tiles, SM_COUNT_B200 * per_sm);
+  fn<<<grid, PACK_THREADS, smem, s.stream>>>(d_chars, d_seg_len, n, n_tiles, stage_bytes, pp, s.tuple_key.p + first,
+                                             WIDE ? s.tuple_hi.p + first : nullptr, s.counters.p + 0);
+}
+
+// HUMID_GPU_PACK=bulk|plain picks the tile movement of the pack kernel.  Measured on B200, 50 M tuples of 24 letters
+// (profiles/r02_sass_grep.md): register-staged 16-byte loads 0.395 ms, bulk copy + mbarrier, two stages, 3 persistent
+// CTAs per SM 0.422 ms — the plain loads stay the default, the bulk path stays tested.
+static bool pack_by_bulk_copy() {
+  const char *e = std::getenv("HUMID_GPU_PACK");  // read per batch: the tests switch it inside one process
+  return e ? std::string(e) == "bulk" : HUMID_PACK_DEFAULT_BULK != 0;
 }
 
 int stage_pack(State &s, const uint8_t *d_chars, const uint16_t *d_seg_len, uint64_t first, uint64_t n) {
@@ -126,6 +241,14 @@ int stage_pack(State &s, const uint8_t *d_chars, const uint16_t *d_seg_len, uint
   for (uint32_t i = 0; i < pp.n_segs; i++) pp.take[i] = s.cfg.seg_take[i];
   // makeWord: n ASCII bytes in, one 8-byte key (two for a word of more than 31 letters) out
   Timed t(s, "pack", n, n * (pp.n + (s.wide() ? 16 : 8)));
+  // the copy engine wants 16-byte aligned tiles: true for every tile when the input is and a tile's size is a multiple
+  if (pack_by_bulk_copy() && (((uintptr_t)d_chars) & 15u) == 0 &&
+      (((uint64_t)(s.wide() ? PACK_ROWS_WIDE : PACK_ROWS) * pp.n) & 15u) == 0) {
+    if (s.wide()) launch_pack_bulk<true, PACK_ROWS_WIDE>(s, d_chars, d_seg_len, first, n, pp);
+    else launch_pack_bulk<false, PACK_ROWS>(s, d_chars, d_seg_len, first, n, pp);
+    HUMID_CUDA(cudaGetLastError());
+    return 1;
+  }
   if (s.wide())
     pack_words_kernel<true, PACK_ROWS_WIDE><<<grid_for(n, PACK_ROWS_WIDE), PACK_THREADS, (size_t)PACK_ROWS_WIDE * pp.n,
                                               s.stream>>>(d_chars, d_seg_len, n, pp, s.tuple_key.p + first,

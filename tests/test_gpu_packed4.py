@@ -74,3 +74,19 @@ def test_packed4_short_segments_filter():
 def test_pack_nibbles_layout():
     x = np.frombuffer(b"ACGTNacgt", dtype=np.uint8).reshape(1, 9)
     assert api.pack_nibbles(x).tolist() == [[0x01, 0x23, 0x44, 0x44, 0x40]]
+
+
+@pytest.mark.parametrize("ci,R,kw", [(1, 30000, {}), (0, 20000, dict(word_length=9, genome_len=2000)), (1, 20000, dict(word_length=36)),
+                                     (4, 5000, {}), (1, 1025, {}), (1, 1, {})])
+def test_pack_tiles_by_bulk_copy(monkeypatch, ci, R, kw):
+    """pack_words_bulk_kernel (cp.async.bulk + mbarrier tile loads, HUMID_GPU_PACK=bulk) against the oracle: whole
+    tiles, a last partial tile, sizes that are not a multiple of 16 bytes, words of 36 letters."""
+    monkeypatch.setenv("HUMID_GPU_PACK", "bulk")
+    cfg = baseline_config(ci, R, **kw)
+    s = Synth(cfg)
+    chars = s.word_chars()
+    hdr, take = s.layout()
+    seg_take = ([hdr] if hdr else []) + take
+    r = oracle.Result(oracle.pack_words(chars, seg_take), cfg.word_length, cfg.distance, cfg.edit, cfg.maximum)
+    with run(chars, seg_take, cfg, False, batches=2) as dd:
+        assert_same_as_oracle(dd, r, R)
