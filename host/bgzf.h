@@ -25,22 +25,37 @@
 
 namespace humid_host {
 
-// First member of the file: gzip magic, deflate, FEXTRA set, and a 'B','C' subfield of length 2.
+// EVERY member of the file: gzip magic, deflate, FEXTRA set, a 'B','C' subfield of length 2 giving the member's size,
+// and at most 64 KiB of data (the BGZF bound; a trailer claiming more is a corrupt or foreign member).  A file that
+// starts with BGZF members and goes on with ordinary gzip members (`cat a.bgz b.gz`) is valid gzip — the reference
+// reads it (lib/fastp/src/fastqreader.cpp:79-133) — but cannot be cut at member headers: it, like any file with a
+// member that fails the test, is left to the one-stream reader.  One small read + seek per member.
 inline bool is_bgzf(const std::string &path) {
   FILE *fp = std::fopen(path.c_str(), "rb");
   if (!fp) return false;
-  unsigned char h[12];
   bool yes = false;
-  if (std::fread(h, 1, 12, fp) == 12 && h[0] == 0x1f && h[1] == 0x8b && h[2] == 8 && (h[3] & 4)) {
+  std::vector<unsigned char> extra;
+  while (true) {
+    unsigned char h[12];
+    const size_t got = std::fread(h, 1, 12, fp);
+    if (got == 0) break;  // clean end of file after >= 1 member (or an empty file: yes stays false)
+    yes = false;
+    if (got != 12 || h[0] != 0x1f || h[1] != 0x8b || h[2] != 8 || !(h[3] & 4)) break;
     const unsigned xlen = h[10] | (h[11] << 8);
-    std::vector<unsigned char> extra(xlen);
-    if (xlen >= 6 && std::fread(extra.data(), 1, xlen, fp) == xlen) {
-      for (unsigned i = 0; i + 4 <= xlen;) {
-        const unsigned slen = extra[i + 2] | (extra[i + 3] << 8);
-        if (extra[i] == 'B' && extra[i + 1] == 'C' && slen == 2) yes = true;
-        i += 4 + slen;
-      }
+    extra.resize(xlen);
+    if (xlen < 6 || std::fread(extra.data(), 1, xlen, fp) != xlen) break;
+    long bsize = -1;
+    for (unsigned i = 0; i + 4 <= xlen;) {
+      const unsigned slen = extra[i + 2] | (extra[i + 3] << 8);
+      if (extra[i] == 'B' && extra[i + 1] == 'C' && slen == 2 && i + 6 <= xlen) bsize = extra[i + 4] | (extra[i + 5] << 8);
+      i += 4 + slen;
     }
+    const long rest = bsize + 1 - 12 - (long)xlen;  // deflate data + CRC-32 + ISIZE
+    unsigned char t[4];
+    if (bsize < 0 || rest < 8 || std::fseek(fp, rest - 4, SEEK_CUR) != 0 || std::fread(t, 1, 4, fp) != 4) break;
+    const uint32_t isize = t[0] | (t[1] << 8) | (t[2] << 16) | ((uint32_t)t[3] << 24);
+    if (isize > 65536u) break;
+    yes = true;
   }
   std::fclose(fp);
   return yes;
@@ -158,6 +173,10 @@ class BgzfInflater {
     m.raw_len = (size_t)rest - 8;
     m.crc = t[0] | (t[1] << 8) | (t[2] << 16) | ((uint32_t)t[3] << 24);
     m.isize = t[4] | (t[5] << 8) | (t[6] << 16) | ((uint32_t)t[7] << 24);
+    if (m.isize > 65536u) {
+      fail("igzip: encountered while decompressing file: " + path_ + " (BGZF member larger than 64 KiB)");
+      return false;
+    }
     m.out_at = out_bytes;
     out_bytes += m.isize;
     if (m.isize) job.members.push_back(m);  // (the end-of-file marker is an empty member)

@@ -63,6 +63,9 @@ void usage(const char *prog) {
             << "  -a\t\twrite annotated FastQ files\n"
             << "  -e\t\tuse edit distance\n"
             << "  -x\t\tuse maximum clustering method\n"
+            << "\nlimits of this implementation (the reference has none): word length 1.." << HUMID_MAX_WORD_LENGTH
+            << "; Hamming distance <= 8;\n  edit distance <= 3, and <= 1 for words of more than " << HUMID_MAX_NARROW_WORD_LENGTH
+            << " letters; fewer than 2^32 - 1 read tuples; at most " << HUMID_MAX_SEGMENTS - 1 << " files\n"
             << "\nnot in the reference:\n"
             << "  -g\t\tnumber of GPUs to share the word table over (default: $HUMID_GPUS, else 1);\n"
             << "    \t\twords of more than 31 letters and edit distances above 1 run on one GPU\n";
@@ -251,6 +254,15 @@ int main(int argc, char **argv) {
     usage(argv[0]);
     return argc > 1 && (string(argv[1]) == "-h" || string(argv[1]) == "--help") ? 0 : 1;
   }
+  // what the device path does not cover is refused here, before any file is read (the reference takes any -n / -m)
+  if (opt.word_length == 0 || opt.word_length > HUMID_MAX_WORD_LENGTH)
+    error_exit("word length (-n) must be 1.." + std::to_string(HUMID_MAX_WORD_LENGTH) + " in this implementation");
+  if (!opt.edit && opt.distance > 8) error_exit("Hamming distance (-m) above 8 is not supported by this implementation");
+  if (opt.edit && opt.distance > 3) error_exit("edit distance (-e -m) above 3 is not supported by this implementation");
+  if (opt.edit && opt.distance >= 2 && opt.word_length > HUMID_MAX_NARROW_WORD_LENGTH)
+    error_exit("edit distance above 1 needs a word length (-n) of at most " + std::to_string(HUMID_MAX_NARROW_WORD_LENGTH) +
+               " in this implementation");
+  if (opt.files.size() > HUMID_MAX_SEGMENTS - 1) error_exit("too many input files");
   std::ofstream log(opt.log_name.c_str(), std::ios::out | std::ios::binary);
   const size_t F = opt.files.size();
 

@@ -171,3 +171,17 @@ def test_output_file_names_like_the_reference_binary(tmp_path, humid_cpu, fname,
     for rel in listing["ref"]:
         if not rel.endswith("run.log"):
             assert open(tmp_path / "ours" / rel, "rb").read() == open(tmp_path / "ref" / rel, "rb").read(), rel
+
+
+@pytest.mark.parametrize("flags,what", [(["-n", "64"], "word length"), (["-m", "9"], "Hamming distance"),
+                                        (["-e", "-m", "4"], "edit distance"), (["-e", "-m", "2", "-n", "40"], "edit distance"),
+                                        (["-n", "0"], "word length")])
+def test_limits_are_refused_before_any_file_is_read(humid_cpu, tmp_path, flags, what):
+    """What the device path does not cover (the reference takes any -n / -m) fails at once with a message that names the
+    option — not after the first pass over the inputs, and not with an error about the (missing) file."""
+    p = subprocess.run([humid_cpu, *flags, "-d", str(tmp_path / "out"), "-l", str(tmp_path / "log"), str(tmp_path / "missing.fastq")],
+                       capture_output=True, text=True)
+    assert p.returncode != 0 and "ERROR" in p.stderr and what in p.stderr and "missing.fastq" not in p.stderr
+    assert not os.path.exists(tmp_path / "out")
+    q = subprocess.run([humid_cpu, "-h"], capture_output=True, text=True)
+    assert "limits of this implementation" in q.stdout

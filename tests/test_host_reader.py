@@ -148,3 +148,37 @@ def test_bgzf_damage_is_an_error(checker, tmp_path):
     env = dict(os.environ, HUMID_INFLATE_THREADS="3")
     got = subprocess.run([checker, "block", path, "4096"], capture_output=True, env=env)
     assert got.returncode != 0 and b"decompressing" in got.stderr
+
+
+def test_bgzf_followed_by_plain_gzip_members(checker, tmp_path):
+    """`cat a.bgz b.gz`: valid gzip that starts like BGZF.  It cannot be cut at member headers, so it takes the one-stream
+    path whatever the number of inflate threads (the reference reads such files, lib/fastp/src/fastqreader.cpp:79-133)."""
+    rng = np.random.default_rng(17)
+    a, b = b"".join(records(200, rng)), b"".join(records(150, rng))
+    raw = bgzf_bytes(a, 700)
+    raw = raw[:-28] + gzip.compress(b)  # without the empty end-of-file member, then an ordinary member
+    path = str(tmp_path / "in.fastq.gz")
+    with open(path, "wb") as f:
+        f.write(raw)
+    assert gzip.open(path, "rb").read() == a + b
+    outs = []
+    for threads in (1, 4):
+        env = dict(os.environ, HUMID_INFLATE_THREADS=str(threads))
+        got = subprocess.run([checker, "block", path, "4096"], capture_output=True, check=True, env=env)
+        outs.append(got.stdout)
+    assert outs[0] == outs[1] and outs[0].endswith(b"records 350\n")
+
+
+def test_bgzf_member_claiming_more_than_64k_is_not_bgzf(checker, tmp_path):
+    """A trailer with ISIZE above the BGZF bound: the file is not treated as BGZF (no 4 GiB buffer is sized from it); the
+    one-stream reader then reports the damage like any other."""
+    data = CASES["plain"](np.random.default_rng(5))
+    raw = bytearray(bgzf_bytes(data, 700))
+    first = 12 + 6 + struct.unpack("<H", raw[16:18])[0] + 1 - 18  # end of the first member
+    raw[first - 4:first] = struct.pack("<I", 0xFFFFFFF0)
+    path = str(tmp_path / "in.fastq.gz")
+    with open(path, "wb") as f:
+        f.write(bytes(raw))
+    env = dict(os.environ, HUMID_INFLATE_THREADS="3")
+    got = subprocess.run([checker, "block", path, "4096"], capture_output=True, env=env)
+    assert got.returncode != 0 and b"decompressing" in got.stderr
