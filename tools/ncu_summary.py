@@ -13,6 +13,8 @@ def launches(path):
         if row.get("Metric Name") != "gpu__time_duration.sum":
             continue
         k = re.sub(r"\(.*", "", row["Kernel Name"]).replace("void ", "").replace("humid::", "")
+        if k.startswith(("at::", "<unnamed>::", "at_cuda", "cub::")):  # torch kernels of the synthetic-data generator
+            continue
         v = float(row["Metric Value"].replace(",", ""))
         v *= {"ns": 1e-3, "us": 1.0, "ms": 1e3}.get(row["Metric Unit"], 1.0)
         a = agg.setdefault(k, [0, 0.0])
