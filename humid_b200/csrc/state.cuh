@@ -172,6 +172,10 @@ struct State {
   // rank-ordered columns
   DevBuf<uint64_t> word_key, key_alt;
   DevBuf<uint32_t> word_slot, slot_alt;
+  DevBuf<uint64_t> compact_key;   // the table's words in compaction (slot) order: key ...
+  DevBuf<uint2> compact_cf;       // ... {Leaf::count, first tuple} ...
+  DevBuf<uint32_t> compact_slot;  // ... and slot number
+  bool word_slot_is_index = false;  // word_slot still holds compaction positions (translated on first look-up set-up)
   DevBuf<uint32_t> word_count, word_first;
 
   // neighbour lists

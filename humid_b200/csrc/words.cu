@@ -394,23 +394,27 @@ __global__ void __launch_bounds__(HUMID_INSERT_THREADS)
   if (ti < (uint32_t)(hi >> 32)) atomicMin(&slots[idx].first, ti);
 }
 
-// Occupied slots -> (key, slot) pairs, any order (they are sorted next).  One atomic per CTA:
+// Occupied slots -> dense columns in any order (they are sorted next): key, {count, first}, slot number.  The whole
+// 16-byte slot is read (the key alone pulls the same sectors in), so count and first come along for free and the
+// rank-ordered columns are later gathered from these dense arrays instead of from the table (which is 3-5x larger and
+// mostly empty: 2.6 GB of DRAM fills for 0.5 GB of useful bytes in round 1's gather).  One atomic per CTA:
 // warp ballots -> per-warp counts -> CTA prefix in shared memory.
 constexpr int COMPACT_ITEMS = 8;
 __global__ void __launch_bounds__(256)
     table_compact_kernel(const Slot *__restrict__ slots, uint64_t cap, uint64_t *__restrict__ keys_out,
-                         uint32_t *__restrict__ slot_out, unsigned long long *__restrict__ counter) {
+                         uint2 *__restrict__ cf_out, uint32_t *__restrict__ slot_out,
+                         unsigned long long *__restrict__ counter) {
   __shared__ uint32_t warp_cnt[COMPACT_ITEMS][8];
   __shared__ unsigned long long cta_base;
   const uint64_t base = (uint64_t)blockIdx.x * (256 * COMPACT_ITEMS);
   const uint32_t lane = lane_id(), w = threadIdx.x >> 5;
-  uint64_t key[COMPACT_ITEMS];
+  uint4 slot[COMPACT_ITEMS];
   unsigned bal[COMPACT_ITEMS];
 #pragma unroll
   for (int j = 0; j < COMPACT_ITEMS; j++) {
     uint64_t i = base + (uint64_t)j * 256 + threadIdx.x;
-    key[j] = i < cap ? ld_stream_u64(&slots[i].key) : KEY_INVALID;
-    bal[j] = __ballot_sync(0xffffffffu, key[j] != KEY_INVALID);
+    slot[j] = i < cap ? ld_stream_u128(slots + i) : make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u);
+    bal[j] = __ballot_sync(0xffffffffu, (slot[j].x & slot[j].y) != 0xFFFFFFFFu);
     if (lane == 0) warp_cnt[j][w] = __popc(bal[j]);
   }
   __syncthreads();
@@ -427,25 +431,33 @@ __global__ void __launch_bounds__(256)
   __syncthreads();
 #pragma unroll
   for (int j = 0; j < COMPACT_ITEMS; j++) {
-    if (key[j] != KEY_INVALID) {
+    if ((slot[j].x & slot[j].y) != 0xFFFFFFFFu) {  // a key never has bit 63 set, so only KEY_INVALID is all ones
       uint64_t pos = cta_base + warp_cnt[j][w] + __popc(bal[j] & ((1u << lane) - 1u));
-      keys_out[pos] = key[j];
+      keys_out[pos] = ((uint64_t)slot[j].y << 32) | slot[j].x;
+      cf_out[pos] = make_uint2(slot[j].z, slot[j].w);
       slot_out[pos] = (uint32_t)(base + (uint64_t)j * 256 + threadIdx.x);
     }
   }
 }
 
-// Rank-ordered columns; the slot's count field is overwritten with the rank so that one
-// probe of the table answers "which rank is this key" — written only when something will ask
-// (stage_ensure_lookup).
+// Rank-ordered columns from the compaction's dense ones: word_index[r] = position of rank r's word in compaction
+// order (the value the sort carried).  One random 8-byte read per word out of a dense array (two random reads — the
+// slot number as well — were slower than round 1's single 16-byte read out of the table: past L2 a random gather costs
+// per access, not per byte).  The slot numbers are only needed for key -> rank look-ups and translated on demand.
 __global__ void __launch_bounds__(256)
-    gather_columns_kernel(const Slot *__restrict__ slots, const uint32_t *__restrict__ word_slot, uint64_t U,
+    gather_columns_kernel(const uint2 *__restrict__ compact_cf, const uint32_t *__restrict__ word_index, uint64_t U,
                           uint32_t *__restrict__ word_count, uint32_t *__restrict__ word_first) {
   uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= U) return;
-  uint4 v = __ldg(reinterpret_cast<const uint4 *>(slots + word_slot[r]));
-  word_count[r] = v.z;
-  word_first[r] = v.w;
+  const uint2 cf = __ldg(compact_cf + word_index[r]);
+  word_count[r] = cf.x;
+  word_first[r] = cf.y;
+}
+
+__global__ void __launch_bounds__(256)
+    index_to_slot_kernel(const uint32_t *__restrict__ compact_slot, uint32_t *word_index_then_slot, uint64_t U) {
+  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < U) word_index_then_slot[r] = __ldg(compact_slot + word_index_then_slot[r]);
 }
 
 __global__ void __launch_bounds__(256)
@@ -577,40 +589,46 @@ int stage_build_table(State &s, bool with_lookup) {
   s.key_alt.ensure(s.usable + 1);
   s.word_slot.ensure(s.usable + 1);
   s.slot_alt.ensure(s.usable + 1);
+  s.compact_key.ensure(s.usable + 1);
+  s.compact_cf.ensure(s.usable + 1);
+  s.compact_slot.ensure(s.usable + 1);
   HUMID_CUDA(cudaMemsetAsync(s.counters.p + 1, 0, sizeof(unsigned long long), s.stream));
   {
-    Timed t(s, "table_compact", cap, cap * 8 + s.usable * 12);
-    table_compact_kernel<<<grid_for(cap, 256, COMPACT_ITEMS), 256, 0, s.stream>>>(s.slots.p, cap, s.word_key.p, s.word_slot.p,
-                                                                   s.counters.p + 1);
+    Timed t(s, "table_compact", cap, cap * 16 + s.usable * 20);
+    table_compact_kernel<<<grid_for(cap, 256, COMPACT_ITEMS), 256, 0, s.stream>>>(s.slots.p, cap, s.compact_key.p,
+                                                                                 s.compact_cf.p, s.compact_slot.p,
+                                                                                 s.counters.p + 1);
   }
   k++;
   HUMID_CUDA(cudaMemcpyAsync(&s.unique, s.counters.p + 1, sizeof(uint64_t), cudaMemcpyDeviceToHost, s.stream));
   HUMID_CUDA(cudaStreamSynchronize(s.stream));
   const uint64_t U = s.unique;
-  uint64_t *kb[2] = {s.word_key.p, s.key_alt.p};
-  uint32_t *vb[2] = {s.word_slot.p, s.slot_alt.p};
-  int launches = 0;
-  int cur;
-  {
-    // per 8-bit pass the (key, slot) pairs are read once and written once; one more read of the keys for the histograms
-    const uint64_t passes = (2 * (uint64_t)s.cfg.word_length + 7) / 8;
-    Timed t(s, "sort_words", U, U * (8 + passes * 2 * (8 + 4)));
-    cur = radix_sort_u64(kb, vb, U, 2 * (int)s.cfg.word_length, s.scratch, s.scan_scratch, s.stream, &launches);
-    t.launches = launches;
-  }
-  k += launches;
-  if (cur == 1) {
-    std::swap(s.word_key, s.key_alt);
-    std::swap(s.word_slot, s.slot_alt);
-  }
   s.word_count.ensure(U + 1);
   s.word_first.ensure(U + 1);
   if (U) {
-    Timed t(s, "rank_columns", U, U * (4 + 16 + 4 + 4));
-    gather_columns_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.slots.p, s.word_slot.p, U, s.word_count.p,
+    uint64_t *kb[2] = {s.word_key.p, s.key_alt.p};
+    uint32_t *vb[2] = {s.word_slot.p, s.slot_alt.p};
+    int launches = 0;
+    int cur;
+    {
+      // per 8-bit pass the (key, index) pairs are read once and written once (the first pass reads keys only: the index
+      // of an element is its position); one more read of the keys for the histograms
+      const uint64_t passes = (2 * (uint64_t)s.cfg.word_length + 7) / 8;
+      Timed t(s, "sort_words", U, U * (8 + passes * 2 * (8 + 4) - 4));
+      cur = radix_sort_bits_indexed(s.compact_key.p, kb, vb, U, 0, 2 * (int)s.cfg.word_length, s.scratch, s.stream, &launches);
+      t.launches = launches;
+    }
+    k += launches;
+    if (cur == 1) {
+      std::swap(s.word_key, s.key_alt);
+      std::swap(s.word_slot, s.slot_alt);
+    }
+    Timed t(s, "rank_columns", U, U * (4 + 8 + 4 + 4));
+    gather_columns_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.compact_cf.p, s.word_slot.p, U, s.word_count.p,
                                                                   s.word_first.p);
     k++;
   }
+  s.word_slot_is_index = true;  // translated to slot numbers when look-ups are set up (stage_ensure_lookup)
   s.ranks_in_table = false;
   s.filter_buckets = 0;
   if (with_lookup) k += stage_ensure_lookup(s);
@@ -624,8 +642,14 @@ int stage_ensure_lookup(State &s) {
   int k = 0;
   const uint64_t U = s.unique;
   if (!s.ranks_in_table && U) {
-    Timed t(s, "table_ranks", U, U * (4 + 4));
+    Timed t(s, "table_ranks", U, U * (4 + 4 + 4 + 4));
+    if (s.word_slot_is_index) {
+      index_to_slot_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.compact_slot.p, s.word_slot.p, U);
+      s.word_slot_is_index = false;
+      k++;
+    }
     scatter_ranks_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.slots.p, s.word_slot.p, U);
+    t.launches = 2;
     k++;
   }
   s.ranks_in_table = true;
