@@ -246,10 +246,13 @@ __global__ void __launch_bounds__(PUSH_THREADS)
   }
 }
 
-// Several device-to-device copies (to other ranks' buffers as well as local) as ONE kernel: blockIdx.y picks the
-// segment.  A dozen small cudaMemcpyAsync peer copies cost their launch + copy-engine latency each (35 of them made the
-// gathering of the open components 1.2 ms long on 8 GPUs); stores from the SMs go over NVLink at full width when
-// consecutive threads write consecutive 16-byte units.  Sizes and addresses are multiples of 4 bytes.
+// Several device-to-device copies (to other ranks' buffers as well as local) as ONE kernel.  A dozen small
+// cudaMemcpyAsync peer copies cost their launch + copy-engine latency each (35 of them made the gathering of the open
+// components 1.2 ms long on 8 GPUs); stores from the SMs go over NVLink at full width when consecutive threads write
+// consecutive 16-byte units.  The segments are INTERLEAVED over the grid (block b works on segment b mod n) and listed
+// starting with the rank after the sender, so that all destinations are in flight at once and the ranks of a group do
+// not all write to the same receiver at the same time: with one segment after the other, in the same order on every
+// rank, the effective bandwidth fell from 440 GB/s on 2 GPUs to 180 GB/s on 8.  Sizes and addresses: multiples of 4 bytes.
 constexpr int COPY_MAX_SEGMENTS = 96;
 struct CopySegments {
   uint32_t n;
@@ -257,12 +260,12 @@ struct CopySegments {
   const void *src[COPY_MAX_SEGMENTS];
   uint64_t bytes[COPY_MAX_SEGMENTS];
 };
-__global__ void __launch_bounds__(256) multi_copy_kernel(const CopySegments S) {
-  const uint32_t k = blockIdx.y;
+__global__ void __launch_bounds__(256) multi_copy_kernel(const CopySegments S, uint32_t blocks_per_segment) {
+  const uint32_t k = blockIdx.x % S.n, bx = blockIdx.x / S.n;
   const uint64_t bytes = S.bytes[k];
   char *dst = static_cast<char *>(S.dst[k]);
   const char *src = static_cast<const char *>(S.src[k]);
-  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x, tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t stride = (uint64_t)blocks_per_segment * blockDim.x, tid = (uint64_t)bx * blockDim.x + threadIdx.x;
   if (((((uintptr_t)dst) | ((uintptr_t)src)) & 15u) == 0) {
     const uint64_t n16 = bytes >> 4;
     for (uint64_t i = tid; i < n16; i += stride) reinterpret_cast<uint4 *>(dst)[i] = reinterpret_cast<const uint4 *>(src)[i];
@@ -275,21 +278,34 @@ __global__ void __launch_bounds__(256) multi_copy_kernel(const CopySegments S) {
 }
 
 struct CopyList {
-  CopySegments S{};
-  uint64_t largest = 0;
-  void add(void *dst, const void *src, size_t bytes) {
-    if (!bytes) return;
-    if (S.n == COPY_MAX_SEGMENTS) throw CudaError{"group: too many copy segments"};
-    S.dst[S.n] = dst;
-    S.src[S.n] = src;
-    S.bytes[S.n] = bytes;
-    S.n++;
-    largest = std::max<uint64_t>(largest, bytes);
+  struct Seg {
+    void *dst;
+    const void *src;
+    uint64_t bytes;
+    uint32_t to;  // destination rank
+  };
+  std::vector<Seg> segs;
+  void add(void *dst, const void *src, size_t bytes, uint32_t to) {
+    if (bytes) segs.push_back({dst, src, bytes, to});
   }
-  void run(cudaStream_t st) {
-    if (!S.n) return;
-    const unsigned gx = (unsigned)std::min<uint64_t>(std::max<uint64_t>((largest / 16 + 255) / 256, 1), 148 * 4);
-    multi_copy_kernel<<<dim3(gx, S.n), 256, 0, st>>>(S);
+  // me / world: this rank and the group's size (destinations are taken in the order me + 1, me + 2, ..., me)
+  void run(cudaStream_t st, uint32_t me, uint32_t world) {
+    if (segs.empty()) return;
+    if (segs.size() > (size_t)COPY_MAX_SEGMENTS) throw CudaError{"group: too many copy segments"};
+    std::stable_sort(segs.begin(), segs.end(), [&](const Seg &a, const Seg &b) {
+      return (a.to + world - me - 1) % world < (b.to + world - me - 1) % world;
+    });
+    CopySegments S{};
+    uint64_t largest = 0;
+    for (const Seg &g : segs) {
+      S.dst[S.n] = g.dst;
+      S.src[S.n] = g.src;
+      S.bytes[S.n] = g.bytes;
+      S.n++;
+      largest = std::max<uint64_t>(largest, g.bytes);
+    }
+    const uint32_t per = (uint32_t)std::min<uint64_t>(std::max<uint64_t>((largest / 16 + 255) / 256, 1), 148 * 2);
+    multi_copy_kernel<<<per * S.n, 256, 0, st>>>(S, per);
     HUMID_CUDA(cudaGetLastError());
   }
 };
@@ -564,11 +580,11 @@ static void group_finalize_body(humid_gpu *h) {
     CopyList words;
     for (uint32_t p = 0; p < W; p++) {
       char *dst = reinterpret_cast<char *>(g.peer[BUF_XFER][p]);
-      words.add(dst + off_at[p] * 8, g.exp_keys.p + seg, counts[p] * 8);
-      words.add(dst + align_up(recv[p] * 8) + off_at[p] * 4, g.exp_ranks.p + seg, counts[p] * 4);
+      words.add(dst + off_at[p] * 8, g.exp_keys.p + seg, counts[p] * 8, p);
+      words.add(dst + align_up(recv[p] * 8) + off_at[p] * 4, g.exp_ranks.p + seg, counts[p] * 4, p);
       seg += counts[p];
     }
-    words.run(s.stream);
+    words.run(s.stream, me, W);
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     group_barrier(g);
     clock.mark("join: words to block owners");
@@ -584,10 +600,10 @@ static void group_finalize_body(humid_gpu *h) {
     seg = 0;
     CopyList ents;
     for (uint32_t p = 0; p < W; p++) {
-      ents.add(reinterpret_cast<char *>(g.peer[BUF_XFER][p]) + eoff[p] * 8, s.join_entries_out.p + seg, ecounts[p] * 8);
+      ents.add(reinterpret_cast<char *>(g.peer[BUF_XFER][p]) + eoff[p] * 8, s.join_entries_out.p + seg, ecounts[p] * 8, p);
       seg += ecounts[p];
     }
-    ents.run(s.stream);
+    ents.run(s.stream, me, W);
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     group_barrier(g);
     ck(humid_gpu_shard_join_import(h, reinterpret_cast<uint64_t *>(g.buf[BUF_XFER].p), erecv[me]));
@@ -626,10 +642,10 @@ static void group_finalize_body(humid_gpu *h) {
     for (uint32_t p = 0; p < W; p++) {
       if (p == me) continue;
       char *dst = reinterpret_cast<char *>(g.peer[BUF_XFER][p]);
-      for (size_t off : cols) open.add(dst + off + open_off * 4, base + off + open_off * 4, n_open * 4);
-      open.add(dst + o_col + eo_off * 4, base + o_col + eo_off * 4, n_open_e * 4);
+      for (size_t off : cols) open.add(dst + off + open_off * 4, base + off + open_off * 4, n_open * 4, p);
+      open.add(dst + o_col + eo_off * 4, base + o_col + eo_off * 4, n_open_e * 4, p);
     }
-    open.run(s.stream);
+    open.run(s.stream, me, W);
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     group_barrier(g);
     clock.mark("open components gathered");
@@ -655,11 +671,11 @@ static void group_finalize_body(humid_gpu *h) {
       HUMID_CUDA(cudaStreamSynchronize(s.stream));
       group_barrier(g);
       CopyList back;  // this rank's own words: what their components' owners found
-      back.add(o.label.p + open_off, base + r_label + open_off * 4, n_open * 4);
-      back.add(o.seed_flag.p + open_off, base + r_flag + open_off * 4, n_open * 4);
-      back.add(o.seed_max.p + open_off, base + r_max + open_off * 4, n_open * 4);
-      back.add(o.seed_size.p + open_off, base + r_size + open_off * 8, n_open * 8);
-      back.run(s.stream);
+      back.add(o.label.p + open_off, base + r_label + open_off * 4, n_open * 4, me);
+      back.add(o.seed_flag.p + open_off, base + r_flag + open_off * 4, n_open * 4, me);
+      back.add(o.seed_max.p + open_off, base + r_max + open_off * 4, n_open * 4, me);
+      back.add(o.seed_size.p + open_off, base + r_size + open_off * 8, n_open * 8, me);
+      back.run(s.stream, me, W);
     };
     struct ClearHook {
       State &s;
@@ -681,8 +697,8 @@ static void group_finalize_body(humid_gpu *h) {
     CopyList ids;
     for (uint32_t p = 0; p < W; p++)
       if (p != me)
-        ids.add(reinterpret_cast<char *>(g.peer[BUF_XFER][p]) + o_ids + open_off * 4, base + o_ids + open_off * 4, n_open * 4);
-    ids.run(s.stream);
+        ids.add(reinterpret_cast<char *>(g.peer[BUF_XFER][p]) + o_ids + open_off * 4, base + o_ids + open_off * 4, n_open * 4, p);
+    ids.run(s.stream, me, W);
     HUMID_CUDA(cudaStreamSynchronize(s.stream));
     group_barrier(g);
     ck(humid_gpu_shard_finish(h, u32(o_ids), g.n_total, usable_total, bases[W], clusters_total));
@@ -713,9 +729,9 @@ static void group_finalize_body(humid_gpu *h) {
       const uint64_t m = g.res_start[q + 1] - g.res_start[q];
       const size_t bb = bits_bytes(m);
       char *dst = reinterpret_cast<char *>(g.peer[BUF_RESULT][g.res_rank[q]]) + bb + align_up(m * 4) + (size_t)me * bb;
-      slices.add(dst, s.keep_bits.p + L.range_off[q], bb);
+      slices.add(dst, s.keep_bits.p + L.range_off[q], bb, g.res_rank[q]);
     }
-    slices.run(s.stream);
+    slices.run(s.stream, me, W);
   }
   stage_histograms_enqueue(s);  // this shard's words / lists / clusters, on their way to page-locked memory
   HUMID_CUDA(cudaStreamSynchronize(s.stream));

@@ -8,8 +8,12 @@ import json
 import os
 import time
 
+import sys
+
 import numpy as np
 import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--config", type=int, default=4)
