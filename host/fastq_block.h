@@ -1,6 +1,7 @@
 // Block-wise FastQ reading for the `humid` executable: SURVEY.md §8(f) item 1, the host ingest in
 // front of the device path.  One BlockReader per input file runs in its own thread
-// (host/humid_main.cc); it reads 16 MiB blocks (plain, gzip, or BGZF inflated by several threads: host/bgzf.h), finds line ends with memchr and
+// (host/humid_main.cc); it reads 16 MiB blocks (plain, gzip through host/inflate_fast.h, or BGZF inflated by several
+// threads: host/bgzf.h), finds line ends with memchr and
 // hands out records as views into its buffer — no allocation and no copy per record.
 //
 // The observable rules are those of host/fastq_io.h's FastqReader (i.e. of fastp's reader as the
@@ -25,6 +26,7 @@
 
 #include "bgzf.h"
 #include "fastq_io.h"
+#include "inflate_fast.h"
 
 namespace humid_host {
 
@@ -33,6 +35,12 @@ inline unsigned default_inflate_threads() {
   if (const char *e = std::getenv("HUMID_INFLATE_THREADS")) return (unsigned)std::max(1, std::atoi(e));
   const unsigned hw = std::thread::hardware_concurrency();
   return std::max(1u, std::min(4u, hw / 4));
+}
+
+// HUMID_INFLATE=zlib: ordinary .gz files through zlib's gzread instead of host/inflate_fast.h (for comparisons).
+inline bool zlib_inflate_wanted() {
+  const char *e = std::getenv("HUMID_INFLATE");
+  return e && std::string(e) == "zlib";
 }
 
 struct Span {
@@ -53,6 +61,9 @@ class BlockReader {
       : path_(path), buf_(block), base_(start) {
     if (ends_with(path, ".gz") && inflate_threads > 1 && !start && is_bgzf(path)) {
       bgzf_.reset(new BgzfInflater(path, inflate_threads));
+    } else if (ends_with(path, ".gz") && !zlib_inflate_wanted()) {
+      if (start) error_exit("cannot seek in a compressed file: " + path);
+      fast_.reset(new GzFastReader(path));
     } else if (ends_with(path, ".gz")) {
       if (start) error_exit("cannot seek in a compressed file: " + path);
       gz_ = gzopen(path.c_str(), "rb");
@@ -73,6 +84,7 @@ class BlockReader {
 
   // Byte offset (in the uncompressed data) of the name line of the record read last: a reader started
   // there sees the same records from that one on.
+  size_t buffer_bytes() const { return buf_.size(); }
   uint64_t offset_of(const RecordView &r) const { return base_ + (uint64_t)(r.name.p - buf_.data()); }
 
   // false at end of input (or at a malformed record).  The views stay valid until the next call.
@@ -99,12 +111,28 @@ class BlockReader {
  private:
   enum { kOk, kNeedMore, kEnd };
 
-  // One line starting at pos.  kNeedMore: no terminator in the buffer and the file has more.
+  // One line starting at pos.  kNeedMore: nothing in the buffer ends it and the file has more.
   int line(size_t &pos, Span &s) {
     const char *b = buf_.data() + pos;
     const size_t avail = end_ - pos;
-    const char *nl = avail ? (const char *)std::memchr(b, '\n', avail) : nullptr;
-    if (!nl && !drained_) return kNeedMore;
+    // [nl_free_from_, nl_free_to_) is known to hold no '\n' (a file with '\r' line ends only would otherwise be
+    // searched to the end of the buffer once per line)
+    const size_t from = (pos >= nl_free_from_ && pos < nl_free_to_) ? nl_free_to_ : pos;
+    const char *nl = from < end_ ? (const char *)std::memchr(buf_.data() + from, '\n', end_ - from) : nullptr;
+    if (!nl) {
+      if (from == pos) nl_free_from_ = pos;
+      nl_free_to_ = end_;
+      if (!drained_) {
+        // a '\r' with data behind it ends the line where it stands (that byte is not a '\n': there is none); as the
+        // last byte in the buffer it may be the first half of "\r\n"
+        const char *cr = avail ? (const char *)std::memchr(b, '\r', avail) : nullptr;
+        if (!cr || (size_t)(cr - b) + 1 >= avail) return kNeedMore;
+        s.p = b;
+        s.n = (size_t)(cr - b);
+        pos += s.n + 1;
+        return kOk;
+      }
+    }
     size_t len = nl ? (size_t)(nl - b) : avail;
     size_t next = nl ? len + 1 : len;
     if (const char *cr = len ? (const char *)std::memchr(b, '\r', len) : nullptr) {
@@ -145,6 +173,8 @@ class BlockReader {
       std::memmove(buf_.data(), buf_.data() + mark_, end_ - mark_);
       end_ -= mark_;
       base_ += mark_;
+      nl_free_from_ = nl_free_from_ > mark_ ? nl_free_from_ - mark_ : 0;
+      nl_free_to_ = nl_free_to_ > mark_ ? nl_free_to_ - mark_ : 0;
       mark_ = 0;
     }
     if (end_ == buf_.size()) buf_.resize(buf_.size() * 2);  // one record longer than the block
@@ -152,6 +182,8 @@ class BlockReader {
     long got;
     if (bgzf_) {
       got = bgzf_->read(buf_.data() + end_, room);
+    } else if (fast_) {
+      got = fast_->read(buf_.data() + end_, room);
     } else if (gz_) {
       got = gzread(gz_, buf_.data() + end_, (unsigned)std::min<size_t>(room, 1u << 30));
       if (got < 0) error_exit("igzip: encountered while decompressing file: " + path_);
@@ -170,11 +202,13 @@ class BlockReader {
   std::vector<char> buf_;
   uint64_t base_ = 0;          // offset of buf_[0] in the (uncompressed) data
   size_t mark_ = 0, end_ = 0;  // [mark_, end_) = bytes not yet handed out
+  size_t nl_free_from_ = 0, nl_free_to_ = 0;
   bool finished_ = false;      // the file has no more bytes
   bool drained_ = false;       // ... and the parser knows: the last line ends at end_
   gzFile gz_ = nullptr;
   FILE *fp_ = nullptr;
   std::unique_ptr<BgzfInflater> bgzf_;
+  std::unique_ptr<GzFastReader> fast_;
 };
 
 }  // namespace humid_host

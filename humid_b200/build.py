@@ -80,7 +80,10 @@ def build_host(force: bool = False) -> str:
     """The `humid` executable (host/humid_main.cc): same CLI as the reference, linked against
     libhumid_gpu.so (found next to the binary through $ORIGIN)."""
     root = os.path.dirname(HERE)
-    srcs = [os.path.join(root, "host", f) for f in ("humid_main.cc", "fastq_io.h", "fastq_block.h", "fastq_rewrite.h", "bgzf.h")] + [os.path.join(root, "include", "humid_gpu.h")]
+    import glob
+
+    srcs = [os.path.join(root, "host", "humid_main.cc")] + sorted(glob.glob(os.path.join(root, "host", "*.h"))) + \
+        sorted(glob.glob(os.path.join(root, "include", "*.h")))
     if not force and os.path.exists(HOST_BIN) and all(os.path.getmtime(s) <= os.path.getmtime(HOST_BIN) for s in srcs):
         return HOST_BIN
     build()

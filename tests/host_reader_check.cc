@@ -60,6 +60,7 @@ int main(int argc, char **argv) {
                 << len << "]\n";
       n++;
     }
+    std::cerr << "buffer " << reader.buffer_bytes() << "\n";
   }
   std::cout << "records " << n << "\n";
   return 0;

@@ -63,6 +63,20 @@ def test_block_reader_matches_line_reader(checker, tmp_path, case, gz):
         assert ref.stdout.endswith(b"records 300\n")
 
 
+def test_lone_cr_files_are_streamed(checker, tmp_path):
+    """A file whose lines end with '\\r' only has no '\\n' to wait for: the block reader must hand its records out block
+    by block instead of growing its buffer to the size of the file."""
+    data = b"".join(records(4000, np.random.default_rng(3), b"\r"))
+    path = str(tmp_path / "in.fastq")
+    with open(path, "wb") as f:
+        f.write(data)
+    ref = subprocess.run([checker, "old", path], capture_output=True, check=True)
+    got = subprocess.run([checker, "block", path, "256"], capture_output=True, check=True)
+    assert got.stdout == ref.stdout and ref.stdout.endswith(b"records 4000\n")
+    grown_to = int(got.stderr.split(b"buffer ")[1].split()[0])
+    assert grown_to <= 1024 < len(data) // 100, grown_to
+
+
 @pytest.mark.parametrize("case", ["plain", "crlf", "mixed_eol", "junk_between", "no_final_newline", "long_lines", "empty",
                                   "truncated_record"])
 @pytest.mark.parametrize("annotate", [0, 1])
