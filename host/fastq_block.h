@@ -1,7 +1,7 @@
 // Block-wise FastQ reading for the `humid` executable: SURVEY.md §8(f) item 1, the host ingest in
 // front of the device path.  One BlockReader per input file runs in its own thread
-// (host/humid_main.cc); it reads 16 MiB blocks (plain, gzip through host/inflate_fast.h, or BGZF inflated by several
-// threads: host/bgzf.h), finds line ends with memchr and
+// (host/humid_main.cc); it reads 16 MiB blocks (plain, gzip through host/inflate_fast.h or — several threads on one
+// member — host/inflate_parallel.h, or BGZF inflated by several threads: host/bgzf.h), finds line ends with memchr and
 // hands out records as views into its buffer — no allocation and no copy per record.
 //
 // The observable rules are those of host/fastq_io.h's FastqReader (i.e. of fastp's reader as the
@@ -27,10 +27,12 @@
 #include "bgzf.h"
 #include "fastq_io.h"
 #include "inflate_fast.h"
+#include "inflate_parallel.h"
 
 namespace humid_host {
 
-// Inflate threads of one BGZF input (HUMID_INFLATE_THREADS overrides; 1 = the one-stream path).
+// Inflate threads of one compressed input (HUMID_INFLATE_THREADS overrides; 1 or 2 = one thread front to back for
+// ordinary members).
 inline unsigned default_inflate_threads() {
   if (const char *e = std::getenv("HUMID_INFLATE_THREADS")) return (unsigned)std::max(1, std::atoi(e));
   const unsigned hw = std::thread::hardware_concurrency();
@@ -63,7 +65,10 @@ class BlockReader {
       bgzf_.reset(new BgzfInflater(path, inflate_threads));
     } else if (ends_with(path, ".gz") && !zlib_inflate_wanted()) {
       if (start) error_exit("cannot seek in a compressed file: " + path);
-      fast_.reset(new GzFastReader(path));
+      // three threads or more decode an ordinary member faster than one does front to back (a speculative decode runs at
+      // about half the speed of a plain one)
+      if (inflate_threads >= 3 && ParallelGzReader::worth_it(path, inflate_threads)) parallel_.reset(new ParallelGzReader(path, inflate_threads));
+      else fast_.reset(new GzFastReader(path));
     } else if (ends_with(path, ".gz")) {
       if (start) error_exit("cannot seek in a compressed file: " + path);
       gz_ = gzopen(path.c_str(), "rb");
@@ -182,6 +187,8 @@ class BlockReader {
     long got;
     if (bgzf_) {
       got = bgzf_->read(buf_.data() + end_, room);
+    } else if (parallel_) {
+      got = parallel_->read(buf_.data() + end_, room);
     } else if (fast_) {
       got = fast_->read(buf_.data() + end_, room);
     } else if (gz_) {
@@ -209,6 +216,7 @@ class BlockReader {
   FILE *fp_ = nullptr;
   std::unique_ptr<BgzfInflater> bgzf_;
   std::unique_ptr<GzFastReader> fast_;
+  std::unique_ptr<ParallelGzReader> parallel_;
 };
 
 }  // namespace humid_host

@@ -30,7 +30,7 @@ namespace humid_host {
 
 class Inflate {
  public:
-  enum Status { kDone, kNeedInput, kNeedOutput, kError };
+  enum Status { kDone, kNeedInput, kNeedOutput, kError, kBoundary };
 
   Inflate() { reset(); }
 
@@ -63,7 +63,36 @@ class Inflate {
   static constexpr size_t kInPad = 32;
   static constexpr size_t kInSlack = 1024;  // > a dynamic block header (at most 14 + 57 + 320 * 14 bits)
   static constexpr size_t kOutSlack = 320;  // three look-ups of literals (4-byte stores) + a match of 258 (+ 7)
-  Status run(const uint8_t *&in, const uint8_t *in_end, bool eof, const uint8_t *window, uint8_t *&out, uint8_t *out_end);
+  //   * boundary (may be null): the call ends with kBoundary in front of the first block header that starts at or
+  //     behind this input position; the stream goes on from there with the next call.
+  Status run(const uint8_t *&in, const uint8_t *in_end, bool eof, const uint8_t *window, uint8_t *&out, uint8_t *out_end,
+             const uint8_t *boundary = nullptr) {
+    return run_t<uint8_t>(in, in_end, eof, window, out, out_end, boundary);
+  }
+  // The same with 16-bit output elements (host/inflate_parallel.h): a deflate stream entered in the middle copies
+  // from 32 KiB it has not seen, so the caller puts 32768 place holders (values >= 0x8000) in front of `out`, they
+  // travel through the matches like bytes, and whoever knows the real bytes later replaces them.
+  Status run_marked(const uint8_t *&in, const uint8_t *in_end, bool eof, const uint16_t *window, uint16_t *&out,
+                    uint16_t *out_end, const uint8_t *boundary = nullptr) {
+    return run_t<uint16_t>(in, in_end, eof, window, out, out_end, boundary);
+  }
+
+  // Enter a stream at bit `bit` (0..7, counted from the low end) of *in: a block header must start there.
+  void start_at(const uint8_t *&in, unsigned bit) {
+    reset();
+    if (bit) {
+      hold_ = (uint64_t)*in++ >> bit;
+      bits_ = 8 - bit;
+    }
+  }
+  // Bits loaded from in front of the caller's `in` and not yet used: the stream stands 8 * offset(in) - pending_bits().
+  unsigned pending_bits() const { return bits_; }
+  bool stream_finished() const { return state_ == kFinished; }
+
+  // Does a dynamic-code block header that a compressor would write start at bit `bit` of p?  (Block finder of the
+  // parallel reader: not final, both code sets complete.)  The header is read up to `end`; 16 bytes behind `end`
+  // must be readable.
+  bool probe_dynamic_header(const uint8_t *p, const uint8_t *end, unsigned bit);
 
  private:
   // Table entries, 32 bits:
@@ -134,7 +163,8 @@ class Inflate {
   // Canonical Huffman code of lens[0..n) -> look-up table, one symbol per entry.  payload[s] = the entry of symbol
   // s without its bit count.  An over-subscribed set of lengths is an error; an incomplete one leaves kInvalid
   // entries (an encoder may send a single distance code, RFC 1951 3.2.7).
-  bool build(const uint8_t *lens, int n, const uint32_t *payload, int index_bits, uint32_t *table, int cap) {
+  bool build(const uint8_t *lens, int n, const uint32_t *payload, int index_bits, uint32_t *table, int cap,
+             bool *complete = nullptr) {
     int count[16] = {0};
     for (int s = 0; s < n; s++) count[lens[s]]++;
     count[0] = 0;
@@ -143,6 +173,7 @@ class Inflate {
       left = 2 * left - count[len];
       if (left < 0) return false;
     }
+    if (complete) *complete = left == 0;
     uint32_t next_code[16];
     uint32_t code = 0;
     for (int len = 1; len <= 15; len++) {
@@ -245,7 +276,19 @@ class Inflate {
   }
 
   Status block_header(const uint8_t *&in, const uint8_t *in_end);
-  Status stored(const uint8_t *&in, const uint8_t *in_end, bool eof, uint8_t *&out, uint8_t *out_end);
+  template <class T>
+  Status stored(const uint8_t *&in, const uint8_t *in_end, bool eof, T *&out, T *out_end);
+  template <class T>
+  Status run_t(const uint8_t *&in, const uint8_t *in_end, bool eof, const T *window, T *&out, T *out_end, const uint8_t *boundary);
+  // n literals of a table entry / `length` elements from `distance` back, for both element types
+  static void put_literals(uint8_t *op, uint32_t bytes) { store32(op, bytes); }
+  static void put_literals(uint16_t *op, uint32_t bytes) {
+    op[0] = (uint16_t)(bytes & 0xFFu);
+    op[1] = (uint16_t)((bytes >> 8) & 0xFFu);
+    op[2] = (uint16_t)((bytes >> 16) & 0xFFu);
+  }
+  static void copy_match(uint8_t *op, uint32_t distance, uint32_t length);
+  static void copy_match(uint16_t *op, uint32_t distance, uint32_t length);
 
   uint64_t hold_;
   unsigned bits_;
@@ -253,6 +296,7 @@ class Inflate {
   bool final_;
   uint32_t stored_left_;
   const char *error_;
+  bool lit_complete_ = false, dist_complete_ = false;
   uint32_t lit_[kLitCap], dist_[kDistCap];
 };
 
@@ -321,27 +365,54 @@ inline Inflate::Status Inflate::block_header(const uint8_t *&in, const uint8_t *
     have += repeat;
   }
   if (!lens[256]) return fail("invalid code -- missing end-of-block");
-  if (!build(lens, (int)n_lit, payloads().litlen, kLitBits, lit_, kLitCap)) return fail("invalid literal/lengths set");
+  if (!build(lens, (int)n_lit, payloads().litlen, kLitBits, lit_, kLitCap, &lit_complete_)) return fail("invalid literal/lengths set");
   pack_literals();
-  if (!build(lens + n_lit, (int)n_dist, payloads().dist, kDistBits, dist_, kDistCap)) return fail("invalid distances set");
+  if (!build(lens + n_lit, (int)n_dist, payloads().dist, kDistBits, dist_, kDistCap, &dist_complete_)) return fail("invalid distances set");
   state_ = kCodes;
   return kDone;
 }
 
+inline bool Inflate::probe_dynamic_header(const uint8_t *p, const uint8_t *end, unsigned bit) {
+  if (end - p < 10) return false;
+  // cheap tests on the first 17 bits: BFINAL = 0, BTYPE = 2, at most 286 / 30 codes
+  const uint64_t v = load64(p) >> bit;
+  if ((v & 7u) != 4u) return false;
+  if (((v >> 3) & 31u) > 29u || ((v >> 8) & 31u) > 29u) return false;
+  // the code-length code must be complete: sum of 2^(7 - len) over its 4..19 three-bit lengths == 2^7
+  const unsigned n_pre = (unsigned)((v >> 13) & 15u) + 4;
+  unsigned at = bit + 17, kraft = 0;
+  for (unsigned i = 0; i < n_pre; i += 16) {
+    uint64_t w = load64(p + (at >> 3)) >> (at & 7);
+    const unsigned n = n_pre - i < 16 ? n_pre - i : 16;
+    for (unsigned k = 0; k < n; k++, w >>= 3)
+      if (w & 7u) kraft += 128u >> (w & 7u);
+    at += 3 * n;
+  }
+  if (kraft != 128u) return false;
+  // the whole header through the ordinary parser
+  const uint8_t *in = p;
+  start_at(in, bit);
+  if (block_header(in, end) != kDone || state_ != kCodes) return false;
+  return lit_complete_ && dist_complete_;
+}
+
 // The bytes of a stored block: from the hold first (whole bytes only: the length fields ended on a byte
 // boundary), then straight from the window.
-inline Inflate::Status Inflate::stored(const uint8_t *&in, const uint8_t *in_end, bool eof, uint8_t *&out, uint8_t *out_end) {
+template <class T>
+inline Inflate::Status Inflate::stored(const uint8_t *&in, const uint8_t *in_end, bool eof, T *&out, T *out_end) {
   hold_ &= bits_ < 64 ? (1ull << bits_) - 1 : ~0ull;
   while (stored_left_ && bits_ >= 8) {
     if (out >= out_end) return kNeedOutput;
-    *out++ = (uint8_t)take(8);
+    *out++ = (T)take(8);
     stored_left_--;
   }
   if (stored_left_) {
     bits_ = 0;
     hold_ = 0;
     const size_t n = std::min<size_t>(std::min<size_t>(stored_left_, (size_t)(in_end - in)), (size_t)(out_end - out));
-    std::memcpy(out, in, n);
+    if (sizeof(T) == 1) std::memcpy(out, in, n);
+    else
+      for (size_t i = 0; i < n; i++) out[i] = (T)in[i];
     in += n;
     out += n;
     stored_left_ -= (uint32_t)n;
@@ -354,17 +425,75 @@ inline Inflate::Status Inflate::stored(const uint8_t *&in, const uint8_t *in_end
   return kDone;
 }
 
-inline Inflate::Status Inflate::run(const uint8_t *&in, const uint8_t *in_end, bool eof, const uint8_t *window, uint8_t *&out,
-                                    uint8_t *out_end) {
+inline void Inflate::copy_match(uint8_t *op, uint32_t distance, uint32_t length) {
+  const uint8_t *from = op - distance;
+  uint8_t *const stop = op + length;
+  if (distance >= 8) {
+    // 16 bytes whatever the length (most matches of FastQ text are shorter), 8 at a time so that a distance of
+    // 8..15 repeats its pattern; up to 15 bytes past `stop` are written: inside kOutSlack
+    store64(op, load64(from));
+    store64(op + 8, load64(from + 8));
+    if (length > 16) {
+      op += 16;
+      from += 16;
+      do {
+        store64(op, load64(from));
+        op += 8;
+        from += 8;
+      } while (op < stop);
+    }
+  } else if (distance == 1) {  // a run of one byte: quality strings are full of them
+    const uint64_t v = 0x0101010101010101ull * *from;
+    do {
+      store64(op, v);
+      op += 8;
+    } while (op < stop);
+  } else {
+    do *op++ = *from++;
+    while (op < stop);
+  }
+}
+
+inline void Inflate::copy_match(uint16_t *op, uint32_t distance, uint32_t length) {
+  const uint16_t *from = op - distance;
+  uint16_t *const stop = op + length;
+  if (distance >= 8) {  // sixteen elements whatever the length, eight (16 bytes) at a time; up to 15 past `stop`
+    std::memcpy(op, from, 16);
+    std::memcpy(op + 8, from + 8, 16);
+    if (length > 16) {
+      op += 16;
+      from += 16;
+      do {
+        std::memcpy(op, from, 16);
+        op += 8;
+        from += 8;
+      } while (op < stop);
+    }
+  } else if (distance >= 4) {  // four elements at a time; up to 3 past `stop`
+    do {
+      std::memcpy(op, from, 8);
+      op += 4;
+      from += 4;
+    } while (op < stop);
+  } else {
+    do *op++ = *from++;
+    while (op < stop);
+  }
+}
+
+template <class T>
+inline Inflate::Status Inflate::run_t(const uint8_t *&in, const uint8_t *in_end, bool eof, const T *window, T *&out, T *out_end,
+                                      const uint8_t *boundary) {
   while (true) {
     if (state_ == kFinished) return kDone;
     if (state_ == kHeader) {
+      if (boundary && in - ((bits_ + 7) >> 3) >= boundary) return kBoundary;
       if (!eof && (size_t)(in_end - in) < kInSlack) return kNeedInput;
       if (block_header(in, in_end) != kDone) return kError;
       continue;
     }
     if (state_ == kStored) {
-      const Status st = stored(in, in_end, eof, out, out_end);
+      const Status st = stored<T>(in, in_end, eof, out, out_end);
       if (st != kDone) return st;
       continue;
     }
@@ -374,10 +503,10 @@ inline Inflate::Status Inflate::run(const uint8_t *&in, const uint8_t *in_end, b
     uint64_t hold = hold_;
     unsigned bits = bits_;
     const uint8_t *ip = in;
-    uint8_t *op = out;
+    T *op = out;
     // one round of the loop loads 8 bytes twice, at ip <= in_limit + 14, and writes less than kOutSlack bytes
     const uint8_t *const in_limit = eof ? in_end : in_end - 24;
-    uint8_t *const out_limit = out_end - kOutSlack;
+    T *const out_limit = out_end - kOutSlack;
     constexpr uint64_t lit_mask = (1u << kLitBits) - 1, dist_mask = (1u << kDistBits) - 1;
     Status st = kDone;
     bool end_of_block = false;
@@ -410,19 +539,19 @@ inline Inflate::Status Inflate::run(const uint8_t *&in, const uint8_t *in_end, b
       // up to three look-ups of literals on one load: each uses at most kLitBits bits (15 through a sub-table,
       // which ends the run), 56 were there
       if (!(e & kKindMask)) {
-        store32(op, e >> 8);
+        put_literals(op, e >> 8);
         op += (e >> 4) & 3u;
         hold >>= e & 15u;
         bits -= e & 15u;
         e = lit_[hold & lit_mask];
         if (!(e & kKindMask)) {
-          store32(op, e >> 8);
+          put_literals(op, e >> 8);
           op += (e >> 4) & 3u;
           hold >>= e & 15u;
           bits -= e & 15u;
           e = lit_[hold & lit_mask];
           if (!(e & kKindMask)) {
-            store32(op, e >> 8);
+            put_literals(op, e >> 8);
             op += (e >> 4) & 3u;
             hold >>= e & 15u;
             bits -= e & 15u;
@@ -439,7 +568,7 @@ inline Inflate::Status Inflate::run(const uint8_t *&in, const uint8_t *in_end, b
         bits -= kLitBits;
         e = lit_[((e >> 8) & 0xFFFFu) + (hold & ((1u << ((e >> 24) & 15u)) - 1))];
         if (!(e & kKindMask)) {  // a literal with a long code
-          *op++ = (uint8_t)(e >> 8);
+          *op++ = (T)((e >> 8) & 0xFFu);
           hold >>= e & 15u;
           bits -= e & 15u;
           continue;
@@ -473,33 +602,8 @@ inline Inflate::Status Inflate::run(const uint8_t *&in, const uint8_t *in_end, b
         st = fail("invalid distance too far back");
         break;
       }
-      const uint8_t *from = op - distance;
-      uint8_t *const stop = op + length;
-      if (distance >= 8) {
-        // 16 bytes whatever the length (most matches of FastQ text are shorter), 8 at a time so that a distance
-        // of 8..15 repeats its pattern; up to 15 bytes past `stop` are written: inside kOutSlack
-        store64(op, load64(from));
-        store64(op + 8, load64(from + 8));
-        if (length > 16) {
-          op += 16;
-          from += 16;
-          do {
-            store64(op, load64(from));
-            op += 8;
-            from += 8;
-          } while (op < stop);
-        }
-      } else if (distance == 1) {  // a run of one byte: quality strings are full of them
-        const uint64_t v = 0x0101010101010101ull * *from;
-        do {
-          store64(op, v);
-          op += 8;
-        } while (op < stop);
-      } else {
-        do *op++ = *from++;
-        while (op < stop);
-      }
-      op = stop;
+      copy_match(op, distance, length);
+      op += length;
     }
     hold_ = hold;
     bits_ = bits;

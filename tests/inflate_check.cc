@@ -1,5 +1,6 @@
 // Test / measurement helper for host/inflate_fast.h (not part of the product):
-//   inflate_check fast|zlib <file.gz> [read_size]      -> "<bytes> <crc32 hex> <seconds>" on stdout, exit 0
+//   inflate_check fast|zlib|parN <file.gz> [read_size]  -> "<bytes> <crc32 hex> <seconds>" on stdout, exit 0
+//                                                         (parN: host/inflate_parallel.h with N threads, N = 1..64)
 //   inflate_check dump <file.gz> <out>                 -> the inflated bytes written to <out> through the fast reader
 // Errors leave through the reader's error_exit (message on stderr, non-zero exit status).
 #include <chrono>
@@ -8,7 +9,7 @@
 #include <string>
 #include <vector>
 
-#include "../host/inflate_fast.h"
+#include "../host/inflate_parallel.h"
 
 int main(int argc, char **argv) {
   if (argc < 3) return 2;
@@ -37,6 +38,10 @@ int main(int argc, char **argv) {
   };
   if (mode == "fast") {
     humid_host::GzFastReader r(path);
+    long got;
+    while ((got = r.read(buf.data(), buf.size())) > 0) account(got);
+  } else if (mode.compare(0, 3, "par") == 0) {
+    humid_host::ParallelGzReader r(path, (unsigned)std::max(1, std::atoi(mode.c_str() + 3)));
     long got;
     while ((got = r.read(buf.data(), buf.size())) > 0) account(got);
   } else {

@@ -36,15 +36,25 @@ def test_host_side_matches_reference_binary(tmp_path, humid_cpu, name, ci, R, kw
 
 
 def test_host_side_with_many_inflate_and_writer_threads(tmp_path, humid_cpu, monkeypatch):
-    """150 000 tuples (73 batches of 2048, 293 output chunks of 512 in this build) in BGZF files with 3 inflate threads per
-    file, against the same input as plain files."""
+    """150 000 tuples (73 batches of 2048, 293 output chunks of 512 in this build) in BGZF files and in ordinary .gz files with
+    3 inflate threads per file, against the same input as plain files."""
     from humid_b200.synth import Synth, baseline_config
     from test_host_reader import bgzf_bytes
     cfg = baseline_config(1, 150_000)
     files = list(Synth(cfg).write_fastq(str(tmp_path / "in"), prefix="x", gzip_output=False))
     outs = {}
-    for kind in ("plain", "bgzf"):
+    for kind in ("plain", "bgzf", "gz"):
         use = files
+        if kind == "gz":  # ordinary one-member files, 3 threads on each (host/inflate_parallel.h), spans of 16 KiB
+            import gzip
+            use = []
+            for f in files:
+                with open(f + ".1.gz", "wb") as out:
+                    out.write(gzip.compress(open(f, "rb").read(), 6))
+                use.append(f + ".1.gz")
+            monkeypatch.setenv("HUMID_INFLATE_THREADS", "3")
+            monkeypatch.setenv("HUMID_INFLATE_SPAN", "16384")
+            monkeypatch.setenv("HUMID_INFLATE_STATS", "1")
         if kind == "bgzf":
             use = []
             for f in files:
@@ -53,12 +63,17 @@ def test_host_side_with_many_inflate_and_writer_threads(tmp_path, humid_cpu, mon
                 use.append(f + ".gz")
             monkeypatch.setenv("HUMID_INFLATE_THREADS", "3")
         d = str(tmp_path / kind)
-        subprocess.run([humid_cpu, *cfg.cli_flags(), "-s", "-a", "-d", d, "-l", str(tmp_path / (kind + ".log")), *use],
-                       check=True, timeout=600)
-        outs[kind] = {f.replace(".gz", ""): G.read_any(os.path.join(d, f)) for f in sorted(os.listdir(d))}
-    assert outs["plain"].keys() == outs["bgzf"].keys() and len(outs["plain"]) == 4 + 2 * len(files)
+        p = subprocess.run([humid_cpu, *cfg.cli_flags(), "-s", "-a", "-d", d, "-l", str(tmp_path / (kind + ".log")), *use],
+                           check=True, timeout=600, capture_output=True, text=True)
+        if kind == "gz":  # both passes of every file went through the parallel reader and used its speculations
+            lines = [l for l in p.stderr.splitlines() if l.startswith("inflate ")]
+            assert len(lines) == 3 * len(files), p.stderr[-2000:]  # ingest, dedup output, annotated output: per file
+            assert all(int(l.split(", ")[1].split()[0]) > 5 for l in lines), lines
+        outs[kind] = {f.replace(".1.gz", "").replace(".gz", ""): G.read_any(os.path.join(d, f)) for f in sorted(os.listdir(d))}
+    assert outs["plain"].keys() == outs["bgzf"].keys() == outs["gz"].keys() and len(outs["plain"]) == 4 + 2 * len(files)
     for f in outs["plain"]:
         assert outs["plain"][f] == outs["bgzf"][f], f
+        assert outs["plain"][f] == outs["gz"][f], f
     dedup = [f for f in outs["plain"] if "_dedup" in f][0]
     assert 0 < outs["plain"][dedup].count(b"\n") // 4 < 150_000
 
