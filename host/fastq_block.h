@@ -90,6 +90,16 @@ class BlockReader {
   // Byte offset (in the uncompressed data) of the name line of the record read last: a reader started
   // there sees the same records from that one on.
   size_t buffer_bytes() const { return buf_.size(); }
+
+  // Bytes the record read last takes in the file when it is stored exactly as the executable writes records back —
+  // four lines, each ended by one '\n', nothing in between (Read::toString, lib/fastp/src/read.cpp:116-118) — else 0.
+  size_t raw_length(const RecordView &r) const {
+    const char *e = buf_.data() + end_;
+    auto ended = [&](const Span &s) { return s.p + s.n < e && s.p[s.n] == '\n'; };
+    if (!ended(r.name) || !ended(r.seq) || !ended(r.strand) || !ended(r.qual)) return 0;
+    if (r.seq.p != r.name.p + r.name.n + 1 || r.strand.p != r.seq.p + r.seq.n + 1 || r.qual.p != r.strand.p + r.strand.n + 1) return 0;
+    return (size_t)(r.qual.p + r.qual.n + 1 - r.name.p);
+  }
   uint64_t offset_of(const RecordView &r) const { return base_ + (uint64_t)(r.name.p - buf_.data()); }
 
   // false at end of input (or at a malformed record).  The views stay valid until the next call.

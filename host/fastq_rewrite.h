@@ -1,13 +1,18 @@
 // Pass 2 of the `humid` executable: writeFiltered / writeAnnotated (reference src/humid.cc:203-292) —
-// every input file is read again and the kept (or all, annotated) records are written out as
-// name + suffix, sequence, strand, quality, each followed by '\n' (Read::toString).
+// the kept (or all, annotated) records are written out as name + suffix, sequence, strand, quality, each
+// followed by '\n' (Read::toString).
 //
-// SURVEY.md §8(f) item 2.  The reference parses the whole input a second time on one thread.  Here pass 1
-// notes the byte offset of every 65 536th record of a plain (uncompressed) file; pass 2 then cuts the file
-// into those chunks and several threads per file parse them side by side, each into its own buffer.  A
-// chunk's place in the output is known as soon as the chunks before it have been parsed, so the buffers
-// are written with pwrite concurrently.  The bytes written are those of the one-thread pass (same parser,
-// same serialisation).
+// SURVEY.md §8(f) item 2.  The reference opens and parses the whole input a second time on one thread
+// (src/humid.cc:220, :268).  Here pass 1 leaves a RecordMap per plain (uncompressed) file: the byte offset of
+// every 65 536th record, the length in bytes of every record, and per chunk of 65 536 records whether all of
+// them are stored exactly as they would be written back.  Pass 2 cuts the file into those chunks; several
+// threads per file take them side by side.  A chunk stored as written is not parsed again: it is read with
+// one pread and the kept records — runs of them as one copy — are gathered by their lengths (annotated
+// output: the id goes in behind the name line's end, the only byte that is looked for).  Any other chunk
+// (line ends with '\r', junk between records, a last line without '\n', a record of 64 KiB or more) goes
+// through the parser as before.  A chunk's place in the output is known as soon as the chunks before it are
+// done, so the buffers are written with pwrite concurrently.  The bytes written are those of the one-thread
+// pass either way.
 //
 // Compressed files: a .gz input cannot be entered in the middle, so one thread inflates and parses it and hands
 // the text of every chunk to the pool; a .gz output is written as one gzip member per chunk (the reference's
@@ -34,6 +39,29 @@ namespace humid_host {
 #define HUMID_REWRITE_CHUNK (1u << 16)
 #endif
 constexpr uint64_t REWRITE_CHUNK = HUMID_REWRITE_CHUNK;  // records between two noted offsets (the tests build with a tiny one)
+
+// What pass 1 notes about one input file for pass 2.
+struct RecordMap {
+  std::vector<uint64_t> chunk_offset;   // byte offset of record c * REWRITE_CHUNK
+  std::vector<uint16_t> raw_length;     // per record (only when `lengths`)
+  std::vector<uint8_t> chunk_verbatim;  // per chunk: every record stored as written back, one behind the other
+  bool lengths = false;                 // plain files: keep raw_length / chunk_verbatim
+  uint64_t expect_ = 0;
+  // record t (0, 1, 2 ... in order) has just been read
+  void note(uint64_t t, const BlockReader &reader, const RecordView &rec) {
+    const uint64_t at = reader.offset_of(rec);
+    if (t % REWRITE_CHUNK == 0) {
+      chunk_offset.push_back(at);
+      if (lengths) chunk_verbatim.push_back(1);
+      expect_ = at;
+    }
+    if (!lengths) return;
+    const size_t len = reader.raw_length(rec);
+    if (len == 0 || len > 0xFFFFu || at != expect_) chunk_verbatim.back() = 0;
+    raw_length.push_back((uint16_t)len);
+    expect_ = at + len;
+  }
+};
 
 inline void append_record(std::string &out, const RecordView &rec, const uint32_t *ids, uint64_t t) {
   out.append(rec.name.p, rec.name.n);
@@ -192,12 +220,45 @@ inline void rewrite_file_piped(const std::string &in_path, const std::string &ou
   out.finish();
 }
 
-// Several threads: offsets[c] = byte offset of record c * REWRITE_CHUNK (noted in pass 1).
+// Records [t0, t1) of a chunk that is stored as written back: `raw` holds the chunk's bytes, the records lie one
+// behind the other with the lengths noted in pass 1.  No line of it is parsed.
+inline void gather_records(const char *raw, const uint16_t *len, uint64_t t0, uint64_t t1, const uint64_t *keep, const uint32_t *ids,
+                           std::string &out) {
+  size_t at = 0;
+  if (ids) {  // every record, ":<id>" behind its name
+    for (uint64_t t = t0; t < t1; t++) {
+      const size_t n = len[t - t0];
+      const char *nl = (const char *)std::memchr(raw + at, '\n', n);
+      const size_t name = (size_t)(nl - (raw + at));
+      out.append(raw + at, name).append(":").append(std::to_string(ids[t]));
+      out.append(raw + at + name, n - name);
+      at += n;
+    }
+    return;
+  }
+  size_t run_from = 0, run = 0;  // kept records that follow one another leave as one copy
+  for (uint64_t t = t0; t < t1; t++) {
+    const size_t n = len[t - t0];
+    if (!keep || (keep[t >> 6] >> (t & 63) & 1)) {
+      if (!run) run_from = at;
+      run += n;
+    } else if (run) {
+      out.append(raw + run_from, run);
+      run = 0;
+    }
+    at += n;
+  }
+  if (run) out.append(raw + run_from, run);
+}
+
+// Several threads over the chunks noted in pass 1.
 inline void rewrite_file_parallel(const std::string &in_path, const std::string &out_path, uint64_t total,
-                                  const uint64_t *keep, const uint32_t *ids, const std::vector<uint64_t> &offsets,
-                                  unsigned n_threads) {
+                                  const uint64_t *keep, const uint32_t *ids, const RecordMap &map, unsigned n_threads) {
+  const std::vector<uint64_t> &offsets = map.chunk_offset;
   const uint64_t n_chunks = (total + REWRITE_CHUNK - 1) / REWRITE_CHUNK;
-  if (n_threads < 2 || n_chunks < 2) {
+  const bool gather = map.lengths && !ends_with(in_path, ".gz") && offsets.size() >= n_chunks && map.raw_length.size() >= total &&
+                      !std::getenv("HUMID_REWRITE_PARSE");  // (set: every chunk through the parser, for comparisons)
+  if ((n_threads < 2 || n_chunks < 2) && !gather) {
     rewrite_file(in_path, out_path, total, keep, ids);
     return;
   }
@@ -207,15 +268,31 @@ inline void rewrite_file_parallel(const std::string &in_path, const std::string 
   }
   OrderedOutput out(out_path);
   std::atomic<uint64_t> next{0};
+  int fd = -1;
+  if (gather) {
+    fd = open(in_path.c_str(), O_RDONLY);
+    if (fd < 0) error_exit("Failed to open file: " + in_path);
+  }
   auto worker = [&] {
     std::string buf, scratch;
+    std::vector<char> raw;
     RecordView rec;
     while (true) {
       const uint64_t c = next.fetch_add(1);
       if (c >= n_chunks) return;
       const uint64_t t0 = c * REWRITE_CHUNK, t1 = std::min(total, t0 + REWRITE_CHUNK);
       buf.clear();
-      {
+      if (gather && map.chunk_verbatim[c]) {
+        size_t bytes = 0;
+        for (uint64_t t = t0; t < t1; t++) bytes += map.raw_length[t];
+        raw.resize(bytes);
+        for (size_t done = 0; done < bytes;) {
+          const ssize_t got = pread(fd, raw.data() + done, bytes - done, (off_t)(offsets[c] + done));
+          if (got <= 0) error_exit("Failed to read: " + in_path);
+          done += (size_t)got;
+        }
+        gather_records(raw.data(), map.raw_length.data() + t0, t0, t1, keep, ids, buf);
+      } else {
         BlockReader reader(in_path, 4u << 20, offsets[c]);
         for (uint64_t t = t0; t < t1 && reader.read(rec); t++) {
           if (keep && !(keep[t >> 6] >> (t & 63) & 1)) continue;
@@ -226,8 +303,9 @@ inline void rewrite_file_parallel(const std::string &in_path, const std::string 
     }
   };
   std::vector<std::thread> pool;
-  for (unsigned i = 0; i < n_threads; i++) pool.emplace_back(worker);
+  for (unsigned i = 0; i < std::max(1u, n_threads); i++) pool.emplace_back(worker);
   for (std::thread &t : pool) t.join();
+  if (fd >= 0) close(fd);
   out.finish();
 }
 

@@ -15,8 +15,9 @@
 // (host/fastq_block.h) and writes its share of every word straight into a page-locked batch
 // buffer; the main thread hands full batches to humid_gpu_add_batch, which uploads them while the
 // next batch is being parsed and the previous one is counted on the device.  The output passes
-// (host/fastq_rewrite.h) cut every plain file into chunks at record offsets noted
-// during ingest and parse / write them with several threads per file.
+// (host/fastq_rewrite.h) do not parse plain files again: ingest notes where every record
+// lies, and several threads per file gather the kept ones by pread.  Compressed inputs are inflated a second
+// time (host/inflate_fast.h, host/inflate_parallel.h, host/bgzf.h) and parsed by one thread per file.
 #include <sys/stat.h>
 
 #include <chrono>
@@ -181,7 +182,7 @@ struct Ingest {
   size_t n = 0, S = 0;          // word length, segments
   vector<size_t> seg_off;       // first column of a segment
   Layout L;
-  vector<vector<uint64_t>> chunk_offset;  // per file: byte offset of every REWRITE_CHUNK-th record (pass 2 starts there)
+  vector<RecordMap> maps;       // per file: what pass 2 needs to know about its records (host/fastq_rewrite.h)
 };
 
 // file i: segment (header UMI ? i + 1 : i); file 0 also fills segment 0 from its headers
@@ -201,7 +202,7 @@ void ingest_file(Ingest &g, const string &path, size_t file) {
     size_t m = 0;
     for (; m < BATCH; m++) {
       if (!reader.read(rec)) { ended = true; break; }
-      if (m % REWRITE_CHUNK == 0) g.chunk_offset[file].push_back(reader.offset_of(rec));  // BATCH is a multiple of it
+      g.maps[file].note(k * BATCH + m, reader, rec);  // (BATCH is a multiple of REWRITE_CHUNK)
       // getNucleotides (src/fastq.cc:116-144) WITHOUT the padding / validation: the device applies
       // makeStringSize_ and the ACGT filter from (chars, seg_len)
       uint8_t *row = s.chars + m * g.n;
@@ -342,10 +343,12 @@ int main(int argc, char **argv) {
 
   t0 = start_message(log, "Reading data");
   uint64_t total = 0;
-  vector<vector<uint64_t>> chunk_offset;
+  vector<RecordMap> maps;
   {
     Ingest g;
-    g.chunk_offset.assign(F, {});
+    g.maps.assign(F, RecordMap());
+    // plain files: the length of every record, so that the output passes gather instead of parsing again
+    for (size_t i = 0; i < F; i++) g.maps[i].lengths = (opt.filter || opt.annotate) && !ends_with(opt.files[i], ".gz");
     g.n = opt.word_length;
     g.S = seg_take.size();
     g.L = L;
@@ -393,7 +396,7 @@ int main(int argc, char **argv) {
       if (g.stop) break;
     }
     for (std::thread &t : readers) t.join();
-    chunk_offset.swap(g.chunk_offset);
+    maps.swap(g.maps);
     for (int j = 0; j < N_SLOTS; j++) {
       humid_gpu_host_unregister(gpu, g.slots[j].chars);
       humid_gpu_host_unregister(gpu, g.slots[j].seg_len);
@@ -425,7 +428,7 @@ int main(int argc, char **argv) {
     vector<std::thread> writers;
     for (size_t i = 0; i < F; i++)
       writers.emplace_back(rewrite_file_parallel, opt.files[i], make_file_name(opt.files[i], opt.dir_name, "dedup"), total,
-                           keep.data(), nullptr, std::cref(chunk_offset[i]), threads_per_file);
+                           keep.data(), nullptr, std::cref(maps[i]), threads_per_file);
     for (std::thread &t : writers) t.join();
     end_message(log, t0);
   }
@@ -443,7 +446,7 @@ int main(int argc, char **argv) {
     vector<std::thread> writers;
     for (size_t i = 0; i < F; i++)
       writers.emplace_back(rewrite_file_parallel, opt.files[i], make_file_name(opt.files[i], opt.dir_name, "annotated"),
-                           total, nullptr, ids.data(), std::cref(chunk_offset[i]), threads_per_file);
+                           total, nullptr, ids.data(), std::cref(maps[i]), threads_per_file);
     for (std::thread &t : writers) t.join();
     end_message(log, t0);
   }

@@ -15,15 +15,13 @@ int main(int argc, char **argv) {
   size_t n = 0;
   if (mode == "rewrite") {  // rewrite <in> <out one thread> <out threads> <seed> <annotate 0|1> <threads>
     // pass 1 as the executable does it: count the records, note the offset of every REWRITE_CHUNK-th
-    std::vector<uint64_t> offsets;
+    RecordMap map;
+    map.lengths = path.size() < 3 || path.compare(path.size() - 3, 3, ".gz") != 0;
     uint64_t total = 0;
     {
       BlockReader reader(path, 64);
       RecordView r;
-      while (reader.read(r)) {
-        if (total % REWRITE_CHUNK == 0) offsets.push_back(reader.offset_of(r));
-        total++;
-      }
+      while (reader.read(r)) map.note(total++, reader, r);
     }
     uint64_t x = std::strtoull(argv[5], nullptr, 10) * 0x9E3779B97F4A7C15ull + 1;
     std::vector<uint64_t> keep((total + 63) / 64 + 1);
@@ -35,9 +33,11 @@ int main(int argc, char **argv) {
     }
     const bool annotate = std::atoi(argv[6]) != 0;
     rewrite_file(path, argv[3], total, annotate ? nullptr : keep.data(), annotate ? ids.data() : nullptr);
-    rewrite_file_parallel(path, argv[4], total, annotate ? nullptr : keep.data(), annotate ? ids.data() : nullptr, offsets,
+    rewrite_file_parallel(path, argv[4], total, annotate ? nullptr : keep.data(), annotate ? ids.data() : nullptr, map,
                           (unsigned)std::atoi(argv[7]));
-    std::cout << "records " << total << " chunks " << offsets.size() << "\n";
+    size_t gathered = 0;
+    for (uint8_t v : map.chunk_verbatim) gathered += v;
+    std::cout << "records " << total << " chunks " << map.chunk_offset.size() << " gathered " << gathered << "\n";
     return 0;
   }
   if (mode == "old") {

@@ -87,12 +87,24 @@ def test_parallel_rewrite_matches_one_thread(checker, tmp_path, case, annotate):
     path = str(tmp_path / "in.fastq")
     with open(path, "wb") as f:
         f.write(data)
+    gathered = {}
     for threads in (1, 2, 5):
         a, b = str(tmp_path / "one.fastq"), str(tmp_path / f"par{threads}.fastq")
-        subprocess.run([checker, "rewrite", path, a, b, str(threads + 10 * annotate), str(annotate), str(threads)], check=True)
+        p = subprocess.run([checker, "rewrite", path, a, b, str(threads + 10 * annotate), str(annotate), str(threads)], check=True,
+                           capture_output=True, text=True)
         assert open(a, "rb").read() == open(b, "rb").read(), (case, threads)
+        words = p.stdout.split()
+        gathered = dict(chunks=int(words[3]), gathered=int(words[5]))
     if case == "plain" and annotate:
         assert open(a, "rb").read().count(b"\n") == 4 * 300  # every record, with ":id" behind its name
+    # chunks stored exactly as they are written back are gathered by record lengths (no second parse); any other goes
+    # through the parser: all of "plain", none of "crlf", some of the mixed ones
+    if case in ("plain", "long_lines"):
+        assert gathered["gathered"] == gathered["chunks"] > 0
+    if case == "crlf":
+        assert gathered["gathered"] == 0
+    if case in ("mixed_eol", "junk_between", "no_final_newline"):
+        assert gathered["gathered"] < gathered["chunks"]
 
 
 @pytest.mark.parametrize("case", ["plain", "mixed_eol", "empty", "truncated_record"])
