@@ -216,29 +216,60 @@ def fastq_files(ci, R, device="cpu"):
     return cfg, files, d, dt
 
 
+def gzip_copies(files, d):
+    """`<file>.gz` next to every plain FastQ file (gzip -1, the files side by side); made once per box like the files."""
+    out = [f + ".gz" for f in files]
+    marker = os.path.join(d, "files_gz.json")
+    if os.path.exists(marker) and all(os.path.exists(f) for f in out):
+        return out, 0.0
+    t0 = time.monotonic()
+    procs = [subprocess.Popen(["gzip", "-1", "-k", "-f", f]) for f in files]
+    for p in procs:
+        if p.wait() != 0:
+            raise RuntimeError("gzip failed")
+    json.dump({"files": [(f, os.path.getsize(f)) for f in out]}, open(marker, "w"))
+    return out, time.monotonic() - t0
+
+
+def sha_inflated(path):
+    import gzip
+
+    h = hashlib.sha256()
+    with gzip.open(path, "rb") as f:
+        for blk in iter(lambda: f.read(1 << 22), b""):
+            h.update(blk)
+    return h
+
+
 def output_digest(out_dir, names):
-    """sha256 over the deduplicated FastQ files and the four statistics files, in a fixed order."""
+    """sha256 over the deduplicated FastQ files (a .gz by its inflated bytes: the deflate libraries of the two arms
+    differ) and the four statistics files, in a fixed order."""
     h = hashlib.sha256()
     per = {}
     for nm in names:
         p = os.path.join(out_dir, nm)
-        hh = sha_file(p)
+        hh = sha_inflated(p) if nm.endswith(".gz") else sha_file(p)
         per[nm] = hh.hexdigest()[:16]
         h.update(hh.digest())
     return h.hexdigest(), per
 
 
-def cli_leg(kind, ci, R, device="cpu", reps=1):
-    """One whole-program run (`kind` = "humid_b200" | "reference") of configs[ci] at R tuples."""
+def cli_leg(kind, ci, R, device="cpu", reps=1, gz=False):
+    """One whole-program run (`kind` = "humid_b200" | "reference") of configs[ci] at R tuples; gz: the same FastQ as
+    .gz files in, .gz files out."""
     import oracle
 
     cfg, files, d, gen_s = fastq_files(ci, R, device)
+    plain_bytes = sum(os.path.getsize(f) for f in files)
+    if gz:
+        files, gz_s = gzip_copies(files, d)
+        gen_s += gz_s
     size = sum(os.path.getsize(f) for f in files)
     out_names = [os.path.basename(f).replace(".fastq", "_dedup.fastq") for f in files]
     out_names += ["stats.dat", "counts.dat", "neigh.dat", "clusters.dat"]
     flags = cfg.cli_flags()
     times, breakdown = [], {}
-    out = os.path.join(d, "out_" + kind)
+    out = os.path.join(d, "out_" + kind + ("_gz" if gz else ""))
     for rep in range(reps):
         shutil.rmtree(out, ignore_errors=True)
         if kind == "reference":
@@ -271,13 +302,15 @@ def cli_leg(kind, ci, R, device="cpu", reps=1):
     sec, breakdown = times[len(times) // 2]
     digest, per = output_digest(out, out_names)
     shutil.rmtree(out, ignore_errors=True)
-    leg = {"config": cfg.name, "flags": " ".join(flags + ["-s"]), "tuples": R, "fastq_bytes": size, "seconds": round(sec, 3),
+    leg = {"config": cfg.name, "input": "gzip -1 files in, .gz files out" if gz else "plain FastQ files",
+           "flags": " ".join(flags + ["-s"]), "tuples": R, "fastq_bytes": plain_bytes, "input_bytes": size, "seconds": round(sec, 3),
            "runs": len(times), "pairs_per_s": R / sec, "breakdown_s": breakdown, "outputs_sha256": digest,
            "outputs": per, "fastq_generated_s": round(gen_s, 1)}
     # the other arm's digest of the same job, if it ran on this box before: the outputs must agree byte for byte
-    note = os.path.join(d, "digest_" + kind + ".json")
+    tag = "_gz" if gz else ""
+    note = os.path.join(d, "digest_" + kind + tag + ".json")
     json.dump({"outputs_sha256": digest}, open(note, "w"))
-    other = os.path.join(d, "digest_" + ("humid_b200" if kind == "reference" else "reference") + ".json")
+    other = os.path.join(d, "digest_" + ("humid_b200" if kind == "reference" else "reference") + tag + ".json")
     if os.path.exists(other):
         try:
             leg["identical_to_other_arm"] = json.load(open(other))["outputs_sha256"] == digest
@@ -293,6 +326,11 @@ def cli_legs(kind, args, device="cpu"):
         if R <= 0:
             continue
         legs.append(cli_leg(kind, ci, R, device, reps=1 if kind == "reference" else 3))
+    # configs[0] once more with compressed files on both sides: the usual way FastQ is stored; the reference reads it
+    # through isa-l and writes through libdeflate, this repo through host/inflate_parallel.h and zlib
+    R = int(CLI_LEGS[0][1] * args.cli_scale)
+    if R > 0 and shutil.which("gzip"):
+        legs.append(cli_leg(kind, CLI_LEGS[0][0], R, device, reps=1 if kind == "reference" else 3, gz=True))
     return legs
 
 
