@@ -40,7 +40,7 @@ struct Record {
 
 class FastqReader {
  public:
-  explicit FastqReader(const std::string &path) : path_(path), buf_(1u << 23) {
+  explicit FastqReader(const std::string &path, size_t buffer_bytes = 1u << 23) : path_(path), buf_(buffer_bytes) {
     if (ends_with(path, ".gz")) {
       gz_ = gzopen(path.c_str(), "rb");
       if (!gz_) error_exit("Failed to open file: " + path);

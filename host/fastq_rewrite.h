@@ -283,15 +283,22 @@ inline void rewrite_file_parallel(const std::string &in_path, const std::string 
       const uint64_t t0 = c * REWRITE_CHUNK, t1 = std::min(total, t0 + REWRITE_CHUNK);
       buf.clear();
       if (gather && map.chunk_verbatim[c]) {
-        size_t bytes = 0;
-        for (uint64_t t = t0; t < t1; t++) bytes += map.raw_length[t];
-        raw.resize(bytes);
-        for (size_t done = 0; done < bytes;) {
-          const ssize_t got = pread(fd, raw.data() + done, bytes - done, (off_t)(offsets[c] + done));
-          if (got <= 0) error_exit("Failed to read: " + in_path);
-          done += (size_t)got;
+        // about 1 MiB of records at a time: read and gathered while they are still in the cache
+        uint64_t at = offsets[c];
+        for (uint64_t t = t0; t < t1;) {
+          size_t bytes = 0;
+          uint64_t upto = t;
+          while (upto < t1 && bytes < (1u << 20)) bytes += map.raw_length[upto++];
+          if (raw.size() < bytes) raw.resize(bytes);
+          for (size_t done = 0; done < bytes;) {
+            const ssize_t got = pread(fd, raw.data() + done, bytes - done, (off_t)(at + done));
+            if (got <= 0) error_exit("Failed to read: " + in_path);
+            done += (size_t)got;
+          }
+          gather_records(raw.data(), map.raw_length.data() + t, t, upto, keep, ids, buf);
+          at += bytes;
+          t = upto;
         }
-        gather_records(raw.data(), map.raw_length.data() + t0, t0, t1, keep, ids, buf);
       } else {
         BlockReader reader(in_path, 4u << 20, offsets[c]);
         for (uint64_t t = t0; t < t1 && reader.read(rec); t++) {

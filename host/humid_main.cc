@@ -141,7 +141,7 @@ Layout pre_compute(const vector<string> &files, size_t word_length) {
   Layout L;
   size_t umi = 0;
   {
-    FastqReader reader(files.front());
+    FastqReader reader(files.front(), 1u << 16);  // one record is all that is read
     Record r;
     if (reader.read(r)) {
       size_t off, len;

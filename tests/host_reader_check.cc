@@ -4,6 +4,8 @@
 #include <cstdlib>
 #include <iostream>
 
+#include <chrono>
+
 #include "../host/fastq_block.h"
 #include "../host/fastq_rewrite.h"
 
@@ -32,9 +34,11 @@ int main(int argc, char **argv) {
       ids[t] = (uint32_t)(x >> 40);
     }
     const bool annotate = std::atoi(argv[6]) != 0;
-    rewrite_file(path, argv[3], total, annotate ? nullptr : keep.data(), annotate ? ids.data() : nullptr);
+    if (std::string(argv[3]) != "-") rewrite_file(path, argv[3], total, annotate ? nullptr : keep.data(), annotate ? ids.data() : nullptr);
+    const auto t0 = std::chrono::steady_clock::now();
     rewrite_file_parallel(path, argv[4], total, annotate ? nullptr : keep.data(), annotate ? ids.data() : nullptr, map,
                           (unsigned)std::atoi(argv[7]));
+    std::cerr << "parallel rewrite " << std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() << " s\n";
     size_t gathered = 0;
     for (uint8_t v : map.chunk_verbatim) gathered += v;
     std::cout << "records " << total << " chunks " << map.chunk_offset.size() << " gathered " << gathered << "\n";
