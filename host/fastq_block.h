@@ -90,6 +90,9 @@ class BlockReader {
   // Byte offset (in the uncompressed data) of the name line of the record read last: a reader started
   // there sees the same records from that one on.
   size_t buffer_bytes() const { return buf_.size(); }
+  // The message of a malformed record goes into *to instead of stderr (a reader that runs ahead of the program's order:
+  // host/ingest_parallel.h prints it when its turn comes).
+  void hold_errors(std::string *to) { held_errors_ = to; }
 
   // Bytes the record read last takes in the file when it is stored exactly as the executable writes records back —
   // four lines, each ended by one '\n', nothing in between (Read::toString, lib/fastp/src/read.cpp:116-118) — else 0.
@@ -114,9 +117,11 @@ class BlockReader {
       if (st == kEnd) return false;
       mark_ = pos;
       if (r.qual.n != r.seq.n) {
-        std::cerr << "ERROR: sequence and quality have different length:\n"
-                  << std::string(r.name.p, r.name.n) << "\n" << std::string(r.seq.p, r.seq.n) << "\n"
-                  << std::string(r.strand.p, r.strand.n) << "\n" << std::string(r.qual.p, r.qual.n) << std::endl;
+        const std::string what = "ERROR: sequence and quality have different length:\n" + std::string(r.name.p, r.name.n) + "\n" +
+                                 std::string(r.seq.p, r.seq.n) + "\n" + std::string(r.strand.p, r.strand.n) + "\n" +
+                                 std::string(r.qual.p, r.qual.n) + "\n";
+        if (held_errors_) *held_errors_ += what;
+        else std::cerr << what << std::flush;
         return false;
       }
       return true;
@@ -224,6 +229,7 @@ class BlockReader {
   bool drained_ = false;       // ... and the parser knows: the last line ends at end_
   gzFile gz_ = nullptr;
   FILE *fp_ = nullptr;
+  std::string *held_errors_ = nullptr;
   std::unique_ptr<BgzfInflater> bgzf_;
   std::unique_ptr<GzFastReader> fast_;
   std::unique_ptr<ParallelGzReader> parallel_;

@@ -49,14 +49,16 @@ struct RecordMap {
   uint64_t expect_ = 0;
   // record t (0, 1, 2 ... in order) has just been read
   void note(uint64_t t, const BlockReader &reader, const RecordView &rec) {
-    const uint64_t at = reader.offset_of(rec);
+    note_values(t, reader.offset_of(rec), lengths ? reader.raw_length(rec) : 0);
+  }
+  // the same from what a parser thread kept: offset of the name line, BlockReader::raw_length
+  void note_values(uint64_t t, uint64_t at, size_t len) {
     if (t % REWRITE_CHUNK == 0) {
       chunk_offset.push_back(at);
       if (lengths) chunk_verbatim.push_back(1);
       expect_ = at;
     }
     if (!lengths) return;
-    const size_t len = reader.raw_length(rec);
     if (len == 0 || len > 0xFFFFu || at != expect_) chunk_verbatim.back() = 0;
     raw_length.push_back((uint16_t)len);
     expect_ = at + len;

@@ -11,9 +11,9 @@
 // steps here: if the library reports an error the program prints it and exits like the
 // reference's error_exit does.
 //
-// Ingest: one thread per input file parses its FastQ in blocks
-// (host/fastq_block.h) and writes its share of every word straight into a page-locked batch
-// buffer; the main thread hands full batches to humid_gpu_add_batch, which uploads them while the
+// Ingest: every input file is parsed in blocks (host/fastq_block.h) — a compressed one by
+// one thread behind its inflate threads, a plain one by several threads side by side (host/ingest_parallel.h) — and
+// its share of every word goes straight into a page-locked batch buffer; the main thread hands full batches to humid_gpu_add_batch, which uploads them while the
 // next batch is being parsed and the previous one is counted on the device.  The output passes
 // (host/fastq_rewrite.h) do not parse plain files again: ingest notes where every record
 // lies, and several threads per file gather the kept ones by pread.  Compressed inputs are inflated a second
@@ -35,6 +35,7 @@
 #include "fastq_block.h"
 #include "fastq_io.h"
 #include "fastq_rewrite.h"
+#include "ingest_parallel.h"
 
 using namespace humid_host;
 using std::string;
@@ -227,6 +228,77 @@ void ingest_file(Ingest &g, const string &path, size_t file) {
   }
 }
 
+// The same for a plain file with several parser threads (host/ingest_parallel.h): the threads keep this file's letters
+// of every record, the commit — in record order — puts them into the batch buffers.
+// row: [take letters, 'N'-padded][u16 letters present] (+ [header UMI letters][u16 present] for file 0)
+void ingest_file_parallel(Ingest &g, const string &path, size_t file, unsigned n_threads) {
+  const size_t seg = g.L.header_umi ? file + 1 : file;
+  const size_t take = g.L.nt_to_take[file], off = g.seg_off[seg];
+  const size_t umi = file == 0 ? g.L.header_umi : 0;
+  const size_t row_bytes = take + 2 + (umi ? umi + 2 : 0);
+  auto put = [](uint8_t *dst, const char *p, size_t have, size_t want) {
+    const size_t c = have < want ? have : want;
+    std::memcpy(dst, p, c);
+    std::memset(dst + c, 'N', want - c);
+    const uint16_t n = (uint16_t)c;
+    std::memcpy(dst + want, &n, 2);
+  };
+  ParallelPlainParser parser(path, row_bytes, [&](const RecordView &rec, uint8_t *row) {
+    put(row, rec.seq.p, rec.seq.n, take);
+    if (umi) {
+      size_t uo, ul;
+      extract_umi(rec.name.p, rec.name.n, uo, ul);
+      put(row + take + 2, rec.name.p + uo, ul, umi);
+    }
+  });
+  Slot *slot = nullptr;
+  uint64_t in_slot = 0, batch = 0;
+  auto acquire = [&]() {  // the buffer of batch `batch`; false: the tuple stream has ended
+    Slot &s = g.slots[batch % N_SLOTS];
+    std::unique_lock<std::mutex> lk(g.mu);
+    g.cv.wait(lk, [&] { return g.stop || s.batch == batch; });
+    if (g.stop) return false;
+    slot = &s;
+    return true;
+  };
+  auto publish = [&]() {
+    std::lock_guard<std::mutex> lk(g.mu);
+    slot->rows[file] = in_slot;
+    slot->done++;
+    g.cv.notify_all();
+    slot = nullptr;
+    in_slot = 0;
+    batch++;
+  };
+  const uint64_t n = parser.run(n_threads, [&](uint64_t t, const uint8_t *row, uint64_t at, uint32_t stored) {
+    if (!slot && !acquire()) return false;
+    uint8_t *chars = slot->chars + in_slot * g.n;
+    uint16_t *sl = slot->seg_len + in_slot * g.S;
+    std::memcpy(chars + off, row, take);
+    std::memcpy(&sl[seg], row + take, 2);
+    if (umi) {
+      std::memcpy(chars, row + take + 2, umi);
+      std::memcpy(&sl[0], row + take + 2 + umi, 2);
+    }
+    g.maps[file].note_values(t, at, stored);
+    if (++in_slot == BATCH) publish();
+    return true;
+  });
+  (void)n;
+  // the file's last batch: short, or empty if the file ended on a batch boundary (what tells the main thread)
+  if (slot || acquire()) publish();
+  if (std::getenv("HUMID_TIMING"))
+    std::cerr << "ingest " << path << ": " << parser.ranges() << " ranges, " << parser.reparsed_ranges() << " parsed again\n";
+}
+
+// Parser threads per plain input file (HUMID_INGEST_THREADS overrides; 1 = one block reader per file).
+unsigned ingest_threads(size_t n_files) {
+  if (const char *e = std::getenv("HUMID_INGEST_THREADS")) return (unsigned)std::max(1, std::atoi(e));
+  const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+  const unsigned per_file = hw / (unsigned)n_files;
+  return per_file > 2 ? std::min(6u, per_file - 1) : 1u;
+}
+
 // Capacity hint for the word table (lets the device count batches while the next one uploads): size
 // of the first file / size of its first record, for plain files.  A wrong guess only costs a recount
 // (too small) or memory (too large), never the result.
@@ -366,7 +438,14 @@ int main(int argc, char **argv) {
       g.slots[j].rows.assign(F, 0);
     }
     vector<std::thread> readers;
-    for (size_t i = 0; i < F; i++) readers.emplace_back(ingest_file, std::ref(g), opt.files[i], i);
+    const unsigned parsers = ingest_threads(F);
+    for (size_t i = 0; i < F; i++) {
+      struct stat st;
+      const bool big_plain = !ends_with(opt.files[i], ".gz") && stat(opt.files[i].c_str(), &st) == 0 && S_ISREG(st.st_mode) &&
+                             (uint64_t)st.st_size >= 2 * ParallelPlainParser::range_size();
+      if (parsers > 1 && big_plain) readers.emplace_back(ingest_file_parallel, std::ref(g), opt.files[i], i, parsers);
+      else readers.emplace_back(ingest_file, std::ref(g), opt.files[i], i);
+    }
     for (uint64_t k = 0;; k++) {
       Slot &s = g.slots[k % N_SLOTS];
       {
@@ -484,5 +563,11 @@ int main(int argc, char **argv) {
   if (std::getenv("HUMID_TIMING"))
     std::cerr << "humid_gpu_destroy: "
               << std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - phase_start).count() << " ms\n";
+  // Every output file and the log are closed, the handles are destroyed.  What is left is the CUDA runtime's own
+  // teardown at exit (its context, the page-locked batch buffers): ~0.1 s that a finished program does not need —
+  // the driver releases everything with the process.  HUMID_FULL_EXIT=1 returns normally (sanitizer / leak checks).
+  std::cout.flush();
+  std::cerr.flush();
+  if (!std::getenv("HUMID_FULL_EXIT")) std::_Exit(0);
   return 0;
 }

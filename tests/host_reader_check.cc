@@ -2,12 +2,14 @@
 // line-by-line reader (mode "old", host/fastq_io.h) or by the block reader (mode "block <bytes>",
 // host/fastq_block.h), one field per line, so that the two can be compared byte for byte.
 #include <cstdlib>
+#include <cstring>
 #include <iostream>
 
 #include <chrono>
 
 #include "../host/fastq_block.h"
 #include "../host/fastq_rewrite.h"
+#include "../host/ingest_parallel.h"
 
 using namespace humid_host;
 
@@ -42,6 +44,38 @@ int main(int argc, char **argv) {
     size_t gathered = 0;
     for (uint8_t v : map.chunk_verbatim) gathered += v;
     std::cout << "records " << total << " chunks " << map.chunk_offset.size() << " gathered " << gathered << "\n";
+    return 0;
+  }
+  if (mode == "hash_seq" || mode == "hash_par") {  // hash_seq <in> | hash_par <in> <threads>: one line per record
+    auto fnv = [](const Span &s) {
+      uint32_t h = 2166136261u;
+      for (size_t i = 0; i < s.n; i++) h = (h ^ (uint8_t)s.p[i]) * 16777619u;
+      return h;
+    };
+    auto extract = [&](const RecordView &r, uint8_t *row) {
+      const uint32_t h[4] = {fnv(r.name), fnv(r.seq), fnv(r.strand), fnv(r.qual)};
+      std::memcpy(row, h, 16);
+    };
+    auto print = [&](uint64_t t, const uint8_t *row, uint64_t at, uint32_t stored) {
+      uint32_t h[4];
+      std::memcpy(h, row, 16);
+      std::cout << t << " @" << at << " +" << stored << " " << h[0] << " " << h[1] << " " << h[2] << " " << h[3] << "\n";
+      return true;
+    };
+    if (mode == "hash_seq") {
+      BlockReader reader(path);
+      RecordView r;
+      uint8_t row[16];
+      while (reader.read(r)) {
+        extract(r, row);
+        print(n++, row, reader.offset_of(r), (uint32_t)reader.raw_length(r));
+      }
+    } else {
+      ParallelPlainParser parser(path, 16, extract);
+      n = parser.run((unsigned)std::atoi(argv[3]), print);
+      std::cerr << "ranges " << parser.ranges() << " reparsed " << parser.reparsed_ranges() << "\n";
+    }
+    std::cout << "records " << n << "\n";
     return 0;
   }
   if (mode == "old") {

@@ -43,8 +43,11 @@ def test_host_side_with_many_inflate_and_writer_threads(tmp_path, humid_cpu, mon
     cfg = baseline_config(1, 150_000)
     files = list(Synth(cfg).write_fastq(str(tmp_path / "in"), prefix="x", gzip_output=False))
     outs = {}
-    for kind in ("plain", "bgzf", "gz"):
+    for kind in ("plain", "bgzf", "gz", "plain_parallel"):
         use = files
+        if kind == "plain_parallel":  # 4 parser threads per file, ranges of 64 KiB
+            monkeypatch.setenv("HUMID_INGEST_THREADS", "4")
+            monkeypatch.setenv("HUMID_INGEST_RANGE", "65536")
         if kind == "gz":  # ordinary one-member files, 3 threads on each (host/inflate_parallel.h), spans of 16 KiB
             import gzip
             use = []
@@ -74,6 +77,7 @@ def test_host_side_with_many_inflate_and_writer_threads(tmp_path, humid_cpu, mon
     for f in outs["plain"]:
         assert outs["plain"][f] == outs["bgzf"][f], f
         assert outs["plain"][f] == outs["gz"][f], f
+        assert outs["plain"][f] == outs["plain_parallel"][f], f
     dedup = [f for f in outs["plain"] if "_dedup" in f][0]
     assert 0 < outs["plain"][dedup].count(b"\n") // 4 < 150_000
 
@@ -82,9 +86,12 @@ ODD_INPUTS = ["crlf", "mixed_eol", "junk_between", "no_final_newline", "truncate
               "only_newlines", "empty"]
 
 
+PARALLEL_INGEST = dict(HUMID_INGEST_THREADS="3", HUMID_INGEST_RANGE="300")  # host/ingest_parallel.h on these small files
+
+
 @pytest.mark.skipif(not oracle.have_ref(), reason="reference binary not built on this machine")
 @pytest.mark.parametrize("case", ODD_INPUTS)
-@pytest.mark.parametrize("gz", [False, True], ids=["plain", "gz"])
+@pytest.mark.parametrize("gz", [False, True, "parallel"], ids=["plain", "gz", "plain_parallel_ingest"])
 def test_odd_fastq_files_like_the_reference_binary(tmp_path, humid_cpu, case, gz):
     """Line endings, junk between records, truncated and malformed records (the inputs of tests/test_host_reader.py), two
     files each, through both executables: same exit status, same output files."""
@@ -93,6 +100,8 @@ def test_odd_fastq_files_like_the_reference_binary(tmp_path, humid_cpu, case, gz
     import numpy as np
     from test_host_reader import CASES
 
+    env = dict(os.environ, **PARALLEL_INGEST) if gz == "parallel" else None
+    gz = gz is True
     files = []
     for i in range(2):
         data = CASES[case](np.random.default_rng(len(case) + 7))  # both files hold the same records
@@ -104,7 +113,7 @@ def test_odd_fastq_files_like_the_reference_binary(tmp_path, humid_cpu, case, gz
     ours, ref = str(tmp_path / "ours"), str(tmp_path / "ref")
     os.makedirs(ref)
     a = subprocess.run([humid_cpu, *flags, "-s", "-a", "-d", ours, "-l", str(tmp_path / "ours.log"), *files],
-                       capture_output=True, timeout=300)
+                       capture_output=True, timeout=300, env=env)
     b = subprocess.run([oracle.REF_HUMID, *flags, "-s", "-a", "-d", ref, "-l", os.path.join(ref, "humid.log"), *files],
                        capture_output=True, timeout=300)
     if b.returncode < 0:  # the reference dies of a signal on inputs without any record (SIGSEGV in preCompute's first
@@ -136,7 +145,8 @@ LAYOUTS = [  # (name, records per file, drop the first record (so that the first
 
 @pytest.mark.skipif(not oracle.have_ref(), reason="reference binary not built on this machine")
 @pytest.mark.parametrize("name,counts,drop_first,flags", LAYOUTS, ids=[c[0] for c in LAYOUTS])
-def test_word_layouts_like_the_reference_binary(tmp_path, humid_cpu, name, counts, drop_first, flags):
+@pytest.mark.parametrize("ingest", ["one_thread_per_file", "parallel_ingest"])
+def test_word_layouts_like_the_reference_binary(tmp_path, humid_cpu, name, counts, drop_first, flags, ingest):
     """preCompute's split of the word over header UMI and files (remainder to the last file), header UMI found or
     not, files of different lengths (the tuple stream ends with the shortest), reads shorter than their share and
     reads with N (filtered): every output file as the reference binary writes it."""
@@ -152,7 +162,12 @@ def test_word_layouts_like_the_reference_binary(tmp_path, humid_cpu, name, count
         files.append(f)
     ours, ref = str(tmp_path / "ours"), str(tmp_path / "ref")
     os.makedirs(ref)
-    subprocess.run([humid_cpu, *flags, "-s", "-a", "-d", ours, "-l", str(tmp_path / "ours.log"), *files], check=True, timeout=300)
+    env = dict(os.environ, **PARALLEL_INGEST, HUMID_TIMING="1") if ingest == "parallel_ingest" else None
+    p = subprocess.run([humid_cpu, *flags, "-s", "-a", "-d", ours, "-l", str(tmp_path / "ours.log"), *files], check=True, timeout=300,
+                       env=env, capture_output=True, text=True)
+    if env:  # every file went through the parser pool, in many ranges
+        lines = [l for l in p.stderr.splitlines() if l.startswith("ingest ")]
+        assert len(lines) == len(files) and all(int(l.split(": ")[1].split()[0]) > 10 for l in lines), p.stderr[-1500:]
     subprocess.run([oracle.REF_HUMID, *flags, "-s", "-a", "-d", ref, "-l", os.path.join(ref, "humid.log"), *files], check=True,
                    timeout=300)
     names = sorted(os.listdir(ref))

@@ -208,3 +208,24 @@ def test_bgzf_member_claiming_more_than_64k_is_not_bgzf(checker, tmp_path):
     env = dict(os.environ, HUMID_INFLATE_THREADS="3")
     got = subprocess.run([checker, "block", path, "4096"], capture_output=True, env=env)
     assert got.returncode != 0 and b"decompressing" in got.stderr
+
+
+@pytest.mark.parametrize("case", sorted(CASES))
+def test_parallel_parser_matches_the_sequential_one(checker, tmp_path, case):
+    """host/ingest_parallel.h (several threads on one plain file: guessed record starts, commit in file order) gives the
+    records of the sequential block reader — same order, offsets, stored lengths, fields — whatever the range size, for
+    every odd input; the message of a malformed record appears exactly when the sequential reader prints it."""
+    data = CASES[case](np.random.default_rng(len(case) + 7))
+    if case in ("plain", "crlf", "junk_between"):
+        data = data * 5
+    path = str(tmp_path / "in.fastq")
+    with open(path, "wb") as f:
+        f.write(data)
+    ref = subprocess.run([checker, "hash_seq", path], capture_output=True, check=True)
+    for rng_bytes, threads in ((64, 3), (333, 2), (4096, 5), (1 << 25, 2)):
+        got = subprocess.run([checker, "hash_par", path, str(threads)], capture_output=True, check=True,
+                             env=dict(os.environ, HUMID_INGEST_RANGE=str(rng_bytes)))
+        assert got.stdout == ref.stdout, (case, rng_bytes)
+        assert (b"different length" in got.stderr) == (b"different length" in ref.stderr), (case, rng_bytes)
+        if case == "plain" and rng_bytes == 4096:  # well-formed text: every guess is right
+            assert b" reparsed 0" in got.stderr and b"ranges 1 " not in got.stderr, got.stderr
