@@ -12,6 +12,10 @@
 //   * a record whose sequence and quality lengths differ is reported on stderr and ends the input;
 //   * missing lines at the end of the data read as empty.
 #pragma once
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
 #include <zlib.h>
 
 #include <cstdint>
@@ -60,7 +64,15 @@ class BlockReader {
   // inflate_threads > 1: a .gz that is BGZF is inflated by that many threads (host/bgzf.h)
   explicit BlockReader(const std::string &path, size_t block = 16u << 20, uint64_t start = 0,
                        unsigned inflate_threads = default_inflate_threads())
-      : path_(path), buf_(block), base_(start) {
+      : path_(path), base_(start) {
+    // a plain file is parsed where the page cache holds it (no copy into a buffer); small blocks — the tests' way of
+    // making every line cross a buffer end — and HUMID_NO_MMAP=1 keep the buffered reads
+    if (!ends_with(path, ".gz") && block >= (1u << 20) && !std::getenv("HUMID_NO_MMAP") && map_file(path)) {
+      mark_ = (size_t)std::min<uint64_t>(start, end_);
+      base_ = 0;
+      return;
+    }
+    buf_.resize(block);
     if (ends_with(path, ".gz") && inflate_threads > 1 && !start && is_bgzf(path)) {
       bgzf_.reset(new BgzfInflater(path, inflate_threads));
     } else if (ends_with(path, ".gz") && !zlib_inflate_wanted()) {
@@ -80,9 +92,17 @@ class BlockReader {
       if (start && fseeko(fp_, (off_t)start, SEEK_SET) != 0) error_exit("Failed to seek in file: " + path);
     }
   }
+  // Over bytes that are in memory already ([mem, mem + size): e.g. a mapping shared by several readers); `start` as above.
+  BlockReader(const char *mem, size_t size, uint64_t start, const std::string &path) : path_(path) {
+    view_ = mem;
+    end_ = size;
+    mark_ = (size_t)std::min<uint64_t>(start, size);
+    finished_ = drained_ = true;
+  }
   ~BlockReader() {
     if (gz_) gzclose(gz_);
     if (fp_) std::fclose(fp_);
+    if (map_) munmap(map_, map_size_);
   }
   BlockReader(const BlockReader &) = delete;
   BlockReader &operator=(const BlockReader &) = delete;
@@ -90,6 +110,7 @@ class BlockReader {
   // Byte offset (in the uncompressed data) of the name line of the record read last: a reader started
   // there sees the same records from that one on.
   size_t buffer_bytes() const { return buf_.size(); }
+  bool mapped() const { return view_ != nullptr; }
   // The message of a malformed record goes into *to instead of stderr (a reader that runs ahead of the program's order:
   // host/ingest_parallel.h prints it when its turn comes).
   void hold_errors(std::string *to) { held_errors_ = to; }
@@ -97,13 +118,13 @@ class BlockReader {
   // Bytes the record read last takes in the file when it is stored exactly as the executable writes records back —
   // four lines, each ended by one '\n', nothing in between (Read::toString, lib/fastp/src/read.cpp:116-118) — else 0.
   size_t raw_length(const RecordView &r) const {
-    const char *e = buf_.data() + end_;
+    const char *e = data() + end_;
     auto ended = [&](const Span &s) { return s.p + s.n < e && s.p[s.n] == '\n'; };
     if (!ended(r.name) || !ended(r.seq) || !ended(r.strand) || !ended(r.qual)) return 0;
     if (r.seq.p != r.name.p + r.name.n + 1 || r.strand.p != r.seq.p + r.seq.n + 1 || r.qual.p != r.strand.p + r.strand.n + 1) return 0;
     return (size_t)(r.qual.p + r.qual.n + 1 - r.name.p);
   }
-  uint64_t offset_of(const RecordView &r) const { return base_ + (uint64_t)(r.name.p - buf_.data()); }
+  uint64_t offset_of(const RecordView &r) const { return base_ + (uint64_t)(r.name.p - data()); }
 
   // false at end of input (or at a malformed record).  The views stay valid until the next call.
   bool read(RecordView &r) {
@@ -133,12 +154,12 @@ class BlockReader {
 
   // One line starting at pos.  kNeedMore: nothing in the buffer ends it and the file has more.
   int line(size_t &pos, Span &s) {
-    const char *b = buf_.data() + pos;
+    const char *b = data() + pos;
     const size_t avail = end_ - pos;
     // [nl_free_from_, nl_free_to_) is known to hold no '\n' (a file with '\r' line ends only would otherwise be
     // searched to the end of the buffer once per line)
     const size_t from = (pos >= nl_free_from_ && pos < nl_free_to_) ? nl_free_to_ : pos;
-    const char *nl = from < end_ ? (const char *)std::memchr(buf_.data() + from, '\n', end_ - from) : nullptr;
+    const char *nl = from < end_ ? (const char *)std::memchr(data() + from, '\n', end_ - from) : nullptr;
     if (!nl) {
       if (from == pos) nl_free_from_ = pos;
       nl_free_to_ = end_;
@@ -220,7 +241,33 @@ class BlockReader {
     return true;
   }
 
+  const char *data() const { return view_ ? view_ : buf_.data(); }
+
+  // The whole file mapped read-only; false: not a regular file / empty / mmap refused (the caller reads it in blocks).
+  bool map_file(const std::string &path) {
+    const int fd = open(path.c_str(), O_RDONLY);
+    if (fd < 0) error_exit("Failed to open file: " + path);
+    struct stat st;
+    if (fstat(fd, &st) != 0 || !S_ISREG(st.st_mode) || st.st_size <= 0) {
+      close(fd);
+      return false;
+    }
+    void *p = mmap(nullptr, (size_t)st.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+    close(fd);
+    if (p == MAP_FAILED) return false;
+    madvise(p, (size_t)st.st_size, MADV_SEQUENTIAL);
+    map_ = p;
+    map_size_ = (size_t)st.st_size;
+    view_ = static_cast<const char *>(p);
+    end_ = map_size_;
+    finished_ = drained_ = true;
+    return true;
+  }
+
   std::string path_;
+  const char *view_ = nullptr;  // the data when it is not in buf_: the mapping, or the caller's memory
+  void *map_ = nullptr;
+  size_t map_size_ = 0;
   std::vector<char> buf_;
   uint64_t base_ = 0;          // offset of buf_[0] in the (uncompressed) data
   size_t mark_ = 0, end_ = 0;  // [mark_, end_) = bytes not yet handed out

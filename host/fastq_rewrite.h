@@ -20,6 +20,8 @@
 // side at the reference's level 4 — the inflated bytes are those of the one-thread pass.
 #pragma once
 #include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
 #include <unistd.h>
 
 #include <zlib.h>
@@ -271,9 +273,19 @@ inline void rewrite_file_parallel(const std::string &in_path, const std::string 
   OrderedOutput out(out_path);
   std::atomic<uint64_t> next{0};
   int fd = -1;
+  const char *mapped = nullptr;  // the records are gathered out of the page cache when the file can be mapped
+  size_t mapped_bytes = 0;
   if (gather) {
     fd = open(in_path.c_str(), O_RDONLY);
     if (fd < 0) error_exit("Failed to open file: " + in_path);
+    struct stat st;
+    if (fstat(fd, &st) == 0 && S_ISREG(st.st_mode) && st.st_size > 0 && !std::getenv("HUMID_NO_MMAP")) {
+      void *p = mmap(nullptr, (size_t)st.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+      if (p != MAP_FAILED) {
+        mapped = static_cast<const char *>(p);
+        mapped_bytes = (size_t)st.st_size;
+      }
+    }
   }
   auto worker = [&] {
     std::string buf, scratch;
@@ -291,13 +303,17 @@ inline void rewrite_file_parallel(const std::string &in_path, const std::string 
           size_t bytes = 0;
           uint64_t upto = t;
           while (upto < t1 && bytes < (1u << 20)) bytes += map.raw_length[upto++];
-          if (raw.size() < bytes) raw.resize(bytes);
-          for (size_t done = 0; done < bytes;) {
-            const ssize_t got = pread(fd, raw.data() + done, bytes - done, (off_t)(at + done));
-            if (got <= 0) error_exit("Failed to read: " + in_path);
-            done += (size_t)got;
+          const char *text = mapped + at;
+          if (!mapped || at + bytes > mapped_bytes) {
+            if (raw.size() < bytes) raw.resize(bytes);
+            for (size_t done = 0; done < bytes;) {
+              const ssize_t got = pread(fd, raw.data() + done, bytes - done, (off_t)(at + done));
+              if (got <= 0) error_exit("Failed to read: " + in_path);
+              done += (size_t)got;
+            }
+            text = raw.data();
           }
-          gather_records(raw.data(), map.raw_length.data() + t, t, upto, keep, ids, buf);
+          gather_records(text, map.raw_length.data() + t, t, upto, keep, ids, buf);
           at += bytes;
           t = upto;
         }
@@ -314,6 +330,7 @@ inline void rewrite_file_parallel(const std::string &in_path, const std::string 
   std::vector<std::thread> pool;
   for (unsigned i = 0; i < std::max(1u, n_threads); i++) pool.emplace_back(worker);
   for (std::thread &t : pool) t.join();
+  if (mapped) munmap(const_cast<char *>(mapped), mapped_bytes);
   if (fd >= 0) close(fd);
   out.finish();
 }

@@ -17,11 +17,14 @@
 // end it, and its message is printed when — and only if — the commit reaches it.
 #pragma once
 #include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
 #include <unistd.h>
 
 #include <atomic>
 #include <condition_variable>
 #include <functional>
+#include <memory>
 #include <mutex>
 #include <thread>
 
@@ -48,13 +51,24 @@ class ParallelPlainParser {
 
   ParallelPlainParser(const std::string &path, size_t row_bytes, Extract extract, uint64_t range_bytes = range_size())
       : path_(path), row_bytes_(row_bytes), extract_(std::move(extract)), range_(range_bytes) {
-    FILE *fp = std::fopen(path.c_str(), "rb");
-    if (!fp) error_exit("Failed to open file: " + path);
-    fseeko(fp, 0, SEEK_END);
-    size_ = (uint64_t)ftello(fp);
-    std::fclose(fp);
+    const int fd = open(path.c_str(), O_RDONLY);
+    if (fd < 0) error_exit("Failed to open file: " + path);
+    struct stat st;
+    if (fstat(fd, &st) != 0) error_exit("Failed to open file: " + path);
+    size_ = (uint64_t)st.st_size;
+    // one read-only mapping for all the pool's readers: the file is parsed where the page cache holds it
+    if (S_ISREG(st.st_mode) && size_ > 0 && !std::getenv("HUMID_NO_MMAP")) {
+      void *p = mmap(nullptr, (size_t)size_, PROT_READ, MAP_PRIVATE, fd, 0);
+      if (p != MAP_FAILED) map_ = static_cast<const char *>(p);
+    }
+    close(fd);
     n_ranges_ = std::max<uint64_t>(1, (size_ + range_ - 1) / range_);
   }
+  ~ParallelPlainParser() {
+    if (map_) munmap(const_cast<char *>(map_), (size_t)size_);
+  }
+  ParallelPlainParser(const ParallelPlainParser &) = delete;
+  ParallelPlainParser &operator=(const ParallelPlainParser &) = delete;
   // HUMID_INGEST_RANGE: bytes per range (the tests use small ones)
   static uint64_t range_size() {
     const char *e = std::getenv("HUMID_INGEST_RANGE");
@@ -77,13 +91,22 @@ class ParallelPlainParser {
   uint64_t guess_start(uint64_t from) const {
     if (from == 0) return 0;
     constexpr size_t kLook = 1u << 20;
-    std::vector<char> w(kLook + 1);
-    const int fd = open(path_.c_str(), O_RDONLY);
-    if (fd < 0) return kNone;
-    const ssize_t got = pread(fd, w.data(), kLook + 1, (off_t)(from - 1));  // one byte earlier: is `from` a line start?
-    close(fd);
+    std::vector<char> w;
+    const char *b;
+    ssize_t got;
+    if (map_) {  // one byte earlier: is `from` a line start?
+      b = map_ + from - 1;
+      got = (ssize_t)std::min<uint64_t>(kLook + 1, size_ - (from - 1));
+    } else {
+      w.resize(kLook + 1);
+      const int fd = open(path_.c_str(), O_RDONLY);
+      if (fd < 0) return kNone;
+      got = pread(fd, w.data(), kLook + 1, (off_t)(from - 1));
+      close(fd);
+      b = w.data();
+    }
     if (got <= 1) return kNone;
-    const char *b = w.data(), *e = b + got;
+    const char *e = b + got;
     const char *line = b + 1;  // == from, if the byte in front of it ends a line
     if (b[0] != '\n') {
       const char *nl = (const char *)std::memchr(b + 1, '\n', (size_t)(e - b - 1));
@@ -109,7 +132,8 @@ class ParallelPlainParser {
     r.stored.clear();
     r.error.clear();
     if (entered == kNone || entered >= size_) return;
-    BlockReader reader(path_, 4u << 20, entered);
+    std::unique_ptr<BlockReader> own(map_ ? new BlockReader(map_, (size_t)size_, entered, path_) : new BlockReader(path_, 4u << 20, entered));
+    BlockReader &reader = *own;
     reader.hold_errors(&r.error);
     RecordView rec;
     while (reader.read(rec)) {
@@ -173,6 +197,7 @@ class ParallelPlainParser {
   size_t row_bytes_;
   Extract extract_;
   uint64_t range_, size_ = 0, n_ranges_ = 0;
+  const char *map_ = nullptr;
   std::mutex mu_;
   std::condition_variable cv_;
   uint64_t next_range_ = 0, turn_ = 0;

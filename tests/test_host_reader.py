@@ -90,8 +90,9 @@ def test_parallel_rewrite_matches_one_thread(checker, tmp_path, case, annotate):
     gathered = {}
     for threads in (1, 2, 5):
         a, b = str(tmp_path / "one.fastq"), str(tmp_path / f"par{threads}.fastq")
+        env = dict(os.environ, HUMID_NO_MMAP="1") if threads == 2 else None  # (gathered with pread instead of from a mapping)
         p = subprocess.run([checker, "rewrite", path, a, b, str(threads + 10 * annotate), str(annotate), str(threads)], check=True,
-                           capture_output=True, text=True)
+                           capture_output=True, text=True, env=env)
         assert open(a, "rb").read() == open(b, "rb").read(), (case, threads)
         words = p.stdout.split()
         gathered = dict(chunks=int(words[3]), gathered=int(words[5]))
@@ -222,9 +223,11 @@ def test_parallel_parser_matches_the_sequential_one(checker, tmp_path, case):
     with open(path, "wb") as f:
         f.write(data)
     ref = subprocess.run([checker, "hash_seq", path], capture_output=True, check=True)
-    for rng_bytes, threads in ((64, 3), (333, 2), (4096, 5), (1 << 25, 2)):
-        got = subprocess.run([checker, "hash_par", path, str(threads)], capture_output=True, check=True,
-                             env=dict(os.environ, HUMID_INGEST_RANGE=str(rng_bytes)))
+    for rng_bytes, threads, no_mmap in ((64, 3, "0"), (333, 2, "1"), (4096, 5, "0"), (1 << 25, 2, "0")):
+        env = dict(os.environ, HUMID_INGEST_RANGE=str(rng_bytes))
+        if no_mmap == "1":  # the file read in blocks instead of parsed out of one shared mapping
+            env["HUMID_NO_MMAP"] = "1"
+        got = subprocess.run([checker, "hash_par", path, str(threads)], capture_output=True, check=True, env=env)
         assert got.stdout == ref.stdout, (case, rng_bytes)
         assert (b"different length" in got.stderr) == (b"different length" in ref.stderr), (case, rng_bytes)
         if case == "plain" and rng_bytes == 4096:  # well-formed text: every guess is right

@@ -1,7 +1,8 @@
 """A/B of the executable's host side on one box: the whole program on bench.py's configs[1] leg (4 M tuples, plain FastQ),
 alternating the default with one of
     --ab rewrite   HUMID_REWRITE_PARSE=1  (every chunk of the output passes parsed again, round 1's pass 2)
-    --ab ingest    HUMID_INGEST_THREADS=1 (one parser thread per input file instead of host/ingest_parallel.h)
+    --ab ingest    HUMID_INGEST_THREADS=1 (one parser thread per input file instead of host/ingest_parallel.h), and that
+                   with HUMID_NO_MMAP=1 (the files read in blocks instead of parsed out of a mapping: round 1's reader)
 Prints every run's phases; the box, the files and the page cache are the same for both.
 
     python tools/cli_ab.py [--ab ingest] [--tuples 4000000] [--runs 5]"""
@@ -26,15 +27,19 @@ def main():
     a = ap.parse_args()
     cfg, files, d, _ = bench.fastq_files(a.config, a.tuples, device="cuda")
     out = os.path.join(d, "out_ab")
-    other = {"rewrite": ("parse_again", dict(HUMID_REWRITE_PARSE="1")), "ingest": ("one_parser_per_file", dict(HUMID_INGEST_THREADS="1"))}[a.ab]
-    rows = {"default": [], other[0]: []}
+    others = {"rewrite": [("parse_again", dict(HUMID_REWRITE_PARSE="1"))],
+              "ingest": [("one_parser_per_file", dict(HUMID_INGEST_THREADS="1")),
+                         ("one_parser_per_file_read_in_blocks", dict(HUMID_INGEST_THREADS="1", HUMID_NO_MMAP="1"))]}[a.ab]
+    envs = dict(others)
+    rows = {"default": []}
+    rows.update({name: [] for name, _ in others})
     for run in range(a.runs):
         for mode in rows:
             shutil.rmtree(out, ignore_errors=True)
             os.makedirs(out)
             env = dict(os.environ, HUMID_TIMING="1")
             if mode != "default":
-                env.update(other[1])
+                env.update(envs[mode])
             t0 = time.monotonic()
             p = subprocess.run([bench.HUMID_EXE, *cfg.cli_flags(), "-s", "-d", out, "-l", os.path.join(out, "log"), *files], check=True,
                                env=env, capture_output=True, text=True)
