@@ -173,6 +173,7 @@ struct Slot {
   uint64_t batch = 0;           // which batch this slot is collecting
   size_t done = 0;              // files that have finished it
   vector<size_t> rows;          // records each file contributed (< BATCH only at its end)
+  vector<size_t> filled;        // several parser threads per file: rows of the batch written so far
 };
 
 struct Ingest {
@@ -229,7 +230,8 @@ void ingest_file(Ingest &g, const string &path, size_t file) {
 }
 
 // The same for a plain file with several parser threads (host/ingest_parallel.h): the threads keep this file's letters
-// of every record, the commit — in record order — puts them into the batch buffers.
+// of every record they parse; once a range's place in the file is known (commit, in file order: only the record map
+// is written there) its thread copies them into the batch buffers, side by side with the other ranges.
 // row: [take letters, 'N'-padded][u16 letters present] (+ [header UMI letters][u16 present] for file 0)
 void ingest_file_parallel(Ingest &g, const string &path, size_t file, unsigned n_threads) {
   const size_t seg = g.L.header_umi ? file + 1 : file;
@@ -251,42 +253,57 @@ void ingest_file_parallel(Ingest &g, const string &path, size_t file, unsigned n
       put(row + take + 2, rec.name.p + uo, ul, umi);
     }
   });
-  Slot *slot = nullptr;
-  uint64_t in_slot = 0, batch = 0;
-  auto acquire = [&]() {  // the buffer of batch `batch`; false: the tuple stream has ended
-    Slot &s = g.slots[batch % N_SLOTS];
+  // the buffer of batch k once the main thread has handed it out again; nullptr: the tuple stream has ended
+  auto slot_of = [&](uint64_t k) -> Slot * {
+    Slot &s = g.slots[k % N_SLOTS];
     std::unique_lock<std::mutex> lk(g.mu);
-    g.cv.wait(lk, [&] { return g.stop || s.batch == batch; });
-    if (g.stop) return false;
-    slot = &s;
-    return true;
+    g.cv.wait(lk, [&] { return g.stop || s.batch == k; });
+    return g.stop ? nullptr : &s;
   };
-  auto publish = [&]() {
-    std::lock_guard<std::mutex> lk(g.mu);
-    slot->rows[file] = in_slot;
-    slot->done++;
+  auto publish = [&](Slot &s, size_t rows) {  // (g.mu held)
+    s.rows[file] = rows;
+    s.filled[file] = 0;
+    s.done++;
     g.cv.notify_all();
-    slot = nullptr;
-    in_slot = 0;
-    batch++;
   };
-  const uint64_t n = parser.run(n_threads, [&](uint64_t t, const uint8_t *row, uint64_t at, uint32_t stored) {
-    if (!slot && !acquire()) return false;
-    uint8_t *chars = slot->chars + in_slot * g.n;
-    uint16_t *sl = slot->seg_len + in_slot * g.S;
-    std::memcpy(chars + off, row, take);
-    std::memcpy(&sl[seg], row + take, 2);
-    if (umi) {
-      std::memcpy(chars, row + take + 2, umi);
-      std::memcpy(&sl[0], row + take + 2 + umi, 2);
-    }
-    g.maps[file].note_values(t, at, stored);
-    if (++in_slot == BATCH) publish();
-    return true;
-  });
-  (void)n;
+  const uint64_t n = parser.run(
+      n_threads,
+      [&](uint64_t first, const ParallelPlainParser::Range &r, bool) {
+        for (size_t i = 0; i < r.at.size(); i++) g.maps[file].note_values(first + i, r.at[i], r.stored[i]);
+        std::lock_guard<std::mutex> lk(g.mu);
+        return !g.stop;
+      },
+      [&](uint64_t first, const ParallelPlainParser::Range &r) {
+        const size_t total = r.at.size();
+        for (size_t i = 0; i < total;) {
+          const uint64_t t = first + i, k = t / BATCH;
+          const size_t m0 = (size_t)(t % BATCH), cnt = std::min(total - i, BATCH - m0);
+          Slot *s = slot_of(k);
+          if (!s) return;
+          for (size_t j = 0; j < cnt; j++) {
+            const uint8_t *row = r.rows.data() + (i + j) * row_bytes;
+            uint8_t *chars = s->chars + (m0 + j) * g.n;
+            uint16_t *sl = s->seg_len + (m0 + j) * g.S;
+            std::memcpy(chars + off, row, take);
+            std::memcpy(&sl[seg], row + take, 2);
+            if (umi) {
+              std::memcpy(chars, row + take + 2, umi);
+              std::memcpy(&sl[0], row + take + 2 + umi, 2);
+            }
+          }
+          {
+            std::lock_guard<std::mutex> lk(g.mu);
+            s->filled[file] += cnt;
+            if (s->filled[file] == BATCH) publish(*s, BATCH);  // (a short last batch is published below)
+          }
+          i += cnt;
+        }
+      });
   // the file's last batch: short, or empty if the file ended on a batch boundary (what tells the main thread)
-  if (slot || acquire()) publish();
+  if (Slot *s = slot_of(n / BATCH)) {
+    std::lock_guard<std::mutex> lk(g.mu);
+    publish(*s, (size_t)(n % BATCH));
+  }
   if (std::getenv("HUMID_TIMING"))
     std::cerr << "ingest " << path << ": " << parser.ranges() << " ranges, " << parser.reparsed_ranges() << " parsed again\n";
 }
@@ -436,6 +453,7 @@ int main(int argc, char **argv) {
       g.slots[j].seg_len = static_cast<uint16_t *>(page_aligned(BATCH * g.S * sizeof(uint16_t)));
       g.slots[j].batch = (uint64_t)j;
       g.slots[j].rows.assign(F, 0);
+      g.slots[j].filled.assign(F, 0);
     }
     vector<std::thread> readers;
     const unsigned parsers = ingest_threads(F);

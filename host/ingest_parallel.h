@@ -76,12 +76,26 @@ class ParallelPlainParser {
     return v >= 64 ? (uint64_t)v : (32ull << 20);
   }
 
-  // Parses the file with n_threads threads; returns the number of records delivered.
-  uint64_t run(unsigned n_threads, const Row &row) {
+  // commit(first, range, last): the range's records are records first, first + 1, ... of the file; called in file
+  //   order, one range at a time — keep it short; last: the file ends with this range; false = stop reading.
+  // scatter(first, range): the same range once more, after its turn, side by side with other ranges (may be empty).
+  using Commit = std::function<bool(uint64_t, const Range &, bool)>;
+  using Scatter = std::function<void(uint64_t, const Range &)>;
+
+  // Parses the file with n_threads threads; returns the number of records accounted for.
+  uint64_t run(unsigned n_threads, const Commit &commit, const Scatter &scatter) {
     std::vector<std::thread> pool;
-    for (unsigned i = 0; i < std::max(1u, n_threads); i++) pool.emplace_back([&] { work(row); });
+    for (unsigned i = 0; i < std::max(1u, n_threads); i++) pool.emplace_back([&] { work(commit, scatter); });
     for (std::thread &t : pool) t.join();
     return delivered_;
+  }
+  // One call per record, in order.
+  uint64_t run(unsigned n_threads, const Row &row) {
+    return run(n_threads, [&](uint64_t first, const Range &r, bool) {
+      for (size_t i = 0; i < r.at.size(); i++)
+        if (!row(first + i, r.rows.data() + i * row_bytes_, r.at[i], r.stored[i])) return false;
+      return true;
+    }, nullptr);
   }
   uint64_t reparsed_ranges() const { return reparsed_; }
   uint64_t ranges() const { return n_ranges_; }
@@ -149,7 +163,7 @@ class ParallelPlainParser {
     }
   }
 
-  void work(const Row &row) {
+  void work(const Commit &commit, const Scatter &scatter) {
     while (true) {
       uint64_t j;
       {
@@ -166,7 +180,9 @@ class ParallelPlainParser {
       cv_.wait(lk, [&] { return stop_ || turn_ == j; });
       if (stop_) return;
       lk.unlock();
-      // ---- this range's turn: the records before it have been delivered, expect_ is where the next one starts ----
+      // ---- this range's turn: the records before it are accounted for, expect_ is where the next one starts ----
+      uint64_t first = delivered_;
+      bool mine = false;
       if (expect_ != kNone && expect_ < hi) {
         if (r.entered != expect_) {
           if (j > 0) {
@@ -177,19 +193,26 @@ class ParallelPlainParser {
         } else {
           misses_in_a_row_ = 0;
         }
-        bool go_on = true;
-        for (size_t i = 0; i < r.at.size() && go_on; i++) {
-          go_on = row(delivered_, r.rows.data() + i * row_bytes_, r.at[i], r.stored[i]);
-          delivered_++;
-        }
+        const bool last = r.next == kNone;
+        const bool go_on = commit(first, r, last);
+        delivered_ += r.at.size();
+        last_signalled_ |= last;
+        mine = go_on;
         if (go_on && !r.error.empty()) std::cerr << r.error << std::flush;
-        expect_ = r.next;  // (kNone: the file, or what can be read of it, ends in this range)
-        if (!go_on) expect_ = kNone;
+        expect_ = go_on ? r.next : kNone;  // (kNone: the file, or what can be read of it, ends in this range)
+      } else if (j + 1 == n_ranges_ && expect_ != kNone && !last_signalled_) {
+        // the record before reaches to the end of the file (or the file is empty): nothing starts in the last range
+        r = Range();
+        commit(first, r, true);
+        last_signalled_ = true;
+        expect_ = kNone;
       }
       lk.lock();
       turn_ = j + 1;
       if (expect_ == kNone) stop_ = true;
       cv_.notify_all();
+      lk.unlock();
+      if (mine && scatter) scatter(first, r);  // side by side with the other ranges' parsing and scattering
     }
   }
 
@@ -205,6 +228,7 @@ class ParallelPlainParser {
   // the commit's state (one thread at a time: turn_)
   uint64_t expect_ = 0, delivered_ = 0, reparsed_ = 0;
   unsigned misses_in_a_row_ = 0;
+  bool last_signalled_ = false;
   std::atomic<bool> speculation_off_{false};
 };
 
