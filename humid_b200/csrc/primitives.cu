@@ -167,12 +167,17 @@ constexpr int RS_LOOK = 8;
 constexpr uint64_t RS_AGGREGATE = 1ull << 62;  // status word: this tile's own count
 constexpr uint64_t RS_INCLUSIVE = 1ull << 63;  // status word: count of this tile and all before it
 
+// The pass works on 64-bit keys (every sort but one) or on 32-bit ones (radix_sort_u32_indexed).
+__device__ __forceinline__ uint64_t ld_stream_key(const uint64_t *p) { return ld_stream_u64(p); }
+__device__ __forceinline__ uint32_t ld_stream_key(const uint32_t *p) { return __ldcs(p); }
+
 __device__ __forceinline__ uint32_t pass_mask(int begin_bit, int end_bit, int p) {
   const int left = end_bit - begin_bit - 8 * p;
   return left >= 8 ? 255u : (1u << left) - 1u;
 }
 
-__global__ void __launch_bounds__(RS_THREADS) radix_digit_hist_kernel(const uint64_t *__restrict__ keys, uint64_t n,
+template <class K>
+__global__ void __launch_bounds__(RS_THREADS) radix_digit_hist_kernel(const K *__restrict__ keys, uint64_t n,
                                                                       int begin_bit, int end_bit, int passes,
                                                                       uint32_t *__restrict__ hist) {
   __shared__ uint32_t h[RS_MAX_PASSES][RS_BINS];
@@ -180,7 +185,7 @@ __global__ void __launch_bounds__(RS_THREADS) radix_digit_hist_kernel(const uint
   __syncthreads();
   const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
   for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride) {
-    uint64_t key = ld_stream_u64(keys + i);
+    const K key = ld_stream_key(keys + i);
     for (int p = 0; p < passes; p++)
       atomicAdd(&h[p][(uint32_t)(key >> (begin_bit + 8 * p)) & pass_mask(begin_bit, end_bit, p)], 1u);
   }
@@ -277,27 +282,13 @@ __device__ __forceinline__ uint32_t same_bit_lanes(uint32_t dig, uint32_t mask) 
   return m ^ flip;
 }
 
-// Keys as they are read (KIn) and as they are ranked, staged and written (KOut = xform(KIn)): 64-bit keys all the way
-// (Same), or a pass that reads 64-bit keys and goes on with 32 of their bits (Narrow: radix_sort_prefix32_indexed).
-struct Same {
-  __device__ __forceinline__ uint64_t operator()(uint64_t k) const { return k; }
-  __device__ __forceinline__ uint32_t operator()(uint32_t k) const { return k; }
-};
-struct Narrow {
-  int shift;
-  __device__ __forceinline__ uint32_t operator()(uint64_t k) const { return (uint32_t)(k >> shift); }
-};
-__device__ __forceinline__ uint64_t ld_stream_key(const uint64_t *p) { return ld_stream_u64(p); }
-__device__ __forceinline__ uint32_t ld_stream_key(const uint32_t *p) { return __ldcs(p); }
-
 // One tile.  FULL: all RS_TILE elements exist (every tile but the last), no bounds tests in the loops.
-template <bool HAS_VALS, bool FULL, class Digit, class KIn, class KOut, class Xform>
-__device__ __forceinline__ uint32_t radix_tile(const KIn *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
-                                               KOut *__restrict__ keys_out, uint32_t *__restrict__ vals_out,
-                                               uint64_t n, uint32_t n_tiles, const Digit &digit_of, const Xform &xform,
-                                               uint32_t my_base, volatile uint64_t *status, uint32_t *ticket,
-                                               uint32_t index_base, uint32_t tile, KOut *stage, uint32_t *svals,
-                                               RadixShared &sh) {
+template <bool HAS_VALS, bool FULL, class Digit, class K>
+__device__ __forceinline__ uint32_t radix_tile(const K *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
+                                               K *__restrict__ keys_out, uint32_t *__restrict__ vals_out,
+                                               uint64_t n, uint32_t n_tiles, const Digit &digit_of, uint32_t my_base,
+                                               volatile uint64_t *status, uint32_t *ticket, uint32_t index_base,
+                                               uint32_t tile, K *stage, uint32_t *svals, RadixShared &sh) {
   const int w = threadIdx.x >> 5;
   const uint32_t lane = lane_id();
   const uint32_t lt = (1u << lane) - 1u;
@@ -308,12 +299,12 @@ __device__ __forceinline__ uint32_t radix_tile(const KIn *__restrict__ keys_in, 
   const uint64_t tile_base = (uint64_t)tile * RS_TILE;
   const uint32_t in_tile = FULL ? (uint32_t)RS_TILE : (uint32_t)(n - tile_base);
   const uint32_t warp_first = (uint32_t)w * (32 * RS_ITEMS) + lane;  // tile-local index of this lane's first element
-  const KIn *kin = keys_in + tile_base + warp_first;
-  KOut key[RS_ITEMS];
+  const K *kin = keys_in + tile_base + warp_first;
+  K key[RS_ITEMS];
   uint32_t val[HAS_VALS ? RS_ITEMS : 1];
   uint16_t lpos[RS_ITEMS];
 #pragma unroll
-  for (int j = 0; j < RS_ITEMS; j++) key[j] = (FULL || warp_first + j * 32 < in_tile) ? xform(ld_stream_key(kin + j * 32)) : (KOut)0;
+  for (int j = 0; j < RS_ITEMS; j++) key[j] = (FULL || warp_first + j * 32 < in_tile) ? ld_stream_key(kin + j * 32) : (K)0;
   if (HAS_VALS) {
     if (vals_in) {
       const uint32_t *vin = vals_in + tile_base + warp_first;
@@ -329,7 +320,7 @@ __device__ __forceinline__ uint32_t radix_tile(const KIn *__restrict__ keys_in, 
   const uint32_t next_tile = sh.next;
   if (next_tile < n_tiles) {  // -> L2 (128-B lines)
     const uint64_t next = (uint64_t)next_tile * RS_TILE;
-    constexpr uint32_t per_line = 128 / sizeof(KIn);
+    constexpr uint32_t per_line = 128 / sizeof(K);
 #pragma unroll
     for (uint32_t l = threadIdx.x; l < RS_TILE / per_line; l += RS_PASS_THREADS)
       if (next + (uint64_t)l * per_line < n) prefetch_l2(keys_in + next + (uint64_t)l * per_line);
@@ -418,7 +409,7 @@ __device__ __forceinline__ uint32_t radix_tile(const KIn *__restrict__ keys_in, 
   for (int k = 0; k < RS_ITEMS; k++) {
     const uint32_t idx = k * RS_PASS_THREADS + threadIdx.x;
     if (FULL || idx < in_tile) {
-      const KOut kk = stage[idx];
+      const K kk = stage[idx];
       const uint32_t out = sh.gbase[digit_of(kk)] + idx;
       keys_out[out] = kk;
       if (HAS_VALS) vals_out[out] = svals[idx];
@@ -428,15 +419,15 @@ __device__ __forceinline__ uint32_t radix_tile(const KIn *__restrict__ keys_in, 
   return next_tile;
 }
 
-template <bool HAS_VALS, class Digit, class KIn, class KOut, class Xform>
+template <bool HAS_VALS, class Digit, class K>
 __global__ void __launch_bounds__(RS_PASS_THREADS, HUMID_RS_CTAS)
-    radix_pass_kernel(const KIn *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
-                      KOut *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n, uint32_t n_tiles,
-                      Digit digit_of, Xform xform, const uint32_t *__restrict__ digit_base, volatile uint64_t *status,
+    radix_pass_kernel(const K *__restrict__ keys_in, const uint32_t *__restrict__ vals_in,
+                      K *__restrict__ keys_out, uint32_t *__restrict__ vals_out, uint64_t n, uint32_t n_tiles,
+                      Digit digit_of, const uint32_t *__restrict__ digit_base, volatile uint64_t *status,
                       uint32_t *ticket, uint32_t index_base) {
   extern __shared__ __align__(16) unsigned char stage_bytes[];  // [RS_TILE] keys, then [RS_TILE] u32 values
   __shared__ RadixShared sh;
-  KOut *const stage = reinterpret_cast<KOut *>(stage_bytes);
+  K *const stage = reinterpret_cast<K *>(stage_bytes);
   uint32_t *const svals = reinterpret_cast<uint32_t *>(stage + RS_TILE);
   const uint32_t my_base = threadIdx.x < RS_BINS ? digit_base[threadIdx.x] : 0u;
 
@@ -446,22 +437,22 @@ __global__ void __launch_bounds__(RS_PASS_THREADS, HUMID_RS_CTAS)
   __syncthreads();
   while (tile < n_tiles) {
     if ((uint64_t)(tile + 1) * RS_TILE <= n)
-      tile = radix_tile<HAS_VALS, true>(keys_in, vals_in, keys_out, vals_out, n, n_tiles, digit_of, xform, my_base, status,
+      tile = radix_tile<HAS_VALS, true>(keys_in, vals_in, keys_out, vals_out, n, n_tiles, digit_of, my_base, status,
                                         ticket, index_base, tile, stage, svals, sh);
     else
-      tile = radix_tile<HAS_VALS, false>(keys_in, vals_in, keys_out, vals_out, n, n_tiles, digit_of, xform, my_base, status,
+      tile = radix_tile<HAS_VALS, false>(keys_in, vals_in, keys_out, vals_out, n, n_tiles, digit_of, my_base, status,
                                          ticket, index_base, tile, stage, svals, sh);
   }
 }
 
-template <bool HAS_VALS, class Digit, class KIn = uint64_t, class KOut = uint64_t, class Xform = Same>
-static void launch_radix_pass(uint32_t n_tiles, cudaStream_t stream, const KIn *keys_in, const uint32_t *vals_in,
-                              KOut *keys_out, uint32_t *vals_out, uint64_t n, Digit dg, const uint32_t *digit_base,
-                              uint64_t *status, uint32_t *ticket, uint32_t index_base, Xform xform = Xform()) {
-  const size_t smem = (size_t)RS_TILE * (sizeof(KOut) + (HAS_VALS ? 4 : 0));
+template <bool HAS_VALS, class Digit, class K>
+static void launch_radix_pass(uint32_t n_tiles, cudaStream_t stream, const K *keys_in, const uint32_t *vals_in,
+                              K *keys_out, uint32_t *vals_out, uint64_t n, Digit dg, const uint32_t *digit_base,
+                              uint64_t *status, uint32_t *ticket, uint32_t index_base) {
+  const size_t smem = (size_t)RS_TILE * (sizeof(K) + (HAS_VALS ? 4 : 0));
   static int resident = 0;  // per instantiation: CTAs of this kernel that fit on the device at once
   if (!resident) {
-    auto *fn = radix_pass_kernel<HAS_VALS, Digit, KIn, KOut, Xform>;
+    auto *fn = radix_pass_kernel<HAS_VALS, Digit, K>;
     HUMID_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int dev = 0, sms = 0, per_sm = 0;
     HUMID_CUDA(cudaGetDevice(&dev));
@@ -471,8 +462,8 @@ static void launch_radix_pass(uint32_t n_tiles, cudaStream_t stream, const KIn *
     resident = sms * per_sm;
   }
   const unsigned grid = std::min<unsigned>(n_tiles, (unsigned)resident);
-  radix_pass_kernel<HAS_VALS, Digit, KIn, KOut, Xform><<<grid, RS_PASS_THREADS, smem, stream>>>(
-      keys_in, vals_in, keys_out, vals_out, n, n_tiles, dg, xform, digit_base, status, ticket, index_base);
+  radix_pass_kernel<HAS_VALS, Digit, K><<<grid, RS_PASS_THREADS, smem, stream>>>(keys_in, vals_in, keys_out, vals_out, n, n_tiles, dg,
+                                                                          digit_base, status, ticket, index_base);
 }
 
 // Passes over bits [begin_bit, end_bit).  The first pass reads (in_keys, in_vals) and writes buffer
@@ -521,10 +512,10 @@ static int radix_sort_impl(const uint64_t *in_keys, const uint32_t *in_vals, uin
   return out ^ 1;
 }
 
-// Sort of (32 bits of the key, position) pairs: see primitives.cuh.
-int radix_sort_prefix32_indexed(const uint64_t *keys_in, uint32_t *prefix[2], uint32_t *index[2], uint64_t n, int shift, int bits,
-                                Scratch &scratch, cudaStream_t stream, int *launches) {
-  if (n == 0 || bits <= 0 || bits > 32) throw CudaError{"radix_sort_prefix32_indexed: 1..32 bits"};
+// Sort of (32-bit key, position) pairs: see primitives.cuh.
+int radix_sort_u32_indexed(const uint32_t *keys_in, uint32_t *keys[2], uint32_t *index[2], uint64_t n, int bits, Scratch &scratch,
+                           cudaStream_t stream, int *launches) {
+  if (n == 0 || bits <= 0 || bits > 32) throw CudaError{"radix_sort_u32_indexed: 1..32 bits"};
   if (n >= 0xFFFFFFFFull) throw CudaError{"radix sort: more than 2^32-1 elements"};
   const int passes = (bits + 7) / 8;
   const uint32_t n_tiles = (uint32_t)((n + RS_TILE - 1) / RS_TILE);
@@ -536,21 +527,19 @@ int radix_sort_prefix32_indexed(const uint64_t *keys_in, uint32_t *prefix[2], ui
   uint32_t *hist = tickets + RS_MAX_PASSES;
   HUMID_CUDA(cudaMemsetAsync(tickets, 0, tail_bytes, stream));
   unsigned hist_grid = (unsigned)std::min<uint64_t>((n + RS_THREADS - 1) / RS_THREADS, 148 * 8);
-  radix_digit_hist_kernel<<<hist_grid, RS_THREADS, 0, stream>>>(keys_in, n, shift, shift + bits, passes, hist);
+  radix_digit_hist_kernel<<<hist_grid, RS_THREADS, 0, stream>>>(keys_in, n, 0, bits, passes, hist);
   radix_digit_bases_kernel<<<passes, RS_THREADS, 0, stream>>>(hist);
   *launches += 2;
+  const uint32_t *src_k = keys_in, *src_v = nullptr;  // (no values yet: the value of element i is i)
   int out = 0;
   for (int p = 0; p < passes; p++) {
     const int left = bits - 8 * p;
     const ShiftDigit dg{8 * p, left >= 8 ? 255u : (1u << left) - 1u};
     HUMID_CUDA(cudaMemsetAsync(status, 0, status_bytes, stream));
-    if (p == 0)  // 64-bit keys in, their 32 sort bits out; the value of element i is i
-      launch_radix_pass<true, ShiftDigit, uint64_t, uint32_t, Narrow>(n_tiles, stream, keys_in, nullptr, prefix[out], index[out], n, dg,
-                                                                      hist, status, tickets, 0u, Narrow{shift});
-    else
-      launch_radix_pass<true, ShiftDigit, uint32_t, uint32_t, Same>(n_tiles, stream, prefix[out ^ 1], index[out ^ 1], prefix[out],
-                                                                    index[out], n, dg, hist + p * RS_BINS, status, tickets + p, 0u);
+    launch_radix_pass<true>(n_tiles, stream, src_k, src_v, keys[out], index[out], n, dg, hist + p * RS_BINS, status, tickets + p, 0u);
     *launches += 1;
+    src_k = keys[out];
+    src_v = index[out];
     out ^= 1;
   }
   HUMID_CUDA(cudaGetLastError());

@@ -52,12 +52,11 @@ int radix_sort_u64(uint64_t *keys[2], uint32_t *vals[2], uint64_t n, int end_bit
 int radix_sort_bits_indexed(const uint64_t *keys_in, uint64_t *keys[2], uint32_t *index[2], uint64_t n, int begin_bit,
                             int end_bit, Scratch &scratch, cudaStream_t stream, int *launches);
 
-// Stable sort of (prefix, position) pairs, prefix = the `bits` (1..32) bits of the key from bit `shift` up: the first
-// pass reads the 64-bit keys and writes 32-bit ones, the others move 8 bytes per element instead of 12.  Elements
-// whose prefixes are equal stay in input order.  Returns the index (0 or 1) of the (prefix, index) buffer pair holding
-// the result.
-int radix_sort_prefix32_indexed(const uint64_t *keys_in, uint32_t *prefix[2], uint32_t *index[2], uint64_t n, int shift, int bits,
-                                Scratch &scratch, cudaStream_t stream, int *launches);
+// Stable sort of (32-bit key, position) pairs by the low `bits` (1..32) bits of the key: 8 bytes per element and pass
+// where the 64-bit sorts move 12.  keys_in is only read; element i carries the value i.  Returns the index (0 or 1) of
+// the (keys, index) buffer pair holding the result.
+int radix_sort_u32_indexed(const uint32_t *keys_in, uint32_t *keys[2], uint32_t *index[2], uint64_t n, int bits, Scratch &scratch,
+                           cudaStream_t stream, int *launches);
 
 // One stable partition pass of (key, value) pairs by the top 8 bits of the key's home slot in an
 // open-addressing table with `slot_mask + 1` slots (slot = mix64(key) & slot_mask): afterwards
