@@ -173,8 +173,8 @@ struct State {
   DevBuf<uint64_t> word_key, key_alt;
   DevBuf<uint32_t> word_slot, slot_alt;
   DevBuf<uint64_t> compact_key;   // the table's words in compaction (slot) order: key ...
-  DevBuf<uint2> compact_cf;       // ... {Leaf::count, first tuple} ...
-  DevBuf<uint32_t> compact_prefix, compact_low;  // ... the key in two parts: its 32 leading bits, the bits below them ...
+  DevBuf<uint4> compact_rec;      // ... the whole slot {key lo, key hi, Leaf::count, first tuple} ...
+  DevBuf<uint32_t> compact_prefix;  // ... the key's 32 leading bits (what sort_words sorts) ...
   DevBuf<uint32_t> compact_slot;  // ... and slot number
   DevBuf<uint32_t> prefix_a, prefix_b;  // sort_words: 32 leading key bits of every word, double buffer
   bool word_slot_is_index = false;  // word_slot still holds compaction positions (translated on first look-up set-up)

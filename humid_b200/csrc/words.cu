@@ -394,9 +394,9 @@ __global__ void __launch_bounds__(HUMID_INSERT_THREADS)
   if (ti < (uint32_t)(hi >> 32)) atomicMin(&slots[idx].first, ti);
 }
 
-// Occupied slots -> dense columns in any order (they are sorted next): the key — as its 32 leading bits (what is sorted)
-// and the bits below them (low_bits of them, at most 30; fetched again behind the sort), or whole for the 64-bit sort
-// (keys_out != nullptr) —, {count, first}, slot number.  The whole
+// Occupied slots -> dense columns in any order (they are sorted next): the key's 32 leading bits (what is sorted; the
+// whole key for the 64-bit sort, keys_out != nullptr), the whole 16-byte slot {key, count, first} (what the gather
+// behind the sort reads: ONE random access per word gives its key and its columns), slot number.  The whole
 // 16-byte slot is read (the key alone pulls the same sectors in), so count and first come along for free and the
 // rank-ordered columns are later gathered from these dense arrays instead of from the table (which is 3-5x larger and
 // mostly empty: 2.6 GB of DRAM fills for 0.5 GB of useful bytes in round 1's gather).  One atomic per CTA:
@@ -404,9 +404,8 @@ __global__ void __launch_bounds__(HUMID_INSERT_THREADS)
 constexpr int COMPACT_ITEMS = 8;
 __global__ void __launch_bounds__(256)
     table_compact_kernel(const Slot *__restrict__ slots, uint64_t cap, uint64_t *__restrict__ keys_out,
-                         uint32_t *__restrict__ prefix_out, uint32_t *__restrict__ low_out, int low_bits,
-                         uint2 *__restrict__ cf_out, uint32_t *__restrict__ slot_out,
-                         unsigned long long *__restrict__ counter) {
+                         uint32_t *__restrict__ prefix_out, int low_bits, uint4 *__restrict__ rec_out,
+                         uint32_t *__restrict__ slot_out, unsigned long long *__restrict__ counter) {
   __shared__ uint32_t warp_cnt[COMPACT_ITEMS][8];
   __shared__ unsigned long long cta_base;
   const uint64_t base = (uint64_t)blockIdx.x * (256 * COMPACT_ITEMS);
@@ -437,13 +436,9 @@ __global__ void __launch_bounds__(256)
     if ((slot[j].x & slot[j].y) != 0xFFFFFFFFu) {  // a key never has bit 63 set, so only KEY_INVALID is all ones
       uint64_t pos = cta_base + warp_cnt[j][w] + __popc(bal[j] & ((1u << lane) - 1u));
       const uint64_t key = ((uint64_t)slot[j].y << 32) | slot[j].x;
-      if (keys_out) {
-        keys_out[pos] = key;
-      } else {
-        prefix_out[pos] = (uint32_t)(key >> low_bits);
-        if (low_bits) low_out[pos] = (uint32_t)key & ((1u << low_bits) - 1u);
-      }
-      cf_out[pos] = make_uint2(slot[j].z, slot[j].w);
+      if (keys_out) keys_out[pos] = key;
+      else prefix_out[pos] = (uint32_t)(key >> low_bits);
+      rec_out[pos] = slot[j];
       slot_out[pos] = (uint32_t)(base + (uint64_t)j * 256 + threadIdx.x);
     }
   }
@@ -454,45 +449,44 @@ __global__ void __launch_bounds__(256)
 // slot number as well — were slower than round 1's single 16-byte read out of the table: past L2 a random gather costs
 // per access, not per byte).  The slot numbers are only needed for key -> rank look-ups and translated on demand.
 __global__ void __launch_bounds__(256)
-    gather_columns_kernel(const uint2 *__restrict__ compact_cf, const uint32_t *__restrict__ word_index, uint64_t U,
+    gather_columns_kernel(const uint4 *__restrict__ compact_rec, const uint32_t *__restrict__ word_index, uint64_t U,
                           uint32_t *__restrict__ word_count, uint32_t *__restrict__ word_first) {
   uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= U) return;
-  const uint2 cf = __ldg(compact_cf + word_index[r]);
-  word_count[r] = cf.x;
-  word_first[r] = cf.y;
+  const uint4 rec = __ldg(compact_rec + word_index[r]);
+  word_count[r] = rec.z;
+  word_first[r] = rec.w;
 }
 
 // ---- sort_words by 32 leading key bits + this gather (the default; HUMID_GPU_SORT=full takes the 64-bit sort above) ----
 // The sort (radix_sort_u32_indexed) ordered the words by the first 32 of their key bits only: 8 bytes per element and
 // pass instead of 12, four passes instead of six for 24-letter words.  Words whose 32 leading bits agree (16 leading
-// letters: rare in a library, common in none) stand next to each other in compaction order.  This kernel puts every
-// word's key together again — leading bits from the sorted array (streamed), the bits below them from compact_low
-// (a random 4-byte read out of an array that mostly stays in L2) — fetches {count, first} (the one random 8-byte read
-// per word the rank columns cost anyway) and finishes the order:
+// letters: rare in a library, common in none) stand next to each other in compaction order.  This kernel fetches
+// every word's slot record — one random 16-byte access per word gives the key and the rank columns; the key's low bits
+// and {count, first} from two smaller arrays were two accesses and slower (0.73 against 0.51 ms, call r02ag) — and
+// finishes the order:
 //   alone with its prefix        write key, count, first
-//   first of a run of 2..64      the thread fetches the run, orders it by the low bits (insertion sort in place) and
+//   first of a run of 2..64      the thread fetches the run, orders it by the whole key (insertion sort in place) and
 //                                writes it, permuting word_index alike
 //   first of a longer run        noted in long_runs for sort_long_runs_kernel
 constexpr uint32_t RUN_SERIAL_MAX = 64;
+__device__ __forceinline__ uint64_t rec_key(const uint4 &r) { return ((uint64_t)r.y << 32) | r.x; }
 
 __global__ void __launch_bounds__(256)
-    gather_sorted_words_kernel(const uint32_t *__restrict__ prefix, uint32_t *word_index, const uint32_t *__restrict__ compact_low,
-                               int low_bits, const uint2 *__restrict__ compact_cf, uint64_t U, uint64_t *__restrict__ word_key,
-                               uint32_t *__restrict__ word_count, uint32_t *__restrict__ word_first,
-                               uint32_t *__restrict__ long_runs, unsigned long long *__restrict__ n_long) {
+    gather_sorted_words_kernel(const uint32_t *__restrict__ prefix, uint32_t *word_index, const uint4 *__restrict__ compact_rec,
+                               uint64_t U, uint64_t *__restrict__ word_key, uint32_t *__restrict__ word_count,
+                               uint32_t *__restrict__ word_first, uint32_t *__restrict__ long_runs,
+                               unsigned long long *__restrict__ n_long) {
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= U) return;
   const uint32_t p = prefix[i];
-  const uint64_t high = (uint64_t)p << low_bits;
   const bool after_same = i > 0 && prefix[i - 1] == p, before_same = i + 1 < U && prefix[i + 1] == p;
   if (after_same) return;  // the run's first thread writes this word
   if (!before_same) {
-    const uint32_t id = word_index[i];
-    const uint2 cf = __ldg(compact_cf + id);
-    word_key[i] = high | (low_bits ? __ldg(compact_low + id) : 0u);
-    word_count[i] = cf.x;
-    word_first[i] = cf.y;
+    const uint4 rec = __ldg(compact_rec + word_index[i]);
+    word_key[i] = rec_key(rec);
+    word_count[i] = rec.z;
+    word_first[i] = rec.w;
     return;
   }
   uint32_t len = 2;
@@ -503,8 +497,8 @@ __global__ void __launch_bounds__(256)
   }
   for (uint32_t k = 0; k < len; k++) {  // (stable insertion by the whole key; the keys of a table are distinct)
     const uint32_t id = word_index[i + k];
-    const uint2 cf = __ldg(compact_cf + id);
-    const uint64_t key = high | __ldg(compact_low + id);
+    const uint4 rec = __ldg(compact_rec + id);
+    const uint64_t key = rec_key(rec);
     uint32_t j = k;
     while (j > 0 && word_key[i + j - 1] > key) {
       word_key[i + j] = word_key[i + j - 1];
@@ -514,8 +508,8 @@ __global__ void __launch_bounds__(256)
       j--;
     }
     word_key[i + j] = key;
-    word_count[i + j] = cf.x;
-    word_first[i + j] = cf.y;
+    word_count[i + j] = rec.z;
+    word_first[i + j] = rec.w;
     word_index[i + j] = id;
   }
 }
@@ -528,8 +522,7 @@ __global__ void __launch_bounds__(256)
 constexpr uint32_t LONG_RUN_SMEM = 2048;
 __global__ void __launch_bounds__(256)
     sort_long_runs_kernel(const uint32_t *__restrict__ prefix, uint32_t *word_index, uint32_t *index_alt,
-                          const uint32_t *__restrict__ compact_low, const uint2 *__restrict__ compact_cf, uint64_t U, int low_bits,
-                          uint64_t *word_key, uint64_t *key_alt,
+                          const uint4 *__restrict__ compact_rec, uint64_t U, int low_bits, uint64_t *word_key, uint64_t *key_alt,
                           uint32_t *__restrict__ word_count, uint32_t *__restrict__ word_first,
                           const uint32_t *__restrict__ long_runs, const unsigned long long *__restrict__ n_long) {
   __shared__ uint64_t skey[LONG_RUN_SMEM];
@@ -540,7 +533,6 @@ __global__ void __launch_bounds__(256)
   for (unsigned long long r = blockIdx.x; r < runs; r += gridDim.x) {
     const uint64_t first = long_runs[r];
     const uint32_t p = prefix[first];
-    const uint64_t high = (uint64_t)p << low_bits;
     if (threadIdx.x == 0) run_len = 0xFFFFFFFFu;
     __syncthreads();
     // the run's length: the first position behind `first` with another prefix (strided search, smallest hit wins)
@@ -558,7 +550,7 @@ __global__ void __launch_bounds__(256)
       while (p2 < len) p2 <<= 1;
       for (uint32_t k = threadIdx.x; k < p2; k += blockDim.x) {
         const uint32_t id = k < len ? word_index[first + k] : 0u;
-        skey[k] = k < len ? (high | __ldg(compact_low + id)) : ~0ull;
+        skey[k] = k < len ? rec_key(__ldg(compact_rec + id)) : ~0ull;
         sidx[k] = id;
       }
       __syncthreads();
@@ -580,16 +572,16 @@ __global__ void __launch_bounds__(256)
           __syncthreads();
         }
       for (uint32_t k = threadIdx.x; k < len; k += blockDim.x) {
-        const uint2 cf = __ldg(compact_cf + sidx[k]);
+        const uint4 rec = __ldg(compact_rec + sidx[k]);
         word_key[first + k] = skey[k];
-        word_count[first + k] = cf.x;
-        word_first[first + k] = cf.y;
+        word_count[first + k] = rec.z;
+        word_first[first + k] = rec.w;
         word_index[first + k] = sidx[k];
       }
     } else {
       uint64_t *ka = word_key + first, *kb = key_alt + first;
       uint32_t *ia = word_index + first, *ib = index_alt + first;
-      for (uint32_t k = threadIdx.x; k < len; k += blockDim.x) ka[k] = high | __ldg(compact_low + ia[k]);
+      for (uint32_t k = threadIdx.x; k < len; k += blockDim.x) ka[k] = rec_key(__ldg(compact_rec + ia[k]));
       __syncthreads();
       const uint32_t piece = (len + blockDim.x - 1) / blockDim.x;
       const uint32_t lo = threadIdx.x * piece < len ? threadIdx.x * piece : len, hi = lo + piece < len ? lo + piece : len;
@@ -623,11 +615,11 @@ __global__ void __launch_bounds__(256)
       for (uint32_t k = threadIdx.x; k < len; k += blockDim.x) {
         const uint64_t key = ka[k];
         const uint32_t id = ia[k];
-        const uint2 cf = __ldg(compact_cf + id);
+        const uint4 rec = __ldg(compact_rec + id);
         word_key[first + k] = key;
         word_index[first + k] = id;
-        word_count[first + k] = cf.x;
-        word_first[first + k] = cf.y;
+        word_count[first + k] = rec.z;
+        word_first[first + k] = rec.w;
       }
     }
     __syncthreads();
@@ -774,20 +766,16 @@ int stage_build_table(State &s, bool with_lookup) {
   const bool by_prefix = !(sort_env && std::string(sort_env) == "full");
   const int key_bits = 2 * (int)s.cfg.word_length;
   const int prefix_bits = std::min(32, key_bits), low_bits = key_bits - prefix_bits;
-  if (by_prefix) {
-    s.compact_prefix.ensure(s.usable + 1);
-    s.compact_low.ensure(low_bits ? s.usable + 1 : 1);
-  } else {
-    s.compact_key.ensure(s.usable + 1);
-  }
-  s.compact_cf.ensure(s.usable + 1);
+  if (by_prefix) s.compact_prefix.ensure(s.usable + 1);
+  else s.compact_key.ensure(s.usable + 1);
+  s.compact_rec.ensure(s.usable + 1);
   s.compact_slot.ensure(s.usable + 1);
   HUMID_CUDA(cudaMemsetAsync(s.counters.p + 1, 0, sizeof(unsigned long long), s.stream));
   {
     Timed t(s, "table_compact", cap, cap * 16 + s.usable * 20);
     table_compact_kernel<<<grid_for(cap, 256, COMPACT_ITEMS), 256, 0, s.stream>>>(s.slots.p, cap, by_prefix ? nullptr : s.compact_key.p,
-                                                                                 s.compact_prefix.p, s.compact_low.p, low_bits,
-                                                                                 s.compact_cf.p, s.compact_slot.p,
+                                                                                 s.compact_prefix.p, low_bits, s.compact_rec.p,
+                                                                                 s.compact_slot.p,
                                                                                  s.counters.p + 1);
   }
   k++;
@@ -817,15 +805,14 @@ int stage_build_table(State &s, bool with_lookup) {
     uint32_t *long_runs = pk[cur ^ 1];  // (the sort's other prefix buffer is free now)
     unsigned long long *n_long = s.counters.p + 14;
     HUMID_CUDA(cudaMemsetAsync(n_long, 0, sizeof(unsigned long long), s.stream));
-    Timed t(s, "rank_columns", U, U * (4 + 4 + 8 + (low_bits ? 4 : 0) + 8 + 4 + 4));
-    gather_sorted_words_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(pk[cur], s.word_slot.p, s.compact_low.p, low_bits,
-                                                                       s.compact_cf.p, U, s.word_key.p, s.word_count.p,
-                                                                       s.word_first.p, long_runs, n_long);
+    Timed t(s, "rank_columns", U, U * (4 + 4 + 16 + 8 + 4 + 4));
+    gather_sorted_words_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(pk[cur], s.word_slot.p, s.compact_rec.p, U, s.word_key.p,
+                                                                       s.word_count.p, s.word_first.p, long_runs, n_long);
     k++;
     if (low_bits) {  // (no low bits: the prefix is the whole key and no two words share it)
-      sort_long_runs_kernel<<<2 * 148, 256, 0, s.stream>>>(pk[cur], s.word_slot.p, s.slot_alt.p, s.compact_low.p, s.compact_cf.p, U,
-                                                           low_bits, s.word_key.p, s.key_alt.p, s.word_count.p, s.word_first.p,
-                                                           long_runs, n_long);
+      sort_long_runs_kernel<<<2 * 148, 256, 0, s.stream>>>(pk[cur], s.word_slot.p, s.slot_alt.p, s.compact_rec.p, U, low_bits,
+                                                           s.word_key.p, s.key_alt.p, s.word_count.p, s.word_first.p, long_runs,
+                                                           n_long);
       k++;
     }
     t.launches = low_bits ? 2 : 1;
@@ -848,7 +835,7 @@ int stage_build_table(State &s, bool with_lookup) {
       std::swap(s.word_slot, s.slot_alt);
     }
     Timed t(s, "rank_columns", U, U * (4 + 8 + 4 + 4));
-    gather_columns_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.compact_cf.p, s.word_slot.p, U, s.word_count.p,
+    gather_columns_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(s.compact_rec.p, s.word_slot.p, U, s.word_count.p,
                                                                   s.word_first.p);
     k++;
   }
