@@ -61,13 +61,13 @@ HUMID_EXE = os.path.join(ROOT, "humid_b200", "humid")
 
 # stage (humid_gpu_stage_stats) -> the kernel that does its work
 KERNEL_OF = {
-    "sort_words": "radix_pass_kernel<true, ShiftDigit> (1 histogram + 6 digit passes)",
+    "sort_words": "radix_pass_kernel<true, ShiftDigit, unsigned int> (1 histogram + 4 digit passes over 32-bit prefixes)",
     "sort_buckets": "bucket_sort_kernel",
     "join_sort": "radix_pass_kernel<true, ShiftDigit> (1 histogram + 3 digit passes)",
     "table_partition": "radix_pass_kernel<true, PrefixDigit>", "table_insert": "table_insert_kernel",
-    "pack": "pack_words_kernel", "rank_columns": "gather_columns_kernel", "join_hamming_b0": "hamming_join_kernel",
+    "pack": "pack_words_kernel", "rank_columns": "gather_sorted_words_kernel", "join_hamming_b0": "hamming_join_kernel",
     "join_hamming_b1": "hamming_join_kernel", "join_hamming_b2": "hamming_join_kernel", "csr_build": "csr_fill_kernel",
-    "union_find": "uf_union_kernel", "replay_directional": "replay_kernel<false>", "replay_maximum": "replay_kernel<true>",
+    "union_find": "uf_union_pairs_kernel", "replay_directional": "replay_small_kernel", "replay_maximum": "replay_small_kernel",
 }
 
 # kernel family of every stage; the family's algorithmic bytes are a formula of the job's counts
@@ -667,6 +667,9 @@ def run_gpu_arm(args):
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "frac_definition": f"SURVEY 8(d) algorithmic bytes of family {f_name} ({b8d:.0f} B per step) / device time "
                                    f"of stage {name}",
+                "family_frac": (kernels_8d.get(f_name) or {}).get("frac"), "family_ms": (kernels_8d.get(f_name) or {}).get("ms"),
+                "family_frac_definition": "the same bytes / device time of ALL stages of the family (the stricter reading: "
+                                          "the family's bytes are not the dominant stage's alone)",
                 "pass_achieved": pass_achieved, "pass_frac": pass_achieved / peak,
                 "pass_frac_definition": "bytes the stage's launches have to move by the method used (e.g. one read + one "
                                         "write per radix pass) / the same time",
