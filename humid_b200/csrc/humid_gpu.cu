@@ -62,6 +62,12 @@ int humid_gpu_create(const humid_gpu_config *cfg, humid_gpu **out) {
     if (count == 0) throw CudaError{"no CUDA device (there is no CPU fallback)"};
     if (cfg->device >= 0) HUMID_CUDA(cudaSetDevice(cfg->device));
     HUMID_CUDA(cudaGetDevice(&s.device));
+    // HUMID_GPU_L2_FETCH=32|64|128: the device's L2 fetch granularity (cudaLimitMaxL2FetchGranularity), for experiments with
+    // the random-access stages; unset = whatever the context has
+    if (const char *e = std::getenv("HUMID_GPU_L2_FETCH")) {
+      const long v = std::strtol(e, nullptr, 10);
+      if (v == 32 || v == 64 || v == 128) HUMID_CUDA(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)v));
+    }
     HUMID_CUDA(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
     HUMID_CUDA(cudaStreamCreateWithFlags(&s.copy_stream, cudaStreamNonBlocking));
     for (int b = 0; b < 2; b++) {
