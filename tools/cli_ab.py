@@ -23,9 +23,12 @@ def main():
     ap.add_argument("--tuples", type=int, default=4_000_000)
     ap.add_argument("--runs", type=int, default=5)
     ap.add_argument("--config", type=int, default=1)
+    ap.add_argument("--gz", action="store_true", help="gzip -1 copies of the files in, .gz files out")
     ap.add_argument("--ab", default="ingest", choices=["ingest", "rewrite"])
     a = ap.parse_args()
     cfg, files, d, _ = bench.fastq_files(a.config, a.tuples, device="cuda")
+    if a.gz:
+        files, _ = bench.gzip_copies(files, d)
     out = os.path.join(d, "out_ab")
     others = {"rewrite": [("parse_again", dict(HUMID_REWRITE_PARSE="1"))],
               "ingest": [("one_parser_per_file", dict(HUMID_INGEST_THREADS="1")),
