@@ -112,6 +112,7 @@ class ParallelGzReader {
           std::lock_guard<std::mutex> lk(mu_);
           segments_.pop_front();
         }
+        give_back(spare_bytes_, seg->bytes);
         cv_.notify_all();
       }
       if (n) return (long)n;
@@ -189,6 +190,25 @@ class ParallelGzReader {
     error_exit("igzip: encountered while decompressing file: " + path_ + " (" + what + ")");
   }
 
+  // Output buffers are handed round instead of freed and allocated again: tens of megabytes per span going through
+  // mmap / munmap and first-touch page faults hold up everything else in the process that maps memory — the CUDA
+  // context that is coming up beside the readers most of all (0.3 s alone, up to 1.1 s next to eight inflate threads).
+  template <class V>
+  void give_back(std::vector<V> &pool, V &buffer) {
+    if (buffer.capacity() == 0) return;
+    std::lock_guard<std::mutex> lk(pool_mu_);
+    if (pool.size() < 2 * max_ahead_) pool.push_back(std::move(buffer));
+    buffer = V();
+  }
+  template <class V>
+  V take(std::vector<V> &pool) {
+    std::lock_guard<std::mutex> lk(pool_mu_);
+    if (pool.empty()) return V();
+    V v = std::move(pool.back());
+    pool.pop_back();
+    return v;
+  }
+
   static Inflate::Status step(Inflate &inf, const uint8_t *&ip, const uint8_t *end, bool eof, std::vector<uint8_t> &out, uint8_t *&op,
                               const uint8_t *boundary) {
     return inf.run(ip, end, eof, out.data(), op, out.data() + out.size(), boundary);
@@ -255,7 +275,8 @@ class ParallelGzReader {
     in.file_size = file_size_;
     Inflate inf;
     int tries = 0;
-    sp.marked.clear();
+    sp.marked = take(spare_marked_);
+    bool holders = false;
     for (uint64_t bit = 8 * lo; bit < 8 * hi && tries < 6; bit++) {
       if (!in.ok) break;
       if (bit / 8 < in.base || bit / 8 + 1200 > in.base + in.len) {
@@ -265,9 +286,10 @@ class ParallelGzReader {
       if ((size_t)(in.end() - p) < 8) break;  // no block fits any more
       if (!inf.probe_dynamic_header(p, std::min(p + 1100, in.end()), (unsigned)(bit & 7))) continue;
       tries++;
-      if (sp.marked.size() < kHistory) {
-        sp.marked.resize(kHistory + (size_t)(4 * span_) + Inflate::kOutSlack);
+      if (!holders) {
+        if (sp.marked.size() < kHistory + (size_t)(4 * span_) + Inflate::kOutSlack) sp.marked.resize(kHistory + (size_t)(4 * span_) + Inflate::kOutSlack);
         for (size_t i = 0; i < kHistory; i++) sp.marked[i] = (uint16_t)(0x8000u | i);
+        holders = true;
       }
       std::string err;
       if (decode_blocks(in, inf, bit, hi, sp.marked, kHistory, kMaxElements, sp.end_bit, sp.stream_end, sp.n, err) &&
@@ -276,7 +298,7 @@ class ParallelGzReader {
         return;  // (state set by the caller, under the lock)
       }
     }
-    sp.marked = std::vector<uint16_t>();
+    give_back(spare_marked_, sp.marked);
     sp.n = 0;
     sp.start_bit = ~0ull;
   }
@@ -365,14 +387,16 @@ class ParallelGzReader {
   // From pos_bit_ with the real window up to the first block boundary at or behind boundary_off.
   void exact(uint64_t boundary_off) {
     auto seg = std::make_shared<Segment>();
-    seg->bytes.assign(window_.begin(), window_.end());
+    seg->bytes = take(spare_bytes_);
+    if (seg->bytes.size() < window_.size()) seg->bytes.resize(window_.size());
+    std::copy(window_.begin(), window_.end(), seg->bytes.begin());
     seg->begin = window_.size();
     uint64_t end_bit = 0;
     bool stream_end = false;
     std::string err;
     chain_input_.fd = fd_;
     chain_input_.file_size = file_size_;
-    seg->bytes.resize(seg->begin + (size_t)(4 * span_) + Inflate::kOutSlack);
+    if (seg->bytes.size() < seg->begin + (size_t)(4 * span_) + Inflate::kOutSlack) seg->bytes.resize(seg->begin + (size_t)(4 * span_) + Inflate::kOutSlack);
     if (!decode_blocks(chain_input_, chain_inflate_, pos_bit_, boundary_off, seg->bytes, seg->begin, kMaxElements, end_bit, stream_end,
                        seg->n, err)) {
       chain_error("igzip: encountered while decompressing file: " + path_ + " (" + err + ")");
@@ -455,7 +479,7 @@ class ParallelGzReader {
       exact((next_spec_ + 1) * span_);
       if (pos_bit_ != before) redone_++;  // (a block that reaches over the whole span leaves nothing to decode)
     }
-    sp.marked = std::vector<uint16_t>();
+    give_back(spare_marked_, sp.marked);
     if (!finished_ && members == members_started_) {
       if (pos_bit_ >= want) next_spec_++;
       else spec_valid_ = false;
@@ -469,7 +493,8 @@ class ParallelGzReader {
     for (unsigned v = 0; v < 256; v++) lut[v] = (uint8_t)v;
     const size_t gap = kHistory - seg.window.size();
     for (size_t i = gap; i < kHistory; i++) lut[0x8000u + i] = seg.window[i - gap];
-    seg.bytes.resize(seg.n);
+    seg.bytes = take(spare_bytes_);
+    if (seg.bytes.size() < seg.n) seg.bytes.resize(seg.n);
     const uint16_t *from = seg.marked.data() + kHistory;
     uint8_t *to = seg.bytes.data();
     for (size_t i = 0; i < seg.n; i++) to[i] = lut[from[i]];
@@ -480,7 +505,7 @@ class ParallelGzReader {
       seg.crc = crc32(seg.crc, to + done, (uInt)n);
       done += n;
     }
-    seg.marked = std::vector<uint16_t>();
+    give_back(spare_marked_, seg.marked);
     seg.window = std::vector<uint8_t>();
   }
 
@@ -511,7 +536,7 @@ class ParallelGzReader {
         chain_busy_ = false;
         chain_span_locked_ = chain_span();
         for (; freed_ < chain_span_locked_ && freed_ < n_spans_; freed_++)  // speculations the chain has passed
-          if (specs_[freed_].state == Spec::kDone || specs_[freed_].state == Spec::kFailed) specs_[freed_].marked = std::vector<uint16_t>();
+          if (specs_[freed_].state == Spec::kDone || specs_[freed_].state == Spec::kFailed) give_back(spare_marked_, specs_[freed_].marked);
         if (moved) {
           cv_.notify_all();
           continue;
@@ -527,7 +552,7 @@ class ParallelGzReader {
           speculate(j, specs_[j]);
           lk.lock();
           specs_[j].state = specs_[j].start_bit == ~0ull ? Spec::kFailed : Spec::kDone;
-          if (j < freed_) specs_[j].marked = std::vector<uint16_t>();  // too late: the chain has gone past
+          if (j < freed_) give_back(spare_marked_, specs_[j].marked);  // too late: the chain has gone past
           cv_.notify_all();
           continue;
         }
@@ -562,6 +587,10 @@ class ParallelGzReader {
   Input chain_input_;
   Inflate chain_inflate_;
   uint64_t used_ = 0, redone_ = 0;
+
+  std::mutex pool_mu_;
+  std::vector<std::vector<uint16_t>> spare_marked_;
+  std::vector<std::vector<uint8_t>> spare_bytes_;
 
   // the reader
   unsigned long member_crc_ = crc32(0L, Z_NULL, 0);
