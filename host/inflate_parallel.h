@@ -197,7 +197,7 @@ class ParallelGzReader {
   void give_back(std::vector<V> &pool, V &buffer) {
     if (buffer.capacity() == 0) return;
     std::lock_guard<std::mutex> lk(pool_mu_);
-    if (pool.size() < 2 * max_ahead_) pool.push_back(std::move(buffer));
+    if (pool.size() < 2 * max_ahead_ && !no_pool_) pool.push_back(std::move(buffer));
     buffer = V();
   }
   template <class V>
@@ -588,6 +588,7 @@ class ParallelGzReader {
   Inflate chain_inflate_;
   uint64_t used_ = 0, redone_ = 0;
 
+  const bool no_pool_ = std::getenv("HUMID_INFLATE_NO_POOL") != nullptr;  // (comparisons)
   std::mutex pool_mu_;
   std::vector<std::vector<uint16_t>> spare_marked_;
   std::vector<std::vector<uint8_t>> spare_bytes_;

@@ -24,13 +24,15 @@ def main():
     ap.add_argument("--runs", type=int, default=5)
     ap.add_argument("--config", type=int, default=1)
     ap.add_argument("--gz", action="store_true", help="gzip -1 copies of the files in, .gz files out")
-    ap.add_argument("--ab", default="ingest", choices=["ingest", "rewrite"])
+    ap.add_argument("--ab", default="ingest", choices=["ingest", "rewrite", "pool"])
     a = ap.parse_args()
     cfg, files, d, _ = bench.fastq_files(a.config, a.tuples, device="cuda")
     if a.gz:
         files, _ = bench.gzip_copies(files, d)
     out = os.path.join(d, "out_ab")
     others = {"rewrite": [("parse_again", dict(HUMID_REWRITE_PARSE="1"))],
+              "pool": [("inflate_buffers_freed_and_allocated", dict(HUMID_INFLATE_NO_POOL="1")),
+                       ("one_inflate_thread_per_file", dict(HUMID_INFLATE_THREADS="1"))],
               "ingest": [("one_parser_per_file", dict(HUMID_INGEST_THREADS="1")),
                          ("one_parser_per_file_read_in_blocks", dict(HUMID_INGEST_THREADS="1", HUMID_NO_MMAP="1"))]}[a.ab]
     envs = dict(others)
@@ -52,9 +54,10 @@ def main():
                 nm, sep, rest = ln.rpartition(": ")
                 if sep and rest.endswith(" ms"):
                     ph[nm.strip()] = float(rest[:-3]) / 1e3
-            rows[mode].append((total, ph.get("Reading data", 0), ph.get("Writing filtered results", 0), ph.get("humid_gpu_destroy", 0)))
+            rows[mode].append((total, ph.get("Reading data", 0), ph.get("Writing filtered results", 0),
+                               ph.get("humid_gpu_create (CUDA context, beside the readers)", 0)))
     for mode, rr in rows.items():
-        print(mode, "total / reading / writing / destroy (s):")
+        print(mode, "total / reading / writing / context creation (s):")
         for r in rr:
             print("   %.3f  %.3f  %.3f  %.3f" % r)
         med = lambda i: sorted(r[i] for r in rr)[len(rr) // 2]
