@@ -36,11 +36,23 @@
 namespace humid_host {
 
 // Inflate threads of one compressed input (HUMID_INFLATE_THREADS overrides; 1 or 2 = one thread front to back for
-// ordinary members).
+// ordinary members).  Without a hint from the program: min(4, cores / 4).
+inline unsigned &inflate_threads_hint() {
+  static unsigned hint = 0;  // 0: not told how many compressed inputs share the machine
+  return hint;
+}
 inline unsigned default_inflate_threads() {
   if (const char *e = std::getenv("HUMID_INFLATE_THREADS")) return (unsigned)std::max(1, std::atoi(e));
+  if (inflate_threads_hint()) return inflate_threads_hint();
   const unsigned hw = std::thread::hardware_concurrency();
   return std::max(1u, std::min(4u, hw / 4));
+}
+// The program reads n_files inputs side by side: the cores are shared out among them (one parser thread each beside
+// the inflate threads), at most 8 inflate threads per file.
+inline void share_inflate_threads(size_t n_files) {
+  const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+  const unsigned per_file = hw / (unsigned)std::max<size_t>(1, n_files);
+  inflate_threads_hint() = per_file > 2 ? std::min(8u, per_file - 1) : 1u;
 }
 
 // HUMID_INFLATE=zlib: ordinary .gz files through zlib's gzread instead of host/inflate_fast.h (for comparisons).

@@ -457,6 +457,7 @@ int main(int argc, char **argv) {
     }
     vector<std::thread> readers;
     const unsigned parsers = ingest_threads(F);
+    share_inflate_threads(F);
     for (size_t i = 0; i < F; i++) {
       struct stat st;
       const bool big_plain = !ends_with(opt.files[i], ".gz") && stat(opt.files[i].c_str(), &st) == 0 && S_ISREG(st.st_mode) &&

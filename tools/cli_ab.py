@@ -24,13 +24,15 @@ def main():
     ap.add_argument("--runs", type=int, default=5)
     ap.add_argument("--config", type=int, default=1)
     ap.add_argument("--gz", action="store_true", help="gzip -1 copies of the files in, .gz files out")
-    ap.add_argument("--ab", default="ingest", choices=["ingest", "rewrite", "pool"])
+    ap.add_argument("--ab", default="ingest", choices=["ingest", "rewrite", "pool", "inflate"])
     a = ap.parse_args()
     cfg, files, d, _ = bench.fastq_files(a.config, a.tuples, device="cuda")
     if a.gz:
         files, _ = bench.gzip_copies(files, d)
     out = os.path.join(d, "out_ab")
     others = {"rewrite": [("parse_again", dict(HUMID_REWRITE_PARSE="1"))],
+              "inflate": [("four_inflate_threads_per_file", dict(HUMID_INFLATE_THREADS="4")),
+                          ("one_inflate_thread_per_file", dict(HUMID_INFLATE_THREADS="1"))],
               "pool": [("inflate_buffers_freed_and_allocated", dict(HUMID_INFLATE_NO_POOL="1")),
                        ("one_inflate_thread_per_file", dict(HUMID_INFLATE_THREADS="1"))],
               "ingest": [("one_parser_per_file", dict(HUMID_INGEST_THREADS="1")),
