@@ -48,6 +48,3 @@ void group_reset(State &s);
 uint64_t group_result_tuples(const State &s);
 const uint32_t *group_result_ids(const State &s);
 }
-
-// shard.cu: the words' cluster ids of a shard (d_open_ids: ids of the open seeds, every owner's filled in); synchronises
-void shard_word_ids(humid::State &s, const uint32_t *d_open_ids);

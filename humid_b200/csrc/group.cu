@@ -68,12 +68,6 @@ struct GroupLink {
   uint64_t my_res_n = 0;  // tuples of the range this rank holds (keep bits / ids are relative to its start)
   size_t my_bits_bytes = 0;
   bool ids_collected = false;
-  // cluster ids are worked out when somebody asks (humid_gpu_group_collect_ids): what finalize left for that
-  struct {
-    bool pending = false;
-    uint64_t id_off = 0, open_off = 0, n_open = 0;
-    size_t o_ids = 0;
-  } ids_todo;
   struct Batch { uint64_t local, global, n; };  // HUMID_GROUP_BATCHES
   std::vector<Batch> batches;
   std::vector<std::pair<const char *, float>> phases;
@@ -698,16 +692,17 @@ static void group_finalize_body(humid_gpu *h) {
       clusters_total += sh.r[r].slot[5];
     }
     clock.mark("open components clustered");
-    // Cluster ids — of the open seeds (every rank fills in the ones it owns, in every rank's copy) and from them of every
-    // word — are not part of keep bits, counts or histograms: they wait for humid_gpu_group_collect_ids.  The transfer
-    // arena keeps the open components until then (nothing else uses it before the next reset).
-    g.ids_todo.pending = true;
-    g.ids_todo.id_off = id_off;
-    g.ids_todo.open_off = open_off;
-    g.ids_todo.n_open = n_open;
-    g.ids_todo.o_ids = o_ids;
-    ck(humid_gpu_shard_finish(h, nullptr, g.n_total, usable_total, bases[W], clusters_total));
-    clock.mark("counts");
+    // ids of the open seeds: every rank fills in the ones it owns, in every rank's copy
+    ck(humid_gpu_shard_assign_ids(h, id_off, u32(o_ids)));
+    CopyList ids;
+    for (uint32_t p = 0; p < W; p++)
+      if (p != me)
+        ids.add(reinterpret_cast<char *>(g.peer[BUF_XFER][p]) + o_ids + open_off * 4, base + o_ids + open_off * 4, n_open * 4, p);
+    ids.run(s.stream, me, W);
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
+    group_barrier(g);
+    ck(humid_gpu_shard_finish(h, u32(o_ids), g.n_total, usable_total, bases[W], clusters_total));
+    clock.mark("cluster ids");
   }
 
   // ---- outputs: keep bits to the ranks that fed the tuples, histograms merged --------------------------------
@@ -786,22 +781,6 @@ static void group_collect_ids_body(humid_gpu *h) {
   State &s = h->s;
   GroupLink &g = *s.group;
   HUMID_CUDA(cudaSetDevice(s.device));
-  if (g.ids_todo.pending) {  // (every rank: finalize left the same flag everywhere)
-    const uint32_t me = g.rank, W = g.world;
-    char *base = reinterpret_cast<char *>(g.buf[BUF_XFER].p);
-    uint32_t *open_ids = reinterpret_cast<uint32_t *>(base + g.ids_todo.o_ids);
-    if (humid_gpu_shard_assign_ids(h, g.ids_todo.id_off, open_ids) != HUMID_GPU_OK) throw CudaError{s.last_error};
-    CopyList ids;
-    for (uint32_t p = 0; p < W; p++)
-      if (p != me)
-        ids.add(reinterpret_cast<char *>(g.peer[BUF_XFER][p]) + g.ids_todo.o_ids + g.ids_todo.open_off * 4,
-                base + g.ids_todo.o_ids + g.ids_todo.open_off * 4, g.ids_todo.n_open * 4, p);
-    ids.run(s.stream, me, W);
-    HUMID_CUDA(cudaStreamSynchronize(s.stream));
-    group_barrier(g);
-    shard_word_ids(s, open_ids);
-    g.ids_todo.pending = false;
-  }
   // filtered tuples never travelled: their id stays 0
   HUMID_CUDA(cudaMemsetAsync(g.buf[BUF_RESULT].p + g.my_bits_bytes, 0, g.my_res_n * 4, s.stream));
   HUMID_CUDA(cudaStreamSynchronize(s.stream));
@@ -829,7 +808,6 @@ void group_reset(State &s) {
   if (!s.group) return;
   s.group->batches.clear();
   s.group->ids_collected = false;
-  s.group->ids_todo.pending = false;
 }
 uint64_t group_result_tuples(const State &s) { return s.group ? s.group->my_res_n : 0; }
 // cluster ids of the tuples this rank holds results for (device memory), or nullptr before collect_ids

@@ -369,8 +369,6 @@ int humid_gpu_debug_words(humid_gpu *h, uint64_t cap, uint64_t *keys, uint32_t *
   if (cap < s.unique) return fail(h, HUMID_GPU_ERR_ARG, "buffers too small");
   const uint64_t U = s.unique;
   if (U == 0) return HUMID_GPU_OK;
-  if (cluster_ids && s.shard_mode && !s.word_ids_valid)
-    return fail(h, HUMID_GPU_ERR_ARG, "the words' cluster ids of a group are worked out by humid_gpu_group_collect_ids: call it first");
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
     if (keys) HUMID_CUDA(cudaMemcpyAsync(keys, s.word_key.p, U * 8, cudaMemcpyDeviceToHost, s.stream));

@@ -683,25 +683,6 @@ int humid_gpu_shard_assign_ids(humid_gpu *h, uint64_t id_offset, uint32_t *d_ope
   });
 }
 
-}  // extern "C"
-
-// Cluster id of every word of the shard (closed components: numbered here; open ones: the ids their owners assigned).
-void shard_word_ids(State &s, const uint32_t *d_open_ids) {
-  const uint64_t U = s.n_shard_words;
-  s.word_cid.ensure(U + 1);
-  if (U) {
-    Timed t(s, "shard_word_ids", U, U * 20);
-    word_ids_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(U, s.is_open.p, s.open_pos.p, s.open_offset, s.open->label.p,
-                                                            d_open_ids, s.label.p, s.seed_index.p, (uint32_t)s.id_offset,
-                                                            s.word_cid.p);
-  }
-  HUMID_CUDA(cudaGetLastError());
-  HUMID_CUDA(cudaStreamSynchronize(s.stream));
-  s.word_ids_valid = true;
-}
-
-extern "C" {
-
 int humid_gpu_shard_finish(humid_gpu *h, const uint32_t *d_open_ids, uint64_t n_tuples, uint64_t n_usable,
                            uint64_t n_words, uint64_t n_clusters) {
   if (int rc = require_shard(h, true)) return rc;
@@ -710,10 +691,16 @@ int humid_gpu_shard_finish(humid_gpu *h, const uint32_t *d_open_ids, uint64_t n_
   if (n_tuples >= 0xFFFFFFFFull) return fail(h, HUMID_GPU_ERR_UNSUPPORTED, "more than 2^32-2 tuples");
   return guarded(h, [&] {
     HUMID_CUDA(cudaSetDevice(s.device));
-    // d_open_ids == nullptr (groups): the words' cluster ids are only worked out when somebody asks for ids
-    // (shard_word_ids below, from humid_gpu_group_collect_ids)
-    s.word_ids_valid = false;
-    if (d_open_ids) shard_word_ids(s, d_open_ids);
+    const uint64_t U = s.n_shard_words;
+    s.word_cid.ensure(U + 1);
+    if (U) {
+      Timed t(s, "shard_word_ids", U, U * 20);
+      word_ids_kernel<<<grid_for(U, 256), 256, 0, s.stream>>>(U, s.is_open.p, s.open_pos.p, s.open_offset,
+                                                              s.open->label.p, d_open_ids, s.label.p, s.seed_index.p,
+                                                              (uint32_t)s.id_offset, s.word_cid.p);
+    }
+    HUMID_CUDA(cudaGetLastError());
+    HUMID_CUDA(cudaStreamSynchronize(s.stream));
     s.report_tuples = n_tuples;
     s.report_usable = n_usable;
     s.report_unique = n_words;
@@ -745,7 +732,6 @@ int humid_gpu_shard_tuple_ids(humid_gpu *h, uint32_t *d_ids) {
   if (int rc = require_shard(h, true)) return rc;
   State &s = h->s;
   if (!s.finalized) return fail(h, HUMID_GPU_ERR_ARG, "not finalized");
-  if (!s.word_ids_valid) return fail(h, HUMID_GPU_ERR_ARG, "tuple_ids: the words' cluster ids have not been worked out");
   if (s.src_n == 0) return HUMID_GPU_OK;
   if (!d_ids) return HUMID_GPU_ERR_ARG;
   return guarded(h, [&] {

@@ -160,7 +160,6 @@ struct State {
   uint64_t n_open_local = 0, n_open_entries_local = 0, open_offset = 0, n_open_total = 0, id_offset = 0;
   uint64_t report_unique = 0, report_clusters = 0;
   DevBuf<uint32_t> is_open, open_pos, open_ent, open_rank, open_first, seed_first, cluster_first, word_cid;
-  bool word_ids_valid = false;  // word_cid holds this job's ids (groups work them out on demand: shard_word_ids)
   uint32_t cluster_col_base = 0;     // stage_cluster: columns are rank + base
   bool cluster_skip_open = false;    // ... and components with a neighbour outside [0, unique) are left for later
   DevBuf<uint32_t> open_flag, comp_open;
