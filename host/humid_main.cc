@@ -174,6 +174,7 @@ struct Slot {
   size_t done = 0;              // files that have finished it
   vector<size_t> rows;          // records each file contributed (< BATCH only at its end)
   vector<size_t> filled;        // several parser threads per file: rows of the batch written so far
+  bool locked = false;          // page-locked for the uploads (main thread, at first use)
 };
 
 struct Ingest {
@@ -474,12 +475,14 @@ int main(int argc, char **argv) {
       if (creator.joinable()) {  // first batch: the device must be there now
         creator.join();
         if (create_rc != HUMID_GPU_OK) error_exit("humid_gpu_create: " + create_msg);
-        bool locked = true;  // page-locking is an optimisation: without it the uploads are staged by the driver
-        for (int j = 0; j < N_SLOTS; j++) {
-          locked &= humid_gpu_host_register(gpu, g.slots[j].chars, BATCH * g.n) == HUMID_GPU_OK;
-          locked &= humid_gpu_host_register(gpu, g.slots[j].seg_len, BATCH * g.S * sizeof(uint16_t)) == HUMID_GPU_OK;
-        }
-        if (!locked && std::getenv("HUMID_TIMING")) std::cerr << "batch buffers could not be page-locked: " << humid_gpu_last_error(gpu) << "\n";
+      }
+      if (!s.locked) {
+        // page-locked when first used (a small job never touches most of the buffers: 30 MB each, ~0.2 ms per MB to pin);
+        // page-locking is an optimisation: without it the uploads are staged by the driver
+        s.locked = true;
+        const bool ok = humid_gpu_host_register(gpu, s.chars, BATCH * g.n) == HUMID_GPU_OK &&
+                        humid_gpu_host_register(gpu, s.seg_len, BATCH * g.S * sizeof(uint16_t)) == HUMID_GPU_OK;
+        if (!ok && std::getenv("HUMID_TIMING")) std::cerr << "batch buffers could not be page-locked: " << humid_gpu_last_error(gpu) << "\n";
       }
       size_t m = BATCH;
       for (size_t r : s.rows) m = r < m ? r : m;
@@ -496,8 +499,10 @@ int main(int argc, char **argv) {
     for (std::thread &t : readers) t.join();
     maps.swap(g.maps);
     for (int j = 0; j < N_SLOTS; j++) {
-      humid_gpu_host_unregister(gpu, g.slots[j].chars);
-      humid_gpu_host_unregister(gpu, g.slots[j].seg_len);
+      if (g.slots[j].locked) {
+        humid_gpu_host_unregister(gpu, g.slots[j].chars);
+        humid_gpu_host_unregister(gpu, g.slots[j].seg_len);
+      }
       std::free(g.slots[j].chars);
       std::free(g.slots[j].seg_len);
     }
