@@ -232,3 +232,40 @@ def test_parallel_parser_matches_the_sequential_one(checker, tmp_path, case):
         assert (b"different length" in got.stderr) == (b"different length" in ref.stderr), (case, rng_bytes)
         if case == "plain" and rng_bytes == 4096:  # well-formed text: every guess is right
             assert b" reparsed 0" in got.stderr and b"ranges 1 " not in got.stderr, got.stderr
+
+
+def test_parallel_parser_with_misleading_lines(checker, tmp_path):
+    """Quality lines that start with '@' or '+', strand lines that repeat the name, sequences of one letter, records of
+    very different sizes, junk lines between records: whatever a range's guessed first record is ('@' line whose second-next
+    line starts with '+'), the commit only uses a range that was entered where the range before it says the next record starts
+    and parses it again otherwise, so the records are the sequential reader's."""
+    rng = np.random.default_rng(2024)
+    out = []
+    for i in range(6000):
+        L = int(rng.choice([0, 1, 2, 5, 40, 150, 700]))
+        seq = bytes(rng.choice(list(b"ACGTN"), L).tolist())
+        first = rng.choice(list(b"@+IF#"))
+        qual = (bytes([first]) + bytes(rng.choice(list(b"@+IF#:,"), L - 1).tolist())) if L else b""
+        strand = b"+" + (b"r%d" % i if i % 4 == 0 else b"")
+        out.append(b"@r%d extra@+fields\n" % i + seq + b"\n" + strand + b"\n" + qual + b"\n")
+        if i % 97 == 0:
+            out.append(b"+junk line\n\nmore junk @ here\n")  # skipped by the reader (no '@' at a line's start)
+    data = b"".join(out)
+    path = str(tmp_path / "in.fastq")
+    with open(path, "wb") as f:
+        f.write(data)
+    ref = subprocess.run([checker, "hash_seq", path], capture_output=True, check=True)
+    assert ref.stdout.count(b"\n") > 100
+    for rng_bytes, threads in ((200, 4), (1000, 3), (4096, 6), (50_000, 2)):
+        got = subprocess.run([checker, "hash_par", path, str(threads)], capture_output=True, check=True,
+                             env=dict(os.environ, HUMID_INGEST_RANGE=str(rng_bytes)))
+        assert got.stdout == ref.stdout, rng_bytes
+        assert (b"different length" in got.stderr) == (b"different length" in ref.stderr)
+    # '\r' line ends leave nothing to guess from (no '\n'): every range is parsed in its turn, same records
+    cr = str(tmp_path / "cr.fastq")
+    with open(cr, "wb") as f:
+        f.write(data.replace(b"\n", b"\r"))
+    ref = subprocess.run([checker, "hash_seq", cr], capture_output=True, check=True)
+    got = subprocess.run([checker, "hash_par", cr, "4"], capture_output=True, check=True, env=dict(os.environ, HUMID_INGEST_RANGE="3000"))
+    assert got.stdout == ref.stdout
+    assert int(got.stderr.split(b" reparsed ")[1].split()[0]) > 0
